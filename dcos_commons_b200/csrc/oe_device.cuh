@@ -1,0 +1,420 @@
+// oe_device.cuh — device-side views of the encoded tables and the per-(offer, class) stage/rule evaluation.
+//
+// The evaluation below is the engine's own formulation of the reference pipeline, NOT a transliteration: placement
+// tallies come from per-key counter arrays reduced once per cycle (K0) instead of re-walking every task for every
+// offer, the pool is a register/local copy of one SoA offer row, and the rule tree is a postfix program over a
+// bit-stack.  Semantics followed (S/ = sdk/scheduler/src/main/java/com/mesosphere/sdk/, P/ = S/offer/evaluate/placement/):
+//   S/offer/MesosResourcePool.java:61-70,282-372   sufficientValue / consumeAtomic / consumeReservableMerged
+//   S/offer/ValueUtils.java:103-106,144-155        fp64 subtract + compare (no FMA, no reassociation)
+//   S/offer/evaluate/PortEvaluationStage.java:72-155,242-298
+//   P/MaxPerRule.java:52-87, P/AbstractRoundRobinRule.java:53-151, P/TaskTypeRule.java:98-217
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/oe_abi.h"
+
+namespace oe {
+
+struct DevOffers {
+  int64_t N;
+  int64_t row_offset;
+  int S, K, R, D, A, Q, E;
+  const double* scalar;
+  const uint32_t* present;
+  const uint32_t* port;
+  const double* msize;
+  const int32_t* mprof;
+  const int32_t* alloc;
+  const int32_t* agent;
+  const int32_t* host;
+  const int32_t* zone;
+  const int32_t* region;
+  const int32_t* attr;
+  const int32_t* rr;
+  const int32_t* exec;
+  const int64_t* rbegin;  // may be null
+  const int32_t* rid;
+  const int32_t* rkind;
+  const double* rval;
+};
+
+struct DevTasks {
+  int64_t T;
+  int64_t cap;  // column stride (rows allocated)
+  int TA, Q, FW;
+  int32_t* name;
+  int32_t* type;
+  int32_t* index;
+  int32_t* agent;
+  int32_t* host;
+  int32_t* zone;
+  int32_t* region;
+  int32_t* attr;    // [TA][cap]
+  int32_t* rr;      // [Q][cap]
+  uint32_t* filter; // [FW][cap]
+};
+
+struct DevProg {
+  int C;
+  int n_csets, n_tsets;
+  int n_agents;
+  const int32_t* op_begin;
+  const oe_stage_op* ops;
+  const oe_rule_node* nodes;
+  const int32_t* pod_role;
+  const int32_t* excl_begin;
+  const uint16_t* excl;
+  const int32_t* rs_begin;
+  const uint32_t* rs;
+  const oe_counter_set* csets;
+  const int64_t* cs_off;  // [n_csets+1] offsets into cnt
+  const int32_t* ts_type;
+  const uint32_t* mbits;
+};
+
+// K0 outputs
+struct DevCounters {
+  const int32_t* cnt;        // concatenated per-counter-set tallies
+  const int4* rrsum;         // [n_csets] {min over keys with cnt>0 (0 if none), max, #keys with cnt>0, 0}
+  const int32_t* type_total; // [n_tsets]
+  const int32_t* type_agent; // [n_tsets][n_agents]
+};
+
+// Requirements whose deployed "self" tasks (S/offer/TaskUtils.java:136-145) change the tallies they see.
+struct DevVariants {
+  int V;
+  const int32_t* cls;        // [V]
+  const int32_t* self_begin; // [V+1]
+  const int32_t* self_rows;  // task rows
+  const int4* rrsum;         // [V][n_csets] round-robin summary with the self rows taken out
+};
+
+struct DevCtx {
+  DevOffers o;
+  DevTasks t;
+  DevProg p;
+  DevCounters c;
+  DevVariants v;
+};
+
+__device__ __forceinline__ bool mbit(const uint32_t* __restrict__ bits, int32_t off, int32_t v) {
+  return v >= 0 && ((__ldg(bits + off + (v >> 5)) >> (v & 31)) & 1u);
+}
+
+__device__ __forceinline__ bool task_filter(const DevTasks& t, int32_t row, int f) {
+  return (t.filter[(int64_t)(f >> 5) * t.cap + row] >> (f & 31)) & 1u;
+}
+
+// How many times key `k` occurs among the keys of the variant's self rows that pass the counter set's filter.
+__device__ inline int self_key_count(const DevCtx& cx, int var, const oe_counter_set& cs, int32_t k) {
+  int n = 0;
+  for (int s = cx.v.self_begin[var]; s < cx.v.self_begin[var + 1]; ++s) {
+    int32_t row = cx.v.self_rows[s];
+    if (!task_filter(cx.t, row, cs.filter_id)) continue;
+    switch (cs.keyspace) {
+      case OE_KS_HOSTNAME: n += cx.t.host[row] == k; break;
+      case OE_KS_ZONE: n += cx.t.zone[row] == k; break;
+      case OE_KS_REGION: n += cx.t.region[row] == k; break;
+      case OE_KS_ATTR:
+        for (int a = 0; a < cx.t.TA; ++a) n += cx.t.attr[(int64_t)a * cx.t.cap + row] == k;
+        break;
+      case OE_KS_RR_ATTR: n += cx.t.rr[(int64_t)cs.rr_col * cx.t.cap + row] == k; break;
+    }
+  }
+  return n;
+}
+
+__device__ inline int self_type_on_agent(const DevCtx& cx, int var, int32_t pod_type, int32_t agent) {
+  int n = 0;
+  for (int s = cx.v.self_begin[var]; s < cx.v.self_begin[var + 1]; ++s) {
+    int32_t row = cx.v.self_rows[s];
+    n += (cx.t.type[row] == pod_type) && (cx.t.agent[row] == agent);
+  }
+  return n;
+}
+
+// Placement columns of one offer row, loaded once per thread.
+struct OfferKeys {
+  int32_t agent, host, zone, region;
+};
+
+// Postfix rule program over a bit-stack (bit 0 = top).
+__device__ inline bool eval_rule(const DevCtx& cx, int64_t i, const OfferKeys& ok, int var, int32_t begin, int32_t count) {
+  uint64_t st = 0;
+  const DevOffers& o = cx.o;
+  for (int32_t n = begin; n < begin + count; ++n) {
+    const oe_rule_node nd = cx.p.nodes[n];
+    bool v = false;
+    switch (nd.op) {
+      case OE_R_TRUE: v = true; break;
+      case OE_R_FALSE: v = false; break;
+      case OE_R_AND: {
+        uint64_t m = nd.a >= 64 ? ~0ull : ((1ull << nd.a) - 1);
+        v = nd.a > 0 && (st & m) == m;
+        st = nd.a >= 64 ? 0 : st >> nd.a;
+      } break;
+      case OE_R_OR: {
+        uint64_t m = nd.a >= 64 ? ~0ull : ((1ull << nd.a) - 1);
+        v = (st & m) != 0;
+        st = nd.a >= 64 ? 0 : st >> nd.a;
+      } break;
+      case OE_R_NOT: v = !(st & 1); st >>= 1; break;
+      case OE_R_AGENT_EQ: v = ok.agent == nd.a; break;
+      case OE_R_ATTR_ANY:
+        for (int a = 0; a < o.A; ++a) v = v || mbit(cx.p.mbits, nd.a, __ldg(o.attr + (int64_t)a * o.N + i));
+        break;
+      case OE_R_HOST_IN: v = mbit(cx.p.mbits, nd.a, ok.host); break;
+      case OE_R_ZONE_IN: v = mbit(cx.p.mbits, nd.a, ok.zone); break;
+      case OE_R_REGION_IN: v = mbit(cx.p.mbits, nd.a, ok.region); break;
+      case OE_R_LOCAL_REGION: v = ok.region < 0 || nd.b == 0 || ok.region == nd.a; break;
+      case OE_R_MAXPER_HOST:
+      case OE_R_MAXPER_ZONE:
+      case OE_R_MAXPER_REGION: {
+        const oe_counter_set cs = cx.p.csets[nd.a];
+        int32_t k = nd.op == OE_R_MAXPER_HOST ? ok.host : (nd.op == OE_R_MAXPER_ZONE ? ok.zone : ok.region);
+        if (k < 0) {
+          v = nd.op != OE_R_MAXPER_ZONE;  // no key: zone rule fails outright, the others have nothing to exceed
+        } else {
+          int c = 1 + __ldg(cx.c.cnt + cx.p.cs_off[nd.a] + k);
+          if (var >= 0) c -= self_key_count(cx, var, cs, k);
+          v = c <= nd.b;
+        }
+      } break;
+      case OE_R_MAXPER_ATTR: {
+        const oe_counter_set cs = cx.p.csets[nd.a];
+        v = true;
+        for (int a = 0; a < o.A; ++a) {
+          int32_t k = __ldg(o.attr + (int64_t)a * o.N + i);
+          if (!mbit(cx.p.mbits, nd.c, k)) continue;
+          int mult = 0;  // duplicate attribute strings in one offer start the tally above 1 (P/MaxPerRule.java:81-86)
+          for (int b = 0; b < o.A; ++b) mult += __ldg(o.attr + (int64_t)b * o.N + i) == k;
+          int c = mult + __ldg(cx.c.cnt + cx.p.cs_off[nd.a] + k);
+          if (var >= 0) c -= self_key_count(cx, var, cs, k);
+          v = v && c <= nd.b;
+        }
+      } break;
+      case OE_R_RR: {
+        const oe_counter_set cs = cx.p.csets[nd.a];
+        int32_t k;
+        switch (cs.keyspace) {
+          case OE_KS_HOSTNAME: k = ok.host; break;
+          case OE_KS_ZONE: k = ok.zone; break;
+          case OE_KS_REGION: k = ok.region; break;
+          case OE_KS_RR_ATTR: k = __ldg(o.rr + (int64_t)cs.rr_col * o.N + i); break;
+          default: k = -1;
+        }
+        if (k < 0) { v = false; break; }
+        int oc = __ldg(cx.c.cnt + cx.p.cs_off[nd.a] + k);
+        int4 sum;
+        if (var >= 0) {
+          oc -= self_key_count(cx, var, cs, k);
+          sum = cx.v.rrsum[(int64_t)var * cx.p.n_csets + nd.a];
+        } else {
+          sum = cx.c.rrsum[nd.a];
+        }
+        if (sum.x == sum.y || oc <= sum.x) {
+          v = nd.b < 0 || sum.z >= nd.b || oc == 0;
+        } else {
+          v = false;
+        }
+      } break;
+      case OE_R_TYPE_AVOID:
+      case OE_R_TYPE_COLOCATE: {
+        if (cx.c.type_total[nd.a] == 0) { v = true; break; }
+        int on = __ldg(cx.c.type_agent + (int64_t)nd.a * cx.p.n_agents + ok.agent);
+        if (var >= 0) on -= self_type_on_agent(cx, var, cx.p.ts_type[nd.a], ok.agent);
+        v = nd.op == OE_R_TYPE_AVOID ? on == 0 : on > 0;
+      } break;
+      default: v = false;
+    }
+    st = (st << 1) | (v ? 1ull : 0ull);
+  }
+  return (st & 1) != 0;
+}
+
+#define OE_DEV_MAX_TAKEN 24  // host ports a single pipeline can take (static + dynamic); checked at load
+
+// Mutable view of one offer's pool while one class's pipeline runs over it.
+struct PairState {
+  double val[OE_MAX_ROLE_SLOTS * OE_MAX_SCALAR_KINDS];
+  uint32_t present;
+  uint32_t mounts_used;
+  // host ports already placed in the pod by earlier stages.  Entries without OE_KEPT were also removed from the
+  // pool; entries with it are re-used reservations that never were in the pool.
+  uint32_t taken[OE_DEV_MAX_TAKEN];
+  int n_taken;
+};
+#define OE_KEPT 0x10000u
+
+__device__ __forceinline__ bool port_in_pool(const DevOffers& o, int64_t i, int slot, int nr, int p) {
+  for (int r = 0; r < nr; ++r) {
+    uint32_t pr = __ldg(o.port + ((int64_t)slot * o.R + r) * o.N + i);
+    int b = pr & 0xFFFF, e = pr >> 16;
+    if (b <= p && p <= e) return true;
+  }
+  return false;
+}
+
+// removed from the pool by an earlier stage
+__device__ __forceinline__ bool port_taken(const PairState& ps, int p) {
+  bool t = false;
+  for (int q = 0; q < ps.n_taken; ++q) t = t || ps.taken[q] == (uint32_t)p;
+  return t;
+}
+// present in the pod's builders (PortEvaluationStage.java:264-269)
+__device__ __forceinline__ bool port_placed(const PairState& ps, int p) {
+  bool t = false;
+  for (int q = 0; q < ps.n_taken; ++q) t = t || (ps.taken[q] & 0xFFFFu) == (uint32_t)p;
+  return t;
+}
+
+// Lowest port of the slot's ranges that is neither taken by an earlier stage of this pipeline, nor declared
+// statically anywhere in the pod, and (when constrained) lies inside the range set.  -1 = none.
+__device__ inline int pick_dynamic_port(const DevCtx& cx, int64_t i, int cls, int slot, int nr, int32_t rset, const PairState& ps) {
+  const DevOffers& o = cx.o;
+  const int eb = cx.p.excl_begin[cls], ee = cx.p.excl_begin[cls + 1];
+  for (int r = 0; r < nr; ++r) {
+    uint32_t pr = __ldg(o.port + ((int64_t)slot * o.R + r) * o.N + i);
+    int b = pr & 0xFFFF, e = pr >> 16;
+    int p = b;
+    while (p <= e) {
+      bool blocked = port_placed(ps, p);
+      for (int q = eb; q < ee && !blocked; ++q) blocked = cx.p.excl[q] == p;
+      if (blocked) { ++p; continue; }
+      if (rset >= 0) {
+        bool in = false;
+        int next = 0x7fffffff;
+        for (int q = cx.p.rs_begin[rset]; q < cx.p.rs_begin[rset + 1]; ++q) {
+          uint32_t rr = cx.p.rs[q];
+          int rb = rr & 0xFFFF, re = rr >> 16;
+          if (rb <= p && p <= re) in = true;
+          else if (rb > p && rb < next) next = rb;
+        }
+        if (!in) { p = next; continue; }  // jump to the next constrained range (or past the end)
+      }
+      return p;
+    }
+  }
+  return -1;
+}
+
+__device__ __forceinline__ bool offer_has_exec(const DevOffers& o, int64_t i, int32_t id) {
+  bool h = false;
+  for (int e = 0; e < o.E; ++e) h = h || __ldg(o.exec + (int64_t)e * o.N + i) == id;
+  return h;
+}
+
+// Runs the stage program of class `cls` over offer row i.  Returns true iff every stage passes.  With RECORD the
+// choices the host needs to materialise the winner (dynamic ports, MOUNT slots, new reservation count) are written.
+template <bool RECORD>
+__device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& ok, int cls, int var, oe_decision* dec) {
+  const DevOffers& o = cx.o;
+  PairState ps;
+  const int SK = o.S * o.K;
+  // consumableResource (MesosResourcePool.java:87-97): an offer allocated to another role contributes nothing
+  const int32_t pod_role = cx.p.pod_role[cls];
+  const int32_t alloc = __ldg(o.alloc + i);
+  const bool consumable = !(pod_role >= 0 && alloc >= 0 && alloc != pod_role);
+  ps.present = consumable ? __ldg(o.present + i) : 0u;
+  for (int q = 0; q < SK; ++q) ps.val[q] = __ldg(o.scalar + (int64_t)q * o.N + i);
+  ps.mounts_used = 0;
+  ps.n_taken = 0;
+  const int nr = consumable ? o.R : 0;
+  const int nd = consumable ? o.D : 0;
+  int n_dyn = 0, n_mount = 0, n_res = 0;
+  bool all = true;
+
+  const int ob = cx.p.op_begin[cls], oe_ = cx.p.op_begin[cls + 1];
+  for (int x = ob; x < oe_; ++x) {
+    const oe_stage_op op = cx.p.ops[x];
+    bool pass = true;
+    if ((op.flags & OE_OPF_SKIP_IF_RUNNING_EXECUTOR) && offer_has_exec(o, i, (int32_t)op.aux)) continue;
+    switch (op.opcode) {
+      case OE_OP_NOP: break;
+      case OE_OP_EXEC_ID: pass = op.arg < 0 || offer_has_exec(o, i, op.arg); break;
+      case OE_OP_RULE: pass = eval_rule(cx, i, ok, var, op.arg, (int32_t)op.aux); break;
+      case OE_OP_SCALAR_NEW: {
+        const int q = op.slot * o.K + op.kind;
+        const double avail = ps.val[q];
+        const double diff = __dsub_rn(op.amount, avail);
+        pass = ((ps.present >> q) & 1u) && !(diff > 0.0);
+        if (pass) { ps.val[q] = __dsub_rn(avail, op.amount); ++n_res; }
+      } break;
+      case OE_OP_PORT_STATIC: {
+        pass = port_in_pool(o, i, op.slot, nr, op.arg) && !port_taken(ps, op.arg);
+        if (pass) { ps.taken[ps.n_taken++] = (uint32_t)op.arg; ++n_res; }
+      } break;
+      case OE_OP_PORT_DYNAMIC: {
+        int p = pick_dynamic_port(cx, i, cls, op.slot, nr, op.arg, ps);
+        pass = p >= 0;
+        if (pass) {
+          ps.taken[ps.n_taken++] = (uint32_t)p;
+          ++n_res;
+          if (RECORD && n_dyn < OE_MAX_DYN_PORTS) dec->dyn_port[n_dyn] = (uint16_t)p;
+        }
+        ++n_dyn;
+      } break;
+      case OE_OP_VOL_MOUNT: {
+        int chosen = -1;
+        for (int d = 0; d < nd; ++d) {
+          if ((ps.mounts_used >> d) & 1u) continue;
+          const double size = __ldg(o.msize + (int64_t)d * o.N + i);
+          const int32_t prof = __ldg(o.mprof + (int64_t)d * o.N + i);
+          const bool prof_ok = prof >= 0 ? ((op.mask >> prof) & 1ull) != 0 : op.mask == 0;
+          if (!(__dsub_rn(op.amount, size) > 0.0) && prof_ok) { chosen = d; break; }
+        }
+        pass = chosen >= 0;
+        if (pass) {
+          ps.mounts_used |= 1u << chosen;
+          ++n_res;
+          if (RECORD && n_mount < OE_MAX_MOUNT_OPS) dec->mount_slot[n_mount] = (int8_t)chosen;
+        }
+        ++n_mount;
+      } break;
+      case OE_OP_SCALAR_RESERVED:
+      case OE_OP_PORT_RESERVED:
+      case OE_OP_MOUNT_RESERVED: {
+        // precondition (checked by the host encoder): one resource id is named by at most one op of a class
+        double reserved = 0.0;
+        bool found = false;
+        if (consumable && o.rbegin) {
+          for (int64_t q = o.rbegin[i]; q < o.rbegin[i + 1]; ++q)
+            if (o.rid[q] == op.arg) { found = true; reserved = o.rval[q]; }
+        }
+        if (!found) { pass = false; break; }
+        if (op.opcode == OE_OP_MOUNT_RESERVED) break;
+        if (op.opcode == OE_OP_PORT_RESERVED) {
+          const int want = (int)op.aux;
+          if ((int)reserved != want) {
+            pass = port_in_pool(o, i, op.slot, nr, want) && !port_taken(ps, want);
+            if (pass) ps.taken[ps.n_taken++] = (uint32_t)want;
+          } else {
+            ps.taken[ps.n_taken++] = (uint32_t)want | OE_KEPT;
+          }
+          break;
+        }
+        if (reserved == op.amount) break;
+        const double diff = __dsub_rn(op.amount, reserved);
+        if (diff > 0.0) {
+          const int q = op.slot * o.K + op.kind;
+          const double avail = ps.val[q];
+          pass = ((ps.present >> q) & 1u) && !(__dsub_rn(diff, avail) > 0.0);
+          if (pass) ps.val[q] = __dsub_rn(avail, diff);
+        }
+      } break;
+      case OE_OP_FREE: {  // scalar only (ports / MOUNT frees are rejected at load)
+        const int q = op.slot * o.K + op.kind;
+        const double cur = ((ps.present >> q) & 1u) ? ps.val[q] : 0.0;
+        ps.val[q] = __dadd_rn(cur, op.amount);
+        ps.present |= 1u << q;
+      } break;
+      default: pass = false;
+    }
+    if (!pass) { all = false; break; }  // failed stages never deduct and the verdict is the AND of all stages
+  }
+  if (RECORD) dec->n_new_reservations = n_res;
+  return all;
+}
+
+}  // namespace oe

@@ -1,0 +1,1193 @@
+// oe_engine.cu — B200 (sm_100a) offer-evaluation engine: kernels + the C ABI of include/oe_abi.h.
+//
+// Kernels (all integer / fp64 compare-and-mask work, HBM- or latency-bound; no tensor cores by design):
+//   K0  k_count_tasks / k_rr_summary    task table → per-key tallies that the placement rules read
+//   K1  k_class_feasibility             offers × requirement classes → class-factored feasibility bits
+//   K1x k_expand_matrix                 class bits → full offers × requirements bit matrix (the HBM-bound pass)
+//   K2  k_commit                        ordered greedy first-fit over the class bits (one warp, shared-memory bitmap)
+//   K2b k_materialize                   winners → chosen dynamic ports / MOUNT slots
+//   K3  k_apply_launches                multi-cycle replay: placed pods → task rows
+//
+// There is no CPU fallback: every entry point needs a CUDA device and fails with an oe_status otherwise.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "oe_device.cuh"
+
+using namespace oe;
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Kernels
+// ---------------------------------------------------------------------------------------------------------------------
+
+// Flags ids outside their dictionary so that later gathers cannot fault.  err[0] receives a non-zero code.
+__global__ void k_validate_ids(const int32_t* __restrict__ col, int64_t n, int32_t lo, int32_t hi, int code, int* err) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    int32_t v = col[i];
+    if (v < lo || v >= hi) atomicMax(err, code);
+  }
+}
+
+// K0: one thread per deployed task; every counter set whose filter the task passes gets the task's keys tallied.
+__global__ void k_count_tasks(DevTasks t, DevProg p, int32_t* __restrict__ cnt, int32_t* __restrict__ type_total,
+                              int32_t* __restrict__ type_agent) {
+  int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= t.T) return;
+  for (int c = 0; c < p.n_csets; ++c) {
+    const oe_counter_set cs = p.csets[c];
+    if (!task_filter(t, (int32_t)row, cs.filter_id)) continue;
+    int32_t* base = cnt + p.cs_off[c];
+    switch (cs.keyspace) {
+      case OE_KS_HOSTNAME: { int32_t k = t.host[row]; if (k >= 0) atomicAdd(base + k, 1); } break;
+      case OE_KS_ZONE: { int32_t k = t.zone[row]; if (k >= 0) atomicAdd(base + k, 1); } break;
+      case OE_KS_REGION: { int32_t k = t.region[row]; if (k >= 0) atomicAdd(base + k, 1); } break;
+      case OE_KS_ATTR:
+        for (int a = 0; a < t.TA; ++a) { int32_t k = t.attr[(int64_t)a * t.cap + row]; if (k >= 0) atomicAdd(base + k, 1); }
+        break;
+      case OE_KS_RR_ATTR: { int32_t k = t.rr[(int64_t)cs.rr_col * t.cap + row]; if (k >= 0) atomicAdd(base + k, 1); } break;
+    }
+  }
+  const int32_t ty = t.type[row];
+  for (int s = 0; s < p.n_tsets; ++s) {
+    if (p.ts_type[s] != ty) continue;
+    atomicAdd(type_total + s, 1);
+    atomicAdd(type_agent + (int64_t)s * p.n_agents + t.agent[row], 1);
+  }
+}
+
+// K0b: per counter set (blockIdx.x) and, for blockIdx.y > 0, per variant y-1 with that variant's self rows taken out:
+// {min over keys with a tally, max, number of keys with a tally}.  One CTA strides over the key space.
+__global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __restrict__ cnt, int4* __restrict__ out_base,
+                                                    int4* __restrict__ out_var) {
+  const int c = blockIdx.x;
+  const int var = (int)blockIdx.y - 1;
+  const oe_counter_set cs = cx.p.csets[c];
+  const int64_t n = cx.p.cs_off[c + 1] - cx.p.cs_off[c];
+  const int32_t* base = cnt + cx.p.cs_off[c];
+  int mn = 0x7fffffff, mx = 0, nk = 0;
+  for (int64_t k = threadIdx.x; k < n; k += blockDim.x) {
+    int v = base[k];
+    if (var >= 0 && v > 0) v -= self_key_count(cx, var, cs, (int32_t)k);
+    if (v > 0) { mn = min(mn, v); mx = max(mx, v); ++nk; }
+  }
+  __shared__ int smn[256], smx[256], snk[256];
+  smn[threadIdx.x] = mn; smx[threadIdx.x] = mx; snk[threadIdx.x] = nk;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      smn[threadIdx.x] = min(smn[threadIdx.x], smn[threadIdx.x + s]);
+      smx[threadIdx.x] = max(smx[threadIdx.x], smx[threadIdx.x + s]);
+      snk[threadIdx.x] += snk[threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    int4 r = make_int4(smn[0] == 0x7fffffff ? 0 : smn[0], smx[0], snk[0], 0);
+    if (var < 0) out_base[c] = r;
+    else out_var[(int64_t)var * cx.p.n_csets + c] = r;
+  }
+}
+
+// K1: thread = one offer row, blockIdx.y = a tile of factored rows (classes first, then variants).  Each warp emits
+// one 32-offer word per row with __ballot_sync.  gridDim.x covers the padded stride so every word is written.
+#define OE_K1_THREADS 128
+__global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, uint32_t* __restrict__ F, int64_t stride,
+                                                                     int rows, int rows_per_tile) {
+  const int64_t i = (int64_t)blockIdx.x * OE_K1_THREADS + threadIdx.x;
+  const bool valid = i < cx.o.N;
+  OfferKeys ok{0, 0, -1, -1};
+  if (valid) {
+    ok.agent = __ldg(cx.o.agent + i);
+    ok.host = __ldg(cx.o.host + i);
+    ok.zone = __ldg(cx.o.zone + i);
+    ok.region = __ldg(cx.o.region + i);
+  }
+  const int r0 = blockIdx.y * rows_per_tile;
+  const int r1 = min(rows, r0 + rows_per_tile);
+  const int64_t word = i >> 5;
+  for (int row = r0; row < r1; ++row) {
+    const int var = row < cx.p.C ? -1 : row - cx.p.C;
+    const int cls = var < 0 ? row : cx.v.cls[var];
+    bool pass = false;
+    if (valid) pass = eval_pair<false>(cx, i, ok, cls, var, nullptr);
+    const uint32_t bits = __ballot_sync(0xffffffffu, pass);
+    if ((threadIdx.x & 31) == 0 && word < stride) F[(int64_t)row * stride + word] = bits;
+  }
+}
+
+// K1x: out[j][w] = F[req_row[j]][w].  A warp moves one 512-byte row segment (uint4 per lane) per requirement; the
+// source rows of one word tile stay L1/L2 resident, the 128-bit streaming stores are the only HBM traffic.
+#define OE_KX_THREADS 256
+__global__ void __launch_bounds__(OE_KX_THREADS) k_expand_matrix(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row,
+                                                                 uint32_t* __restrict__ out, int64_t stride, int64_t M,
+                                                                 int reqs_per_block) {
+  const int64_t w4 = ((int64_t)blockIdx.x * OE_KX_THREADS + threadIdx.x) * 4;  // first word of this lane's uint4
+  if (w4 >= stride) return;
+  const int64_t j0 = (int64_t)blockIdx.y * reqs_per_block;
+  const int64_t j1 = min(M, j0 + reqs_per_block);
+  int64_t j = j0;
+  for (; j + 4 <= j1; j += 4) {
+    const int32_t ra = __ldg(req_row + j), rb = __ldg(req_row + j + 1), rc = __ldg(req_row + j + 2), rd = __ldg(req_row + j + 3);
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)ra * stride + w4));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rb * stride + w4));
+    const uint4 c = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rc * stride + w4));
+    const uint4 d = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rd * stride + w4));
+    __stcs(reinterpret_cast<uint4*>(out + (j + 0) * stride + w4), a);
+    __stcs(reinterpret_cast<uint4*>(out + (j + 1) * stride + w4), b);
+    __stcs(reinterpret_cast<uint4*>(out + (j + 2) * stride + w4), c);
+    __stcs(reinterpret_cast<uint4*>(out + (j + 3) * stride + w4), d);
+  }
+  for (; j < j1; ++j) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)__ldg(req_row + j) * stride + w4));
+    __stcs(reinterpret_cast<uint4*>(out + j * stride + w4), a);
+  }
+}
+
+// K2: the greedy commit of PlanScheduler.resourceOffers.  Requirements are taken in order; each claims the lowest
+// offer whose bit is set in its factored row and that no earlier requirement claimed.  Because the claimed set only
+// grows and the rows are frozen within a cycle, each row keeps a cursor that never moves backwards, so the total scan
+// work is O(rows * N/32 + M) instead of O(M * N/32).  One warp; `used` bitmap, cursors and a direct-mapped cache of
+// 32-word row windows live in shared memory when they fit.
+struct CommitArgs {
+  const uint32_t* F;
+  int64_t stride;        // words per (shard, row)
+  int rows;
+  int64_t shard_words;   // words of one shard in global word index space (== stride when not sharded)
+  int64_t total_words;   // global words to scan
+  const int32_t* req_row;
+  int64_t M;
+  oe_decision* dec;
+  uint32_t* used_g;      // global-memory fallbacks (used when the shared-memory budget is exceeded)
+  int32_t* cursor_g;
+  int used_in_smem, cursor_in_smem;
+  int* n_placed;
+};
+#define OE_WIN_SLOTS 128
+
+__global__ void __launch_bounds__(256) k_commit(CommitArgs a) {
+  extern __shared__ uint32_t smem[];
+  uint32_t* win = smem;                                   // [OE_WIN_SLOTS][32]
+  int32_t* win_row = (int32_t*)(win + OE_WIN_SLOTS * 32); // [OE_WIN_SLOTS]
+  int64_t* win_base = (int64_t*)(win_row + OE_WIN_SLOTS); // [OE_WIN_SLOTS]
+  uint32_t* p = (uint32_t*)(win_base + OE_WIN_SLOTS);
+  int32_t* cursor = a.cursor_g;
+  if (a.cursor_in_smem) { cursor = (int32_t*)p; p += a.rows; }
+  uint32_t* used = a.used_in_smem ? p : a.used_g;
+
+  for (int64_t k = threadIdx.x; k < a.total_words; k += blockDim.x) used[k] = 0;
+  for (int k = threadIdx.x; k < a.rows; k += blockDim.x) cursor[k] = 0;
+  for (int k = threadIdx.x; k < OE_WIN_SLOTS; k += blockDim.x) { win_row[k] = -1; win_base[k] = 0; }
+  __syncthreads();
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  int placed = 0;
+
+  for (int64_t j0 = 0; j0 < a.M; j0 += 32) {
+    const int32_t my_row = (j0 + lane < a.M) ? a.req_row[j0 + lane] : 0;
+    const int nj = (int)min((int64_t)32, a.M - j0);
+    for (int jj = 0; jj < nj; ++jj) {
+      const int row = __shfl_sync(0xffffffffu, my_row, jj);
+      const int slot = row & (OE_WIN_SLOTS - 1);
+      int64_t cur = cursor[row];
+      int64_t found = -1;
+      while (cur < a.total_words) {
+        // window of 32 consecutive words of this row starting at `cur` (cached when the cursor did not leave it)
+        const bool hit = win_row[slot] == row && win_base[slot] == cur;
+        const int64_t gw = cur + lane;
+        uint32_t f;
+        if (hit) {
+          f = win[slot * 32 + lane];
+        } else {
+          f = 0;
+          if (gw < a.total_words) {
+            const int64_t shard = gw / a.shard_words, lw = gw - shard * a.shard_words;
+            f = a.F[(shard * a.rows + row) * a.stride + lw];
+          }
+          __syncwarp();
+          win[slot * 32 + lane] = f;
+          if (lane == 0) { win_row[slot] = row; win_base[slot] = cur; }
+        }
+        const uint32_t w = (gw < a.total_words) ? (f & ~used[gw]) : 0u;
+        const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
+        if (m) {
+          const int L = __ffs(m) - 1;
+          const uint32_t wl = __shfl_sync(0xffffffffu, w, L);
+          const int b = __ffs(wl) - 1;
+          found = (cur + L) * 32 + b;
+          if (lane == L) used[gw] |= 1u << b;
+          break;  // cursor stays on this window: lower words of it are exhausted for good, `used` masks the rest
+        }
+        cur += 32;
+        __syncwarp();
+      }
+      if (lane == 0) {
+        cursor[row] = (int32_t)min(cur, a.total_words);
+        a.dec[j0 + jj].offer_row = (int32_t)found;
+      }
+      placed += found >= 0;
+      __syncwarp();
+    }
+  }
+  if (lane == 0) *a.n_placed = placed;
+}
+
+// K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
+__global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  oe_decision d = dec[j];
+  d.n_new_reservations = 0;
+  for (int q = 0; q < OE_MAX_DYN_PORTS; ++q) d.dyn_port[q] = 0;
+  for (int q = 0; q < OE_MAX_MOUNT_OPS; ++q) d.mount_slot[q] = -1;
+  d.reserved0 = 0;
+  const int64_t i = (int64_t)d.offer_row - cx.o.row_offset;
+  if (d.offer_row >= 0 && i >= 0 && i < cx.o.N) {
+    const int row = req_row[j];
+    const int var = row < cx.p.C ? -1 : row - cx.p.C;
+    const int cls = var < 0 ? row : cx.v.cls[var];
+    OfferKeys ok{cx.o.agent[i], cx.o.host[i], cx.o.zone[i], cx.o.region[i]};
+    const bool pass = eval_pair<true>(cx, i, ok, cls, var, &d);
+    if (!pass) d.reserved0 = 0xDEADu;  // cannot happen: the commit only picks offers whose bit is set
+  }
+  dec[j] = d;
+}
+
+// K3: multi-cycle replay.  One thread per stored task: copies the winning offer's placement columns into a task row.
+struct LaunchArgs {
+  int64_t n;
+  const int32_t* dst_row;   // task row to (over)write
+  const int32_t* req;       // requirement that placed it
+  const int32_t* name_id;
+  const uint32_t* filter;   // [n][FW]
+  const int32_t* req_type;
+  const int32_t* req_index;
+};
+__global__ void k_apply_launches(LaunchArgs a, DevOffers o, DevTasks t, const oe_decision* __restrict__ dec) {
+  const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= a.n) return;
+  const int32_t j = a.req[x];
+  const int64_t i = (int64_t)dec[j].offer_row - o.row_offset;
+  const int64_t r = a.dst_row[x];
+  t.name[r] = a.name_id[x];
+  t.type[r] = a.req_type[j];
+  t.index[r] = a.req_index[j];
+  t.agent[r] = o.agent[i];
+  t.host[r] = o.host[i];
+  t.zone[r] = o.zone[i];
+  t.region[r] = o.region[i];
+  for (int q = 0; q < t.TA; ++q) t.attr[(int64_t)q * t.cap + r] = q < o.A ? o.attr[(int64_t)q * o.N + i] : -1;
+  for (int q = 0; q < t.Q; ++q) t.rr[(int64_t)q * t.cap + r] = o.rr[(int64_t)q * o.N + i];
+  for (int q = 0; q < t.FW; ++q) t.filter[(int64_t)q * t.cap + r] = a.filter[x * t.FW + q];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+}  // namespace
+
+struct oe_engine {
+  int device = 0, rank = 0, world = 1;
+  uint32_t flags = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::string err;
+  int smem_optin = 0;
+
+  // ---- programs (host copies kept for validation, variant detection and launch bookkeeping)
+  bool hasP = false, hasT = false, hasO = false, hasR = false;
+  oe_dict_sizes dict{};
+  int C = 0, n_csets = 0, n_tsets = 0;
+  std::vector<int32_t> h_op_begin;
+  std::vector<oe_stage_op> h_ops;
+  std::vector<oe_rule_node> h_nodes;
+  std::vector<oe_counter_set> h_csets;
+  std::vector<int64_t> h_cs_off;
+  std::vector<uint8_t> class_self_sensitive;
+  DevBuf d_op_begin, d_ops, d_nodes, d_pod_role, d_excl_begin, d_excl, d_rs_begin, d_rs, d_csets, d_cs_off, d_ts_type, d_mbits;
+  DevProg dp{};
+
+  // ---- tasks
+  DevTasks dt{};
+  DevBuf d_tcols[7], d_tattr, d_trr, d_tfilter;
+  std::vector<int32_t> h_tname, h_ttype, h_tindex;  // host mirror of what apply_launches / self detection need
+  std::unordered_map<int32_t, int32_t> name_to_row;
+
+  // ---- offers
+  DevOffers dof{};
+  int64_t N = 0, N_global = 0, row_offset = 0, shard_rows = 0;
+  DevBuf d_scalar, d_present, d_port, d_msize, d_mprof, d_ocols[5], d_oattr, d_orr, d_oexec, d_rbegin, d_rid, d_rkind, d_rval;
+
+  // ---- requirements
+  int64_t M = 0;
+  int V = 0;
+  std::vector<int32_t> h_class, h_rtype, h_rindex, h_req_row;
+  std::vector<int32_t> h_launch_begin, h_launch_name;
+  std::vector<uint32_t> h_launch_filter;
+  DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
+
+  // ---- derived / outputs
+  DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced;
+  DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter;
+  bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
+  std::vector<oe_decision> h_last_dec;
+  cudaEvent_t ev[8]{};
+
+  int fail(int code, const char* fmt, ...) {
+    char buf[768];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    err = buf;
+    return code;
+  }
+  int cuda_fail(cudaError_t e, const char* what) {
+    return fail(OE_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  }
+  int64_t stride() const {
+    const int64_t rows = (world > 1 && shard_rows > 0) ? shard_rows : N;
+    return std::max<int64_t>(128, round_up((rows + 31) / 32, 128));
+  }
+  int rows_factored() const { return C + V; }
+  DevCtx ctx() const {
+    DevCtx cx;
+    cx.o = dof; cx.t = dt; cx.p = dp;
+    cx.c.cnt = d_cnt.as<int32_t>(); cx.c.rrsum = d_rrsum.as<int4>();
+    cx.c.type_total = d_type_total.as<int32_t>(); cx.c.type_agent = d_type_agent.as<int32_t>();
+    cx.v.V = V; cx.v.cls = d_vcls.as<int32_t>(); cx.v.self_begin = d_vself_begin.as<int32_t>();
+    cx.v.self_rows = d_vself_rows.as<int32_t>(); cx.v.rrsum = d_vrrsum.as<int4>();
+    return cx;
+  }
+};
+
+#define CU(call)                                                   \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return h->cuda_fail(e__, #call);       \
+  } while (0)
+
+namespace {
+
+template <class T>
+int upload(oe_engine* h, DevBuf& b, const T* src, size_t n) {
+  CU(b.ensure(std::max<size_t>(n, 1) * sizeof(T)));
+  if (n) CU(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+  return 0;
+}
+
+int check_ids(oe_engine* h, const int32_t* dcol, int64_t n, int32_t lo, int32_t hi, int code) {
+  if (n <= 0) return 0;
+  k_validate_ids<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(dcol, n, lo, hi, code, h->d_err.as<int>());
+  return 0;
+}
+
+int fetch_err_flag(oe_engine* h, const char* what) {
+  int flag = 0;
+  CU(cudaMemcpyAsync(&flag, h->d_err.p, sizeof flag, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (flag) {
+    CU(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
+    return h->fail(OE_ERR_INVALID, "%s: id column %d holds a value outside its dictionary", what, flag);
+  }
+  return 0;
+}
+
+int keyspace_size(const oe_dict_sizes& d, int ks) {
+  switch (ks) {
+    case OE_KS_HOSTNAME: return d.n_hostnames;
+    case OE_KS_ZONE: return d.n_zones;
+    case OE_KS_REGION: return d.n_regions;
+    case OE_KS_ATTR: return d.n_attrs;
+    case OE_KS_RR_ATTR: return d.n_rr_values;
+  }
+  return -1;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t oe_abi_version(void) { return OE_ABI_VERSION; }
+
+const char* oe_last_error(const oe_engine* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int32_t oe_create(const oe_config* cfg, oe_engine** out) {
+  if (!cfg || !out) { g_create_error = "oe_create: null argument"; return OE_ERR_INVALID; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("oe_create: no CUDA device (") + cudaGetErrorString(e) + "); this engine has no CPU path";
+    return OE_ERR_NO_DEVICE;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "oe_create: device ordinal out of range"; return OE_ERR_INVALID; }
+  if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) { g_create_error = "oe_create: bad rank/world"; return OE_ERR_INVALID; }
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, cfg->device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OE_ERR_CUDA; }
+  if (prop.major != 10) {
+    char b[160];
+    snprintf(b, sizeof b, "oe_create: device %d is sm_%d%d; this build carries sm_100a code only", cfg->device, prop.major, prop.minor);
+    g_create_error = b;
+    return OE_ERR_NO_DEVICE;
+  }
+  if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return OE_ERR_CUDA; }
+  oe_engine* h = new oe_engine();
+  h->device = cfg->device; h->rank = cfg->rank; h->world = cfg->world; h->flags = cfg->flags;
+  h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  if (cfg->stream) {
+    h->stream = (cudaStream_t)cfg->stream;
+  } else {
+    if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+      g_create_error = cudaGetErrorString(e); delete h; return OE_ERR_CUDA;
+    }
+    h->own_stream = true;
+  }
+  for (auto& ev : h->ev) cudaEventCreate(&ev);
+  if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
+    g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
+  }
+  cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream);
+  cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin);
+  *out = h;
+  return OE_OK;
+}
+
+void oe_destroy(oe_engine* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  DevBuf* all[] = {&h->d_op_begin, &h->d_ops, &h->d_nodes, &h->d_pod_role, &h->d_excl_begin, &h->d_excl, &h->d_rs_begin, &h->d_rs,
+                   &h->d_csets, &h->d_cs_off, &h->d_ts_type, &h->d_mbits, &h->d_tattr, &h->d_trr, &h->d_tfilter, &h->d_scalar,
+                   &h->d_present, &h->d_port, &h->d_msize, &h->d_mprof, &h->d_oattr, &h->d_orr, &h->d_oexec, &h->d_rbegin, &h->d_rid,
+                   &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
+                   &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
+                   &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter};
+  for (auto* b : all) b->release();
+  for (auto& b : h->d_tcols) b.release();
+  for (auto& b : h->d_ocols) b.release();
+  for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+  if (h->own_stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+void* oe_stream(oe_engine* h) { return h ? (void*)h->stream : nullptr; }
+
+int64_t oe_matrix_stride_words(const oe_engine* h) { return h ? h->stride() : 0; }
+
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Loading
+// ---------------------------------------------------------------------------------------------------------------------
+int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
+  if (!h || !t) return OE_ERR_INVALID;
+  CU(cudaSetDevice(h->device));
+  h->hasP = h->hasT = h->hasO = h->hasR = false;
+  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  const int C = t->n_classes;
+  if (C < 0 || C > OE_MAX_CLASSES) return h->fail(OE_ERR_LIMIT, "n_classes %d exceeds OE_MAX_CLASSES", C);
+  if (!t->op_begin || (t->n_ops && !t->ops) || !t->pod_role || !t->port_excl_begin)
+    return h->fail(OE_ERR_INVALID, "oe_load_programs: missing column");
+  const oe_dict_sizes& d = t->dict;
+  if (d.n_agents < 0 || d.n_hostnames < 0 || d.n_zones < 0 || d.n_regions < 0 || d.n_attrs < 0 || d.n_rr_values < 0 ||
+      d.n_pod_types < 0 || d.n_filters < 0)
+    return h->fail(OE_ERR_INVALID, "oe_load_programs: negative dictionary size");
+  if (t->op_begin[0] != 0 || t->op_begin[C] != t->n_ops) return h->fail(OE_ERR_INVALID, "op_begin does not span ops");
+  if (t->n_counter_sets < 0 || t->n_type_sets < 0 || t->n_range_sets < 0 || t->n_rule_nodes < 0 || t->n_matcher_words < 0)
+    return h->fail(OE_ERR_INVALID, "oe_load_programs: negative count");
+  auto words_for = [](int n) { return (int64_t)((n + 31) / 32); };
+  auto matcher_ok = [&](int32_t off, int n_values) { return off >= 0 && off + words_for(n_values) <= t->n_matcher_words; };
+
+  // counter sets → offsets into one tally array
+  h->h_csets.assign(t->counter_sets, t->counter_sets + t->n_counter_sets);
+  h->h_cs_off.assign((size_t)t->n_counter_sets + 1, 0);
+  for (int c = 0; c < t->n_counter_sets; ++c) {
+    const oe_counter_set& cs = t->counter_sets[c];
+    int n = keyspace_size(d, cs.keyspace);
+    if (n < 0) return h->fail(OE_ERR_INVALID, "counter set %d: unknown key space %d", c, cs.keyspace);
+    if (cs.filter_id < 0 || cs.filter_id >= std::max(d.n_filters, 1)) return h->fail(OE_ERR_INVALID, "counter set %d: filter id out of range", c);
+    if (cs.keyspace == OE_KS_RR_ATTR && (cs.rr_col < 0 || cs.rr_col >= OE_MAX_RR_COLS)) return h->fail(OE_ERR_INVALID, "counter set %d: rr column", c);
+    h->h_cs_off[c + 1] = h->h_cs_off[c] + n;
+  }
+  for (int s = 0; s < t->n_type_sets; ++s)
+    if (t->type_set_pod_type[s] < 0 || t->type_set_pod_type[s] >= d.n_pod_types) return h->fail(OE_ERR_INVALID, "type set %d: pod type out of range", s);
+
+  // rule programs: node fields + postfix stack discipline
+  h->class_self_sensitive.assign((size_t)C, 0);
+  for (int c = 0; c < C; ++c) {
+    const int ob = t->op_begin[c], oe_ = t->op_begin[c + 1];
+    if (oe_ < ob || oe_ - ob > OE_MAX_STAGE_OPS) return h->fail(OE_ERR_LIMIT, "class %d: %d stage ops (max %d)", c, oe_ - ob, OE_MAX_STAGE_OPS);
+    if (t->pod_role[c] < -1) return h->fail(OE_ERR_INVALID, "class %d: pod_role", c);
+    if (t->port_excl_begin[c + 1] < t->port_excl_begin[c]) return h->fail(OE_ERR_INVALID, "class %d: port_excl_begin not monotone", c);
+    int n_port_ops = 0;
+    for (int x = ob; x < oe_; ++x) {
+      const oe_stage_op& op = t->ops[x];
+      if (op.opcode >= OE_OP__COUNT) return h->fail(OE_ERR_INVALID, "class %d op %d: unknown opcode %d", c, x - ob, op.opcode);
+      const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
+      const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
+      if (slotted && op.slot >= OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_INVALID, "class %d op %d: role slot %d", c, x - ob, op.slot);
+      if (op.opcode == OE_OP_FREE && op.kind >= OE_MAX_SCALAR_KINDS)
+        return h->fail(OE_ERR_LIMIT, "class %d op %d: OE_OP_FREE of ports / MOUNT disks is not supported by this engine build", c, x - ob);
+      if (scalar_like && op.kind >= OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_INVALID, "class %d op %d: scalar kind %d", c, x - ob, op.kind);
+      if (op.opcode == OE_OP_PORT_STATIC && (op.arg < 0 || op.arg > 65535)) return h->fail(OE_ERR_INVALID, "class %d op %d: port %d", c, x - ob, op.arg);
+      if (op.opcode == OE_OP_PORT_RESERVED && op.aux > 65535) return h->fail(OE_ERR_INVALID, "class %d op %d: port", c, x - ob);
+      if (op.opcode == OE_OP_PORT_DYNAMIC && (op.arg < -1 || op.arg >= t->n_range_sets)) return h->fail(OE_ERR_INVALID, "class %d op %d: range set %d", c, x - ob, op.arg);
+      if (op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED) ++n_port_ops;
+      if (op.opcode == OE_OP_RULE) {
+        const int32_t nb = op.arg, nc = (int32_t)op.aux;
+        if (nb < 0 || nc < 1 || nc > OE_MAX_RULE_NODES || (int64_t)nb + nc > t->n_rule_nodes) return h->fail(OE_ERR_INVALID, "class %d: rule program range", c);
+        int depth = 0;
+        for (int n = nb; n < nb + nc; ++n) {
+          const oe_rule_node& nd = t->rule_nodes[n];
+          switch (nd.op) {
+            case OE_R_TRUE: case OE_R_FALSE: break;
+            case OE_R_AND: case OE_R_OR:
+              if (nd.a < 0 || nd.a > depth) return h->fail(OE_ERR_INVALID, "class %d rule node %d: child count %d exceeds stack %d", c, n - nb, nd.a, depth);
+              depth -= nd.a; break;
+            case OE_R_NOT: if (depth < 1) return h->fail(OE_ERR_INVALID, "class %d rule node %d: NOT on empty stack", c, n - nb); depth -= 1; break;
+            case OE_R_AGENT_EQ: break;
+            case OE_R_ATTR_ANY: if (!matcher_ok(nd.a, d.n_attrs)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb); break;
+            case OE_R_HOST_IN: if (!matcher_ok(nd.a, d.n_hostnames)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb); break;
+            case OE_R_ZONE_IN: if (!matcher_ok(nd.a, d.n_zones)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb); break;
+            case OE_R_REGION_IN: if (!matcher_ok(nd.a, d.n_regions)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb); break;
+            case OE_R_LOCAL_REGION: break;
+            case OE_R_MAXPER_HOST: case OE_R_MAXPER_ZONE: case OE_R_MAXPER_REGION: case OE_R_MAXPER_ATTR: case OE_R_RR: {
+              if (nd.a < 0 || nd.a >= t->n_counter_sets) return h->fail(OE_ERR_INVALID, "class %d rule node %d: counter set %d", c, n - nb, nd.a);
+              const int ks = t->counter_sets[nd.a].keyspace;
+              const int want = nd.op == OE_R_MAXPER_HOST ? OE_KS_HOSTNAME : nd.op == OE_R_MAXPER_ZONE ? OE_KS_ZONE
+                             : nd.op == OE_R_MAXPER_REGION ? OE_KS_REGION : nd.op == OE_R_MAXPER_ATTR ? OE_KS_ATTR : -1;
+              if (want >= 0 && ks != want) return h->fail(OE_ERR_INVALID, "class %d rule node %d: counter set key space %d does not fit the rule", c, n - nb, ks);
+              if (nd.op == OE_R_RR && ks == OE_KS_ATTR) return h->fail(OE_ERR_INVALID, "class %d rule node %d: round robin over the multi-key space", c, n - nb);
+              if (nd.op == OE_R_MAXPER_ATTR && !matcher_ok(nd.c, d.n_attrs)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb);
+              h->class_self_sensitive[c] = 1;
+            } break;
+            case OE_R_TYPE_AVOID: case OE_R_TYPE_COLOCATE:
+              if (nd.a < 0 || nd.a >= t->n_type_sets) return h->fail(OE_ERR_INVALID, "class %d rule node %d: type set %d", c, n - nb, nd.a);
+              h->class_self_sensitive[c] = 1;
+              break;
+            default: return h->fail(OE_ERR_INVALID, "class %d rule node %d: unknown op %d", c, n - nb, nd.op);
+          }
+          if (++depth > 64) return h->fail(OE_ERR_LIMIT, "class %d: rule stack deeper than 64", c);
+        }
+        if (depth < 1) return h->fail(OE_ERR_INVALID, "class %d: rule program leaves an empty stack", c);
+      }
+    }
+    if (n_port_ops > OE_DEV_MAX_TAKEN) return h->fail(OE_ERR_LIMIT, "class %d: %d host-port stages (max %d)", c, n_port_ops, OE_DEV_MAX_TAKEN);
+  }
+  for (int r = 0; r < t->n_range_sets; ++r)
+    if (t->range_set_begin[r + 1] < t->range_set_begin[r]) return h->fail(OE_ERR_INVALID, "range_set_begin not monotone");
+
+  h->dict = d;
+  h->C = C; h->n_csets = t->n_counter_sets; h->n_tsets = t->n_type_sets;
+  h->h_op_begin.assign(t->op_begin, t->op_begin + C + 1);
+  h->h_ops.assign(t->ops, t->ops + t->n_ops);
+  h->h_nodes.assign(t->rule_nodes, t->rule_nodes + t->n_rule_nodes);
+
+  if (int rc = upload(h, h->d_op_begin, t->op_begin, (size_t)C + 1)) return rc;
+  if (int rc = upload(h, h->d_ops, t->ops, (size_t)t->n_ops)) return rc;
+  if (int rc = upload(h, h->d_nodes, t->rule_nodes, (size_t)t->n_rule_nodes)) return rc;
+  if (int rc = upload(h, h->d_pod_role, t->pod_role, (size_t)C)) return rc;
+  if (int rc = upload(h, h->d_excl_begin, t->port_excl_begin, (size_t)C + 1)) return rc;
+  if (int rc = upload(h, h->d_excl, t->port_excl, (size_t)t->port_excl_begin[C])) return rc;
+  static const int32_t zero_begin[1] = {0};
+  if (int rc = upload(h, h->d_rs_begin, t->n_range_sets ? t->range_set_begin : zero_begin, (size_t)t->n_range_sets + 1)) return rc;
+  if (int rc = upload(h, h->d_rs, t->range_set, t->n_range_sets ? (size_t)t->range_set_begin[t->n_range_sets] : 0)) return rc;
+  if (int rc = upload(h, h->d_csets, t->counter_sets, (size_t)t->n_counter_sets)) return rc;
+  if (int rc = upload(h, h->d_cs_off, h->h_cs_off.data(), h->h_cs_off.size())) return rc;
+  if (int rc = upload(h, h->d_ts_type, t->type_set_pod_type, (size_t)t->n_type_sets)) return rc;
+  if (int rc = upload(h, h->d_mbits, t->matcher_bits, (size_t)t->n_matcher_words)) return rc;
+
+  CU(h->d_cnt.ensure(std::max<size_t>((size_t)h->h_cs_off.back(), 1) * 4));
+  CU(h->d_rrsum.ensure(std::max<size_t>((size_t)h->n_csets, 1) * sizeof(int4)));
+  CU(h->d_type_total.ensure(std::max<size_t>((size_t)h->n_tsets, 1) * 4));
+  CU(h->d_type_agent.ensure(std::max<size_t>((size_t)h->n_tsets * std::max(d.n_agents, 1), 1) * 4));
+
+  DevProg& p = h->dp;
+  p.C = C; p.n_csets = h->n_csets; p.n_tsets = h->n_tsets; p.n_agents = std::max(d.n_agents, 1);
+  p.op_begin = h->d_op_begin.as<int32_t>(); p.ops = h->d_ops.as<oe_stage_op>(); p.nodes = h->d_nodes.as<oe_rule_node>();
+  p.pod_role = h->d_pod_role.as<int32_t>(); p.excl_begin = h->d_excl_begin.as<int32_t>(); p.excl = h->d_excl.as<uint16_t>();
+  p.rs_begin = h->d_rs_begin.as<int32_t>(); p.rs = h->d_rs.as<uint32_t>(); p.csets = h->d_csets.as<oe_counter_set>();
+  p.cs_off = h->d_cs_off.as<int64_t>(); p.ts_type = h->d_ts_type.as<int32_t>(); p.mbits = h->d_mbits.as<uint32_t>();
+  CU(cudaStreamSynchronize(h->stream));  // the caller may free its buffers after return
+  h->hasP = true;
+  return OE_OK;
+}
+
+namespace {
+// Grows the device task columns to `cap` rows, keeping the first `keep` rows.
+int reserve_tasks(oe_engine* h, int64_t cap, int64_t keep) {
+  DevTasks& t = h->dt;
+  if (cap <= t.cap) return 0;
+  cap = cap + cap / 4 + 64;
+  auto grow = [&](DevBuf& b, int slots, void** field) -> int {
+    DevBuf nb;
+    CU(nb.ensure((size_t)cap * slots * 4));
+    for (int s = 0; s < slots && keep > 0; ++s)
+      CU(cudaMemcpyAsync((char*)nb.p + (size_t)s * cap * 4, (char*)b.p + (size_t)s * t.cap * 4, (size_t)keep * 4, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    b.release();
+    b = nb;
+    *field = b.p;
+    return 0;
+  };
+  void** fields[7] = {(void**)&t.name, (void**)&t.type, (void**)&t.index, (void**)&t.agent, (void**)&t.host, (void**)&t.zone, (void**)&t.region};
+  for (int c = 0; c < 7; ++c) if (int rc = grow(h->d_tcols[c], 1, fields[c])) return rc;
+  if (int rc = grow(h->d_tattr, std::max(t.TA, 1), (void**)&t.attr)) return rc;
+  if (int rc = grow(h->d_trr, std::max(t.Q, 1), (void**)&t.rr)) return rc;
+  if (int rc = grow(h->d_tfilter, std::max(t.FW, 1), (void**)&t.filter)) return rc;
+  t.cap = cap;
+  return 0;
+}
+}  // namespace
+
+int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
+  if (!h || !t) return OE_ERR_INVALID;
+  if (!h->hasP) return h->fail(OE_ERR_STATE, "oe_load_tasks: load programs first");
+  CU(cudaSetDevice(h->device));
+  h->hasT = h->hasR = false;
+  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  const int64_t T = t->n_tasks;
+  if (T < 0 || T > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_tasks");
+  if (t->n_attr_slots < 0 || t->n_attr_slots > OE_MAX_ATTR_SLOTS) return h->fail(OE_ERR_LIMIT, "task attr slots");
+  if (t->n_rr_cols < 0 || t->n_rr_cols > OE_MAX_RR_COLS) return h->fail(OE_ERR_LIMIT, "task rr cols");
+  if (t->n_filter_words < (h->dict.n_filters + 31) / 32) return h->fail(OE_ERR_INVALID, "n_filter_words too small for n_filters");
+  for (auto& cs : h->h_csets)
+    if (cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= t->n_rr_cols) return h->fail(OE_ERR_INVALID, "a counter set names rr column %d, task table has %d", cs.rr_col, t->n_rr_cols);
+  if (T > 0 && (!t->name_id || !t->pod_type_id || !t->pod_index || !t->agent_id || !t->hostname_id || !t->zone_id || !t->region_id ||
+                (t->n_attr_slots && !t->attr_id) || (t->n_rr_cols && !t->rr_key) || (t->n_filter_words && !t->filter_bits)))
+    return h->fail(OE_ERR_INVALID, "oe_load_tasks: missing column");
+  DevTasks& d = h->dt;
+  // a change of column widths invalidates the old layout
+  if (d.TA != t->n_attr_slots || d.Q != t->n_rr_cols || d.FW != t->n_filter_words) {
+    d.cap = 0; d.TA = t->n_attr_slots; d.Q = t->n_rr_cols; d.FW = t->n_filter_words;
+  }
+  d.T = 0;
+  if (int rc = reserve_tasks(h, std::max<int64_t>(T, 1), 0)) return rc;
+  const int32_t* cols[7] = {t->name_id, t->pod_type_id, t->pod_index, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
+  int32_t* dst[7] = {d.name, d.type, d.index, d.agent, d.host, d.zone, d.region};
+  if (T > 0) {
+    for (int c = 0; c < 7; ++c) CU(cudaMemcpyAsync(dst[c], cols[c], (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    for (int a = 0; a < d.TA; ++a) CU(cudaMemcpyAsync(d.attr + (size_t)a * d.cap, t->attr_id + (size_t)a * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    for (int q = 0; q < d.Q; ++q) CU(cudaMemcpyAsync(d.rr + (size_t)q * d.cap, t->rr_key + (size_t)q * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    for (int w = 0; w < d.FW; ++w) CU(cudaMemcpyAsync(d.filter + (size_t)w * d.cap, t->filter_bits + (size_t)w * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+  }
+  d.T = T;
+  const oe_dict_sizes& dc = h->dict;
+  check_ids(h, d.type, T, -1, dc.n_pod_types, 1);
+  check_ids(h, d.agent, T, 0, std::max(dc.n_agents, 1), 2);
+  check_ids(h, d.host, T, -1, dc.n_hostnames, 3);
+  check_ids(h, d.zone, T, -1, dc.n_zones, 4);
+  check_ids(h, d.region, T, -1, dc.n_regions, 5);
+  for (int a = 0; a < d.TA; ++a) check_ids(h, d.attr + (size_t)a * d.cap, T, -1, dc.n_attrs, 6);
+  for (int q = 0; q < d.Q; ++q) check_ids(h, d.rr + (size_t)q * d.cap, T, -1, dc.n_rr_values, 7);
+  h->h_tname.assign(t->name_id, t->name_id + T);
+  h->h_ttype.assign(t->pod_type_id, t->pod_type_id + T);
+  h->h_tindex.assign(t->pod_index, t->pod_index + T);
+  h->name_to_row.clear();
+  for (int64_t r = 0; r < T; ++r) h->name_to_row[h->h_tname[r]] = (int32_t)r;
+  if (int rc = fetch_err_flag(h, "oe_load_tasks")) return rc;
+  h->hasT = true;
+  return OE_OK;
+}
+
+int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
+  if (!h || !t) return OE_ERR_INVALID;
+  if (!h->hasP) return h->fail(OE_ERR_STATE, "oe_load_offers: load programs first");
+  CU(cudaSetDevice(h->device));
+  h->hasO = false;
+  h->class_bits_fresh = h->cycle_done = false;
+  const int64_t N = t->n_offers;
+  if (N < 0 || N > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_offers");
+  if (t->n_role_slots < 1 || t->n_role_slots > OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_LIMIT, "n_role_slots %d", t->n_role_slots);
+  if (t->n_scalar_kinds < 1 || t->n_scalar_kinds > OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_LIMIT, "n_scalar_kinds %d", t->n_scalar_kinds);
+  if (t->n_role_slots * t->n_scalar_kinds > 32) return h->fail(OE_ERR_LIMIT, "role slots x scalar kinds exceeds the 32-bit presence mask");
+  if (t->n_port_ranges < 0 || t->n_port_ranges > OE_MAX_PORT_RANGES) return h->fail(OE_ERR_LIMIT, "n_port_ranges %d", t->n_port_ranges);
+  if (t->n_mount_slots < 0 || t->n_mount_slots > OE_MAX_MOUNT_SLOTS) return h->fail(OE_ERR_LIMIT, "n_mount_slots %d", t->n_mount_slots);
+  if (t->n_attr_slots < 0 || t->n_attr_slots > OE_MAX_ATTR_SLOTS) return h->fail(OE_ERR_LIMIT, "n_attr_slots %d", t->n_attr_slots);
+  if (t->n_rr_cols < 0 || t->n_rr_cols > OE_MAX_RR_COLS) return h->fail(OE_ERR_LIMIT, "n_rr_cols %d", t->n_rr_cols);
+  if (t->n_exec_slots < 0 || t->n_exec_slots > OE_MAX_EXEC_SLOTS) return h->fail(OE_ERR_LIMIT, "n_exec_slots %d", t->n_exec_slots);
+  for (auto& op : h->h_ops) {
+    const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
+    const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
+    if (slotted && op.slot >= t->n_role_slots) return h->fail(OE_ERR_INVALID, "a stage op names role slot %d, offer table has %d", op.slot, t->n_role_slots);
+    if (scalar_like && op.kind >= t->n_scalar_kinds) return h->fail(OE_ERR_INVALID, "a stage op names scalar kind %d, offer table has %d", op.kind, t->n_scalar_kinds);
+  }
+  for (auto& cs : h->h_csets)
+    if (cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= t->n_rr_cols) return h->fail(OE_ERR_INVALID, "a counter set names rr column %d, offer table has %d", cs.rr_col, t->n_rr_cols);
+  if (h->world > 1) {
+    if (t->shard_rows <= 0 || t->shard_rows % 1024 != 0) return h->fail(OE_ERR_INVALID, "sharded offer table needs shard_rows, a multiple of 1024");
+    if (t->row_offset != (int64_t)h->rank * t->shard_rows) return h->fail(OE_ERR_INVALID, "row_offset must be rank * shard_rows");
+    if (N > t->shard_rows) return h->fail(OE_ERR_INVALID, "shard holds more than shard_rows offers");
+  } else if (t->row_offset != 0) {
+    return h->fail(OE_ERR_INVALID, "row_offset must be 0 when not sharded");
+  }
+  if (N > 0 && (!t->scalar || !t->scalar_present || !t->alloc_role || !t->agent_id || !t->hostname_id || !t->zone_id || !t->region_id ||
+                (t->n_port_ranges && !t->port_range) || (t->n_mount_slots && (!t->mount_size || !t->mount_profile)) ||
+                (t->n_attr_slots && !t->attr_id) || (t->n_rr_cols && !t->rr_key) || (t->n_exec_slots && !t->exec_id)))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers: missing column");
+  if (t->n_reserved < 0 || (t->n_reserved > 0 && (!t->reserved_begin || !t->reserved_id || !t->reserved_kind || !t->reserved_value)))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers: reserved side table");
+  if (t->n_reserved > 0) {
+    if (t->reserved_begin[0] != 0 || t->reserved_begin[N] != t->n_reserved) return h->fail(OE_ERR_INVALID, "reserved_begin does not span the side table");
+    for (int64_t i = 0; i < N; ++i)
+      if (t->reserved_begin[i + 1] < t->reserved_begin[i]) return h->fail(OE_ERR_INVALID, "reserved_begin not monotone");
+  }
+
+  DevOffers& o = h->dof;
+  o.N = N; o.row_offset = t->row_offset;
+  o.S = t->n_role_slots; o.K = t->n_scalar_kinds; o.R = t->n_port_ranges; o.D = t->n_mount_slots;
+  o.A = t->n_attr_slots; o.Q = t->n_rr_cols; o.E = t->n_exec_slots;
+  h->N = N; h->row_offset = t->row_offset; h->shard_rows = t->shard_rows;
+  h->N_global = t->n_offers_global > 0 ? t->n_offers_global : N;
+  const size_t n = (size_t)N;
+  if (int rc = upload(h, h->d_scalar, t->scalar, n * o.S * o.K)) return rc;
+  if (int rc = upload(h, h->d_present, t->scalar_present, n)) return rc;
+  if (int rc = upload(h, h->d_port, t->port_range, n * o.S * o.R)) return rc;
+  if (int rc = upload(h, h->d_msize, t->mount_size, n * o.D)) return rc;
+  if (int rc = upload(h, h->d_mprof, t->mount_profile, n * o.D)) return rc;
+  const int32_t* cols[5] = {t->alloc_role, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
+  for (int c = 0; c < 5; ++c) if (int rc = upload(h, h->d_ocols[c], cols[c], n)) return rc;
+  if (int rc = upload(h, h->d_oattr, t->attr_id, n * o.A)) return rc;
+  if (int rc = upload(h, h->d_orr, t->rr_key, n * o.Q)) return rc;
+  if (int rc = upload(h, h->d_oexec, t->exec_id, n * o.E)) return rc;
+  o.scalar = h->d_scalar.as<double>(); o.present = h->d_present.as<uint32_t>(); o.port = h->d_port.as<uint32_t>();
+  o.msize = h->d_msize.as<double>(); o.mprof = h->d_mprof.as<int32_t>();
+  o.alloc = h->d_ocols[0].as<int32_t>(); o.agent = h->d_ocols[1].as<int32_t>(); o.host = h->d_ocols[2].as<int32_t>();
+  o.zone = h->d_ocols[3].as<int32_t>(); o.region = h->d_ocols[4].as<int32_t>();
+  o.attr = h->d_oattr.as<int32_t>(); o.rr = h->d_orr.as<int32_t>(); o.exec = h->d_oexec.as<int32_t>();
+  if (t->n_reserved > 0) {
+    if (int rc = upload(h, h->d_rbegin, t->reserved_begin, n + 1)) return rc;
+    if (int rc = upload(h, h->d_rid, t->reserved_id, (size_t)t->n_reserved)) return rc;
+    if (int rc = upload(h, h->d_rkind, t->reserved_kind, (size_t)t->n_reserved)) return rc;
+    if (int rc = upload(h, h->d_rval, t->reserved_value, (size_t)t->n_reserved)) return rc;
+    o.rbegin = h->d_rbegin.as<int64_t>(); o.rid = h->d_rid.as<int32_t>(); o.rkind = h->d_rkind.as<int32_t>(); o.rval = h->d_rval.as<double>();
+  } else {
+    o.rbegin = nullptr; o.rid = nullptr; o.rkind = nullptr; o.rval = nullptr;
+  }
+  const oe_dict_sizes& dc = h->dict;
+  check_ids(h, o.agent, N, 0, std::max(dc.n_agents, 1), 11);
+  check_ids(h, o.host, N, 0, std::max(dc.n_hostnames, 1), 12);
+  check_ids(h, o.zone, N, -1, dc.n_zones, 13);
+  check_ids(h, o.region, N, -1, dc.n_regions, 14);
+  check_ids(h, o.attr, N * o.A, -1, dc.n_attrs, 15);
+  check_ids(h, o.rr, N * o.Q, -1, dc.n_rr_values, 16);
+  check_ids(h, o.mprof, N * o.D, -1, OE_MAX_PROFILES, 17);
+  if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
+  h->hasO = true;
+  return OE_OK;
+}
+
+int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
+  if (!h || !t) return OE_ERR_INVALID;
+  if (!h->hasP || !h->hasT) return h->fail(OE_ERR_STATE, "oe_load_requirements: load programs and tasks first");
+  CU(cudaSetDevice(h->device));
+  h->hasR = false;
+  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  const int64_t M = t->n_reqs;
+  if (M < 0 || M > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_reqs");
+  if (M > 0 && (!t->class_id || !t->pod_type_id || !t->pod_index)) return h->fail(OE_ERR_INVALID, "oe_load_requirements: missing column");
+  for (int64_t j = 0; j < M; ++j) {
+    if (t->class_id[j] < 0 || t->class_id[j] >= h->C) return h->fail(OE_ERR_INVALID, "requirement %lld: class id %d", (long long)j, t->class_id[j]);
+    if (t->pod_type_id[j] < 0 || t->pod_type_id[j] >= std::max(h->dict.n_pod_types, 1)) return h->fail(OE_ERR_INVALID, "requirement %lld: pod type", (long long)j);
+  }
+  h->M = M;
+  h->h_class.assign(t->class_id, t->class_id + M);
+  h->h_rtype.assign(t->pod_type_id, t->pod_type_id + M);
+  h->h_rindex.assign(t->pod_index, t->pod_index + M);
+
+  // Variants: requirements that have deployed tasks of the same pod type + index AND whose class reads tallies.
+  const int64_t T = (int64_t)h->h_ttype.size();
+  std::vector<int32_t> vcls, vself_begin(1, 0), vself_rows;
+  h->h_req_row.assign(t->class_id, t->class_id + M);
+  auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
+    if (n > OE_MAX_SELF_ROWS) return h->fail(OE_ERR_LIMIT, "requirement %lld: %d equivalent deployed tasks (max %d)", (long long)j, n, OE_MAX_SELF_ROWS);
+    h->h_req_row[j] = h->C + (int32_t)vcls.size();
+    vcls.push_back(h->h_class[j]);
+    vself_rows.insert(vself_rows.end(), rows, rows + n);
+    vself_begin.push_back((int32_t)vself_rows.size());
+    return 0;
+  };
+  if (t->self_begin) {
+    for (int64_t j = 0; j < M; ++j) {
+      const int b = t->self_begin[j], e = t->self_begin[j + 1];
+      if (e < b) return h->fail(OE_ERR_INVALID, "self_begin not monotone");
+      if (e == b || !h->class_self_sensitive[h->h_class[j]]) continue;
+      for (int q = b; q < e; ++q) if (t->self_rows[q] < 0 || t->self_rows[q] >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
+      if (int rc = add_variant(j, t->self_rows + b, e - b)) return rc;
+    }
+  } else if (T > 0) {
+    std::unordered_map<uint64_t, std::vector<int32_t>> by_pod;
+    for (int64_t r = 0; r < T; ++r) {
+      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
+      by_pod[((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r]].push_back((int32_t)r);
+    }
+    for (int64_t j = 0; j < M; ++j) {
+      if (!h->class_self_sensitive[h->h_class[j]]) continue;
+      auto it = by_pod.find(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
+      if (it == by_pod.end()) continue;
+      if (int rc = add_variant(j, it->second.data(), (int)it->second.size())) return rc;
+    }
+  }
+  h->V = (int)vcls.size();
+  if (int rc = upload(h, h->d_req_row, h->h_req_row.data(), (size_t)M)) return rc;
+  if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M)) return rc;
+  if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M)) return rc;
+  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size())) return rc;
+  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size())) return rc;
+  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size())) return rc;
+  CU(h->d_vrrsum.ensure(std::max<size_t>((size_t)h->V * std::max(h->n_csets, 1), 1) * sizeof(int4)));
+  CU(h->d_dec.ensure(std::max<size_t>((size_t)M, 1) * sizeof(oe_decision)));
+
+  h->h_launch_begin.clear(); h->h_launch_name.clear(); h->h_launch_filter.clear();
+  if (t->launch_begin) {
+    if (t->launch_begin[0] != 0) return h->fail(OE_ERR_INVALID, "launch_begin[0] != 0");
+    for (int64_t j = 0; j < M; ++j) if (t->launch_begin[j + 1] < t->launch_begin[j]) return h->fail(OE_ERR_INVALID, "launch_begin not monotone");
+    const size_t nl = (size_t)t->launch_begin[M];
+    if (nl && (!t->launch_name_id || (h->dt.FW && !t->launch_filter_bits))) return h->fail(OE_ERR_INVALID, "launch rows missing");
+    h->h_launch_begin.assign(t->launch_begin, t->launch_begin + M + 1);
+    h->h_launch_name.assign(t->launch_name_id, t->launch_name_id + nl);
+    h->h_launch_filter.assign(t->launch_filter_bits, t->launch_filter_bits + nl * h->dt.FW);
+  }
+  CU(cudaStreamSynchronize(h->stream));
+  h->hasR = true;
+  return OE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Evaluation
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct Phase { cudaEvent_t a, b; };
+
+int run_counters(oe_engine* h, int64_t* launches) {
+  const size_t ncnt = (size_t)h->h_cs_off.back();
+  if (ncnt) CU(cudaMemsetAsync(h->d_cnt.p, 0, ncnt * 4, h->stream));
+  if (h->n_tsets) {
+    CU(cudaMemsetAsync(h->d_type_total.p, 0, (size_t)h->n_tsets * 4, h->stream));
+    CU(cudaMemsetAsync(h->d_type_agent.p, 0, (size_t)h->n_tsets * h->dp.n_agents * 4, h->stream));
+  }
+  if (h->dt.T > 0 && (h->n_csets || h->n_tsets)) {
+    k_count_tasks<<<(unsigned)((h->dt.T + 255) / 256), 256, 0, h->stream>>>(h->dt, h->dp, h->d_cnt.as<int32_t>(), h->d_type_total.as<int32_t>(),
+                                                                         h->d_type_agent.as<int32_t>());
+    ++*launches;
+  }
+  if (h->n_csets) {
+    dim3 grid((unsigned)h->n_csets, (unsigned)(1 + h->V));
+    k_rr_summary<<<grid, 256, 0, h->stream>>>(h->ctx(), h->d_cnt.as<int32_t>(), h->d_rrsum.as<int4>(), h->d_vrrsum.as<int4>());
+    ++*launches;
+  }
+  CU(cudaGetLastError());
+  h->counters_fresh = true;
+  return 0;
+}
+
+int run_class_feasibility(oe_engine* h, int64_t* launches) {
+  const int64_t stride = h->stride();
+  const int rows = h->rows_factored();
+  CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
+  if (rows > 0) {
+    // enough row tiles to fill the machine when there are few offers, few enough to amortise the offer-row loads
+    const int64_t xblocks = stride * 32 / OE_K1_THREADS;
+    int tiles = (int)std::min<int64_t>(rows, std::max<int64_t>(1, (148 * 16 + xblocks - 1) / xblocks));
+    int rows_per_tile = (rows + tiles - 1) / tiles;
+    tiles = (rows + rows_per_tile - 1) / rows_per_tile;
+    dim3 grid((unsigned)xblocks, (unsigned)tiles);
+    k_class_feasibility<<<grid, OE_K1_THREADS, 0, h->stream>>>(h->ctx(), h->d_F.as<uint32_t>(), stride, rows, rows_per_tile);
+    ++*launches;
+    CU(cudaGetLastError());
+  }
+  h->class_bits_fresh = true;
+  return 0;
+}
+
+int run_expand(oe_engine* h, int64_t* launches) {
+  const int64_t stride = h->stride();
+  CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
+  if (h->M > 0) {
+    const unsigned xblocks = (unsigned)((stride / 4 + OE_KX_THREADS - 1) / OE_KX_THREADS);
+    // ~8 CTAs per SM overall; each CTA streams a [reqs_per_block x 4 KiB] slab
+    int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 63) / 64, (148 * 8 + xblocks - 1) / xblocks));
+    const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
+    yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
+    dim3 grid(xblocks, (unsigned)yblocks);
+    k_expand_matrix<<<grid, OE_KX_THREADS, 0, h->stream>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(), h->d_matrix.as<uint32_t>(), stride,
+                                                          h->M, reqs_per_block);
+    ++*launches;
+    CU(cudaGetLastError());
+  }
+  return 0;
+}
+
+int run_commit(oe_engine* h, int64_t* launches) {
+  const int64_t stride = h->stride();
+  const int rows = h->rows_factored();
+  CommitArgs a{};
+  if (h->world > 1) {
+    a.F = h->d_Fglobal.as<uint32_t>();
+    a.shard_words = h->shard_rows / 32;
+    a.total_words = std::min<int64_t>((h->N_global + 31) / 32, (int64_t)h->world * a.shard_words);
+  } else {
+    a.F = h->d_F.as<uint32_t>();
+    a.shard_words = stride;
+    a.total_words = (h->N + 31) / 32;
+  }
+  a.stride = stride; a.rows = rows; a.req_row = h->d_req_row.as<int32_t>(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
+  a.n_placed = h->d_nplaced.as<int>();
+  size_t smem = (size_t)OE_WIN_SLOTS * 32 * 4 + OE_WIN_SLOTS * 4 + OE_WIN_SLOTS * 8;
+  const size_t budget = (size_t)h->smem_optin;
+  a.cursor_in_smem = smem + (size_t)rows * 4 <= budget / 4;
+  if (a.cursor_in_smem) smem += (size_t)rows * 4;
+  else { CU(h->d_cursor.ensure(std::max<size_t>(rows, 1) * 4)); a.cursor_g = h->d_cursor.as<int32_t>(); }
+  a.used_in_smem = smem + (size_t)a.total_words * 4 <= budget;
+  if (a.used_in_smem) smem += (size_t)a.total_words * 4;
+  else { CU(h->d_used.ensure(std::max<size_t>(a.total_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
+  CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->stream));
+  k_commit<<<1, 256, smem, h->stream>>>(a);
+  ++*launches;
+  CU(cudaGetLastError());
+  if (h->M > 0) {
+    k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+    ++*launches;
+    CU(cudaGetLastError());
+  }
+  return 0;
+}
+
+float ms_between(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, a, b);
+  return ms;
+}
+
+int ready(oe_engine* h, const char* who) {
+  if (!h) return OE_ERR_INVALID;
+  if (!(h->hasP && h->hasT && h->hasO && h->hasR)) return h->fail(OE_ERR_STATE, "%s: tables not loaded (programs, tasks, offers, requirements)", who);
+  for (auto& cs : h->h_csets)
+    if (cs.keyspace == OE_KS_RR_ATTR && (cs.rr_col >= h->dof.Q || cs.rr_col >= h->dt.Q)) return h->fail(OE_ERR_INVALID, "%s: rr column mismatch", who);
+  if (cudaSetDevice(h->device) != cudaSuccess) return h->fail(OE_ERR_CUDA, "cudaSetDevice");
+  return 0;
+}
+
+}  // namespace
+
+int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
+  if (int rc = ready(h, "oe_class_feasibility")) return rc;
+  int64_t launches = 0;
+  CU(cudaEventRecord(h->ev[0], h->stream));
+  if (int rc = run_counters(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[1], h->stream));
+  if (int rc = run_class_feasibility(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[2], h->stream));
+  if (bits) CU(cudaMemcpyAsync(bits, h->d_F.p, (size_t)h->rows_factored() * h->stride() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaEventRecord(h->ev[3], h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (stats) {
+    std::memset(stats, 0, sizeof *stats);
+    stats->ms_counters = ms_between(h->ev[0], h->ev[1]);
+    stats->ms_feasibility = ms_between(h->ev[1], h->ev[2]);
+    stats->ms_d2h = ms_between(h->ev[2], h->ev[3]);
+    stats->ms_total = ms_between(h->ev[0], h->ev[3]);
+    stats->n_pairs = h->N * h->M;
+    stats->kernel_launches = launches;
+  }
+  return OE_OK;
+}
+
+int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
+  if (int rc = ready(h, "oe_feasibility")) return rc;
+  int64_t launches = 0;
+  CU(cudaEventRecord(h->ev[0], h->stream));
+  if (int rc = run_counters(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[1], h->stream));
+  if (int rc = run_class_feasibility(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[2], h->stream));
+  if (int rc = run_expand(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[3], h->stream));
+  if (bits) CU(cudaMemcpyAsync(bits, h->d_matrix.p, (size_t)h->M * h->stride() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaEventRecord(h->ev[4], h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (stats) {
+    std::memset(stats, 0, sizeof *stats);
+    stats->ms_counters = ms_between(h->ev[0], h->ev[1]);
+    stats->ms_feasibility = ms_between(h->ev[1], h->ev[2]);
+    stats->ms_expand = ms_between(h->ev[2], h->ev[3]);
+    stats->ms_d2h = ms_between(h->ev[3], h->ev[4]);
+    stats->ms_total = ms_between(h->ev[0], h->ev[4]);
+    stats->n_pairs = h->N * h->M;
+    stats->kernel_launches = launches;
+  }
+  return OE_OK;
+}
+
+int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
+  if (int rc = ready(h, "oe_evaluate_cycle")) return rc;
+  if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
+  int64_t launches = 0;
+  CU(cudaEventRecord(h->ev[0], h->stream));
+  if (h->world > 1) {
+    // sharded: the caller ran oe_class_feasibility on every shard and gathered the rows into OE_BUF_CLASS_BITS_GLOBAL
+    if (!h->class_bits_fresh) return h->fail(OE_ERR_STATE, "oe_evaluate_cycle (sharded): run oe_class_feasibility and gather first");
+    if (h->d_Fglobal.cap < (size_t)h->world * h->rows_factored() * h->stride() * 4) return h->fail(OE_ERR_STATE, "gathered class bits buffer was not requested");
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+  } else {
+    if (int rc = run_counters(h, &launches)) return rc;
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    if (int rc = run_class_feasibility(h, &launches)) return rc;
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) if (int rc = run_expand(h, &launches)) return rc;
+    CU(cudaEventRecord(h->ev[3], h->stream));
+  }
+  if (int rc = run_commit(h, &launches)) return rc;
+  CU(cudaEventRecord(h->ev[4], h->stream));
+  int n_placed = 0;
+  if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(&n_placed, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaEventRecord(h->ev[5], h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->h_last_dec.assign(out, out + h->M);
+  h->cycle_done = true;
+  if (stats) {
+    std::memset(stats, 0, sizeof *stats);
+    stats->ms_counters = ms_between(h->ev[0], h->ev[1]);
+    stats->ms_feasibility = ms_between(h->ev[1], h->ev[2]);
+    stats->ms_expand = ms_between(h->ev[2], h->ev[3]);
+    stats->ms_commit = ms_between(h->ev[3], h->ev[4]);
+    stats->ms_d2h = ms_between(h->ev[4], h->ev[5]);
+    stats->ms_total = ms_between(h->ev[0], h->ev[5]);
+    stats->n_placed = n_placed;
+    stats->n_pairs = h->N_global * h->M;
+    stats->kernel_launches = launches;
+  }
+  return OE_OK;
+}
+
+int32_t oe_apply_launches(oe_engine* h) {
+  if (int rc = ready(h, "oe_apply_launches")) return rc;
+  if (!h->cycle_done) return h->fail(OE_ERR_STATE, "oe_apply_launches: no cycle evaluated since the last load");
+  if (h->world > 1) return h->fail(OE_ERR_STATE, "oe_apply_launches: not available on a sharded engine (winning rows live on other shards)");
+  if (h->h_launch_begin.empty()) return h->fail(OE_ERR_STATE, "oe_apply_launches: the requirement table carries no launch rows");
+  if (h->dt.TA < h->dof.A) return h->fail(OE_ERR_INVALID, "oe_apply_launches: task table has fewer attribute slots than the offer table");
+  std::vector<int32_t> dst, req, name;
+  std::vector<uint32_t> filt;
+  int64_t T = h->dt.T;
+  const int FW = h->dt.FW;
+  for (int64_t j = 0; j < h->M; ++j) {
+    if (h->h_last_dec[j].offer_row < 0) continue;
+    for (int32_t l = h->h_launch_begin[j]; l < h->h_launch_begin[j + 1]; ++l) {
+      const int32_t nm = h->h_launch_name[l];
+      auto it = h->name_to_row.find(nm);
+      int32_t row;
+      if (it == h->name_to_row.end()) {
+        row = (int32_t)T++;
+        h->name_to_row[nm] = row;
+        h->h_tname.push_back(nm); h->h_ttype.push_back(0); h->h_tindex.push_back(0);
+      } else {
+        row = it->second;
+      }
+      h->h_ttype[row] = h->h_rtype[j];
+      h->h_tindex[row] = h->h_rindex[j];
+      dst.push_back(row); req.push_back((int32_t)j); name.push_back(nm);
+      for (int w = 0; w < FW; ++w) filt.push_back(h->h_launch_filter[(size_t)l * FW + w]);
+    }
+  }
+  if (int rc = reserve_tasks(h, T, h->dt.T)) return rc;
+  if (!dst.empty()) {
+    if (int rc = upload(h, h->d_l_dst, dst.data(), dst.size())) return rc;
+    if (int rc = upload(h, h->d_l_req, req.data(), req.size())) return rc;
+    if (int rc = upload(h, h->d_l_name, name.data(), name.size())) return rc;
+    if (int rc = upload(h, h->d_l_filter, filt.data(), filt.size())) return rc;
+    LaunchArgs a{(int64_t)dst.size(), h->d_l_dst.as<int32_t>(), h->d_l_req.as<int32_t>(), h->d_l_name.as<int32_t>(), h->d_l_filter.as<uint32_t>(),
+                 h->d_rtype.as<int32_t>(), h->d_rindex.as<int32_t>()};
+    // a pod stores each task name once, and names are unique rows, so no two threads write one row
+    k_apply_launches<<<(unsigned)((a.n + 127) / 128), 128, 0, h->stream>>>(a, h->dof, h->dt, h->d_dec.as<oe_decision>());
+    CU(cudaGetLastError());
+  }
+  h->dt.T = T;
+  CU(cudaStreamSynchronize(h->stream));
+  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  return OE_OK;
+}
+
+int32_t oe_export_tasks(oe_engine* h, int64_t* n_tasks, int32_t* name_id, int32_t* pod_type_id, int32_t* pod_index, int32_t* agent_id,
+                        int32_t* hostname_id, int32_t* zone_id, int32_t* region_id, int32_t* attr_id, int32_t* rr_key, uint32_t* filter_bits) {
+  if (!h || !h->hasT) return OE_ERR_STATE;
+  CU(cudaSetDevice(h->device));
+  const DevTasks& t = h->dt;
+  if (n_tasks) *n_tasks = t.T;
+  if (!name_id) return OE_OK;
+  const size_t n = (size_t)t.T;
+  int32_t* dst[7] = {name_id, pod_type_id, pod_index, agent_id, hostname_id, zone_id, region_id};
+  const int32_t* src[7] = {t.name, t.type, t.index, t.agent, t.host, t.zone, t.region};
+  for (int c = 0; c < 7; ++c) CU(cudaMemcpyAsync(dst[c], src[c], n * 4, cudaMemcpyDeviceToHost, h->stream));
+  for (int a = 0; a < t.TA; ++a) CU(cudaMemcpyAsync(attr_id + (size_t)a * n, t.attr + (size_t)a * t.cap, n * 4, cudaMemcpyDeviceToHost, h->stream));
+  for (int q = 0; q < t.Q; ++q) CU(cudaMemcpyAsync(rr_key + (size_t)q * n, t.rr + (size_t)q * t.cap, n * 4, cudaMemcpyDeviceToHost, h->stream));
+  for (int w = 0; w < t.FW; ++w) CU(cudaMemcpyAsync(filter_bits + (size_t)w * n, t.filter + (size_t)w * t.cap, n * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return OE_OK;
+}
+
+int32_t oe_device_buffer(oe_engine* h, int32_t which, void** dev_ptr, int64_t* n_bytes) {
+  if (!h || !dev_ptr || !n_bytes) return OE_ERR_INVALID;
+  CU(cudaSetDevice(h->device));
+  const int64_t stride = h->stride();
+  switch (which) {
+    case OE_BUF_CLASS_BITS_LOCAL:
+      *n_bytes = (int64_t)h->rows_factored() * stride * 4;
+      CU(h->d_F.ensure(std::max<int64_t>(*n_bytes, 4)));
+      *dev_ptr = h->d_F.p;
+      break;
+    case OE_BUF_CLASS_BITS_GLOBAL:
+      *n_bytes = (int64_t)h->world * h->rows_factored() * stride * 4;
+      CU(h->d_Fglobal.ensure(std::max<int64_t>(*n_bytes, 4)));
+      *dev_ptr = h->d_Fglobal.p;
+      break;
+    case OE_BUF_MATRIX:
+      *n_bytes = h->M * stride * 4;
+      CU(h->d_matrix.ensure(std::max<int64_t>(*n_bytes, 4)));
+      *dev_ptr = h->d_matrix.p;
+      break;
+    case OE_BUF_DECISIONS:
+      *n_bytes = h->M * (int64_t)sizeof(oe_decision);
+      CU(h->d_dec.ensure(std::max<int64_t>(*n_bytes, 4)));
+      *dev_ptr = h->d_dec.p;
+      break;
+    default: return h->fail(OE_ERR_INVALID, "oe_device_buffer: unknown buffer %d", which);
+  }
+  return OE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,190 @@
+"""GPU parity: the CUDA engine, driven through the C ABI, against the CPU oracle on identical encoded tables."""
+import numpy as np
+import pytest
+
+from dcos_commons_b200 import Engine, abi, synth, unpack_bits
+from fuzz_tables import random_tables
+from oracle_binding import Oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+    e = Engine(device=0)
+    yield e
+    e.close()
+
+
+def _compare_all(eng, t, two_cycles=True):
+    orc = Oracle().load(t)
+    eng.load(t)
+    N = t.n_offers
+    m_cpu, _ = orc.feasibility()
+    m_gpu, st = eng.feasibility()
+    assert m_gpu.shape == m_cpu.shape
+    assert np.array_equal(unpack_bits(m_gpu, N), unpack_bits(m_cpu, N))
+    assert not m_gpu[:, (N + 31) // 32:].any(), "padding words must be zero"
+    d_cpu, s_cpu = orc.evaluate_cycle()
+    d_gpu, s_gpu = eng.evaluate_cycle()
+    assert d_gpu.tobytes() == d_cpu.tobytes()
+    assert s_gpu["n_placed"] == s_cpu["n_placed"]
+    if two_cycles and t.launch_begin is not None:
+        orc.apply_launches()
+        eng.apply_launches()
+        tc, tg = orc.export_tasks(), eng.export_tasks()
+        for k in tc:
+            assert np.array_equal(tc[k], tg[k]), f"task column {k} differs after apply_launches"
+        d_cpu2, _ = orc.evaluate_cycle()
+        d_gpu2, _ = eng.evaluate_cycle()
+        assert d_gpu2.tobytes() == d_cpu2.tobytes()
+    orc.close()
+
+
+@pytest.mark.parametrize("seed", range(120))
+def test_fuzz_matrix_cycle_and_replay(engine, seed):
+    _compare_all(engine, random_tables(seed))
+
+
+@pytest.mark.parametrize("seed", range(1000, 1010))
+def test_fuzz_wider(engine, seed):
+    _compare_all(engine, random_tables(seed, n_offers=1500 + seed % 7, n_reqs=60, n_tasks=150, big_dicts=True))
+
+
+def test_empty_inputs(engine):
+    t = random_tables(5, n_offers=40, n_reqs=6, n_tasks=0)
+    _compare_all(engine, t)
+    t = random_tables(6, n_offers=1, n_reqs=1, n_tasks=3)
+    _compare_all(engine, t)
+
+
+def test_c4_shape_small(engine):
+    cl = synth.make_cluster(2000, 300, 8, 3, 4, 0, "c4")
+    _compare_all(engine, cl.tables)
+
+
+def test_c5_shape_small_with_deployed_tasks(engine):
+    cl = synth.make_cluster(4000, 320, 32, 8, 6, 640, "c5")
+    _compare_all(engine, cl.tables)
+
+
+def test_c4_multi_cycle_replay(engine):
+    """Config 4's replay: 500 steps per cycle (scaled down), tallies updated between cycles."""
+    cl = synth.make_cluster(1500, 400, 8, 3, 4, 0, "c4")
+    t = cl.tables
+    orc = Oracle()
+    per = 100
+    import copy
+    for cyc in range(4):
+        sub = copy.copy(t)
+        sl = slice(cyc * per, (cyc + 1) * per)
+        sub.class_id, sub.r_pod_type_id, sub.r_pod_index = t.class_id[sl].copy(), t.r_pod_type_id[sl].copy(), t.r_pod_index[sl].copy()
+        sub.launch_begin = (t.launch_begin[sl.start: sl.stop + 1] - t.launch_begin[sl.start]).astype(np.int32)
+        sub.launch_name_id = t.launch_name_id[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.launch_filter_bits = t.launch_filter_bits[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.normalise()
+        if cyc == 0:
+            orc.load(sub)
+            engine.load(sub)
+        else:
+            for h in (orc, engine):
+                h.tables = sub
+                h.load_requirements(sub)
+        d_cpu, _ = orc.evaluate_cycle()
+        d_gpu, _ = engine.evaluate_cycle()
+        assert d_gpu.tobytes() == d_cpu.tobytes(), f"cycle {cyc}"
+        orc.apply_launches()
+        engine.apply_launches()
+    tc, tg = orc.export_tasks(), engine.export_tasks()
+    assert len(tc["name_id"]) == len(tg["name_id"]) > 0
+    for k in tc:
+        assert np.array_equal(tc[k], tg[k])
+
+
+def test_class_rows_expand_to_matrix(engine):
+    cl = synth.make_cluster(5000, 500, 8, 3, 4, 80, "c5")
+    engine.load(cl.tables)
+    m, _ = engine.feasibility()
+    f, _ = engine.class_feasibility()
+    assert f.shape[0] == engine.factored_rows()
+    # fresh instances (no deployed twin) copy their class row
+    for j in range(0, cl.tables.n_reqs, 37):
+        assert np.array_equal(m[j], f[cl.tables.class_id[j]])
+
+
+def test_c4_full_size_sampled_rows_and_properties(engine):
+    """Config 4 at full size: sampled matrix rows against the oracle, plus size-independent properties."""
+    cl = synth.config_c4()
+    t = cl.tables
+    engine.load(t)
+    m, _ = engine.feasibility()
+    N = t.n_offers
+    orc = Oracle().load(t)
+    rng = np.random.default_rng(1)
+    for j in rng.integers(0, t.n_reqs, 12):
+        row = orc.feasibility_rows(int(j), int(j) + 1)
+        assert np.array_equal(unpack_bits(m[j:j + 1], N), unpack_bits(row, N)), f"row {j}"
+    dec, st = engine.evaluate_cycle()
+    _check_commit_properties(t, m, dec)
+    d_cpu, _ = orc.evaluate_cycle()
+    assert dec.tobytes() == d_cpu.tobytes()
+
+
+def _check_commit_properties(t, m, dec):
+    """Every winner is feasible, no offer is taken twice, and the choice is first-fit given earlier winners."""
+    N = t.n_offers
+    bits = unpack_bits(m, N)
+    used = np.zeros(N, bool)
+    for j in range(t.n_reqs):
+        row = bits[j] & ~used
+        first = int(np.argmax(row)) if row.any() else -1
+        assert dec["offer_row"][j] == first, f"requirement {j}: got {dec['offer_row'][j]}, first fit is {first}"
+        if first >= 0:
+            used[first] = True
+
+
+def test_c5_tenth_scale_properties(engine):
+    cl = synth.config_c5(0.1)
+    t = cl.tables
+    engine.load(t)
+    m, st = engine.feasibility()
+    assert st["n_pairs"] == t.n_offers * t.n_reqs
+    dec, _ = engine.evaluate_cycle()
+    # linear-time replay of the first-fit property using per-class rows
+    f, _ = engine.class_feasibility()
+    N = t.n_offers
+    fb = unpack_bits(f, N)
+    for j in range(0, t.n_reqs, 997):
+        assert np.array_equal(unpack_bits(m[j:j + 1], N)[0], fb[t.class_id[j]])
+    used = np.zeros(N, bool)
+    cursors = np.zeros(fb.shape[0], np.int64)
+    order = [np.flatnonzero(fb[c]) for c in range(fb.shape[0])]
+    for j in range(t.n_reqs):
+        c = t.class_id[j]
+        cand = order[c]
+        k = cursors[c]
+        while k < len(cand) and used[cand[k]]:
+            k += 1
+        cursors[c] = k
+        want = int(cand[k]) if k < len(cand) else -1
+        assert dec["offer_row"][j] == want
+        if want >= 0:
+            used[want] = True
+    # determinism: a second run gives the same bytes
+    dec2, _ = engine.evaluate_cycle()
+    assert dec.tobytes() == dec2.tobytes()
+
+
+def test_invalid_tables_are_rejected_not_faulted(engine):
+    t = random_tables(3, n_offers=50, n_reqs=5, n_tasks=10)
+    t.hostname_id = t.hostname_id.copy()
+    t.hostname_id[7] = 10 ** 6
+    with pytest.raises(abi.EngineError):
+        engine.load(t)
+    t2 = random_tables(3, n_offers=50, n_reqs=5, n_tasks=10)
+    t2.class_id = t2.class_id.copy()
+    t2.class_id[0] = 99
+    with pytest.raises(abi.EngineError):
+        engine.load(t2)
+    # the engine is still usable afterwards
+    _compare_all(engine, random_tables(4))
