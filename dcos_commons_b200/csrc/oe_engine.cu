@@ -352,7 +352,8 @@ struct oe_engine {
   int64_t M = 0;
   int V = 0;
   std::vector<int32_t> h_class, h_rtype, h_rindex, h_req_row;
-  std::vector<int32_t> h_launch_begin, h_launch_name;
+  std::vector<int32_t> h_launch_begin, h_launch_name, h_self_begin, h_self_rows;
+  bool self_provided = false;
   std::vector<uint32_t> h_launch_filter;
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
 
@@ -808,6 +809,51 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   return OE_OK;
 }
 
+namespace {
+// Variants: requirements that have deployed tasks of the same pod type + index (S/offer/TaskUtils.java:136-145) AND
+// whose class reads tallies.  Each gets a factored row of its own (row C + v) evaluated with those tasks taken out.
+int rebuild_variants(oe_engine* h) {
+  const int64_t M = h->M;
+  const int64_t T = (int64_t)h->h_ttype.size();
+  std::vector<int32_t> vcls, vself_begin(1, 0), vself_rows;
+  h->h_req_row.assign(h->h_class.begin(), h->h_class.end());
+  auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
+    h->h_req_row[j] = h->C + (int32_t)vcls.size();
+    vcls.push_back(h->h_class[j]);
+    vself_rows.insert(vself_rows.end(), rows, rows + n);
+    vself_begin.push_back((int32_t)vself_rows.size());
+    return 0;
+  };
+  if (h->self_provided) {
+    for (int64_t j = 0; j < M; ++j) {
+      const int b = h->h_self_begin[j], e = h->h_self_begin[j + 1];
+      if (e == b || !h->class_self_sensitive[h->h_class[j]]) continue;
+      if (int rc = add_variant(j, h->h_self_rows.data() + b, e - b)) return rc;
+    }
+  } else if (T > 0) {
+    std::unordered_map<uint64_t, std::vector<int32_t>> by_pod;
+    for (int64_t r = 0; r < T; ++r) {
+      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
+      by_pod[((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r]].push_back((int32_t)r);
+    }
+    for (int64_t j = 0; j < M; ++j) {
+      if (!h->class_self_sensitive[h->h_class[j]]) continue;
+      auto it = by_pod.find(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
+      if (it == by_pod.end()) continue;
+      if (int rc = add_variant(j, it->second.data(), (int)it->second.size())) return rc;
+    }
+  }
+  h->V = (int)vcls.size();
+  if (int rc = upload(h, h->d_req_row, h->h_req_row.data(), (size_t)M)) return rc;
+  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size())) return rc;
+  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size())) return rc;
+  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size())) return rc;
+  CU(h->d_vrrsum.ensure(std::max<size_t>((size_t)h->V * std::max(h->n_csets, 1), 1) * sizeof(int4)));
+  CU(cudaStreamSynchronize(h->stream));  // the vectors above are locals
+  return 0;
+}
+}  // namespace
+
 int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   if (!h || !t) return OE_ERR_INVALID;
   if (!h->hasP || !h->hasT) return h->fail(OE_ERR_STATE, "oe_load_requirements: load programs and tasks first");
@@ -826,47 +872,18 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   h->h_rtype.assign(t->pod_type_id, t->pod_type_id + M);
   h->h_rindex.assign(t->pod_index, t->pod_index + M);
 
-  // Variants: requirements that have deployed tasks of the same pod type + index AND whose class reads tallies.
-  const int64_t T = (int64_t)h->h_ttype.size();
-  std::vector<int32_t> vcls, vself_begin(1, 0), vself_rows;
-  h->h_req_row.assign(t->class_id, t->class_id + M);
-  auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
-    if (n > OE_MAX_SELF_ROWS) return h->fail(OE_ERR_LIMIT, "requirement %lld: %d equivalent deployed tasks (max %d)", (long long)j, n, OE_MAX_SELF_ROWS);
-    h->h_req_row[j] = h->C + (int32_t)vcls.size();
-    vcls.push_back(h->h_class[j]);
-    vself_rows.insert(vself_rows.end(), rows, rows + n);
-    vself_begin.push_back((int32_t)vself_rows.size());
-    return 0;
-  };
-  if (t->self_begin) {
-    for (int64_t j = 0; j < M; ++j) {
-      const int b = t->self_begin[j], e = t->self_begin[j + 1];
-      if (e < b) return h->fail(OE_ERR_INVALID, "self_begin not monotone");
-      if (e == b || !h->class_self_sensitive[h->h_class[j]]) continue;
-      for (int q = b; q < e; ++q) if (t->self_rows[q] < 0 || t->self_rows[q] >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
-      if (int rc = add_variant(j, t->self_rows + b, e - b)) return rc;
-    }
-  } else if (T > 0) {
-    std::unordered_map<uint64_t, std::vector<int32_t>> by_pod;
-    for (int64_t r = 0; r < T; ++r) {
-      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
-      by_pod[((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r]].push_back((int32_t)r);
-    }
-    for (int64_t j = 0; j < M; ++j) {
-      if (!h->class_self_sensitive[h->h_class[j]]) continue;
-      auto it = by_pod.find(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
-      if (it == by_pod.end()) continue;
-      if (int rc = add_variant(j, it->second.data(), (int)it->second.size())) return rc;
-    }
+  h->self_provided = t->self_begin != nullptr;
+  h->h_self_begin.clear(); h->h_self_rows.clear();
+  if (h->self_provided) {
+    const int64_t T = (int64_t)h->h_ttype.size();
+    for (int64_t j = 0; j < M; ++j) if (t->self_begin[j + 1] < t->self_begin[j]) return h->fail(OE_ERR_INVALID, "self_begin not monotone");
+    h->h_self_begin.assign(t->self_begin, t->self_begin + M + 1);
+    h->h_self_rows.assign(t->self_rows, t->self_rows + t->self_begin[M]);
+    for (int32_t r : h->h_self_rows) if (r < 0 || r >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
   }
-  h->V = (int)vcls.size();
-  if (int rc = upload(h, h->d_req_row, h->h_req_row.data(), (size_t)M)) return rc;
+  if (int rc = rebuild_variants(h)) return rc;
   if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M)) return rc;
   if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M)) return rc;
-  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size())) return rc;
-  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size())) return rc;
-  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size())) return rc;
-  CU(h->d_vrrsum.ensure(std::max<size_t>((size_t)h->V * std::max(h->n_csets, 1), 1) * sizeof(int4)));
   CU(h->d_dec.ensure(std::max<size_t>((size_t)M, 1) * sizeof(oe_decision)));
 
   h->h_launch_begin.clear(); h->h_launch_name.clear(); h->h_launch_filter.clear();
@@ -1139,6 +1156,11 @@ int32_t oe_apply_launches(oe_engine* h) {
   h->dt.T = T;
   CU(cudaStreamSynchronize(h->stream));
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  if (h->self_provided) {
+    h->hasR = false;  // the caller's equivalent-task lists name rows of the old table: requirements must be re-loaded
+  } else if (int rc = rebuild_variants(h)) {
+    return rc;  // the stored tasks are now "equivalent" to the requirements that placed them
+  }
   return OE_OK;
 }
 

@@ -57,7 +57,6 @@ typedef enum {
 #define OE_MAX_CLASSES 4096     /* requirement classes per cycle                                          */
 #define OE_MAX_DYN_PORTS 8      /* dynamic host ports per class (reported in oe_decision)                 */
 #define OE_MAX_MOUNT_OPS 4      /* MOUNT volumes per class (reported in oe_decision)                      */
-#define OE_MAX_SELF_ROWS 16     /* deployed tasks equivalent to one requirement (same pod type + index)   */
 #define OE_MAX_PROFILES 64      /* volume profile dictionary (profile sets are u64 masks)                 */
 
 #define OE_PORT_EMPTY 0x0000FFFFu /* packed range with begin(65535) > end(0): unused range slot           */

@@ -528,7 +528,7 @@ struct Oracle {
   }
 };
 
-int64_t stride_words(int64_t n) { return ((n + 31) / 32 + 31) / 32 * 32; }
+int64_t stride_words(int64_t n) { return std::max<int64_t>(128, ((n + 31) / 32 + 127) / 128 * 128); }
 
 }  // namespace
 
