@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""Benchmark of the offer-evaluation hot path (BASELINE.json: offer x pod evaluations/sec, placement-cycle latency).
+
+  python bench.py --gpus 1 --steps K --warmup W                 our arm (CUDA engine through the C ABI)
+  python bench.py --impl reference --gpus N --steps K --warmup W  the reference path on the host cores (CPU oracle)
+
+A "step" is one pass of the hot path over one batch: all offers x all requirements of the workload.
+  value : N*M / t(K0 + K1 + K1x) with the tables resident in HBM (device time, CUDA events on the engine's stream)
+  e2e   : N*M / t(one placement cycle through the C ABI from pinned HOST tables: H2D of every table, K0, K1, K1x, K2,
+          D2H of the decisions)
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "offer x pod-instance evaluations/sec"
+UNIT = "evaluations/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--workload", default="c5", choices=["c5", "c4"])
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debugging only; invalid as a bench number)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def make_workload(args):
+    from dcos_commons_b200 import synth
+    cl = synth.config_c5(args.scale) if args.workload == "c5" else synth.config_c4(args.scale)
+    return cl
+
+
+def table_bytes(t, lo=0, hi=None):
+    """Bytes of the encoded tables (what one cycle uploads)."""
+    n = t.n_offers
+    hi = n if hi is None else hi
+    frac = (hi - lo) / max(n, 1)
+    offer_cols = ("scalar", "scalar_present", "port_range", "mount_size", "mount_profile", "alloc_role", "agent_id", "hostname_id",
+                  "zone_id", "region_id", "attr_id", "rr_key", "exec_id")
+    other = ("op_begin", "ops", "rule_nodes", "pod_role", "port_excl_begin", "port_excl", "range_set_begin", "range_set", "counter_sets",
+             "type_set_pod_type", "matcher_bits", "t_name_id", "t_pod_type_id", "t_pod_index", "t_agent_id", "t_hostname_id", "t_zone_id",
+             "t_region_id", "t_attr_id", "t_rr_key", "t_filter_bits", "class_id", "r_pod_type_id", "r_pod_index", "launch_begin",
+             "launch_name_id", "launch_filter_bits")
+    b_off = sum(getattr(t, c).nbytes for c in offer_cols)
+    b_other = sum(getattr(t, c).nbytes for c in other if getattr(t, c) is not None)
+    return int(b_off * frac) + b_other, b_off // max(n, 1)
+
+
+def algorithmic_bytes(t, n_local):
+    """every offer row read once, every requirement once, one result bit per pair written once."""
+    _, b_offer = table_bytes(t)
+    b_class = (t.ops.nbytes + t.rule_nodes.nbytes + t.matcher_bits.nbytes + t.port_excl.nbytes) // max(t.n_classes, 1)
+    d = t.dict_sizes
+    ks = {0: d["n_hostnames"], 1: d["n_zones"], 2: d["n_regions"], 3: d["n_attrs"], 4: d["n_rr_values"]}
+    counters = sum(ks[int(c["keyspace"])] * 4 for c in t.counter_sets)
+    M, C = t.n_reqs, t.n_classes
+    words = (n_local + 31) // 32
+    k1 = n_local * b_offer + C * b_class + counters + C * words * 4      # class-factored feasibility
+    k1x = C * words * 4 + M * 4 + M * words * 4                            # expansion: read class rows + req->row, write matrix
+    return dict(k1=k1, k1x=k1x, total=n_local * b_offer + M * 4 + C * b_class + counters + M * words * 4, b_offer=b_offer, b_class=b_class)
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons DURING the timed region (NVML at ~1 kHz; nvidia-smi when NVML is missing)."""
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.sm, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self.thread = None
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop.is_set():
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+            r = int(get_reasons(h))
+            for name, bit in bits.items():
+                if r & bit:
+                    self.reasons.add(name)
+            time.sleep(0.001)
+
+    def _smi_loop(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout
+            except Exception:
+                return
+            r = [x.strip() for x in out.strip().split(",")]
+            if len(r) >= 9:
+                try:
+                    self.sm.append(float(r[1]))
+                    self.max_mhz = float(r[2])
+                except ValueError:
+                    pass
+                for k, name in enumerate(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]):
+                    if r[5 + k].lower() == "active":
+                        self.reasons.add(name)
+
+    def start(self):
+        try:
+            import pynvml  # noqa: F401
+            target = self._nvml_loop
+        except Exception:
+            target = self._smi_loop
+        self.thread = threading.Thread(target=target, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.thread:
+            self.thread.join(timeout=6)
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.sm)}
+
+
+def pin_tables(t):
+    """Copies every column into pinned host memory (torch is only the allocator here)."""
+    import copy
+    import torch
+    p = copy.copy(t)
+    p._keep = []
+    for name, val in vars(t).items():
+        if isinstance(val, np.ndarray) and val.size:
+            if val.dtype.fields is not None:  # structured dtypes: pin as raw bytes
+                raw = torch.from_numpy(val.view(np.uint8).copy()).pin_memory()
+                setattr(p, name, raw.numpy().view(val.dtype).reshape(val.shape))
+            else:
+                setattr(p, name, torch.from_numpy(val.copy()).pin_memory().numpy())
+    return p
+
+
+class _CudaView:
+    """Exposes a raw device pointer through __cuda_array_interface__ so torch.distributed can gather engine memory."""
+
+    def __init__(self, ptr, n_words):
+        self.__cuda_array_interface__ = {"shape": (n_words,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+
+
+def cpu_baseline_sample(t, seconds, n_sample_offers=1000):
+    """Reference path (CPU oracle, 1 thread) on a bounded sample of the same workload: whole requirement rows over the
+    first `n_sample_offers` offers, until the time budget is used."""
+    from oracle_binding import Oracle
+    import copy
+    n = min(n_sample_offers, t.n_offers)
+    orc = Oracle()
+    orc.tables = t
+    orc.load_programs(t)
+    orc.load_tasks(t)
+    orc.load_offers(t, 0, n)
+    orc.load_requirements(t)
+    t0 = time.perf_counter()
+    rows = 0
+    while rows < t.n_reqs and (time.perf_counter() - t0 < seconds or rows == 0):
+        orc.feasibility_rows(rows, rows + 1)
+        rows += 1
+    dt = time.perf_counter() - t0
+    orc.close()
+    return {"value": rows * n / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{rows} requirement rows x first {n} offers of the workload ({t.n_tasks} deployed tasks walked per rule, as the reference does), "
+                      f"{dt:.1f} s, CPU oracle oracle/oe_oracle.cpp -O2"}
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's own CPU path for the same metric: the CPU oracle (the JVM reference cannot run on this box), one
+    process per host core, each evaluating whole requirement rows over a sample of the workload's offers."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cl = make_workload(args)
+    t = cl.tables
+    cores = os.cpu_count() or 1
+    global _REF_T
+    _REF_T = t
+    # calibrate the sample so that one step takes a few seconds
+    probe = cpu_baseline_sample(t, 1.0, n_sample_offers=200)
+    per_core = probe["value"]
+    n = int(min(t.n_offers, max(200, per_core * 3.0)))  # ~3 s per row per core
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores, initializer=_ref_init, initargs=(n,)) as pool:
+        times = []
+        for s in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            pool.map(_ref_row, [(s * cores + k) % t.n_reqs for k in range(cores)])
+            if s >= args.warmup:
+                times.append(time.perf_counter() - t0)
+    total = sum(times)
+    value = args.steps * cores * n / total
+    sample = f"each step: {cores} requirement rows (one per process) x first {n} offers; {t.n_tasks} deployed tasks"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64+int32",
+            "data": "synthetic", "config": {"workload": cl.name, "offers": t.n_offers, "requirements": t.n_reqs, "classes": t.n_classes,
+                                            "deployed_tasks": t.n_tasks},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+_REF_T = None
+_REF_ORC = None
+
+
+def _ref_init(n):
+    global _REF_ORC
+    from oracle_binding import Oracle
+    t = _REF_T
+    o = Oracle()
+    o.tables = t
+    o.load_programs(t)
+    o.load_tasks(t)
+    o.load_offers(t, 0, n)
+    o.load_requirements(t)
+    _REF_ORC = o
+
+
+def _ref_row(j):
+    _REF_ORC.feasibility_rows(j, j + 1)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+def run_engine(args):
+    import torch
+    from dcos_commons_b200 import Engine, abi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+
+    cl = make_workload(args)
+    t = cl.tables
+    N, M = t.n_offers, t.n_reqs
+    if world > 1:
+        shard_rows = ((N + world - 1) // world + 1023) // 1024 * 1024
+        lo, hi = min(N, rank * shard_rows), min(N, (rank + 1) * shard_rows)
+    else:
+        shard_rows, lo, hi = 0, 0, N
+    n_local = hi - lo
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- resident-in-HBM arm -------------------------------------------------------------------------------------------
+    eng = Engine(device=local_rank, rank=rank, world=world)
+    eng.load(t, lo, hi, shard_rows)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    ext = torch.cuda.ExternalStream(eng.cuda_stream())
+
+    def flush_l2():
+        with torch.cuda.stream(ext):
+            flush.zero_()
+
+    for _ in range(args.warmup):
+        flush_l2()
+        eng.feasibility(fetch=False)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_steps, k0, k1, k1x, launches = [], 0.0, 0.0, 0.0, 0
+    for _ in range(args.steps):
+        flush_l2()
+        _, st = eng.feasibility(fetch=False)   # synchronises the engine stream; st holds CUDA-event times of this step
+        ms_steps.append(st["ms_counters"] + st["ms_feasibility"] + st["ms_expand"])
+        k0 += st["ms_counters"]; k1 += st["ms_feasibility"]; k1x += st["ms_expand"]
+        launches += st["kernel_launches"]
+    barrier()
+    clocks = sampler.stop()
+    dev_ms = sum(ms_steps)
+    if dist is not None:
+        tmax = torch.tensor([dev_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dev_ms = float(tmax.item())
+    value = args.steps * N * M / (dev_ms * 1e-3)
+
+    # ---- end-to-end arm: pinned host tables -> C ABI -> decisions in pinned host memory ------------------------------------
+    pt = pin_tables(t)
+    out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+    eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX)
+    gl = None
+
+    def cycle():
+        eng2.load(pt, lo, hi, shard_rows)
+        if world > 1:
+            eng2.feasibility(fetch=False)
+            nonlocal gl
+            lp, lb = eng2.device_buffer(abi.BUF_CLASS_BITS_LOCAL)
+            gp, gb = eng2.device_buffer(abi.BUF_CLASS_BITS_GLOBAL)
+            local = torch.as_tensor(_CudaView(lp, lb // 4), device="cuda")
+            glob = torch.as_tensor(_CudaView(gp, gb // 4), device="cuda")
+            dist.all_gather_into_tensor(glob, local)
+            torch.cuda.current_stream().synchronize()
+        return eng2.evaluate_cycle_into(out.data_ptr())
+
+    cyc_stats = None
+    for _ in range(max(1, min(args.warmup, 3))):
+        cyc_stats = cycle()
+    barrier()
+    e2e_steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        cyc_stats = cycle()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        tmax = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        e2e_s = float(tmax.item())
+    h2d, _ = table_bytes(t, lo, hi)
+    d2h = M * abi.DECISION_DTYPE.itemsize + 4
+    e2e = {"value": e2e_steps * N * M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
+           "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
+           "placed": cyc_stats["n_placed"]}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    ab = algorithmic_bytes(t, n_local)
+    k1_ms, k1x_ms = k1 / args.steps, k1x / args.steps
+    kernels = [
+        {"kernel": "k_expand_matrix", "ms": k1x_ms, "algorithmic_bytes": ab["k1x"], "achieved_gbs": ab["k1x"] / (k1x_ms * 1e-3) / 1e9 if k1x_ms else None},
+        {"kernel": "k_class_feasibility", "ms": k1_ms, "algorithmic_bytes": ab["k1"], "achieved_gbs": ab["k1"] / (k1_ms * 1e-3) / 1e9 if k1_ms else None},
+        {"kernel": "k_count_tasks+k_rr_summary", "ms": k0 / args.steps},
+    ]
+    dom = max(kernels[:2], key=lambda k: k["ms"])
+    roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                "frac": dom["achieved_gbs"] / peak if dom["achieved_gbs"] else None, "traffic": None, "peak_source": peak_src,
+                "pass_achieved": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9, "pass_frac": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9 / peak,
+                "pass_note": "pass_* = SURVEY.md §8(d) bytes_K1 (un-factored: one bit per pair written) over K0+K1+K1x device time",
+                "bytes_per_eval": ab["total"] / max(n_local * M, 1), "kernels": kernels}
+
+    cpu = cpu_baseline_sample(t, args.cpu_seconds) if world == 1 else None
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64+int32", "data": "synthetic",
+            "config": {"workload": cl.name, "offers": N, "requirements": M, "classes": t.n_classes, "deployed_tasks": t.n_tasks,
+                       "offers_per_gpu": n_local, "parallelism": f"offers row-sharded x{world}" if world > 1 else "single GPU",
+                       "l2": "256 MiB memset between timed steps flushes L2; the written matrix (N*M/8 bytes per step) is far larger than L2"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -4,9 +4,10 @@
 //   K0  k_count_tasks / k_rr_summary    task table → per-key tallies that the placement rules read
 //   K1  k_class_feasibility             offers × requirement classes → class-factored feasibility bits
 //   K1x k_expand_matrix                 class bits → full offers × requirements bit matrix (the HBM-bound pass)
-//   K2  k_commit                        ordered greedy first-fit over the class bits (one warp, shared-memory bitmap)
+//   K3  k_tile_popc / k_row_offsets / k_compact_rows   class bits → ascending candidate lists per factored row
+//   K2  k_commit                        ordered greedy first-fit: batched propose / in-order resolve, shared-memory bitmap
 //   K2b k_materialize                   winners → chosen dynamic ports / MOUNT slots
-//   K3  k_apply_launches                multi-cycle replay: placed pods → task rows
+//   K4  k_apply_launches                multi-cycle replay: placed pods → task rows
 //
 // There is no CPU fallback: every entry point needs a CUDA device and fails with an oe_status otherwise.
 #include <cuda_runtime.h>
@@ -151,90 +152,261 @@ __global__ void __launch_bounds__(OE_KX_THREADS) k_expand_matrix(const uint32_t*
   }
 }
 
-// K2: the greedy commit of PlanScheduler.resourceOffers.  Requirements are taken in order; each claims the lowest
-// offer whose bit is set in its factored row and that no earlier requirement claimed.  Because the claimed set only
-// grows and the rows are frozen within a cycle, each row keeps a cursor that never moves backwards, so the total scan
-// work is O(rows * N/32 + M) instead of O(M * N/32).  One warp; `used` bitmap, cursors and a direct-mapped cache of
-// 32-word row windows live in shared memory when they fit.
-struct CommitArgs {
+// View of the factored bit rows in GLOBAL offer order: word gw of row r lives in shard gw / shard_words.
+struct RowBits {
   const uint32_t* F;
-  int64_t stride;        // words per (shard, row)
+  int64_t stride;       // words per (shard, row)
   int rows;
-  int64_t shard_words;   // words of one shard in global word index space (== stride when not sharded)
-  int64_t total_words;   // global words to scan
+  int64_t shard_words;  // words of one shard in global word index space (== stride when not sharded)
+  int64_t total_words;  // global words that hold offers
+  __device__ __forceinline__ uint32_t word(int row, int64_t gw) const {
+    const int64_t shard = gw / shard_words, lw = gw - shard * shard_words;
+    return F[(shard * rows + row) * stride + lw];
+  }
+};
+
+// K3a: set bits per (row, tile of 1024 words).
+#define OE_TILE_WORDS 1024
+__global__ void __launch_bounds__(256) k_tile_popc(RowBits rb, int tiles, int32_t* __restrict__ tile_cnt) {
+  const int row = blockIdx.y, tile = blockIdx.x;
+  int c = 0;
+  for (int q = threadIdx.x; q < OE_TILE_WORDS; q += 256) {
+    const int64_t gw = (int64_t)tile * OE_TILE_WORDS + q;
+    if (gw < rb.total_words) c += __popc(rb.word(row, gw));
+  }
+  __shared__ int sc[256];
+  sc[threadIdx.x] = c;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) sc[threadIdx.x] += sc[threadIdx.x + s];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tile_cnt[(int64_t)row * tiles + tile] = sc[0];
+}
+
+// K3b: one CTA.  Per row: exclusive scan of its tile counts (in place) and the list length min(total, cap); then the
+// exclusive scan of the lengths gives every row's base in the candidate array.  row_base[rows] = total entries.
+__global__ void __launch_bounds__(1024) k_row_offsets(int rows, int tiles, int64_t cap, int32_t* __restrict__ tile_cnt,
+                                                      int64_t* __restrict__ row_base, int32_t* __restrict__ row_len) {
+  __shared__ int64_t carry;
+  __shared__ int64_t warp_sum[32];
+  // per-row tile scans: a warp per row
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int row = warp; row < rows; row += 32) {
+    int32_t* c = tile_cnt + (int64_t)row * tiles;
+    int64_t run = 0;
+    for (int t0 = 0; t0 < tiles; t0 += 32) {
+      const int t = t0 + lane;
+      int v = t < tiles ? c[t] : 0;
+      int incl = v;
+      for (int d = 1; d < 32; d <<= 1) { int n = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += n; }
+      if (t < tiles) c[t] = (int32_t)min((int64_t)0x7fffffff, run + incl - v);
+      run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) row_len[row] = (int32_t)min(run, cap);
+  }
+  __syncthreads();
+  // exclusive scan of row_len over rows
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int r0 = 0; r0 < rows; r0 += 1024) {
+    const int r = r0 + threadIdx.x;
+    int64_t v = r < rows ? row_len[r] : 0;
+    int64_t incl = v;
+    for (int d = 1; d < 32; d <<= 1) { int64_t n = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += n; }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int64_t w = warp_sum[lane], wi = w;
+      for (int d = 1; d < 32; d <<= 1) { int64_t n = __shfl_up_sync(0xffffffffu, wi, d); if (lane >= d) wi += n; }
+      warp_sum[lane] = wi - w;
+    }
+    __syncthreads();
+    const int64_t excl = carry + warp_sum[warp] + incl - v;
+    if (r < rows) row_base[r] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) row_base[rows] = carry;
+}
+
+// K3c: ascending list of feasible GLOBAL offer indices per row (first row_len[r] of them).
+__global__ void __launch_bounds__(256) k_compact_rows(RowBits rb, int tiles, const int32_t* __restrict__ tile_off,
+                                                      const int64_t* __restrict__ row_base, const int32_t* __restrict__ row_len,
+                                                      int32_t* __restrict__ cand) {
+  const int row = blockIdx.y, tile = blockIdx.x;
+  const int len = row_len[row];
+  const int64_t toff = tile_off[(int64_t)row * tiles + tile];
+  if (toff >= len) return;
+  // each thread owns 4 consecutive words of the tile
+  const int64_t gw0 = (int64_t)tile * OE_TILE_WORDS + threadIdx.x * 4;
+  uint32_t w[4];
+  int c = 0;
+  for (int q = 0; q < 4; ++q) {
+    w[q] = (gw0 + q < rb.total_words) ? rb.word(row, gw0 + q) : 0u;
+    c += __popc(w[q]);
+  }
+  __shared__ int warp_tot[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = c;
+  for (int d = 1; d < 32; d <<= 1) { int n = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += n; }
+  if (lane == 31) warp_tot[warp] = incl;
+  __syncthreads();
+  int before = 0;
+  for (int q = 0; q < warp; ++q) before += warp_tot[q];
+  int64_t pos = toff + before + incl - c;
+  int32_t* out = cand + row_base[row];
+  for (int q = 0; q < 4; ++q) {
+    uint32_t x = w[q];
+    while (x) {
+      const int b = __ffs(x) - 1;
+      x &= x - 1;
+      if (pos < len) out[pos] = (int32_t)((gw0 + q) * 32 + b);
+      ++pos;
+    }
+  }
+}
+
+// K2: the greedy commit of PlanScheduler.resourceOffers (S/scheduler/plan/PlanScheduler.java:56-67): requirements in
+// order, each claims the lowest-index feasible offer that no earlier requirement of the cycle claimed.
+//
+// One warp takes 32 consecutive requirements at a time, one per lane.  Every unresolved lane PROPOSES an offer: the
+// (rank)-th unclaimed candidate of its row at or after the row's cursor, where rank counts the unresolved lanes of the
+// same row below it.  Proposals are then RESOLVED in requirement order: the longest prefix of unresolved lanes whose
+// proposals are pairwise distinct is final (an earlier requirement can only disturb a later one by claiming exactly the
+// offer the later one proposed — anything lower that the later one could use is by construction already claimed).  The
+// first lane that lost its offer re-proposes in the next round.  Claimed offers live in a shared-memory bitmap.
+struct CommitArgs {
+  const int32_t* cand;
+  const int64_t* row_base;
+  const int32_t* row_len;
+  int rows;
+  int64_t used_words;
   const int32_t* req_row;
   int64_t M;
   oe_decision* dec;
-  uint32_t* used_g;      // global-memory fallbacks (used when the shared-memory budget is exceeded)
+  uint32_t* used_g;   // global-memory fallbacks (when the shared-memory budget is exceeded)
   int32_t* cursor_g;
   int used_in_smem, cursor_in_smem;
   int* n_placed;
 };
-#define OE_WIN_SLOTS 128
+#define OE_PROPOSE_WINDOW 8
+#define OE_WIN_SLOTS 64     // direct-mapped cache of candidate windows, one row per slot
+#define OE_WIN_ENTRIES 64   // candidates per cached window
 
 __global__ void __launch_bounds__(256) k_commit(CommitArgs a) {
   extern __shared__ uint32_t smem[];
-  uint32_t* win = smem;                                   // [OE_WIN_SLOTS][32]
-  int32_t* win_row = (int32_t*)(win + OE_WIN_SLOTS * 32); // [OE_WIN_SLOTS]
-  int64_t* win_base = (int64_t*)(win_row + OE_WIN_SLOTS); // [OE_WIN_SLOTS]
+  int32_t* win = (int32_t*)smem;                                  // [OE_WIN_SLOTS][OE_WIN_ENTRIES]
+  int32_t* win_row = win + OE_WIN_SLOTS * OE_WIN_ENTRIES;         // [OE_WIN_SLOTS]
+  int32_t* win_base = win_row + OE_WIN_SLOTS;                     // [OE_WIN_SLOTS]
   uint32_t* p = (uint32_t*)(win_base + OE_WIN_SLOTS);
   int32_t* cursor = a.cursor_g;
   if (a.cursor_in_smem) { cursor = (int32_t*)p; p += a.rows; }
   uint32_t* used = a.used_in_smem ? p : a.used_g;
-
-  for (int64_t k = threadIdx.x; k < a.total_words; k += blockDim.x) used[k] = 0;
+  for (int64_t k = threadIdx.x; k < a.used_words; k += blockDim.x) used[k] = 0;
   for (int k = threadIdx.x; k < a.rows; k += blockDim.x) cursor[k] = 0;
   for (int k = threadIdx.x; k < OE_WIN_SLOTS; k += blockDim.x) { win_row[k] = -1; win_base[k] = 0; }
   __syncthreads();
   if (threadIdx.x >= 32) return;
   const int lane = threadIdx.x;
+  const uint32_t lt = (1u << lane) - 1u;
   int placed = 0;
 
   for (int64_t j0 = 0; j0 < a.M; j0 += 32) {
-    const int32_t my_row = (j0 + lane < a.M) ? a.req_row[j0 + lane] : 0;
-    const int nj = (int)min((int64_t)32, a.M - j0);
-    for (int jj = 0; jj < nj; ++jj) {
-      const int row = __shfl_sync(0xffffffffu, my_row, jj);
-      const int slot = row & (OE_WIN_SLOTS - 1);
-      int64_t cur = cursor[row];
-      int64_t found = -1;
-      while (cur < a.total_words) {
-        // window of 32 consecutive words of this row starting at `cur` (cached when the cursor did not leave it)
-        const bool hit = win_row[slot] == row && win_base[slot] == cur;
-        const int64_t gw = cur + lane;
-        uint32_t f;
-        if (hit) {
-          f = win[slot * 32 + lane];
-        } else {
-          f = 0;
-          if (gw < a.total_words) {
-            const int64_t shard = gw / a.shard_words, lw = gw - shard * a.shard_words;
-            f = a.F[(shard * a.rows + row) * a.stride + lw];
-          }
-          __syncwarp();
-          win[slot * 32 + lane] = f;
-          if (lane == 0) { win_row[slot] = row; win_base[slot] = cur; }
-        }
-        const uint32_t w = (gw < a.total_words) ? (f & ~used[gw]) : 0u;
-        const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
-        if (m) {
-          const int L = __ffs(m) - 1;
-          const uint32_t wl = __shfl_sync(0xffffffffu, w, L);
-          const int b = __ffs(wl) - 1;
-          found = (cur + L) * 32 + b;
-          if (lane == L) used[gw] |= 1u << b;
-          break;  // cursor stays on this window: lower words of it are exhausted for good, `used` masks the rest
-        }
-        cur += 32;
+    const bool active = j0 + lane < a.M;
+    const int row = active ? a.req_row[j0 + lane] : -1 - lane;
+    const int len = active ? a.row_len[row] : 0;
+    const int32_t* list = active ? a.cand + a.row_base[row] : nullptr;
+    const int slot = row & (OE_WIN_SLOTS - 1);
+    bool final = !active;
+    int pick = -1;
+    uint32_t open = __ballot_sync(0xffffffffu, !final);
+    while (open) {
+      // ---- make sure the window [cursor, cursor + OE_PROPOSE_WINDOW) of every unresolved lane's row is cached
+      int k = 0;
+      bool need = false;
+      if (!final) {
+        k = cursor[row];
+        need = !(win_row[slot] == row && win_base[slot] <= k && k + OE_PROPOSE_WINDOW <= win_base[slot] + OE_WIN_ENTRIES);
+      }
+      uint32_t needs = __ballot_sync(0xffffffffu, need);
+      while (needs) {
+        const int leader = __ffs(needs) - 1;
+        const int r = __shfl_sync(0xffffffffu, row, leader);
+        const int kk = __shfl_sync(0xffffffffu, k, leader);
+        const int rl = __shfl_sync(0xffffffffu, len, leader);
+        const int32_t* rlist = a.cand + a.row_base[r];
+        const int rs = r & (OE_WIN_SLOTS - 1);
         __syncwarp();
+        win[rs * OE_WIN_ENTRIES + lane] = (kk + lane < rl) ? __ldg(rlist + kk + lane) : -1;
+        win[rs * OE_WIN_ENTRIES + 32 + lane] = (kk + 32 + lane < rl) ? __ldg(rlist + kk + 32 + lane) : -1;
+        if (lane == leader) { win_row[rs] = r; win_base[rs] = kk; }
+        __syncwarp();
+        needs &= ~(1u << leader);
+        // other lanes of the same row at the same cursor are served by this refill
+        needs &= ~__ballot_sync(0xffffffffu, need && row == r);
       }
-      if (lane == 0) {
-        cursor[row] = (int32_t)min(cur, a.total_words);
-        a.dec[j0 + jj].offer_row = (int32_t)found;
+      // ---- propose
+      int prop = -2;  // -2 = cannot tell yet, -1 = the row has nothing left for this lane, >= 0 = offer
+      int prop_k = 0, scanned_to = 0;
+      if (!final) {
+        const uint32_t peers = __match_any_sync(open, row);
+        const int rank = __popc(peers & lt);
+        int o[OE_PROPOSE_WINDOW];
+        const bool hit = win_row[slot] == row && win_base[slot] <= k && k + OE_PROPOSE_WINDOW <= win_base[slot] + OE_WIN_ENTRIES;
+        if (hit) {
+          const int32_t* w = win + slot * OE_WIN_ENTRIES + (k - win_base[slot]);
+#pragma unroll
+          for (int t = 0; t < OE_PROPOSE_WINDOW; ++t) o[t] = w[t];
+        } else {  // slot stolen by another row of this batch: read through
+#pragma unroll
+          for (int t = 0; t < OE_PROPOSE_WINDOW; ++t) o[t] = (k + t < len) ? __ldg(list + k + t) : -1;
+        }
+        uint32_t unused = 0;
+#pragma unroll
+        for (int t = 0; t < OE_PROPOSE_WINDOW; ++t)
+          if (o[t] >= 0 && !((used[o[t] >> 5] >> (o[t] & 31)) & 1u)) unused |= 1u << t;
+        const int n_unused = __popc(unused);
+        if (rank < n_unused) {
+          const int t = __fns(unused, 0, rank + 1);
+          prop_k = k + t;
+#pragma unroll
+          for (int q = 0; q < OE_PROPOSE_WINDOW; ++q) if (q == t) prop = o[q];
+        } else if (k + OE_PROPOSE_WINDOW >= len) {
+          prop = -1;  // list exhausted: fewer unclaimed candidates than earlier requirements of this row will take
+        } else if (rank == 0) {
+          scanned_to = k + OE_PROPOSE_WINDOW;  // whole window claimed: move the cursor and look again
+        }
       }
-      placed += found >= 0;
+      // ---- resolve in requirement order
+      bool ok = false;
+      if (!final) {
+        const uint32_t proposing = __ballot_sync(open, prop >= 0);
+        if (prop == -1) {
+          ok = true;
+        } else if (prop >= 0) {
+          const uint32_t grp = __match_any_sync(proposing, prop);
+          ok = (__ffs(grp) - 1) == lane;
+        }
+      }
+      const uint32_t bad = __ballot_sync(0xffffffffu, !final && !ok);
+      const int first_bad = bad ? __ffs(bad) - 1 : 32;
+      if (!final && lane < first_bad) {
+        final = true;
+        pick = prop;
+        if (prop >= 0) {
+          atomicOr(&used[prop >> 5], 1u << (prop & 31));
+          atomicMax(&cursor[row], prop_k + 1);
+        }
+      } else if (!final && scanned_to > 0) {
+        atomicMax(&cursor[row], scanned_to);
+      }
       __syncwarp();
+      open = __ballot_sync(0xffffffffu, !final);
     }
+    if (active) a.dec[j0 + lane].offer_row = pick;
+    placed += __popc(__ballot_sync(0xffffffffu, pick >= 0));
   }
   if (lane == 0) *a.n_placed = placed;
 }
@@ -260,7 +432,7 @@ __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, in
   dec[j] = d;
 }
 
-// K3: multi-cycle replay.  One thread per stored task: copies the winning offer's placement columns into a task row.
+// K4: multi-cycle replay.  One thread per stored task: copies the winning offer's placement columns into a task row.
 struct LaunchArgs {
   int64_t n;
   const int32_t* dst_row;   // task row to (over)write
@@ -359,7 +531,7 @@ struct oe_engine {
 
   // ---- derived / outputs
   DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced;
-  DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter;
+  DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
   cudaEvent_t ev[8]{};
@@ -493,7 +665,8 @@ void oe_destroy(oe_engine* h) {
                    &h->d_present, &h->d_port, &h->d_msize, &h->d_mprof, &h->d_oattr, &h->d_orr, &h->d_oexec, &h->d_rbegin, &h->d_rid,
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
-                   &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter};
+                   &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -970,35 +1143,60 @@ int run_expand(oe_engine* h, int64_t* launches) {
 int run_commit(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
-  CommitArgs a{};
+  RowBits rb{};
+  rb.stride = stride; rb.rows = rows;
   if (h->world > 1) {
-    a.F = h->d_Fglobal.as<uint32_t>();
-    a.shard_words = h->shard_rows / 32;
-    a.total_words = std::min<int64_t>((h->N_global + 31) / 32, (int64_t)h->world * a.shard_words);
+    rb.F = h->d_Fglobal.as<uint32_t>();
+    rb.shard_words = h->shard_rows / 32;
+    rb.total_words = std::min<int64_t>((h->N_global + 31) / 32, (int64_t)h->world * rb.shard_words);
   } else {
-    a.F = h->d_F.as<uint32_t>();
-    a.shard_words = stride;
-    a.total_words = (h->N + 31) / 32;
+    rb.F = h->d_F.as<uint32_t>();
+    rb.shard_words = stride;
+    rb.total_words = (h->N + 31) / 32;
   }
-  a.stride = stride; a.rows = rows; a.req_row = h->d_req_row.as<int32_t>(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
-  a.n_placed = h->d_nplaced.as<int>();
-  size_t smem = (size_t)OE_WIN_SLOTS * 32 * 4 + OE_WIN_SLOTS * 4 + OE_WIN_SLOTS * 8;
-  const size_t budget = (size_t)h->smem_optin;
-  a.cursor_in_smem = smem + (size_t)rows * 4 <= budget / 4;
-  if (a.cursor_in_smem) smem += (size_t)rows * 4;
-  else { CU(h->d_cursor.ensure(std::max<size_t>(rows, 1) * 4)); a.cursor_g = h->d_cursor.as<int32_t>(); }
-  a.used_in_smem = smem + (size_t)a.total_words * 4 <= budget;
-  if (a.used_in_smem) smem += (size_t)a.total_words * 4;
-  else { CU(h->d_used.ensure(std::max<size_t>(a.total_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
   CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->stream));
+  if (rows == 0 || h->M == 0) {
+    CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
+    return 0;
+  }
+  // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
+  const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
+  const int64_t cap = h->M + 2 * OE_PROPOSE_WINDOW;
+  CU(h->d_tile_cnt.ensure((size_t)rows * tiles * 4));
+  CU(h->d_row_base.ensure(((size_t)rows + 1) * 8));
+  CU(h->d_row_len.ensure((size_t)rows * 4));
+  dim3 tgrid((unsigned)tiles, (unsigned)rows);
+  k_tile_popc<<<tgrid, 256, 0, h->stream>>>(rb, tiles, h->d_tile_cnt.as<int32_t>());
+  k_row_offsets<<<1, 1024, 0, h->stream>>>(rows, tiles, cap, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>());
+  *launches += 2;
+  CU(cudaGetLastError());
+  int64_t n_cand = 0;
+  CU(cudaMemcpyAsync(&n_cand, h->d_row_base.as<int64_t>() + rows, 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  CU(h->d_cand.ensure(std::max<size_t>((size_t)n_cand, 1) * 4));
+  k_compact_rows<<<tgrid, 256, 0, h->stream>>>(rb, tiles, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(),
+                                               h->d_cand.as<int32_t>());
+  ++*launches;
+  CU(cudaGetLastError());
+
+  CommitArgs a{};
+  a.cand = h->d_cand.as<int32_t>(); a.row_base = h->d_row_base.as<int64_t>(); a.row_len = h->d_row_len.as<int32_t>();
+  a.rows = rows; a.used_words = rb.total_words; a.req_row = h->d_req_row.as<int32_t>(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
+  a.n_placed = h->d_nplaced.as<int>();
+  size_t smem = (size_t)OE_WIN_SLOTS * OE_WIN_ENTRIES * 4 + OE_WIN_SLOTS * 8;
+  const size_t budget = (size_t)h->smem_optin;
+  a.cursor_in_smem = (size_t)rows * 4 <= budget / 4;
+  if (a.cursor_in_smem) smem += (size_t)rows * 4;
+  else { CU(h->d_cursor.ensure((size_t)rows * 4)); a.cursor_g = h->d_cursor.as<int32_t>(); }
+  a.used_in_smem = smem + (size_t)a.used_words * 4 <= budget;
+  if (a.used_in_smem) smem += (size_t)a.used_words * 4;
+  else { CU(h->d_used.ensure(std::max<size_t>(a.used_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
   k_commit<<<1, 256, smem, h->stream>>>(a);
   ++*launches;
   CU(cudaGetLastError());
-  if (h->M > 0) {
-    k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
-    ++*launches;
-    CU(cudaGetLastError());
-  }
+  k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+  ++*launches;
+  CU(cudaGetLastError());
   return 0;
 }
 

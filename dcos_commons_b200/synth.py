@@ -140,7 +140,16 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
     if T > 0:
         t_type = np.repeat(np.arange(Cn, dtype=np.int32), deployed_per_class)
         t_index = np.tile(np.arange(deployed_per_class, dtype=np.int32), Cn)
-        t_agent = rng.integers(0, N, T).astype(np.int32)
+        if rules == "c5":
+            # pods deployed earlier obeyed the same RegionRule: class c lives in region c % n_regions
+            by_region = [np.flatnonzero(region == r) for r in range(n_regions)]
+            t_agent = np.empty(T, np.int32)
+            for c in range(Cn):
+                pool = by_region[c % n_regions]
+                sel = slice(c * deployed_per_class, (c + 1) * deployed_per_class)
+                t_agent[sel] = pool[rng.integers(0, len(pool), deployed_per_class)] if len(pool) else rng.integers(0, N, deployed_per_class)
+        else:
+            t_agent = rng.integers(0, N, T).astype(np.int32)
         fb = np.zeros((FW, T), np.uint32)
         fb[t_type >> 5, np.arange(T)] = (np.uint32(1) << (t_type & 31).astype(np.uint32))
         tasks = dict(t_name_id=np.arange(T, dtype=np.int32), t_pod_type_id=t_type, t_pod_index=t_index, t_agent_id=t_agent,
