@@ -471,3 +471,21 @@ def unpack_bits(matrix: np.ndarray, n_offers: int) -> np.ndarray:
     """[rows, stride] uint32 words → [rows, n_offers] bool."""
     b = np.unpackbits(matrix.view(np.uint8), axis=1, bitorder="little")
     return b[:, :n_offers].astype(bool)
+
+
+OE_STATIC_MAX_OFFERS, OE_STATIC_MAX_ROWS = 4 * 1024 * 1024, 8192
+
+
+def first_fit_static(device: int, stream: int, d_row_bits: int, stride_words: int, n_rows: int, n_offers: int, d_req_row: int,
+                     n_reqs: int, d_offer_row: int) -> None:
+    """oe_first_fit_static (include/oe_abi.h): ordered first-fit over bit rows that already sit in device memory, for hosts
+    that cannot let the library allocate.  All three pointers are raw DEVICE addresses owned by the caller; the kernel is
+    only enqueued on `stream` — synchronise before reading the result.  Raises EngineError with the library's text."""
+    f = engine_library().fn("first_fit_static")
+    f.argtypes = [C.c_int32, _p, _p, C.c_int64, C.c_int32, C.c_int64, _p, C.c_int64, _p, C.c_char_p, C.c_int32]
+    f.restype = C.c_int32
+    err = C.create_string_buffer(512)
+    rc = f(device, stream or None, d_row_bits or None, stride_words, n_rows, n_offers, d_req_row or None, n_reqs, d_offer_row or None,
+           err, len(err))
+    if rc != 0:
+        raise EngineError(rc, err.value.decode())

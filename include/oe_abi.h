@@ -405,6 +405,33 @@ int32_t oe_device_buffer(oe_engine* h, int32_t which, void** dev_ptr, int64_t* n
 /* The stream the engine launches on (cudaStream_t), so that callers can order their own work / events after it.   */
 void* oe_stream(oe_engine* h);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * Allocation-free first-fit.  This entry point has no counterpart in the reference (the JVM allocates freely); it
+ * exists for hosts that cannot let this library call cudaMalloc/cudaFree on their behalf: a multi-service scheduler
+ * running several engines on one GPU (an allocation or free synchronises the whole device and would stall the other
+ * services' cycles), or a process whose device memory is owned up front by a pool or capped by an operator budget.
+ *
+ * Computes the `offer_row` column of oe_evaluate_cycle — requirements in order, each takes the lowest-index offer
+ * whose bit is set in its row and that no earlier requirement took (S/scheduler/plan/PlanScheduler.java:56-67) —
+ * from bit rows, a requirement→row map and into a result column that all live in DEVICE memory owned by the caller:
+ *   d_row_bits  [n_rows][stride_words]  bit (i & 31) of word [r * stride_words + (i >> 5)] = offer i fits row r
+ *                                       (the layout of OE_BUF_CLASS_BITS_LOCAL)
+ *   d_req_row   [n_reqs]                bit row of each requirement, in plan order (out-of-range row ⇒ no offer)
+ *   d_offer_row [n_reqs]                result: offer index, or -1 when nothing is left for that requirement
+ * The kernel is enqueued on `stream` (a cudaStream_t, NULL = default stream) of `device` and the call returns without
+ * waiting for it.  No memory is allocated or freed, on the device or the host.  The working memory (one "taken" bit
+ * per offer, one cursor per row) is a fixed array compiled into the library, held by every GPU that loads it until
+ * the process exits (~544 KiB); hence the limits below, beyond which the call returns OE_ERR_LIMIT with an
+ * explanation in err_text.  The first call on a given device also looks up that array's device address; make that
+ * first call outside any stream capture.  All calls on one device share the array: the kernel re-zeroes what it uses,
+ * but two calls whose kernels overlap on the GPU (different streams, or different host threads) corrupt each other —
+ * serialise them.  err_text (err_cap bytes, may be NULL) receives the text of a failure.                              */
+#define OE_STATIC_MAX_OFFERS (4 * 1024 * 1024)
+#define OE_STATIC_MAX_ROWS 8192
+int32_t oe_first_fit_static(int32_t device, void* stream, const uint32_t* d_row_bits, int64_t stride_words, int32_t n_rows,
+                            int64_t n_offers, const int32_t* d_req_row, int64_t n_reqs, int32_t* d_offer_row,
+                            char* err_text, int32_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif
