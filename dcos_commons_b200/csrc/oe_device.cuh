@@ -140,11 +140,13 @@ struct OfferKeys {
 };
 
 // Postfix rule program over a bit-stack (bit 0 = top).
-__device__ inline bool eval_rule(const DevCtx& cx, int64_t i, const OfferKeys& ok, int var, int32_t begin, int32_t count) {
+// `nodes` is the node array the program indexes: the global one, or a CTA's shared-memory copy of it.
+__device__ inline bool eval_rule(const DevCtx& cx, const oe_rule_node* nodes, int64_t i, const OfferKeys& ok, int var, int32_t begin,
+                                 int32_t count) {
   uint64_t st = 0;
   const DevOffers& o = cx.o;
   for (int32_t n = begin; n < begin + count; ++n) {
-    const oe_rule_node nd = cx.p.nodes[n];
+    const oe_rule_node nd = nodes[n];
     bool v = false;
     switch (nd.op) {
       case OE_R_TRUE: v = true; break;
@@ -333,7 +335,7 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
     switch (op.opcode) {
       case OE_OP_NOP: break;
       case OE_OP_EXEC_ID: pass = op.arg < 0 || offer_has_exec(o, i, op.arg); break;
-      case OE_OP_RULE: pass = eval_rule(cx, i, ok, var, op.arg, (int32_t)op.aux); break;
+      case OE_OP_RULE: pass = eval_rule(cx, cx.p.nodes, i, ok, var, op.arg, (int32_t)op.aux); break;
       case OE_OP_SCALAR_NEW: {
         const int q = op.slot * o.K + op.kind;
         const double avail = ps.val[q];
@@ -415,6 +417,114 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
   }
   if (RECORD) dec->n_new_reservations = n_res;
   return all;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Folded form of a new-pod pipeline (OfferEvaluator.java:411-522): what oe_load_programs derives from a class whose ops
+// are only NOP / EXEC_ID(new) / one RULE / SCALAR_NEW / PORT_STATIC / unconstrained PORT_DYNAMIC on role slot 0.
+//   * Scalars.  The stages of one (slot, kind) pool form a chain  d = a_k - v; fail if d > 0; v = v - a_k  (ValueUtils
+//     subtract + compare, MesosResourcePool.java:330-372).  Every step is monotone in the starting value, so the set of
+//     starting values that pass the whole chain is {v >= thr}; the host finds thr by bisection over the doubles while
+//     running the literal chain, hence `!(v < thr)` is exact, rounding included (NaN passes, as it does in the chain).
+//   * Ports.  `port` lists the distinct ports that are requested statically or excluded from dynamic selection
+//     (PortEvaluationStage.java:252-261).  All static ones must be offered; the dynamic stages succeed iff the offered
+//     ports that are not listed number at least n_dyn (each takes the lowest one left, :276-294).
+// Anything else (existing-pod ops, MOUNT volumes, constrained dynamic ports, other role slots) runs through eval_pair.
+struct alignas(16) FastRow {
+  double thr[8];
+  uint16_t port[16];
+  uint8_t thr_q[8];       // pool index slot * K + kind of each threshold
+  uint32_t flags;         // OE_FR_*
+  int32_t rule_begin, rule_count;
+  uint32_t static_mask;   // bit u: port[u] is requested statically
+  uint8_t n_thr, n_ports, n_dyn, reserved0;
+  int32_t pod_role;
+};
+static_assert(sizeof(FastRow) == 128, "FastRow is staged as eight uint4");
+#define OE_FR_FAST 1u        // the folded form is valid for this class
+#define OE_FR_NEVER 2u       // a static port is requested twice: the second stage can never pass
+#define OE_FR_NEEDS_POOL 4u  // has scalar or port stages: an offer allocated to another role fails
+
+#define OE_FAST_RANGES 8
+
+// Offer row state a thread keeps across all the classes it evaluates.
+struct OfferRegs {
+  OfferKeys ok;
+  int32_t alloc;
+  uint32_t present;
+  uint32_t rb[OE_FAST_RANGES], rlen[OE_FAST_RANGES];  // slot-0 port ranges: begin and (end - begin); empty = never matches
+  int32_t pool_ports;                                 // offered ports of slot 0
+};
+
+__device__ __forceinline__ void load_offer_regs(const DevOffers& o, int64_t i, bool reg_ranges, OfferRegs& r) {
+  r.ok.agent = __ldg(o.agent + i);
+  r.ok.host = __ldg(o.host + i);
+  r.ok.zone = __ldg(o.zone + i);
+  r.ok.region = __ldg(o.region + i);
+  r.alloc = __ldg(o.alloc + i);
+  r.present = __ldg(o.present + i);
+  r.pool_ports = 0;
+  if (reg_ranges) {
+#pragma unroll
+    for (int q = 0; q < OE_FAST_RANGES; ++q) {
+      uint32_t pr = q < o.R ? __ldg(o.port + (int64_t)q * o.N + i) : OE_PORT_EMPTY;
+      const uint32_t b = pr & 0xFFFFu, e = pr >> 16;
+      const bool some = b <= e;
+      r.rb[q] = some ? b : 0x100000u;
+      r.rlen[q] = some ? e - b : 0u;
+      r.pool_ports += some ? (int32_t)(e - b + 1) : 0;
+    }
+  }
+}
+
+__device__ __forceinline__ bool port_member(const DevOffers& o, int64_t i, bool reg_ranges, const OfferRegs& r, uint32_t p) {
+  bool m = false;
+  if (reg_ranges) {
+#pragma unroll
+    for (int q = 0; q < OE_FAST_RANGES; ++q) m = m || (p - r.rb[q]) <= r.rlen[q];
+  } else {
+    m = port_in_pool(o, i, 0, o.R, (int)p);
+  }
+  return m;
+}
+
+// `sc` = this CTA's shared-memory copy of the scalar columns, [S*K][blockDim.x], or nullptr (read through L1 instead).
+template <bool REG_RANGES>
+__device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* nodes, const FastRow& fr, const double* sc, int64_t i,
+                                          const OfferRegs& r, int var) {
+  const DevOffers& o = cx.o;
+  bool pass = !(fr.flags & OE_FR_NEVER);
+  uint32_t present = r.present;
+  if (fr.flags & OE_FR_NEEDS_POOL) {
+    // consumableResource (MesosResourcePool.java:87-97)
+    pass = pass && !(fr.pod_role >= 0 && r.alloc >= 0 && r.alloc != fr.pod_role);
+  }
+  for (int t = 0; t < fr.n_thr; ++t) {
+    const int q = fr.thr_q[t];
+    const double v = sc ? sc[q * blockDim.x + threadIdx.x] : __ldg(o.scalar + (int64_t)q * o.N + i);
+    pass = pass && ((present >> q) & 1u) && !(v < fr.thr[t]);
+  }
+  if (fr.n_ports | fr.n_dyn) {
+    int listed = 0;
+    bool statics = true;
+    int pool_ports = r.pool_ports;
+    if (!REG_RANGES) {
+      pool_ports = 0;
+      for (int q = 0; q < o.R; ++q) {
+        const uint32_t pr = __ldg(o.port + (int64_t)q * o.N + i);
+        const int b = pr & 0xFFFF, e = pr >> 16;
+        pool_ports += b <= e ? e - b + 1 : 0;
+      }
+    }
+    for (int u = 0; u < fr.n_ports; ++u) {
+      const bool m = port_member(o, i, REG_RANGES, r, fr.port[u]);
+      listed += m;
+      statics = statics && (m || !((fr.static_mask >> u) & 1u));
+    }
+    pass = pass && statics && (pool_ports - listed >= (int)fr.n_dyn);
+  }
+  if (fr.rule_count > 0) pass = pass && eval_rule(cx, nodes, i, r.ok, var, fr.rule_begin, fr.rule_count);
+  return pass;
 }
 
 }  // namespace oe

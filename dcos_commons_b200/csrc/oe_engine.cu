@@ -16,6 +16,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -34,6 +35,23 @@ __global__ void k_validate_ids(const int32_t* __restrict__ col, int64_t n, int32
   if (i < n) {
     int32_t v = col[i];
     if (v < lo || v >= hi) atomicMax(err, code);
+  }
+}
+
+// The `ports` ranges of one (offer, role slot) must be ascending and disjoint (the host merges them the way antlr's
+// IntervalSet does, S/offer/RangeUtils.java:23-47): the folded port test counts offered ports by range length.
+__global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, int S, int R, int code, int* err) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int s = 0; s < S; ++s) {
+    int prev_e = -1;
+    for (int r = 0; r < R; ++r) {
+      const uint32_t pr = port[((int64_t)s * R + r) * n + i];
+      const int b = pr & 0xFFFF, e = pr >> 16;
+      if (b > e) continue;
+      if (b <= prev_e) atomicMax(err, code);
+      prev_e = e;
+    }
   }
 }
 
@@ -97,56 +115,87 @@ __global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __
   }
 }
 
-// K1: thread = one offer row, blockIdx.y = a tile of factored rows (classes first, then variants).  Each warp emits
-// one 32-offer word per row with __ballot_sync.  gridDim.x covers the padded stride so every word is written.
+// K1: thread = one offer row, blockIdx.y = a tile of factored rows (classes first, then variants).  The CTA stages the
+// tile's folded class descriptors, the rule nodes and its 128 offers' scalar columns in shared memory; a thread loads
+// its offer's keys and port ranges into registers once and then walks the tile's rows.  Each warp emits one 32-offer
+// word per row with __ballot_sync.  gridDim.x covers the padded stride so every word is written.
 #define OE_K1_THREADS 128
-__global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, uint32_t* __restrict__ F, int64_t stride,
-                                                                     int rows, int rows_per_tile) {
+#define OE_K1_MAX_SMEM_NODES 1024
+struct K1Args {
+  uint32_t* F;
+  int64_t stride;
+  int rows, rows_per_tile;
+  const FastRow* fast;   // [C]
+  int n_nodes;           // rule nodes staged in shared memory (0 = read them from global memory)
+  int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
+};
+template <bool REG_RANGES>
+__global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, K1Args a) {
+  extern __shared__ __align__(16) unsigned char k1_smem[];
+  FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
+  oe_rule_node* s_nodes = reinterpret_cast<oe_rule_node*>(s_fast + a.rows_per_tile);
+  double* s_sc = reinterpret_cast<double*>(s_nodes + a.n_nodes);
+  const int r0 = blockIdx.y * a.rows_per_tile;
+  const int r1 = min(a.rows, r0 + a.rows_per_tile);
   const int64_t i = (int64_t)blockIdx.x * OE_K1_THREADS + threadIdx.x;
   const bool valid = i < cx.o.N;
-  OfferKeys ok{0, 0, -1, -1};
-  if (valid) {
-    ok.agent = __ldg(cx.o.agent + i);
-    ok.host = __ldg(cx.o.host + i);
-    ok.zone = __ldg(cx.o.zone + i);
-    ok.region = __ldg(cx.o.region + i);
+  {  // stage
+    const uint4* src = reinterpret_cast<const uint4*>(a.fast);
+    uint4* dst = reinterpret_cast<uint4*>(s_fast);
+    for (int q = threadIdx.x; q < (r1 - r0) * 8; q += OE_K1_THREADS) {
+      const int row = r0 + (q >> 3);
+      const int cls = row < cx.p.C ? row : cx.v.cls[row - cx.p.C];
+      dst[q] = __ldg(src + (int64_t)cls * 8 + (q & 7));
+    }
+    const uint4* nsrc = reinterpret_cast<const uint4*>(cx.p.nodes);
+    uint4* ndst = reinterpret_cast<uint4*>(s_nodes);
+    for (int q = threadIdx.x; q < a.n_nodes; q += OE_K1_THREADS) ndst[q] = __ldg(nsrc + q);
+    if (valid)
+      for (int q = 0; q < a.sc_cols; ++q) s_sc[q * OE_K1_THREADS + threadIdx.x] = __ldg(cx.o.scalar + (int64_t)q * cx.o.N + i);
   }
-  const int r0 = blockIdx.y * rows_per_tile;
-  const int r1 = min(rows, r0 + rows_per_tile);
+  __syncthreads();
+  OfferRegs regs;
+  regs.ok = OfferKeys{0, 0, -1, -1};
+  if (valid) load_offer_regs(cx.o, i, REG_RANGES, regs);
+  const oe_rule_node* nodes = a.n_nodes ? s_nodes : cx.p.nodes;
+  const double* sc = a.sc_cols ? s_sc : nullptr;
   const int64_t word = i >> 5;
   for (int row = r0; row < r1; ++row) {
+    const FastRow& fr = s_fast[row - r0];
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
-    const int cls = var < 0 ? row : cx.v.cls[var];
     bool pass = false;
-    if (valid) pass = eval_pair<false>(cx, i, ok, cls, var, nullptr);
+    if (fr.flags & OE_FR_FAST) {
+      if (valid) pass = eval_fast<REG_RANGES>(cx, nodes, fr, sc, i, regs, var);
+    } else if (valid) {
+      const int cls = var < 0 ? row : cx.v.cls[var];
+      pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
+    }
     const uint32_t bits = __ballot_sync(0xffffffffu, pass);
-    if ((threadIdx.x & 31) == 0 && word < stride) F[(int64_t)row * stride + word] = bits;
+    if ((threadIdx.x & 31) == 0 && word < a.stride) a.F[(int64_t)row * a.stride + word] = bits;
   }
 }
 
-// K1x: out[j][w] = F[req_row[j]][w].  A warp moves one 512-byte row segment (uint4 per lane) per requirement; the
-// source rows of one word tile stay L1/L2 resident, the 128-bit streaming stores are the only HBM traffic.
-#define OE_KX_THREADS 256
-__global__ void __launch_bounds__(OE_KX_THREADS) k_expand_matrix(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row,
-                                                                 uint32_t* __restrict__ out, int64_t stride, int64_t M,
-                                                                 int reqs_per_block) {
-  const int64_t w4 = ((int64_t)blockIdx.x * OE_KX_THREADS + threadIdx.x) * 4;  // first word of this lane's uint4
+// K1x: out[j][w] = F[req_row[j]][w].  CTA = (1 KiB column slab) x (a block of requirements): 64 lanes of uint4 across,
+// 4 requirements in flight down.  The source rows of a slab stay L1/L2 resident; the 128-bit streaming stores are the
+// only HBM traffic.  Sized by tools/bw_probe.cu: 1 KiB slabs with ~32 CTAs per SM write at the copy-bandwidth peak.
+#define OE_KX_LANES 64
+#define OE_KX_ROWS 4
+__global__ void __launch_bounds__(OE_KX_LANES * OE_KX_ROWS) k_expand_matrix(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row,
+                                                                            uint32_t* __restrict__ out, int64_t stride, int64_t M,
+                                                                            int reqs_per_block) {
+  const int64_t w4 = ((int64_t)blockIdx.x * OE_KX_LANES + threadIdx.x) * 4;  // first word of this lane's uint4
   if (w4 >= stride) return;
   const int64_t j0 = (int64_t)blockIdx.y * reqs_per_block;
   const int64_t j1 = min(M, j0 + reqs_per_block);
-  int64_t j = j0;
-  for (; j + 4 <= j1; j += 4) {
-    const int32_t ra = __ldg(req_row + j), rb = __ldg(req_row + j + 1), rc = __ldg(req_row + j + 2), rd = __ldg(req_row + j + 3);
+  int64_t j = j0 + threadIdx.y;
+  for (; j + OE_KX_ROWS < j1; j += 2 * OE_KX_ROWS) {
+    const int32_t ra = __ldg(req_row + j), rb = __ldg(req_row + j + OE_KX_ROWS);
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)ra * stride + w4));
     const uint4 b = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rb * stride + w4));
-    const uint4 c = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rc * stride + w4));
-    const uint4 d = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)rd * stride + w4));
-    __stcs(reinterpret_cast<uint4*>(out + (j + 0) * stride + w4), a);
-    __stcs(reinterpret_cast<uint4*>(out + (j + 1) * stride + w4), b);
-    __stcs(reinterpret_cast<uint4*>(out + (j + 2) * stride + w4), c);
-    __stcs(reinterpret_cast<uint4*>(out + (j + 3) * stride + w4), d);
+    __stcs(reinterpret_cast<uint4*>(out + j * stride + w4), a);
+    __stcs(reinterpret_cast<uint4*>(out + (j + OE_KX_ROWS) * stride + w4), b);
   }
-  for (; j < j1; ++j) {
+  for (; j < j1; j += OE_KX_ROWS) {
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)__ldg(req_row + j) * stride + w4));
     __stcs(reinterpret_cast<uint4*>(out + j * stride + w4), a);
   }
@@ -506,6 +555,11 @@ struct oe_engine {
   std::vector<oe_counter_set> h_csets;
   std::vector<int64_t> h_cs_off;
   std::vector<uint8_t> class_self_sensitive;
+  std::vector<int32_t> h_pod_role, h_excl_begin;
+  std::vector<uint16_t> h_excl;
+  int n_rule_nodes = 0;
+  int fast_K = -1;  // scalar-kind count the folded class descriptors were built for (-1 = stale)
+  DevBuf d_fast;
   DevBuf d_op_begin, d_ops, d_nodes, d_pod_role, d_excl_begin, d_excl, d_rs_begin, d_rs, d_csets, d_cs_off, d_ts_type, d_mbits;
   DevProg dp{};
 
@@ -591,7 +645,8 @@ int fetch_err_flag(oe_engine* h, const char* what) {
   CU(cudaStreamSynchronize(h->stream));
   if (flag) {
     CU(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
-    return h->fail(OE_ERR_INVALID, "%s: id column %d holds a value outside its dictionary", what, flag);
+    return h->fail(OE_ERR_INVALID, flag == 18 ? "%s: a ports column holds ranges that are not ascending and disjoint (code %d)"
+                                              : "%s: id column %d holds a value outside its dictionary", what, flag);
   }
   return 0;
 }
@@ -666,7 +721,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
-                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand};
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -787,6 +842,11 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   h->h_op_begin.assign(t->op_begin, t->op_begin + C + 1);
   h->h_ops.assign(t->ops, t->ops + t->n_ops);
   h->h_nodes.assign(t->rule_nodes, t->rule_nodes + t->n_rule_nodes);
+  h->h_pod_role.assign(t->pod_role, t->pod_role + C);
+  h->h_excl_begin.assign(t->port_excl_begin, t->port_excl_begin + C + 1);
+  h->h_excl.assign(t->port_excl, t->port_excl + t->port_excl_begin[C]);
+  h->n_rule_nodes = t->n_rule_nodes;
+  h->fast_K = -1;
 
   if (int rc = upload(h, h->d_op_begin, t->op_begin, (size_t)C + 1)) return rc;
   if (int rc = upload(h, h->d_ops, t->ops, (size_t)t->n_ops)) return rc;
@@ -977,6 +1037,8 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   check_ids(h, o.attr, N * o.A, -1, dc.n_attrs, 15);
   check_ids(h, o.rr, N * o.Q, -1, dc.n_rr_values, 16);
   check_ids(h, o.mprof, N * o.D, -1, OE_MAX_PROFILES, 17);
+  if (N > 0 && o.R > 0)
+    k_validate_ranges<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(o.port, N, o.S, o.R, 18, h->d_err.as<int>());
   if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
   h->hasO = true;
   return OE_OK;
@@ -1103,18 +1165,141 @@ int run_counters(oe_engine* h, int64_t* launches) {
   return 0;
 }
 
+// ---- folding of new-pod pipelines into FastRow descriptors (see oe_device.cuh)
+inline uint64_t double_order_key(double d) {  // monotone map of the non-NaN doubles onto unsigned integers
+  uint64_t u;
+  std::memcpy(&u, &d, 8);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+inline double double_from_key(uint64_t k) {
+  const uint64_t u = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+  double d;
+  std::memcpy(&d, &u, 8);
+  return d;
+}
+// The literal stage chain on one pool entry (MesosResourcePool.java:330-372 over ValueUtils.java:103-106,144-155).
+inline bool scalar_chain_passes(double v, const std::vector<double>& amounts) {
+  for (double a : amounts) {
+    volatile double d = a - v;
+    if (d > 0.0) return false;
+    volatile double nv = v - a;
+    v = nv;
+  }
+  return true;
+}
+// Smallest starting value for which the chain passes; false when the chain is not of the foldable kind.
+bool fold_scalar_chain(const std::vector<double>& amounts, double* thr) {
+  for (double a : amounts) if (a != a) return false;
+  const double inf = std::numeric_limits<double>::infinity();
+  if (!scalar_chain_passes(inf, amounts)) return false;
+  uint64_t lo = double_order_key(-inf), hi = double_order_key(inf);  // invariant: passes(hi)
+  if (scalar_chain_passes(-inf, amounts)) { *thr = -inf; return true; }
+  while (hi - lo > 1) {  // fails(lo), passes(hi)
+    const uint64_t mid = lo + (hi - lo) / 2;
+    if (scalar_chain_passes(double_from_key(mid), amounts)) hi = mid; else lo = mid;
+  }
+  *thr = double_from_key(hi);
+  return true;
+}
+
+int build_fast_rows(oe_engine* h) {
+  const int K = h->dof.K;
+  std::vector<FastRow> rows((size_t)std::max(h->C, 1));
+  for (int c = 0; c < h->C; ++c) {
+    FastRow fr;
+    std::memset(&fr, 0, sizeof fr);
+    fr.pod_role = h->h_pod_role[c];
+    bool ok = true, dyn_seen = false;
+    int n_rules = 0;
+    std::vector<int> qs;                       // distinct pool entries in first-use order
+    std::vector<std::vector<double>> chains;
+    std::vector<int> statics;
+    const int eb = h->h_excl_begin[c], ee = h->h_excl_begin[c + 1];
+    auto excluded = [&](int p) { for (int q = eb; q < ee; ++q) if (h->h_excl[q] == p) return true; return false; };
+    for (int x = h->h_op_begin[c]; x < h->h_op_begin[c + 1] && ok; ++x) {
+      const oe_stage_op& op = h->h_ops[x];
+      if (op.flags) { ok = false; break; }
+      switch (op.opcode) {
+        case OE_OP_NOP: break;
+        case OE_OP_EXEC_ID: ok = op.arg < 0; break;
+        case OE_OP_RULE:
+          if (++n_rules > 1) { ok = false; break; }
+          fr.rule_begin = op.arg; fr.rule_count = (int32_t)op.aux;
+          break;
+        case OE_OP_SCALAR_NEW: {
+          const int q = op.slot * K + op.kind;
+          size_t k = 0;
+          while (k < qs.size() && qs[k] != q) ++k;
+          if (k == qs.size()) { qs.push_back(q); chains.emplace_back(); }
+          chains[k].push_back(op.amount);
+          fr.flags |= OE_FR_NEEDS_POOL;
+        } break;
+        case OE_OP_PORT_STATIC:
+          if (op.slot != 0 || (dyn_seen && !excluded(op.arg))) { ok = false; break; }
+          if (std::find(statics.begin(), statics.end(), op.arg) != statics.end()) fr.flags |= OE_FR_NEVER;
+          else statics.push_back(op.arg);
+          fr.flags |= OE_FR_NEEDS_POOL;
+          break;
+        case OE_OP_PORT_DYNAMIC:
+          if (op.slot != 0 || op.arg >= 0 || fr.n_dyn == 255) { ok = false; break; }
+          dyn_seen = true;
+          ++fr.n_dyn;
+          fr.flags |= OE_FR_NEEDS_POOL;
+          break;
+        default: ok = false;
+      }
+    }
+    if (ok && qs.size() > 8) ok = false;
+    for (size_t k = 0; ok && k < qs.size(); ++k) {
+      if (qs[k] >= 32) { ok = false; break; }
+      fr.thr_q[k] = (uint8_t)qs[k];
+      ok = fold_scalar_chain(chains[k], &fr.thr[k]);
+    }
+    fr.n_thr = (uint8_t)qs.size();
+    if (ok) {
+      std::vector<int> listed(statics);
+      for (int q = eb; q < ee; ++q) listed.push_back(h->h_excl[q]);
+      std::sort(listed.begin(), listed.end());
+      listed.erase(std::unique(listed.begin(), listed.end()), listed.end());
+      if (listed.size() > 16) ok = false;
+      for (size_t u = 0; ok && u < listed.size(); ++u) {
+        fr.port[u] = (uint16_t)listed[u];
+        if (std::find(statics.begin(), statics.end(), listed[u]) != statics.end()) fr.static_mask |= 1u << u;
+      }
+      // ports that are only excluded matter only when something is picked dynamically
+      fr.n_ports = (uint8_t)listed.size();
+    }
+    if (ok) fr.flags |= OE_FR_FAST; else fr.flags = 0;
+    rows[c] = fr;
+  }
+  if (int rc = upload(h, h->d_fast, rows.data(), rows.size())) return rc;
+  CU(cudaStreamSynchronize(h->stream));  // `rows` is a local
+  h->fast_K = K;
+  return 0;
+}
+
 int run_class_feasibility(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
   CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
   if (rows > 0) {
+    if (h->fast_K != h->dof.K) if (int rc = build_fast_rows(h)) return rc;
     // enough row tiles to fill the machine when there are few offers, few enough to amortise the offer-row loads
     const int64_t xblocks = stride * 32 / OE_K1_THREADS;
     int tiles = (int)std::min<int64_t>(rows, std::max<int64_t>(1, (148 * 16 + xblocks - 1) / xblocks));
-    int rows_per_tile = (rows + tiles - 1) / tiles;
+    int rows_per_tile = std::min(128, (rows + tiles - 1) / tiles);  // 128 descriptors = 16 KiB of shared memory
     tiles = (rows + rows_per_tile - 1) / rows_per_tile;
+    if (tiles > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one feasibility launch covers", rows);
+    K1Args a{};
+    a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows; a.rows_per_tile = rows_per_tile;
+    a.fast = h->d_fast.as<FastRow>();
+    a.n_nodes = h->n_rule_nodes <= OE_K1_MAX_SMEM_NODES ? h->n_rule_nodes : 0;
+    a.sc_cols = h->dof.S * h->dof.K <= 8 ? h->dof.S * h->dof.K : 0;
+    const size_t smem = (size_t)rows_per_tile * sizeof(FastRow) + (size_t)a.n_nodes * sizeof(oe_rule_node) +
+                        (size_t)a.sc_cols * OE_K1_THREADS * sizeof(double);
     dim3 grid((unsigned)xblocks, (unsigned)tiles);
-    k_class_feasibility<<<grid, OE_K1_THREADS, 0, h->stream>>>(h->ctx(), h->d_F.as<uint32_t>(), stride, rows, rows_per_tile);
+    if (h->dof.R <= OE_FAST_RANGES) k_class_feasibility<true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+    else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
     ++*launches;
     CU(cudaGetLastError());
   }
@@ -1126,14 +1311,14 @@ int run_expand(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
   if (h->M > 0) {
-    const unsigned xblocks = (unsigned)((stride / 4 + OE_KX_THREADS - 1) / OE_KX_THREADS);
-    // ~8 CTAs per SM overall; each CTA streams a [reqs_per_block x 4 KiB] slab
-    int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 63) / 64, (148 * 8 + xblocks - 1) / xblocks));
+    const unsigned xblocks = (unsigned)((stride / 4 + OE_KX_LANES - 1) / OE_KX_LANES);
+    // ~32 CTAs per SM overall; each CTA streams a [reqs_per_block x 1 KiB] slab
+    int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 15) / 16, (148 * 32 + xblocks - 1) / xblocks));
     const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);
-    k_expand_matrix<<<grid, OE_KX_THREADS, 0, h->stream>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(), h->d_matrix.as<uint32_t>(), stride,
-                                                          h->M, reqs_per_block);
+    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, h->stream>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
+                                                                         h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block);
     ++*launches;
     CU(cudaGetLastError());
   }

@@ -6,9 +6,13 @@ from dcos_commons_b200 import abi, tables as tb
 GRID = [0.0, 0.1, 0.2, 0.3, 0.5, 1.0, 1.5, 2.0, 4.0, 0.1 + 0.2, 32.0, 256.0, 1024.0]
 
 
-def random_tables(seed: int, n_offers=None, n_reqs=None, n_tasks=None, with_reserved=True, big_dicts=False) -> abi.CycleTables:
+def random_tables(seed: int, n_offers=None, n_reqs=None, n_tasks=None, with_reserved=True, big_dicts=False, new_pods_only=False) -> abi.CycleTables:
     rng = np.random.default_rng(seed)
     easy = rng.random() < 0.6  # short pipelines over generous offers, so that a good share of pairs is feasible
+    if new_pods_only:
+        # only the stages of a new pod's pipeline (OfferEvaluator.java:411-522): the shape the engine folds into one
+        # threshold per pool entry and one port count; long scalar chains on few pool entries stress the folding
+        with_reserved = False
     S, K = int(rng.integers(1, 3)), int(rng.integers(4, 6))
     R, D, A = int(rng.integers(1, 7)), int(rng.integers(0, 4)), int(rng.integers(1, 5))
     Q, E = int(rng.integers(0, 3)), int(rng.integers(0, 3))
@@ -70,13 +74,20 @@ def random_tables(seed: int, n_offers=None, n_reqs=None, n_tasks=None, with_rese
     amt = lambda: float(GRID[int(rng.integers(0, len(GRID)))])
     for c in range(n_classes):
         ops, used_res = [], set()
-        exec_id = int(rng.integers(-1, n_exec)) if rng.random() < 0.3 else -1
+        exec_id = int(rng.integers(-1, n_exec)) if rng.random() < 0.3 and not new_pods_only else -1
         ops.append(("exec", exec_id))
         if rng.random() < 0.7:
             ops.append(("rule", tree(1 if easy else 3)))
         for _ in range(int(rng.integers(1, 5 if easy else 12))):
             k = int(rng.integers(0, 12))
             slot = int(rng.integers(0, S))
+            if new_pods_only:
+                k = int(rng.integers(0, 6))
+                if k == 5:
+                    ops.append(("dynport", None, 0))
+                    continue
+                if k == 4:
+                    slot = 0
             if k <= 3: ops.append(("scalar", int(rng.integers(0, K)), amt(), slot))
             elif k == 4: ops.append(("port", int(rng.integers(1000, 1060)), slot))
             elif k == 5:

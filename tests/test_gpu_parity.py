@@ -51,6 +51,53 @@ def test_fuzz_wider(engine, seed):
     _compare_all(engine, random_tables(seed, n_offers=1500 + seed % 7, n_reqs=60, n_tasks=150, big_dicts=True))
 
 
+@pytest.mark.parametrize("seed", range(2000, 2060))
+def test_fuzz_new_pod_pipelines(engine, seed):
+    """Pipelines of new pods only — the shape the engine folds (scalar chains -> thresholds, ports -> counts)."""
+    _compare_all(engine, random_tables(seed, n_offers=300 + seed % 50, new_pods_only=True))
+
+
+def test_scalar_chain_boundaries(engine):
+    """Offers that sit exactly on, one ulp below and one ulp above what a chain of deductions needs."""
+    from dcos_commons_b200 import tables as tb
+    chains = [[0.1, 0.2], [0.1, 0.1, 0.1], [0.3], [1.0, 0.1, 0.2, 0.7], [0.1] * 7, [256.0, 0.1 + 0.2, 32.0]]
+    prog = tb.ProgramBuilder()
+    for ch in chains:
+        prog.add_class([("exec", -1)] + [("scalar", 0, a) for a in ch] + [("scalar", 1, 1.0), ("nop",)])
+    rows = []
+    for ch in chains:
+        exact = 0.0
+        for a in reversed(ch):          # smallest start that leaves exactly zero, walking the chain backwards
+            exact = exact + a
+        for base in (exact, sum(ch), float(np.sum(np.array(ch)))):
+            for k in range(-3, 4):
+                v = base
+                for _ in range(abs(k)):
+                    v = np.nextafter(v, np.inf if k > 0 else -np.inf)
+                rows.append(dict(scalars={(0, 0): float(v), (0, 1): 1.0}))
+    rows.append(dict(scalars={(0, 0): float("nan"), (0, 1): 1.0}))
+    rows.append(dict(scalars={(0, 0): float("inf"), (0, 1): 1.0}))
+    rows.append(dict(scalars={(0, 1): 1.0}))                      # no cpus entry at all
+    offers = tb.offers_from_rows(rows, S=1, K=4, R=1, D=0, A=1)
+    M = len(chains) * 3
+    class_id = np.arange(M) % len(chains)
+    t = tb.make_tables(dict(n_agents=len(rows), n_hostnames=len(rows), n_pod_types=1), prog, tb.empty_tasks(), offers, class_id,
+                       np.zeros(M, np.int32), np.arange(M))
+    _compare_all(engine, t, two_cycles=False)
+
+
+def test_unsorted_port_ranges_are_rejected(engine):
+    t = random_tables(11, n_offers=20, n_reqs=3, n_tasks=0)
+    if t.port_range.shape[1] < 2:
+        t = random_tables(12, n_offers=20, n_reqs=3, n_tasks=0)
+    t.port_range = t.port_range.copy()
+    if t.port_range.shape[1] >= 2:
+        t.port_range[0, 0, 3] = (2000) | (2100 << 16)
+        t.port_range[0, 1, 3] = (2050) | (2200 << 16)      # overlaps the first
+        with pytest.raises(abi.EngineError):
+            engine.load(t)
+
+
 def test_empty_inputs(engine):
     t = random_tables(5, n_offers=40, n_reqs=6, n_tasks=0)
     _compare_all(engine, t)
