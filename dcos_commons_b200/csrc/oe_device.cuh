@@ -444,6 +444,8 @@ static_assert(sizeof(FastRow) == 128, "FastRow is staged as eight uint4");
 #define OE_FR_FAST 1u        // the folded form is valid for this class
 #define OE_FR_NEVER 2u       // a static port is requested twice: the second stage can never pass
 #define OE_FR_NEEDS_POOL 4u  // has scalar or port stages: an offer allocated to another role fails
+#define OE_FR_RULE_TAB 8u    // every leaf of the rule reads only the offer's zone / region: the rule is tabulated per
+                             // (factored row, zone, region) by k_rule_tables and K1 looks the verdict up
 
 #define OE_FAST_RANGES 8
 
@@ -489,9 +491,15 @@ __device__ __forceinline__ bool port_member(const DevOffers& o, int64_t i, bool 
 }
 
 // `sc` = this CTA's shared-memory copy of the scalar columns, [S*K][blockDim.x], or nullptr (read through L1 instead).
+// Rule verdicts tabulated over (zone, region): bit (region + 1) * zdim + (zone + 1) of row `row` (absent = -1 -> 0).
+struct RuleTab {
+  const uint32_t* bits;  // [rows][words]
+  int words, zdim;
+};
+
 template <bool REG_RANGES>
 __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* nodes, const FastRow& fr, const double* sc, int64_t i,
-                                          const OfferRegs& r, int var) {
+                                          const OfferRegs& r, int var, const RuleTab& tab, int row) {
   const DevOffers& o = cx.o;
   bool pass = !(fr.flags & OE_FR_NEVER);
   uint32_t present = r.present;
@@ -523,7 +531,12 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
     }
     pass = pass && statics && (pool_ports - listed >= (int)fr.n_dyn);
   }
-  if (fr.rule_count > 0) pass = pass && eval_rule(cx, nodes, i, r.ok, var, fr.rule_begin, fr.rule_count);
+  if (fr.flags & OE_FR_RULE_TAB) {
+    const int idx = (r.ok.region + 1) * tab.zdim + (r.ok.zone + 1);
+    pass = pass && ((__ldg(tab.bits + (int64_t)row * tab.words + (idx >> 5)) >> (idx & 31)) & 1u);
+  } else if (fr.rule_count > 0) {
+    pass = pass && eval_rule(cx, nodes, i, r.ok, var, fr.rule_begin, fr.rule_count);
+  }
   return pass;
 }
 

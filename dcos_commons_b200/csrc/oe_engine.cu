@@ -128,7 +128,27 @@ struct K1Args {
   const FastRow* fast;   // [C]
   int n_nodes;           // rule nodes staged in shared memory (0 = read them from global memory)
   int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
+  RuleTab tab;
 };
+
+// K0c: rules whose leaves read only the offer's zone / region are evaluated once per (factored row, zone, region)
+// instead of once per offer.  thread = one (zone, region) combination, blockIdx.y = factored row.
+__global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* __restrict__ fast, uint32_t* __restrict__ tab, int words,
+                                                     int zdim, int rdim) {
+  const int row = blockIdx.y;
+  const int var = row < cx.p.C ? -1 : row - cx.p.C;
+  const int cls = var < 0 ? row : cx.v.cls[var];
+  const FastRow& fr = fast[cls];
+  if (!(fr.flags & OE_FR_RULE_TAB)) return;
+  const int idx = blockIdx.x * 128 + threadIdx.x;
+  bool v = false;
+  if (idx < zdim * rdim) {
+    OfferKeys ok{0, 0, idx % zdim - 1, idx / zdim - 1};
+    v = eval_rule(cx, cx.p.nodes, 0, ok, var, fr.rule_begin, fr.rule_count);
+  }
+  const uint32_t bits = __ballot_sync(0xffffffffu, v);
+  if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
+}
 template <bool REG_RANGES>
 __global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, K1Args a) {
   extern __shared__ __align__(16) unsigned char k1_smem[];
@@ -165,7 +185,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, 
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
     bool pass = false;
     if (fr.flags & OE_FR_FAST) {
-      if (valid) pass = eval_fast<REG_RANGES>(cx, nodes, fr, sc, i, regs, var);
+      if (valid) pass = eval_fast<REG_RANGES>(cx, nodes, fr, sc, i, regs, var, a.tab, row);
     } else if (valid) {
       const int cls = var < 0 ? row : cx.v.cls[var];
       pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
@@ -559,7 +579,9 @@ struct oe_engine {
   std::vector<uint16_t> h_excl;
   int n_rule_nodes = 0;
   int fast_K = -1;  // scalar-kind count the folded class descriptors were built for (-1 = stale)
-  DevBuf d_fast;
+  int tab_words = 0, tab_zdim = 1, tab_rdim = 1;
+  bool any_rule_tab = false;
+  DevBuf d_fast, d_rule_tab;
   DevBuf d_op_begin, d_ops, d_nodes, d_pod_role, d_excl_begin, d_excl, d_rs_begin, d_rs, d_csets, d_cs_off, d_ts_type, d_mbits;
   DevProg dp{};
 
@@ -721,7 +743,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
-                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast};
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -1205,6 +1227,12 @@ bool fold_scalar_chain(const std::vector<double>& amounts, double* thr) {
 int build_fast_rows(oe_engine* h) {
   const int K = h->dof.K;
   std::vector<FastRow> rows((size_t)std::max(h->C, 1));
+  bool any_tab = false;
+  // (zone, region) combinations incl. "absent": tabulate rules only while a row's table stays small
+  h->tab_zdim = h->dict.n_zones + 1;
+  h->tab_rdim = h->dict.n_regions + 1;
+  const int64_t combos = (int64_t)h->tab_zdim * h->tab_rdim;
+  h->tab_words = combos <= 8192 ? (int)((combos + 31) / 32) : 0;
   for (int c = 0; c < h->C; ++c) {
     FastRow fr;
     std::memset(&fr, 0, sizeof fr);
@@ -1269,12 +1297,30 @@ int build_fast_rows(oe_engine* h) {
       // ports that are only excluded matter only when something is picked dynamically
       fr.n_ports = (uint8_t)listed.size();
     }
+    if (ok && fr.rule_count > 0 && h->tab_words > 0) {
+      bool zone_region_only = true;
+      for (int n = fr.rule_begin; n < fr.rule_begin + fr.rule_count; ++n) {
+        const oe_rule_node& nd = h->h_nodes[n];
+        switch (nd.op) {
+          case OE_R_TRUE: case OE_R_FALSE: case OE_R_AND: case OE_R_OR: case OE_R_NOT:
+          case OE_R_ZONE_IN: case OE_R_REGION_IN: case OE_R_LOCAL_REGION: case OE_R_MAXPER_ZONE: case OE_R_MAXPER_REGION: break;
+          case OE_R_RR: {
+            const int ks = h->h_csets[nd.a].keyspace;
+            if (ks != OE_KS_ZONE && ks != OE_KS_REGION) zone_region_only = false;
+          } break;
+          default: zone_region_only = false;
+        }
+      }
+      if (zone_region_only) fr.flags |= OE_FR_RULE_TAB;
+    }
     if (ok) fr.flags |= OE_FR_FAST; else fr.flags = 0;
+    any_tab = any_tab || (fr.flags & OE_FR_RULE_TAB);
     rows[c] = fr;
   }
   if (int rc = upload(h, h->d_fast, rows.data(), rows.size())) return rc;
   CU(cudaStreamSynchronize(h->stream));  // `rows` is a local
   h->fast_K = K;
+  h->any_rule_tab = any_tab;
   return 0;
 }
 
@@ -1291,6 +1337,16 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
     tiles = (rows + rows_per_tile - 1) / rows_per_tile;
     if (tiles > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one feasibility launch covers", rows);
     K1Args a{};
+    a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
+    if (h->any_rule_tab) {
+      CU(h->d_rule_tab.ensure((size_t)rows * h->tab_words * 4));
+      a.tab.bits = h->d_rule_tab.as<uint32_t>();
+      dim3 tgrid((unsigned)((h->tab_zdim * h->tab_rdim + 127) / 128), (unsigned)rows);
+      if (rows > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one rule-table launch covers", rows);
+      k_rule_tables<<<tgrid, 128, 0, h->stream>>>(h->ctx(), h->d_fast.as<FastRow>(), h->d_rule_tab.as<uint32_t>(), h->tab_words,
+                                                  h->tab_zdim, h->tab_rdim);
+      ++*launches;
+    }
     a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows; a.rows_per_tile = rows_per_tile;
     a.fast = h->d_fast.as<FastRow>();
     a.n_nodes = h->n_rule_nodes <= OE_K1_MAX_SMEM_NODES ? h->n_rule_nodes : 0;
