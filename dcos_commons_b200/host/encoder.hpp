@@ -1,0 +1,652 @@
+// encoder.hpp — turns one cycle's Offers, TaskInfos and PodInstanceRequirements into the columnar, dictionary-encoded
+// tables of include/oe_abi.h.  This is the host half of the drop-in: everything string-shaped is resolved here
+// (dictionaries, StringMatchers, attribute formatting), and the stage pipeline the reference would build per
+// requirement (S/offer/evaluate/OfferEvaluator.java:411-522) is flattened into a class program.
+//
+// Reference semantics restated (S/ = sdk/scheduler/src/main/java/com/mesosphere/sdk/):
+//   S/offer/MesosResourcePool.java:53-147,432-455   pool partition: merged by role, reserved by id, atomic MOUNT disks
+//   S/offer/MesosResource.java:26-62                isAtomic, getRole
+//   S/offer/ResourceUtils.java:82-117               getReservation / getResourceId
+//   S/offer/RangeUtils.java:23-47 (antlr IntervalSet) merged port ranges: sorted, disjoint, adjacency-coalesced
+//   S/offer/taskdata/TaskLabelReader.java:47-92     what a deployed task contributes to the task table
+//   S/offer/evaluate/OfferEvaluator.java:380-403,411-536   stage order of a new pod
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <set>
+#include <stdexcept>
+#include <unordered_map>
+
+#include "specification.hpp"
+
+namespace sdk {
+
+// S/offer/InvalidRequirementException.java
+struct InvalidRequirementException : std::runtime_error { using std::runtime_error::runtime_error; };
+
+namespace labels {  // S/offer/taskdata/LabelConstants.java
+constexpr const char* OFFER_ATTRIBUTES = "offer_attributes";
+constexpr const char* OFFER_HOSTNAME = "offer_hostname";
+constexpr const char* OFFER_ZONE = "offer_zone";
+constexpr const char* OFFER_REGION = "offer_region";
+constexpr const char* TASK_TYPE = "task_type";
+constexpr const char* TASK_INDEX = "index";
+constexpr const char* RESOURCE_ID = "resource_id";
+}  // namespace labels
+
+// S/offer/taskdata/TaskLabelWriter.java (the setters LaunchEvaluationStage.java:58-68 uses)
+struct TaskLabelWriter {
+  mesos::TaskInfo& task;
+  explicit TaskLabelWriter(mesos::TaskInfo& t) : task(t) {}
+  TaskLabelWriter& setType(const std::string& t) { task.labels[labels::TASK_TYPE] = t; return *this; }
+  TaskLabelWriter& setIndex(int i) { task.labels[labels::TASK_INDEX] = std::to_string(i); return *this; }
+  TaskLabelWriter& setHostname(const mesos::Offer& o) { task.labels[labels::OFFER_HOSTNAME] = o.hostname; return *this; }
+  TaskLabelWriter& setOfferAttributes(const mesos::Offer& o) { task.labels[labels::OFFER_ATTRIBUTES] = AttributeStringUtils::toString(o.attributes); return *this; }
+  TaskLabelWriter& setZone(const std::string& z) { task.labels[labels::OFFER_ZONE] = z; return *this; }
+  TaskLabelWriter& setRegion(const std::string& r) { task.labels[labels::OFFER_REGION] = r; return *this; }
+};
+
+struct ResourceUtils {
+  // S/offer/ResourceUtils.java:82-117: the effective reservation is the last entry of the refinement stack
+  static std::optional<std::string> getResourceId(const mesos::Resource& r) {
+    if (r.reservations.empty()) return std::nullopt;
+    auto it = r.reservations.back().labels.find(labels::RESOURCE_ID);
+    if (it == r.reservations.back().labels.end()) return std::nullopt;
+    return it->second;
+  }
+  static std::string getRole(const mesos::Resource& r) { return r.reservations.empty() ? ANY_ROLE : r.reservations.back().role; }  // MesosResource.java:52-62
+  static bool isAtomic(const mesos::Resource& r) { return r.disk && r.disk->source == mesos::DiskInfo::MOUNT; }                    // MesosResource.java:26-30
+};
+
+// antlr4 IntervalSet as S/offer/RangeUtils.java uses it: closed intervals kept sorted, disjoint and adjacency-coalesced.
+struct IntervalSet {
+  std::vector<std::pair<int64_t, int64_t>> iv;
+  void add(int64_t a, int64_t b) {
+    if (b < a) return;
+    std::vector<std::pair<int64_t, int64_t>> out;
+    bool placed = false;
+    for (auto& x : iv) {
+      if (x.second + 1 < a) out.push_back(x);
+      else if (b + 1 < x.first) { if (!placed) { out.push_back({a, b}); placed = true; } out.push_back(x); }
+      else { a = std::min(a, x.first); b = std::max(b, x.second); }
+    }
+    if (!placed) out.push_back({a, b});
+    std::sort(out.begin(), out.end());
+    iv.swap(out);
+  }
+};
+
+class Dictionary {
+ public:
+  int32_t intern(const std::string& s) {
+    auto it = ids_.find(s);
+    if (it != ids_.end()) return it->second;
+    const int32_t id = (int32_t)values_.size();
+    ids_.emplace(s, id);
+    values_.push_back(s);
+    return id;
+  }
+  int32_t find(const std::string& s) const { auto it = ids_.find(s); return it == ids_.end() ? -1 : it->second; }
+  int32_t size() const { return (int32_t)values_.size(); }
+  const std::vector<std::string>& values() const { return values_; }
+ private:
+  std::unordered_map<std::string, int32_t> ids_;
+  std::vector<std::string> values_;
+};
+
+// Host-side shadow of one OfferEvaluationStage of a class, index-aligned with the class's oe_stage_op list.  It is what
+// the adapter needs to turn the engine's decision for the WINNING offer back into recommendations.
+struct StageInfo {
+  enum Kind { EXECUTOR, PLACEMENT, RESOURCE, PORT, VOLUME, TLS, LAUNCH };
+  Kind kind = EXECUTOR;
+  std::string resourceName;             // RESOURCE / PORT / VOLUME
+  double value = 0.0;
+  int port = 0;                         // PORT: requested port (0 = dynamic)
+  bool hostPort = true;                 // PORT: false = overlay network, no reservation
+  VolumeSpec::Type volumeType = VolumeSpec::ROOT;
+  std::string containerPath;
+  std::vector<std::string> taskNames;   // task spec names that receive the resource; empty = executor level
+  std::string taskSpecName;             // LAUNCH
+  bool shouldLaunch = false;            // LAUNCH
+  std::string role, preReservedRole, principal;
+};
+
+struct EncodedCycle {
+  // programs
+  std::vector<int32_t> op_begin{0};
+  std::vector<oe_stage_op> ops;
+  std::vector<oe_rule_node> nodes;
+  std::vector<int32_t> pod_role;
+  std::vector<int32_t> excl_begin{0};
+  std::vector<uint16_t> excl;
+  std::vector<int32_t> rs_begin{0};
+  std::vector<uint32_t> rs;
+  std::vector<oe_counter_set> csets;
+  std::vector<int32_t> tsets;
+  std::vector<uint32_t> mbits;
+  // tasks
+  int TA = 1, Q = 0, FW = 1;
+  std::vector<int32_t> t_name, t_type, t_index, t_agent, t_host, t_zone, t_region, t_attr, t_rr;
+  std::vector<uint32_t> t_filter;
+  // offers
+  int S = 1, K = 4, R = 1, D = 0, A = 1, E = 0;
+  std::vector<double> o_scalar, o_msize, o_rval;
+  std::vector<uint32_t> o_present, o_port;
+  std::vector<int32_t> o_mprof, o_alloc, o_agent, o_host, o_zone, o_region, o_attr, o_rr, o_exec, o_rid, o_rkind;
+  std::vector<int64_t> o_rbegin;
+  // requirements
+  std::vector<int32_t> r_class, r_type, r_index, l_begin{0}, l_name;
+  std::vector<uint32_t> l_filter;
+  // host-side shadows
+  std::vector<std::vector<StageInfo>> classStages;
+  int64_t N = 0, T = 0, M = 0;
+  oe_dict_sizes dict{};
+
+  oe_program_table programTable() const {
+    oe_program_table t{};
+    t.n_classes = (int32_t)pod_role.size(); t.n_ops = (int32_t)ops.size(); t.n_rule_nodes = (int32_t)nodes.size();
+    t.n_counter_sets = (int32_t)csets.size(); t.n_type_sets = (int32_t)tsets.size(); t.n_range_sets = (int32_t)rs_begin.size() - 1;
+    t.n_matcher_words = (int64_t)mbits.size();
+    t.op_begin = op_begin.data(); t.ops = ops.data(); t.rule_nodes = nodes.data(); t.pod_role = pod_role.data();
+    t.port_excl_begin = excl_begin.data(); t.port_excl = excl.data(); t.range_set_begin = rs_begin.data(); t.range_set = rs.data();
+    t.counter_sets = csets.data(); t.type_set_pod_type = tsets.data(); t.matcher_bits = mbits.data(); t.dict = dict;
+    return t;
+  }
+  oe_task_table taskTable() const {
+    oe_task_table t{};
+    t.n_tasks = T; t.n_attr_slots = TA; t.n_rr_cols = Q; t.n_filter_words = FW;
+    t.name_id = t_name.data(); t.pod_type_id = t_type.data(); t.pod_index = t_index.data(); t.agent_id = t_agent.data();
+    t.hostname_id = t_host.data(); t.zone_id = t_zone.data(); t.region_id = t_region.data(); t.attr_id = t_attr.data();
+    t.rr_key = t_rr.data(); t.filter_bits = t_filter.data();
+    return t;
+  }
+  oe_offer_table offerTable() const {
+    oe_offer_table t{};
+    t.n_offers = N; t.row_offset = 0; t.n_offers_global = N; t.shard_rows = 0;
+    t.n_role_slots = S; t.n_scalar_kinds = K; t.n_port_ranges = R; t.n_mount_slots = D; t.n_attr_slots = A; t.n_rr_cols = Q; t.n_exec_slots = E;
+    t.scalar = o_scalar.data(); t.scalar_present = o_present.data(); t.port_range = o_port.data(); t.mount_size = o_msize.data();
+    t.mount_profile = o_mprof.data(); t.alloc_role = o_alloc.data(); t.agent_id = o_agent.data(); t.hostname_id = o_host.data();
+    t.zone_id = o_zone.data(); t.region_id = o_region.data(); t.attr_id = o_attr.data(); t.rr_key = o_rr.data(); t.exec_id = o_exec.data();
+    t.n_reserved = (int64_t)o_rid.size();
+    if (t.n_reserved) { t.reserved_begin = o_rbegin.data(); t.reserved_id = o_rid.data(); t.reserved_kind = o_rkind.data(); t.reserved_value = o_rval.data(); }
+    return t;
+  }
+  oe_req_table reqTable() const {
+    oe_req_table t{};
+    t.n_reqs = M; t.class_id = r_class.data(); t.pod_type_id = r_type.data(); t.pod_index = r_index.data();
+    t.launch_begin = l_begin.data(); t.launch_name_id = l_name.data(); t.launch_filter_bits = l_filter.data();
+    return t;
+  }
+};
+
+// One requirement as the encoder sees it: either a full pod pipeline or (for rule-level tests, the counterpart of
+// calling PlacementRule.filter directly) just a rule.
+struct EncoderRequirement {
+  const PodInstanceRequirement* requirement = nullptr;
+  RulePtr ruleOnly;          // when set: the class is [PlacementRuleEvaluationStage(ruleOnly)]
+  PodInstance podInstance;   // used with ruleOnly
+};
+
+class CycleEncoder : private RuleDictionary, private RuleEmitter {
+ public:
+  explicit CycleEncoder(SchedulerConfig cfg = SchedulerConfig()) : cfg_(cfg) {}
+
+  EncodedCycle encode(const std::vector<mesos::Offer>& offers, const std::vector<mesos::TaskInfo>& tasks,
+                      const std::vector<EncoderRequirement>& reqs) {
+    if (used_) throw std::logic_error("CycleEncoder: one encoder per cycle");
+    used_ = true;
+    roles_.intern(ANY_ROLE);  // role slot 0
+    slots_.intern(ANY_ROLE);
+    for (const char* k : {"cpus", "mem", "disk", "gpus"}) kinds_.intern(k);
+
+    // ---- pass 1: dictionaries
+    for (auto& o : offers) {
+      agents_.intern(o.slave_id);
+      hosts_.intern(o.hostname);
+      if (o.domain) { zones_.intern(o.domain->zone); regions_.intern(o.domain->region); }
+      for (auto& a : o.attributes) attrs_.intern(AttributeStringUtils::toString(a));
+      for (auto& e : o.executor_ids) execs_.intern(e);
+      for (auto& r : o.resources) {
+        if (r.allocation_role) roles_.intern(*r.allocation_role);
+        if (r.value.type == mesos::Value::SCALAR && !ResourceUtils::isAtomic(r)) kinds_.intern(r.name);
+        if (auto id = ResourceUtils::getResourceId(r)) resids_.intern(*id);
+        else if (!ResourceUtils::isAtomic(r)) slots_.intern(ResourceUtils::getRole(r));
+        if (r.disk && r.disk->profile) profiles_.intern(*r.disk->profile);
+      }
+    }
+    for (auto& t : tasks) {
+      names_.intern(t.name);
+      agents_.intern(t.slave_id);
+      if (auto v = label(t, labels::OFFER_HOSTNAME)) hosts_.intern(*v);
+      if (auto v = label(t, labels::OFFER_ZONE)) zones_.intern(*v);
+      if (auto v = label(t, labels::OFFER_REGION)) regions_.intern(*v);
+      if (auto v = label(t, labels::TASK_TYPE)) types_.intern(*v);
+      if (auto v = label(t, labels::OFFER_ATTRIBUTES)) for (auto& a : AttributeStringUtils::toStringList(*v)) attrs_.intern(a);
+    }
+    for (auto& r : reqs) {
+      const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
+      types_.intern(pi.pod->type);
+      if (r.ruleOnly) r.ruleOnly->declare(*this);
+      else {
+        if (pi.pod->placementRule) (*pi.pod->placementRule)->declare(*this);
+        for (auto& ts : pi.pod->tasks) {
+          names_.intern(taskInstanceName(pi, ts.name));
+          for (auto& rs : ts.resourceSet.resources) {
+            roles_.intern(rs.role); slots_.intern(rs.preReservedRole);
+            if (!rs.isPort) kinds_.intern(rs.name);
+          }
+          for (auto& v : ts.resourceSet.volumes) { slots_.intern(v.preReservedRole); for (auto& p : v.profiles) profiles_.intern(p); }
+        }
+        for (auto& v : pi.pod->volumes) { slots_.intern(v.preReservedRole); for (auto& p : v.profiles) profiles_.intern(p); }
+      }
+    }
+    if (slots_.size() > OE_MAX_ROLE_SLOTS) throw InvalidRequirementException("more reservable roles in one cycle than OE_MAX_ROLE_SLOTS");
+    if (kinds_.size() > OE_MAX_SCALAR_KINDS) throw InvalidRequirementException("more scalar resource names than OE_MAX_SCALAR_KINDS");
+    if (profiles_.size() > OE_MAX_PROFILES) throw InvalidRequirementException("more volume profiles than OE_MAX_PROFILES");
+    if (rrAttrs_.size() > OE_MAX_RR_COLS) throw InvalidRequirementException("more round-robin attribute names than OE_MAX_RR_COLS");
+    // round-robin value dictionary: the values of the named attributes, on offers and in task labels
+    for (auto& o : offers) for (auto& a : o.attributes) if (rrColumn(a.name) >= 0) rrValues_.intern(AttributeStringUtils::toString(a.value));
+    for (auto& t : tasks)
+      if (auto v = label(t, labels::OFFER_ATTRIBUTES))
+        for (auto& a : AttributeStringUtils::toStringList(*v)) {
+          const size_t k = a.find(':');
+          if (k != std::string::npos && rrColumn(a.substr(0, k)) >= 0) rrValues_.intern(a.substr(k + 1));
+        }
+
+    encodeOffers(offers);
+    encodeTasks(tasks);
+
+    // ---- programs and requirements
+    std::map<std::string, int> classOf;
+    for (auto& r : reqs) {
+      const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
+      std::string key;
+      if (r.ruleOnly) key = "rule@" + std::to_string((uintptr_t)r.ruleOnly.get());
+      else {
+        key = "pod@" + std::to_string((uintptr_t)pi.pod.get()) + "|" + std::to_string((int)r.requirement->recoveryType);
+        for (auto& t : r.requirement->tasksToLaunch) key += "|" + t;
+      }
+      auto it = classOf.find(key);
+      int cls;
+      if (it != classOf.end()) cls = it->second;
+      else {
+        cls = r.ruleOnly ? addRuleOnlyClass(*r.ruleOnly) : addNewPodClass(*r.requirement);
+        classOf[key] = cls;
+      }
+      out_.r_class.push_back(cls);
+      out_.r_type.push_back(types_.find(pi.pod->type));
+      out_.r_index.push_back(pi.index);
+      if (!r.ruleOnly)
+        for (auto& ts : pi.pod->tasks) pendingLaunchNames_.push_back(taskInstanceName(pi, ts.name));
+      pendingLaunchEnd_.push_back((int32_t)pendingLaunchNames_.size());
+    }
+    out_.M = (int64_t)reqs.size();
+    // launch rows (LaunchEvaluationStage stores every task of the pod, launched or not: :49-54)
+    const int FW = std::max(1, (filters_.size() + 31) / 32);
+    out_.FW = FW;
+    for (size_t j = 0, l = 0; j < reqs.size(); ++j) {
+      for (; l < (size_t)pendingLaunchEnd_[j]; ++l) {
+        out_.l_name.push_back(names_.find(pendingLaunchNames_[l]));
+        for (int w = 0; w < FW; ++w) out_.l_filter.push_back(filterWord(pendingLaunchNames_[l], w));
+      }
+      out_.l_begin.push_back((int32_t)out_.l_name.size());
+    }
+    // task filter bits (filters are only known after the rules were emitted)
+    out_.t_filter.assign((size_t)FW * std::max<int64_t>(out_.T, 1), 0u);
+    for (int64_t t = 0; t < out_.T; ++t)
+      for (int w = 0; w < FW; ++w) out_.t_filter[(size_t)w * out_.T + t] = filterWord(tasks[(size_t)t].name, w);
+
+    oe_dict_sizes& d = out_.dict;
+    d.n_agents = std::max(agents_.size(), 1); d.n_hostnames = std::max(hosts_.size(), 1); d.n_zones = zones_.size(); d.n_regions = regions_.size();
+    d.n_attrs = attrs_.size(); d.n_rr_values = rrValues_.size(); d.n_pod_types = std::max(types_.size(), 1); d.n_task_names = names_.size();
+    d.n_filters = std::max(filters_.size(), 1); d.n_exec_ids = execs_.size(); d.n_roles = roles_.size(); d.n_res_ids = resids_.size();
+    return std::move(out_);
+  }
+
+  const Dictionary& hostnames() const { return hosts_; }
+
+ private:
+  static std::optional<std::string> label(const mesos::TaskInfo& t, const char* key) {
+    auto it = t.labels.find(key);
+    if (it == t.labels.end()) return std::nullopt;
+    return it->second;
+  }
+  static std::string lower(std::string s) { for (auto& c : s) c = (char)std::tolower((unsigned char)c); return s; }
+  int rrColumn(const std::string& attrName) const { return rrAttrs_.find(lower(attrName)); }  // equalsIgnoreCase
+
+  uint32_t filterWord(const std::string& taskName, int w) const {
+    uint32_t bits = 0;
+    for (int f = w * 32; f < std::min(filters_.size(), (w + 1) * 32); ++f)
+      if (filterMatchers_[(size_t)f]->matches(taskName)) bits |= 1u << (f & 31);
+    return bits;
+  }
+
+  // ---- offers -------------------------------------------------------------------------------------------------------
+  void encodeOffers(const std::vector<mesos::Offer>& offers) {
+    EncodedCycle& o = out_;
+    const int64_t N = (int64_t)offers.size();
+    o.N = N;
+    o.S = std::max(1, slots_.size());
+    o.K = std::max(4, kinds_.size());
+    o.Q = rrAttrs_.size();
+    struct Row { std::vector<IntervalSet> ports; std::vector<std::pair<double, int32_t>> mounts; };
+    std::vector<Row> rows((size_t)N);
+    int R = 1, D = 0, A = 1, E = 0;
+    for (int64_t i = 0; i < N; ++i) {
+      rows[(size_t)i].ports.resize((size_t)o.S);
+      A = std::max<int>(A, (int)offers[(size_t)i].attributes.size());
+      E = std::max<int>(E, (int)offers[(size_t)i].executor_ids.size());
+    }
+    if (A > OE_MAX_ATTR_SLOTS || E > OE_MAX_EXEC_SLOTS) throw InvalidRequirementException("offer exceeds the attribute / executor-id slot limits");
+    const size_t n = (size_t)std::max<int64_t>(N, 1);
+    o.o_scalar.assign((size_t)o.S * o.K * n, 0.0);
+    o.o_present.assign(n, 0u);
+    o.o_alloc.assign(n, -1); o.o_agent.assign(n, 0); o.o_host.assign(n, 0); o.o_zone.assign(n, -1); o.o_region.assign(n, -1);
+    o.o_rbegin.assign((size_t)N + 1, 0);
+    for (int64_t i = 0; i < N; ++i) {
+      const mesos::Offer& of = offers[(size_t)i];
+      o.o_agent[(size_t)i] = agents_.find(of.slave_id);
+      o.o_host[(size_t)i] = hosts_.find(of.hostname);
+      if (of.domain) { o.o_zone[(size_t)i] = zones_.find(of.domain->zone); o.o_region[(size_t)i] = regions_.find(of.domain->region); }
+      std::optional<std::string> alloc;
+      for (auto& r : of.resources) {
+        if (r.allocation_role) {
+          if (alloc && *alloc != *r.allocation_role)
+            throw InvalidRequirementException("offer " + of.id + " mixes allocation roles; the table carries one per offer");
+          alloc = r.allocation_role;
+        }
+        if (auto id = ResourceUtils::getResourceId(r)) {  // dynamicallyReservedPoolByResourceId (MesosResourcePool.java:119-131)
+          o.o_rid.push_back(resids_.find(*id));
+          if (ResourceUtils::isAtomic(r)) { o.o_rkind.push_back(OE_KIND_MOUNT); o.o_rval.push_back(r.value.scalar); }
+          else if (r.value.type == mesos::Value::RANGES) { o.o_rkind.push_back(OE_KIND_PORTS); o.o_rval.push_back(r.value.ranges.empty() ? 0.0 : (double)r.value.ranges[0].first); }
+          else { o.o_rkind.push_back(kinds_.find(r.name)); o.o_rval.push_back(r.value.scalar); }
+          continue;
+        }
+        if (ResourceUtils::isAtomic(r)) {  // unreservedAtomicPool (MesosResourcePool.java:99-117)
+          if (r.name == "disk") rows[(size_t)i].mounts.push_back({r.value.scalar, r.disk->profile ? profiles_.find(*r.disk->profile) : -1});
+          continue;
+        }
+        const int slot = slots_.find(ResourceUtils::getRole(r));  // reservableMergedPoolByRole (MesosResourcePool.java:432-455)
+        if (r.value.type == mesos::Value::SCALAR) {
+          const int kind = kinds_.find(r.name);
+          const size_t q = ((size_t)slot * o.K + kind) * n + (size_t)i;
+          const bool had = (o.o_present[(size_t)i] >> (slot * o.K + kind)) & 1u;
+          // ValueUtils.add(zero, v) then + v2 ...: the sum runs in offer-resource order (MesosResourcePool.java:133-147)
+          o.o_scalar[q] = (had ? o.o_scalar[q] : 0.0) + r.value.scalar;
+          o.o_present[(size_t)i] |= 1u << (slot * o.K + kind);
+        } else if (r.value.type == mesos::Value::RANGES && r.name == "ports") {
+          for (auto& iv : r.value.ranges) rows[(size_t)i].ports[(size_t)slot].add((int)iv.first, (int)iv.second);  // RangeUtils.java:65-67 narrows with (int)
+        }
+      }
+      if (alloc) o.o_alloc[(size_t)i] = roles_.find(*alloc);
+      o.o_rbegin[(size_t)i + 1] = (int64_t)o.o_rid.size();
+      for (auto& p : rows[(size_t)i].ports) R = std::max<int>(R, (int)p.iv.size());
+      D = std::max<int>(D, (int)rows[(size_t)i].mounts.size());
+    }
+    if (R > OE_MAX_PORT_RANGES || D > OE_MAX_MOUNT_SLOTS) throw InvalidRequirementException("offer exceeds the port-range / MOUNT-disk slot limits");
+    o.R = R; o.D = D; o.A = A; o.E = E;
+    o.o_port.assign((size_t)o.S * R * n, OE_PORT_EMPTY);
+    o.o_msize.assign((size_t)std::max(D, 1) * n, -std::numeric_limits<double>::infinity());
+    o.o_mprof.assign((size_t)std::max(D, 1) * n, -1);
+    o.o_attr.assign((size_t)A * n, -1);
+    o.o_rr.assign((size_t)std::max(o.Q, 1) * n, -1);
+    o.o_exec.assign((size_t)std::max(E, 1) * n, -1);
+    for (int64_t i = 0; i < N; ++i) {
+      const mesos::Offer& of = offers[(size_t)i];
+      for (int s = 0; s < o.S; ++s)
+        for (size_t r = 0; r < rows[(size_t)i].ports[(size_t)s].iv.size(); ++r) {
+          auto iv = rows[(size_t)i].ports[(size_t)s].iv[r];
+          o.o_port[((size_t)s * R + r) * n + (size_t)i] = OE_PORT_PACK(iv.first, iv.second);
+        }
+      for (size_t d = 0; d < rows[(size_t)i].mounts.size(); ++d) {
+        o.o_msize[d * n + (size_t)i] = rows[(size_t)i].mounts[d].first;
+        o.o_mprof[d * n + (size_t)i] = rows[(size_t)i].mounts[d].second;
+      }
+      for (size_t a = 0; a < of.attributes.size(); ++a) o.o_attr[a * n + (size_t)i] = attrs_.find(AttributeStringUtils::toString(of.attributes[a]));
+      for (int q = 0; q < o.Q; ++q)
+        for (auto& a : of.attributes)
+          if (rrColumn(a.name) == q) { o.o_rr[(size_t)q * n + (size_t)i] = rrValues_.find(AttributeStringUtils::toString(a.value)); break; }  // first match wins
+      for (size_t e = 0; e < of.executor_ids.size(); ++e) o.o_exec[e * n + (size_t)i] = execs_.find(of.executor_ids[e]);
+    }
+  }
+
+  // ---- tasks ---------------------------------------------------------------------------------------------------------
+  void encodeTasks(const std::vector<mesos::TaskInfo>& tasks) {
+    EncodedCycle& o = out_;
+    const int64_t T = (int64_t)tasks.size();
+    o.T = T;
+    int TA = std::max(1, o.A);
+    std::vector<std::vector<std::string>> attrStrings((size_t)T);
+    for (int64_t t = 0; t < T; ++t) {
+      if (auto v = label(tasks[(size_t)t], labels::OFFER_ATTRIBUTES)) attrStrings[(size_t)t] = AttributeStringUtils::toStringList(*v);
+      TA = std::max<int>(TA, (int)attrStrings[(size_t)t].size());
+    }
+    if (TA > OE_MAX_ATTR_SLOTS) throw InvalidRequirementException("task exceeds the attribute slot limit");
+    o.TA = TA;
+    const size_t n = (size_t)std::max<int64_t>(T, 1);
+    o.t_name.assign(n, 0); o.t_type.assign(n, -1); o.t_index.assign(n, OE_NO_INDEX); o.t_agent.assign(n, 0);
+    o.t_host.assign(n, -1); o.t_zone.assign(n, -1); o.t_region.assign(n, -1);
+    o.t_attr.assign((size_t)TA * n, -1);
+    o.t_rr.assign((size_t)std::max(o.Q, 1) * n, -1);
+    for (int64_t t = 0; t < T; ++t) {
+      const mesos::TaskInfo& ti = tasks[(size_t)t];
+      o.t_name[(size_t)t] = names_.find(ti.name);
+      o.t_agent[(size_t)t] = agents_.find(ti.slave_id);
+      if (auto v = label(ti, labels::TASK_TYPE)) o.t_type[(size_t)t] = types_.find(*v);
+      if (auto v = label(ti, labels::TASK_INDEX)) {  // Integer.parseInt (TaskLabelReader.java:57-59); unparsable = not equivalent to anything
+        char* end = nullptr;
+        const long x = std::strtol(v->c_str(), &end, 10);
+        if (!v->empty() && end && *end == 0 && x >= INT32_MIN + 1 && x <= INT32_MAX) o.t_index[(size_t)t] = (int32_t)x;
+      }
+      if (auto v = label(ti, labels::OFFER_HOSTNAME)) o.t_host[(size_t)t] = hosts_.find(*v);
+      if (auto v = label(ti, labels::OFFER_ZONE)) o.t_zone[(size_t)t] = zones_.find(*v);
+      if (auto v = label(ti, labels::OFFER_REGION)) o.t_region[(size_t)t] = regions_.find(*v);
+      for (size_t a = 0; a < attrStrings[(size_t)t].size(); ++a) o.t_attr[a * n + (size_t)t] = attrs_.find(attrStrings[(size_t)t][a]);
+      for (int q = 0; q < o.Q; ++q)
+        for (auto& a : attrStrings[(size_t)t]) {
+          const size_t k = a.find(':');
+          if (k == std::string::npos) throw std::invalid_argument("Unable to split attribute into name:value elements: " + a);  // AttributeStringUtils.split
+          if (rrColumn(a.substr(0, k)) == q) { o.t_rr[(size_t)q * n + (size_t)t] = rrValues_.find(a.substr(k + 1)); break; }
+        }
+    }
+  }
+
+  // ---- classes -------------------------------------------------------------------------------------------------------
+  oe_stage_op op(int opcode, int kind = 0, int slot = 0, int arg = 0, double amount = 0.0, uint64_t mask = 0, uint64_t aux = 0) {
+    oe_stage_op x{};
+    x.opcode = (uint8_t)opcode; x.kind = (uint8_t)kind; x.slot = (uint8_t)slot; x.arg = arg; x.amount = amount; x.mask = mask; x.aux = aux;
+    return x;
+  }
+  void pushRule(const PlacementRule& rule, std::vector<oe_stage_op>& ops) {
+    const int begin = (int)out_.nodes.size();
+    rule.emit(*this);
+    const int count = (int)out_.nodes.size() - begin;
+    if (count > OE_MAX_RULE_NODES) throw InvalidRequirementException("placement rule larger than OE_MAX_RULE_NODES");
+    ops.push_back(op(OE_OP_RULE, 0, 0, begin, 0.0, 0, (uint64_t)count));
+  }
+  int finishClass(std::vector<oe_stage_op>& ops, std::vector<StageInfo>& stages, int podRole, const std::vector<int>& staticPorts) {
+    if (ops.size() > OE_MAX_STAGE_OPS) throw InvalidRequirementException("pipeline longer than OE_MAX_STAGE_OPS");
+    out_.ops.insert(out_.ops.end(), ops.begin(), ops.end());
+    out_.op_begin.push_back((int32_t)out_.ops.size());
+    out_.pod_role.push_back(podRole);
+    std::set<int> excl(staticPorts.begin(), staticPorts.end());
+    for (int p : excl) out_.excl.push_back((uint16_t)p);
+    out_.excl_begin.push_back((int32_t)out_.excl.size());
+    out_.classStages.push_back(stages);
+    return (int)out_.pod_role.size() - 1;
+  }
+  int addRuleOnlyClass(const PlacementRule& rule) {
+    std::vector<oe_stage_op> ops;
+    std::vector<StageInfo> stages(1);
+    stages[0].kind = StageInfo::PLACEMENT;
+    pushRule(rule, ops);
+    return finishClass(ops, stages, -1, {});
+  }
+
+  // PortEvaluationStage.requireHostPorts (PortEvaluationStage.java:325-334): no network = host network; otherwise only
+  // networks that map ports (S/dcos/DcosConstants.java: the "mesos-bridge" network) need host ports
+  static bool requireHostPorts(const std::vector<std::string>& networkNames) {
+    if (networkNames.empty()) return true;
+    for (auto& n : networkNames) if (n == "mesos-bridge") return true;
+    return false;
+  }
+
+  // getNewEvaluationPipeline (OfferEvaluator.java:411-522)
+  int addNewPodClass(const PodInstanceRequirement& req) {
+    const PodSpec& pod = *req.podInstance.pod;
+    std::vector<oe_stage_op> ops;
+    std::vector<StageInfo> stages;
+    auto stage = [&](StageInfo s, oe_stage_op o) { stages.push_back(std::move(s)); ops.push_back(o); };
+    { StageInfo s; s.kind = StageInfo::EXECUTOR; stage(s, op(OE_OP_EXEC_ID, 0, 0, -1)); }                                  // :417
+    if (pod.placementRule) { StageInfo s; s.kind = StageInfo::PLACEMENT; stages.push_back(s); pushRule(**pod.placementRule, ops); }   // :419-422
+    for (auto& v : pod.volumes) volumeStage(v, {}, stage);                                                                    // :424-427
+    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; stage(s, op(OE_OP_NOP)); }             // :431-437
+    // static ports declared anywhere in the pod are never picked dynamically (PortEvaluationStage.java:252-261)
+    std::vector<int> staticPorts;
+    for (auto& ts : pod.tasks) for (auto& rs : ts.resourceSet.resources) if (rs.isPort && rs.port != 0) staticPorts.push_back(rs.port);
+
+    std::map<std::string, const TaskSpec*> byName;  // TreeMap: task spec name order (:439-449)
+    for (auto& ts : pod.tasks) {
+      if (!byName.emplace(ts.name, &ts).second) throw std::logic_error("Duplicate key " + ts.name);
+    }
+    bool addedExecutorResources = false;
+    std::set<std::string> addedResourceSets;
+    for (auto& [taskSpecName, ts] : byName) {
+      const ResourceSet& rset = ts->resourceSet;
+      // getOrderedResourceSpecs (:380-403): static ports, dynamic ports, everything else
+      std::vector<const ResourceSpec*> ordered;
+      for (auto& r : rset.resources) if (r.isPort && r.port != 0) ordered.push_back(&r);
+      for (auto& r : rset.resources) if (r.isPort && r.port == 0) ordered.push_back(&r);
+      for (auto& r : rset.resources) if (!r.isPort) ordered.push_back(&r);
+      if (!addedExecutorResources) {  // :460-478
+        addedExecutorResources = true;
+        if (ordered.empty()) throw InvalidRequirementException("resource set " + rset.id + " has no resources");  // resourceSpecs.get(0)
+        for (auto& [name, value] : cfg_.getExecutorResources()) {
+          StageInfo s;
+          s.kind = StageInfo::RESOURCE; s.resourceName = name; s.value = value;
+          s.role = ordered[0]->role; s.preReservedRole = ordered[0]->preReservedRole; s.principal = ordered[0]->principal;
+          stage(s, op(OE_OP_SCALAR_NEW, kinds_.find(name), slots_.find(ordered[0]->preReservedRole), 0, value));
+        }
+      }
+      if (!addedResourceSets.count(rset.id)) {  // :480-513
+        addedResourceSets.insert(rset.id);
+        std::vector<std::string> taskNames;
+        for (auto& [n2, t2] : byName) if (t2->resourceSet.id == rset.id) taskNames.push_back(n2);
+        for (const ResourceSpec* r : ordered) {
+          StageInfo s;
+          s.taskNames = taskNames; s.role = r->role; s.preReservedRole = r->preReservedRole; s.principal = r->principal;
+          const int slot = slots_.find(r->preReservedRole);
+          if (r->isPort) {
+            s.kind = StageInfo::PORT; s.resourceName = "ports"; s.port = r->port; s.hostPort = requireHostPorts(r->networkNames);
+            if (!s.hostPort) stage(s, op(OE_OP_NOP));                                           // PortEvaluationStage.java:145-154
+            else if (r->port != 0) {
+              if (r->port < 0 || r->port > 65535) throw InvalidRequirementException("port out of range");
+              stage(s, op(OE_OP_PORT_STATIC, 0, slot, r->port));
+            } else {
+              int rangeSet = -1;
+              if (!r->ranges.empty()) {
+                for (auto& rg : r->ranges) out_.rs.push_back(OE_PORT_PACK(std::clamp(rg.begin, 0, 65535), std::clamp(rg.end, 0, 65535)));
+                out_.rs_begin.push_back((int32_t)out_.rs.size());
+                rangeSet = (int)out_.rs_begin.size() - 2;
+              }
+              stage(s, op(OE_OP_PORT_DYNAMIC, 0, slot, rangeSet));
+            }
+          } else {
+            s.kind = StageInfo::RESOURCE; s.resourceName = r->name; s.value = r->value;
+            stage(s, op(OE_OP_SCALAR_NEW, kinds_.find(r->name), slot, 0, r->value));
+          }
+        }
+        for (auto& v : rset.volumes) volumeStage(v, taskNames, stage);  // :509-512
+      }
+      StageInfo s;  // :515-518
+      s.kind = StageInfo::LAUNCH; s.taskSpecName = taskSpecName;
+      s.shouldLaunch = std::find(req.tasksToLaunch.begin(), req.tasksToLaunch.end(), taskSpecName) != req.tasksToLaunch.end();
+      stage(s, op(OE_OP_NOP));
+    }
+    // OfferEvaluationUtils.getRole(podSpec) (OfferEvaluationUtils.java:229-235): role of the first resource spec
+    int podRole = -1;
+    for (auto& ts : pod.tasks) { if (!ts.resourceSet.resources.empty()) { podRole = roles_.find(ts.resourceSet.resources[0].role); break; } }
+    return finishClass(ops, stages, podRole, staticPorts);
+  }
+
+  template <class StageFn>
+  void volumeStage(const VolumeSpec& v, const std::vector<std::string>& taskNames, StageFn& stage) {
+    StageInfo s;
+    s.kind = StageInfo::VOLUME; s.resourceName = "disk"; s.value = v.size; s.volumeType = v.type; s.containerPath = v.containerPath;
+    s.taskNames = taskNames; s.role = v.role; s.preReservedRole = v.preReservedRole; s.principal = v.principal;
+    if (v.type == VolumeSpec::ROOT) {  // VolumeEvaluationStage.java:155-181
+      stage(s, op(OE_OP_SCALAR_NEW, kinds_.find("disk"), slots_.find(v.preReservedRole), 0, v.size));
+    } else {                           // consumeAtomic (:182-186, MesosResourcePool.java:282-328)
+      uint64_t mask = 0;
+      for (auto& p : v.profiles) mask |= 1ull << profiles_.find(p);
+      stage(s, op(OE_OP_VOL_MOUNT, 0, 0, 0, v.size, mask));
+    }
+  }
+
+  // ---- RuleDictionary ------------------------------------------------------------------------------------------------
+  void needAgent(const std::string& a) override { agents_.intern(a); }
+  void needRegion(const std::string& r) override { regions_.intern(r); }
+  void needPodType(const std::string& t) override { types_.intern(t); }
+  void needRoundRobinAttribute(const std::string& name) override { rrAttrs_.intern(lower(name)); }
+  void needTaskFilter(const StringMatcher&) override {}
+
+  // ---- RuleEmitter ---------------------------------------------------------------------------------------------------
+  void node(int opc, int a, int b, int c) override { out_.nodes.push_back(oe_rule_node{opc, a, b, c}); }
+  int matcherOver(const Dictionary& dict, const char* tag, const StringMatcher& m) {
+    const std::string key = std::string(tag) + m.toString();
+    auto it = matcherCache_.find(key);
+    if (it != matcherCache_.end()) return it->second;
+    const int off = (int)out_.mbits.size();
+    const int words = std::max(1, (dict.size() + 31) / 32);
+    out_.mbits.resize(out_.mbits.size() + (size_t)words, 0u);
+    for (int v = 0; v < dict.size(); ++v)
+      if (m.matches(dict.values()[(size_t)v])) out_.mbits[(size_t)off + (v >> 5)] |= 1u << (v & 31);
+    matcherCache_[key] = off;
+    return off;
+  }
+  int matcherOverAttributes(const StringMatcher& m) override { return matcherOver(attrs_, "attr:", m); }
+  int matcherOverHostnames(const StringMatcher& m) override { return matcherOver(hosts_, "host:", m); }
+  int matcherOverZones(const StringMatcher& m) override { return matcherOver(zones_, "zone:", m); }
+  int matcherOverRegions(const StringMatcher& m) override { return matcherOver(regions_, "region:", m); }
+  int counterSet(int keyspace, const StringMatcher& taskFilter, const std::string& rrAttributeName) override {
+    const std::string fkey = taskFilter.toString();
+    int f = filters_.find(fkey);
+    if (f < 0) {
+      f = filters_.intern(fkey);
+      // keep our own copy of the matcher: the rule object may not outlive the encoder call in every caller
+      filterMatchers_.push_back(cloneMatcher(taskFilter));
+    }
+    const int col = keyspace == OE_KS_RR_ATTR ? rrColumn(rrAttributeName) : 0;
+    for (size_t c = 0; c < out_.csets.size(); ++c)
+      if (out_.csets[c].keyspace == keyspace && out_.csets[c].rr_col == col && out_.csets[c].filter_id == f) return (int)c;
+    out_.csets.push_back(oe_counter_set{keyspace, col, f, 0});
+    return (int)out_.csets.size() - 1;
+  }
+  static MatcherPtr cloneMatcher(const StringMatcher& m) {
+    if (auto* r = dynamic_cast<const RegexMatcher*>(&m)) return RegexMatcher::create(r->pattern);
+    if (auto* e = dynamic_cast<const ExactMatcher*>(&m)) { auto p = std::make_shared<ExactMatcher>(""); p->str = e->str; return p; }
+    return AnyMatcher::create();
+  }
+  int typeSet(const std::string& podType) override {
+    const int t = types_.find(podType);
+    for (size_t s = 0; s < out_.tsets.size(); ++s) if (out_.tsets[s] == t) return (int)s;
+    out_.tsets.push_back(t);
+    return (int)out_.tsets.size() - 1;
+  }
+  int agentId(const std::string& slaveId) override { return agents_.find(slaveId); }
+  int regionId(const std::string& region) override { return regions_.find(region); }
+
+  SchedulerConfig cfg_;
+  EncodedCycle out_;
+  bool used_ = false;
+  Dictionary agents_, hosts_, zones_, regions_, attrs_, rrValues_, rrAttrs_, types_, names_, filters_, execs_, roles_, slots_, kinds_, resids_, profiles_;
+  std::vector<MatcherPtr> filterMatchers_;
+  std::unordered_map<std::string, int> matcherCache_;
+  std::vector<std::string> pendingLaunchNames_;
+  std::vector<int32_t> pendingLaunchEnd_;
+};
+
+}  // namespace sdk

@@ -1,0 +1,350 @@
+// offer_evaluator.hpp — the reference-facing entry points, backed by the C ABI of include/oe_abi.h:
+//   OfferEvaluator::evaluate(requirement, offers)        S/offer/evaluate/OfferEvaluator.java:113-248
+//   PlanScheduler::resourceOffers(offers, steps)         S/scheduler/plan/PlanScheduler.java:50-70
+//   PlacementRuleFilter::filter(rule, offer, pod, tasks)  P/PlacementRule.java:38 (as the unit tests call it)
+// Same names, argument meaning and error behaviour as the reference (S/ = sdk/scheduler/src/main/java/com/mesosphere/
+// sdk/).  Matching is done by the engine; this layer encodes the inputs (encoder.hpp) and, for the ONE winning offer per
+// requirement, turns the engine's decision back into the recommendation list the reference would have produced
+// (RESERVE / CREATE / LAUNCH_GROUP / StoreTaskInfo, in stage order).
+//
+// The library behind the ABI is liboe_b200.so — the CUDA engine; there is no CPU implementation in this layer.  Tests may
+// bind the same ABI to the oracle (oracle/liboe_oracle.so, prefix "oeo_") to pin the ORACLE against the reference's
+// JUnit vectors; that constructor is named forTesting() and nothing under dcos_commons_b200/ calls it.
+#pragma once
+#include <dlfcn.h>
+
+#include <functional>
+#include <random>
+
+#include "encoder.hpp"
+
+namespace sdk {
+
+struct EngineError : std::runtime_error {  // surfaces as IOException in the Java adapter (PlanScheduler.java:99-104)
+  int code;
+  EngineError(int c, const std::string& what) : std::runtime_error(what), code(c) {}
+};
+
+class EngineLibrary {
+ public:
+  // The product path: the CUDA engine next to this header's package.
+  static EngineLibrary open(const std::string& path) { return EngineLibrary(path, "oe_"); }
+  // Test infrastructure only: any library exporting the same ABI under another prefix (the CPU oracle).
+  static EngineLibrary forTesting(const std::string& path, const std::string& prefix) { return EngineLibrary(path, prefix); }
+
+  int32_t (*create)(const oe_config*, oe_engine**) = nullptr;
+  void (*destroy)(oe_engine*) = nullptr;
+  const char* (*last_error)(const oe_engine*) = nullptr;
+  int32_t (*load_programs)(oe_engine*, const oe_program_table*) = nullptr;
+  int32_t (*load_tasks)(oe_engine*, const oe_task_table*) = nullptr;
+  int32_t (*load_offers)(oe_engine*, const oe_offer_table*) = nullptr;
+  int32_t (*load_requirements)(oe_engine*, const oe_req_table*) = nullptr;
+  int64_t (*matrix_stride_words)(const oe_engine*) = nullptr;
+  int32_t (*feasibility)(oe_engine*, uint32_t*, oe_stats*) = nullptr;
+  int32_t (*evaluate_cycle)(oe_engine*, oe_decision*, oe_stats*) = nullptr;
+  int32_t (*apply_launches)(oe_engine*) = nullptr;
+  std::string path;
+
+ private:
+  EngineLibrary(const std::string& p, const std::string& prefix) : path(p) {
+    void* h = dlopen(p.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!h) throw std::runtime_error(std::string("cannot load ") + p + ": " + dlerror());
+    auto sym = [&](const char* name) {
+      void* s = dlsym(h, (prefix + name).c_str());
+      if (!s) throw std::runtime_error(p + " does not export " + prefix + name);
+      return s;
+    };
+    create = (decltype(create))sym("create"); destroy = (decltype(destroy))sym("destroy");
+    last_error = (decltype(last_error))sym("last_error");
+    load_programs = (decltype(load_programs))sym("load_programs"); load_tasks = (decltype(load_tasks))sym("load_tasks");
+    load_offers = (decltype(load_offers))sym("load_offers"); load_requirements = (decltype(load_requirements))sym("load_requirements");
+    matrix_stride_words = (decltype(matrix_stride_words))sym("matrix_stride_words");
+    feasibility = (decltype(feasibility))sym("feasibility"); evaluate_cycle = (decltype(evaluate_cycle))sym("evaluate_cycle");
+    apply_launches = (decltype(apply_launches))sym("apply_launches");
+  }
+};
+
+// One engine handle (one per service, like OfferEvaluator: S/scheduler/DefaultScheduler.java:198-210).
+class Engine {
+ public:
+  explicit Engine(const EngineLibrary& lib, int device = 0) : lib_(lib) {
+    oe_config cfg{};
+    cfg.device = device; cfg.rank = 0; cfg.world = 1;
+    const int rc = lib_.create(&cfg, &h_);
+    if (rc != 0) throw EngineError(rc, std::string("oe_create: ") + lib_.last_error(nullptr));
+  }
+  ~Engine() { if (h_) lib_.destroy(h_); }
+  Engine(const Engine&) = delete;
+  Engine& operator=(const Engine&) = delete;
+
+  void load(const EncodedCycle& c) {
+    auto p = c.programTable(); check(lib_.load_programs(h_, &p), "oe_load_programs");
+    auto t = c.taskTable(); check(lib_.load_tasks(h_, &t), "oe_load_tasks");
+    auto o = c.offerTable(); check(lib_.load_offers(h_, &o), "oe_load_offers");
+    auto r = c.reqTable(); check(lib_.load_requirements(h_, &r), "oe_load_requirements");
+    M_ = c.M; N_ = c.N;
+  }
+  std::vector<oe_decision> evaluateCycle() {
+    std::vector<oe_decision> d((size_t)std::max<int64_t>(M_, 1));
+    oe_stats st{};
+    check(lib_.evaluate_cycle(h_, d.data(), &st), "oe_evaluate_cycle");
+    d.resize((size_t)M_);
+    return d;
+  }
+  // feasibility bit of (requirement j, offer i)
+  std::vector<std::vector<bool>> feasibility() {
+    const int64_t stride = lib_.matrix_stride_words(h_);
+    std::vector<uint32_t> bits((size_t)std::max<int64_t>(M_ * stride, 1));
+    oe_stats st{};
+    check(lib_.feasibility(h_, bits.data(), &st), "oe_feasibility");
+    std::vector<std::vector<bool>> out((size_t)M_, std::vector<bool>((size_t)N_));
+    for (int64_t j = 0; j < M_; ++j)
+      for (int64_t i = 0; i < N_; ++i) out[(size_t)j][(size_t)i] = (bits[(size_t)(j * stride + (i >> 5))] >> (i & 31)) & 1u;
+    return out;
+  }
+
+ private:
+  void check(int rc, const char* what) {
+    if (rc != 0) throw EngineError(rc, std::string(what) + ": " + lib_.last_error(h_));
+  }
+  const EngineLibrary& lib_;
+  oe_engine* h_ = nullptr;
+  int64_t M_ = 0, N_ = 0;
+};
+
+// ---- recommendations (S/offer/*OfferRecommendation.java) ---------------------------------------------------------------
+struct OfferRecommendation {
+  enum Type { RESERVE, UNRESERVE, CREATE, DESTROY, LAUNCH_GROUP, STORE_TASK };
+  Type type = RESERVE;
+  std::string offerId, agentId;
+  mesos::Resource resource;               // RESERVE / CREATE
+  std::optional<mesos::TaskInfo> task;    // LAUNCH_GROUP / STORE_TASK
+  bool hasOperation() const { return type != STORE_TASK; }   // StoreTaskInfoRecommendation carries no Mesos operation
+};
+
+// S/state/StateStore.java:340 fetchTasks / storeTasks, reduced to an in-memory map (the MemPersister role in the
+// reference's tests, T/offer/evaluate/OfferEvaluatorTestBase.java:32-50).
+class StateStore {
+ public:
+  void storeTasks(const std::vector<mesos::TaskInfo>& tasks) { for (auto& t : tasks) tasks_[t.name] = t; }
+  std::vector<mesos::TaskInfo> fetchTasks() const {
+    std::vector<mesos::TaskInfo> out;
+    for (auto& [n, t] : tasks_) out.push_back(t);
+    return out;
+  }
+  void clear() { tasks_.clear(); }
+ private:
+  std::map<std::string, mesos::TaskInfo> tasks_;
+};
+
+// Direct counterpart of calling `rule.filter(offer, podInstance, tasks).isPassing()` in the reference's rule tests.
+struct PlacementRuleFilter {
+  const EngineLibrary& lib;
+  bool filter(const RulePtr& rule, const mesos::Offer& offer, const PodInstance& podInstance, const std::vector<mesos::TaskInfo>& tasks) const {
+    CycleEncoder enc;
+    EncoderRequirement r;
+    r.ruleOnly = rule; r.podInstance = podInstance;
+    EncodedCycle c = enc.encode({offer}, tasks, {r});
+    Engine e(lib);
+    e.load(c);
+    return e.feasibility()[0][0];
+  }
+};
+
+class OfferEvaluator {
+ public:
+  OfferEvaluator(const EngineLibrary& lib, StateStore& stateStore, std::string serviceName = "test-service", SchedulerConfig cfg = SchedulerConfig())
+      : lib_(lib), stateStore_(stateStore), serviceName_(std::move(serviceName)), cfg_(cfg) {}
+
+  // S/offer/evaluate/OfferEvaluator.java:113-248: recommendations of the first offer (list order) all of whose stages
+  // pass; empty when none does.
+  std::vector<OfferRecommendation> evaluate(const PodInstanceRequirement& requirement, const std::vector<mesos::Offer>& offers) {
+    auto all = evaluateCycle({requirement}, offers);
+    return all.empty() ? std::vector<OfferRecommendation>() : all[0];
+  }
+
+  // The whole-cycle form PlanScheduler uses: one engine call for every requirement; result[j] belongs to requirement j.
+  std::vector<std::vector<OfferRecommendation>> evaluateCycle(const std::vector<PodInstanceRequirement>& requirements,
+                                                              const std::vector<mesos::Offer>& offers) {
+    std::vector<std::vector<OfferRecommendation>> out(requirements.size());
+    if (requirements.empty()) return out;
+    const std::vector<mesos::TaskInfo> allTasks = stateStore_.fetchTasks();  // OfferEvaluator.java:124 (once per cycle here)
+    for (auto& req : requirements) requireNewPod(req, allTasks);
+    CycleEncoder enc(cfg_);
+    std::vector<EncoderRequirement> ers(requirements.size());
+    for (size_t j = 0; j < requirements.size(); ++j) ers[j].requirement = &requirements[j];
+    EncodedCycle c = enc.encode(offers, allTasks, ers);
+    Engine e(lib_);
+    e.load(c);
+    const std::vector<oe_decision> dec = e.evaluateCycle();
+    lastDecisions_ = dec;
+    for (size_t j = 0; j < requirements.size(); ++j)
+      if (dec[j].offer_row >= 0)
+        out[j] = materialise(requirements[j], offers[(size_t)dec[j].offer_row], c.classStages[(size_t)c.r_class[j]], dec[j]);
+    return out;
+  }
+  const std::vector<oe_decision>& lastDecisions() const { return lastDecisions_; }
+
+ private:
+  // This layer covers the new-pod / permanently-failed pipeline (OfferEvaluator.java:250-310).  A pod whose stored tasks
+  // still hold reservations takes the existing-pod pipeline, which is expressed in the ABI (OE_OP_*_RESERVED, OE_OP_FREE)
+  // but not yet built by this encoder.
+  void requireNewPod(const PodInstanceRequirement& req, const std::vector<mesos::TaskInfo>& allTasks) const {
+    if (req.recoveryType == RecoveryType::PERMANENT) return;
+    for (auto& t : allTasks) {
+      auto ty = t.labels.find(labels::TASK_TYPE);
+      auto ix = t.labels.find(labels::TASK_INDEX);
+      if (ty == t.labels.end() || ix == t.labels.end()) continue;
+      if (ty->second != req.podInstance.pod->type || ix->second != std::to_string(req.podInstance.index)) continue;
+      for (auto& r : t.resources)
+        if (auto id = ResourceUtils::getResourceId(r); id && !id->empty())
+          throw InvalidRequirementException("pod " + req.podInstance.getName() + " has launched tasks with reservations: existing-pod pipeline");
+    }
+  }
+
+  std::string newResourceId() {  // ResourceBuilder.java:318,343 mints UUID.randomUUID(): 36 characters
+    static const char* hex = "0123456789abcdef";
+    std::string s(36, '-');
+    for (int k = 0; k < 36; ++k) if (k != 8 && k != 13 && k != 18 && k != 23) s[(size_t)k] = hex[rng_() & 15];
+    return s;
+  }
+
+  mesos::Resource reservedResource(const StageInfo& s, const mesos::Value& v) {
+    mesos::Resource r;
+    r.name = s.resourceName; r.value = v;
+    if (s.preReservedRole != ANY_ROLE) {  // refined reservation on top of the pre-reserved role (MesosResourcePool.java:349-357)
+      mesos::ReservationInfo st;
+      st.type = mesos::ReservationInfo::STATIC; st.role = s.preReservedRole;
+      r.reservations.push_back(st);
+    }
+    mesos::ReservationInfo dyn;
+    dyn.type = mesos::ReservationInfo::DYNAMIC; dyn.role = s.role; dyn.principal = s.principal;
+    dyn.labels[labels::RESOURCE_ID] = newResourceId();
+    r.reservations.push_back(dyn);
+    return r;
+  }
+
+  std::vector<OfferRecommendation> materialise(const PodInstanceRequirement& req, const mesos::Offer& offer,
+                                               const std::vector<StageInfo>& stages, const oe_decision& d) {
+    std::vector<OfferRecommendation> recs;
+    const PodInstance& pi = req.podInstance;
+    std::map<std::string, mesos::TaskInfo> taskBuilders;  // PodInfoBuilder: one TaskInfo per task spec
+    mesos::ExecutorInfo executor;
+    for (auto& ts : pi.pod->tasks) {
+      mesos::TaskInfo t;
+      t.name = taskInstanceName(pi, ts.name);
+      taskBuilders[ts.name] = t;
+    }
+    int dyn = 0, mount = 0, newIds = 0;
+    auto rec = [&](OfferRecommendation::Type type) -> OfferRecommendation& {
+      OfferRecommendation r;
+      r.type = type; r.offerId = offer.id; r.agentId = offer.slave_id;
+      recs.push_back(r);
+      return recs.back();
+    };
+    auto attach = [&](const StageInfo& s, const mesos::Resource& r) {
+      if (s.taskNames.empty()) executor.resources.push_back(r);
+      else for (auto& n : s.taskNames) taskBuilders[n].resources.push_back(r);
+    };
+    for (auto& s : stages) {
+      switch (s.kind) {
+        case StageInfo::EXECUTOR: case StageInfo::PLACEMENT: case StageInfo::TLS: break;
+        case StageInfo::RESOURCE: {
+          mesos::Resource r = reservedResource(s, mesos::Value::Scalar(s.value));
+          ++newIds;
+          rec(OfferRecommendation::RESERVE).resource = r;
+          attach(s, r);
+        } break;
+        case StageInfo::PORT: {
+          int port = s.port;
+          if (s.hostPort && port == 0) port = d.dyn_port[dyn < OE_MAX_DYN_PORTS ? dyn : OE_MAX_DYN_PORTS - 1];
+          if (s.hostPort && s.port == 0) ++dyn;
+          if (!s.hostPort) break;  // overlay: no reservation (PortEvaluationStage.java:145-154)
+          mesos::Resource r = reservedResource(s, mesos::Value::Ranges({{port, port}}));
+          ++newIds;
+          rec(OfferRecommendation::RESERVE).resource = r;
+          attach(s, r);
+        } break;
+        case StageInfo::VOLUME: {
+          mesos::Value v = mesos::Value::Scalar(s.value);
+          mesos::DiskInfo disk;
+          disk.container_path = s.containerPath;
+          disk.persistence_id = newResourceId();
+          if (s.volumeType != VolumeSpec::ROOT) {
+            // the whole MOUNT disk is taken (VolumeEvaluationStage.java:205-215: setValue(mesosResource.getValue()))
+            const int slot = d.mount_slot[mount < OE_MAX_MOUNT_OPS ? mount : OE_MAX_MOUNT_OPS - 1];
+            ++mount;
+            int seen = 0;
+            for (auto& or_ : offer.resources)
+              if (ResourceUtils::isAtomic(or_) && !ResourceUtils::getResourceId(or_) && or_.name == "disk" && seen++ == slot) {
+                v = or_.value; disk.source = mesos::DiskInfo::MOUNT; disk.profile = or_.disk->profile;
+              }
+          }
+          mesos::Resource r = reservedResource(s, v);
+          r.disk = disk;
+          ++newIds;
+          rec(OfferRecommendation::RESERVE).resource = r;
+          rec(OfferRecommendation::CREATE).resource = r;   // no persistence id yet: createsVolume() (:222-226)
+          attach(s, r);
+        } break;
+        case StageInfo::LAUNCH: {  // LaunchEvaluationStage.java:42-90
+          mesos::TaskInfo& t = taskBuilders[s.taskSpecName];
+          t.task_id = s.shouldLaunch ? t.name + "__" + newResourceId() : "";
+          t.slave_id = offer.slave_id;
+          TaskLabelWriter w(t);
+          w.setOfferAttributes(offer).setType(pi.pod->type).setIndex(pi.index).setHostname(offer);
+          if (offer.domain) w.setRegion(offer.domain->region).setZone(offer.domain->zone);
+          t.executor = executor;
+          if (s.shouldLaunch) rec(OfferRecommendation::LAUNCH_GROUP).task = t;
+          rec(OfferRecommendation::STORE_TASK).task = t;
+        } break;
+      }
+    }
+    if (newIds != d.n_new_reservations)
+      throw std::logic_error("engine and adapter disagree on the number of new reservations (" + std::to_string(d.n_new_reservations) +
+                             " vs " + std::to_string(newIds) + ")");
+    return recs;
+  }
+
+  const EngineLibrary& lib_;
+  StateStore& stateStore_;
+  std::string serviceName_;
+  SchedulerConfig cfg_;
+  std::mt19937_64 rng_{20240607};
+  std::vector<oe_decision> lastDecisions_;
+};
+
+// S/scheduler/plan/Step.java reduced to what PlanScheduler reads.
+struct Step {
+  std::string name;
+  std::optional<PodInstanceRequirement> requirement;
+  enum Status { PENDING, PREPARED, STARTING, COMPLETE } status = PENDING;
+  bool isPendingOrPrepared() const { return status == PENDING || status == PREPARED; }
+};
+
+// S/scheduler/plan/PlanScheduler.java:50-124
+class PlanScheduler {
+ public:
+  explicit PlanScheduler(OfferEvaluator& e) : evaluator_(e) {}
+  // Steps in order; each takes the first offer that fits among the offers no earlier step of this cycle used (:56-67).
+  // Steps that are not pending / prepared, or carry no requirement, are skipped (:73-92).  `steps` get STARTING on success.
+  std::vector<OfferRecommendation> resourceOffers(const std::vector<mesos::Offer>& offers, std::vector<Step>& steps) {
+    std::vector<OfferRecommendation> all;
+    if (offers.empty() || steps.empty()) return all;  // :52-54
+    std::vector<PodInstanceRequirement> reqs;
+    std::vector<size_t> which;
+    for (size_t k = 0; k < steps.size(); ++k)
+      if (steps[k].isPendingOrPrepared() && steps[k].requirement) { reqs.push_back(*steps[k].requirement); which.push_back(k); }
+    auto per = evaluator_.evaluateCycle(reqs, offers);
+    for (size_t j = 0; j < per.size(); ++j) {
+      if (per[j].empty()) continue;
+      steps[which[j]].status = Step::STARTING;
+      all.insert(all.end(), per[j].begin(), per[j].end());
+    }
+    return all;
+  }
+ private:
+  OfferEvaluator& evaluator_;
+};
+
+}  // namespace sdk

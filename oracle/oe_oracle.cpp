@@ -23,7 +23,7 @@
 //   S/offer/TaskUtils.java:136-145                       equivalent()
 //   S/offer/evaluate/LaunchEvaluationStage.java:58-68, S/state/PersistentLaunchRecorder.java:74-137   apply_launches()
 //
-// Parity pin: tests/test_kat_*.py restate the reference's JUnit vectors against this oracle.  The JVM
+// Parity pin: tests/kat/*.cpp (run by tests/test_kat.py) restate the reference's JUnit vectors against this oracle.  The JVM
 // reference itself cannot be built or run in this environment (no JDK, no Maven cache).
 #include <algorithm>
 #include <cmath>
