@@ -153,13 +153,6 @@ def pin_tables(t):
     return p
 
 
-class _CudaView:
-    """Exposes a raw device pointer through __cuda_array_interface__ so torch.distributed can gather engine memory."""
-
-    def __init__(self, ptr, n_words):
-        self.__cuda_array_interface__ = {"shape": (n_words,), "typestr": "<i4", "data": (ptr, False), "version": 2}
-
-
 def cpu_baseline_sample(t, seconds, n_sample_offers=1000):
     """Reference path (CPU oracle, 1 thread) on a bounded sample of the same workload: whole requirement rows over the
     first `n_sample_offers` offers, until the time budget is used."""
@@ -246,7 +239,7 @@ def _ref_row(j):
 # ----------------------------------------------------------------------------------------------------------------------
 def run_engine(args):
     import torch
-    from dcos_commons_b200 import Engine, abi
+    from dcos_commons_b200 import Engine, abi, sharded
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -261,11 +254,8 @@ def run_engine(args):
     cl = make_workload(args)
     t = cl.tables
     N, M = t.n_offers, t.n_reqs
-    if world > 1:
-        shard_rows = ((N + world - 1) // world + 1023) // 1024 * 1024
-        lo, hi = min(N, rank * shard_rows), min(N, (rank + 1) * shard_rows)
-    else:
-        shard_rows, lo, hi = 0, 0, N
+    shard_rows, bounds = sharded.shard_plan(N, world)
+    lo, hi = bounds[rank]
     n_local = hi - lo
 
     def barrier():
@@ -310,20 +300,13 @@ def run_engine(args):
     pt = pin_tables(t)
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX)
-    gl = None
 
     def cycle():
         eng2.load(pt, lo, hi, shard_rows)
         if world > 1:
-            eng2.feasibility(fetch=False)
-            nonlocal gl
-            lp, lb = eng2.device_buffer(abi.BUF_CLASS_BITS_LOCAL)
-            gp, gb = eng2.device_buffer(abi.BUF_CLASS_BITS_GLOBAL)
-            local = torch.as_tensor(_CudaView(lp, lb // 4), device="cuda")
-            glob = torch.as_tensor(_CudaView(gp, gb // 4), device="cuda")
-            dist.all_gather_into_tensor(glob, local)
-            torch.cuda.current_stream().synchronize()
-        return eng2.evaluate_cycle_into(out.data_ptr())
+            eng2.feasibility(fetch=False)                 # K0 + K1 + K1x on this rank's shard
+            sharded.gather_class_bits(eng2, dist)         # the one exchange step: class rows of every shard
+        return eng2.evaluate_cycle_into(out.data_ptr())   # K3 + K2 (replayed identically on every rank) + D2H
 
     cyc_stats = None
     for _ in range(max(1, min(args.warmup, 3))):
