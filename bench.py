@@ -301,17 +301,30 @@ def run_engine(args):
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX)
 
+    host_ms = {}
+
+    def timed(name, fn):
+        t0 = time.perf_counter()
+        r = fn()
+        host_ms[name] = host_ms.get(name, 0.0) + 1e3 * (time.perf_counter() - t0)
+        return r
+
     def cycle():
-        eng2.load(pt, lo, hi, shard_rows)
+        eng2.tables = pt
+        timed("load_programs", lambda: eng2.load_programs(pt))
+        timed("load_tasks", lambda: eng2.load_tasks(pt))
+        timed("load_offers", lambda: eng2.load_offers(pt, lo, hi, shard_rows))
+        timed("load_requirements", lambda: eng2.load_requirements(pt))
         if world > 1:
             eng2.feasibility(fetch=False)                 # K0 + K1 + K1x on this rank's shard
             sharded.gather_class_bits(eng2, dist)         # the one exchange step: class rows of every shard
-        return eng2.evaluate_cycle_into(out.data_ptr())   # K3 + K2 (replayed identically on every rank) + D2H
+        return timed("evaluate_cycle", lambda: eng2.evaluate_cycle_into(out.data_ptr()))   # K3 + K2 (replayed identically on every rank) + D2H
 
     cyc_stats = None
     for _ in range(max(1, min(args.warmup, 3))):
         cyc_stats = cycle()
     barrier()
+    host_ms.clear()
     e2e_steps = max(1, min(args.steps, 5))
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -327,7 +340,7 @@ def run_engine(args):
     e2e = {"value": e2e_steps * N * M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
            "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
-           "placed": cyc_stats["n_placed"]}
+           "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"]}
 
     if rank != 0:
         if dist is not None:

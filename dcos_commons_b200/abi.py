@@ -227,7 +227,7 @@ class CycleTables:
         t.attr_id, t.rr_key, t.filter_bits = _ptr(self.t_attr_id), _ptr(self.t_rr_key), _ptr(self.t_filter_bits)
         return t
 
-    def c_offers(self, lo: int = 0, hi: Optional[int] = None, shard_rows: int = 0) -> OeOfferTable:
+    def c_offers(self, lo: int = 0, hi: Optional[int] = None, shard_rows: int = 0, row_offset: Optional[int] = None) -> OeOfferTable:
         """Offer table for rows [lo, hi) (a shard when lo/hi are given)."""
         n_all = self.n_offers
         hi = n_all if hi is None else hi
@@ -240,7 +240,8 @@ class CycleTables:
             self._keep.append(b)
             return b
         t = OeOfferTable()
-        t.n_offers, t.row_offset, t.n_offers_global, t.shard_rows = hi - lo, lo, n_all, shard_rows
+        # an empty trailing shard still sits at its nominal offset (rank * shard_rows)
+        t.n_offers, t.row_offset, t.n_offers_global, t.shard_rows = hi - lo, (row_offset if row_offset is not None else lo), n_all, shard_rows
         S, K, _ = self.scalar.shape
         t.n_role_slots, t.n_scalar_kinds = S, K
         t.n_port_ranges = self.port_range.shape[1]
@@ -351,7 +352,7 @@ class Handle:
         self._check(self.b.fn("load_tasks")(self.h, C.byref(self._ct)))
 
     def load_offers(self, t: CycleTables, lo=0, hi=None, shard_rows=0):
-        self._co = t.c_offers(lo, hi, shard_rows)
+        self._co = t.c_offers(lo, hi, shard_rows, self.rank * shard_rows if (shard_rows and self.world > 1) else None)
         self._n_local = int(self._co.n_offers)
         self._check(self.b.fn("load_offers")(self.h, C.byref(self._co)))
 

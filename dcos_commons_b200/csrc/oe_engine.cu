@@ -340,12 +340,14 @@ __global__ void __launch_bounds__(256) k_compact_rows(RowBits rb, int tiles, con
 // K2: the greedy commit of PlanScheduler.resourceOffers (S/scheduler/plan/PlanScheduler.java:56-67): requirements in
 // order, each claims the lowest-index feasible offer that no earlier requirement of the cycle claimed.
 //
-// One warp takes 32 consecutive requirements at a time, one per lane.  Every unresolved lane PROPOSES an offer: the
-// (rank)-th unclaimed candidate of its row at or after the row's cursor, where rank counts the unresolved lanes of the
-// same row below it.  Proposals are then RESOLVED in requirement order: the longest prefix of unresolved lanes whose
-// proposals are pairwise distinct is final (an earlier requirement can only disturb a later one by claiming exactly the
-// offer the later one proposed — anything lower that the later one could use is by construction already claimed).  The
-// first lane that lost its offer re-proposes in the next round.  Claimed offers live in a shared-memory bitmap.
+// One warp takes 32 consecutive requirements at a time, one per lane.  Round: every unresolved lane scans the next
+// OE_SCAN entries of its row's candidate list from the row's cursor and HOLDS its first OE_HOLD unclaimed candidates in
+// registers (a lane that shares its row with r earlier unresolved lanes skips r of them: those lanes take at least that
+// many).  The lanes are then resolved in registers: a lane whose head candidate is held as head or pick by no earlier
+// lane, and that sits before the first lane still in doubt, is final; a lane whose head was taken by a final earlier
+// lane drops it and offers its next one.  A lane that runs out of held candidates while its list may have more goes
+// again next round (with everything after it); a lane whose list is exhausted for good gets -1.  Claimed offers live
+// in a shared-memory bitmap; candidate lists are read through a small shared-memory window cache.
 struct CommitArgs {
   const int32_t* cand;
   const int64_t* row_base;
@@ -360,7 +362,9 @@ struct CommitArgs {
   int used_in_smem, cursor_in_smem;
   int* n_placed;
 };
-#define OE_PROPOSE_WINDOW 8
+#define OE_SCAN 8           // list entries a lane looks at per round
+#define OE_HOLD 4           // unclaimed candidates a lane holds in registers per round
+#define OE_PROPOSE_WINDOW OE_SCAN
 #define OE_WIN_SLOTS 64     // direct-mapped cache of candidate windows, one row per slot
 #define OE_WIN_ENTRIES 64   // candidates per cached window
 
@@ -381,23 +385,25 @@ __global__ void __launch_bounds__(256) k_commit(CommitArgs a) {
   const int lane = threadIdx.x;
   const uint32_t lt = (1u << lane) - 1u;
   int placed = 0;
+  int next_row = lane < a.M ? __ldg(a.req_row + lane) : -1 - lane;
 
   for (int64_t j0 = 0; j0 < a.M; j0 += 32) {
     const bool active = j0 + lane < a.M;
-    const int row = active ? a.req_row[j0 + lane] : -1 - lane;
-    const int len = active ? a.row_len[row] : 0;
-    const int32_t* list = active ? a.cand + a.row_base[row] : nullptr;
+    const int row = next_row;
+    next_row = (j0 + 32 + lane < a.M) ? __ldg(a.req_row + j0 + 32 + lane) : -1 - lane;  // in flight while this batch resolves
+    const int len = active ? __ldg(a.row_len + row) : 0;
+    const int32_t* list = active ? a.cand + __ldg(a.row_base + row) : nullptr;
     const int slot = row & (OE_WIN_SLOTS - 1);
     bool final = !active;
     int pick = -1;
     uint32_t open = __ballot_sync(0xffffffffu, !final);
     while (open) {
-      // ---- make sure the window [cursor, cursor + OE_PROPOSE_WINDOW) of every unresolved lane's row is cached
+      // ---- make sure the window [cursor, cursor + OE_SCAN) of every unresolved lane's row is cached
       int k = 0;
       bool need = false;
       if (!final) {
         k = cursor[row];
-        need = !(win_row[slot] == row && win_base[slot] <= k && k + OE_PROPOSE_WINDOW <= win_base[slot] + OE_WIN_ENTRIES);
+        need = !(win_row[slot] == row && win_base[slot] <= k && k + OE_SCAN <= win_base[slot] + OE_WIN_ENTRIES);
       }
       uint32_t needs = __ballot_sync(0xffffffffu, need);
       while (needs) {
@@ -416,60 +422,70 @@ __global__ void __launch_bounds__(256) k_commit(CommitArgs a) {
         // other lanes of the same row at the same cursor are served by this refill
         needs &= ~__ballot_sync(0xffffffffu, need && row == r);
       }
-      // ---- propose
-      int prop = -2;  // -2 = cannot tell yet, -1 = the row has nothing left for this lane, >= 0 = offer
-      int prop_k = 0, scanned_to = 0;
+      // ---- hold the first OE_HOLD unclaimed candidates of the scan in registers
+      int o[OE_HOLD], off[OE_HOLD];
+      uint32_t valid = 0, unclaimed = 0;
+      bool more = false;
+#pragma unroll
+      for (int c = 0; c < OE_HOLD; ++c) { o[c] = -1; off[c] = 0; }
       if (!final) {
-        const uint32_t peers = __match_any_sync(open, row);
-        const int rank = __popc(peers & lt);
-        int o[OE_PROPOSE_WINDOW];
-        const bool hit = win_row[slot] == row && win_base[slot] <= k && k + OE_PROPOSE_WINDOW <= win_base[slot] + OE_WIN_ENTRIES;
-        if (hit) {
-          const int32_t* w = win + slot * OE_WIN_ENTRIES + (k - win_base[slot]);
+        const bool hit = win_row[slot] == row && win_base[slot] <= k && k + OE_SCAN <= win_base[slot] + OE_WIN_ENTRIES;
+        const int32_t* w = win + slot * OE_WIN_ENTRIES + (k - win_base[slot]);
+        int cv[OE_SCAN];
 #pragma unroll
-          for (int t = 0; t < OE_PROPOSE_WINDOW; ++t) o[t] = w[t];
-        } else {  // slot stolen by another row of this batch: read through
-#pragma unroll
-          for (int t = 0; t < OE_PROPOSE_WINDOW; ++t) o[t] = (k + t < len) ? __ldg(list + k + t) : -1;
+        for (int t = 0; t < OE_SCAN; ++t) {
+          // a slot stolen by another row of this batch is read through
+          cv[t] = hit ? w[t] : ((k + t < len) ? __ldg(list + k + t) : -1);
+          if (cv[t] >= 0 && !((used[cv[t] >> 5] >> (cv[t] & 31)) & 1u)) unclaimed |= 1u << t;
         }
-        uint32_t unused = 0;
+        // same-row lanes below this one take at least one candidate each, in list order: skip that many
+        const int rank = __popc(__match_any_sync(open, row) & lt);
+        uint32_t rest = unclaimed;
+        for (int q = 0; q < rank && rest; ++q) rest &= rest - 1;
+        more = (k + OE_SCAN < len) || __popc(rest) > OE_HOLD;
 #pragma unroll
-        for (int t = 0; t < OE_PROPOSE_WINDOW; ++t)
-          if (o[t] >= 0 && !((used[o[t] >> 5] >> (o[t] & 31)) & 1u)) unused |= 1u << t;
-        const int n_unused = __popc(unused);
-        if (rank < n_unused) {
-          const int t = __fns(unused, 0, rank + 1);
-          prop_k = k + t;
+        for (int c = 0; c < OE_HOLD; ++c) {
+          if (rest) {
+            const int t = __ffs(rest) - 1;
+            rest &= rest - 1;
+            off[c] = t;
+            int v = -1;
 #pragma unroll
-          for (int q = 0; q < OE_PROPOSE_WINDOW; ++q) if (q == t) prop = o[q];
-        } else if (k + OE_PROPOSE_WINDOW >= len) {
-          prop = -1;  // list exhausted: fewer unclaimed candidates than earlier requirements of this row will take
-        } else if (rank == 0) {
-          scanned_to = k + OE_PROPOSE_WINDOW;  // whole window claimed: move the cursor and look again
+            for (int q = 0; q < OE_SCAN; ++q) if (q == t) v = cv[q];
+            o[c] = v;
+            valid |= 1u << c;
+          }
         }
       }
-      // ---- resolve in requirement order
-      bool ok = false;
-      if (!final) {
-        const uint32_t proposing = __ballot_sync(open, prop >= 0);
-        if (prop == -1) {
-          ok = true;
-        } else if (prop >= 0) {
-          const uint32_t grp = __match_any_sync(proposing, prop);
-          ok = (__ffs(grp) - 1) == lane;
-        }
+      // ---- resolve in registers
+      uint32_t fin_mask = __ballot_sync(0xffffffffu, final);
+      bool done_now = false;
+      int pos = 0;
+      for (;;) {
+        int head = -1, hoff = 0;
+#pragma unroll
+        for (int c = OE_HOLD - 1; c >= 0; --c)
+          if ((valid >> c) & 1u) { head = o[c]; hoff = off[c]; }
+        int key = final ? pick : head;
+        if (key < 0) key = -1 - lane;
+        const uint32_t lower = __match_any_sync(0xffffffffu, key) & lt;
+        const bool in_doubt = !final && head < 0 && more;  // ran out of held candidates, the list may have more
+        const bool conflicted = !final && head >= 0 && lower != 0u;
+        const uint32_t stop = __ballot_sync(0xffffffffu, in_doubt || conflicted);
+        const int first_stop = stop ? __ffs(stop) - 1 : 32;
+        const bool fin_now = !final && !in_doubt && !conflicted && (head < 0 || lane < first_stop);
+        const uint32_t newly = __ballot_sync(0xffffffffu, fin_now);
+        if (fin_now) { final = true; done_now = true; pick = head; pos = k + hoff + 1; }
+        fin_mask |= newly;
+        const bool drop = conflicted && (lower & fin_mask) != 0u;  // the earlier holder is final: that offer is gone
+        if (drop) valid &= valid - 1;
+        if (!(newly | __ballot_sync(0xffffffffu, drop))) break;
       }
-      const uint32_t bad = __ballot_sync(0xffffffffu, !final && !ok);
-      const int first_bad = bad ? __ffs(bad) - 1 : 32;
-      if (!final && lane < first_bad) {
-        final = true;
-        pick = prop;
-        if (prop >= 0) {
-          atomicOr(&used[prop >> 5], 1u << (prop & 31));
-          atomicMax(&cursor[row], prop_k + 1);
-        }
-      } else if (!final && scanned_to > 0) {
-        atomicMax(&cursor[row], scanned_to);
+      if (done_now && pick >= 0) {
+        atomicOr(&used[pick >> 5], 1u << (pick & 31));
+        atomicMax(&cursor[row], pos);  // everything before the winner was claimed, or it would have won
+      } else if (!final && unclaimed == 0u && k + OE_SCAN < len) {
+        atomicMax(&cursor[row], k + OE_SCAN);  // the whole scan is claimed: move on
       }
       __syncwarp();
       open = __ballot_sync(0xffffffffu, !final);
@@ -590,6 +606,7 @@ struct oe_engine {
   DevBuf d_tcols[7], d_tattr, d_trr, d_tfilter;
   std::vector<int32_t> h_tname, h_ttype, h_tindex;  // host mirror of what apply_launches / self detection need
   std::unordered_map<int32_t, int32_t> name_to_row;
+  bool name_map_built = false;
 
   // ---- offers
   DevOffers dof{};
@@ -971,7 +988,7 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   h->h_ttype.assign(t->pod_type_id, t->pod_type_id + T);
   h->h_tindex.assign(t->pod_index, t->pod_index + T);
   h->name_to_row.clear();
-  for (int64_t r = 0; r < T; ++r) h->name_to_row[h->h_tname[r]] = (int32_t)r;
+  h->name_map_built = false;  // only oe_apply_launches needs it: built on first use
   if (int rc = fetch_err_flag(h, "oe_load_tasks")) return rc;
   h->hasT = true;
   return OE_OK;
@@ -1087,17 +1104,34 @@ int rebuild_variants(oe_engine* h) {
       if (e == b || !h->class_self_sensitive[h->h_class[j]]) continue;
       if (int rc = add_variant(j, h->h_self_rows.data() + b, e - b)) return rc;
     }
-  } else if (T > 0) {
-    std::unordered_map<uint64_t, std::vector<int32_t>> by_pod;
-    for (int64_t r = 0; r < T; ++r) {
+  } else if (T > 0 && std::any_of(h->class_self_sensitive.begin(), h->class_self_sensitive.end(), [](uint8_t x) { return x != 0; })) {
+    // open-addressing table pod key (type, index) -> chain of task rows; no per-entry allocation
+    size_t cap = 16;
+    while (cap < (size_t)T * 2) cap <<= 1;
+    const uint64_t EMPTY = ~0ull;
+    std::vector<uint64_t> keys(cap, EMPTY);
+    std::vector<int32_t> head(cap, -1), next((size_t)T, -1);
+    auto slot_of = [&](uint64_t key) {
+      size_t q = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 17) & (cap - 1);
+      while (keys[q] != EMPTY && keys[q] != key) q = (q + 1) & (cap - 1);
+      return q;
+    };
+    for (int64_t r = T - 1; r >= 0; --r) {  // descending, so that every chain lists its rows in ascending order
       if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
-      by_pod[((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r]].push_back((int32_t)r);
+      const uint64_t key = ((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r];
+      const size_t q = slot_of(key);
+      keys[q] = key;
+      next[(size_t)r] = head[q];
+      head[q] = (int32_t)r;
     }
+    std::vector<int32_t> chain;
     for (int64_t j = 0; j < M; ++j) {
       if (!h->class_self_sensitive[h->h_class[j]]) continue;
-      auto it = by_pod.find(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
-      if (it == by_pod.end()) continue;
-      if (int rc = add_variant(j, it->second.data(), (int)it->second.size())) return rc;
+      const size_t q = slot_of(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
+      if (keys[q] == EMPTY) continue;
+      chain.clear();
+      for (int32_t r = head[q]; r >= 0; r = next[(size_t)r]) chain.push_back(r);
+      if (int rc = add_variant(j, chain.data(), (int)chain.size())) return rc;
     }
   }
   h->V = (int)vcls.size();
@@ -1559,6 +1593,11 @@ int32_t oe_apply_launches(oe_engine* h) {
   if (h->dt.TA < h->dof.A) return h->fail(OE_ERR_INVALID, "oe_apply_launches: task table has fewer attribute slots than the offer table");
   std::vector<int32_t> dst, req, name;
   std::vector<uint32_t> filt;
+  if (!h->name_map_built) {
+    h->name_to_row.reserve(h->h_tname.size() * 2 + 16);
+    for (size_t r = 0; r < h->h_tname.size(); ++r) h->name_to_row[h->h_tname[r]] = (int32_t)r;
+    h->name_map_built = true;
+  }
   int64_t T = h->dt.T;
   const int FW = h->dt.FW;
   for (int64_t j = 0; j < h->M; ++j) {
