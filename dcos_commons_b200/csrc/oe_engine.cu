@@ -5,7 +5,8 @@
 //   K1  k_class_feasibility             offers × requirement classes → class-factored feasibility bits
 //   K1x k_expand_matrix                 class bits → full offers × requirements bit matrix (the HBM-bound pass)
 //   K3  k_tile_popc / k_row_offsets / k_compact_rows   class bits → ascending candidate lists per factored row
-//   K2  k_commit                        ordered greedy first-fit: batched propose / in-order resolve, shared-memory bitmap
+//   K3d k_row_overlap                   which bit rows share an offer (components that commit independently)
+//   K2  k_commit                        ordered greedy first-fit: one lane per component, shared-memory claimed bitmap
 //   K2b k_materialize                   winners → chosen dynamic ports / MOUNT slots
 //   K4  k_apply_launches                multi-cycle replay: placed pods → task rows
 //
@@ -337,17 +338,33 @@ __global__ void __launch_bounds__(256) k_compact_rows(RowBits rb, int tiles, con
   }
 }
 
+// K3d: which bit rows share an offer.  adj[r] gets bit q set iff rows r and q are both feasible for some offer.  Rows that
+// share nothing can be committed independently of each other.  thread = one 32-offer word; only used when rows <= 64.
+#define OE_ADJ_MAX_ROWS 64
+__global__ void __launch_bounds__(128) k_row_overlap(RowBits rb, unsigned long long* __restrict__ adj) {
+  __shared__ uint32_t tile[OE_ADJ_MAX_ROWS][128];
+  const int64_t gw = (int64_t)blockIdx.x * 128 + threadIdx.x;
+  for (int r = 0; r < rb.rows; ++r) tile[r][threadIdx.x] = gw < rb.total_words ? rb.word(r, gw) : 0u;
+  for (int r = 0; r < rb.rows; ++r) {
+    const uint32_t w = tile[r][threadIdx.x];
+    unsigned long long acc = 0ull;
+    if (w)
+      for (int q = 0; q < rb.rows; ++q) acc |= (unsigned long long)((w & tile[q][threadIdx.x]) != 0u) << q;
+    for (int d = 16; d > 0; d >>= 1) acc |= __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0 && acc) atomicOr(adj + r, acc);
+  }
+}
+
 // K2: the greedy commit of PlanScheduler.resourceOffers (S/scheduler/plan/PlanScheduler.java:56-67): requirements in
 // order, each claims the lowest-index feasible offer that no earlier requirement of the cycle claimed.
 //
-// One warp takes 32 consecutive requirements at a time, one per lane.  Round: every unresolved lane scans the next
-// OE_SCAN entries of its row's candidate list from the row's cursor and HOLDS its first OE_HOLD unclaimed candidates in
-// registers (a lane that shares its row with r earlier unresolved lanes skips r of them: those lanes take at least that
-// many).  The lanes are then resolved in registers: a lane whose head candidate is held as head or pick by no earlier
-// lane, and that sits before the first lane still in doubt, is final; a lane whose head was taken by a final earlier
-// lane drops it and offers its next one.  A lane that runs out of held candidates while its list may have more goes
-// again next round (with everything after it); a lane whose list is exhausted for good gets -1.  Claimed offers live
-// in a shared-memory bitmap; candidate lists are read through a small shared-memory window cache.
+// The order only matters between requirements that can compete for an offer.  Bit rows are grouped into connected
+// components of the "share an offer" relation (K3d); requirements of different components commute, so each component
+// is replayed strictly in plan order by ONE lane of a warp, up to 32 components side by side.  A lane's step is a short
+// dependent chain: row state (cursor, length, list) from shared memory, next candidate from the row's ascending list
+// (read-only global memory, L1 resident since a lane walks it forwards), claimed bit from the shared-memory bitmap.
+// Prologue (whole CTA): label the components, then a stable counting sort of the requirements by component.
+struct RowState { int cursor, len; long long base; };
 struct CommitArgs {
   const int32_t* cand;
   const int64_t* row_base;
@@ -357,143 +374,120 @@ struct CommitArgs {
   const int32_t* req_row;
   int64_t M;
   oe_decision* dec;
-  uint32_t* used_g;   // global-memory fallbacks (when the shared-memory budget is exceeded)
-  int32_t* cursor_g;
-  int used_in_smem, cursor_in_smem;
+  uint32_t* used_g;                  // global-memory fallbacks when the bitmap / row states exceed shared memory
+  struct RowState* rows_g;
+  int used_in_smem, rows_in_smem;
+  const unsigned long long* adj;     // [rows] from K3d, or null (one component)
+  int2* order;                       // [M] scratch: (requirement, row) grouped by component, plan order kept inside a group
   int* n_placed;
 };
-#define OE_SCAN 8           // list entries a lane looks at per round
-#define OE_HOLD 4           // unclaimed candidates a lane holds in registers per round
-#define OE_PROPOSE_WINDOW OE_SCAN
-#define OE_WIN_SLOTS 64     // direct-mapped cache of candidate windows, one row per slot
-#define OE_WIN_ENTRIES 64   // candidates per cached window
+#define OE_COMMIT_THREADS 1024  // 32 warps: one per component
+#define OE_SORT_THREADS 256     // threads that take part in the counting sort of the prologue
 
-__global__ void __launch_bounds__(256) k_commit(CommitArgs a) {
-  extern __shared__ uint32_t smem[];
-  int32_t* win = (int32_t*)smem;                                  // [OE_WIN_SLOTS][OE_WIN_ENTRIES]
-  int32_t* win_row = win + OE_WIN_SLOTS * OE_WIN_ENTRIES;         // [OE_WIN_SLOTS]
-  int32_t* win_base = win_row + OE_WIN_SLOTS;                     // [OE_WIN_SLOTS]
-  uint32_t* p = (uint32_t*)(win_base + OE_WIN_SLOTS);
-  int32_t* cursor = a.cursor_g;
-  if (a.cursor_in_smem) { cursor = (int32_t*)p; p += a.rows; }
-  uint32_t* used = a.used_in_smem ? p : a.used_g;
-  for (int64_t k = threadIdx.x; k < a.used_words; k += blockDim.x) used[k] = 0;
-  for (int k = threadIdx.x; k < a.rows; k += blockDim.x) cursor[k] = 0;
-  for (int k = threadIdx.x; k < OE_WIN_SLOTS; k += blockDim.x) { win_row[k] = -1; win_base[k] = 0; }
-  __syncthreads();
-  if (threadIdx.x >= 32) return;
-  const int lane = threadIdx.x;
-  const uint32_t lt = (1u << lane) - 1u;
-  int placed = 0;
-  int next_row = lane < a.M ? __ldg(a.req_row + lane) : -1 - lane;
-
-  for (int64_t j0 = 0; j0 < a.M; j0 += 32) {
-    const bool active = j0 + lane < a.M;
-    const int row = next_row;
-    next_row = (j0 + 32 + lane < a.M) ? __ldg(a.req_row + j0 + 32 + lane) : -1 - lane;  // in flight while this batch resolves
-    const int len = active ? __ldg(a.row_len + row) : 0;
-    const int32_t* list = active ? a.cand + __ldg(a.row_base + row) : nullptr;
-    const int slot = row & (OE_WIN_SLOTS - 1);
-    bool final = !active;
-    int pick = -1;
-    uint32_t open = __ballot_sync(0xffffffffu, !final);
-    while (open) {
-      // ---- make sure the window [cursor, cursor + OE_SCAN) of every unresolved lane's row is cached
-      int k = 0;
-      bool need = false;
-      if (!final) {
-        k = cursor[row];
-        need = !(win_row[slot] == row && win_base[slot] <= k && k + OE_SCAN <= win_base[slot] + OE_WIN_ENTRIES);
-      }
-      uint32_t needs = __ballot_sync(0xffffffffu, need);
-      while (needs) {
-        const int leader = __ffs(needs) - 1;
-        const int r = __shfl_sync(0xffffffffu, row, leader);
-        const int kk = __shfl_sync(0xffffffffu, k, leader);
-        const int rl = __shfl_sync(0xffffffffu, len, leader);
-        const int32_t* rlist = a.cand + a.row_base[r];
-        const int rs = r & (OE_WIN_SLOTS - 1);
-        __syncwarp();
-        win[rs * OE_WIN_ENTRIES + lane] = (kk + lane < rl) ? __ldg(rlist + kk + lane) : -1;
-        win[rs * OE_WIN_ENTRIES + 32 + lane] = (kk + 32 + lane < rl) ? __ldg(rlist + kk + 32 + lane) : -1;
-        if (lane == leader) { win_row[rs] = r; win_base[rs] = kk; }
-        __syncwarp();
-        needs &= ~(1u << leader);
-        // other lanes of the same row at the same cursor are served by this refill
-        needs &= ~__ballot_sync(0xffffffffu, need && row == r);
-      }
-      // ---- hold the first OE_HOLD unclaimed candidates of the scan in registers
-      int o[OE_HOLD], off[OE_HOLD];
-      uint32_t valid = 0, unclaimed = 0;
-      bool more = false;
-#pragma unroll
-      for (int c = 0; c < OE_HOLD; ++c) { o[c] = -1; off[c] = 0; }
-      if (!final) {
-        const bool hit = win_row[slot] == row && win_base[slot] <= k && k + OE_SCAN <= win_base[slot] + OE_WIN_ENTRIES;
-        const int32_t* w = win + slot * OE_WIN_ENTRIES + (k - win_base[slot]);
-        int cv[OE_SCAN];
-#pragma unroll
-        for (int t = 0; t < OE_SCAN; ++t) {
-          // a slot stolen by another row of this batch is read through
-          cv[t] = hit ? w[t] : ((k + t < len) ? __ldg(list + k + t) : -1);
-          if (cv[t] >= 0 && !((used[cv[t] >> 5] >> (cv[t] & 31)) & 1u)) unclaimed |= 1u << t;
+__global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
+  extern __shared__ __align__(16) unsigned char commit_smem[];
+  __shared__ int comp_of[OE_ADJ_MAX_ROWS];
+  __shared__ int n_comp_s, placed_s;
+  __shared__ int cnt[32][OE_SORT_THREADS + 1];
+  __shared__ int comp_begin[33];
+  RowState* rs = a.rows_in_smem ? reinterpret_cast<RowState*>(commit_smem) : a.rows_g;   // [rows]
+  uint32_t* used = a.used_in_smem ? reinterpret_cast<uint32_t*>(commit_smem + (a.rows_in_smem ? (size_t)a.rows * sizeof(RowState) : 0)) : a.used_g;
+  const int tid = threadIdx.x;
+  for (int64_t k = tid; k < a.used_words; k += OE_COMMIT_THREADS) used[k] = 0u;
+  for (int r = tid; r < a.rows; r += OE_COMMIT_THREADS) { rs[r].cursor = 0; rs[r].len = a.row_len[r]; rs[r].base = a.row_base[r]; }
+  // ---- components of the rows (labels 0..n_comp-1 in order of their lowest row; folded onto 32 warps)
+  if (tid == 0) {
+    placed_s = 0;
+    int n = 1;
+    if (a.adj) {
+      n = 0;
+      unsigned long long seen = 0ull;
+      for (int r = 0; r < a.rows; ++r) {
+        if ((seen >> r) & 1ull) continue;
+        unsigned long long group = 1ull << r, frontier = group;
+        while (frontier) {
+          const int q = __ffsll((long long)frontier) - 1;
+          frontier &= frontier - 1;
+          const unsigned long long nb = a.adj[q] & ~group;
+          group |= nb;
+          frontier |= nb;
         }
-        // same-row lanes below this one take at least one candidate each, in list order: skip that many
-        const int rank = __popc(__match_any_sync(open, row) & lt);
-        uint32_t rest = unclaimed;
-        for (int q = 0; q < rank && rest; ++q) rest &= rest - 1;
-        more = (k + OE_SCAN < len) || __popc(rest) > OE_HOLD;
-#pragma unroll
-        for (int c = 0; c < OE_HOLD; ++c) {
-          if (rest) {
-            const int t = __ffs(rest) - 1;
-            rest &= rest - 1;
-            off[c] = t;
-            int v = -1;
-#pragma unroll
-            for (int q = 0; q < OE_SCAN; ++q) if (q == t) v = cv[q];
-            o[c] = v;
-            valid |= 1u << c;
-          }
-        }
+        seen |= group;
+        for (int q = 0; q < a.rows; ++q) if ((group >> q) & 1ull) comp_of[q] = n & 31;
+        ++n;
       }
-      // ---- resolve in registers
-      uint32_t fin_mask = __ballot_sync(0xffffffffu, final);
-      bool done_now = false;
-      int pos = 0;
-      for (;;) {
-        int head = -1, hoff = 0;
-#pragma unroll
-        for (int c = OE_HOLD - 1; c >= 0; --c)
-          if ((valid >> c) & 1u) { head = o[c]; hoff = off[c]; }
-        int key = final ? pick : head;
-        if (key < 0) key = -1 - lane;
-        const uint32_t lower = __match_any_sync(0xffffffffu, key) & lt;
-        const bool in_doubt = !final && head < 0 && more;  // ran out of held candidates, the list may have more
-        const bool conflicted = !final && head >= 0 && lower != 0u;
-        const uint32_t stop = __ballot_sync(0xffffffffu, in_doubt || conflicted);
-        const int first_stop = stop ? __ffs(stop) - 1 : 32;
-        const bool fin_now = !final && !in_doubt && !conflicted && (head < 0 || lane < first_stop);
-        const uint32_t newly = __ballot_sync(0xffffffffu, fin_now);
-        if (fin_now) { final = true; done_now = true; pick = head; pos = k + hoff + 1; }
-        fin_mask |= newly;
-        const bool drop = conflicted && (lower & fin_mask) != 0u;  // the earlier holder is final: that offer is gone
-        if (drop) valid &= valid - 1;
-        if (!(newly | __ballot_sync(0xffffffffu, drop))) break;
-      }
-      if (done_now && pick >= 0) {
-        atomicOr(&used[pick >> 5], 1u << (pick & 31));
-        atomicMax(&cursor[row], pos);  // everything before the winner was claimed, or it would have won
-      } else if (!final && unclaimed == 0u && k + OE_SCAN < len) {
-        atomicMax(&cursor[row], k + OE_SCAN);  // the whole scan is claimed: move on
-      }
-      __syncwarp();
-      open = __ballot_sync(0xffffffffu, !final);
+      n = n > 32 ? 32 : n;
     }
-    if (active) a.dec[j0 + lane].offer_row = pick;
-    placed += __popc(__ballot_sync(0xffffffffu, pick >= 0));
+    n_comp_s = n;
   }
-  if (lane == 0) *a.n_placed = placed;
+  __syncthreads();
+  const int n_comp = n_comp_s;
+  // ---- stable counting sort of the requirements by component (first OE_SORT_THREADS threads)
+  const int64_t chunk = (a.M + OE_SORT_THREADS - 1) / OE_SORT_THREADS;
+  const int64_t j_lo = tid < OE_SORT_THREADS ? min(a.M, (int64_t)tid * chunk) : 0, j_hi = tid < OE_SORT_THREADS ? min(a.M, j_lo + chunk) : 0;
+  if (tid < OE_SORT_THREADS) {
+    for (int c = 0; c < n_comp; ++c) cnt[c][tid] = 0;
+    for (int64_t j = j_lo; j < j_hi; ++j) {
+      const int row = a.req_row[j];
+      ++cnt[a.adj ? comp_of[row] : 0][tid];
+    }
+  }
+  __syncthreads();
+  if (tid < n_comp) {  // exclusive scan over the threads, per component
+    int run = 0;
+    for (int t = 0; t < OE_SORT_THREADS; ++t) { const int v = cnt[tid][t]; cnt[tid][t] = run; run += v; }
+    cnt[tid][OE_SORT_THREADS] = run;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int c = 0; c < n_comp; ++c) { comp_begin[c] = run; run += cnt[c][OE_SORT_THREADS]; }
+    comp_begin[n_comp] = run;
+  }
+  __syncthreads();
+  for (int64_t j = j_lo; j < j_hi; ++j) {
+    const int row = a.req_row[j];
+    const int c = a.adj ? comp_of[row] : 0;
+    a.order[comp_begin[c] + cnt[c][tid]++] = make_int2((int)j, row);
+  }
+  __syncthreads();
+  // ---- replay: warp = component, the 32 lanes test 32 candidates of the row's list per step
+  const int warp = tid >> 5, lane = tid & 31;
+  int placed = 0;
+  const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
+  int2 next = begin < end ? a.order[begin] : make_int2(0, 0);
+  for (int pos = begin; pos < end; ++pos) {
+    const int2 jr = next;
+    if (pos + 1 < end) next = a.order[pos + 1];  // off the dependent chain of this step
+    const RowState st = rs[jr.y];
+    const int32_t* list = a.cand + st.base;
+    int pick = -1;
+    int k = st.cursor;
+    while (k < st.len) {
+      const int idx = k + lane;
+      const int c = idx < st.len ? __ldg(list + idx) : -1;
+      // warps of other components share bitmap words, never bits: the OR must be atomic, the test need not be
+      const bool is_free = c >= 0 && !(reinterpret_cast<volatile uint32_t*>(used)[c >> 5] & (1u << (c & 31)));
+      const uint32_t m = __ballot_sync(0xffffffffu, is_free);
+      if (m) {
+        const int f = __ffs(m) - 1;
+        pick = __shfl_sync(0xffffffffu, c, f);
+        if (lane == f) atomicOr(&used[c >> 5], 1u << (c & 31));
+        k += f + 1;
+        break;
+      }
+      k += 32;
+    }
+    if (lane == 0) {
+      rs[jr.y].cursor = min(k, st.len);  // everything before it is claimed
+      a.dec[jr.x].offer_row = pick;
+    }
+    placed += pick >= 0;
+    __syncwarp();
+  }
+  if (lane == 0 && placed) atomicAdd(&placed_s, placed);
+  __syncthreads();
+  if (tid == 0) *a.n_placed = placed_s;
 }
 
 // K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
@@ -579,7 +573,7 @@ struct oe_engine {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   std::string err;
-  int smem_optin = 0;
+  int smem_optin = 0, commit_static_smem = 0;
 
   // ---- programs (host copies kept for validation, variant detection and launch bookkeeping)
   bool hasP = false, hasT = false, hasO = false, hasR = false;
@@ -623,7 +617,7 @@ struct oe_engine {
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
 
   // ---- derived / outputs
-  DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced;
+  DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj;
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -745,7 +739,16 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
   cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream);
-  cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin);
+  {  // the commit kernel may use all the shared memory left beside its static arrays
+    cudaFuncAttributes fa{};
+    if ((e = cudaFuncGetAttributes(&fa, k_commit)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes)) != cudaSuccess) {
+      g_create_error = std::string("oe_create: shared memory opt-in for the commit kernel: ") + cudaGetErrorString(e);
+      delete h;
+      return OE_ERR_CUDA;
+    }
+    h->commit_static_smem = (int)fa.sharedSizeBytes;
+  }
   *out = h;
   return OE_OK;
 }
@@ -760,7 +763,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
-                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab};
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -1436,7 +1439,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   }
   // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
-  const int64_t cap = h->M + 2 * OE_PROPOSE_WINDOW;
+  const int64_t cap = h->M + 16;
   CU(h->d_tile_cnt.ensure((size_t)rows * tiles * 4));
   CU(h->d_row_base.ensure(((size_t)rows + 1) * 8));
   CU(h->d_row_len.ensure((size_t)rows * 4));
@@ -1458,15 +1461,24 @@ int run_commit(oe_engine* h, int64_t* launches) {
   a.cand = h->d_cand.as<int32_t>(); a.row_base = h->d_row_base.as<int64_t>(); a.row_len = h->d_row_len.as<int32_t>();
   a.rows = rows; a.used_words = rb.total_words; a.req_row = h->d_req_row.as<int32_t>(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
   a.n_placed = h->d_nplaced.as<int>();
-  size_t smem = (size_t)OE_WIN_SLOTS * OE_WIN_ENTRIES * 4 + OE_WIN_SLOTS * 8;
-  const size_t budget = (size_t)h->smem_optin;
-  a.cursor_in_smem = (size_t)rows * 4 <= budget / 4;
-  if (a.cursor_in_smem) smem += (size_t)rows * 4;
-  else { CU(h->d_cursor.ensure((size_t)rows * 4)); a.cursor_g = h->d_cursor.as<int32_t>(); }
+  CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
+  a.order = h->d_order.as<int2>();
+  if (rows <= OE_ADJ_MAX_ROWS && rows > 1) {
+    CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
+    CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, h->stream));
+    k_row_overlap<<<(unsigned)((rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
+    ++*launches;
+    a.adj = h->d_adj.as<unsigned long long>();
+  }
+  const size_t budget = (size_t)h->smem_optin - h->commit_static_smem - 1024;  // static arrays (sort counters) share the pool
+  size_t smem = 0;
+  a.rows_in_smem = (size_t)rows * sizeof(RowState) <= budget / 4;
+  if (a.rows_in_smem) smem += (size_t)rows * sizeof(RowState);
+  else { CU(h->d_cursor.ensure((size_t)rows * sizeof(RowState))); a.rows_g = h->d_cursor.as<RowState>(); }
   a.used_in_smem = smem + (size_t)a.used_words * 4 <= budget;
   if (a.used_in_smem) smem += (size_t)a.used_words * 4;
   else { CU(h->d_used.ensure(std::max<size_t>(a.used_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
-  k_commit<<<1, 256, smem, h->stream>>>(a);
+  k_commit<<<1, OE_COMMIT_THREADS, smem, h->stream>>>(a);
   ++*launches;
   CU(cudaGetLastError());
   k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());

@@ -100,7 +100,7 @@ class Dictionary {
 // Host-side shadow of one OfferEvaluationStage of a class, index-aligned with the class's oe_stage_op list.  It is what
 // the adapter needs to turn the engine's decision for the WINNING offer back into recommendations.
 struct StageInfo {
-  enum Kind { EXECUTOR, PLACEMENT, RESOURCE, PORT, VOLUME, TLS, LAUNCH };
+  enum Kind { EXECUTOR, PLACEMENT, RESOURCE, PORT, VOLUME, TLS, LAUNCH, UNRESERVE, DESTROY };
   Kind kind = EXECUTOR;
   std::string resourceName;             // RESOURCE / PORT / VOLUME
   double value = 0.0;
@@ -112,6 +112,21 @@ struct StageInfo {
   std::string taskSpecName;             // LAUNCH
   bool shouldLaunch = false;            // LAUNCH
   std::string role, preReservedRole, principal;
+  std::string portName;                 // PORT: PortSpec.getPortName()
+  // existing-pod path: the reservation this stage expects to find in the offer (ResourceEvaluationStage.requiredResourceId)
+  std::optional<std::string> resourceId;
+  std::optional<std::string> persistenceId;
+  bool skipIfRunningExecutor = false;   // executor-level resource of a pod whose executor still runs
+  std::string executorId;
+  mesos::Resource orphan;               // UNRESERVE / DESTROY: the resource no spec claims any more
+};
+
+// What OfferEvaluator.getEvaluationPipeline (OfferEvaluator.java:250-310) derives from the state store for a pod that has
+// launched before: its stored tasks and the executor to re-use, if one is still alive.
+struct ExistingPod {
+  std::map<std::string, mesos::TaskInfo> podTasks;  // by task name
+  std::optional<std::string> executorId;            // a task of the pod that is not being relaunched still runs in it
+  mesos::ExecutorInfo executorInfo;
 };
 
 struct EncodedCycle {
@@ -186,6 +201,7 @@ struct EncodedCycle {
 // calling PlacementRule.filter directly) just a rule.
 struct EncoderRequirement {
   const PodInstanceRequirement* requirement = nullptr;
+  std::shared_ptr<const ExistingPod> existing;  // set: getExistingEvaluationPipeline; null: getNewEvaluationPipeline
   RulePtr ruleOnly;          // when set: the class is [PlacementRuleEvaluationStage(ruleOnly)]
   PodInstance podInstance;   // used with ruleOnly
 };
@@ -229,6 +245,11 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     for (auto& r : reqs) {
       const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
       types_.intern(pi.pod->type);
+      if (r.existing) {
+        if (r.existing->executorId) execs_.intern(*r.existing->executorId);
+        for (auto& res : r.existing->executorInfo.resources) if (auto id = ResourceUtils::getResourceId(res)) resids_.intern(*id);
+        for (auto& [n, t] : r.existing->podTasks) for (auto& res : t.resources) if (auto id = ResourceUtils::getResourceId(res)) resids_.intern(*id);
+      }
       if (r.ruleOnly) r.ruleOnly->declare(*this);
       else {
         if (pi.pod->placementRule) (*pi.pod->placementRule)->declare(*this);
@@ -265,6 +286,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
       std::string key;
       if (r.ruleOnly) key = "rule@" + std::to_string((uintptr_t)r.ruleOnly.get());
+      else if (r.existing) key = "existing@" + std::to_string(out_.r_class.size());   // reservations are per pod instance
       else {
         key = "pod@" + std::to_string((uintptr_t)pi.pod.get()) + "|" + std::to_string((int)r.requirement->recoveryType);
         for (auto& t : r.requirement->tasksToLaunch) key += "|" + t;
@@ -273,7 +295,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       int cls;
       if (it != classOf.end()) cls = it->second;
       else {
-        cls = r.ruleOnly ? addRuleOnlyClass(*r.ruleOnly) : addNewPodClass(*r.requirement);
+        cls = r.ruleOnly ? addRuleOnlyClass(*r.ruleOnly) : r.existing ? addExistingPodClass(*r.requirement, *r.existing) : addNewPodClass(*r.requirement);
         classOf[key] = cls;
       }
       out_.r_class.push_back(cls);
@@ -541,6 +563,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
           const int slot = slots_.find(r->preReservedRole);
           if (r->isPort) {
             s.kind = StageInfo::PORT; s.resourceName = "ports"; s.port = r->port; s.hostPort = requireHostPorts(r->networkNames);
+            s.portName = r->portName;
             if (!s.hostPort) stage(s, op(OE_OP_NOP));                                           // PortEvaluationStage.java:145-154
             else if (r->port != 0) {
               if (r->port < 0 || r->port > 65535) throw InvalidRequirementException("port out of range");
@@ -567,6 +590,187 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       stage(s, op(OE_OP_NOP));
     }
     // OfferEvaluationUtils.getRole(podSpec) (OfferEvaluationUtils.java:229-235): role of the first resource spec
+    int podRole = -1;
+    for (auto& ts : pod.tasks) { if (!ts.resourceSet.resources.empty()) { podRole = roles_.find(ts.resourceSet.resources[0].role); break; } }
+    return finishClass(ops, stages, podRole, staticPorts);
+  }
+
+  // ---- getExistingEvaluationPipeline (OfferEvaluator.java:538-728) with ExecutorResourceMapper.java:66-129,
+  // TaskResourceMapper.java:80-194 and ResourceMapperUtils.java:26-72
+  struct SpecRef {  // a ResourceSpec or a VolumeSpec ("disk"), as the mappers' `remainingResourceSpecs` hold them
+    const ResourceSpec* r = nullptr;
+    const VolumeSpec* v = nullptr;
+    const std::string name() const { return v ? std::string("disk") : r->name; }
+  };
+  int slotOfPreviousRole(const mesos::Resource& r) {  // MesosResource.getPreviousRole (MesosResource.java:64-83)
+    const std::string role = r.reservations.size() >= 2 ? r.reservations[r.reservations.size() - 2].role : std::string(ANY_ROLE);
+    const int s = slots_.find(role);
+    if (s < 0) throw InvalidRequirementException("orphaned reservation returns to role '" + role + "', which no table of this cycle carries");
+    return s;
+  }
+  template <class StageFn>
+  void unreserveStage(const mesos::Resource& r, StageFn& stage) {  // UnreserveEvaluationStage.java:24-36 -> MesosResourcePool.free
+    StageInfo s;
+    s.kind = StageInfo::UNRESERVE; s.orphan = r; s.resourceName = r.name;
+    if (ResourceUtils::isAtomic(r) || r.value.type != mesos::Value::SCALAR)
+      throw InvalidRequirementException("returning an orphaned " + r.name + " reservation of this kind to the pool is not supported by the engine (OE_OP_FREE is scalar-only)");
+    stage(s, op(OE_OP_FREE, kinds_.find(r.name), slotOfPreviousRole(r), resids_.find(*ResourceUtils::getResourceId(r)), r.value.scalar));
+  }
+  template <class StageFn>
+  void updateStage(const SpecRef& spec, const mesos::Resource& prior, const std::vector<std::string>& taskNames, const ExistingPod& ex,
+                   const std::map<std::string, int64_t>& priorPorts, StageFn& stage) {
+    StageInfo s;
+    s.taskNames = taskNames;
+    s.resourceId = ResourceUtils::getResourceId(prior);
+    const int resid = resids_.find(*s.resourceId);
+    const bool executorLevel = taskNames.empty();
+    uint8_t flags = 0;
+    uint64_t aux = 0;
+    if (executorLevel && ex.executorId) { s.skipIfRunningExecutor = true; s.executorId = *ex.executorId; flags = OE_OPF_SKIP_IF_RUNNING_EXECUTOR; aux = (uint64_t)execs_.find(*ex.executorId); }
+    if (spec.v) {  // VolumeEvaluationStage.getExisting: the size is the one already reserved (ResourceMapperUtils.java:40-48)
+      s.kind = StageInfo::VOLUME; s.resourceName = "disk"; s.volumeType = spec.v->type; s.containerPath = spec.v->containerPath;
+      s.value = prior.disk ? prior.value.scalar : spec.v->size;
+      s.role = spec.v->role; s.preReservedRole = spec.v->preReservedRole; s.principal = spec.v->principal;
+      if (prior.disk) s.persistenceId = prior.disk->persistence_id;
+      // the running-executor shortcut of volumes additionally needs a persistence id (VolumeEvaluationStage.java:126-154)
+      if (!(s.persistenceId && executorLevel && ex.executorId)) { flags = 0; aux = 0; s.skipIfRunningExecutor = false; }
+      oe_stage_op o = spec.v->type == VolumeSpec::ROOT ? op(OE_OP_SCALAR_RESERVED, kinds_.find("disk"), slots_.find(spec.v->preReservedRole), resid, s.value)
+                                                       : op(OE_OP_MOUNT_RESERVED, 0, 0, resid);
+      o.flags = flags; o.aux = aux;
+      stage(s, o);
+    } else if (spec.r->isPort) {  // PortEvaluationStage with a resource id (PortEvaluationStage.java:75-127)
+      s.kind = StageInfo::PORT; s.resourceName = "ports"; s.hostPort = requireHostPorts(spec.r->networkNames); s.portName = spec.r->portName;
+      s.role = spec.r->role; s.preReservedRole = spec.r->preReservedRole; s.principal = spec.r->principal;
+      int port = spec.r->port;
+      if (port == 0) { auto it = priorPorts.find(spec.r->portName); if (it != priorPorts.end()) port = (int)it->second; }
+      s.port = port;
+      if (!s.hostPort) { stage(s, op(OE_OP_NOP)); return; }
+      stage(s, op(OE_OP_PORT_RESERVED, 0, slots_.find(spec.r->preReservedRole), resid, 0.0, 0, (uint64_t)port));
+    } else {  // ResourceEvaluationStage with a resource id (ResourceEvaluationStage.java:62-122)
+      s.kind = StageInfo::RESOURCE; s.resourceName = spec.r->name; s.value = spec.r->value;
+      s.role = spec.r->role; s.preReservedRole = spec.r->preReservedRole; s.principal = spec.r->principal;
+      oe_stage_op o = op(OE_OP_SCALAR_RESERVED, kinds_.find(spec.r->name), slots_.find(spec.r->preReservedRole), resid, spec.r->value);
+      o.flags = flags; o.aux = aux;
+      stage(s, o);
+    }
+  }
+  template <class StageFn>
+  void createStage(const SpecRef& spec, const std::vector<std::string>& taskNames, const std::map<std::string, int64_t>& priorPorts, StageFn& stage) {
+    if (spec.v) { volumeStage(*spec.v, taskNames, stage); return; }
+    StageInfo s;
+    s.taskNames = taskNames; s.role = spec.r->role; s.preReservedRole = spec.r->preReservedRole; s.principal = spec.r->principal;
+    const int slot = slots_.find(spec.r->preReservedRole);
+    if (spec.r->isPort) {
+      s.kind = StageInfo::PORT; s.resourceName = "ports"; s.port = spec.r->port; s.hostPort = requireHostPorts(spec.r->networkNames); s.portName = spec.r->portName;
+      int port = spec.r->port;
+      if (port == 0) { auto it = priorPorts.find(spec.r->portName); if (it != priorPorts.end()) port = (int)it->second; }  // PortEvaluationStage.java:79-87
+      if (!s.hostPort) stage(s, op(OE_OP_NOP));
+      else if (port != 0) { s.port = port; stage(s, op(OE_OP_PORT_STATIC, 0, slot, port)); }
+      else {
+        int rangeSet = -1;
+        if (!spec.r->ranges.empty()) {
+          for (auto& rg : spec.r->ranges) out_.rs.push_back(OE_PORT_PACK(std::clamp(rg.begin, 0, 65535), std::clamp(rg.end, 0, 65535)));
+          out_.rs_begin.push_back((int32_t)out_.rs.size());
+          rangeSet = (int)out_.rs_begin.size() - 2;
+        }
+        stage(s, op(OE_OP_PORT_DYNAMIC, 0, slot, rangeSet));
+      }
+    } else {
+      s.kind = StageInfo::RESOURCE; s.resourceName = spec.r->name; s.value = spec.r->value;
+      stage(s, op(OE_OP_SCALAR_NEW, kinds_.find(spec.r->name), slot, 0, spec.r->value));
+    }
+  }
+
+  int addExistingPodClass(const PodInstanceRequirement& req, const ExistingPod& ex) {
+    const PodSpec& pod = *req.podInstance.pod;
+    std::vector<oe_stage_op> ops;
+    std::vector<StageInfo> stages;
+    auto stage = [&](StageInfo s, oe_stage_op o) { stages.push_back(std::move(s)); ops.push_back(o); };
+    { StageInfo s; s.kind = StageInfo::EXECUTOR; if (ex.executorId) s.executorId = *ex.executorId;
+      stage(s, op(OE_OP_EXEC_ID, 0, 0, ex.executorId ? execs_.find(*ex.executorId) : -1)); }                     // OfferEvaluator.java:295-304
+    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; stage(s, op(OE_OP_NOP)); }  // :548-554
+    // (a PERMANENT recovery never comes here: it takes the new-pod pipeline, :268-271)
+    std::vector<int> staticPorts;
+    for (auto& ts : pod.tasks) for (auto& rs : ts.resourceSet.resources) if (rs.isPort && rs.port != 0) staticPorts.push_back(rs.port);
+
+    // ---- executor resources (ExecutorResourceMapper.java:66-129): volumes first, then the overhead specs
+    const ResourceSpec* any = nullptr;
+    for (auto& ts : pod.tasks) if (!ts.resourceSet.resources.empty()) { any = &ts.resourceSet.resources[0]; break; }
+    if (!any) throw InvalidRequirementException("pod " + pod.type + " has no resource spec to take role and principal from");
+    std::vector<ResourceSpec> executorSpecs;
+    for (auto& [name, value] : cfg_.getExecutorResources()) executorSpecs.push_back(ResourceSpec::scalar(name, value, any->role, any->preReservedRole, any->principal));
+    {
+      std::vector<SpecRef> remaining;
+      for (auto& v : pod.volumes) { SpecRef s; s.v = &v; remaining.push_back(s); }
+      for (auto& r : executorSpecs) { SpecRef s; s.r = &r; remaining.push_back(s); }
+      std::vector<std::pair<SpecRef, const mesos::Resource*>> matched;
+      std::vector<const mesos::Resource*> orphaned;
+      for (auto& res : ex.executorInfo.resources) {
+        int hit = -1;
+        if (ResourceUtils::getResourceId(res)) {
+          for (size_t k = 0; k < remaining.size() && hit < 0; ++k) {
+            if (res.name == "disk" && res.disk) { if (remaining[k].v && remaining[k].v->containerPath == res.disk->container_path) hit = (int)k; }
+            else if (remaining[k].name() == res.name) hit = (int)k;
+          }
+        }
+        if (hit >= 0) { matched.push_back({remaining[(size_t)hit], &res}); remaining.erase(remaining.begin() + hit); }
+        else if (res.disk) orphaned.push_back(&res);
+      }
+      for (auto* o : orphaned) { StageInfo s; s.kind = StageInfo::DESTROY; s.orphan = *o; stage(s, op(OE_OP_NOP)); }   // DestroyEvaluationStage
+      for (auto* o : orphaned) unreserveStage(*o, stage);
+      for (auto& [spec, res] : matched) updateStage(spec, *res, {}, ex, {}, stage);
+      for (auto& spec : remaining) createStage(spec, {}, {}, stage);
+    }
+
+    // ---- task resources (getExistingTaskEvaluationPipeline, OfferEvaluator.java:598-668)
+    std::map<std::string, const TaskSpec*> byName;
+    for (auto& ts : pod.tasks) if (!byName.emplace(ts.name, &ts).second) throw std::logic_error("Duplicate key " + ts.name);
+    std::set<std::string> updatedResourceSets;
+    for (auto& launchName : req.tasksToLaunch) {
+      auto it = byName.find(launchName);
+      if (it == byName.end()) throw std::logic_error("Unable to find task to launch " + launchName + " among the defined tasks of pod " + pod.type);
+      const ResourceSet& rset = it->second->resourceSet;
+      if (!updatedResourceSets.insert(rset.id).second) continue;
+      std::vector<std::string> namesInSet;  // TreeSet order
+      for (auto& [n2, t2] : byName) if (t2->resourceSet.id == rset.id) namesInSet.push_back(n2);
+      const mesos::TaskInfo* prior = nullptr;
+      for (auto& n2 : namesInSet) {
+        auto pt = ex.podTasks.find(taskInstanceName(req.podInstance, n2));
+        if (pt != ex.podTasks.end()) { prior = &pt->second; break; }
+      }
+      if (prior) {  // TaskResourceMapper.java:80-139; without a stored TaskInfo the reference adds no resource stages at all (:690-697)
+        std::vector<SpecRef> remaining;
+        for (auto& r : rset.resources) { SpecRef s; s.r = &r; remaining.push_back(s); }
+        for (auto& v : rset.volumes) { SpecRef s; s.v = &v; remaining.push_back(s); }
+        std::vector<std::pair<SpecRef, const mesos::Resource*>> matched;
+        std::vector<const mesos::Resource*> orphaned;
+        for (auto& res : prior->resources) {
+          int hit = -1;
+          const bool hasId = ResourceUtils::getResourceId(res).has_value();
+          for (size_t k = 0; k < remaining.size() && hit < 0 && hasId; ++k) {
+            const SpecRef& sp = remaining[k];
+            if (res.name == "disk") { if (sp.v && res.disk && sp.v->containerPath == res.disk->container_path) hit = (int)k; }
+            else if (res.name == "ports") {  // findMatchingPortSpec (:141-194): single-port resources only
+              if (res.value.ranges.size() != 1 || res.value.ranges[0].first != res.value.ranges[0].second || !sp.r || !sp.r->isPort) continue;
+              const int64_t p = res.value.ranges[0].first;
+              if (sp.r->port == 0) { auto pp = prior->discovery_ports.find(sp.r->portName); if (pp != prior->discovery_ports.end() && pp->second == p) hit = (int)k; }
+              else if (sp.r->port == p) hit = (int)k;
+            } else if (sp.name() == res.name) hit = (int)k;
+          }
+          if (hit >= 0) { matched.push_back({remaining[(size_t)hit], &res}); remaining.erase(remaining.begin() + hit); }
+          else orphaned.push_back(&res);
+        }
+        for (auto* o : orphaned) unreserveStage(*o, stage);
+        for (auto& [spec, res] : matched) updateStage(spec, *res, namesInSet, ex, prior->discovery_ports, stage);
+        for (auto& spec : remaining) createStage(spec, namesInSet, prior->discovery_ports, stage);
+      }
+      for (auto& n2 : namesInSet) {
+        StageInfo s;
+        s.kind = StageInfo::LAUNCH; s.taskSpecName = n2;
+        s.shouldLaunch = std::find(req.tasksToLaunch.begin(), req.tasksToLaunch.end(), n2) != req.tasksToLaunch.end();
+        stage(s, op(OE_OP_NOP));
+      }
+    }
     int podRole = -1;
     for (auto& ts : pod.tasks) { if (!ts.resourceSet.resources.empty()) { podRole = roles_.find(ts.resourceSet.resources[0].role); break; } }
     return finishClass(ops, stages, podRole, staticPorts);

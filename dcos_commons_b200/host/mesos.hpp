@@ -77,6 +77,7 @@ struct TaskInfo {
   std::map<std::string, std::string> labels;
   std::vector<Resource> resources;
   ExecutorInfo executor;
+  std::map<std::string, int64_t> discovery_ports;  // discovery.ports: port name -> number (how a dynamic port is remembered)
 };
 
 }  // namespace mesos

@@ -132,9 +132,17 @@ class StateStore {
     for (auto& [n, t] : tasks_) out.push_back(t);
     return out;
   }
-  void clear() { tasks_.clear(); }
+  // S/state/StateStore.java storeStatus / fetchStatus: the TaskState name ("TASK_RUNNING", ...) last reported for a task
+  void storeStatus(const std::string& taskName, const std::string& state) { statuses_[taskName] = state; }
+  std::optional<std::string> fetchStatus(const std::string& taskName) const {
+    auto it = statuses_.find(taskName);
+    if (it == statuses_.end()) return std::nullopt;
+    return it->second;
+  }
+  void clear() { tasks_.clear(); statuses_.clear(); }
  private:
   std::map<std::string, mesos::TaskInfo> tasks_;
+  std::map<std::string, std::string> statuses_;
 };
 
 // Direct counterpart of calling `rule.filter(offer, podInstance, tasks).isPassing()` in the reference's rule tests.
@@ -169,10 +177,12 @@ class OfferEvaluator {
     std::vector<std::vector<OfferRecommendation>> out(requirements.size());
     if (requirements.empty()) return out;
     const std::vector<mesos::TaskInfo> allTasks = stateStore_.fetchTasks();  // OfferEvaluator.java:124 (once per cycle here)
-    for (auto& req : requirements) requireNewPod(req, allTasks);
     CycleEncoder enc(cfg_);
     std::vector<EncoderRequirement> ers(requirements.size());
-    for (size_t j = 0; j < requirements.size(); ++j) ers[j].requirement = &requirements[j];
+    for (size_t j = 0; j < requirements.size(); ++j) {
+      ers[j].requirement = &requirements[j];
+      ers[j].existing = existingPod(requirements[j], allTasks);
+    }
     EncodedCycle c = enc.encode(offers, allTasks, ers);
     Engine e(lib_);
     e.load(c);
@@ -180,26 +190,44 @@ class OfferEvaluator {
     lastDecisions_ = dec;
     for (size_t j = 0; j < requirements.size(); ++j)
       if (dec[j].offer_row >= 0)
-        out[j] = materialise(requirements[j], offers[(size_t)dec[j].offer_row], c.classStages[(size_t)c.r_class[j]], dec[j]);
+        out[j] = materialise(requirements[j], offers[(size_t)dec[j].offer_row], c.classStages[(size_t)c.r_class[j]], dec[j], ers[j].existing.get());
     return out;
   }
   const std::vector<oe_decision>& lastDecisions() const { return lastDecisions_; }
 
  private:
-  // This layer covers the new-pod / permanently-failed pipeline (OfferEvaluator.java:250-310).  A pod whose stored tasks
-  // still hold reservations takes the existing-pod pipeline, which is expressed in the ABI (OE_OP_*_RESERVED, OE_OP_FREE)
-  // but not yet built by this encoder.
-  void requireNewPod(const PodInstanceRequirement& req, const std::vector<mesos::TaskInfo>& allTasks) const {
-    if (req.recoveryType == RecoveryType::PERMANENT) return;
-    for (auto& t : allTasks) {
-      auto ty = t.labels.find(labels::TASK_TYPE);
-      auto ix = t.labels.find(labels::TASK_INDEX);
-      if (ty == t.labels.end() || ix == t.labels.end()) continue;
-      if (ty->second != req.podInstance.pod->type || ix->second != std::to_string(req.podInstance.index)) continue;
-      for (auto& r : t.resources)
-        if (auto id = ResourceUtils::getResourceId(r); id && !id->empty())
-          throw InvalidRequirementException("pod " + req.podInstance.getName() + " has launched tasks with reservations: existing-pod pipeline");
+  static bool isPermanentlyFailed(const mesos::TaskInfo& t) {  // S/scheduler/recovery/FailureUtils.java: label "permanently-failed"
+    auto it = t.labels.find("permanently-failed");
+    return it != t.labels.end() && it->second == "true";
+  }
+  // getEvaluationPipeline's choice (OfferEvaluator.java:250-310): null = new / failed pod, else the existing-pod context.
+  std::shared_ptr<const ExistingPod> existingPod(const PodInstanceRequirement& req, const std::vector<mesos::TaskInfo>& allTasks) const {
+    auto ex = std::make_shared<ExistingPod>();
+    for (auto& ts : req.podInstance.pod->tasks) {  // thisPodTasks (:127-131)
+      const std::string name = taskInstanceName(req.podInstance, ts.name);
+      for (auto& t : allTasks) if (t.name == name) ex->podTasks[name] = t;
     }
+    bool noLaunchedTasksExist = true, allFailed = !ex->podTasks.empty();
+    for (auto& [n, t] : ex->podTasks) {
+      for (auto& r : t.resources) if (auto id = ResourceUtils::getResourceId(r); id && !id->empty()) noLaunchedTasksExist = false;
+      allFailed = allFailed && isPermanentlyFailed(t);
+    }
+    if (req.recoveryType == RecoveryType::PERMANENT || allFailed || noLaunchedTasksExist) return nullptr;
+    // getExecutorInfo (:312-345): a task of the pod that is NOT being relaunched and still runs keeps its executor alive
+    std::set<std::string> launching;
+    for (auto& n : req.tasksToLaunch) launching.insert(taskInstanceName(req.podInstance, n));
+    for (auto& [n, t] : ex->podTasks) {
+      if (launching.count(n) || isPermanentlyFailed(t)) continue;
+      auto st = stateStore_.fetchStatus(n);
+      if (st && (*st == "TASK_STAGING" || *st == "TASK_STARTING" || *st == "TASK_RUNNING")) {
+        ex->executorId = t.executor.executor_id;
+        ex->executorInfo = t.executor;
+        return ex;
+      }
+    }
+    ex->executorInfo = ex->podTasks.begin()->second.executor;
+    ex->executorInfo.executor_id.clear();
+    return ex;
   }
 
   std::string newResourceId() {  // ResourceBuilder.java:318,343 mints UUID.randomUUID(): 36 characters
@@ -224,8 +252,18 @@ class OfferEvaluator {
     return r;
   }
 
+  static const mesos::Resource* reservedInOffer(const mesos::Offer& offer, const std::string& id) {
+    for (auto& r : offer.resources) if (auto rid = ResourceUtils::getResourceId(r); rid && *rid == id) return &r;
+    return nullptr;
+  }
+  mesos::Resource withId(const StageInfo& s, const mesos::Value& v, const std::string& id) {
+    mesos::Resource r = reservedResource(s, v);
+    r.reservations.back().labels[labels::RESOURCE_ID] = id;
+    return r;
+  }
+
   std::vector<OfferRecommendation> materialise(const PodInstanceRequirement& req, const mesos::Offer& offer,
-                                               const std::vector<StageInfo>& stages, const oe_decision& d) {
+                                               const std::vector<StageInfo>& stages, const oe_decision& d, const ExistingPod* existing) {
     std::vector<OfferRecommendation> recs;
     const PodInstance& pi = req.podInstance;
     std::map<std::string, mesos::TaskInfo> taskBuilders;  // PodInfoBuilder: one TaskInfo per task spec
@@ -246,9 +284,43 @@ class OfferEvaluator {
       if (s.taskNames.empty()) executor.resources.push_back(r);
       else for (auto& n : s.taskNames) taskBuilders[n].resources.push_back(r);
     };
+    const bool runningExecutor = existing && existing->executorId &&
+                                 std::find(offer.executor_ids.begin(), offer.executor_ids.end(), *existing->executorId) != offer.executor_ids.end();
+    if (existing && existing->executorId) executor.executor_id = *existing->executorId;
     for (auto& s : stages) {
+      if (s.resourceId && s.kind != StageInfo::UNRESERVE && s.kind != StageInfo::DESTROY) {
+        // ---- a stage that expects an earlier reservation (evaluateSimpleResource with a resource id,
+        // OfferEvaluationUtils.java:105-225; VolumeEvaluationStage.java:126-226)
+        mesos::Value want = s.kind == StageInfo::PORT ? mesos::Value::Ranges({{s.port, s.port}}) : mesos::Value::Scalar(s.value);
+        mesos::Resource r = withId(s, want, *s.resourceId);
+        if (s.kind == StageInfo::VOLUME) {
+          mesos::DiskInfo disk;
+          disk.container_path = s.containerPath; disk.persistence_id = s.persistenceId;
+          if (s.volumeType != VolumeSpec::ROOT) disk.source = mesos::DiskInfo::MOUNT;
+          r.disk = disk;
+        }
+        if (s.kind == StageInfo::PORT && !s.hostPort) { attach(s, r); continue; }
+        if (!(s.skipIfRunningExecutor && runningExecutor)) {
+          const mesos::Resource* have = reservedInOffer(offer, *s.resourceId);
+          if (!have) throw std::logic_error("engine accepted an offer that lacks reservation " + *s.resourceId);
+          if (s.kind == StageInfo::PORT) {
+            const int64_t had = have->value.ranges.empty() ? 0 : have->value.ranges[0].first;
+            if (had != s.port) rec(OfferRecommendation::RESERVE).resource = r;   // the port moved: reserve the new one under the same id
+          } else if (!(s.kind == StageInfo::VOLUME && s.volumeType != VolumeSpec::ROOT)) {
+            const double had = have->value.scalar;
+            if (s.value > had) rec(OfferRecommendation::RESERVE).resource = withId(s, mesos::Value::Scalar(s.value - had), *s.resourceId);
+            else if (s.value < had) rec(OfferRecommendation::UNRESERVE).resource = withId(s, mesos::Value::Scalar(had - s.value), *s.resourceId);
+          }
+          if (s.kind == StageInfo::VOLUME && !s.persistenceId) { r.disk->persistence_id = newResourceId(); rec(OfferRecommendation::CREATE).resource = r; }
+        }
+        if (s.kind == StageInfo::PORT) for (auto& n : s.taskNames) taskBuilders[n].discovery_ports[s.portName] = s.port;
+        attach(s, r);
+        continue;
+      }
       switch (s.kind) {
         case StageInfo::EXECUTOR: case StageInfo::PLACEMENT: case StageInfo::TLS: break;
+        case StageInfo::DESTROY: rec(OfferRecommendation::DESTROY).resource = s.orphan; break;
+        case StageInfo::UNRESERVE: rec(OfferRecommendation::UNRESERVE).resource = s.orphan; break;
         case StageInfo::RESOURCE: {
           mesos::Resource r = reservedResource(s, mesos::Value::Scalar(s.value));
           ++newIds;
@@ -263,6 +335,7 @@ class OfferEvaluator {
           mesos::Resource r = reservedResource(s, mesos::Value::Ranges({{port, port}}));
           ++newIds;
           rec(OfferRecommendation::RESERVE).resource = r;
+          for (auto& n : s.taskNames) taskBuilders[n].discovery_ports[s.portName] = port;
           attach(s, r);
         } break;
         case StageInfo::VOLUME: {
