@@ -406,6 +406,26 @@ class Handle:
         self._check(self.b.fn("evaluate_cycle")(self.h, out_ptr, C.byref(st)))
         return st.as_dict()
 
+    def stage_failures(self, j0=0, j1=None):
+        """[j1 - j0, n_local_offers] uint64 failed-stage masks (oe_stage_failures)."""
+        j1 = self.tables.n_reqs if j1 is None else j1
+        f = self.b.fn("stage_failures")
+        f.argtypes = [_p, C.c_int64, C.c_int64, _p]
+        out = np.zeros((j1 - j0, self._n_local), np.uint64)
+        self._check(f(self.h, j0, j1, out.ctypes.data if out.size else None))
+        return out
+
+    def unexpected_resources(self, keep_bits: np.ndarray, only_unused_offers=True):
+        """Per reserved side-table entry: 1 iff its resource id is not in the keep set (oe_unexpected_resources)."""
+        f = self.b.fn("unexpected_resources")
+        f.argtypes = [_p, _p, C.c_int32, _p, C.POINTER(C.c_int64)]
+        n = 0 if self.tables.reserved_id is None else len(self.tables.reserved_id)
+        out = np.zeros(n, np.uint8)
+        cnt = C.c_int64()
+        keep = np.ascontiguousarray(keep_bits, np.uint32)
+        self._check(f(self.h, keep.ctypes.data if keep.size else None, int(only_unused_offers), out.ctypes.data if n else None, C.byref(cnt)))
+        return out, int(cnt.value)
+
     def apply_launches(self):
         self._check(self.b.fn("apply_launches")(self.h))
 

@@ -309,8 +309,11 @@ __device__ __forceinline__ bool offer_has_exec(const DevOffers& o, int64_t i, in
 
 // Runs the stage program of class `cls` over offer row i.  Returns true iff every stage passes.  With RECORD the
 // choices the host needs to materialise the winner (dynamic ports, MOUNT slots, new reservation count) are written.
+// With `failed` non-null every stage runs, as in the reference (OfferEvaluator.java:165-171: no short-circuit, a failed
+// stage leaves the pool untouched and the later stages still see it), and bit min(stage, 63) is set per failed stage.
 template <bool RECORD>
-__device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& ok, int cls, int var, oe_decision* dec) {
+__device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& ok, int cls, int var, oe_decision* dec,
+                                 uint64_t* failed = nullptr) {
   const DevOffers& o = cx.o;
   PairState ps;
   const int SK = o.S * o.K;
@@ -413,7 +416,11 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
       } break;
       default: pass = false;
     }
-    if (!pass) { all = false; break; }  // failed stages never deduct and the verdict is the AND of all stages
+    if (!pass) {  // failed stages never deduct and the verdict is the AND of all stages
+      all = false;
+      if (!failed) break;
+      *failed |= 1ull << min(x - ob, 63);
+    }
   }
   if (RECORD) dec->n_new_reservations = n_res;
   return all;

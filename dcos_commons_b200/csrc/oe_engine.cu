@@ -511,6 +511,46 @@ __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, in
   dec[j] = d;
 }
 
+// Kdbg: failed-stage mask of every (requirement in [j0, j1), offer) pair — what OfferEvaluator.java:173-214 feeds into the
+// offer-outcome trackers.  thread = offer, blockIdx.y = requirement.
+__global__ void __launch_bounds__(128) k_stage_failures(DevCtx cx, const int32_t* __restrict__ req_row, int64_t j0,
+                                                        unsigned long long* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
+  if (i >= cx.o.N) return;
+  const int64_t j = j0 + blockIdx.y;
+  const int row = req_row[j];
+  const int var = row < cx.p.C ? -1 : row - cx.p.C;
+  const int cls = var < 0 ? row : cx.v.cls[var];
+  OfferKeys ok{cx.o.agent[i], cx.o.host[i], cx.o.zone[i], cx.o.region[i]};
+  uint64_t failed = 0;
+  eval_pair<false>(cx, i, ok, cls, var, nullptr, &failed);
+  out[(int64_t)blockIdx.y * cx.o.N + i] = failed;
+}
+
+// Kgc: reservation garbage scan.  k_mark_taken flags the offers the last cycle accepted; k_unexpected tests every reserved
+// side-table entry of every offer row against the keep set.
+__global__ void k_mark_taken(const oe_decision* __restrict__ dec, int64_t M, int64_t row_offset, int64_t N, uint32_t* __restrict__ taken) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const int64_t i = (int64_t)dec[j].offer_row - row_offset;
+  if (dec[j].offer_row >= 0 && i >= 0 && i < N) atomicOr(taken + (i >> 5), 1u << (i & 31));
+}
+__global__ void k_unexpected(DevOffers o, const uint32_t* __restrict__ keep, const uint32_t* __restrict__ taken,
+                             uint8_t* __restrict__ out, unsigned long long* __restrict__ n_out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int n = 0;
+  if (i < o.N && !(taken && ((taken[i >> 5] >> (i & 31)) & 1u))) {
+    for (int64_t q = o.rbegin[i]; q < o.rbegin[i + 1]; ++q) {
+      const int32_t id = o.rid[q];
+      const bool unexpected = !((keep[id >> 5] >> (id & 31)) & 1u);
+      out[q] = unexpected;
+      n += unexpected;
+    }
+  }
+  for (int d = 16; d > 0; d >>= 1) n += __shfl_xor_sync(0xffffffffu, n, d);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(n_out, (unsigned long long)n);
+}
+
 // K4: multi-cycle replay.  One thread per stored task: copies the winning offer's placement columns into a task row.
 struct LaunchArgs {
   int64_t n;
@@ -604,7 +644,7 @@ struct oe_engine {
 
   // ---- offers
   DevOffers dof{};
-  int64_t N = 0, N_global = 0, row_offset = 0, shard_rows = 0;
+  int64_t N = 0, N_global = 0, row_offset = 0, shard_rows = 0, n_reserved = 0;
   DevBuf d_scalar, d_present, d_port, d_msize, d_mprof, d_ocols[5], d_oattr, d_orr, d_oexec, d_rbegin, d_rid, d_rkind, d_rval;
 
   // ---- requirements
@@ -617,7 +657,7 @@ struct oe_engine {
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
 
   // ---- derived / outputs
-  DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj;
+  DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj, d_dbg, d_keep, d_gc_out, d_taken;
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -763,7 +803,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
-                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj};
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -1044,7 +1084,7 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   o.N = N; o.row_offset = t->row_offset;
   o.S = t->n_role_slots; o.K = t->n_scalar_kinds; o.R = t->n_port_ranges; o.D = t->n_mount_slots;
   o.A = t->n_attr_slots; o.Q = t->n_rr_cols; o.E = t->n_exec_slots;
-  h->N = N; h->row_offset = t->row_offset; h->shard_rows = t->shard_rows;
+  h->N = N; h->row_offset = t->row_offset; h->shard_rows = t->shard_rows; h->n_reserved = t->n_reserved;
   h->N_global = t->n_offers_global > 0 ? t->n_offers_global : N;
   const size_t n = (size_t)N;
   if (int rc = upload(h, h->d_scalar, t->scalar, n * o.S * o.K)) return rc;
@@ -1079,6 +1119,7 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   check_ids(h, o.attr, N * o.A, -1, dc.n_attrs, 15);
   check_ids(h, o.rr, N * o.Q, -1, dc.n_rr_values, 16);
   check_ids(h, o.mprof, N * o.D, -1, OE_MAX_PROFILES, 17);
+  if (t->n_reserved > 0) check_ids(h, o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19);
   if (N > 0 && o.R > 0)
     k_validate_ranges<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(o.port, N, o.S, o.R, 18, h->d_err.as<int>());
   if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
@@ -1594,6 +1635,55 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     stats->n_pairs = h->N_global * h->M;
     stats->kernel_launches = launches;
   }
+  return OE_OK;
+}
+
+int32_t oe_stage_failures(oe_engine* h, int64_t req_begin, int64_t req_end, uint64_t* failed) {
+  if (int rc = ready(h, "oe_stage_failures")) return rc;
+  if (req_begin < 0 || req_end < req_begin || req_end > h->M) return h->fail(OE_ERR_INVALID, "oe_stage_failures: requirement range");
+  if (req_end - req_begin > 65535) return h->fail(OE_ERR_LIMIT, "oe_stage_failures: at most 65535 requirements per call");
+  const int64_t n = (req_end - req_begin) * h->N;
+  if (n == 0) return OE_OK;
+  if (!failed) return h->fail(OE_ERR_INVALID, "oe_stage_failures: null output");
+  int64_t launches = 0;
+  if (!h->counters_fresh) if (int rc = run_counters(h, &launches)) return rc;
+  CU(h->d_dbg.ensure((size_t)n * 8));
+  dim3 grid((unsigned)((h->N + 127) / 128), (unsigned)(req_end - req_begin));
+  k_stage_failures<<<grid, 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), req_begin, h->d_dbg.as<unsigned long long>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(failed, h->d_dbg.p, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return OE_OK;
+}
+
+int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t only_unused_offers, uint8_t* unexpected, int64_t* n_unexpected) {
+  if (int rc = ready(h, "oe_unexpected_resources")) return rc;
+  if (n_unexpected) *n_unexpected = 0;
+  const int64_t n_res = h->n_reserved;
+  if (n_res == 0) return OE_OK;
+  if (!keep_bits || !unexpected) return h->fail(OE_ERR_INVALID, "oe_unexpected_resources: null argument");
+  const size_t keep_words = (size_t)(h->dict.n_res_ids + 31) / 32;
+  CU(h->d_keep.ensure(std::max<size_t>(keep_words, 1) * 4));
+  CU(cudaMemcpyAsync(h->d_keep.p, keep_bits, keep_words * 4, cudaMemcpyHostToDevice, h->stream));
+  const size_t out_bytes = ((size_t)n_res + 7) / 8 * 8;  // the 8-byte counter sits behind the flags
+  CU(h->d_gc_out.ensure(out_bytes + 8));
+  CU(cudaMemsetAsync(h->d_gc_out.p, 0, out_bytes + 8, h->stream));
+  unsigned long long* d_count = reinterpret_cast<unsigned long long*>(h->d_gc_out.as<uint8_t>() + out_bytes);
+  uint32_t* taken = nullptr;
+  if (only_unused_offers && h->cycle_done && h->M > 0) {
+    const size_t words = (size_t)(h->N + 31) / 32;
+    CU(h->d_taken.ensure(std::max<size_t>(words, 1) * 4));
+    CU(cudaMemsetAsync(h->d_taken.p, 0, words * 4, h->stream));
+    k_mark_taken<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_dec.as<oe_decision>(), h->M, h->row_offset, h->N, h->d_taken.as<uint32_t>());
+    taken = h->d_taken.as<uint32_t>();
+  }
+  k_unexpected<<<(unsigned)((h->N + 127) / 128), 128, 0, h->stream>>>(h->dof, h->d_keep.as<uint32_t>(), taken, h->d_gc_out.as<uint8_t>(), d_count);
+  CU(cudaGetLastError());
+  unsigned long long count = 0;
+  CU(cudaMemcpyAsync(unexpected, h->d_gc_out.p, (size_t)n_res, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(&count, d_count, 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (n_unexpected) *n_unexpected = (int64_t)count;
   return OE_OK;
 }
 

@@ -383,6 +383,23 @@ int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats);
  * rank: all ranks compute the same decisions.                                                                      */
 int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats);
 
+/* Why did an offer not fit?  For requirements [req_begin, req_end) and every loaded offer: bit min(s, 63) of
+ * failed[(j - req_begin) * n_offers + i] is set iff stage s of requirement j's pipeline fails on offer i.  All stages are
+ * run, as the reference does (S/offer/evaluate/OfferEvaluator.java:165-171: no short-circuit; a failed stage leaves the pool
+ * untouched and later stages still run), so the masks are what OfferEvaluator.java:173-214 records into the offer-outcome
+ * trackers (S/debug/OfferOutcomeTrackerV2.java:52-120, a ring of the 100 most recent offers).  Mask 0 = the pair is feasible. */
+int32_t oe_stage_failures(oe_engine* h, int64_t req_begin, int64_t req_end, uint64_t* failed);
+
+/* Reservation garbage scan — DefaultScheduler.getUnexpectedResources (S/scheduler/DefaultScheduler.java:483-538): every
+ * reserved resource (an entry of the offer table's reserved side table, i.e. one that carries a resource-id label) whose id
+ * is NOT in the keep set is unexpected and will be unreserved / destroyed by the host.  keep_bits: bit r set iff resource id
+ * r belongs to a stored task that is neither permanently failed nor being decommissioned (:487-499), ceil(n_res_ids / 32)
+ * words.  With only_unused_offers != 0 the entries of offers accepted by the last oe_evaluate_cycle are skipped (the
+ * reference scans `unusedOffers`, S/framework/OfferProcessor.java:451-455).  unexpected[q] (one byte per side-table entry,
+ * in table order) receives 0 / 1; *n_unexpected the number of ones.                                                   */
+int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t only_unused_offers, uint8_t* unexpected,
+                                int64_t* n_unexpected);
+
 /* Multi-cycle replay: store the tasks of every pod placed by the last oe_evaluate_cycle into the device task table
  * (rows with the same task name are overwritten, as StateStore.storeTasks does), so that the next cycle's tallies
  * see them (LaunchEvaluationStage.java:58-68 → PersistentLaunchRecorder.java:74-137).                              */

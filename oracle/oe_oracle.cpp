@@ -544,6 +544,7 @@ void oeo_destroy(Oracle* h) { delete h; }
 const char* oeo_last_error(const Oracle* h) { return h ? h->err.c_str() : ""; }
 
 int32_t oeo_load_programs(Oracle* h, const oe_program_table* t) {
+  h->last_decisions.clear();
   Programs& P = h->P;
   P = Programs();
   P.C = t->n_classes;
@@ -565,6 +566,7 @@ int32_t oeo_load_programs(Oracle* h, const oe_program_table* t) {
 }
 
 int32_t oeo_load_tasks(Oracle* h, const oe_task_table* t) {
+  h->last_decisions.clear();
   Tasks& T = h->T;
   T = Tasks();
   size_t n = (size_t)t->n_tasks;
@@ -588,6 +590,7 @@ int32_t oeo_load_tasks(Oracle* h, const oe_task_table* t) {
 }
 
 int32_t oeo_load_offers(Oracle* h, const oe_offer_table* t) {
+  h->last_decisions.clear();
   Offers& O = h->O;
   O = Offers();
   size_t n = (size_t)t->n_offers;
@@ -619,6 +622,7 @@ int32_t oeo_load_offers(Oracle* h, const oe_offer_table* t) {
 }
 
 int32_t oeo_load_requirements(Oracle* h, const oe_req_table* t) {
+  h->last_decisions.clear();
   Reqs& R = h->R;
   R = Reqs();
   size_t m = (size_t)t->n_reqs;
@@ -736,6 +740,28 @@ int32_t oeo_apply_launches(Oracle* h) {
     }
   }
   return 0;
+}
+
+// DefaultScheduler.getUnexpectedResources (S/scheduler/DefaultScheduler.java:483-538): for every unused offer, every resource
+// with a resource id that is not in the keep set.
+int32_t oeo_unexpected_resources(Oracle* h, const uint32_t* keep_bits, int32_t only_unused_offers, uint8_t* unexpected, int64_t* n_unexpected) {
+  if (int rc = h->check_loaded()) return rc;
+  int64_t count = 0;
+  std::vector<char> taken((size_t)h->O.N, 0);
+  if (only_unused_offers)
+    for (auto& d : h->last_decisions) if (d.offer_row >= 0 && d.offer_row < h->O.N) taken[(size_t)d.offer_row] = 1;
+  for (int64_t i = 0; i < h->O.N; ++i) {
+    for (int64_t q = h->O.reserved_begin.empty() ? 0 : h->O.reserved_begin[i]; !h->O.reserved_begin.empty() && q < h->O.reserved_begin[i + 1]; ++q) {
+      unexpected[q] = 0;
+      if (taken[(size_t)i]) continue;
+      const int32_t id = h->O.reserved_id[q];
+      const bool keep = (keep_bits[id >> 5] >> (id & 31)) & 1u;
+      unexpected[q] = !keep;
+      count += !keep;
+    }
+  }
+  if (n_unexpected) *n_unexpected = count;
+  return OE_OK;
 }
 
 int64_t oeo_task_count(const Oracle* h) { return h->T.T; }

@@ -1,0 +1,257 @@
+// kat_existing.cpp — relaunching a pod that already holds reservations (S/offer/evaluate/OfferEvaluator.java:538-728,
+// TaskResourceMapper, ExecutorResourceMapper, evaluateSimpleResource with a resource id), restated from
+// T/offer/evaluate/OfferEvaluatorTest.java:105-305, OfferEvaluatorPortsTest.java:72-259 and OfferEvaluatorVolumesTest.java.
+#include "kat.hpp"
+
+using namespace sdk;
+using namespace testutils;
+using Rec = OfferRecommendation;
+
+namespace {
+
+struct Fixture {
+  StateStore stateStore;
+  OfferEvaluator evaluator;
+  Fixture() : evaluator(*kat::library(), stateStore, TestConstants::SERVICE_NAME) {}
+  // T/offer/evaluate/OfferEvaluatorTestBase.java:52-94: evaluate, store the TaskInfos, hand back the reserved resources
+  std::vector<mesos::Resource> recordLaunch(const mesos::Offer& offer, const PodInstanceRequirement& req) {
+    auto recs = evaluator.evaluate(req, {offer});
+    std::vector<mesos::Resource> reserved;
+    std::vector<mesos::TaskInfo> store;
+    for (auto& r : recs) {
+      if (r.type == Rec::RESERVE) reserved.push_back(r.resource);
+      if (r.type == Rec::STORE_TASK) store.push_back(*r.task);
+    }
+    stateStore.storeTasks(store);
+    return reserved;
+  }
+  std::vector<mesos::Resource> recordLaunchWithCompleteOfferedResources(const PodInstanceRequirement& req, std::vector<mesos::Resource> offered,
+                                                                        const std::string& preReservedRole = ANY_ROLE) {
+    return recordLaunch(OfferTestUtils::getCompleteOffer(offered, preReservedRole), req);
+  }
+  // getExpectedExecutorResources (OfferEvaluatorTest.java:64-99): the executor's reservations as the agent would re-offer them
+  std::vector<mesos::Resource> expectedExecutorResources() { return stateStore.fetchTasks().front().executor.resources; }
+};
+
+std::string types(const std::vector<Rec>& recs) {
+  std::string s;
+  for (auto& r : recs)
+    s += r.type == Rec::RESERVE ? 'R' : r.type == Rec::UNRESERVE ? 'U' : r.type == Rec::CREATE ? 'C' : r.type == Rec::DESTROY ? 'D'
+       : r.type == Rec::LAUNCH_GROUP ? 'L' : '-';
+  return s;
+}
+std::string resourceId(const mesos::Resource& r) { return ResourceUtils::getResourceId(r).value_or(""); }
+mesos::Resource withValue(mesos::Resource r, double v) { r.value = mesos::Value::Scalar(v); return r; }
+
+}  // namespace
+
+KAT(OfferEvaluatorTest_testRelaunchExpectedScalar) {  // :105-129
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getCpuRequirement(1.0);
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(2.0)});
+  const std::string id = resourceId(reserved[3]);
+  auto expected = f.expectedExecutorResources();
+  expected.push_back(reserved[3]);
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(expected)});
+  assertEquals(2u, recs.size());
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(id, resourceId(recs[0].task->resources[0]));
+}
+KAT(OfferEvaluatorTest_testIncreaseReservationScalar) {  // :131-177
+  Fixture f;
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(PodInstanceRequirementTestUtils::getCpuRequirement(1.0), {ResourceTestUtils::getUnreservedCpus(2.0)});
+  const std::string id = resourceId(reserved[3]);
+  auto expected = f.expectedExecutorResources();
+  expected.push_back(reserved[3]);                            // 1.0 cpus reserved
+  expected.push_back(ResourceTestUtils::getUnreservedCpus(1.0));
+  auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getCpuRequirement(2.0), {OfferTestUtils::getOffer(expected)});
+  assertEquals(std::string("RL-"), types(recs));
+  assertEquals(1.0, recs[0].resource.value.scalar);           // only the difference is reserved, under the same id
+  assertEquals(id, resourceId(recs[0].resource));
+  assertEquals(TestConstants::ROLE, ResourceUtils::getRole(recs[0].resource));
+  assertEquals(id, resourceId(recs[1].task->resources[0]));
+  assertEquals(2.0, recs[1].task->resources[0].value.scalar);
+}
+KAT(OfferEvaluatorTest_testIncreasePreReservedReservationScalar) {  // :190-236
+  Fixture f;
+  const std::string role = "slave_public";
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(PodInstanceRequirementTestUtils::getCpuRequirement(1.0, role),
+                                                             {ResourceTestUtils::getUnreservedCpus(2.0, role)}, role);
+  const std::string id = resourceId(reserved[3]);
+  auto expected = f.expectedExecutorResources();
+  expected.push_back(reserved[3]);
+  expected.push_back(ResourceTestUtils::getUnreservedCpus(1.0, role));
+  auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getCpuRequirement(2.0, role), {OfferTestUtils::getOffer(expected)});
+  assertEquals(std::string("RL-"), types(recs));
+  assertEquals(1.0, recs[0].resource.value.scalar);
+  assertEquals(id, resourceId(recs[0].resource));
+  // ... and the extra cpu must come from the pre-reserved role's pool, not from "*"
+  expected.back() = ResourceTestUtils::getUnreservedCpus(1.0);
+  assertEquals(0u, f.evaluator.evaluate(PodInstanceRequirementTestUtils::getCpuRequirement(2.0, role), {OfferTestUtils::getOffer(expected)}).size());
+}
+KAT(OfferEvaluatorTest_testDecreaseReservationScalar) {  // :238-280
+  Fixture f;
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(PodInstanceRequirementTestUtils::getCpuRequirement(2.0), {ResourceTestUtils::getUnreservedCpus(2.0)});
+  const std::string id = resourceId(reserved[3]);
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);                             // 2.0 cpus reserved
+  offered.push_back(ResourceTestUtils::getUnreservedCpus(1.0));
+  auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getCpuRequirement(1.0), {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("UL-"), types(recs));
+  assertEquals(1.0, recs[0].resource.value.scalar);
+  assertEquals(id, resourceId(recs[0].resource));
+  assertEquals(id, resourceId(recs[1].task->resources[0]));
+  assertEquals(1.0, recs[1].task->resources[0].value.scalar);
+}
+KAT(OfferEvaluatorTest_testFailIncreaseReservationScalar) {  // :292-305
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getCpuRequirement(2.0);
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(2.0)});
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getCompleteOffer(withValue(reserved[3], 1.0))});
+  assertEquals(0u, recs.size());
+  // the same with the executor's reservations offered back and nothing unreserved to grow into
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(withValue(reserved[3], 1.0));
+  assertEquals(0u, f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)}).size());
+  offered.push_back(ResourceTestUtils::getUnreservedCpus(0.5));
+  assertEquals(0u, f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)}).size());
+  offered.back() = ResourceTestUtils::getUnreservedCpus(1.0);
+  assertEquals(std::string("RL-"), types(f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)})));
+}
+// an offer that lacks one of the pod's reservations is refused ("Offer lacks previously reserved ...", OfferEvaluationUtils.java:90-99),
+// and the first offer that carries them all wins
+KAT(OfferEvaluator_relaunchNeedsEveryReservation) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getCpuRequirement(1.0);
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(2.0)});
+  auto all = f.expectedExecutorResources();
+  all.push_back(reserved[3]);
+  auto missingExecutorMem = all;
+  missingExecutorMem.erase(missingExecutorMem.begin() + 2);
+  mesos::Offer a = OfferTestUtils::getCompleteOffer(ResourceTestUtils::getUnreservedCpus(8.0));  // plenty of room, but not OUR reservations
+  a.id = "fresh";
+  mesos::Offer b = OfferTestUtils::getOffer(missingExecutorMem);
+  b.id = "partial";
+  mesos::Offer c = OfferTestUtils::getOffer(all);
+  c.id = "home";
+  auto recs = f.evaluator.evaluate(req, {a, b, c});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(std::string("home"), recs[0].offerId);
+}
+// OfferEvaluatorPortsTest.java:72-118 (testLaunchExpectedStaticPort) and :120-165 (testLaunchExpectedDynamicPort)
+KAT(OfferEvaluatorPortsTest_testLaunchExpectedStaticPort) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getPortRequirement({555});
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedPorts(555, 555)});
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(resourceId(reserved[3]), resourceId(recs[0].task->resources[0]));
+  assertEquals((int64_t)555, recs[0].task->resources[0].value.ranges[0].first);
+}
+KAT(OfferEvaluatorPortsTest_testLaunchExpectedDynamicPort) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getPortRequirement({0});
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedPorts(10000, 10000)});
+  assertEquals((int64_t)10000, reserved[3].value.ranges[0].first);
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)});     // the port chosen last time is kept
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals((int64_t)10000, recs[0].task->resources[0].value.ranges[0].first);
+  assertEquals(resourceId(reserved[3]), resourceId(recs[0].task->resources[0]));
+}
+// OfferEvaluatorPortsTest.java:167-213 (testUpdateStaticToStaticPort): the old port's reservation is orphaned (UNRESERVE would
+// return ports to the pool, which this engine build does not express) — covered instead: static port unchanged while cpus are added
+KAT(OfferEvaluator_addResourceToExistingPod) {
+  Fixture f;
+  auto req1 = PodInstanceRequirementTestUtils::getPortRequirement({555});
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req1, {ResourceTestUtils::getUnreservedPorts(555, 555)});
+  auto b = PodInstanceRequirementTestUtils::builder();
+  b.port("test-port-555", 555).cpus(1.0);
+  auto req2 = PodInstanceRequirementTestUtils::getRequirement(b.build(), 0);
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);
+  assertEquals(0u, f.evaluator.evaluate(req2, {OfferTestUtils::getOffer(offered)}).size());  // no cpus to be had
+  offered.push_back(ResourceTestUtils::getUnreservedCpus(1.5));
+  auto recs = f.evaluator.evaluate(req2, {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("RL-"), types(recs));    // matched port: nothing to do; missing cpus spec: new reservation
+  assertEquals(std::string("cpus"), recs[0].resource.name);
+  assertFalse(resourceId(recs[0].resource) == resourceId(reserved[3]));
+}
+// OfferEvaluatorVolumesTest.java:95-182 (testExpectedRootVolume) and :244-300 (testExpectedMountVolume)
+KAT(OfferEvaluatorVolumesTest_testExpectedRootVolume) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getRootVolumeRequirement(1.0, 1500);
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(1.0), ResourceTestUtils::getUnreservedDisk(2000)});
+  assertEquals(5u, reserved.size());
+  auto stored = f.stateStore.fetchTasks().front();
+  auto offered = f.expectedExecutorResources();
+  for (auto& r : stored.resources) offered.push_back(r);   // cpus + the created volume, as the agent re-offers them
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(*stored.resources[1].disk->persistence_id, *recs[0].task->resources[1].disk->persistence_id);
+  assertEquals(resourceId(stored.resources[1]), resourceId(recs[0].task->resources[1]));
+}
+KAT(OfferEvaluatorVolumesTest_testExpectedMountVolume) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getMountVolumeRequirement(1.0, 1500);
+  f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(1.0), ResourceTestUtils::getUnreservedMountVolume(2000)});
+  auto stored = f.stateStore.fetchTasks().front();
+  auto offered = f.expectedExecutorResources();
+  for (auto& r : stored.resources) offered.push_back(r);
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(2000.0, recs[0].task->resources[1].value.scalar);
+  // without the volume's reservation in the offer the pod cannot come back there
+  offered.pop_back();
+  offered.push_back(ResourceTestUtils::getUnreservedMountVolume(2000));
+  assertEquals(0u, f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)}).size());
+}
+// OfferEvaluator.java:268-293: a permanently failed pod (or `pod replace`) starts over with the new-pod pipeline
+KAT(OfferEvaluator_permanentRecoveryUsesTheNewPodPipeline) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getCpuRequirement(1.0);
+  f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(2.0)});
+  auto fresh = OfferTestUtils::getCompleteOffer(ResourceTestUtils::getUnreservedCpus(2.0));
+  assertEquals(0u, f.evaluator.evaluate(req, {fresh}).size());     // existing pod: wants its reservations back
+  auto replace = req;
+  replace.recoveryType = RecoveryType::PERMANENT;
+  assertEquals(std::string("RRRRL-"), types(f.evaluator.evaluate(replace, {fresh})));
+  auto failed = f.stateStore.fetchTasks();
+  for (auto& t : failed) t.labels["permanently-failed"] = "true";   // FailureUtils.setPermanentlyFailed
+  f.stateStore.storeTasks(failed);
+  assertEquals(std::string("RRRRL-"), types(f.evaluator.evaluate(req, {fresh})));
+}
+// ExecutorEvaluationStage.java:32-81 + ResourceEvaluationStage.java:65-84: a second task of a pod whose executor still runs must
+// land on the agent that lists that executor id, and the executor's own reservations are not looked for in the offer
+KAT(ExecutorEvaluationStage_runningExecutorIsReused) {
+  Fixture f;
+  auto pod = std::make_shared<PodSpec>();
+  pod->type = TestConstants::POD_TYPE;
+  for (const char* name : {"a", "b"}) {
+    TaskSpec t;
+    t.name = name;
+    t.resourceSet = ResourceSetBuilder(TestConstants::ROLE, ANY_ROLE, TestConstants::PRINCIPAL).id(std::string("rs-") + name).cpus(1.0).build();
+    pod->tasks.push_back(t);
+  }
+  PodInstance pi{pod, 0};
+  auto both = PodInstanceRequirement::newBuilder(pi, {"a", "b"});
+  f.recordLaunch(OfferTestUtils::getCompleteOffer({ResourceTestUtils::getUnreservedCpus(4.0)}), both);
+  auto tasks = f.stateStore.fetchTasks();
+  assertEquals(2u, tasks.size());
+  for (auto& t : tasks) { t.executor.executor_id = "executor-1"; }
+  f.stateStore.storeTasks(tasks);
+  f.stateStore.storeStatus(tasks[0].name, "TASK_RUNNING");   // task a keeps running, task b is relaunched
+  auto relaunchB = PodInstanceRequirement::newBuilder(pi, {"b"});
+  mesos::Offer wrongAgent = OfferTestUtils::getOffer(tasks[1].resources);      // b's reservation, but the executor is not there
+  wrongAgent.id = "wrong";
+  mesos::Offer home = wrongAgent;
+  home.id = "home";
+  home.executor_ids = {"executor-1"};
+  auto recs = f.evaluator.evaluate(relaunchB, {wrongAgent, home});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(std::string("home"), recs[0].offerId);
+  assertEquals(std::string("executor-1"), recs[0].task->executor.executor_id);
+}

@@ -98,6 +98,40 @@ def test_unsorted_port_ranges_are_rejected(engine):
             engine.load(t)
 
 
+@pytest.mark.parametrize("seed", range(40))
+def test_failed_stage_masks(engine, seed):
+    """Per-stage outcomes (every stage runs, failed stages do not deduct) against the oracle's literal pipeline."""
+    t = random_tables(seed)
+    orc = Oracle().load(t)
+    engine.load(t)
+    want, bits = orc.stage_failures()
+    got = engine.stage_failures()
+    assert np.array_equal(got, want)
+    assert np.array_equal(got == 0, unpack_bits(bits, t.n_offers))
+    if t.n_reqs > 2:
+        assert np.array_equal(engine.stage_failures(1, t.n_reqs - 1), want[1:-1])
+    orc.close()
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_unexpected_resource_scan(engine, seed):
+    """DefaultScheduler.getUnexpectedResources: reservations whose id is not in the keep set, on offers the cycle left unused."""
+    t = random_tables(seed, n_offers=150 + seed)
+    rng = np.random.default_rng(seed)
+    keep = rng.integers(0, 2 ** 32, (t.dict_sizes["n_res_ids"] + 31) // 32, dtype=np.uint64).astype(np.uint32)
+    orc = Oracle().load(t)
+    engine.load(t)
+    for unused_only in (False, True):
+        assert engine.unexpected_resources(keep, unused_only)[0].tolist() == orc.unexpected_resources(keep, unused_only)[0].tolist()
+    orc.evaluate_cycle()
+    engine.evaluate_cycle()
+    for unused_only in (False, True):
+        got, n_got = engine.unexpected_resources(keep, unused_only)
+        want, n_want = orc.unexpected_resources(keep, unused_only)
+        assert got.tolist() == want.tolist() and n_got == n_want == int(want.sum())
+    orc.close()
+
+
 def test_empty_inputs(engine):
     t = random_tables(5, n_offers=40, n_reqs=6, n_tasks=0)
     _compare_all(engine, t)
