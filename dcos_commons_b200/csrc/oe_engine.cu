@@ -828,7 +828,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
   const int C = t->n_classes;
   if (C < 0 || C > OE_MAX_CLASSES) return h->fail(OE_ERR_LIMIT, "n_classes %d exceeds OE_MAX_CLASSES", C);
-  if (!t->op_begin || (t->n_ops && !t->ops) || !t->pod_role || !t->port_excl_begin)
+  if (!t->op_begin || (t->n_ops && !t->ops) || (C > 0 && !t->pod_role) || !t->port_excl_begin)
     return h->fail(OE_ERR_INVALID, "oe_load_programs: missing column");
   const oe_dict_sizes& d = t->dict;
   if (d.n_agents < 0 || d.n_hostnames < 0 || d.n_zones < 0 || d.n_regions < 0 || d.n_attrs < 0 || d.n_rr_values < 0 ||
@@ -1446,8 +1446,9 @@ int run_expand(oe_engine* h, int64_t* launches) {
   CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
   if (h->M > 0) {
     const unsigned xblocks = (unsigned)((stride / 4 + OE_KX_LANES - 1) / OE_KX_LANES);
-    // ~32 CTAs per SM overall; each CTA streams a [reqs_per_block x 1 KiB] slab
-    int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 15) / 16, (148 * 32 + xblocks - 1) / xblocks));
+    // ~64 CTAs per SM overall (profiles/r01e_bw_probe.txt: 6.75 TB/s vs 6.50 at 32); each CTA streams a
+    // [reqs_per_block x 1 KiB] slab
+    int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 15) / 16, (148 * 64 + xblocks - 1) / xblocks));
     const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);

@@ -329,6 +329,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   }
 
   const Dictionary& hostnames() const { return hosts_; }
+  const Dictionary& resourceIds() const { return resids_; }
 
  private:
   static std::optional<std::string> label(const mesos::TaskInfo& t, const char* key) {

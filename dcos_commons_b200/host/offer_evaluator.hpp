@@ -43,6 +43,7 @@ class EngineLibrary {
   int32_t (*feasibility)(oe_engine*, uint32_t*, oe_stats*) = nullptr;
   int32_t (*evaluate_cycle)(oe_engine*, oe_decision*, oe_stats*) = nullptr;
   int32_t (*apply_launches)(oe_engine*) = nullptr;
+  int32_t (*unexpected_resources)(oe_engine*, const uint32_t*, int32_t, uint8_t*, int64_t*) = nullptr;
   std::string path;
 
  private:
@@ -61,6 +62,7 @@ class EngineLibrary {
     matrix_stride_words = (decltype(matrix_stride_words))sym("matrix_stride_words");
     feasibility = (decltype(feasibility))sym("feasibility"); evaluate_cycle = (decltype(evaluate_cycle))sym("evaluate_cycle");
     apply_launches = (decltype(apply_launches))sym("apply_launches");
+    unexpected_resources = (decltype(unexpected_resources))sym("unexpected_resources");
   }
 };
 
@@ -90,6 +92,14 @@ class Engine {
     check(lib_.evaluate_cycle(h_, d.data(), &st), "oe_evaluate_cycle");
     d.resize((size_t)M_);
     return d;
+  }
+  // flags per reserved side-table entry (offers in order, their id-carrying resources in order)
+  std::vector<uint8_t> unexpectedResources(const std::vector<uint32_t>& keepBits, size_t nReserved, bool onlyUnusedOffers) {
+    std::vector<uint8_t> out(std::max<size_t>(nReserved, 1));
+    int64_t n = 0;
+    check(lib_.unexpected_resources(h_, keepBits.data(), onlyUnusedOffers ? 1 : 0, out.data(), &n), "oe_unexpected_resources");
+    out.resize(nReserved);
+    return out;
   }
   // feasibility bit of (requirement j, offer i)
   std::vector<std::vector<bool>> feasibility() {
@@ -139,10 +149,16 @@ class StateStore {
     if (it == statuses_.end()) return std::nullopt;
     return it->second;
   }
-  void clear() { tasks_.clear(); statuses_.clear(); }
+  // S/state/StateStore.java storeGoalOverrideStatus / fetchGoalOverrideStatus (the decommission plan sets "DECOMMISSIONING")
+  void storeGoalOverrideStatus(const std::string& taskName, const std::string& status) { overrides_[taskName] = status; }
+  std::string fetchGoalOverrideStatus(const std::string& taskName) const {
+    auto it = overrides_.find(taskName);
+    return it == overrides_.end() ? std::string("NONE") : it->second;
+  }
+  void clear() { tasks_.clear(); statuses_.clear(); overrides_.clear(); }
  private:
   std::map<std::string, mesos::TaskInfo> tasks_;
-  std::map<std::string, std::string> statuses_;
+  std::map<std::string, std::string> statuses_, overrides_;
 };
 
 // Direct counterpart of calling `rule.filter(offer, podInstance, tasks).isPassing()` in the reference's rule tests.
@@ -385,6 +401,50 @@ class OfferEvaluator {
   SchedulerConfig cfg_;
   std::mt19937_64 rng_{20240607};
   std::vector<oe_decision> lastDecisions_;
+};
+
+// S/scheduler/DefaultScheduler.java:483-538 getUnexpectedResources: reservations found in the unused offers that no stored
+// task (that is neither permanently failed nor being decommissioned) still claims.  The keep set is built on the host, the
+// scan over every reserved resource of every unused offer runs on the engine.
+struct OfferResources {  // S/offer/OfferResources.java
+  mesos::Offer offer;
+  std::vector<mesos::Resource> resources;
+};
+class UnexpectedResourceScanner {
+ public:
+  UnexpectedResourceScanner(const EngineLibrary& lib, StateStore& stateStore) : lib_(lib), stateStore_(stateStore) {}
+  std::vector<OfferResources> getUnexpectedResources(const std::vector<mesos::Offer>& unusedOffers) {
+    std::vector<OfferResources> out;
+    if (unusedOffers.empty()) return out;
+    std::set<std::string> resourceIdsToKeep;  // :487-499
+    for (auto& t : stateStore_.fetchTasks()) {
+      auto failed = t.labels.find("permanently-failed");
+      if (failed != t.labels.end() && failed->second == "true") continue;
+      if (stateStore_.fetchGoalOverrideStatus(t.name) == "DECOMMISSIONING") continue;
+      for (auto& r : t.resources) if (auto id = ResourceUtils::getResourceId(r)) resourceIdsToKeep.insert(*id);
+      for (auto& r : t.executor.resources) if (auto id = ResourceUtils::getResourceId(r)) resourceIdsToKeep.insert(*id);  // getAllResources
+    }
+    CycleEncoder enc;
+    EncodedCycle c = enc.encode(unusedOffers, {}, {});
+    const Dictionary& ids = enc.resourceIds();
+    std::vector<uint32_t> keep((size_t)std::max(1, (ids.size() + 31) / 32), 0u);
+    for (int v = 0; v < ids.size(); ++v)
+      if (resourceIdsToKeep.count(ids.values()[(size_t)v])) keep[(size_t)v >> 5] |= 1u << (v & 31);
+    Engine e(lib_);
+    e.load(c);
+    const std::vector<uint8_t> flags = e.unexpectedResources(keep, c.o_rid.size(), false);
+    size_t q = 0;
+    for (auto& offer : unusedOffers) {  // side-table order: offers in order, their id-carrying resources in order
+      OfferResources found{offer, {}};
+      for (auto& r : offer.resources)
+        if (ResourceUtils::getResourceId(r) && flags[q++]) found.resources.push_back(r);
+      if (!found.resources.empty()) out.push_back(found);
+    }
+    return out;
+  }
+ private:
+  const EngineLibrary& lib_;
+  StateStore& stateStore_;
 };
 
 // S/scheduler/plan/Step.java reduced to what PlanScheduler reads.

@@ -255,3 +255,56 @@ KAT(ExecutorEvaluationStage_runningExecutorIsReused) {
   assertEquals(std::string("home"), recs[0].offerId);
   assertEquals(std::string("executor-1"), recs[0].task->executor.executor_id);
 }
+
+// ---- S/scheduler/DefaultScheduler.java:483-538, T/scheduler/DefaultSchedulerTest.java:697-752
+namespace {
+struct Installed : Fixture {
+  mesos::TaskInfo task;
+  Installed() {
+    auto req = PodInstanceRequirementTestUtils::getRootVolumeRequirement(1.0, 1500);
+    recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(1.0), ResourceTestUtils::getUnreservedDisk(2000)});
+    task = stateStore.fetchTasks().front();
+  }
+  std::vector<OfferResources> scan(const std::vector<mesos::Offer>& offers) { return UnexpectedResourceScanner(*kat::library(), stateStore).getUnexpectedResources(offers); }
+};
+}  // namespace
+KAT(DefaultSchedulerTest_testUnexpectedPermanentlyFailedResources) {
+  Installed f;
+  assertFalse(f.task.resources.empty());
+  std::vector<mesos::Offer> offers = {OfferTestUtils::getOffer(f.task.resources)};
+  assertTrue(f.scan(offers).empty());                       // currently expected
+  f.task.labels["permanently-failed"] = "true";
+  f.stateStore.storeTasks({f.task});
+  auto found = f.scan(offers);
+  assertEquals(1u, found.size());
+  assertEquals(f.task.resources.size(), found[0].resources.size());
+  for (size_t k = 0; k < f.task.resources.size(); ++k) assertEquals(resourceId(f.task.resources[k]), resourceId(found[0].resources[k]));
+}
+KAT(DefaultSchedulerTest_testUnexpectedDecommissioningResources) {
+  Installed f;
+  std::vector<mesos::Offer> offers = {OfferTestUtils::getOffer(f.task.resources)};
+  assertTrue(f.scan(offers).empty());
+  f.stateStore.storeGoalOverrideStatus(f.task.name, "DECOMMISSIONING");
+  auto found = f.scan(offers);
+  assertEquals(1u, found.size());
+  assertEquals(f.task.resources.size(), found[0].resources.size());
+}
+KAT(DefaultScheduler_unexpectedResourcesAcrossManyOffers) {
+  Installed f;
+  mesos::Resource stray = ResourceTestUtils::getUnreservedCpus(0.5);
+  mesos::ReservationInfo dyn;
+  dyn.role = TestConstants::ROLE; dyn.labels[labels::RESOURCE_ID] = "left-behind-by-an-old-task";
+  stray.reservations.push_back(dyn);
+  std::vector<mesos::Offer> offers;
+  offers.push_back(OfferTestUtils::getCompleteOffer(ResourceTestUtils::getUnreservedCpus(4.0)));  // nothing reserved: not listed
+  offers.push_back(OfferTestUtils::getOffer({f.task.resources[0], stray, ResourceTestUtils::getUnreservedMem(64)}));
+  offers.push_back(OfferTestUtils::getOffer(f.task.executor.resources));                            // executor resources are kept too
+  offers.push_back(OfferTestUtils::getOffer({stray}));
+  for (size_t k = 0; k < offers.size(); ++k) offers[k].id = "offer-" + std::to_string(k);
+  auto found = f.scan(offers);
+  assertEquals(2u, found.size());
+  assertEquals(std::string("offer-1"), found[0].offer.id);
+  assertEquals(1u, found[0].resources.size());
+  assertEquals(std::string("left-behind-by-an-old-task"), resourceId(found[0].resources[0]));
+  assertEquals(std::string("offer-3"), found[1].offer.id);
+}

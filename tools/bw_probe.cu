@@ -23,6 +23,39 @@ __global__ void k_fill(uint4* out, size_t n4) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) __stcs(out + i, v);
 }
 
+template <int MODE>
+__device__ __forceinline__ void store_mode(uint4* p, const uint4 v) {
+  if (MODE == 0) *p = v;
+  else if (MODE == 1) __stcs(p, v);
+  else if (MODE == 2) __stcg(p, v);
+  else __stwt(p, v);
+}
+template <int MODE>
+__global__ void k_fill_mode(uint4* out, size_t n4) {
+  const uint4 v = make_uint4(1, 2, 3, 4);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) store_mode<MODE>(out + i, v);
+}
+// block-contiguous variant: each CTA owns a contiguous chunk
+template <int MODE>
+__global__ void k_fill_chunk(uint4* out, size_t n4) {
+  const uint4 v = make_uint4(1, 2, 3, 4);
+  const size_t per = (n4 + gridDim.x - 1) / gridDim.x;
+  const size_t b = (size_t)blockIdx.x * per, e = b + per < n4 ? b + per : n4;
+  for (size_t i = b + threadIdx.x; i < e; i += blockDim.x) store_mode<MODE>(out + i, v);
+}
+template <int MODE>
+__global__ void k_expand_mode(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row, uint32_t* __restrict__ out, int64_t stride,
+                              int64_t M, int rows_per_block) {
+  const int64_t w4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (w4 >= stride) return;
+  const int64_t j0 = (int64_t)blockIdx.y * rows_per_block;
+  const int64_t j1 = min(M, j0 + rows_per_block);
+  for (int64_t j = j0 + threadIdx.y; j < j1; j += blockDim.y) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(F + (int64_t)__ldg(req_row + j) * stride + w4));
+    store_mode<MODE>(reinterpret_cast<uint4*>(out + j * stride + w4), a);
+  }
+}
+
 // slab of `lanes` uint4 per row (lanes * 16 bytes), blockDim = (lanes, rows_in_flight)
 __global__ void k_expand(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row, uint32_t* __restrict__ out, int64_t stride,
                          int64_t M, int rows_per_block) {
@@ -101,7 +134,29 @@ int main(int argc, char** argv) {
   report("memset", 0, time_ms([&] { cudaMemsetAsync(out, 0, bytes); }));
   for (int mult : {4, 8, 16}) report("fill", mult, time_ms([&] { k_fill<<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
 
-  for (int W : {128, 256, 512, 1024, 4096}) {
+  for (int mult : {8, 32}) {
+    report("fill/st", mult, time_ms([&] { k_fill_mode<0><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+    report("fill/cs", mult, time_ms([&] { k_fill_mode<1><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+    report("fill/cg", mult, time_ms([&] { k_fill_mode<2><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+    report("fill/wt", mult, time_ms([&] { k_fill_mode<3><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+    report("chunk/st", mult, time_ms([&] { k_fill_chunk<0><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+    report("chunk/cs", mult, time_ms([&] { k_fill_chunk<1><<<148 * mult, 256>>>((uint4*)out, bytes / 16); }));
+  }
+  {
+    const int W = 1024, lanes = 64;
+    dim3 block(lanes, 4);
+    const unsigned xb = (unsigned)((stride * 4 + W - 1) / W);
+    for (int target : {148 * 32, 148 * 64}) {
+      int64_t yb = std::max<int64_t>(1, (target + xb - 1) / xb);
+      int rpb = (int)((M + yb - 1) / yb);
+      yb = (M + rpb - 1) / rpb;
+      report("expand/st", target / 148, time_ms([&] { k_expand_mode<0><<<dim3(xb, (unsigned)yb), block>>>(F, req, out, stride, M, rpb); }));
+      report("expand/cs", target / 148, time_ms([&] { k_expand_mode<1><<<dim3(xb, (unsigned)yb), block>>>(F, req, out, stride, M, rpb); }));
+      report("expand/cg", target / 148, time_ms([&] { k_expand_mode<2><<<dim3(xb, (unsigned)yb), block>>>(F, req, out, stride, M, rpb); }));
+      report("expand/wt", target / 148, time_ms([&] { k_expand_mode<3><<<dim3(xb, (unsigned)yb), block>>>(F, req, out, stride, M, rpb); }));
+    }
+  }
+  for (int W : {1024}) {
     const int lanes = W / 16;
     dim3 block(lanes, 256 / lanes);
     const unsigned xb = (unsigned)((stride * 4 + W - 1) / W);
@@ -114,7 +169,7 @@ int main(int argc, char** argv) {
     }
   }
   CK(cudaFuncSetAttribute(k_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  for (int W : {128, 256, 512, 1024, 2048, 4096}) {
+  for (int W : {512}) {
     const int slab_words = W / 4;
     if (stride % slab_words) continue;
     const unsigned xb = (unsigned)(stride / slab_words);
