@@ -236,6 +236,7 @@ __device__ inline bool eval_rule(const DevCtx& cx, const oe_rule_node* nodes, in
 }
 
 #define OE_DEV_MAX_TAKEN 24  // host ports a single pipeline can take (static + dynamic); checked at load
+#define OE_DEV_MAX_FREED 4   // ports / MOUNT disks one pipeline returns to the pool (OE_OP_FREE); checked at load
 
 // Mutable view of one offer's pool while one class's pipeline runs over it.
 struct PairState {
@@ -246,6 +247,13 @@ struct PairState {
   // pool; entries with it are re-used reservations that never were in the pool.
   uint32_t taken[OE_DEV_MAX_TAKEN];
   int n_taken;
+  // orphaned reservations handed back by OE_OP_FREE (MesosResourcePool.free, :374-430): ports as slot << 16 | port, MOUNT
+  // disks appended behind the offer's own (reported as slot OE_MAX_MOUNT_SLOTS + k)
+  uint32_t freed_port[OE_DEV_MAX_FREED];
+  double freed_mount_size[OE_DEV_MAX_FREED];
+  int32_t freed_mount_prof[OE_DEV_MAX_FREED];
+  int n_freed_ports, n_freed_mounts;
+  uint32_t freed_mounts_used;
 };
 #define OE_KEPT 0x10000u
 
@@ -256,6 +264,12 @@ __device__ __forceinline__ bool port_in_pool(const DevOffers& o, int64_t i, int 
     if (b <= p && p <= e) return true;
   }
   return false;
+}
+
+__device__ __forceinline__ bool port_freed(const PairState& ps, int slot, int p) {
+  bool f = false;
+  for (int q = 0; q < ps.n_freed_ports; ++q) f = f || ps.freed_port[q] == (((uint32_t)slot << 16) | (uint32_t)p);
+  return f;
 }
 
 // removed from the pool by an earlier stage
@@ -273,7 +287,18 @@ __device__ __forceinline__ bool port_placed(const PairState& ps, int p) {
 
 // Lowest port of the slot's ranges that is neither taken by an earlier stage of this pipeline, nor declared
 // statically anywhere in the pod, and (when constrained) lies inside the range set.  -1 = none.
-__device__ inline int pick_dynamic_port(const DevCtx& cx, int64_t i, int cls, int slot, int nr, int32_t rset, const PairState& ps) {
+__device__ inline bool dynamic_port_ok(const DevCtx& cx, int cls, int32_t rset, const PairState& ps, int p) {
+  if (port_placed(ps, p)) return false;
+  for (int q = cx.p.excl_begin[cls]; q < cx.p.excl_begin[cls + 1]; ++q) if (cx.p.excl[q] == p) return false;
+  if (rset < 0) return true;
+  for (int q = cx.p.rs_begin[rset]; q < cx.p.rs_begin[rset + 1]; ++q) {
+    const uint32_t rr = cx.p.rs[q];
+    if ((int)(rr & 0xFFFF) <= p && p <= (int)(rr >> 16)) return true;
+  }
+  return false;
+}
+
+__device__ inline int pick_dynamic_port_in_ranges(const DevCtx& cx, int64_t i, int cls, int slot, int nr, int32_t rset, const PairState& ps) {
   const DevOffers& o = cx.o;
   const int eb = cx.p.excl_begin[cls], ee = cx.p.excl_begin[cls + 1];
   for (int r = 0; r < nr; ++r) {
@@ -301,6 +326,17 @@ __device__ inline int pick_dynamic_port(const DevCtx& cx, int64_t i, int cls, in
   return -1;
 }
 
+// ... over the offered ranges and the ports handed back by earlier OE_OP_FREE stages of this pipeline
+__device__ inline int pick_dynamic_port(const DevCtx& cx, int64_t i, int cls, int slot, int nr, int32_t rset, const PairState& ps) {
+  int best = pick_dynamic_port_in_ranges(cx, i, cls, slot, nr, rset, ps);
+  for (int q = 0; q < ps.n_freed_ports; ++q) {
+    if ((int)(ps.freed_port[q] >> 16) != slot) continue;
+    const int p = (int)(ps.freed_port[q] & 0xFFFFu);
+    if ((best < 0 || p < best) && dynamic_port_ok(cx, cls, rset, ps, p)) best = p;
+  }
+  return best;
+}
+
 __device__ __forceinline__ bool offer_has_exec(const DevOffers& o, int64_t i, int32_t id) {
   bool h = false;
   for (int e = 0; e < o.E; ++e) h = h || __ldg(o.exec + (int64_t)e * o.N + i) == id;
@@ -325,6 +361,7 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
   for (int q = 0; q < SK; ++q) ps.val[q] = __ldg(o.scalar + (int64_t)q * o.N + i);
   ps.mounts_used = 0;
   ps.n_taken = 0;
+  ps.n_freed_ports = 0; ps.n_freed_mounts = 0; ps.freed_mounts_used = 0;
   const int nr = consumable ? o.R : 0;
   const int nd = consumable ? o.D : 0;
   int n_dyn = 0, n_mount = 0, n_res = 0;
@@ -347,7 +384,7 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
         if (pass) { ps.val[q] = __dsub_rn(avail, op.amount); ++n_res; }
       } break;
       case OE_OP_PORT_STATIC: {
-        pass = port_in_pool(o, i, op.slot, nr, op.arg) && !port_taken(ps, op.arg);
+        pass = (port_in_pool(o, i, op.slot, nr, op.arg) || port_freed(ps, op.slot, op.arg)) && !port_taken(ps, op.arg);
         if (pass) { ps.taken[ps.n_taken++] = (uint32_t)op.arg; ++n_res; }
       } break;
       case OE_OP_PORT_DYNAMIC: {
@@ -369,9 +406,16 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
           const bool prof_ok = prof >= 0 ? ((op.mask >> prof) & 1ull) != 0 : op.mask == 0;
           if (!(__dsub_rn(op.amount, size) > 0.0) && prof_ok) { chosen = d; break; }
         }
+        for (int d = 0; d < ps.n_freed_mounts && chosen < 0; ++d) {
+          if ((ps.freed_mounts_used >> d) & 1u) continue;
+          const int32_t prof = ps.freed_mount_prof[d];
+          const bool prof_ok = prof >= 0 ? ((op.mask >> prof) & 1ull) != 0 : op.mask == 0;
+          if (!(__dsub_rn(op.amount, ps.freed_mount_size[d]) > 0.0) && prof_ok) chosen = OE_MAX_MOUNT_SLOTS + d;
+        }
         pass = chosen >= 0;
         if (pass) {
-          ps.mounts_used |= 1u << chosen;
+          if (chosen >= OE_MAX_MOUNT_SLOTS) ps.freed_mounts_used |= 1u << (chosen - OE_MAX_MOUNT_SLOTS);
+          else ps.mounts_used |= 1u << chosen;
           ++n_res;
           if (RECORD && n_mount < OE_MAX_MOUNT_OPS) dec->mount_slot[n_mount] = (int8_t)chosen;
         }
@@ -392,7 +436,7 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
         if (op.opcode == OE_OP_PORT_RESERVED) {
           const int want = (int)op.aux;
           if ((int)reserved != want) {
-            pass = port_in_pool(o, i, op.slot, nr, want) && !port_taken(ps, want);
+            pass = (port_in_pool(o, i, op.slot, nr, want) || port_freed(ps, op.slot, want)) && !port_taken(ps, want);
             if (pass) ps.taken[ps.n_taken++] = (uint32_t)want;
           } else {
             ps.taken[ps.n_taken++] = (uint32_t)want | OE_KEPT;
@@ -408,7 +452,18 @@ __device__ inline bool eval_pair(const DevCtx& cx, int64_t i, const OfferKeys& o
           if (pass) ps.val[q] = __dsub_rn(avail, diff);
         }
       } break;
-      case OE_OP_FREE: {  // scalar only (ports / MOUNT frees are rejected at load)
+      case OE_OP_FREE: {
+        if (op.kind == OE_KIND_PORTS) {  // aux = the port
+          if (ps.n_freed_ports < OE_DEV_MAX_FREED) ps.freed_port[ps.n_freed_ports++] = ((uint32_t)op.slot << 16) | (uint32_t)op.aux;
+          break;
+        }
+        if (op.kind == OE_KIND_MOUNT) {  // amount = size, aux = profile id + 1
+          if (ps.n_freed_mounts < OE_DEV_MAX_FREED) {
+            ps.freed_mount_size[ps.n_freed_mounts] = op.amount;
+            ps.freed_mount_prof[ps.n_freed_mounts++] = (int32_t)op.aux - 1;
+          }
+          break;
+        }
         const int q = op.slot * o.K + op.kind;
         const double cur = ((ps.present >> q) & 1u) ? ps.val[q] : 0.0;
         ps.val[q] = __dadd_rn(cur, op.amount);
@@ -451,6 +506,8 @@ static_assert(sizeof(FastRow) == 128, "FastRow is staged as eight uint4");
 #define OE_FR_FAST 1u        // the folded form is valid for this class
 #define OE_FR_NEVER 2u       // a static port is requested twice: the second stage can never pass
 #define OE_FR_NEEDS_POOL 4u  // has scalar or port stages: an offer allocated to another role fails
+#define OE_FR_DENSE 16u      // S*K <= 8: thr[] is indexed by pool entry (-inf where the class asks nothing) and the entries
+                             // that must be present are the mask in thr_q[0..3]; K1 then tests register copies
 #define OE_FR_RULE_TAB 8u    // every leaf of the rule reads only the offer's zone / region: the rule is tabulated per
                              // (factored row, zone, region) by k_rule_tables and K1 looks the verdict up
 
@@ -463,6 +520,7 @@ struct OfferRegs {
   uint32_t present;
   uint32_t rb[OE_FAST_RANGES], rlen[OE_FAST_RANGES];  // slot-0 port ranges: begin and (end - begin); empty = never matches
   int32_t pool_ports;                                 // offered ports of slot 0
+  double sv[8];                                       // the pool entries, when S*K <= 8
 };
 
 __device__ __forceinline__ void load_offer_regs(const DevOffers& o, int64_t i, bool reg_ranges, OfferRegs& r) {
@@ -473,6 +531,8 @@ __device__ __forceinline__ void load_offer_regs(const DevOffers& o, int64_t i, b
   r.alloc = __ldg(o.alloc + i);
   r.present = __ldg(o.present + i);
   r.pool_ports = 0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) r.sv[q] = (o.S * o.K <= 8 && q < o.S * o.K) ? __ldg(o.scalar + (int64_t)q * o.N + i) : 0.0;
   if (reg_ranges) {
 #pragma unroll
     for (int q = 0; q < OE_FAST_RANGES; ++q) {
@@ -514,10 +574,17 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
     // consumableResource (MesosResourcePool.java:87-97)
     pass = pass && !(fr.pod_role >= 0 && r.alloc >= 0 && r.alloc != fr.pod_role);
   }
-  for (int t = 0; t < fr.n_thr; ++t) {
-    const int q = fr.thr_q[t];
-    const double v = sc ? sc[q * blockDim.x + threadIdx.x] : __ldg(o.scalar + (int64_t)q * o.N + i);
-    pass = pass && ((present >> q) & 1u) && !(v < fr.thr[t]);
+  if (fr.flags & OE_FR_DENSE) {
+    const uint32_t need = *reinterpret_cast<const uint32_t*>(fr.thr_q);
+    pass = pass && (present & need) == need;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) pass = pass && !(r.sv[q] < fr.thr[q]);
+  } else {
+    for (int t = 0; t < fr.n_thr; ++t) {
+      const int q = fr.thr_q[t];
+      const double v = sc ? sc[q * blockDim.x + threadIdx.x] : __ldg(o.scalar + (int64_t)q * o.N + i);
+      pass = pass && ((present >> q) & 1u) && !(v < fr.thr[t]);
+    }
   }
   if (fr.n_ports | fr.n_dyn) {
     int listed = 0;

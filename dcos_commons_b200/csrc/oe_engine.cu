@@ -628,7 +628,7 @@ struct oe_engine {
   std::vector<int32_t> h_pod_role, h_excl_begin;
   std::vector<uint16_t> h_excl;
   int n_rule_nodes = 0;
-  int fast_K = -1;  // scalar-kind count the folded class descriptors were built for (-1 = stale)
+  int fast_K = -1, fast_S = -1;  // offer-table shape the folded class descriptors were built for (-1 = stale)
   int tab_words = 0, tab_zdim = 1, tab_rdim = 1;
   bool any_rule_tab = false;
   DevBuf d_fast, d_rule_tab;
@@ -861,16 +861,19 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
     if (oe_ < ob || oe_ - ob > OE_MAX_STAGE_OPS) return h->fail(OE_ERR_LIMIT, "class %d: %d stage ops (max %d)", c, oe_ - ob, OE_MAX_STAGE_OPS);
     if (t->pod_role[c] < -1) return h->fail(OE_ERR_INVALID, "class %d: pod_role", c);
     if (t->port_excl_begin[c + 1] < t->port_excl_begin[c]) return h->fail(OE_ERR_INVALID, "class %d: port_excl_begin not monotone", c);
-    int n_port_ops = 0;
+    int n_port_ops = 0, n_free_ports = 0, n_free_mounts = 0;
     for (int x = ob; x < oe_; ++x) {
       const oe_stage_op& op = t->ops[x];
       if (op.opcode >= OE_OP__COUNT) return h->fail(OE_ERR_INVALID, "class %d op %d: unknown opcode %d", c, x - ob, op.opcode);
       const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
       const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
       if (slotted && op.slot >= OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_INVALID, "class %d op %d: role slot %d", c, x - ob, op.slot);
-      if (op.opcode == OE_OP_FREE && op.kind >= OE_MAX_SCALAR_KINDS)
-        return h->fail(OE_ERR_LIMIT, "class %d op %d: OE_OP_FREE of ports / MOUNT disks is not supported by this engine build", c, x - ob);
-      if (scalar_like && op.kind >= OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_INVALID, "class %d op %d: scalar kind %d", c, x - ob, op.kind);
+      const bool free_port = op.opcode == OE_OP_FREE && op.kind == OE_KIND_PORTS, free_mount = op.opcode == OE_OP_FREE && op.kind == OE_KIND_MOUNT;
+      if (free_port && op.aux > 65535) return h->fail(OE_ERR_INVALID, "class %d op %d: freed port", c, x - ob);
+      if (free_mount && op.aux > OE_MAX_PROFILES) return h->fail(OE_ERR_INVALID, "class %d op %d: freed MOUNT profile", c, x - ob);
+      if (free_port) ++n_free_ports;
+      if (free_mount) ++n_free_mounts;
+      if (scalar_like && !free_port && !free_mount && op.kind >= OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_INVALID, "class %d op %d: scalar kind %d", c, x - ob, op.kind);
       if (op.opcode == OE_OP_PORT_STATIC && (op.arg < 0 || op.arg > 65535)) return h->fail(OE_ERR_INVALID, "class %d op %d: port %d", c, x - ob, op.arg);
       if (op.opcode == OE_OP_PORT_RESERVED && op.aux > 65535) return h->fail(OE_ERR_INVALID, "class %d op %d: port", c, x - ob);
       if (op.opcode == OE_OP_PORT_DYNAMIC && (op.arg < -1 || op.arg >= t->n_range_sets)) return h->fail(OE_ERR_INVALID, "class %d op %d: range set %d", c, x - ob, op.arg);
@@ -915,6 +918,8 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
       }
     }
     if (n_port_ops > OE_DEV_MAX_TAKEN) return h->fail(OE_ERR_LIMIT, "class %d: %d host-port stages (max %d)", c, n_port_ops, OE_DEV_MAX_TAKEN);
+    if (n_free_ports > OE_DEV_MAX_FREED || n_free_mounts > OE_DEV_MAX_FREED)
+      return h->fail(OE_ERR_LIMIT, "class %d: more than %d orphaned ports / MOUNT disks returned to the pool", c, OE_DEV_MAX_FREED);
   }
   for (int r = 0; r < t->n_range_sets; ++r)
     if (t->range_set_begin[r + 1] < t->range_set_begin[r]) return h->fail(OE_ERR_INVALID, "range_set_begin not monotone");
@@ -1057,7 +1062,8 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
     const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
     const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
     if (slotted && op.slot >= t->n_role_slots) return h->fail(OE_ERR_INVALID, "a stage op names role slot %d, offer table has %d", op.slot, t->n_role_slots);
-    if (scalar_like && op.kind >= t->n_scalar_kinds) return h->fail(OE_ERR_INVALID, "a stage op names scalar kind %d, offer table has %d", op.kind, t->n_scalar_kinds);
+    const bool free_other = op.opcode == OE_OP_FREE && (op.kind == OE_KIND_PORTS || op.kind == OE_KIND_MOUNT);
+    if (scalar_like && !free_other && op.kind >= t->n_scalar_kinds) return h->fail(OE_ERR_INVALID, "a stage op names scalar kind %d, offer table has %d", op.kind, t->n_scalar_kinds);
   }
   for (auto& cs : h->h_csets)
     if (cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= t->n_rr_cols) return h->fail(OE_ERR_INVALID, "a counter set names rr column %d, offer table has %d", cs.rr_col, t->n_rr_cols);
@@ -1356,10 +1362,22 @@ int build_fast_rows(oe_engine* h) {
       }
     }
     if (ok && qs.size() > 8) ok = false;
-    for (size_t k = 0; ok && k < qs.size(); ++k) {
-      if (qs[k] >= 32) { ok = false; break; }
-      fr.thr_q[k] = (uint8_t)qs[k];
-      ok = fold_scalar_chain(chains[k], &fr.thr[k]);
+    const bool dense = h->dof.S * K <= 8;
+    if (dense) {
+      uint32_t need = 0;
+      for (int q = 0; q < 8; ++q) fr.thr[q] = -std::numeric_limits<double>::infinity();
+      for (size_t k = 0; ok && k < qs.size(); ++k) {
+        ok = qs[k] < 8 && fold_scalar_chain(chains[k], &fr.thr[qs[k]]);
+        need |= 1u << qs[k];
+      }
+      std::memcpy(fr.thr_q, &need, 4);
+      fr.flags |= OE_FR_DENSE;
+    } else {
+      for (size_t k = 0; ok && k < qs.size(); ++k) {
+        if (qs[k] >= 32) { ok = false; break; }
+        fr.thr_q[k] = (uint8_t)qs[k];
+        ok = fold_scalar_chain(chains[k], &fr.thr[k]);
+      }
     }
     fr.n_thr = (uint8_t)qs.size();
     if (ok) {
@@ -1398,6 +1416,7 @@ int build_fast_rows(oe_engine* h) {
   if (int rc = upload(h, h->d_fast, rows.data(), rows.size())) return rc;
   CU(cudaStreamSynchronize(h->stream));  // `rows` is a local
   h->fast_K = K;
+  h->fast_S = h->dof.S;
   h->any_rule_tab = any_tab;
   return 0;
 }
@@ -1407,7 +1426,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
   const int rows = h->rows_factored();
   CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
   if (rows > 0) {
-    if (h->fast_K != h->dof.K) if (int rc = build_fast_rows(h)) return rc;
+    if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;
     // enough row tiles to fill the machine when there are few offers, few enough to amortise the offer-row loads
     const int64_t xblocks = stride * 32 / OE_K1_THREADS;
     int tiles = (int)std::min<int64_t>(rows, std::max<int64_t>(1, (148 * 16 + xblocks - 1) / xblocks));
@@ -1428,7 +1447,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
     a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows; a.rows_per_tile = rows_per_tile;
     a.fast = h->d_fast.as<FastRow>();
     a.n_nodes = h->n_rule_nodes <= OE_K1_MAX_SMEM_NODES ? h->n_rule_nodes : 0;
-    a.sc_cols = h->dof.S * h->dof.K <= 8 ? h->dof.S * h->dof.K : 0;
+    a.sc_cols = 0;  // S*K <= 8: the pool entries live in registers (OE_FR_DENSE); otherwise they are read through L1
     const size_t smem = (size_t)rows_per_tile * sizeof(FastRow) + (size_t)a.n_nodes * sizeof(oe_rule_node) +
                         (size_t)a.sc_cols * OE_K1_THREADS * sizeof(double);
     dim3 grid((unsigned)xblocks, (unsigned)tiles);

@@ -613,9 +613,18 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   void unreserveStage(const mesos::Resource& r, StageFn& stage) {  // UnreserveEvaluationStage.java:24-36 -> MesosResourcePool.free
     StageInfo s;
     s.kind = StageInfo::UNRESERVE; s.orphan = r; s.resourceName = r.name;
-    if (ResourceUtils::isAtomic(r) || r.value.type != mesos::Value::SCALAR)
-      throw InvalidRequirementException("returning an orphaned " + r.name + " reservation of this kind to the pool is not supported by the engine (OE_OP_FREE is scalar-only)");
-    stage(s, op(OE_OP_FREE, kinds_.find(r.name), slotOfPreviousRole(r), resids_.find(*ResourceUtils::getResourceId(r)), r.value.scalar));
+    const int resid = resids_.find(*ResourceUtils::getResourceId(r));
+    if (ResourceUtils::isAtomic(r)) {  // freeAtomicResource (:408-430): the bare disk rejoins the MOUNT list
+      stage(s, op(OE_OP_FREE, OE_KIND_MOUNT, 0, resid, r.value.scalar, 0, (uint64_t)((r.disk->profile ? profiles_.intern(*r.disk->profile) : -1) + 1)));
+    } else if (r.value.type == mesos::Value::RANGES) {
+      if (r.name != "ports" || r.value.ranges.size() != 1 || r.value.ranges[0].first != r.value.ranges[0].second)
+        throw InvalidRequirementException("returning an orphaned multi-port reservation to the pool is not supported");
+      stage(s, op(OE_OP_FREE, OE_KIND_PORTS, slotOfPreviousRole(r), resid, 0.0, 0, (uint64_t)r.value.ranges[0].first));
+    } else if (r.value.type == mesos::Value::SCALAR) {
+      stage(s, op(OE_OP_FREE, kinds_.find(r.name), slotOfPreviousRole(r), resid, r.value.scalar));
+    } else {
+      throw InvalidRequirementException("orphaned " + r.name + " reservation of an unsupported value type");
+    }
   }
   template <class StageFn>
   void updateStage(const SpecRef& spec, const mesos::Resource& prior, const std::vector<std::string>& taskNames, const ExistingPod& ex,

@@ -13,7 +13,7 @@ A stage op is a tuple:
   ("nop",) ("exec", exec_id_or_-1) ("rule", tree) ("scalar", kind, amount[, slot]) ("port", port[, slot])
   ("dynport", [ (b,e), ... ] or None[, slot]) ("mount", amount, profile_mask)
   ("scalar_reserved", kind, amount, res_id[, slot, flags, exec_id]) ("port_reserved", res_id, port[, slot])
-  ("mount_reserved", res_id) ("free", kind, amount, res_id, slot)
+  ("mount_reserved", res_id) ("free", kind, amount, res_id, slot[, aux])   kind OE_KIND_PORTS: aux = port; OE_KIND_MOUNT: aux = profile + 1
 """
 from __future__ import annotations
 
@@ -130,7 +130,7 @@ class ProgramBuilder:
             elif k == "mount_reserved":
                 rec.update(opcode=abi.OP_MOUNT_RESERVED, arg=op[1])
             elif k == "free":
-                rec.update(opcode=abi.OP_FREE, kind=op[1], amount=op[2], arg=op[3], slot=op[4])
+                rec.update(opcode=abi.OP_FREE, kind=op[1], amount=op[2], arg=op[3], slot=op[4], aux=op[5] if len(op) > 5 else 0)
             else:
                 raise ValueError(f"unknown stage op {k}")
             self.ops.append(tuple(rec[f] for f in STAGE_OP_DTYPE.names))

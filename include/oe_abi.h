@@ -214,8 +214,11 @@ typedef enum {
   OE_OP_SCALAR_RESERVED = 7,
   OE_OP_PORT_RESERVED = 8,  /* same for a port kept from the prior launch: arg = resource id, aux = port          */
   OE_OP_MOUNT_RESERVED = 9, /* VolumeEvaluationStage.java:188-197: FAIL unless offer holds resource id `arg`      */
-  /* UnreserveEvaluationStage.java:24-36 → MesosResourcePool.free (:374-406): if the offer holds non-atomic
-   * resource id `arg`, add its value to pool[slot = previous role][kind] and forget the id; always passes        */
+  /* UnreserveEvaluationStage.java:24-36 → MesosResourcePool.free (:374-430): the orphaned reservation `arg` goes back
+   * into the pool and its id is forgotten; always passes.  Scalar kind: amount is added to pool[slot = previous
+   * role][kind].  kind OE_KIND_PORTS: aux = the port, added to the slot's ports.  kind OE_KIND_MOUNT: amount = size,
+   * aux = profile id + 1 (0 = none); the disk joins the end of the MOUNT list and is reported as mount slot
+   * OE_MAX_MOUNT_SLOTS + k (k-th freed disk of the pipeline).                                                      */
   OE_OP_FREE = 10,
   OE_OP__COUNT
 } oe_opcode;

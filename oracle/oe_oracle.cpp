@@ -153,6 +153,7 @@ struct Pool {
   bool ports_present[OE_MAX_ROLE_SLOTS];
   IntervalSet ports[OE_MAX_ROLE_SLOTS];
   std::vector<Mount> mounts;                                    // unreservedAtomicPool["disk"]
+  int n_freed_mounts = 0;                                       // disks handed back by OE_OP_FREE get slots OE_MAX_MOUNT_SLOTS + k
   std::map<int32_t, Reserved> reserved;                         // dynamicallyReservedPoolByResourceId
 
   // MesosResourcePool.java:61-70 on scalars
@@ -506,7 +507,7 @@ struct Oracle {
             pool.ports_present[op.slot] = true;
             pool.ports[op.slot].add((int)op.aux, (int)op.aux);
           } else if (op.kind == OE_KIND_MOUNT) {
-            pool.mounts.push_back({op.amount, (int32_t)op.aux - 1, -1});
+            pool.mounts.push_back({op.amount, (int32_t)op.aux - 1, OE_MAX_MOUNT_SLOTS + pool.n_freed_mounts++});
           } else {
             pool.role_present[op.slot] = true;
             double cur = pool.present[op.slot][op.kind] ? pool.val[op.slot][op.kind] : 0.0;

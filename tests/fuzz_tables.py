@@ -107,7 +107,11 @@ def random_tables(seed: int, n_offers=None, n_reqs=None, n_tasks=None, with_rese
                     ops.append(("scalar_reserved", int(rng.integers(0, K)), amt(), res, slot, flags, int(rng.integers(0, n_exec))))
                 elif k == 8: ops.append(("port_reserved", res, int(rng.integers(1000, 1060)), slot))
                 elif k == 9: ops.append(("mount_reserved", res))
-                else: ops.append(("free", int(rng.integers(0, K)), amt(), res, slot))
+                else:
+                    which = rng.random()
+                    if which < 0.5: ops.append(("free", int(rng.integers(0, K)), amt(), res, slot))
+                    elif which < 0.8: ops.append(("free", abi.OE_KIND_PORTS, 0.0, res, slot, int(rng.integers(1000, 1060))))
+                    else: ops.append(("free", abi.OE_KIND_MOUNT, amt(), res, 0, int(rng.integers(0, n_prof + 1))))
             else:
                 ops.append(("nop",))
         excl = None if rng.random() < 0.5 else [int(x) for x in rng.integers(1000, 1060, int(rng.integers(0, 5)))]

@@ -162,8 +162,61 @@ KAT(OfferEvaluatorPortsTest_testLaunchExpectedDynamicPort) {
   assertEquals((int64_t)10000, recs[0].task->resources[0].value.ranges[0].first);
   assertEquals(resourceId(reserved[3]), resourceId(recs[0].task->resources[0]));
 }
-// OfferEvaluatorPortsTest.java:167-213 (testUpdateStaticToStaticPort): the old port's reservation is orphaned (UNRESERVE would
-// return ports to the pool, which this engine build does not express) — covered instead: static port unchanged while cpus are added
+// OfferEvaluatorPortsTest.java:150-186 (testUpdateStaticToStaticPort) and :190-222 (testUpdateDynamicToStaticPort): the old
+// port's reservation matches no spec any more -> UNRESERVE (and it is back in the pool), the new port is a fresh RESERVE
+namespace {
+void movesToPort666(int firstPort) {
+  Fixture f;
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(PodInstanceRequirementTestUtils::getPortRequirement({firstPort}), {ResourceTestUtils::getUnreservedPorts(555, 555)});
+  assertEquals((int64_t)555, reserved[3].value.ranges[0].first);
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);
+  offered.push_back(ResourceTestUtils::getUnreservedPorts(666, 666));
+  auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getPortRequirement({666}), {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("URL-"), types(recs));
+  assertEquals((int64_t)555, recs[0].resource.value.ranges[0].first);
+  assertEquals(resourceId(reserved[3]), resourceId(recs[0].resource));
+  assertEquals((int64_t)666, recs[1].resource.value.ranges[0].first);
+  assertEquals((int64_t)666, recs[2].task->resources[0].value.ranges[0].first);
+  // without 666 on offer the move is impossible ...
+  offered.pop_back();
+  assertEquals(0u, f.evaluator.evaluate(PodInstanceRequirementTestUtils::getPortRequirement({666}), {OfferTestUtils::getOffer(offered)}).size());
+  // ... but the port that was just handed back is usable by a new spec of the same pod (MesosResourcePool.free)
+  auto b = PodInstanceRequirementTestUtils::builder();
+  b.port("renamed-port", 555);
+  auto renamed = PodInstanceRequirementTestUtils::getRequirement(b.build(), 0);
+  if (firstPort != 0) assertEquals(std::string("L-"), types(f.evaluator.evaluate(renamed, {OfferTestUtils::getOffer(offered)})));  // same number: matched, kept
+}
+}  // namespace
+KAT(OfferEvaluatorPortsTest_testUpdateStaticToStaticPort) { movesToPort666(555); }
+KAT(OfferEvaluatorPortsTest_testUpdateDynamicToStaticPort) { movesToPort666(0); }
+KAT(OfferEvaluatorPortsTest_testLaunchExpectedMultiplePorts) {  // :224-258
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getPortRequirement({10000, 10001});
+  auto reserved = f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedPorts(10000, 10001)});
+  assertEquals(5u, reserved.size());
+  auto offered = f.expectedExecutorResources();
+  offered.push_back(reserved[3]);
+  offered.push_back(reserved[4]);
+  auto recs = f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)});
+  assertEquals(std::string("L-"), types(recs));
+  assertEquals(2u, recs[0].task->resources.size());
+  assertEquals(resourceId(reserved[3]), resourceId(recs[0].task->resources[0]));
+  assertEquals(resourceId(reserved[4]), resourceId(recs[0].task->resources[1]));
+}
+// a volume whose container path no spec names any more: DESTROY is the host's business, the disk space returns to the pool
+KAT(OfferEvaluator_orphanedRootVolumeIsUnreserved) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getRootVolumeRequirement(1.0, 1500);
+  f.recordLaunchWithCompleteOfferedResources(req, {ResourceTestUtils::getUnreservedCpus(1.0), ResourceTestUtils::getUnreservedDisk(2000)});
+  auto stored = f.stateStore.fetchTasks().front();
+  auto offered = f.expectedExecutorResources();
+  for (auto& r : stored.resources) offered.push_back(r);
+  auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getCpuRequirement(1.0), {OfferTestUtils::getOffer(offered)});  // the volume is gone from the spec
+  assertEquals(std::string("UL-"), types(recs));
+  assertEquals(std::string("disk"), recs[0].resource.name);
+  assertEquals(1u, recs[1].task->resources.size());
+}
 KAT(OfferEvaluator_addResourceToExistingPod) {
   Fixture f;
   auto req1 = PodInstanceRequirementTestUtils::getPortRequirement({555});
