@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
 template <bool REG_RANGES>
-__global__ void __launch_bounds__(OE_K1_THREADS) k_class_feasibility(DevCtx cx, K1Args a) {
+__global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx cx, K1Args a) {
   extern __shared__ __align__(16) unsigned char k1_smem[];
   FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
   oe_rule_node* s_nodes = reinterpret_cast<oe_rule_node*>(s_fast + a.rows_per_tile);
