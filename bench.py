@@ -297,7 +297,7 @@ def run_engine(args):
     value = args.steps * N * M / (dev_ms * 1e-3)
 
     # ---- end-to-end arm: pinned host tables -> C ABI -> decisions in pinned host memory ------------------------------------
-    pt = pin_tables(t)
+    pt = pin_tables(t.cut_offers(lo, hi) if world > 1 else t)   # each rank keeps only its shard of the offers, pinned
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX)
 
@@ -385,10 +385,16 @@ def run_engine(args):
 
 def main():
     args = parse_args()
+    # exactly ONE line may reach stdout: libraries that print there (NCCL's version banner) are sent to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     if args.impl == "reference":
         run_reference(args)
     else:
         run_engine(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":

@@ -162,6 +162,9 @@ class CycleTables:
     launch_begin: Optional[np.ndarray] = None
     launch_name_id: Optional[np.ndarray] = None
     launch_filter_bits: Optional[np.ndarray] = None  # [n_launch, FW]
+    # set by cut_offers(): the offer columns hold only rows [offer_lo, offer_lo + n_offers) of a table of n_offers_global rows
+    offer_lo: int = 0
+    n_offers_global: Optional[int] = None
     _keep: list = field(default_factory=list, repr=False)
 
     def normalise(self):
@@ -200,6 +203,22 @@ class CycleTables:
     @property
     def n_classes(self): return int(self.op_begin.shape[0] - 1)
 
+    OFFER_COLUMNS = ("scalar", "scalar_present", "port_range", "mount_size", "mount_profile", "alloc_role", "agent_id", "hostname_id",
+                     "zone_id", "region_id", "attr_id", "rr_key", "exec_id")
+
+    def cut_offers(self, lo: int, hi: int) -> "CycleTables":
+        """A copy of the tables whose offer columns hold only rows [lo, hi): what one rank of a sharded run keeps in (pinned)
+        host memory.  Programs, tasks and requirements are shared with the original."""
+        import copy
+        if self.reserved_begin is not None and len(self.reserved_id):
+            raise NotImplementedError("sharding a table with a reserved side table")
+        c = copy.copy(self)
+        c._keep = []
+        for name in self.OFFER_COLUMNS:
+            setattr(c, name, np.ascontiguousarray(getattr(self, name)[..., lo:hi]))
+        c.offer_lo, c.n_offers_global = lo, self.n_offers
+        return c
+
     # ---- C views
     def c_programs(self) -> OeProgramTable:
         t = OeProgramTable()
@@ -230,8 +249,12 @@ class CycleTables:
     def c_offers(self, lo: int = 0, hi: Optional[int] = None, shard_rows: int = 0, row_offset: Optional[int] = None) -> OeOfferTable:
         """Offer table for rows [lo, hi) (a shard when lo/hi are given)."""
         n_all = self.n_offers
-        hi = n_all if hi is None else hi
-        whole = lo == 0 and hi == n_all
+        if self.n_offers_global is not None:  # pre-cut shard (cut_offers): every row present belongs to this rank
+            lo, hi, whole = self.offer_lo, self.offer_lo + n_all, True
+            n_all = self.n_offers_global
+        else:
+            hi = n_all if hi is None else hi
+            whole = lo == 0 and hi == n_all
 
         def cut(a):
             if whole:
