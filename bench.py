@@ -361,8 +361,16 @@ def run_engine(args):
         {"kernel": "k_count_tasks+k_rr_summary", "ms": k0 / args.steps},
     ]
     dom = max(kernels[:2], key=lambda k: k["ms"])
+    # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same command
+    traffic, traffic_path = None, os.path.join(ROOT, "profiles", "kernel_traffic.json")
+    if world == 1 and args.workload == "c5" and args.scale == 1.0 and os.path.exists(traffic_path):
+        kt = json.load(open(traffic_path)).get(dom["kernel"])
+        if kt:
+            traffic = kt["dram_bytes_read"] + kt["dram_bytes_write"]
     roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                "frac": dom["achieved_gbs"] / peak if dom["achieved_gbs"] else None, "traffic": None, "peak_source": peak_src,
+                "frac": dom["achieved_gbs"] / peak if dom["achieved_gbs"] else None, "traffic": traffic,
+                "traffic_source": "profiles/kernel_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)" if traffic else None,
+                "algorithmic_bytes": dom["algorithmic_bytes"], "peak_source": peak_src,
                 "pass_achieved": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9, "pass_frac": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9 / peak,
                 "pass_note": "pass_* = SURVEY.md §8(d) bytes_K1 (un-factored: one bit per pair written) over K0+K1+K1x device time",
                 "bytes_per_eval": ab["total"] / max(n_local * M, 1), "kernels": kernels}

@@ -50,3 +50,15 @@ def test_oracle_exports_the_same_entry_points_under_its_own_prefix(oracle_lib):
     for n in ("create", "destroy", "load_programs", "load_tasks", "load_offers", "load_requirements", "feasibility", "evaluate_cycle",
               "apply_launches", "export_tasks", "matrix_stride_words"):
         assert oracle_lib.has(n)
+
+
+def test_header_is_plain_c_and_a_c_program_links_against_the_library(tmp_path, engine_lib):
+    """include/oe_abi.h must be usable from C (what a JNI shim is written in); the program is built, and run only as far as
+    oe_create, which refuses cleanly on a box without a GPU."""
+    import subprocess
+    exe = tmp_path / "c_abi_link"
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-o", str(exe), os.path.join(ROOT, "tests", "c_abi_link.c"),
+                           abi.ENGINE_LIB, "-Wl,-rpath," + os.path.dirname(abi.ENGINE_LIB)])
+    import torch
+    rc = subprocess.run([str(exe)]).returncode
+    assert rc == 0 if torch.cuda.is_available() else rc in (0, 1), rc

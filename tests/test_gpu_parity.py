@@ -182,6 +182,42 @@ def test_c4_multi_cycle_replay(engine):
         assert np.array_equal(tc[k], tg[k])
 
 
+def test_c4_full_size_multi_cycle_replay(engine):
+    """BASELINE config 4's replay at full size: 10 000 offers, 500 steps per cycle, tallies updated between cycles
+    (oe_apply_launches); every cycle's decisions against the oracle."""
+    import copy
+    cl = synth.config_c4()
+    t = cl.tables
+    orc = Oracle()
+    per = 500
+    for cyc in range(6):
+        sub = copy.copy(t)
+        sl = slice(cyc * per, (cyc + 1) * per)
+        sub.class_id, sub.r_pod_type_id, sub.r_pod_index = t.class_id[sl].copy(), t.r_pod_type_id[sl].copy(), t.r_pod_index[sl].copy()
+        sub.launch_begin = (t.launch_begin[sl.start: sl.stop + 1] - t.launch_begin[sl.start]).astype(np.int32)
+        sub.launch_name_id = t.launch_name_id[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.launch_filter_bits = t.launch_filter_bits[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.normalise()
+        if cyc == 0:
+            orc.load(sub)
+            engine.load(sub)
+        else:
+            for h in (orc, engine):
+                h.tables = sub
+                h.load_requirements(sub)
+        d_cpu, _ = orc.evaluate_cycle()
+        d_gpu, _ = engine.evaluate_cycle()
+        assert d_gpu.tobytes() == d_cpu.tobytes(), f"cycle {cyc}"
+        assert (d_gpu["offer_row"] >= 0).sum() > 0
+        orc.apply_launches()
+        engine.apply_launches()
+    tc, tg = orc.export_tasks(), engine.export_tasks()
+    assert len(tc["name_id"]) == len(tg["name_id"]) > 2000
+    for k in tc:
+        assert np.array_equal(tc[k], tg[k])
+    orc.close()
+
+
 def test_class_rows_expand_to_matrix(engine):
     cl = synth.make_cluster(5000, 500, 8, 3, 4, 80, "c5")
     engine.load(cl.tables)
