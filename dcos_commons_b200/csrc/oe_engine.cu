@@ -611,8 +611,6 @@ struct oe_engine {
   int device = 0, rank = 0, world = 1;
   uint32_t flags = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t aux_stream = nullptr;  // K1x runs here while the commit runs on `stream` (neither needs the other's output)
-  cudaEvent_t ev_fork = nullptr, ev_x0 = nullptr, ev_x1 = nullptr;
   bool own_stream = false;
   std::string err;
   int smem_optin = 0, commit_static_smem = 0;
@@ -777,10 +775,6 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
     h->own_stream = true;
   }
   for (auto& ev : h->ev) cudaEventCreate(&ev);
-  if (cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&h->ev_fork) != cudaSuccess ||
-      cudaEventCreate(&h->ev_x0) != cudaSuccess || cudaEventCreate(&h->ev_x1) != cudaSuccess) {
-    g_create_error = "oe_create: auxiliary stream"; delete h; return OE_ERR_CUDA;
-  }
   if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
@@ -814,8 +808,6 @@ void oe_destroy(oe_engine* h) {
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
-  if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
-  for (cudaEvent_t e : {h->ev_fork, h->ev_x0, h->ev_x1}) if (e) cudaEventDestroy(e);
   if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -1468,8 +1460,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
   return 0;
 }
 
-int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr) {
-  if (!on) on = h->stream;
+int run_expand(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
   if (h->M > 0) {
@@ -1480,7 +1471,7 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr) {
     const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);
-    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
+    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, h->stream>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
                                                                          h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block);
     ++*launches;
     CU(cudaGetLastError());
@@ -1627,7 +1618,6 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   if (int rc = ready(h, "oe_evaluate_cycle")) return rc;
   if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
-  bool expand_overlapped = false;
   CU(cudaEventRecord(h->ev[0], h->stream));
   if (h->world > 1) {
     // sharded: the caller ran oe_class_feasibility on every shard and gathered the rows into OE_BUF_CLASS_BITS_GLOBAL
@@ -1641,24 +1631,11 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     CU(cudaEventRecord(h->ev[1], h->stream));
     if (int rc = run_class_feasibility(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[2], h->stream));
+    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) if (int rc = run_expand(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[3], h->stream));
-    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
-      expand_overlapped = true;
-      CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));  // before the fork: an allocation would serialise the device
-      CU(cudaEventRecord(h->ev_fork, h->stream));
-    }
   }
   if (int rc = run_commit(h, &launches)) return rc;
   CU(cudaEventRecord(h->ev[4], h->stream));
-  if (expand_overlapped) {
-    // K1x needs only the class bits (ev_fork), the commit does not need the matrix: the expansion, which keeps every SM's
-    // store path busy, is enqueued behind the commit's single CTA and runs beside it
-    CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
-    CU(cudaEventRecord(h->ev_x0, h->aux_stream));
-    if (int rc = run_expand(h, &launches, h->aux_stream)) return rc;
-    CU(cudaEventRecord(h->ev_x1, h->aux_stream));
-    CU(cudaStreamWaitEvent(h->stream, h->ev_x1, 0));
-  }
   int n_placed = 0;
   if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaMemcpyAsync(&n_placed, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -1670,7 +1647,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     std::memset(stats, 0, sizeof *stats);
     stats->ms_counters = ms_between(h->ev[0], h->ev[1]);
     stats->ms_feasibility = ms_between(h->ev[1], h->ev[2]);
-    stats->ms_expand = expand_overlapped ? ms_between(h->ev_x0, h->ev_x1) : ms_between(h->ev[2], h->ev[3]);  // overlaps ms_commit
+    stats->ms_expand = ms_between(h->ev[2], h->ev[3]);
     stats->ms_commit = ms_between(h->ev[3], h->ev[4]);
     stats->ms_d2h = ms_between(h->ev[4], h->ev[5]);
     stats->ms_total = ms_between(h->ev[0], h->ev[5]);
