@@ -299,7 +299,8 @@ def run_engine(args):
     # ---- end-to-end arm: pinned host tables -> C ABI -> decisions in pinned host memory ------------------------------------
     pt = pin_tables(t.cut_offers(lo, hi) if world > 1 else t)   # each rank keeps only its shard of the offers, pinned
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
-    eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX)
+    # the tables stay alive in pinned memory for the whole cycle, so the loads may return before their copies have landed
+    eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
 
     host_ms = {}
 

@@ -20,6 +20,7 @@ OE_PORT_EMPTY = 0x0000FFFF
 OE_NO_INDEX = -(2 ** 31)
 OE_KIND_PORTS, OE_KIND_MOUNT = 100, 101
 OE_CFG_MATERIALIZE_MATRIX = 1
+OE_CFG_ASYNC_LOADS = 2
 OE_MAX_DYN_PORTS, OE_MAX_MOUNT_OPS = 8, 4
 
 # opcodes (oe_opcode)

@@ -651,7 +651,8 @@ struct oe_engine {
   int64_t M = 0;
   int V = 0;
   std::vector<int32_t> h_class, h_rtype, h_rindex, h_req_row;
-  std::vector<int32_t> h_launch_begin, h_launch_name, h_self_begin, h_self_rows;
+  std::vector<int32_t> h_launch_begin, h_launch_name, h_self_begin, h_self_rows, h_vcls, h_vself_begin, h_vself_rows;
+  bool validation_pending = false;
   bool self_provided = false;
   std::vector<uint32_t> h_launch_filter;
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
@@ -662,6 +663,8 @@ struct oe_engine {
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
   cudaEvent_t ev[8]{};
+  cudaEvent_t ev_variants = nullptr, ev_side = nullptr;
+  cudaStream_t side_stream = nullptr;
 
   int fail(int code, const char* fmt, ...) {
     char buf[768];
@@ -700,9 +703,16 @@ struct oe_engine {
 namespace {
 
 template <class T>
-int upload(oe_engine* h, DevBuf& b, const T* src, size_t n) {
+int upload(oe_engine* h, DevBuf& b, const T* src, size_t n, cudaStream_t on = nullptr) {
   CU(b.ensure(std::max<size_t>(n, 1) * sizeof(T)));
-  if (n) CU(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+  if (n) CU(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, on ? on : h->stream));
+  return 0;
+}
+// The requirement-side uploads are small and come from pageable memory; on the main stream they would queue behind a large
+// offer-table copy that is still in flight (OE_CFG_ASYNC_LOADS), so they go through a side stream that the main stream joins.
+int join_side_uploads(oe_engine* h) {
+  CU(cudaEventRecord(h->ev_side, h->side_stream));
+  CU(cudaStreamWaitEvent(h->stream, h->ev_side, 0));
   return 0;
 }
 
@@ -775,6 +785,11 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
     h->own_stream = true;
   }
   for (auto& ev : h->ev) cudaEventCreate(&ev);
+  cudaEventCreate(&h->ev_variants);
+  cudaEventRecord(h->ev_variants, h->stream);
+  if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&h->ev_side) != cudaSuccess) {
+    g_create_error = "oe_create: side stream"; delete h; return OE_ERR_CUDA;
+  }
   if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
@@ -808,6 +823,9 @@ void oe_destroy(oe_engine* h) {
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+  if (h->ev_variants) cudaEventDestroy(h->ev_variants);
+  if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
+  if (h->ev_side) cudaEventDestroy(h->ev_side);
   if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -960,7 +978,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   p.pod_role = h->d_pod_role.as<int32_t>(); p.excl_begin = h->d_excl_begin.as<int32_t>(); p.excl = h->d_excl.as<uint16_t>();
   p.rs_begin = h->d_rs_begin.as<int32_t>(); p.rs = h->d_rs.as<uint32_t>(); p.csets = h->d_csets.as<oe_counter_set>();
   p.cs_off = h->d_cs_off.as<int64_t>(); p.ts_type = h->d_ts_type.as<int32_t>(); p.mbits = h->d_mbits.as<uint32_t>();
-  CU(cudaStreamSynchronize(h->stream));  // the caller may free its buffers after return
+  if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamSynchronize(h->stream));  // the caller may free its buffers after return
   h->hasP = true;
   return OE_OK;
 }
@@ -1037,7 +1055,8 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   h->h_tindex.assign(t->pod_index, t->pod_index + T);
   h->name_to_row.clear();
   h->name_map_built = false;  // only oe_apply_launches needs it: built on first use
-  if (int rc = fetch_err_flag(h, "oe_load_tasks")) return rc;
+  if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
+  else if (int rc = fetch_err_flag(h, "oe_load_tasks")) return rc;
   h->hasT = true;
   return OE_OK;
 }
@@ -1128,7 +1147,8 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   if (t->n_reserved > 0) check_ids(h, o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19);
   if (N > 0 && o.R > 0)
     k_validate_ranges<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(o.port, N, o.S, o.R, 18, h->d_err.as<int>());
-  if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
+  if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
+  else if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
   h->hasO = true;
   return OE_OK;
 }
@@ -1139,7 +1159,10 @@ namespace {
 int rebuild_variants(oe_engine* h) {
   const int64_t M = h->M;
   const int64_t T = (int64_t)h->h_ttype.size();
-  std::vector<int32_t> vcls, vself_begin(1, 0), vself_rows;
+  // members, not locals: their uploads may still be in flight when this returns (OE_CFG_ASYNC_LOADS)
+  std::vector<int32_t>& vcls = h->h_vcls; std::vector<int32_t>& vself_begin = h->h_vself_begin; std::vector<int32_t>& vself_rows = h->h_vself_rows;
+  CU(cudaEventSynchronize(h->ev_variants));  // ... and their previous upload must be finished before they are rewritten
+  vcls.clear(); vself_begin.assign(1, 0); vself_rows.clear();
   h->h_req_row.assign(h->h_class.begin(), h->h_class.end());
   auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
     h->h_req_row[j] = h->C + (int32_t)vcls.size();
@@ -1185,12 +1208,16 @@ int rebuild_variants(oe_engine* h) {
     }
   }
   h->V = (int)vcls.size();
-  if (int rc = upload(h, h->d_req_row, h->h_req_row.data(), (size_t)M)) return rc;
-  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size())) return rc;
-  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size())) return rc;
-  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size())) return rc;
+  // the previous contents of these device buffers may still be read by kernels of the main stream: the side stream starts behind it
+  CU(cudaEventRecord(h->ev_side, h->stream));
+  if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamWaitEvent(h->side_stream, h->ev_side, 0));
+  if (int rc = upload(h, h->d_req_row, h->h_req_row.data(), (size_t)M, h->side_stream)) return rc;
+  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size(), h->side_stream)) return rc;
+  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size(), h->side_stream)) return rc;
+  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size(), h->side_stream)) return rc;
   CU(h->d_vrrsum.ensure(std::max<size_t>((size_t)h->V * std::max(h->n_csets, 1), 1) * sizeof(int4)));
-  CU(cudaStreamSynchronize(h->stream));  // the vectors above are locals
+  CU(cudaEventRecord(h->ev_variants, h->side_stream));
+  if (int rc = join_side_uploads(h)) return rc;
   return 0;
 }
 }  // namespace
@@ -1223,8 +1250,9 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
     for (int32_t r : h->h_self_rows) if (r < 0 || r >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
   }
   if (int rc = rebuild_variants(h)) return rc;
-  if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M)) return rc;
-  if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M)) return rc;
+  if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M, h->side_stream)) return rc;
+  if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M, h->side_stream)) return rc;
+  if (int rc = join_side_uploads(h)) return rc;
   CU(h->d_dec.ensure(std::max<size_t>((size_t)M, 1) * sizeof(oe_decision)));
 
   h->h_launch_begin.clear(); h->h_launch_name.clear(); h->h_launch_filter.clear();
@@ -1237,7 +1265,7 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
     h->h_launch_name.assign(t->launch_name_id, t->launch_name_id + nl);
     h->h_launch_filter.assign(t->launch_filter_bits, t->launch_filter_bits + nl * h->dt.FW);
   }
-  CU(cudaStreamSynchronize(h->stream));
+  if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamSynchronize(h->stream));
   h->hasR = true;
   return OE_OK;
 }
@@ -1560,6 +1588,10 @@ int ready(oe_engine* h, const char* who) {
   for (auto& cs : h->h_csets)
     if (cs.keyspace == OE_KS_RR_ATTR && (cs.rr_col >= h->dof.Q || cs.rr_col >= h->dt.Q)) return h->fail(OE_ERR_INVALID, "%s: rr column mismatch", who);
   if (cudaSetDevice(h->device) != cudaSuccess) return h->fail(OE_ERR_CUDA, "cudaSetDevice");
+  if (h->validation_pending) {  // OE_CFG_ASYNC_LOADS: the id checks of the loads are read back here, before any kernel gathers through them
+    h->validation_pending = false;
+    if (int rc = fetch_err_flag(h, who)) { h->hasT = h->hasO = h->hasR = false; return rc; }
+  }
   return 0;
 }
 

@@ -7,9 +7,10 @@
 // requirement, turns the engine's decision back into the recommendation list the reference would have produced
 // (RESERVE / CREATE / LAUNCH_GROUP / StoreTaskInfo, in stage order).
 //
-// The library behind the ABI is liboe_b200.so — the CUDA engine; there is no CPU implementation in this layer.  Tests may
-// bind the same ABI to the oracle (oracle/liboe_oracle.so, prefix "oeo_") to pin the ORACLE against the reference's
-// JUnit vectors; that constructor is named forTesting() and nothing under dcos_commons_b200/ calls it.
+// The library behind the ABI is liboe_b200.so — the CUDA engine; there is no CPU implementation in this layer and no way to
+// ask this header for one: EngineLibrary::open() binds the "oe_" entry points only.  (The known-answer tests derive their own
+// loader from EngineLibrary in tests/kat/kat.hpp to point the same host code at the oracle and so pin the ORACLE against the
+// reference's JUnit vectors; that subclass lives under tests/.)
 #pragma once
 #include <dlfcn.h>
 
@@ -27,10 +28,8 @@ struct EngineError : std::runtime_error {  // surfaces as IOException in the Jav
 
 class EngineLibrary {
  public:
-  // The product path: the CUDA engine next to this header's package.
+  // The CUDA engine (liboe_b200.so, built from dcos_commons_b200/csrc).
   static EngineLibrary open(const std::string& path) { return EngineLibrary(path, "oe_"); }
-  // Test infrastructure only: any library exporting the same ABI under another prefix (the CPU oracle).
-  static EngineLibrary forTesting(const std::string& path, const std::string& prefix) { return EngineLibrary(path, prefix); }
 
   int32_t (*create)(const oe_config*, oe_engine**) = nullptr;
   void (*destroy)(oe_engine*) = nullptr;
@@ -46,7 +45,7 @@ class EngineLibrary {
   int32_t (*unexpected_resources)(oe_engine*, const uint32_t*, int32_t, uint8_t*, int64_t*) = nullptr;
   std::string path;
 
- private:
+ protected:
   EngineLibrary(const std::string& p, const std::string& prefix) : path(p) {
     void* h = dlopen(p.c_str(), RTLD_NOW | RTLD_LOCAL);
     if (!h) throw std::runtime_error(std::string("cannot load ") + p + ": " + dlerror());

@@ -79,6 +79,11 @@ typedef struct {
 #define OE_CFG_DEFAULT 0u
 /* oe_evaluate_cycle also writes the full offers x requirements bit matrix into OE_BUF_MATRIX (K1x) */
 #define OE_CFG_MATERIALIZE_MATRIX 1u
+/* oe_load_* only ENQUEUE their host→device copies and return; the caller keeps every table buffer alive and unchanged until
+ * the next evaluation call on the handle returns (that call reports a malformed id column, which a synchronous load would
+ * have reported itself).  With pinned host buffers the upload of the offer table then overlaps the host-side part of the
+ * other loads.  Without this flag a load returns only when the caller may reuse its buffers.                             */
+#define OE_CFG_ASYNC_LOADS 2u
 
 int32_t oe_abi_version(void);
 /* Replaces the construction of S/offer/evaluate/OfferEvaluator.java:85-111 (one per service,

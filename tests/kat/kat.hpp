@@ -14,6 +14,11 @@
 
 namespace kat {
 
+// Test-only loader: the same ABI exported under another prefix (the CPU oracle, "oeo_").  The product header offers no such door.
+struct OracleLibrary : sdk::EngineLibrary {
+  OracleLibrary(const std::string& path, const std::string& prefix) : sdk::EngineLibrary(path, prefix) {}
+};
+
 struct Failure : std::runtime_error { using std::runtime_error::runtime_error; };
 
 inline std::map<std::string, std::function<void()>>& registry() { static std::map<std::string, std::function<void()>> r; return r; }

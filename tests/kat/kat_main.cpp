@@ -18,8 +18,10 @@ int main(int argc, char** argv) {
     return 0;
   }
   if (lib.empty()) { std::cerr << "usage: kat_runner --lib <path> --prefix <oe_|oeo_> [--list] [--test NAME]\n"; return 2; }
-  sdk::EngineLibrary library = prefix == "oe_" ? sdk::EngineLibrary::open(lib) : sdk::EngineLibrary::forTesting(lib, prefix);
-  kat::library() = &library;
+  std::unique_ptr<sdk::EngineLibrary> library;
+  if (prefix == "oe_") library.reset(new sdk::EngineLibrary(sdk::EngineLibrary::open(lib)));
+  else library.reset(new kat::OracleLibrary(lib, prefix));
+  kat::library() = library.get();
   int failed = 0, ran = 0;
   for (auto& [name, fn] : kat::registry()) {
     if (!only.empty() && std::find(only.begin(), only.end(), name) == only.end()) continue;

@@ -132,6 +132,30 @@ def test_unexpected_resource_scan(engine, seed):
     orc.close()
 
 
+def test_async_loads_give_the_same_answers_and_still_validate():
+    eng = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    for seed in (1, 2, 3):
+        t = random_tables(seed, n_offers=400)
+        orc = Oracle().load(t)
+        eng.load(t)
+        assert eng.evaluate_cycle()[0].tobytes() == orc.evaluate_cycle()[0].tobytes()
+        eng.load(t)
+        assert np.array_equal(eng.feasibility()[0], orc.feasibility()[0])
+        orc.close()
+    bad = random_tables(3, n_offers=50, n_reqs=5, n_tasks=10)
+    bad.hostname_id = bad.hostname_id.copy()
+    bad.hostname_id[7] = 10 ** 6
+    eng.load(bad)                      # enqueued only ...
+    with pytest.raises(abi.EngineError):
+        eng.evaluate_cycle()           # ... reported by the evaluation, before any kernel gathers through the id
+    with pytest.raises(abi.EngineError):
+        eng.evaluate_cycle()           # and the handle stays unusable until tables are loaded again
+    t = random_tables(4)
+    eng.load(t)
+    assert eng.evaluate_cycle()[0].tobytes() == Oracle().load(t).evaluate_cycle()[0].tobytes()
+    eng.close()
+
+
 def test_empty_inputs(engine):
     t = random_tables(5, n_offers=40, n_reqs=6, n_tasks=0)
     _compare_all(engine, t)
