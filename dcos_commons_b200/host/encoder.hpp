@@ -202,6 +202,10 @@ struct EncodedCycle {
 struct EncoderRequirement {
   const PodInstanceRequirement* requirement = nullptr;
   std::shared_ptr<const ExistingPod> existing;  // set: getExistingEvaluationPipeline; null: getNewEvaluationPipeline
+  // PodInfoBuilder.portsByTask (PodInfoBuilder.java:130-140): task spec name -> port name -> the port the stored task of that name
+  // (unless permanently failed) advertises; a dynamic port that had a value keeps it (PortEvaluationStage.java:79-87), also when
+  // the pod goes through the new-pod pipeline (recovery type PERMANENT without the failed label)
+  std::map<std::string, std::map<std::string, int64_t>> priorPorts;
   RulePtr ruleOnly;          // when set: the class is [PlacementRuleEvaluationStage(ruleOnly)]
   PodInstance podInstance;   // used with ruleOnly
 };
@@ -287,6 +291,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       std::string key;
       if (r.ruleOnly) key = "rule@" + std::to_string((uintptr_t)r.ruleOnly.get());
       else if (r.existing) key = "existing@" + std::to_string(out_.r_class.size());   // reservations are per pod instance
+      else if (!r.priorPorts.empty()) key = "sticky@" + std::to_string(out_.r_class.size());  // remembered ports are per pod instance
       else {
         key = "pod@" + std::to_string((uintptr_t)pi.pod.get()) + "|" + std::to_string((int)r.requirement->recoveryType);
         for (auto& t : r.requirement->tasksToLaunch) key += "|" + t;
@@ -295,7 +300,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       int cls;
       if (it != classOf.end()) cls = it->second;
       else {
-        cls = r.ruleOnly ? addRuleOnlyClass(*r.ruleOnly) : r.existing ? addExistingPodClass(*r.requirement, *r.existing) : addNewPodClass(*r.requirement);
+        cls = r.ruleOnly ? addRuleOnlyClass(*r.ruleOnly) : r.existing ? addExistingPodClass(*r.requirement, *r.existing) : addNewPodClass(*r.requirement, r.priorPorts);
         classOf[key] = cls;
       }
       out_.r_class.push_back(cls);
@@ -517,16 +522,38 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     return false;
   }
 
+  // PodInfoBuilder's assignedOverlayPorts (PodInfoBuilder.java:118-122): every explicitly requested port of the pod is taken
+  void resetOverlayPorts(const PodSpec& pod) {
+    overlayAssigned_.clear();
+    for (auto& ts : pod.tasks) for (auto& rs : ts.resourceSet.resources) if (rs.isPort && rs.port > 0) overlayAssigned_.insert(rs.port);
+  }
+  // PortEvaluationStage.selectOverlayPort (:300-313): the next free port of 1025..2025 (S/dcos/DcosConstants.java), offer-independent
+  int selectOverlayPort() {
+    for (int p = 1025; p <= 2025; ++p) if (overlayAssigned_.insert(p).second) return p;
+    throw InvalidRequirementException("no overlay port left in 1025..2025");  // the stage would fail on every offer
+  }
+  using PriorPorts = std::map<std::string, std::map<std::string, int64_t>>;
+  static int priorPortFor(const PriorPorts& prior, const std::vector<std::string>& taskNames, const std::string& portName) {
+    for (auto& n : taskNames) {  // getTaskNames().stream().map(getPriorPortForTask)...findAny() (PortEvaluationStage.java:80-84)
+      auto pt = prior.find(n);
+      if (pt == prior.end()) continue;
+      auto pp = pt->second.find(portName);
+      if (pp != pt->second.end()) return (int)pp->second;
+    }
+    return 0;
+  }
+
   // getNewEvaluationPipeline (OfferEvaluator.java:411-522)
-  int addNewPodClass(const PodInstanceRequirement& req) {
+  int addNewPodClass(const PodInstanceRequirement& req, const PriorPorts& priorPorts = {}) {
     const PodSpec& pod = *req.podInstance.pod;
     std::vector<oe_stage_op> ops;
     std::vector<StageInfo> stages;
+    resetOverlayPorts(pod);
     auto stage = [&](StageInfo s, oe_stage_op o) { stages.push_back(std::move(s)); ops.push_back(o); };
     { StageInfo s; s.kind = StageInfo::EXECUTOR; stage(s, op(OE_OP_EXEC_ID, 0, 0, -1)); }                                  // :417
     if (pod.placementRule) { StageInfo s; s.kind = StageInfo::PLACEMENT; stages.push_back(s); pushRule(**pod.placementRule, ops); }   // :419-422
     for (auto& v : pod.volumes) volumeStage(v, {}, stage);                                                                    // :424-427
-    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; stage(s, op(OE_OP_NOP)); }             // :431-437
+    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; s.taskSpecName = ts.name; stage(s, op(OE_OP_NOP)); }  // :431-437
     // static ports declared anywhere in the pod are never picked dynamically (PortEvaluationStage.java:252-261)
     std::vector<int> staticPorts;
     for (auto& ts : pod.tasks) for (auto& rs : ts.resourceSet.resources) if (rs.isPort && rs.port != 0) staticPorts.push_back(rs.port);
@@ -563,12 +590,16 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
           s.taskNames = taskNames; s.role = r->role; s.preReservedRole = r->preReservedRole; s.principal = r->principal;
           const int slot = slots_.find(r->preReservedRole);
           if (r->isPort) {
-            s.kind = StageInfo::PORT; s.resourceName = "ports"; s.port = r->port; s.hostPort = requireHostPorts(r->networkNames);
+            s.kind = StageInfo::PORT; s.resourceName = "ports"; s.hostPort = requireHostPorts(r->networkNames);
             s.portName = r->portName;
+            int port = r->port;
+            if (port == 0) port = priorPortFor(priorPorts, taskNames, r->portName);           // PortEvaluationStage.java:79-87
+            if (port == 0 && !s.hostPort) port = selectOverlayPort();
+            s.port = port;
             if (!s.hostPort) stage(s, op(OE_OP_NOP));                                           // PortEvaluationStage.java:145-154
-            else if (r->port != 0) {
-              if (r->port < 0 || r->port > 65535) throw InvalidRequirementException("port out of range");
-              stage(s, op(OE_OP_PORT_STATIC, 0, slot, r->port));
+            else if (port != 0) {
+              if (port < 0 || port > 65535) throw InvalidRequirementException("port out of range");
+              stage(s, op(OE_OP_PORT_STATIC, 0, slot, port));
             } else {
               int rangeSet = -1;
               if (!r->ranges.empty()) {
@@ -653,6 +684,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       s.role = spec.r->role; s.preReservedRole = spec.r->preReservedRole; s.principal = spec.r->principal;
       int port = spec.r->port;
       if (port == 0) { auto it = priorPorts.find(spec.r->portName); if (it != priorPorts.end()) port = (int)it->second; }
+      if (port == 0 && !s.hostPort) port = selectOverlayPort();
       s.port = port;
       if (!s.hostPort) { stage(s, op(OE_OP_NOP)); return; }
       stage(s, op(OE_OP_PORT_RESERVED, 0, slots_.find(spec.r->preReservedRole), resid, 0.0, 0, (uint64_t)port));
@@ -674,7 +706,8 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       s.kind = StageInfo::PORT; s.resourceName = "ports"; s.port = spec.r->port; s.hostPort = requireHostPorts(spec.r->networkNames); s.portName = spec.r->portName;
       int port = spec.r->port;
       if (port == 0) { auto it = priorPorts.find(spec.r->portName); if (it != priorPorts.end()) port = (int)it->second; }  // PortEvaluationStage.java:79-87
-      if (!s.hostPort) stage(s, op(OE_OP_NOP));
+      if (port == 0 && !s.hostPort) port = selectOverlayPort();
+      if (!s.hostPort) { s.port = port; stage(s, op(OE_OP_NOP)); }
       else if (port != 0) { s.port = port; stage(s, op(OE_OP_PORT_STATIC, 0, slot, port)); }
       else {
         int rangeSet = -1;
@@ -696,9 +729,10 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     std::vector<oe_stage_op> ops;
     std::vector<StageInfo> stages;
     auto stage = [&](StageInfo s, oe_stage_op o) { stages.push_back(std::move(s)); ops.push_back(o); };
+    resetOverlayPorts(pod);
     { StageInfo s; s.kind = StageInfo::EXECUTOR; if (ex.executorId) s.executorId = *ex.executorId;
       stage(s, op(OE_OP_EXEC_ID, 0, 0, ex.executorId ? execs_.find(*ex.executorId) : -1)); }                     // OfferEvaluator.java:295-304
-    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; stage(s, op(OE_OP_NOP)); }  // :548-554
+    for (auto& ts : pod.tasks) if (ts.usesTLS) { StageInfo s; s.kind = StageInfo::TLS; s.taskSpecName = ts.name; stage(s, op(OE_OP_NOP)); }  // :548-554
     // (a PERMANENT recovery never comes here: it takes the new-pod pipeline, :268-271)
     std::vector<int> staticPorts;
     for (auto& ts : pod.tasks) for (auto& rs : ts.resourceSet.resources) if (rs.isPort && rs.port != 0) staticPorts.push_back(rs.port);
@@ -859,6 +893,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   Dictionary agents_, hosts_, zones_, regions_, attrs_, rrValues_, rrAttrs_, types_, names_, filters_, execs_, roles_, slots_, kinds_, resids_, profiles_;
   std::vector<MatcherPtr> filterMatchers_;
   std::unordered_map<std::string, int> matcherCache_;
+  std::set<int> overlayAssigned_;
   std::vector<std::string> pendingLaunchNames_;
   std::vector<int32_t> pendingLaunchEnd_;
 };

@@ -197,6 +197,11 @@ class OfferEvaluator {
     for (size_t j = 0; j < requirements.size(); ++j) {
       ers[j].requirement = &requirements[j];
       ers[j].existing = existingPod(requirements[j], allTasks);
+      for (auto& ts : requirements[j].podInstance.pod->tasks) {  // PodInfoBuilder.portsByTask (PodInfoBuilder.java:130-140)
+        const std::string name = taskInstanceName(requirements[j].podInstance, ts.name);
+        for (auto& t : allTasks)
+          if (t.name == name && !isPermanentlyFailed(t) && !t.discovery_ports.empty()) ers[j].priorPorts[ts.name] = t.discovery_ports;
+      }
     }
     EncodedCycle c = enc.encode(offers, allTasks, ers);
     Engine e(lib_);
@@ -346,7 +351,10 @@ class OfferEvaluator {
           int port = s.port;
           if (s.hostPort && port == 0) port = d.dyn_port[dyn < OE_MAX_DYN_PORTS ? dyn : OE_MAX_DYN_PORTS - 1];
           if (s.hostPort && s.port == 0) ++dyn;
-          if (!s.hostPort) break;  // overlay: no reservation (PortEvaluationStage.java:145-154)
+          if (!s.hostPort) {  // overlay: no reservation, the port is only advertised (PortEvaluationStage.java:145-154)
+            for (auto& n : s.taskNames) taskBuilders[n].discovery_ports[s.portName] = s.port;
+            break;
+          }
           mesos::Resource r = reservedResource(s, mesos::Value::Ranges({{port, port}}));
           ++newIds;
           rec(OfferRecommendation::RESERVE).resource = r;
@@ -451,7 +459,12 @@ struct Step {
   std::string name;
   std::optional<PodInstanceRequirement> requirement;
   enum Status { PENDING, PREPARED, STARTING, COMPLETE } status = PENDING;
-  bool isPendingOrPrepared() const { return status == PENDING || status == PREPARED; }
+  bool isPending() const { return status == PENDING; }
+  bool isPrepared() const { return status == PREPARED; }
+  bool isPendingOrPrepared() const { return isPending() || isPrepared(); }
+  void start() {}  // DeploymentStep.start (S/scheduler/plan/DeploymentStep.java:106-108) does nothing
+  // DeploymentStep.updateOfferStatus (:122-136): no operations -> PREPARED, waiting for another offer cycle; operations sent -> STARTING
+  void updateOfferStatus(size_t nOperations) { status = nOperations == 0 ? PREPARED : STARTING; }
 };
 
 // S/scheduler/plan/PlanScheduler.java:50-124
@@ -462,15 +475,22 @@ class PlanScheduler {
   // Steps that are not pending / prepared, or carry no requirement, are skipped (:73-92).  `steps` get STARTING on success.
   std::vector<OfferRecommendation> resourceOffers(const std::vector<mesos::Offer>& offers, std::vector<Step>& steps) {
     std::vector<OfferRecommendation> all;
-    if (offers.empty() || steps.empty()) return all;  // :52-54
+    if (steps.empty()) return all;
     std::vector<PodInstanceRequirement> reqs;
     std::vector<size_t> which;
-    for (size_t k = 0; k < steps.size(); ++k)
-      if (steps[k].isPendingOrPrepared() && steps[k].requirement) { reqs.push_back(*steps[k].requirement); which.push_back(k); }
-    auto per = evaluator_.evaluateCycle(reqs, offers);
+    for (size_t k = 0; k < steps.size(); ++k) {
+      if (!steps[k].isPendingOrPrepared()) continue;                                   // :73-78
+      steps[k].start();                                                                // :81
+      if (!steps[k].requirement) { steps[k].updateOfferStatus(0); continue; }          // :84-88
+      reqs.push_back(*steps[k].requirement);
+      which.push_back(k);
+    }
+    // no offers: every evaluate() comes back empty (OfferEvaluator.java:136 loops over nothing); the steps still move to PREPARED
+    auto per = offers.empty() ? std::vector<std::vector<OfferRecommendation>>(reqs.size()) : evaluator_.evaluateCycle(reqs, offers);
     for (size_t j = 0; j < per.size(); ++j) {
-      if (per[j].empty()) continue;
-      steps[which[j]].status = Step::STARTING;
+      size_t nOperations = 0;  // only what is actually sent to Mesos counts (:115-118)
+      for (auto& r : per[j]) nOperations += r.hasOperation();
+      steps[which[j]].updateOfferStatus(nOperations);
       all.insert(all.end(), per[j].begin(), per[j].end());
     }
     return all;

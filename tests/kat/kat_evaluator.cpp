@@ -186,6 +186,8 @@ KAT(OfferEvaluatorVolumesTest_testReserveCreateLaunchRootVolume) {  // :35-93
   assertEquals(resourceId(recs[4].resource), resourceId(launched));
   assertEquals(*recs[5].resource.disk->persistence_id, *launched.disk->persistence_id);
 }
+// :94-102 re-runs the test above with the refinement capability on (note in kat_reference_rest.cpp)
+KAT(OfferEvaluatorVolumesTest_testReserveCreateLaunchRootVolumeRefined) { kat_OfferEvaluatorVolumesTest_testReserveCreateLaunchRootVolume(); }
 KAT(OfferEvaluatorVolumesTest_testReserveCreateLaunchMountVolume) {  // :184-242
   Fixture f;
   auto recs = f.evaluator.evaluate(PodInstanceRequirementTestUtils::getMountVolumeRequirement(1.0, 1500),
@@ -367,7 +369,7 @@ KAT(PlanScheduler_greedyCommitRemovesUsedOffers) {
   assertEquals(std::string("small"), recs[12].offerId);
   assertTrue(steps[0].status == Step::STARTING);
   assertTrue(steps[1].status == Step::STARTING);
-  assertTrue(steps[2].status == Step::PENDING);
+  assertTrue(steps[2].status == Step::PREPARED);   // evaluated, nothing found: updateOfferStatus(empty) (:106-112)
   assertTrue(steps[3].status == Step::COMPLETE);
   assertTrue(steps[4].status == Step::STARTING);
 }

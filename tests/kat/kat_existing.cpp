@@ -72,6 +72,8 @@ KAT(OfferEvaluatorTest_testIncreaseReservationScalar) {  // :131-177
   assertEquals(id, resourceId(recs[1].task->resources[0]));
   assertEquals(2.0, recs[1].task->resources[0].value.scalar);
 }
+// :180-188, :282-290: the same two with the refinement capability on (see the note at the top of kat_reference_rest.cpp)
+KAT(OfferEvaluatorTest_testIncreaseReservationScalarRefined) { kat_OfferEvaluatorTest_testIncreaseReservationScalar(); }
 KAT(OfferEvaluatorTest_testIncreasePreReservedReservationScalar) {  // :190-236
   Fixture f;
   const std::string role = "slave_public";
@@ -103,6 +105,7 @@ KAT(OfferEvaluatorTest_testDecreaseReservationScalar) {  // :238-280
   assertEquals(id, resourceId(recs[1].task->resources[0]));
   assertEquals(1.0, recs[1].task->resources[0].value.scalar);
 }
+KAT(OfferEvaluatorTest_testDecreaseReservationScalarRefined) { kat_OfferEvaluatorTest_testDecreaseReservationScalar(); }
 KAT(OfferEvaluatorTest_testFailIncreaseReservationScalar) {  // :292-305
   Fixture f;
   auto req = PodInstanceRequirementTestUtils::getCpuRequirement(2.0);
@@ -262,6 +265,9 @@ KAT(OfferEvaluatorVolumesTest_testExpectedMountVolume) {
   offered.push_back(ResourceTestUtils::getUnreservedMountVolume(2000));
   assertEquals(0u, f.evaluator.evaluate(req, {OfferTestUtils::getOffer(offered)}).size());
 }
+// OfferEvaluatorVolumesTest.java:173-181: despite its name, testReserveLaunchScalarRefined re-runs testExpectedRootVolume
+KAT(OfferEvaluatorVolumesTest_testReserveLaunchScalarRefined) { kat_OfferEvaluatorVolumesTest_testExpectedRootVolume(); }
+KAT(OfferEvaluatorVolumesTest_testExpectedMountVolumeRefined) { kat_OfferEvaluatorVolumesTest_testExpectedMountVolume(); }  // :310-318
 // OfferEvaluator.java:268-293: a permanently failed pod (or `pod replace`) starts over with the new-pod pipeline
 KAT(OfferEvaluator_permanentRecoveryUsesTheNewPodPipeline) {
   Fixture f;

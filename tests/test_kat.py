@@ -52,7 +52,7 @@ def oracle_verdicts():
 
 
 def test_the_suite_restates_enough_vectors():
-    assert len(NAMES) >= 85
+    assert len(NAMES) >= 170
 
 
 @pytest.mark.parametrize("name", NAMES)
