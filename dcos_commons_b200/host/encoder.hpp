@@ -206,6 +206,11 @@ struct EncoderRequirement {
   // (unless permanently failed) advertises; a dynamic port that had a value keeps it (PortEvaluationStage.java:79-87), also when
   // the pod goes through the new-pod pipeline (recovery type PERMANENT without the failed label)
   std::map<std::string, std::map<std::string, int64_t>> priorPorts;
+  // Multi-service cycles (S/scheduler/multi/MultiServiceEventClient.java:312-372): the service the requirement belongs to.  Its
+  // placement rules count, and its pod is compared with, the tasks of the SAME service only (every service has its own state
+  // store), so pod types, task names and task filters are namespaced by it.  "" = the single-service scheduler.
+  std::string service;
+  const SchedulerConfig* schedulerConfig = nullptr;  // the service's own executor overhead; null = the encoder's
   RulePtr ruleOnly;          // when set: the class is [PlacementRuleEvaluationStage(ruleOnly)]
   PodInstance podInstance;   // used with ruleOnly
 };
@@ -214,10 +219,13 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
  public:
   explicit CycleEncoder(SchedulerConfig cfg = SchedulerConfig()) : cfg_(cfg) {}
 
+  // `taskServices`: empty, or one service name per task (the state store the task came from)
   EncodedCycle encode(const std::vector<mesos::Offer>& offers, const std::vector<mesos::TaskInfo>& tasks,
-                      const std::vector<EncoderRequirement>& reqs) {
+                      const std::vector<EncoderRequirement>& reqs, const std::vector<std::string>& taskServices = {}) {
     if (used_) throw std::logic_error("CycleEncoder: one encoder per cycle");
     used_ = true;
+    if (!taskServices.empty() && taskServices.size() != tasks.size()) throw std::logic_error("CycleEncoder: one service name per task");
+    auto serviceOf = [&](size_t t) -> const std::string& { static const std::string none; return taskServices.empty() ? none : taskServices[t]; };
     roles_.intern(ANY_ROLE);  // role slot 0
     slots_.intern(ANY_ROLE);
     for (const char* k : {"cpus", "mem", "disk", "gpus"}) kinds_.intern(k);
@@ -237,18 +245,20 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
         if (r.disk && r.disk->profile) profiles_.intern(*r.disk->profile);
       }
     }
-    for (auto& t : tasks) {
-      names_.intern(t.name);
+    for (size_t ti = 0; ti < tasks.size(); ++ti) {
+      const mesos::TaskInfo& t = tasks[ti];
+      names_.intern(ns(serviceOf(ti), t.name));
       agents_.intern(t.slave_id);
       if (auto v = label(t, labels::OFFER_HOSTNAME)) hosts_.intern(*v);
       if (auto v = label(t, labels::OFFER_ZONE)) zones_.intern(*v);
       if (auto v = label(t, labels::OFFER_REGION)) regions_.intern(*v);
-      if (auto v = label(t, labels::TASK_TYPE)) types_.intern(*v);
+      if (auto v = label(t, labels::TASK_TYPE)) types_.intern(ns(serviceOf(ti), *v));
       if (auto v = label(t, labels::OFFER_ATTRIBUTES)) for (auto& a : AttributeStringUtils::toStringList(*v)) attrs_.intern(a);
     }
     for (auto& r : reqs) {
       const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
-      types_.intern(pi.pod->type);
+      curService_ = r.service;
+      types_.intern(ns(r.service, pi.pod->type));
       if (r.existing) {
         if (r.existing->executorId) execs_.intern(*r.existing->executorId);
         for (auto& res : r.existing->executorInfo.resources) if (auto id = ResourceUtils::getResourceId(res)) resids_.intern(*id);
@@ -258,7 +268,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       else {
         if (pi.pod->placementRule) (*pi.pod->placementRule)->declare(*this);
         for (auto& ts : pi.pod->tasks) {
-          names_.intern(taskInstanceName(pi, ts.name));
+          names_.intern(ns(r.service, taskInstanceName(pi, ts.name)));
           for (auto& rs : ts.resourceSet.resources) {
             roles_.intern(rs.role); slots_.intern(rs.preReservedRole);
             if (!rs.isPort) kinds_.intern(rs.name);
@@ -282,18 +292,20 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
         }
 
     encodeOffers(offers);
-    encodeTasks(tasks);
+    encodeTasks(tasks, taskServices);
 
     // ---- programs and requirements
     std::map<std::string, int> classOf;
     for (auto& r : reqs) {
       const PodInstance& pi = r.ruleOnly ? r.podInstance : r.requirement->podInstance;
+      curService_ = r.service;
+      curCfg_ = r.schedulerConfig ? r.schedulerConfig : &cfg_;
       std::string key;
-      if (r.ruleOnly) key = "rule@" + std::to_string((uintptr_t)r.ruleOnly.get());
+      if (r.ruleOnly) key = "rule@" + std::to_string((uintptr_t)r.ruleOnly.get()) + "|" + r.service;
       else if (r.existing) key = "existing@" + std::to_string(out_.r_class.size());   // reservations are per pod instance
       else if (!r.priorPorts.empty()) key = "sticky@" + std::to_string(out_.r_class.size());  // remembered ports are per pod instance
       else {
-        key = "pod@" + std::to_string((uintptr_t)pi.pod.get()) + "|" + std::to_string((int)r.requirement->recoveryType);
+        key = "pod@" + std::to_string((uintptr_t)pi.pod.get()) + "|" + r.service + "|" + std::to_string((int)r.requirement->recoveryType);
         for (auto& t : r.requirement->tasksToLaunch) key += "|" + t;
       }
       auto it = classOf.find(key);
@@ -304,10 +316,10 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
         classOf[key] = cls;
       }
       out_.r_class.push_back(cls);
-      out_.r_type.push_back(types_.find(pi.pod->type));
+      out_.r_type.push_back(types_.find(ns(r.service, pi.pod->type)));
       out_.r_index.push_back(pi.index);
       if (!r.ruleOnly)
-        for (auto& ts : pi.pod->tasks) pendingLaunchNames_.push_back(taskInstanceName(pi, ts.name));
+        for (auto& ts : pi.pod->tasks) pendingLaunchNames_.push_back({r.service, taskInstanceName(pi, ts.name)});
       pendingLaunchEnd_.push_back((int32_t)pendingLaunchNames_.size());
     }
     out_.M = (int64_t)reqs.size();
@@ -316,15 +328,15 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     out_.FW = FW;
     for (size_t j = 0, l = 0; j < reqs.size(); ++j) {
       for (; l < (size_t)pendingLaunchEnd_[j]; ++l) {
-        out_.l_name.push_back(names_.find(pendingLaunchNames_[l]));
-        for (int w = 0; w < FW; ++w) out_.l_filter.push_back(filterWord(pendingLaunchNames_[l], w));
+        out_.l_name.push_back(names_.find(ns(pendingLaunchNames_[l].first, pendingLaunchNames_[l].second)));
+        for (int w = 0; w < FW; ++w) out_.l_filter.push_back(filterWord(pendingLaunchNames_[l].first, pendingLaunchNames_[l].second, w));
       }
       out_.l_begin.push_back((int32_t)out_.l_name.size());
     }
     // task filter bits (filters are only known after the rules were emitted)
     out_.t_filter.assign((size_t)FW * std::max<int64_t>(out_.T, 1), 0u);
     for (int64_t t = 0; t < out_.T; ++t)
-      for (int w = 0; w < FW; ++w) out_.t_filter[(size_t)w * out_.T + t] = filterWord(tasks[(size_t)t].name, w);
+      for (int w = 0; w < FW; ++w) out_.t_filter[(size_t)w * out_.T + t] = filterWord(serviceOf((size_t)t), tasks[(size_t)t].name, w);
 
     oe_dict_sizes& d = out_.dict;
     d.n_agents = std::max(agents_.size(), 1); d.n_hostnames = std::max(hosts_.size(), 1); d.n_zones = zones_.size(); d.n_regions = regions_.size();
@@ -345,10 +357,12 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   static std::string lower(std::string s) { for (auto& c : s) c = (char)std::tolower((unsigned char)c); return s; }
   int rrColumn(const std::string& attrName) const { return rrAttrs_.find(lower(attrName)); }  // equalsIgnoreCase
 
-  uint32_t filterWord(const std::string& taskName, int w) const {
+  // a name inside a service's own namespace (the unit separator cannot occur in a Mesos id)
+  static std::string ns(const std::string& service, const std::string& x) { return service.empty() ? x : service + '\x1f' + x; }
+  uint32_t filterWord(const std::string& service, const std::string& taskName, int w) const {
     uint32_t bits = 0;
     for (int f = w * 32; f < std::min(filters_.size(), (w + 1) * 32); ++f)
-      if (filterMatchers_[(size_t)f]->matches(taskName)) bits |= 1u << (f & 31);
+      if (filterService_[(size_t)f] == service && filterMatchers_[(size_t)f]->matches(taskName)) bits |= 1u << (f & 31);
     return bits;
   }
 
@@ -442,8 +456,9 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   }
 
   // ---- tasks ---------------------------------------------------------------------------------------------------------
-  void encodeTasks(const std::vector<mesos::TaskInfo>& tasks) {
+  void encodeTasks(const std::vector<mesos::TaskInfo>& tasks, const std::vector<std::string>& taskServices) {
     EncodedCycle& o = out_;
+    auto serviceOf = [&](size_t t) -> const std::string& { static const std::string none; return taskServices.empty() ? none : taskServices[t]; };
     const int64_t T = (int64_t)tasks.size();
     o.T = T;
     int TA = std::max(1, o.A);
@@ -461,9 +476,9 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     o.t_rr.assign((size_t)std::max(o.Q, 1) * n, -1);
     for (int64_t t = 0; t < T; ++t) {
       const mesos::TaskInfo& ti = tasks[(size_t)t];
-      o.t_name[(size_t)t] = names_.find(ti.name);
+      o.t_name[(size_t)t] = names_.find(ns(serviceOf((size_t)t), ti.name));
       o.t_agent[(size_t)t] = agents_.find(ti.slave_id);
-      if (auto v = label(ti, labels::TASK_TYPE)) o.t_type[(size_t)t] = types_.find(*v);
+      if (auto v = label(ti, labels::TASK_TYPE)) o.t_type[(size_t)t] = types_.find(ns(serviceOf((size_t)t), *v));
       if (auto v = label(ti, labels::TASK_INDEX)) {  // Integer.parseInt (TaskLabelReader.java:57-59); unparsable = not equivalent to anything
         char* end = nullptr;
         const long x = std::strtol(v->c_str(), &end, 10);
@@ -574,7 +589,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
       if (!addedExecutorResources) {  // :460-478
         addedExecutorResources = true;
         if (ordered.empty()) throw InvalidRequirementException("resource set " + rset.id + " has no resources");  // resourceSpecs.get(0)
-        for (auto& [name, value] : cfg_.getExecutorResources()) {
+        for (auto& [name, value] : curCfg_->getExecutorResources()) {
           StageInfo s;
           s.kind = StageInfo::RESOURCE; s.resourceName = name; s.value = value;
           s.role = ordered[0]->role; s.preReservedRole = ordered[0]->preReservedRole; s.principal = ordered[0]->principal;
@@ -742,7 +757,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     for (auto& ts : pod.tasks) if (!ts.resourceSet.resources.empty()) { any = &ts.resourceSet.resources[0]; break; }
     if (!any) throw InvalidRequirementException("pod " + pod.type + " has no resource spec to take role and principal from");
     std::vector<ResourceSpec> executorSpecs;
-    for (auto& [name, value] : cfg_.getExecutorResources()) executorSpecs.push_back(ResourceSpec::scalar(name, value, any->role, any->preReservedRole, any->principal));
+    for (auto& [name, value] : curCfg_->getExecutorResources()) executorSpecs.push_back(ResourceSpec::scalar(name, value, any->role, any->preReservedRole, any->principal));
     {
       std::vector<SpecRef> remaining;
       for (auto& v : pod.volumes) { SpecRef s; s.v = &v; remaining.push_back(s); }
@@ -837,7 +852,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   // ---- RuleDictionary ------------------------------------------------------------------------------------------------
   void needAgent(const std::string& a) override { agents_.intern(a); }
   void needRegion(const std::string& r) override { regions_.intern(r); }
-  void needPodType(const std::string& t) override { types_.intern(t); }
+  void needPodType(const std::string& t) override { types_.intern(ns(curService_, t)); }
   void needRoundRobinAttribute(const std::string& name) override { rrAttrs_.intern(lower(name)); }
   void needTaskFilter(const StringMatcher&) override {}
 
@@ -860,12 +875,13 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   int matcherOverZones(const StringMatcher& m) override { return matcherOver(zones_, "zone:", m); }
   int matcherOverRegions(const StringMatcher& m) override { return matcherOver(regions_, "region:", m); }
   int counterSet(int keyspace, const StringMatcher& taskFilter, const std::string& rrAttributeName) override {
-    const std::string fkey = taskFilter.toString();
+    const std::string fkey = ns(curService_, taskFilter.toString());
     int f = filters_.find(fkey);
     if (f < 0) {
       f = filters_.intern(fkey);
       // keep our own copy of the matcher: the rule object may not outlive the encoder call in every caller
       filterMatchers_.push_back(cloneMatcher(taskFilter));
+      filterService_.push_back(curService_);
     }
     const int col = keyspace == OE_KS_RR_ATTR ? rrColumn(rrAttributeName) : 0;
     for (size_t c = 0; c < out_.csets.size(); ++c)
@@ -879,7 +895,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     return AnyMatcher::create();
   }
   int typeSet(const std::string& podType) override {
-    const int t = types_.find(podType);
+    const int t = types_.find(ns(curService_, podType));
     for (size_t s = 0; s < out_.tsets.size(); ++s) if (out_.tsets[s] == t) return (int)s;
     out_.tsets.push_back(t);
     return (int)out_.tsets.size() - 1;
@@ -892,9 +908,12 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   bool used_ = false;
   Dictionary agents_, hosts_, zones_, regions_, attrs_, rrValues_, rrAttrs_, types_, names_, filters_, execs_, roles_, slots_, kinds_, resids_, profiles_;
   std::vector<MatcherPtr> filterMatchers_;
+  std::vector<std::string> filterService_;  // the service whose tasks filter f looks at
+  std::string curService_;                  // the service of the requirement being declared / emitted
+  const SchedulerConfig* curCfg_ = &cfg_;
   std::unordered_map<std::string, int> matcherCache_;
   std::set<int> overlayAssigned_;
-  std::vector<std::string> pendingLaunchNames_;
+  std::vector<std::pair<std::string, std::string>> pendingLaunchNames_;  // (service, task name)
   std::vector<int32_t> pendingLaunchEnd_;
 };
 

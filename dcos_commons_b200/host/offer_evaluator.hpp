@@ -193,16 +193,7 @@ class OfferEvaluator {
     if (requirements.empty()) return out;
     const std::vector<mesos::TaskInfo> allTasks = stateStore_.fetchTasks();  // OfferEvaluator.java:124 (once per cycle here)
     CycleEncoder enc(cfg_);
-    std::vector<EncoderRequirement> ers(requirements.size());
-    for (size_t j = 0; j < requirements.size(); ++j) {
-      ers[j].requirement = &requirements[j];
-      ers[j].existing = existingPod(requirements[j], allTasks);
-      for (auto& ts : requirements[j].podInstance.pod->tasks) {  // PodInfoBuilder.portsByTask (PodInfoBuilder.java:130-140)
-        const std::string name = taskInstanceName(requirements[j].podInstance, ts.name);
-        for (auto& t : allTasks)
-          if (t.name == name && !isPermanentlyFailed(t) && !t.discovery_ports.empty()) ers[j].priorPorts[ts.name] = t.discovery_ports;
-      }
-    }
+    std::vector<EncoderRequirement> ers = encoderRequirements(requirements, allTasks);
     EncodedCycle c = enc.encode(offers, allTasks, ers);
     Engine e(lib_);
     e.load(c);
@@ -213,6 +204,31 @@ class OfferEvaluator {
         out[j] = materialise(requirements[j], offers[(size_t)dec[j].offer_row], c.classStages[(size_t)c.r_class[j]], dec[j], ers[j].existing.get());
     return out;
   }
+
+  // The two halves of evaluateCycle, for callers that put several services' requirements into ONE engine cycle
+  // (MultiServiceEventClient below).  `requirements` must outlive the returned vector.
+  std::vector<EncoderRequirement> encoderRequirements(const std::vector<PodInstanceRequirement>& requirements,
+                                                      const std::vector<mesos::TaskInfo>& allTasks, const std::string& service = "") const {
+    std::vector<EncoderRequirement> ers(requirements.size());
+    for (size_t j = 0; j < requirements.size(); ++j) {
+      ers[j].requirement = &requirements[j];
+      ers[j].service = service;
+      ers[j].schedulerConfig = &cfg_;
+      ers[j].existing = existingPod(requirements[j], allTasks);
+      for (auto& ts : requirements[j].podInstance.pod->tasks) {  // PodInfoBuilder.portsByTask (PodInfoBuilder.java:130-140)
+        const std::string name = taskInstanceName(requirements[j].podInstance, ts.name);
+        for (auto& t : allTasks)
+          if (t.name == name && !isPermanentlyFailed(t) && !t.discovery_ports.empty()) ers[j].priorPorts[ts.name] = t.discovery_ports;
+      }
+    }
+    return ers;
+  }
+  std::vector<OfferRecommendation> recommendationsFor(const PodInstanceRequirement& requirement, const mesos::Offer& winner,
+                                                      const std::vector<StageInfo>& stages, const oe_decision& decision, const ExistingPod* existing) {
+    return materialise(requirement, winner, stages, decision, existing);
+  }
+  StateStore& stateStore() { return stateStore_; }
+  const std::string& serviceName() const { return serviceName_; }
   const std::vector<oe_decision>& lastDecisions() const { return lastDecisions_; }
 
  private:
@@ -497,6 +513,71 @@ class PlanScheduler {
   }
  private:
   OfferEvaluator& evaluator_;
+};
+
+// S/scheduler/multi/MultiServiceEventClient.java:312-372 offers(): the services take their turn in order, each seeing the offers
+// the earlier ones left (OfferUtils.filterOutAcceptedOffers).  Every service runs PlanScheduler.resourceOffers over its own
+// candidate steps against its own state store, so the whole fan-out is ONE ordered first-fit over the concatenation of the
+// services' requirements — one engine cycle instead of one per service, the services' tasks told apart by namespace.
+class MultiServiceEventClient {
+ public:
+  struct Service {
+    OfferEvaluator* evaluator;   // carries the service's name, state store and scheduler config
+    std::vector<Step>* steps;    // the candidate steps of this cycle (PlanCoordinator.getCandidates), in order
+  };
+  explicit MultiServiceEventClient(const EngineLibrary& lib) : lib_(lib) {}
+
+  std::vector<OfferRecommendation> offers(const std::vector<mesos::Offer>& offers, const std::vector<Service>& services) {
+    std::vector<OfferRecommendation> all;
+    struct Pending { size_t service, step; };
+    std::vector<Pending> which;
+    std::vector<std::vector<PodInstanceRequirement>> reqs(services.size());
+    std::vector<mesos::TaskInfo> allTasks;
+    std::vector<std::string> taskServices;
+    std::vector<EncoderRequirement> ers;
+    for (size_t s = 0; s < services.size(); ++s) {
+      std::vector<Step>& steps = *services[s].steps;
+      for (size_t k = 0; k < steps.size(); ++k) {  // PlanScheduler.java:72-92
+        if (!steps[k].isPendingOrPrepared()) continue;
+        steps[k].start();
+        if (!steps[k].requirement) { steps[k].updateOfferStatus(0); continue; }
+        reqs[s].push_back(*steps[k].requirement);
+        which.push_back({s, k});
+      }
+    }
+    for (size_t s = 0; s < services.size(); ++s) {
+      const std::vector<mesos::TaskInfo> tasks = services[s].evaluator->stateStore().fetchTasks();
+      auto e = services[s].evaluator->encoderRequirements(reqs[s], tasks, services[s].evaluator->serviceName());
+      ers.insert(ers.end(), e.begin(), e.end());
+      allTasks.insert(allTasks.end(), tasks.begin(), tasks.end());
+      taskServices.insert(taskServices.end(), tasks.size(), services[s].evaluator->serviceName());
+    }
+    std::vector<oe_decision> dec(ers.size());
+    EncodedCycle c;
+    if (!offers.empty() && !ers.empty()) {  // with no offers left the services are still cranked (:327-328): nothing can match
+      CycleEncoder enc;
+      c = enc.encode(offers, allTasks, ers, taskServices);
+      Engine e(lib_);
+      e.load(c);
+      dec = e.evaluateCycle();
+    } else {
+      for (auto& d : dec) d.offer_row = -1;
+    }
+    for (size_t j = 0; j < ers.size(); ++j) {
+      Step& step = (*services[which[j].service].steps)[which[j].step];
+      if (dec[j].offer_row < 0) { step.updateOfferStatus(0); continue; }
+      auto recs = services[which[j].service].evaluator->recommendationsFor(*ers[j].requirement, offers[(size_t)dec[j].offer_row],
+                                                                           c.classStages[(size_t)c.r_class[j]], dec[j], ers[j].existing.get());
+      size_t nOperations = 0;
+      for (auto& r : recs) nOperations += r.hasOperation();
+      step.updateOfferStatus(nOperations);
+      all.insert(all.end(), recs.begin(), recs.end());
+    }
+    return all;
+  }
+
+ private:
+  const EngineLibrary& lib_;
 };
 
 }  // namespace sdk
