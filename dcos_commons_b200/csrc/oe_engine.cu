@@ -360,10 +360,17 @@ __global__ void __launch_bounds__(128) k_row_overlap(RowBits rb, unsigned long l
 //
 // The order only matters between requirements that can compete for an offer.  Bit rows are grouped into connected
 // components of the "share an offer" relation (K3d); requirements of different components commute, so each component
-// is replayed strictly in plan order by ONE lane of a warp, up to 32 components side by side.  A lane's step is a short
-// dependent chain: row state (cursor, length, list) from shared memory, next candidate from the row's ascending list
-// (read-only global memory, L1 resident since a lane walks it forwards), claimed bit from the shared-memory bitmap.
+// is replayed strictly in plan order by ONE warp, up to 32 components side by side.
 // Prologue (whole CTA): label the components, then a stable counting sort of the requirements by component.
+//
+// A lone warp retires a dependent instruction every ~6 cycles, so what a requirement costs is the NUMBER of instructions on
+// its path (measured: a step of ~100 instructions — window from shared memory, claimed words, ballot, shuffle — took ~600
+// cycles, and probing four requirements side by side took four times that).  replay_component therefore keeps everything a
+// step needs in registers: lane l holds entry l of the current 32-candidate window of each of the component's R rows, and one
+// warp-uniform mask per row says which entries are still free.  A requirement of row k takes the lowest set bit of mask k;
+// the claimed offer is then struck from every row's mask with one compare + ballot per row (rows of one component may list
+// the same offer).  Shared memory (claimed bitmap) and global memory (the row's list) are touched only when a row's window
+// has no free entry left; the window after next is prefetched into registers, so a refill does not wait for memory either.
 struct RowState { int cursor, len; long long base; };
 struct CommitArgs {
   const int32_t* cand;
@@ -382,16 +389,135 @@ struct CommitArgs {
   int* n_placed;
 };
 #define OE_COMMIT_THREADS 1024  // 32 warps: one per component
+#define OE_COMP_ROWS 8          // rows per component that replay_component keeps in registers (more: list-walking fallback)
 #define OE_SORT_THREADS 256     // threads that take part in the counting sort of the prologue
 
+// One component, R <= OE_COMP_ROWS rows, replayed by one warp (see above).  wrow[k] = bit row of local row k; lrow[row] = k.
+//
+// Measured on this part (tools/warp_latency.cu): a taken branch ~19 cycles, SHFL / VOTE / LDS ~30 each when dependent, and an
+// `if (lane == 0) { atomicOr; store; }` inside the loop ~100 — so the step below has no divergent code and no memory
+// operation at all: the lane whose turn it is keeps the pick in a register, and claims (shared-memory bitmap) and decisions
+// (global memory) are written 32 at a time at the end of a batch, or just before a window refill reads the bitmap.
+template <int R>
+__device__ __forceinline__ int replay_component(const CommitArgs& a, RowState* rs, uint32_t* used, const int* wrow, const int* lrow,
+                                                int* win, const int n_rows, const int begin, const int end, const int lane) {
+  volatile uint32_t* vused = reinterpret_cast<volatile uint32_t*>(used);
+  int c[R], cn[R];        // lane's entry of row k's current window / of the window after it
+  uint32_t mine_free = 0;  // bit k: this lane's entry of row k is still free (lane-local, so striking an offer needs no ballot)
+#pragma unroll
+  for (int k = 0; k < R; ++k) {
+    c[k] = cn[k] = -1;
+    if (k < n_rows) {
+      const RowState st = rs[wrow[k]];
+      if (lane < st.len) c[k] = __ldg(a.cand + st.base + lane);
+      if (32 + lane < st.len) cn[k] = __ldg(a.cand + st.base + 32 + lane);
+    }
+    if (c[k] >= 0) mine_free |= 1u << k;   // nothing of this component is claimed yet
+    if (k < n_rows) win[k * 32 + lane] = c[k];  // a copy in shared memory: "my entry of row k" for a run-time k is one load, not R selects
+  }
+  __syncwarp();
+  // next window of local row k (a uniform value): registers <- prefetched registers, then test against the claimed bitmap
+  auto refill = [&](const int k) {
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+      if (q != k) continue;
+      for (;;) {
+        const RowState st = rs[wrow[q]];
+        const int start = st.cursor + 32;
+        if (start >= st.len) break;  // the row is exhausted: nothing free stays nothing free
+        c[q] = cn[q];
+        win[q * 32 + lane] = c[q];
+        cn[q] = start + 32 + lane < st.len ? __ldg(a.cand + st.base + start + 32 + lane) : -1;
+        if (lane == 0) rs[wrow[q]].cursor = start;
+        __syncwarp();
+        const uint32_t w = vused[max(c[q], 0) >> 5];
+        const bool is_free = c[q] >= 0 && !((w >> (c[q] & 31)) & 1u);
+        mine_free = is_free ? mine_free | (1u << q) : mine_free & ~(1u << q);
+        if (__ballot_sync(0xffffffffu, is_free)) break;
+      }
+    }
+  };
+  int placed = 0;
+  int2 nx = begin + lane < end ? a.order[begin + lane] : make_int2(0, 0);
+  for (int b0 = begin; b0 < end; b0 += 32) {
+    const int my_req = nx.x, my_k = lrow[nx.y];               // plan position b0 + lane
+    if (b0 + 32 + lane < end) nx = a.order[b0 + 32 + lane];   // a batch ahead of its use
+    const int cnt = min(32, end - b0);
+    int my_o = -1;                                            // what the requirement at b0 + lane takes
+    auto flush = [&]() {  // idempotent: claims of this batch so far into the bitmap
+      if (my_o >= 0) atomicOr(&used[my_o >> 5], 1u << (my_o & 31));
+      __syncwarp();
+    };
+    if (R == 1) {
+      // one row: nothing to arbitrate, the i-th requirement of the batch takes the i-th free entry — all lanes at once
+      int done = 0;
+      while (done < cnt) {
+        uint32_t fm = __ballot_sync(0xffffffffu, mine_free & 1u);
+        if (fm == 0u) { flush(); refill(0); fm = __ballot_sync(0xffffffffu, mine_free & 1u); if (fm == 0u) break; }
+        const int take = min(__popc(fm), cnt - done);
+        const bool mine = lane >= done && lane < done + take;
+        const int p = mine ? (int)__fns(fm, 0, lane - done + 1) : 0;
+        const int o = __shfl_sync(0xffffffffu, c[0], p);
+        if (mine) my_o = o;
+        const uint32_t gone = __reduce_or_sync(0xffffffffu, mine ? 1u << p : 0u);
+        mine_free &= ~((gone >> lane) & 1u);
+        done += take;
+      }
+      placed += done;
+    } else {
+      for (int i = 0; i < cnt; ++i) {
+        const int k = __shfl_sync(0xffffffffu, my_k, i);
+        const int ck = win[k * 32 + lane];  // issued early: k and the windows are known long before fmk is
+        uint32_t fmk = __ballot_sync(0xffffffffu, (mine_free >> k) & 1u);   // the free entries of row k's window
+        bool fmk_refilled = false;
+        if (fmk == 0u) {  // rare: once per 32 claimed entries of a row
+          flush();
+          refill(k);
+          __syncwarp();
+          fmk = __ballot_sync(0xffffffffu, (mine_free >> k) & 1u);
+          fmk_refilled = true;
+        }
+        const int o = __shfl_sync(0xffffffffu, fmk_refilled ? win[k * 32 + lane] : ck, (__ffs(fmk) - 1) & 31);
+        const bool got = fmk != 0u;
+        // the offer is gone from every row that lists it (rows of one component may share offers): each lane strikes its own
+        // entries, no ballot.  Window padding is -1 and o >= 0 whenever `got`.
+#pragma unroll
+        for (int q = 0; q < R; ++q) mine_free = (got && c[q] == o) ? mine_free & ~(1u << q) : mine_free;
+        my_o = (lane == i && got) ? o : my_o;
+        placed += got;
+      }
+    }
+    flush();
+    if (lane < cnt) a.dec[my_req].offer_row = my_o;
+  }
+  return placed;
+}
+
+// SMEM = row states and claimed bitmap both live in dynamic shared memory.  It is a template parameter and not a run-time choice
+// of pointer because a pointer that MAY be global makes every bitmap access a generic one (LD.E / ATOM.E instead of LDS / ATOMS),
+// and a generic atomic on a shared-memory address costs several hundred cycles on the step's dependent chain.
+template <bool SMEM>
 __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
   extern __shared__ __align__(16) unsigned char commit_smem[];
   __shared__ int comp_of[OE_ADJ_MAX_ROWS];
   __shared__ int n_comp_s, placed_s;
   __shared__ int cnt[32][OE_SORT_THREADS + 1];
   __shared__ int comp_begin[33];
-  RowState* rs = a.rows_in_smem ? reinterpret_cast<RowState*>(commit_smem) : a.rows_g;   // [rows]
-  uint32_t* used = a.used_in_smem ? reinterpret_cast<uint32_t*>(commit_smem + (a.rows_in_smem ? (size_t)a.rows * sizeof(RowState) : 0)) : a.used_g;
+  __shared__ int lrow[OE_ADJ_MAX_ROWS];              // row -> its index among the rows of its warp's component(s)
+  __shared__ int wrow[32][OE_COMP_ROWS];             // warp -> the rows it replays (first OE_COMP_ROWS of them)
+  __shared__ int wrows[32];                          // warp -> how many rows it replays
+  __shared__ int win[OE_ADJ_MAX_ROWS * 32];          // the rows' current windows, warp by warp (a copy of the registers, see replay_component)
+  __shared__ int woff[32];                           // warp -> where its windows start in win[]
+  const bool in_regs = SMEM && a.rows <= OE_ADJ_MAX_ROWS && a.M < (1 << 28);  // (requirement, local row) packs into one register
+  RowState* rs;    // [rows]
+  uint32_t* used;  // [used_words]
+  if (SMEM) {
+    rs = reinterpret_cast<RowState*>(commit_smem);
+    used = reinterpret_cast<uint32_t*>(commit_smem + (size_t)a.rows * sizeof(RowState));
+  } else {
+    rs = a.rows_in_smem ? reinterpret_cast<RowState*>(commit_smem) : a.rows_g;
+    used = a.used_in_smem ? reinterpret_cast<uint32_t*>(commit_smem + (a.rows_in_smem ? (size_t)a.rows * sizeof(RowState) : 0)) : a.used_g;
+  }
   const int tid = threadIdx.x;
   for (int64_t k = tid; k < a.used_words; k += OE_COMMIT_THREADS) used[k] = 0u;
   for (int r = tid; r < a.rows; r += OE_COMMIT_THREADS) { rs[r].cursor = 0; rs[r].len = a.row_len[r]; rs[r].base = a.row_base[r]; }
@@ -419,6 +545,16 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
       n = n > 32 ? 32 : n;
     }
     n_comp_s = n;
+    if (a.rows <= OE_ADJ_MAX_ROWS) {
+      for (int w = 0; w < 32; ++w) wrows[w] = 0;
+      for (int r = 0; r < a.rows; ++r) {
+        const int w = a.adj ? comp_of[r] : 0;
+        const int k = wrows[w]++;
+        lrow[r] = k & (OE_COMP_ROWS - 1);
+        if (k < OE_COMP_ROWS) wrow[w][k] = r;
+      }
+      for (int w = 0, run = 0; w < 32; ++w) { woff[w] = run * 32; run += wrows[w]; }
+    }
   }
   __syncthreads();
   const int n_comp = n_comp_s;
@@ -455,10 +591,27 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
   const int warp = tid >> 5, lane = tid & 31;
   int placed = 0;
   const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
-  int2 next = begin < end ? a.order[begin] : make_int2(0, 0);
+  // the component's (requirement, row) pairs come in 32 at a time, one per lane, a batch ahead of their use: a load per step, even
+  // issued a step early, would put an L2 round trip on every step
+  int2 batch = begin + lane < end ? a.order[begin + lane] : make_int2(0, 0);
+  int2 ahead = begin + 32 + lane < end ? a.order[begin + 32 + lane] : make_int2(0, 0);
+  auto next_pair = [&](int pos) {
+    const int q = (pos - begin) & 31;
+    if (q == 0 && pos != begin) {
+      batch = ahead;
+      ahead = pos + 32 + lane < end ? a.order[pos + 32 + lane] : make_int2(0, 0);
+    }
+    return make_int2(__shfl_sync(0xffffffffu, batch.x, q), __shfl_sync(0xffffffffu, batch.y, q));
+  };
+  if (in_regs && begin < end && wrows[warp] <= OE_COMP_ROWS) {
+    const int n_rows = wrows[warp];
+    if (n_rows == 1) placed = replay_component<1>(a, rs, used, wrow[warp], lrow, win + woff[warp], n_rows, begin, end, lane);
+    else if (n_rows == 2) placed = replay_component<2>(a, rs, used, wrow[warp], lrow, win + woff[warp], n_rows, begin, end, lane);
+    else if (n_rows <= 4) placed = replay_component<4>(a, rs, used, wrow[warp], lrow, win + woff[warp], n_rows, begin, end, lane);
+    else placed = replay_component<8>(a, rs, used, wrow[warp], lrow, win + woff[warp], n_rows, begin, end, lane);
+  } else
   for (int pos = begin; pos < end; ++pos) {
-    const int2 jr = next;
-    if (pos + 1 < end) next = a.order[pos + 1];  // off the dependent chain of this step
+    const int2 jr = next_pair(pos);
     const RowState st = rs[jr.y];
     const int32_t* list = a.cand + st.base;
     int pick = -1;
@@ -796,8 +949,9 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
   cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream);
   {  // the commit kernel may use all the shared memory left beside its static arrays
     cudaFuncAttributes fa{};
-    if ((e = cudaFuncGetAttributes(&fa, k_commit)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes)) != cudaSuccess) {
+    if ((e = cudaFuncGetAttributes(&fa, k_commit<true>)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_commit<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_commit<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fa.sharedSizeBytes)) != cudaSuccess) {
       g_create_error = std::string("oe_create: shared memory opt-in for the commit kernel: ") + cudaGetErrorString(e);
       delete h;
       return OE_ERR_CUDA;
@@ -1560,14 +1714,21 @@ int run_commit(oe_engine* h, int64_t* launches) {
     a.adj = h->d_adj.as<unsigned long long>();
   }
   const size_t budget = (size_t)h->smem_optin - h->commit_static_smem - 1024;  // static arrays (sort counters) share the pool
-  size_t smem = 0;
-  a.rows_in_smem = (size_t)rows * sizeof(RowState) <= budget / 4;
-  if (a.rows_in_smem) smem += (size_t)rows * sizeof(RowState);
-  else { CU(h->d_cursor.ensure((size_t)rows * sizeof(RowState))); a.rows_g = h->d_cursor.as<RowState>(); }
-  a.used_in_smem = smem + (size_t)a.used_words * 4 <= budget;
-  if (a.used_in_smem) smem += (size_t)a.used_words * 4;
-  else { CU(h->d_used.ensure(std::max<size_t>(a.used_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
-  k_commit<<<1, OE_COMMIT_THREADS, smem, h->stream>>>(a);
+  // everything in shared memory (row states, claimed bitmap): the fast variant
+  const size_t all_in = (size_t)rows * sizeof(RowState) + (size_t)a.used_words * 4;
+  if (all_in <= budget) {
+    a.rows_in_smem = a.used_in_smem = 1;
+    k_commit<true><<<1, OE_COMMIT_THREADS, all_in, h->stream>>>(a);
+  } else {
+    size_t smem = 0;
+    a.rows_in_smem = (size_t)rows * sizeof(RowState) <= budget / 4;
+    if (a.rows_in_smem) smem += (size_t)rows * sizeof(RowState);
+    else { CU(h->d_cursor.ensure((size_t)rows * sizeof(RowState))); a.rows_g = h->d_cursor.as<RowState>(); }
+    a.used_in_smem = smem + (size_t)a.used_words * 4 <= budget;
+    if (a.used_in_smem) smem += (size_t)a.used_words * 4;
+    else { CU(h->d_used.ensure(std::max<size_t>(a.used_words, 1) * 4)); a.used_g = h->d_used.as<uint32_t>(); }
+    k_commit<false><<<1, OE_COMMIT_THREADS, smem, h->stream>>>(a);
+  }
   ++*launches;
   CU(cudaGetLastError());
   k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
