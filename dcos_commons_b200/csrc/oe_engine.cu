@@ -390,7 +390,6 @@ struct CommitArgs {
 };
 #define OE_COMMIT_THREADS 1024  // 32 warps: one per component
 #define OE_COMP_ROWS 8          // rows per component that replay_component keeps in registers (more: list-walking fallback)
-#define OE_SORT_THREADS 256     // threads that take part in the counting sort of the prologue
 
 // One component, R <= OE_COMP_ROWS rows, replayed by one warp (see above).  wrow[k] = bit row of local row k; lrow[row] = k.
 //
@@ -501,7 +500,7 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
   extern __shared__ __align__(16) unsigned char commit_smem[];
   __shared__ int comp_of[OE_ADJ_MAX_ROWS];
   __shared__ int n_comp_s, placed_s;
-  __shared__ int cnt[32][OE_SORT_THREADS + 1];
+  __shared__ int cnt[32][33];   // [component][warp], [component][32] = total
   __shared__ int comp_begin[33];
   __shared__ int lrow[OE_ADJ_MAX_ROWS];              // row -> its index among the rows of its warp's component(s)
   __shared__ int wrow[32][OE_COMP_ROWS];             // warp -> the rows it replays (first OE_COMP_ROWS of them)
@@ -558,37 +557,46 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
   }
   __syncthreads();
   const int n_comp = n_comp_s;
-  // ---- stable counting sort of the requirements by component (first OE_SORT_THREADS threads)
-  const int64_t chunk = (a.M + OE_SORT_THREADS - 1) / OE_SORT_THREADS;
-  const int64_t j_lo = tid < OE_SORT_THREADS ? min(a.M, (int64_t)tid * chunk) : 0, j_hi = tid < OE_SORT_THREADS ? min(a.M, j_lo + chunk) : 0;
-  if (tid < OE_SORT_THREADS) {
-    for (int c = 0; c < n_comp; ++c) cnt[c][tid] = 0;
-    for (int64_t j = j_lo; j < j_hi; ++j) {
-      const int row = a.req_row[j];
-      ++cnt[a.adj ? comp_of[row] : 0][tid];
-    }
+  // ---- stable counting sort of the requirements by component.  A warp owns a contiguous chunk of the plan and walks it 32
+  // requirements at a time; lanes of one component find each other with match_any, so a batch costs a handful of instructions
+  // whatever the number of components (cnt[c][w] = requirements of component c in warp w's chunk, then its running offset).
+  const int warp = tid >> 5, lane = tid & 31;
+  const int64_t chunk = ((a.M + 31) / 32 + 31) / 32 * 32;  // per warp, a multiple of 32
+  const int64_t j_lo = min(a.M, (int64_t)warp * chunk), j_hi = min(a.M, j_lo + chunk);
+  cnt[lane][warp] = 0;
+  __syncwarp();
+  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 32) {
+    const int64_t j = j0 + lane;
+    const int c = j < j_hi ? (a.adj ? comp_of[a.req_row[j]] : 0) : 32 + lane;  // past the end: a group of its own, not counted
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
+    __syncwarp();
   }
   __syncthreads();
-  if (tid < n_comp) {  // exclusive scan over the threads, per component
+  if (tid < n_comp) {  // exclusive scan over the warps, per component
     int run = 0;
-    for (int t = 0; t < OE_SORT_THREADS; ++t) { const int v = cnt[tid][t]; cnt[tid][t] = run; run += v; }
-    cnt[tid][OE_SORT_THREADS] = run;
+    for (int w = 0; w < 32; ++w) { const int v = cnt[tid][w]; cnt[tid][w] = run; run += v; }
+    cnt[tid][32] = run;
   }
   __syncthreads();
   if (tid == 0) {
     int run = 0;
-    for (int c = 0; c < n_comp; ++c) { comp_begin[c] = run; run += cnt[c][OE_SORT_THREADS]; }
+    for (int c = 0; c < n_comp; ++c) { comp_begin[c] = run; run += cnt[c][32]; }
     comp_begin[n_comp] = run;
   }
   __syncthreads();
-  for (int64_t j = j_lo; j < j_hi; ++j) {
-    const int row = a.req_row[j];
-    const int c = a.adj ? comp_of[row] : 0;
-    a.order[comp_begin[c] + cnt[c][tid]++] = make_int2((int)j, row);
+  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 32) {
+    const int64_t j = j0 + lane;
+    const int row = j < j_hi ? a.req_row[j] : 0;
+    const int c = j < j_hi ? (a.adj ? comp_of[row] : 0) : 32 + lane;
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32) a.order[comp_begin[c] + cnt[c][warp] + __popc(same & ((1u << lane) - 1u))] = make_int2((int)j, row);
+    __syncwarp();
+    if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
+    __syncwarp();
   }
   __syncthreads();
-  // ---- replay: warp = component, the 32 lanes test 32 candidates of the row's list per step
-  const int warp = tid >> 5, lane = tid & 31;
+  // ---- replay: warp = component
   int placed = 0;
   const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
   // the component's (requirement, row) pairs come in 32 at a time, one per lane, a batch ahead of their use: a load per step, even
