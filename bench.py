@@ -87,20 +87,26 @@ class ClockSampler:
         self._stop = threading.Event()
         self.thread = None
 
-    def _nvml_loop(self):
+    def _nvml_init(self):
         import pynvml as nv
         nv.nvmlInit()
-        h = nv.nvmlDeviceGetHandleByIndex(self.index)
-        self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        self._nv = nv
+        self._h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM))
+        self._get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+
+    def _nvml_sample(self):
         bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
-        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        self.sm.append(float(self._nv.nvmlDeviceGetClockInfo(self._h, self._nv.NVML_CLOCK_SM)))
+        r = int(self._get_reasons(self._h))
+        for name, bit in bits.items():
+            if r & bit:
+                self.reasons.add(name)
+
+    def _nvml_loop(self):
         while not self._stop.is_set():
-            self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-            r = int(get_reasons(h))
-            for name, bit in bits.items():
-                if r & bit:
-                    self.reasons.add(name)
-            time.sleep(0.001)
+            self._nvml_sample()
+            time.sleep(0.0002)
 
     def _smi_loop(self):
         while not self._stop.is_set():
@@ -122,7 +128,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            import pynvml  # noqa: F401
+            self._nvml_init()   # before the timed region starts: a short region (N = 8: a few ms) must still be sampled
             target = self._nvml_loop
         except Exception:
             target = self._smi_loop

@@ -651,6 +651,278 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
   if (tid == 0) *a.n_placed = placed_s;
 }
 
+// ---- K2 over union lists (rows <= OE_UNION_MAX_ROWS) --------------------------------------------------------------------------
+// A component's rows mostly list the SAME offers (that is what makes them a component), so per-row windows hold the same
+// offers several times over, drain together and have to be struck one by one.  Here every component gets ONE ascending list of
+// the offers any of its rows can use, with a membership mask per entry (bit k = the component's k-th row lists it):
+//   K3u-a k_label_components   components of the rows -> CommitMeta (one warp)
+//   K3u-b k_union_bits         U[w] = OR of the bit rows of component w
+//   K3a-c                      (as for rows) ascending list of U[w]
+//   K3u-c k_union_masks        membership mask of every list entry
+// The replay then keeps a 64-entry window of that list in registers (two halves + a prefetched third) with two warp-uniform
+// "still free" words; a requirement of row k ANDs them with row k's membership words (shared memory, written when a half is
+// loaded), takes the lowest set bit and clears it: a handful of ALU instructions, no collective, no memory write.
+#define OE_UNION_MAX_ROWS 32
+struct CommitMeta {
+  int n_comp;
+  int comp_of[OE_UNION_MAX_ROWS];   // row -> warp (component, folded onto 32 warps)
+  int lrow[OE_UNION_MAX_ROWS];      // row -> index among its warp's rows
+  int wrows[32];                    // warp -> number of rows
+  int woff[33];                     // warp -> first slot in wrow[]
+  int wrow[OE_UNION_MAX_ROWS];      // the rows, warp by warp
+};
+
+__global__ void k_label_components(int rows, const unsigned long long* __restrict__ adj, CommitMeta* __restrict__ meta) {
+  if (threadIdx.x != 0) return;
+  int n = 0;
+  unsigned long long seen = 0ull;
+  for (int r = 0; r < rows; ++r) {
+    if ((seen >> r) & 1ull) continue;
+    unsigned long long group = 1ull << r, frontier = group;
+    while (adj && frontier) {
+      const int q = __ffsll((long long)frontier) - 1;
+      frontier &= frontier - 1;
+      const unsigned long long nb = adj[q] & ~group;
+      group |= nb;
+      frontier |= nb;
+    }
+    seen |= group;
+    for (int q = 0; q < rows; ++q) if ((group >> q) & 1ull) meta->comp_of[q] = n & 31;
+    ++n;
+  }
+  meta->n_comp = n > 32 ? 32 : n;
+  for (int w = 0; w < 32; ++w) meta->wrows[w] = 0;
+  for (int r = 0; r < rows; ++r) meta->lrow[r] = meta->wrows[meta->comp_of[r]]++;
+  int run = 0;
+  for (int w = 0; w < 32; ++w) { meta->woff[w] = run; run += meta->wrows[w]; }
+  meta->woff[32] = run;
+  int fill[32];
+  for (int w = 0; w < 32; ++w) fill[w] = 0;
+  for (int r = 0; r < rows; ++r) { const int w = meta->comp_of[r]; meta->wrow[meta->woff[w] + fill[w]++] = r; }
+}
+
+// thread = (union row w, word): OR of the member rows' words
+__global__ void __launch_bounds__(256) k_union_bits(RowBits rb, const CommitMeta* __restrict__ meta, uint32_t* __restrict__ U, int64_t ustride) {
+  const int w = blockIdx.y;
+  const int64_t gw = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (gw >= rb.total_words) return;
+  uint32_t x = 0u;
+  const int b = meta->woff[w], e = meta->woff[w + 1];
+  for (int q = b; q < e; ++q) x |= rb.word(meta->wrow[q], gw);
+  U[(int64_t)w * ustride + gw] = x;
+}
+
+// thread = one list entry: which of the component's rows list this offer
+__global__ void __launch_bounds__(256) k_union_masks(RowBits rb, const CommitMeta* __restrict__ meta, const int32_t* __restrict__ ucand,
+                                                     const int64_t* __restrict__ ubase, const int32_t* __restrict__ ulen,
+                                                     uint32_t* __restrict__ umask) {
+  const int w = blockIdx.y;
+  const int len = ulen[w];
+  const int b = meta->woff[w], n = meta->woff[w + 1] - b;
+  for (int e = blockIdx.x * 256 + threadIdx.x; e < len; e += gridDim.x * 256) {
+    const int o = ucand[ubase[w] + e];
+    uint32_t m = 0u;
+    for (int k = 0; k < n; ++k) m |= ((rb.word(meta->wrow[b + k], o >> 5) >> (o & 31)) & 1u) << k;
+    umask[ubase[w] + e] = m;
+  }
+}
+
+struct UnionArgs {
+  const CommitMeta* meta;
+  const int32_t* ucand;      // union lists, component by component
+  const uint32_t* umask;
+  const int64_t* ubase;      // [32]
+  const int32_t* ulen;       // [32]
+  int64_t used_words;
+  const int32_t* req_row;
+  int64_t M;
+  oe_decision* dec;
+  int2* order;
+  int* n_placed;
+};
+
+__global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs a) {
+  extern __shared__ __align__(16) unsigned char commit_smem[];
+  uint32_t* used = reinterpret_cast<uint32_t*>(commit_smem);   // claims made BEYOND a window (the window's own live in registers)
+  __shared__ CommitMeta meta;
+  __shared__ int cnt[32][33];
+  __shared__ int comp_begin[33];
+  __shared__ uint2 rmem[OE_UNION_MAX_ROWS];   // per (warp, local row): which entries of the two window halves list the row
+  __shared__ int bcur[OE_UNION_MAX_ROWS];     // per (warp, local row): where a search beyond the window resumes
+  __shared__ int placed_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int64_t k = tid; k < a.used_words; k += OE_COMMIT_THREADS) used[k] = 0u;
+  for (int k = tid; k < (int)(sizeof(CommitMeta) / 4); k += OE_COMMIT_THREADS) reinterpret_cast<int*>(&meta)[k] = reinterpret_cast<const int*>(a.meta)[k];
+  if (tid == 0) placed_s = 0;
+  if (tid < OE_UNION_MAX_ROWS) bcur[tid] = 0;
+  __syncthreads();
+  const int n_comp = meta.n_comp;
+  // ---- stable counting sort of the requirements by component (see k_commit)
+  const int64_t chunk = ((a.M + 31) / 32 + 31) / 32 * 32;
+  const int64_t j_lo = min(a.M, (int64_t)warp * chunk), j_hi = min(a.M, j_lo + chunk);
+  cnt[lane][warp] = 0;
+  __syncwarp();
+  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 32) {
+    const int64_t j = j0 + lane;
+    const int c = j < j_hi ? meta.comp_of[a.req_row[j]] : 32 + lane;
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
+    __syncwarp();
+  }
+  __syncthreads();
+  if (tid < n_comp) {
+    int run = 0;
+    for (int w = 0; w < 32; ++w) { const int v = cnt[tid][w]; cnt[tid][w] = run; run += v; }
+    cnt[tid][32] = run;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int c = 0; c < n_comp; ++c) { comp_begin[c] = run; run += cnt[c][32]; }
+    comp_begin[n_comp] = run;
+  }
+  __syncthreads();
+  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 32) {
+    const int64_t j = j0 + lane;
+    const int row = j < j_hi ? a.req_row[j] : 0;
+    const int c = j < j_hi ? meta.comp_of[row] : 32 + lane;
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32) a.order[comp_begin[c] + cnt[c][warp] + __popc(same & ((1u << lane) - 1u))] = make_int2((int)j, meta.lrow[row]);
+    __syncwarp();
+    if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
+    __syncwarp();
+  }
+  __syncthreads();
+  // ---- replay: warp = component
+  int placed = 0;
+  const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
+  if (begin < end) {
+    volatile uint32_t* vused = reinterpret_cast<volatile uint32_t*>(used);
+    const int R = meta.wrows[warp];
+    uint2* rm = rmem + meta.woff[warp];
+    int* bc = bcur + meta.woff[warp];
+    const int32_t* L = a.ucand + a.ubase[warp];
+    const uint32_t* Mk = a.umask + a.ubase[warp];
+    const int len = a.ulen[warp];
+    int wpos = 0;  // list index of the first entry of half 0
+    int u0 = lane < len ? __ldg(L + lane) : -1, u1 = 32 + lane < len ? __ldg(L + 32 + lane) : -1, un = 64 + lane < len ? __ldg(L + 64 + lane) : -1;
+    uint32_t m0 = lane < len ? __ldg(Mk + lane) : 0u, m1 = 32 + lane < len ? __ldg(Mk + 32 + lane) : 0u, mn = 64 + lane < len ? __ldg(Mk + 64 + lane) : 0u;
+    uint32_t free0 = __ballot_sync(0xffffffffu, u0 >= 0), free1 = __ballot_sync(0xffffffffu, u1 >= 0);
+    {
+      uint2 mine = make_uint2(0u, 0u);
+      for (int k = 0; k < R; ++k) {
+        const uint32_t x = __ballot_sync(0xffffffffu, (m0 >> k) & 1u), y = __ballot_sync(0xffffffffu, (m1 >> k) & 1u);
+        if (lane == k) mine = make_uint2(x, y);
+      }
+      if (lane < R) rm[lane] = mine;
+      __syncwarp();
+    }
+    int2 nx = begin + lane < end ? a.order[begin + lane] : make_int2(0, 0);
+    for (int b0 = begin; b0 < end; b0 += 32) {
+      const int my_req = nx.x, my_k = nx.y;                       // plan position b0 + lane
+      if (b0 + 32 + lane < end) nx = a.order[b0 + 32 + lane];     // a batch ahead of its use
+      const int cnt_b = min(32, end - b0);
+      int my_o = -1;
+      int my_pos = -1;  // window position taken by the requirement at b0 + lane; -2 = nothing of its row was free in the window
+      // the picks made inside the window, read out of the registers
+      auto read_out = [&]() {
+        const int o0 = __shfl_sync(0xffffffffu, u0, my_pos & 31), o1 = __shfl_sync(0xffffffffu, u1, my_pos & 31);
+        if (my_pos >= 0) { my_o = my_pos < 32 ? o0 : o1; my_pos = -1; }
+      };
+      // requirements whose row had nothing free inside the window, in plan order: they look beyond it, from where the last
+      // such search of the row ended
+      auto beyond = [&]() {
+        for (uint32_t pend = __ballot_sync(0xffffffffu, my_pos == -2); pend; pend &= pend - 1) {
+          const int i = __ffs(pend) - 1;
+          const int k = __shfl_sync(0xffffffffu, my_k, i);
+          int start = max(bc[k], wpos + 64);
+          int o = -1;
+          while (start < len) {
+            const int idx = start + lane;
+            const int u = idx < len ? __ldg(L + idx) : -1;
+            const uint32_t m = idx < len ? __ldg(Mk + idx) : 0u;
+            const bool ok = ((m >> k) & 1u) && !((vused[max(u, 0) >> 5] >> (u & 31)) & 1u);
+            const uint32_t b = __ballot_sync(0xffffffffu, ok);
+            if (b) {
+              const int p = __ffs(b) - 1;
+              o = __shfl_sync(0xffffffffu, u, p);
+              if (lane == p) atomicOr(&used[u >> 5], 1u << (u & 31));
+              start += p + 1;
+              break;
+            }
+            start += 32;
+          }
+          if (lane == 0) bc[k] = min(start, len);
+          __syncwarp();
+          if (lane == i) { my_o = o; my_pos = -1; }
+          placed += o >= 0;
+        }
+      };
+      // Straight-line steps, eight at a time: no branch, no collective except the shuffle that fetches the row (off the
+      // chain), no memory write.  What happens rarely is only noted and dealt with between the groups of eight: a requirement
+      // whose row has nothing free inside the window (it takes an entry BEYOND the window, which no step inside the window
+      // can touch, so deferring it changes nothing — as long as it is served before the window moves), and moving the window
+      // on once half 0 is used up (until then the steps simply draw on half 1).
+      for (int i0 = 0; i0 < cnt_b; i0 += 8) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          const int i = i0 + t;
+          const int k = __shfl_sync(0xffffffffu, my_k, i);
+          const uint2 r = rm[k];
+          // the dependent chain from one step to the next is and -> negate -> and -> xor on free0 (one select more on free1)
+          const uint32_t act = i < cnt_b ? 0xffffffffu : 0u;
+          const uint32_t a0 = r.x & free0 & act, a1 = r.y & free1 & act;
+          const uint32_t bit0 = a0 & (0u - a0);                      // lowest free entry of the row in half 0, if any
+          const uint32_t bit1 = a0 ? 0u : a1 & (0u - a1);            // ... else in half 1
+          free0 ^= bit0;
+          free1 ^= bit1;
+          // off the chain: where that was, for the lane whose requirement this is (bfind of a one-bit word = its position)
+          const uint32_t both = bit0 | bit1;
+          const int none = -1 - (int)(act & 1u);
+          asm volatile(
+              "{ .reg .pred q0, qa, qme; .reg .s32 pos, hi, v;\n"
+              "  bfind.u32 pos, %2;\n"
+              "  setp.ne.u32 q0, %3, 0;\n"
+              "  selp.s32 hi, 0, 32, q0;\n"
+              "  add.s32 pos, pos, hi;\n"
+              "  setp.ne.u32 qa, %2, 0;\n"
+              "  selp.s32 v, pos, %4, qa;\n"
+              "  setp.eq.s32 qme, %1, %5;\n"
+              "  selp.s32 %0, v, %0, qme; }"
+              : "+r"(my_pos)
+              : "r"(lane), "r"(both), "r"(bit0), "r"(none), "r"(i));
+          placed += both != 0u;
+        }
+        if (free0 == 0u && wpos < len) {
+          beyond();
+          read_out();
+          do {  // half 0 is used up: half 1 -> half 0, prefetched -> half 1
+            u0 = u1; m0 = m1; free0 = free1;
+            u1 = un; m1 = mn;
+            wpos += 32;
+            un = wpos + 64 + lane < len ? __ldg(L + wpos + 64 + lane) : -1;
+            mn = wpos + 64 + lane < len ? __ldg(Mk + wpos + 64 + lane) : 0u;
+            free1 = __ballot_sync(0xffffffffu, u1 >= 0 && !((vused[max(u1, 0) >> 5] >> (u1 & 31)) & 1u));
+            uint32_t y = 0u;
+            for (int q = 0; q < R; ++q) {
+              const uint32_t v = __ballot_sync(0xffffffffu, (m1 >> q) & 1u);
+              if (lane == q) y = v;
+            }
+            if (lane < R) rm[lane] = make_uint2(rm[lane].y, y);
+            __syncwarp();
+          } while (free0 == 0u && wpos < len);
+        }
+      }
+      beyond();
+      read_out();
+      if (lane < cnt_b) a.dec[my_req].offer_row = my_o;
+    }
+  }
+  if (lane == 0 && placed) atomicAdd(&placed_s, placed);
+  __syncthreads();
+  if (tid == 0) *a.n_placed = placed_s;
+}
+
 // K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
 __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -774,7 +1046,7 @@ struct oe_engine {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   std::string err;
-  int smem_optin = 0, commit_static_smem = 0;
+  int smem_optin = 0, commit_static_smem = 0, union_static_smem = 0;
 
   // ---- programs (host copies kept for validation, variant detection and launch bookkeeping)
   bool hasP = false, hasT = false, hasO = false, hasR = false;
@@ -821,6 +1093,7 @@ struct oe_engine {
   // ---- derived / outputs
   DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj, d_dbg, d_keep, d_gc_out, d_taken;
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
+  DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
   cudaEvent_t ev[8]{};
@@ -965,6 +1238,14 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
       return OE_ERR_CUDA;
     }
     h->commit_static_smem = (int)fa.sharedSizeBytes;
+    cudaFuncAttributes fu{};
+    if ((e = cudaFuncGetAttributes(&fu, k_commit_union)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_commit_union, cudaFuncAttributeMaxDynamicSharedMemorySize, h->smem_optin - (int)fu.sharedSizeBytes)) != cudaSuccess) {
+      g_create_error = std::string("oe_create: shared memory opt-in for the union commit kernel: ") + cudaGetErrorString(e);
+      delete h;
+      return OE_ERR_CUDA;
+    }
+    h->union_static_smem = (int)fu.sharedSizeBytes;
   }
   *out = h;
   return OE_OK;
@@ -1688,8 +1969,55 @@ int run_commit(oe_engine* h, int64_t* launches) {
     CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
     return 0;
   }
-  // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
+  if (rows <= OE_UNION_MAX_ROWS && (size_t)rb.total_words * 4 + 1024 <= (size_t)h->smem_optin - h->union_static_smem) {
+    // ---- commit over union lists (see k_commit_union)
+    const unsigned long long* adj = nullptr;
+    if (rows > 1) {
+      CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
+      CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, h->stream));
+      k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
+      ++*launches;
+      adj = h->d_adj.as<unsigned long long>();
+    }
+    CU(h->d_meta.ensure(sizeof(CommitMeta)));
+    CommitMeta* meta = h->d_meta.as<CommitMeta>();
+    k_label_components<<<1, 32, 0, h->stream>>>(rows, adj, meta);
+    const int64_t ustride = rb.total_words;
+    CU(h->d_union.ensure(std::max<size_t>((size_t)32 * ustride, 1) * 4));
+    k_union_bits<<<dim3((unsigned)std::max<int64_t>(1, (ustride + 255) / 256), 32), 256, 0, h->stream>>>(rb, meta, h->d_union.as<uint32_t>(), ustride);
+    RowBits ub{};
+    ub.F = h->d_union.as<uint32_t>(); ub.stride = ustride; ub.rows = 32; ub.shard_words = ustride; ub.total_words = ustride;
+    CU(h->d_tile_cnt.ensure((size_t)32 * tiles * 4));
+    CU(h->d_row_base.ensure((size_t)33 * 8));
+    CU(h->d_row_len.ensure((size_t)32 * 4));
+    // components share no offer, so all union lists together hold at most one entry per offer: no size read-back needed
+    CU(h->d_cand.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
+    CU(h->d_umask.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
+    dim3 ugrid((unsigned)tiles, 32);
+    k_tile_popc<<<ugrid, 256, 0, h->stream>>>(ub, tiles, h->d_tile_cnt.as<int32_t>());
+    k_row_offsets<<<1, 1024, 0, h->stream>>>(32, tiles, (int64_t)0x7fffffff, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>());
+    k_compact_rows<<<ugrid, 256, 0, h->stream>>>(ub, tiles, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(),
+                                                 h->d_cand.as<int32_t>());
+    k_union_masks<<<dim3((unsigned)std::max<int64_t>(1, std::min<int64_t>(1024, (ustride * 32 + 255) / 256)), 32), 256, 0, h->stream>>>(
+        rb, meta, h->d_cand.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(), h->d_umask.as<uint32_t>());
+    *launches += 6;
+    CU(cudaGetLastError());
+    UnionArgs ua{};
+    ua.meta = meta; ua.ucand = h->d_cand.as<int32_t>(); ua.umask = h->d_umask.as<uint32_t>(); ua.ubase = h->d_row_base.as<int64_t>();
+    ua.ulen = h->d_row_len.as<int32_t>(); ua.used_words = rb.total_words; ua.req_row = h->d_req_row.as<int32_t>(); ua.M = h->M;
+    ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
+    CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
+    ua.order = h->d_order.as<int2>();
+    k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->stream>>>(ua);
+    ++*launches;
+    CU(cudaGetLastError());
+    k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+    ++*launches;
+    CU(cudaGetLastError());
+    return 0;
+  }
+  // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
   const int64_t cap = h->M + 16;
   CU(h->d_tile_cnt.ensure((size_t)rows * tiles * 4));
   CU(h->d_row_base.ensure(((size_t)rows + 1) * 8));
@@ -1717,7 +2045,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   if (rows <= OE_ADJ_MAX_ROWS && rows > 1) {
     CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
     CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, h->stream));
-    k_row_overlap<<<(unsigned)((rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
+    k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
     ++*launches;
     a.adj = h->d_adj.as<unsigned long long>();
   }
