@@ -284,6 +284,25 @@ class CycleTables:
             t.reserved_kind, t.reserved_value = _ptr(self.reserved_kind), _ptr(self.reserved_value)
         return t
 
+    OFFER_COLUMNS = ("scalar", "scalar_present", "port_range", "mount_size", "mount_profile", "alloc_role", "agent_id", "hostname_id",
+                     "zone_id", "region_id", "attr_id", "rr_key", "exec_id")
+
+    def c_offer_rows(self, rows) -> OeOfferTable:
+        """The given rows of the offer table as a small table of their own (what oe_update_offers takes)."""
+        rows = np.asarray(rows, np.int64)
+        t = OeOfferTable()
+        t.n_offers, t.row_offset, t.n_offers_global, t.shard_rows = len(rows), 0, len(rows), 0
+        S, K, _ = self.scalar.shape
+        t.n_role_slots, t.n_scalar_kinds = S, K
+        t.n_port_ranges = self.port_range.shape[1]
+        t.n_mount_slots = self.mount_size.shape[0]
+        t.n_attr_slots, t.n_rr_cols, t.n_exec_slots = self.attr_id.shape[0], self.rr_key.shape[0], self.exec_id.shape[0]
+        for name in self.OFFER_COLUMNS:
+            b = np.ascontiguousarray(getattr(self, name)[..., rows])
+            self._keep.append(b)
+            setattr(t, name, _ptr(b))
+        return t
+
     def c_reqs(self) -> OeReqTable:
         t = OeReqTable()
         t.n_reqs = self.n_reqs
@@ -379,6 +398,16 @@ class Handle:
         self._co = t.c_offers(lo, hi, shard_rows, self.rank * shard_rows if (shard_rows and self.world > 1) else None)
         self._n_local = int(self._co.n_offers)
         self._check(self.b.fn("load_offers")(self.h, C.byref(self._co)))
+
+    def update_offers(self, rows, values: CycleTables, value_rows=None):
+        """oe_update_offers: resident row rows[k] <- row value_rows[k] of `values` (default: the same row numbers)."""
+        rows = np.ascontiguousarray(rows, np.int64)
+        values.normalise()
+        co = values.c_offer_rows(rows if value_rows is None else value_rows)
+        f = self.b.fn("update_offers")
+        f.argtypes = [_p, _p, C.c_int64, _p]
+        self._check(f(self.h, rows.ctypes.data if len(rows) else None, len(rows), C.byref(co)))
+        self._upd = (rows, co)
 
     def load_requirements(self, t: CycleTables):
         self._cr = t.c_reqs()

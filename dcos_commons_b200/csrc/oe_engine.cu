@@ -41,6 +41,15 @@ __global__ void k_validate_ids(const int32_t* __restrict__ col, int64_t n, int32
 
 // The `ports` ranges of one (offer, role slot) must be ascending and disjoint (the host merges them the way antlr's
 // IntervalSet does, S/offer/RangeUtils.java:23-47): the folded port test counts offered ports by range length.
+// oe_update_offers: dst[slot][rows[k]] = src[slot][k] for a slot-major column (4- or 8-byte elements)
+template <class T>
+__global__ void k_scatter_rows(T* __restrict__ dst, int64_t N, const T* __restrict__ src, int64_t n, int slots, const int64_t* __restrict__ rows) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * slots) return;
+  const int64_t slot = q / n, k = q - slot * n;
+  dst[slot * N + rows[k]] = src[q];
+}
+
 __global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, int S, int R, int code, int* err) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -1106,6 +1115,7 @@ struct oe_engine {
   DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj, d_dbg, d_keep, d_gc_out, d_taken;
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
+  DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
   cudaEvent_t ev[8]{};
@@ -1605,6 +1615,68 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
   else if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
   h->hasO = true;
+  return OE_OK;
+}
+
+int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* t) {
+  if (!h || !t || (n_rows > 0 && !rows)) return OE_ERR_INVALID;
+  if (!h->hasO) return h->fail(OE_ERR_STATE, "oe_update_offers: no resident offer table (oe_load_offers first)");
+  CU(cudaSetDevice(h->device));
+  const DevOffers& o = h->dof;
+  if (h->n_reserved > 0 || t->n_reserved > 0)
+    return h->fail(OE_ERR_STATE, "oe_update_offers: a table with a reserved side table cannot be patched in place; reload it with oe_load_offers");
+  if (n_rows < 0 || n_rows > o.N || t->n_offers != n_rows) return h->fail(OE_ERR_INVALID, "oe_update_offers: n_rows");
+  if (t->n_role_slots != o.S || t->n_scalar_kinds != o.K || t->n_port_ranges != o.R || t->n_mount_slots != o.D || t->n_attr_slots != o.A ||
+      t->n_rr_cols != o.Q || t->n_exec_slots != o.E)
+    return h->fail(OE_ERR_INVALID, "oe_update_offers: slot counts differ from the resident table");
+  if (n_rows == 0) return OE_OK;
+  if (!t->scalar || !t->scalar_present || !t->alloc_role || !t->agent_id || !t->hostname_id || !t->zone_id || !t->region_id ||
+      (o.R && !t->port_range) || (o.D && (!t->mount_size || !t->mount_profile)) || (o.A && !t->attr_id) || (o.Q && !t->rr_key) || (o.E && !t->exec_id))
+    return h->fail(OE_ERR_INVALID, "oe_update_offers: missing column");
+  for (int64_t k = 0; k < n_rows; ++k)
+    if (rows[k] < 0 || rows[k] >= o.N) return h->fail(OE_ERR_INVALID, "oe_update_offers: rows[%lld] = %lld is not a row of the resident table", (long long)k, (long long)rows[k]);
+  h->class_bits_fresh = h->cycle_done = false;
+  const size_t n = (size_t)n_rows;
+  // one staging buffer, column after column, each 8-byte aligned
+  const size_t slots8 = (size_t)o.S * o.K + o.D, slots4 = 1 + (size_t)o.S * o.R + o.D + 5 + o.A + o.Q + o.E;
+  CU(h->d_stage.ensure(n * (slots8 * 8 + slots4 * 4) + 64 * 16));
+  CU(h->d_stage_rows.ensure(n * 8));
+  CU(cudaMemcpyAsync(h->d_stage_rows.p, rows, n * 8, cudaMemcpyHostToDevice, h->stream));
+  const int64_t* d_rows = h->d_stage_rows.as<int64_t>();
+  unsigned char* cursor = h->d_stage.as<unsigned char>();
+  const oe_dict_sizes& dc = h->dict;
+  auto column = [&](auto* dst, const auto* src, int slots, int32_t lo, int32_t hi, int code) -> int {
+    using T = std::remove_pointer_t<decltype(dst)>;
+    if (slots <= 0) return 0;
+    T* st = reinterpret_cast<T*>(cursor);
+    const size_t bytes = n * (size_t)slots * sizeof(T);
+    cursor += (bytes + 15) / 16 * 16;
+    CU(cudaMemcpyAsync(st, src, bytes, cudaMemcpyHostToDevice, h->stream));
+    if constexpr (std::is_same_v<T, int32_t>) { if (code) check_ids(h, st, (int64_t)n * slots, lo, hi, code); }
+    const int64_t total = (int64_t)n * slots;
+    k_scatter_rows<T><<<(unsigned)((total + 255) / 256), 256, 0, h->stream>>>(dst, o.N, st, (int64_t)n, slots, d_rows);
+    return 0;
+  };
+  if (int rc = column(h->d_scalar.as<double>(), t->scalar, o.S * o.K, 0, 0, 0)) return rc;
+  if (int rc = column(h->d_present.as<uint32_t>(), t->scalar_present, 1, 0, 0, 0)) return rc;
+  if (o.R > 0) {
+    uint32_t* st = reinterpret_cast<uint32_t*>(cursor);
+    if (int rc = column(h->d_port.as<uint32_t>(), t->port_range, o.S * o.R, 0, 0, 0)) return rc;
+    k_validate_ranges<<<(unsigned)((n_rows + 255) / 256), 256, 0, h->stream>>>(st, n_rows, o.S, o.R, 18, h->d_err.as<int>());
+  }
+  if (int rc = column(h->d_msize.as<double>(), t->mount_size, o.D, 0, 0, 0)) return rc;
+  if (int rc = column(h->d_mprof.as<int32_t>(), t->mount_profile, o.D, -1, OE_MAX_PROFILES, 17)) return rc;
+  if (int rc = column(h->d_ocols[0].as<int32_t>(), t->alloc_role, 1, 0, 0, 0)) return rc;
+  if (int rc = column(h->d_ocols[1].as<int32_t>(), t->agent_id, 1, 0, std::max(dc.n_agents, 1), 11)) return rc;
+  if (int rc = column(h->d_ocols[2].as<int32_t>(), t->hostname_id, 1, 0, std::max(dc.n_hostnames, 1), 12)) return rc;
+  if (int rc = column(h->d_ocols[3].as<int32_t>(), t->zone_id, 1, -1, dc.n_zones, 13)) return rc;
+  if (int rc = column(h->d_ocols[4].as<int32_t>(), t->region_id, 1, -1, dc.n_regions, 14)) return rc;
+  if (int rc = column(h->d_oattr.as<int32_t>(), t->attr_id, o.A, -1, dc.n_attrs, 15)) return rc;
+  if (int rc = column(h->d_orr.as<int32_t>(), t->rr_key, o.Q, -1, dc.n_rr_values, 16)) return rc;
+  if (int rc = column(h->d_oexec.as<int32_t>(), t->exec_id, o.E, 0, 0, 0)) return rc;
+  CU(cudaGetLastError());
+  if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
+  else if (int rc = fetch_err_flag(h, "oe_update_offers")) { h->hasO = false; return rc; }  // the resident table may hold bad ids now
   return OE_OK;
 }
 

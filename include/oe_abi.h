@@ -366,6 +366,15 @@ typedef struct {
 int32_t oe_load_programs(oe_engine* h, const oe_program_table* t);
 int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t);
 int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t);
+/* Delta upload: replaces rows of the RESIDENT offer table in place.  Between two cycles only a few agents' offers change
+ * (the reference's queue takes what arrived and drops what was rescinded, S/framework/OfferQueue.java:46-85, and the
+ * evaluator sees the new list, S/framework/OfferProcessor.java:240-262); the host re-encodes those and sends them here
+ * instead of the whole table.  Row rows[k] (local row index of this engine, 0 <= rows[k] < n_offers, all distinct) receives
+ * row k of `values`, a table of n_rows rows with the same slot counts as the resident one (n_offers = n_rows; row_offset,
+ * n_offers_global and shard_rows are ignored).  A withdrawn offer is a row whose scalar_present is 0 and whose port ranges
+ * are all OE_PORT_EMPTY: nothing fits it.  Tables with a reserved side table (resident or in `values`) cannot be patched —
+ * OE_ERR_STATE, reload with oe_load_offers.  Dictionary ids are validated like those of a load.                          */
+int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* values);
 int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t);
 
 /* ------------------------------------------------------------------------------------------------------------------

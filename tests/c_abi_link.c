@@ -14,7 +14,7 @@ int main(void) {
   (void)oe_load_programs(h, NULL); (void)oe_load_tasks(h, NULL); (void)oe_load_offers(h, NULL); (void)oe_load_requirements(h, NULL);
   (void)oe_matrix_stride_words(h); (void)oe_feasibility(h, NULL, &st); (void)oe_class_feasibility(h, NULL, &st);
   (void)oe_evaluate_cycle(h, NULL, &st); (void)oe_stage_failures(h, 0, 0, NULL); (void)oe_unexpected_resources(h, NULL, 0, NULL, &n);
-  (void)oe_apply_launches(h); (void)oe_export_tasks(h, &n, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL);
+  (void)oe_update_offers(h, NULL, 0, NULL); (void)oe_apply_launches(h); (void)oe_export_tasks(h, &n, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL);
   (void)oe_device_buffer(h, OE_BUF_DECISIONS, NULL, &n); (void)oe_stream(h);
   (void)oe_first_fit_static(0, NULL, NULL, 0, 0, 0, NULL, 0, NULL, NULL, 0);
   oe_destroy(h);

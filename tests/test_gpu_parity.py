@@ -156,6 +156,58 @@ def test_async_loads_give_the_same_answers_and_still_validate():
     eng.close()
 
 
+def _patched(t, rows, src_rows):
+    """A copy of the tables whose offer rows `rows` hold what rows `src_rows` held."""
+    import copy
+    p = copy.copy(t)
+    p._keep = []
+    for name in abi.CycleTables.OFFER_COLUMNS:
+        col = getattr(t, name).copy()
+        col[..., rows] = getattr(t, name)[..., src_rows]
+        setattr(p, name, col)
+    return p
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_update_offers_equals_a_full_reload(engine, seed):
+    """oe_update_offers (delta upload of the rows that changed between two cycles) against loading the patched table whole."""
+    rng = np.random.default_rng(1000 + seed)
+    t = random_tables(seed, n_offers=int(rng.integers(2, 400)), with_reserved=False)
+    t.normalise()
+    n = t.n_offers
+    k = int(rng.integers(1, max(2, n // 3)))
+    rows = rng.choice(n, size=k, replace=False).astype(np.int64)     # unordered on purpose
+    src = rng.integers(0, n, size=k)                                 # what the re-offered agents look like now
+    want = _patched(t, rows, src)
+    orc = Oracle().load(want)
+    engine.load(t)
+    engine.evaluate_cycle()                                          # a cycle on the old table, then the delta
+    engine.update_offers(rows, t, value_rows=src)
+    engine.tables = want
+    assert np.array_equal(engine.feasibility()[0], orc.feasibility()[0])
+    assert engine.evaluate_cycle()[0].tobytes() == orc.evaluate_cycle()[0].tobytes()
+    orc.close()
+
+
+def test_update_offers_rejects_what_it_cannot_patch(engine):
+    t = random_tables(7, n_offers=60, with_reserved=False)
+    engine.load(t)
+    with pytest.raises(abi.EngineError):
+        engine.update_offers(np.array([60], np.int64), t, value_rows=[0])          # not a row of the resident table
+    bad = _patched(t, [3], [4])
+    bad.hostname_id = bad.hostname_id.copy()
+    bad.hostname_id[3] = 10 ** 6
+    with pytest.raises(abi.EngineError):
+        engine.update_offers(np.array([3], np.int64), bad)                          # ids are validated like those of a load
+    with pytest.raises(abi.EngineError):
+        engine.evaluate_cycle()                                                     # ... and the resident table is not trusted any more
+    r = random_tables(8, n_offers=60, with_reserved=True)
+    engine.load(r)
+    if r.reserved_begin is not None and len(r.reserved_id):
+        with pytest.raises(abi.EngineError):
+            engine.update_offers(np.array([1], np.int64), r)                        # a reserved side table cannot be patched in place
+
+
 def test_empty_inputs(engine):
     t = random_tables(5, n_offers=40, n_reqs=6, n_tasks=0)
     _compare_all(engine, t)
