@@ -1065,6 +1065,11 @@ struct oe_engine {
   int device = 0, rank = 0, world = 1;
   uint32_t flags = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t aux_stream = nullptr;  // lowest priority: K1x runs here beside the commit kernel (neither needs the other's output)
+  cudaStream_t hi_stream = nullptr;   // highest priority: the commit kernel, so that its one CTA is placed before K1x floods the SMs
+  cudaEvent_t ev_commit = nullptr;
+  bool fork_expand = false;           // evaluate_cycle -> run_commit: start K1x at the point where the commit kernel is launched
+  cudaEvent_t ev_fork = nullptr, ev_x0 = nullptr, ev_x1 = nullptr;
   bool own_stream = false;
   std::string err;
   int smem_optin = 0, commit_static_smem = 0, union_static_smem = 0;
@@ -1246,6 +1251,15 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
   if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&h->ev_side) != cudaSuccess) {
     g_create_error = "oe_create: side stream"; delete h; return OE_ERR_CUDA;
   }
+  {
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    if (cudaStreamCreateWithPriority(&h->aux_stream, cudaStreamNonBlocking, least) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&h->hi_stream, cudaStreamNonBlocking, greatest) != cudaSuccess || cudaEventCreate(&h->ev_fork) != cudaSuccess ||
+        cudaEventCreate(&h->ev_x0) != cudaSuccess || cudaEventCreate(&h->ev_x1) != cudaSuccess || cudaEventCreate(&h->ev_commit) != cudaSuccess) {
+      g_create_error = "oe_create: auxiliary streams"; delete h; return OE_ERR_CUDA;
+    }
+  }
   if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
@@ -1283,7 +1297,8 @@ void oe_destroy(oe_engine* h) {
                    &h->d_rkind, &h->d_rval, &h->d_req_row, &h->d_rtype, &h->d_rindex, &h->d_vcls, &h->d_vself_begin, &h->d_vself_rows,
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
-                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken};
+                   &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
+                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -1291,6 +1306,9 @@ void oe_destroy(oe_engine* h) {
   if (h->ev_variants) cudaEventDestroy(h->ev_variants);
   if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
   if (h->ev_side) cudaEventDestroy(h->ev_side);
+  if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
+  if (h->hi_stream) { cudaStreamSynchronize(h->hi_stream); cudaStreamDestroy(h->hi_stream); }
+  for (cudaEvent_t e : {h->ev_fork, h->ev_x0, h->ev_x1, h->ev_commit}) if (e) cudaEventDestroy(e);
   if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -2015,7 +2033,8 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
   return 0;
 }
 
-int run_expand(oe_engine* h, int64_t* launches) {
+int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr) {
+  if (!on) on = h->stream;
   const int64_t stride = h->stride();
   CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
   if (h->M > 0) {
@@ -2026,7 +2045,7 @@ int run_expand(oe_engine* h, int64_t* launches) {
     const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);
-    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, h->stream>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
+    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
                                                                          h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block);
     ++*launches;
     CU(cudaGetLastError());
@@ -2093,7 +2112,24 @@ int run_commit(oe_engine* h, int64_t* launches) {
     ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
     CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
     ua.order = h->d_order.as<int2>();
-    k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->stream>>>(ua);
+    if (h->fork_expand) {
+      // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
+      // kernel on the highest-priority stream, so that its single CTA (1024 threads x 64 registers: a whole SM) is placed
+      // while the SMs are still empty, K1x on the lowest-priority one, filling the other 147.  (Started any earlier, K1x
+      // occupies every SM and the commit CTA waits for the expansion to drain.)
+      h->fork_expand = false;
+      CU(cudaEventRecord(h->ev_fork, h->stream));
+      CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
+      k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->hi_stream>>>(ua);
+      CU(cudaEventRecord(h->ev_commit, h->hi_stream));
+      CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
+      CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+      if (int rc = run_expand(h, launches, h->aux_stream)) return rc;
+      CU(cudaEventRecord(h->ev_x1, h->aux_stream));
+      CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
+    } else {
+      k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->stream>>>(ua);
+    }
     ++*launches;
     CU(cudaGetLastError());
     k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
@@ -2231,6 +2267,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   if (int rc = ready(h, "oe_evaluate_cycle")) return rc;
   if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
+  bool expand_overlapped = false;
   CU(cudaEventRecord(h->ev[0], h->stream));
   if (h->world > 1) {
     // sharded: the caller ran oe_class_feasibility on every shard and gathered the rows into OE_BUF_CLASS_BITS_GLOBAL
@@ -2244,11 +2281,26 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     CU(cudaEventRecord(h->ev[1], h->stream));
     if (int rc = run_class_feasibility(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[2], h->stream));
-    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) if (int rc = run_expand(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[3], h->stream));
+    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
+      expand_overlapped = true;
+      CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));  // before the fork: an allocation would serialise the device
+      h->fork_expand = true;
+    }
   }
-  if (int rc = run_commit(h, &launches)) return rc;
+  if (int rc = run_commit(h, &launches)) { h->fork_expand = false; return rc; }
   CU(cudaEventRecord(h->ev[4], h->stream));
+  if (expand_overlapped) {
+    if (h->fork_expand) {  // the commit path had no fork point (no requirements, or more bit rows than the union path takes)
+      h->fork_expand = false;
+      CU(cudaEventRecord(h->ev_fork, h->stream));
+      CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
+      CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+      if (int rc = run_expand(h, &launches, h->aux_stream)) return rc;
+      CU(cudaEventRecord(h->ev_x1, h->aux_stream));
+    }
+    CU(cudaStreamWaitEvent(h->stream, h->ev_x1, 0));
+  }
   int n_placed = 0;
   if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaMemcpyAsync(&n_placed, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -2260,7 +2312,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     std::memset(stats, 0, sizeof *stats);
     stats->ms_counters = ms_between(h->ev[0], h->ev[1]);
     stats->ms_feasibility = ms_between(h->ev[1], h->ev[2]);
-    stats->ms_expand = ms_between(h->ev[2], h->ev[3]);
+    stats->ms_expand = expand_overlapped ? ms_between(h->ev_x0, h->ev_x1) : ms_between(h->ev[2], h->ev[3]);  // overlaps ms_commit
     stats->ms_commit = ms_between(h->ev[3], h->ev[4]);
     stats->ms_d2h = ms_between(h->ev[4], h->ev[5]);
     stats->ms_total = ms_between(h->ev[0], h->ev[5]);
