@@ -11,6 +11,7 @@
 //   K4  k_apply_launches                multi-cycle replay: placed pods → task rows
 //
 // There is no CPU fallback: every entry point needs a CUDA device and fails with an oe_status otherwise.
+#include <cuda_pipeline.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -672,6 +673,7 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS) k_commit(CommitArgs a) {
 // "still free" words; a requirement of row k ANDs them with row k's membership words (shared memory, written when a half is
 // loaded), takes the lowest set bit and clears it: a handful of ALU instructions, no collective, no memory write.
 #define OE_UNION_MAX_ROWS 32
+#define OE_RING 4   // list chunks of 32 entries a warp keeps in flight towards shared memory (cp.async), beyond its 64-entry window
 struct CommitMeta {
   int n_comp;
   int comp_of[OE_UNION_MAX_ROWS];   // row -> warp (component, folded onto 32 warps)
@@ -753,6 +755,7 @@ struct UnionArgs {
 __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs a) {
   extern __shared__ __align__(16) unsigned char commit_smem[];
   uint32_t* used = reinterpret_cast<uint32_t*>(commit_smem);   // claims made BEYOND a window (the window's own live in registers)
+  int2* rings = reinterpret_cast<int2*>(commit_smem + (a.used_words * 4 + 15) / 16 * 16);   // [warp][OE_RING][lane] (offer, mask)
   __shared__ CommitMeta meta;
   __shared__ int cnt[32][33];
   __shared__ int comp_begin[33];
@@ -826,8 +829,24 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
     const uint32_t* Mk = a.umask + a.ubase[warp];
     const int len = a.ulen[warp];
     int wpos = 0;  // list index of the first entry of half 0
-    int u0 = lane < len ? __ldg(L + lane) : -1, u1 = 32 + lane < len ? __ldg(L + 32 + lane) : -1, un = 64 + lane < len ? __ldg(L + 64 + lane) : -1;
-    uint32_t m0 = lane < len ? __ldg(Mk + lane) : 0u, m1 = 32 + lane < len ? __ldg(Mk + 32 + lane) : 0u, mn = 64 + lane < len ? __ldg(Mk + 64 + lane) : 0u;
+    int u0 = lane < len ? __ldg(L + lane) : -1, u1 = 32 + lane < len ? __ldg(L + 32 + lane) : -1;
+    uint32_t m0 = lane < len ? __ldg(Mk + lane) : 0u, m1 = 32 + lane < len ? __ldg(Mk + 32 + lane) : 0u;
+    // The list chunks after the window travel to shared memory asynchronously, OE_RING chunks ahead (one cp.async group per
+    // chunk; a lane copies, and later reads, only its own entry): when the matrix expansion runs beside this kernel a load
+    // takes several microseconds, far more than the 32 steps that a one-chunk-ahead register prefetch covers.
+    int2* ring = rings + warp * (OE_RING * 32);
+    auto fetch_chunk = [&](int chunk) {
+      int2* slot = ring + (chunk & (OE_RING - 1)) * 32 + lane;
+      const int idx = chunk * 32 + lane;
+      if (idx < len) {
+        __pipeline_memcpy_async(&slot->x, L + idx, 4);
+        __pipeline_memcpy_async(&slot->y, Mk + idx, 4);
+      } else {
+        *slot = make_int2(-1, 0);
+      }
+      __pipeline_commit();
+    };
+    for (int c = 2; c < 2 + OE_RING; ++c) fetch_chunk(c);
     uint32_t free0 = __ballot_sync(0xffffffffu, u0 >= 0), free1 = __ballot_sync(0xffffffffu, u1 >= 0);
     {
       uint2 mine = make_uint2(0u, 0u);
@@ -839,9 +858,11 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
       __syncwarp();
     }
     int2 nx = begin + lane < end ? a.order[begin + lane] : make_int2(0, 0);
+    int2 nx2 = begin + 32 + lane < end ? a.order[begin + 32 + lane] : make_int2(0, 0);
     for (int b0 = begin; b0 < end; b0 += 32) {
       const int my_req = nx.x, my_k = nx.y;                       // plan position b0 + lane
-      if (b0 + 32 + lane < end) nx = a.order[b0 + 32 + lane];     // a batch ahead of its use
+      nx = nx2;
+      if (b0 + 64 + lane < end) nx2 = a.order[b0 + 64 + lane];    // two batches ahead of its use
       const int cnt_b = min(32, end - b0);
       int my_o = -1;
       int my_pos = -1;  // window position taken by the requirement at b0 + lane; -2 = nothing of its row was free in the window
@@ -919,10 +940,12 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
           read_out();
           do {  // half 0 is used up: half 1 -> half 0, prefetched -> half 1
             u0 = u1; m0 = m1; free0 = free1;
-            u1 = un; m1 = mn;
+            __pipeline_wait_prior(OE_RING - 1);   // the oldest chunk in flight is the one that follows half 1
+            const int chunk = wpos / 32 + 2;
+            const volatile int* slot = reinterpret_cast<const volatile int*>(ring + (chunk & (OE_RING - 1)) * 32 + lane);
+            u1 = slot[0]; m1 = (uint32_t)slot[1];
+            fetch_chunk(chunk + OE_RING);         // into the slot just read
             wpos += 32;
-            un = wpos + 64 + lane < len ? __ldg(L + wpos + 64 + lane) : -1;
-            mn = wpos + 64 + lane < len ? __ldg(Mk + wpos + 64 + lane) : 0u;
             free1 = __ballot_sync(0xffffffffu, u1 >= 0 && !((vused[max(u1, 0) >> 5] >> (u1 & 31)) & 1u));
             uint32_t y = 0u;
             for (int q = 0; q < R; ++q) {
@@ -2073,7 +2096,8 @@ int run_commit(oe_engine* h, int64_t* launches) {
     return 0;
   }
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
-  if (rows <= OE_UNION_MAX_ROWS && (size_t)rb.total_words * 4 + 1024 <= (size_t)h->smem_optin - h->union_static_smem) {
+  const size_t union_smem = ((size_t)rb.total_words * 4 + 15) / 16 * 16 + (size_t)32 * OE_RING * 32 * sizeof(int2);
+  if (rows <= OE_UNION_MAX_ROWS && union_smem + 1024 <= (size_t)h->smem_optin - h->union_static_smem) {
     // ---- commit over union lists (see k_commit_union)
     const unsigned long long* adj = nullptr;
     if (rows > 1) {
@@ -2112,6 +2136,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
     ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
     CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
     ua.order = h->d_order.as<int2>();
+    bool materialized = false;
     if (h->fork_expand) {
       // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
       // kernel on the highest-priority stream, so that its single CTA (1024 threads x 64 registers: a whole SM) is placed
@@ -2120,7 +2145,11 @@ int run_commit(oe_engine* h, int64_t* launches) {
       h->fork_expand = false;
       CU(cudaEventRecord(h->ev_fork, h->stream));
       CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
-      k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->hi_stream>>>(ua);
+      k_commit_union<<<1, OE_COMMIT_THREADS, union_smem, h->hi_stream>>>(ua);
+      // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
+      // behind the expansion's grid
+      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+      materialized = true;
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
       CU(cudaEventRecord(h->ev_x0, h->aux_stream));
@@ -2128,11 +2157,11 @@ int run_commit(oe_engine* h, int64_t* launches) {
       CU(cudaEventRecord(h->ev_x1, h->aux_stream));
       CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
     } else {
-      k_commit_union<<<1, OE_COMMIT_THREADS, (size_t)rb.total_words * 4, h->stream>>>(ua);
+      k_commit_union<<<1, OE_COMMIT_THREADS, union_smem, h->stream>>>(ua);
     }
     ++*launches;
     CU(cudaGetLastError());
-    k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+    if (!materialized) k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
     ++*launches;
     CU(cudaGetLastError());
     return 0;

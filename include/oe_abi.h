@@ -350,7 +350,8 @@ typedef struct {
   float ms_h2d;          /* host→device copies issued by the last evaluate call (0 when tables were resident)    */
   float ms_counters;     /* K0: task table → per-key tallies                                                      */
   float ms_feasibility;  /* K1: offers × classes stage programs + rule programs                                   */
-  float ms_expand;       /* K1x: class bits → offers × requirements bit matrix                                    */
+  float ms_expand;       /* K1x: class bits → offers × requirements bit matrix (in oe_evaluate_cycle it runs BESIDE
+                            the commit: ms_expand and ms_commit + ms_d2h then overlap)                            */
   float ms_commit;       /* K2: ordered greedy commit + winner materialisation                                    */
   float ms_d2h;          /* device→host copy of the results                                                       */
   float ms_total;
