@@ -750,6 +750,7 @@ struct UnionArgs {
   oe_decision* dec;
   int2* order;
   int* n_placed;
+  long long* trace;          // optional (OE_COMMIT_TRACE=1): per warp {steps, cycles, slides, top-ups, deferred, searches beyond, prologue cycles}
 };
 
 __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs a) {
@@ -763,6 +764,8 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
   __shared__ int bcur[OE_UNION_MAX_ROWS];     // per (warp, local row): where a search beyond the window resumes
   __shared__ int placed_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const long long t_start = clock64();
+  int n_slides = 0, n_topups = 0, n_deferred = 0, n_searches = 0;
   for (int64_t k = tid; k < a.used_words; k += OE_COMMIT_THREADS) used[k] = 0u;
   for (int k = tid; k < (int)(sizeof(CommitMeta) / 4); k += OE_COMMIT_THREADS) reinterpret_cast<int*>(&meta)[k] = reinterpret_cast<const int*>(a.meta)[k];
   if (tid == 0) placed_s = 0;
@@ -819,6 +822,7 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
   __syncthreads();
   // ---- replay: warp = component
   int placed = 0;
+  const long long t_replay = clock64();
   const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
   if (begin < end) {
     volatile uint32_t* vused = reinterpret_cast<volatile uint32_t*>(used);
@@ -828,7 +832,8 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
     const int32_t* L = a.ucand + a.ubase[warp];
     const uint32_t* Mk = a.umask + a.ubase[warp];
     const int len = a.ulen[warp];
-    int wpos = 0;  // list index of the first entry of half 0
+    int rd = 64;          // list index of the first entry that is not in the window yet
+    int nf = 2 + OE_RING;  // next list chunk to send for
     int u0 = lane < len ? __ldg(L + lane) : -1, u1 = 32 + lane < len ? __ldg(L + 32 + lane) : -1;
     uint32_t m0 = lane < len ? __ldg(Mk + lane) : 0u, m1 = 32 + lane < len ? __ldg(Mk + 32 + lane) : 0u;
     // The list chunks after the window travel to shared memory asynchronously, OE_RING chunks ahead (one cp.async group per
@@ -847,16 +852,27 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
       __pipeline_commit();
     };
     for (int c = 2; c < 2 + OE_RING; ++c) fetch_chunk(c);
-    uint32_t free0 = __ballot_sync(0xffffffffu, u0 >= 0), free1 = __ballot_sync(0xffffffffu, u1 >= 0);
-    {
+    const volatile int* ring_flat = reinterpret_cast<const volatile int*>(ring);   // entry idx (< nf * 32) sits at [(idx & (OE_RING * 32 - 1)) * 2]
+    auto landed = [&](int upto) {   // entries up to list index `upto` are in shared memory, for every lane
+      const int newer = nf - (upto >> 5) - 1;   // groups sent for after the one that carries `upto`
+      __pipeline_wait_prior(newer < 0 ? 0 : newer > 7 ? 7 : newer);
+      __syncwarp();
+    };
+    auto advanced = [&]() {         // rd moved: chunks that lie wholly before it give their ring slots to the chunks OE_RING later
+      __syncwarp();
+      while (nf - OE_RING < (rd >> 5)) fetch_chunk(nf++);
+    };
+    auto membership = [&]() {       // rm[k] <- which entries of the two halves list row k
       uint2 mine = make_uint2(0u, 0u);
-      for (int k = 0; k < R; ++k) {
-        const uint32_t x = __ballot_sync(0xffffffffu, (m0 >> k) & 1u), y = __ballot_sync(0xffffffffu, (m1 >> k) & 1u);
-        if (lane == k) mine = make_uint2(x, y);
+      for (int q = 0; q < R; ++q) {
+        const uint32_t x = __ballot_sync(0xffffffffu, (m0 >> q) & 1u), y = __ballot_sync(0xffffffffu, (m1 >> q) & 1u);
+        if (lane == q) mine = make_uint2(x, y);
       }
       if (lane < R) rm[lane] = mine;
       __syncwarp();
-    }
+    };
+    uint32_t free0 = __ballot_sync(0xffffffffu, u0 >= 0), free1 = __ballot_sync(0xffffffffu, u1 >= 0);
+    membership();
     int2 nx = begin + lane < end ? a.order[begin + lane] : make_int2(0, 0);
     int2 nx2 = begin + 32 + lane < end ? a.order[begin + 32 + lane] : make_int2(0, 0);
     for (int b0 = begin; b0 < end; b0 += 32) {
@@ -871,31 +887,84 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
         const int o0 = __shfl_sync(0xffffffffu, u0, my_pos & 31), o1 = __shfl_sync(0xffffffffu, u1, my_pos & 31);
         if (my_pos >= 0) { my_o = my_pos < 32 ? o0 : o1; my_pos = -1; }
       };
-      // requirements whose row had nothing free inside the window, in plan order: they look beyond it, from where the last
-      // such search of the row ended
-      auto beyond = [&]() {
-        for (uint32_t pend = __ballot_sync(0xffffffffu, my_pos == -2); pend; pend &= pend - 1) {
+      // The window is topped up to 64 FREE entries: what is still free moves to the front (order kept), the list supplies the
+      // rest.  Needed when the free entries left in half 0 are ones that the rows asking now do not list: half 0 never empties,
+      // the window stops moving, and row after row finds nothing in it.
+      auto compact = [&]() {
+        const int n0 = __popc(free0), n1 = __popc(free1), keep = n0 + n1, n_new = 64 - keep;
+        ++n_topups;
+        landed(rd + n_new - 1);
+        int nu[2];
+        uint32_t nm[2];
+        bool nfree[2];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int d = hh * 32 + lane;
+          const int s0 = d < n0 ? (int)__fns(free0, 0, d + 1) : 0, s1 = (d >= n0 && d < keep) ? (int)__fns(free1, 0, d - n0 + 1) : 0;
+          const int ua = __shfl_sync(0xffffffffu, u0, s0), ub = __shfl_sync(0xffffffffu, u1, s1);
+          const uint32_t ma = __shfl_sync(0xffffffffu, m0, s0), mb = __shfl_sync(0xffffffffu, m1, s1);
+          const int e = ((rd + d - keep) & (OE_RING * 32 - 1)) * 2;
+          const int un_ = d >= keep ? ring_flat[e] : -1;
+          const uint32_t mn_ = d >= keep ? (uint32_t)ring_flat[e + 1] : 0u;
+          nu[hh] = d < n0 ? ua : d < keep ? ub : un_;
+          nm[hh] = d < n0 ? ma : d < keep ? mb : mn_;
+          nfree[hh] = d < keep || (un_ >= 0 && !((vused[max(un_, 0) >> 5] >> (un_ & 31)) & 1u));
+        }
+        u0 = nu[0]; m0 = nm[0]; u1 = nu[1]; m1 = nm[1];
+        free0 = __ballot_sync(0xffffffffu, nfree[0]);
+        free1 = __ballot_sync(0xffffffffu, nfree[1]);
+        rd += n_new;
+        advanced();
+        membership();
+      };
+      // Requirements whose row had nothing free inside the window, in plan order.  First the window is topped up; if the row
+      // still finds nothing, the list is searched beyond the window, from where the last such search of the row ended.
+      auto serve_deferred = [&]() {
+        uint32_t pend = __ballot_sync(0xffffffffu, my_pos == -2);
+        if (!pend) return;
+        read_out();
+        if (rd < len && __popc(free0) + __popc(free1) < 64) compact();
+        for (; pend; pend &= pend - 1) {
           const int i = __ffs(pend) - 1;
           const int k = __shfl_sync(0xffffffffu, my_k, i);
-          int start = max(bc[k], wpos + 64);
+          const uint2 r = rm[k];
+          const uint32_t a0 = r.x & free0, a1 = r.y & free1;
           int o = -1;
-          while (start < len) {
-            const int idx = start + lane;
-            const int u = idx < len ? __ldg(L + idx) : -1;
-            const uint32_t m = idx < len ? __ldg(Mk + idx) : 0u;
-            const bool ok = ((m >> k) & 1u) && !((vused[max(u, 0) >> 5] >> (u & 31)) & 1u);
-            const uint32_t b = __ballot_sync(0xffffffffu, ok);
-            if (b) {
-              const int p = __ffs(b) - 1;
-              o = __shfl_sync(0xffffffffu, u, p);
-              if (lane == p) atomicOr(&used[u >> 5], 1u << (u & 31));
-              start += p + 1;
-              break;
+          ++n_deferred;
+          if (a0 | a1) {
+            const int p = __ffs(a0 ? a0 : a1) - 1;
+            const int o0 = __shfl_sync(0xffffffffu, u0, p), o1 = __shfl_sync(0xffffffffu, u1, p);
+            o = a0 ? o0 : o1;
+            if (a0) free0 ^= 1u << p; else free1 ^= 1u << p;
+          } else {
+            int start = max(bc[k], rd);
+            ++n_searches;
+            __pipeline_wait_prior(0);
+            __syncwarp();
+            while (start < len) {
+              const int chunk = start >> 5, first = start & 31, idx = chunk * 32 + lane;
+              int u = -1;
+              uint32_t m = 0u;
+              if (chunk < nf) {
+                const int e = (idx & (OE_RING * 32 - 1)) * 2;
+                u = ring_flat[e]; m = (uint32_t)ring_flat[e + 1];
+              } else if (idx < len) {
+                u = __ldg(L + idx); m = __ldg(Mk + idx);
+              }
+              const bool ok = lane >= first && u >= 0 && ((m >> k) & 1u) && !((vused[max(u, 0) >> 5] >> (u & 31)) & 1u);
+              const uint32_t b = __ballot_sync(0xffffffffu, ok);
+              if (b) {
+                const int p = __ffs(b) - 1;
+                o = __shfl_sync(0xffffffffu, u, p);
+                if (lane == p) atomicOr(&used[u >> 5], 1u << (u & 31));
+                start = chunk * 32 + p + 1;
+                break;
+              }
+              start = (chunk + 1) * 32;
             }
-            start += 32;
+            if (lane == 0) bc[k] = min(start, len);
+            __syncwarp();
           }
-          if (lane == 0) bc[k] = min(start, len);
-          __syncwarp();
           if (lane == i) { my_o = o; my_pos = -1; }
           placed += o >= 0;
         }
@@ -935,17 +1004,17 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
               : "r"(lane), "r"(both), "r"(bit0), "r"(none), "r"(i));
           placed += both != 0u;
         }
-        if (free0 == 0u && wpos < len) {
-          beyond();
+        serve_deferred();
+        if (free0 == 0u && rd < len + 64) {
           read_out();
-          do {  // half 0 is used up: half 1 -> half 0, prefetched -> half 1
+          do {  // half 0 is used up: half 1 -> half 0, the next 32 list entries -> half 1
+            ++n_slides;
             u0 = u1; m0 = m1; free0 = free1;
-            __pipeline_wait_prior(OE_RING - 1);   // the oldest chunk in flight is the one that follows half 1
-            const int chunk = wpos / 32 + 2;
-            const volatile int* slot = reinterpret_cast<const volatile int*>(ring + (chunk & (OE_RING - 1)) * 32 + lane);
-            u1 = slot[0]; m1 = (uint32_t)slot[1];
-            fetch_chunk(chunk + OE_RING);         // into the slot just read
-            wpos += 32;
+            landed(rd + 31);
+            const int e = ((rd + lane) & (OE_RING * 32 - 1)) * 2;
+            u1 = ring_flat[e]; m1 = (uint32_t)ring_flat[e + 1];
+            rd += 32;
+            advanced();
             free1 = __ballot_sync(0xffffffffu, u1 >= 0 && !((vused[max(u1, 0) >> 5] >> (u1 & 31)) & 1u));
             uint32_t y = 0u;
             for (int q = 0; q < R; ++q) {
@@ -954,13 +1023,18 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
             }
             if (lane < R) rm[lane] = make_uint2(rm[lane].y, y);
             __syncwarp();
-          } while (free0 == 0u && wpos < len);
+          } while (free0 == 0u && rd < len + 64);
         }
       }
-      beyond();
+      serve_deferred();
       read_out();
       if (lane < cnt_b) a.dec[my_req].offer_row = my_o;
     }
+  }
+  if (a.trace && lane == 0) {
+    long long* d = a.trace + warp * 8;
+    d[0] = warp < n_comp ? comp_begin[warp + 1] - comp_begin[warp] : 0; d[1] = clock64() - t_replay; d[2] = n_slides; d[3] = n_topups; d[4] = n_deferred;
+    d[5] = n_searches; d[6] = t_replay - t_start;
   }
   if (lane == 0 && placed) atomicAdd(&placed_s, placed);
   __syncthreads();
@@ -2136,6 +2210,12 @@ int run_commit(oe_engine* h, int64_t* launches) {
     ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
     CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
     ua.order = h->d_order.as<int2>();
+    static const bool trace_on = getenv("OE_COMMIT_TRACE") != nullptr;   // debugging aid (tools/commit_probe.py): per-warp counters on stderr
+    if (trace_on) {
+      CU(h->d_dbg.ensure(32 * 8 * sizeof(long long)));
+      CU(cudaMemsetAsync(h->d_dbg.p, 0, 32 * 8 * sizeof(long long), h->stream));
+      ua.trace = h->d_dbg.as<long long>();
+    }
     bool materialized = false;
     if (h->fork_expand) {
       // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
@@ -2164,6 +2244,15 @@ int run_commit(oe_engine* h, int64_t* launches) {
     if (!materialized) k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
     ++*launches;
     CU(cudaGetLastError());
+    if (trace_on) {
+      long long d[32 * 8];
+      CU(cudaMemcpyAsync(d, ua.trace, sizeof d, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaStreamSynchronize(h->stream));
+      for (int w = 0; w < 32; ++w)
+        if (d[w * 8])
+          fprintf(stderr, "commit trace: warp %2d  %6lld requirements  %8lld cycles  %4lld slides  %4lld top-ups  %5lld deferred  %5lld searches beyond  (prologue %lld cycles)\n",
+                  w, d[w * 8], d[w * 8 + 1], d[w * 8 + 2], d[w * 8 + 3], d[w * 8 + 4], d[w * 8 + 5], d[w * 8 + 6]);
+    }
     return 0;
   }
   // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
