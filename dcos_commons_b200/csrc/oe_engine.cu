@@ -749,86 +749,101 @@ struct UnionArgs {
   int64_t M;
   oe_decision* dec;
   int2* order;
+  const int* comp_begin;     // [33] from k_sort_scatter
   int* n_placed;
   long long* trace;          // optional (OE_COMMIT_TRACE=1): per warp {steps, cycles, slides, top-ups, deferred, searches beyond, prologue cycles}
 };
 
-__global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs a) {
+// K2a: stable counting sort of the requirements by component, two small multi-CTA kernels: per-block histograms, then every
+// block ranks its own chunk (tiles of 256 requirements, in order) behind the blocks before it.  order[] = (requirement, local
+// row) grouped by component, plan order kept inside a group; comp_begin[c] = where component c starts.
+#define OE_SORT_BLOCKS 64
+__global__ void __launch_bounds__(256) k_sort_hist(const int32_t* __restrict__ req_row, int64_t M, const CommitMeta* __restrict__ meta,
+                                                   int* __restrict__ hist) {
+  __shared__ int h[32];
+  __shared__ int comp_of[OE_UNION_MAX_ROWS];
+  if (threadIdx.x < 32) { h[threadIdx.x] = 0; comp_of[threadIdx.x] = meta->comp_of[threadIdx.x]; }
+  __syncthreads();
+  const int64_t chunk = ((M + OE_SORT_BLOCKS - 1) / OE_SORT_BLOCKS + 255) / 256 * 256;
+  const int64_t lo = min(M, (int64_t)blockIdx.x * chunk), hi = min(M, lo + chunk);
+  const int lane = threadIdx.x & 31;
+  for (int64_t j0 = lo; j0 < hi; j0 += 256) {
+    const int64_t j = j0 + threadIdx.x;
+    const int c = j < hi ? comp_of[req_row[j]] : 32 + lane;   // past the end: a group of its own, not counted
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32 && lane == __ffs(same) - 1) atomicAdd(&h[c], __popc(same));
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) hist[blockIdx.x * 32 + threadIdx.x] = h[threadIdx.x];
+}
+__global__ void __launch_bounds__(256) k_sort_scatter(const int32_t* __restrict__ req_row, int64_t M, const CommitMeta* __restrict__ meta,
+                                                      const int* __restrict__ hist, int2* __restrict__ order, int* __restrict__ comp_begin_out) {
+  __shared__ int run[32];          // next free slot of every component for this block
+  __shared__ int wc[8][32];        // per warp of the tile: requirements of every component
+  __shared__ int comp_of[OE_UNION_MAX_ROWS], lrow[OE_UNION_MAX_ROWS];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid < 32) {
+    comp_of[tid] = meta->comp_of[tid]; lrow[tid] = meta->lrow[tid];
+    int before = 0, total = 0;   // of component `tid`: in the blocks before this one / in all blocks
+    for (int b = 0; b < OE_SORT_BLOCKS; ++b) { const int v = hist[b * 32 + tid]; total += v; if (b < (int)blockIdx.x) before += v; }
+    int begin = total;           // exclusive scan of the totals over the components
+    for (int d = 1; d < 32; d <<= 1) { const int n = __shfl_up_sync(0xffffffffu, begin, d); if (lane >= d) begin += n; }
+    begin -= total;
+    run[tid] = begin + before;
+    if (blockIdx.x == 0) { comp_begin_out[tid] = begin; if (tid == 31) comp_begin_out[32] = begin + total; }
+  }
+  __syncthreads();
+  const int64_t chunk = ((M + OE_SORT_BLOCKS - 1) / OE_SORT_BLOCKS + 255) / 256 * 256;
+  const int64_t lo = min(M, (int64_t)blockIdx.x * chunk), hi = min(M, lo + chunk);
+  for (int64_t j0 = lo; j0 < hi; j0 += 256) {
+    const int64_t j = j0 + tid;
+    const int row = j < hi ? req_row[j] : 0;
+    const int c = j < hi ? comp_of[row] : 32 + lane;
+    wc[warp][lane] = 0;
+    __syncwarp();
+    const uint32_t same = __match_any_sync(0xffffffffu, c);
+    if (c < 32 && lane == __ffs(same) - 1) wc[warp][c] = __popc(same);
+    __syncthreads();
+    if (c < 32) {
+      int at = run[c] + __popc(same & ((1u << lane) - 1u));
+      for (int w = 0; w < warp; ++w) at += wc[w][c];
+      order[at] = make_int2((int)j, lrow[row]);
+    }
+    __syncthreads();
+    if (tid < 32) { int add = 0; for (int w = 0; w < 8; ++w) add += wc[w][tid]; run[tid] += add; }
+    __syncthreads();
+  }
+}
+
+// K2: one CTA of one warp per component, each on an SM of its own (a lone warp retires a dependent instruction every few cycles;
+// 23 such warps on ONE SM compete for its four schedulers and each runs at less than half that rate).
+__global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
   extern __shared__ __align__(16) unsigned char commit_smem[];
   uint32_t* used = reinterpret_cast<uint32_t*>(commit_smem);   // claims made BEYOND a window (the window's own live in registers)
-  int2* rings = reinterpret_cast<int2*>(commit_smem + (a.used_words * 4 + 15) / 16 * 16);   // [warp][OE_RING][lane] (offer, mask)
+  int2* rings = reinterpret_cast<int2*>(commit_smem + (a.used_words * 4 + 15) / 16 * 16);   // [OE_RING][lane] (offer, mask)
   __shared__ CommitMeta meta;
-  __shared__ int cnt[32][33];
-  __shared__ int comp_begin[33];
-  __shared__ uint2 rmem[OE_UNION_MAX_ROWS];   // per (warp, local row): which entries of the two window halves list the row
-  __shared__ int bcur[OE_UNION_MAX_ROWS];     // per (warp, local row): where a search beyond the window resumes
-  __shared__ int placed_s;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  __shared__ uint2 rmem[OE_UNION_MAX_ROWS];   // per local row: which entries of the two window halves list the row
+  __shared__ int bcur[OE_UNION_MAX_ROWS];     // per local row: where a search beyond the window resumes
+  const int lane = threadIdx.x, warp = blockIdx.x;   // "warp" = component
   const long long t_start = clock64();
   int n_slides = 0, n_topups = 0, n_deferred = 0, n_searches = 0;
-  for (int64_t k = tid; k < a.used_words; k += OE_COMMIT_THREADS) used[k] = 0u;
-  for (int k = tid; k < (int)(sizeof(CommitMeta) / 4); k += OE_COMMIT_THREADS) reinterpret_cast<int*>(&meta)[k] = reinterpret_cast<const int*>(a.meta)[k];
-  if (tid == 0) placed_s = 0;
-  if (tid < OE_UNION_MAX_ROWS) bcur[tid] = 0;
-  __syncthreads();
-  const int n_comp = meta.n_comp;
-  // ---- stable counting sort of the requirements by component (see k_commit)
-  const int64_t chunk = ((a.M + 31) / 32 + 31) / 32 * 32;
-  const int64_t j_lo = min(a.M, (int64_t)warp * chunk), j_hi = min(a.M, j_lo + chunk);
-  cnt[lane][warp] = 0;
+  for (int k = lane; k < (int)(sizeof(CommitMeta) / 4); k += 32) reinterpret_cast<int*>(&meta)[k] = reinterpret_cast<const int*>(a.meta)[k];
   __syncwarp();
-  // (four batches' rows are fetched before any is used: one L2 round trip per four batches instead of one per batch)
-  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 128) {
-    int rows4[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) rows4[q] = j0 + q * 32 + lane < j_hi ? a.req_row[j0 + q * 32 + lane] : -1;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int c = rows4[q] >= 0 ? meta.comp_of[rows4[q]] : 32 + lane;
-      const uint32_t same = __match_any_sync(0xffffffffu, c);
-      if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
-      __syncwarp();
-    }
-  }
-  __syncthreads();
-  if (tid < n_comp) {
-    int run = 0;
-    for (int w = 0; w < 32; ++w) { const int v = cnt[tid][w]; cnt[tid][w] = run; run += v; }
-    cnt[tid][32] = run;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    int run = 0;
-    for (int c = 0; c < n_comp; ++c) { comp_begin[c] = run; run += cnt[c][32]; }
-    comp_begin[n_comp] = run;
-  }
-  __syncthreads();
-  for (int64_t j0 = j_lo; j0 < j_hi; j0 += 128) {
-    int rows4[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) rows4[q] = j0 + q * 32 + lane < j_hi ? a.req_row[j0 + q * 32 + lane] : -1;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int row = rows4[q];
-      const int c = row >= 0 ? meta.comp_of[row] : 32 + lane;
-      const uint32_t same = __match_any_sync(0xffffffffu, c);
-      if (c < 32)
-        a.order[comp_begin[c] + cnt[c][warp] + __popc(same & ((1u << lane) - 1u))] = make_int2((int)(j0 + q * 32 + lane), meta.lrow[row]);
-      __syncwarp();
-      if (c < 32 && lane == __ffs(same) - 1) cnt[c][warp] += __popc(same);
-      __syncwarp();
-    }
-  }
-  __syncthreads();
+  const int n_comp = meta.n_comp;
+  if (warp >= n_comp) return;
+  for (int64_t k = lane; k < (a.used_words + 3) / 4; k += 32) reinterpret_cast<uint4*>(used)[k] = make_uint4(0u, 0u, 0u, 0u);
+  bcur[lane] = 0;
+  __syncwarp();
+  const int* comp_begin = a.comp_begin;
   // ---- replay: warp = component
   int placed = 0;
   const long long t_replay = clock64();
-  const int begin = warp < n_comp ? comp_begin[warp] : 0, end = warp < n_comp ? comp_begin[warp + 1] : 0;
+  const int begin = comp_begin[warp], end = comp_begin[warp + 1];
   if (begin < end) {
     volatile uint32_t* vused = reinterpret_cast<volatile uint32_t*>(used);
     const int R = meta.wrows[warp];
-    uint2* rm = rmem + meta.woff[warp];
-    int* bc = bcur + meta.woff[warp];
+    uint2* rm = rmem;
+    int* bc = bcur;
     const int32_t* L = a.ucand + a.ubase[warp];
     const uint32_t* Mk = a.umask + a.ubase[warp];
     const int len = a.ulen[warp];
@@ -839,7 +854,7 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
     // The list chunks after the window travel to shared memory asynchronously, OE_RING chunks ahead (one cp.async group per
     // chunk; a lane copies, and later reads, only its own entry): when the matrix expansion runs beside this kernel a load
     // takes several microseconds, far more than the 32 steps that a one-chunk-ahead register prefetch covers.
-    int2* ring = rings + warp * (OE_RING * 32);
+    int2* ring = rings;
     auto fetch_chunk = [&](int chunk) {
       int2* slot = ring + (chunk & (OE_RING - 1)) * 32 + lane;
       const int idx = chunk * 32 + lane;
@@ -1033,12 +1048,10 @@ __global__ void __launch_bounds__(OE_COMMIT_THREADS, 1) k_commit_union(UnionArgs
   }
   if (a.trace && lane == 0) {
     long long* d = a.trace + warp * 8;
-    d[0] = warp < n_comp ? comp_begin[warp + 1] - comp_begin[warp] : 0; d[1] = clock64() - t_replay; d[2] = n_slides; d[3] = n_topups; d[4] = n_deferred;
+    d[0] = end - begin; d[1] = clock64() - t_replay; d[2] = n_slides; d[3] = n_topups; d[4] = n_deferred;
     d[5] = n_searches; d[6] = t_replay - t_start;
   }
-  if (lane == 0 && placed) atomicAdd(&placed_s, placed);
-  __syncthreads();
-  if (tid == 0) *a.n_placed = placed_s;
+  if (lane == 0 && placed) atomicAdd(a.n_placed, placed);
 }
 
 // K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
@@ -1217,6 +1230,7 @@ struct oe_engine {
   DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj, d_dbg, d_keep, d_gc_out, d_taken;
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
+  DevBuf d_sort_hist, d_comp_begin;
   DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -1395,7 +1409,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
-                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows};
+                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin};
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -2170,7 +2184,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
     return 0;
   }
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
-  const size_t union_smem = ((size_t)rb.total_words * 4 + 15) / 16 * 16 + (size_t)32 * OE_RING * 32 * sizeof(int2);
+  const size_t union_smem = ((size_t)rb.total_words * 4 + 15) / 16 * 16 + (size_t)OE_RING * 32 * sizeof(int2);
   if (rows <= OE_UNION_MAX_ROWS && union_smem + 1024 <= (size_t)h->smem_optin - h->union_static_smem) {
     // ---- commit over union lists (see k_commit_union)
     const unsigned long long* adj = nullptr;
@@ -2210,6 +2224,13 @@ int run_commit(oe_engine* h, int64_t* launches) {
     ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
     CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
     ua.order = h->d_order.as<int2>();
+    CU(h->d_sort_hist.ensure((size_t)OE_SORT_BLOCKS * 32 * sizeof(int)));
+    CU(h->d_comp_begin.ensure(33 * sizeof(int)));
+    k_sort_hist<<<OE_SORT_BLOCKS, 256, 0, h->stream>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>());
+    k_sort_scatter<<<OE_SORT_BLOCKS, 256, 0, h->stream>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>(), ua.order, h->d_comp_begin.as<int>());
+    *launches += 2;
+    ua.comp_begin = h->d_comp_begin.as<int>();
+    CU(cudaMemsetAsync(ua.n_placed, 0, sizeof(int), h->stream));
     static const bool trace_on = getenv("OE_COMMIT_TRACE") != nullptr;   // debugging aid (tools/commit_probe.py): per-warp counters on stderr
     if (trace_on) {
       CU(h->d_dbg.ensure(32 * 8 * sizeof(long long)));
@@ -2225,7 +2246,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
       h->fork_expand = false;
       CU(cudaEventRecord(h->ev_fork, h->stream));
       CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
-      k_commit_union<<<1, OE_COMMIT_THREADS, union_smem, h->hi_stream>>>(ua);
+      k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
       // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
       // behind the expansion's grid
       k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
@@ -2237,7 +2258,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
       CU(cudaEventRecord(h->ev_x1, h->aux_stream));
       CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
     } else {
-      k_commit_union<<<1, OE_COMMIT_THREADS, union_smem, h->stream>>>(ua);
+      k_commit_union<<<32, 32, union_smem, h->stream>>>(ua);
     }
     ++*launches;
     CU(cudaGetLastError());
