@@ -2240,9 +2240,9 @@ int run_commit(oe_engine* h, int64_t* launches) {
     bool materialized = false;
     if (h->fork_expand) {
       // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
-      // kernel on the highest-priority stream, so that its single CTA (1024 threads x 64 registers: a whole SM) is placed
-      // while the SMs are still empty, K1x on the lowest-priority one, filling the other 147.  (Started any earlier, K1x
-      // occupies every SM and the commit CTA waits for the expansion to drain.)
+      // kernel on the highest-priority stream, so that its CTAs (one per component, each with the claimed bitmap in shared
+      // memory) are placed while the SMs are still empty, K1x on the lowest-priority one, filling the rest.  (Started any
+      // earlier, K1x occupies every SM and the commit waits for the expansion to drain.)
       h->fork_expand = false;
       CU(cudaEventRecord(h->ev_fork, h->stream));
       CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
