@@ -349,6 +349,24 @@ def run_engine(args):
            "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
            "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"]}
 
+    # the same cycle when the caller only wants the decisions (what the scheduler adapter asks for): no matrix is written
+    if world == 1:
+        eng3 = Engine(device=local_rank, flags=abi.OE_CFG_ASYNC_LOADS)
+
+        def cycle_decisions_only():
+            eng3.tables = pt
+            eng3.load_programs(pt); eng3.load_tasks(pt); eng3.load_offers(pt, lo, hi, shard_rows); eng3.load_requirements(pt)
+            return eng3.evaluate_cycle_into(out.data_ptr())
+        for _ in range(2):
+            cycle_decisions_only()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            st3 = cycle_decisions_only()
+        e2e["decisions_only"] = {"cycle_latency_ms": 1e3 * (time.perf_counter() - t0) / e2e_steps,
+                                 "device_ms": {k: st3[k] for k in ("ms_counters", "ms_feasibility", "ms_commit", "ms_d2h")},
+                                 "note": "same tables and copies, OE_CFG_MATERIALIZE_MATRIX off: K0 + K1 + commit, the N x M matrix stays factored"}
+        eng3.close()
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
