@@ -1231,6 +1231,8 @@ struct oe_engine {
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
   DevBuf d_sort_hist, d_comp_begin;
+  std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
+  std::vector<int32_t> h_vcand;
   DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -1834,33 +1836,56 @@ int rebuild_variants(oe_engine* h) {
       if (int rc = add_variant(j, h->h_self_rows.data() + b, e - b)) return rc;
     }
   } else if (T > 0 && std::any_of(h->class_self_sensitive.begin(), h->class_self_sensitive.end(), [](uint8_t x) { return x != 0; })) {
-    // open-addressing table pod key (type, index) -> chain of task rows; no per-entry allocation
-    size_t cap = 16;
-    while (cap < (size_t)T * 2) cap <<= 1;
-    const uint64_t EMPTY = ~0ull;
-    std::vector<uint64_t> keys(cap, EMPTY);
-    std::vector<int32_t> head(cap, -1), next((size_t)T, -1);
-    auto slot_of = [&](uint64_t key) {
-      size_t q = (size_t)((key * 0x9E3779B97F4A7C15ull) >> 17) & (cap - 1);
-      while (keys[q] != EMPTY && keys[q] != key) q = (q + 1) & (cap - 1);
-      return q;
-    };
-    for (int64_t r = T - 1; r >= 0; --r) {  // descending, so that every chain lists its rows in ascending order
-      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
-      const uint64_t key = ((uint64_t)(uint32_t)h->h_ttype[r] << 32) | (uint32_t)h->h_tindex[r];
-      const size_t q = slot_of(key);
-      keys[q] = key;
-      next[(size_t)r] = head[q];
-      head[q] = (int32_t)r;
-    }
-    std::vector<int32_t> chain;
+    // Which deployed tasks share (pod type, index) with a requirement of this cycle?  Usually very few (new instances) or all
+    // of them (a rolling restart).  A bit filter over the requirements' keys first discards the tasks that match nothing —
+    // it is small enough to stay in cache, whereas a table over all tasks costs a cache miss per task and per requirement —
+    // then an open-addressing table pod key -> chain of task rows is built over the tasks that are left.
+    auto key_of = [](int32_t type, int32_t index) { return ((uint64_t)(uint32_t)type << 32) | (uint32_t)index; };
+    auto mix = [](uint64_t key) { return (key * 0x9E3779B97F4A7C15ull) >> 17; };
+    size_t fbits = 1u << 16;
+    while (fbits < (size_t)M * 32 && fbits < (1u << 24)) fbits <<= 1;
+    std::vector<uint64_t>& filter = h->h_vfilter;
+    filter.assign(fbits / 64, 0ull);
     for (int64_t j = 0; j < M; ++j) {
       if (!h->class_self_sensitive[h->h_class[j]]) continue;
-      const size_t q = slot_of(((uint64_t)(uint32_t)h->h_rtype[j] << 32) | (uint32_t)h->h_rindex[j]);
-      if (keys[q] == EMPTY) continue;
-      chain.clear();
-      for (int32_t r = head[q]; r >= 0; r = next[(size_t)r]) chain.push_back(r);
-      if (int rc = add_variant(j, chain.data(), (int)chain.size())) return rc;
+      const uint64_t q = mix(key_of(h->h_rtype[j], h->h_rindex[j])) & (fbits - 1);
+      filter[q >> 6] |= 1ull << (q & 63);
+    }
+    std::vector<int32_t>& cand = h->h_vcand;  // task rows that may match a requirement, ascending
+    cand.clear();
+    for (int64_t r = 0; r < T; ++r) {
+      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
+      const uint64_t q = mix(key_of(h->h_ttype[r], h->h_tindex[r])) & (fbits - 1);
+      if ((filter[q >> 6] >> (q & 63)) & 1ull) cand.push_back((int32_t)r);
+    }
+    if (!cand.empty()) {
+      size_t cap = 16;
+      while (cap < cand.size() * 2) cap <<= 1;
+      const uint64_t EMPTY = ~0ull;
+      std::vector<uint64_t> keys(cap, EMPTY);
+      std::vector<int32_t> head(cap, -1), next(cand.size(), -1);   // chains hold positions in cand[]
+      auto slot_of = [&](uint64_t key) {
+        size_t q = (size_t)mix(key) & (cap - 1);
+        while (keys[q] != EMPTY && keys[q] != key) q = (q + 1) & (cap - 1);
+        return q;
+      };
+      for (int64_t c = (int64_t)cand.size() - 1; c >= 0; --c) {  // descending, so that every chain lists its rows in ascending order
+        const int32_t r = cand[(size_t)c];
+        const uint64_t key = key_of(h->h_ttype[r], h->h_tindex[r]);
+        const size_t q = slot_of(key);
+        keys[q] = key;
+        next[(size_t)c] = head[q];
+        head[q] = (int32_t)c;
+      }
+      std::vector<int32_t> chain;
+      for (int64_t j = 0; j < M; ++j) {
+        if (!h->class_self_sensitive[h->h_class[j]]) continue;
+        const size_t q = slot_of(key_of(h->h_rtype[j], h->h_rindex[j]));
+        if (keys[q] == EMPTY) continue;
+        chain.clear();
+        for (int32_t c = head[q]; c >= 0; c = next[(size_t)c]) chain.push_back(cand[(size_t)c]);
+        if (int rc = add_variant(j, chain.data(), (int)chain.size())) return rc;
+      }
     }
   }
   h->V = (int)vcls.size();
