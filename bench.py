@@ -316,16 +316,36 @@ def run_engine(args):
         host_ms[name] = host_ms.get(name, 0.0) + 1e3 * (time.perf_counter() - t0)
         return r
 
+    exchange = None
+
     def cycle():
         eng2.tables = pt
         timed("load_programs", lambda: eng2.load_programs(pt))
         timed("load_tasks", lambda: eng2.load_tasks(pt))
         timed("load_offers", lambda: eng2.load_offers(pt, lo, hi, shard_rows))
         timed("load_requirements", lambda: eng2.load_requirements(pt))
-        if world > 1:
+        if world > 1 and exchange == "nccl all-gather":
             eng2.feasibility(fetch=False)                 # K0 + K1 + K1x on this rank's shard
             sharded.gather_class_bits(eng2, dist)         # the one exchange step: class rows of every shard
-        return timed("evaluate_cycle", lambda: eng2.evaluate_cycle_into(out.data_ptr()))   # K3 + K2 (replayed identically on every rank) + D2H
+        # peers attached: the pass publishes its rows into every rank's exchange region itself, this call is the whole cycle
+        return timed("evaluate_cycle", lambda: eng2.evaluate_cycle_into(out.data_ptr()))   # [K0 + K1 (+ K1x beside)] K3 + K2 (replayed identically on every rank) + D2H
+
+    if world > 1:
+        # the exchange regions are wired up once, outside the cycles (a scheduler does it at start-up): needs the offers' shape
+        eng2.load_programs(pt); eng2.load_tasks(pt); eng2.load_offers(pt, lo, hi, shard_rows); eng2.load_requirements(pt)
+        ok = torch.ones(1, device="cuda")
+        try:
+            if os.environ.get("OE_BENCH_EXCHANGE", "peer") != "peer":
+                raise RuntimeError("OE_BENCH_EXCHANGE asks for the NCCL all-gather")
+            sharded.attach_peers(eng2, dist, max_rows=max(64, 2 * eng2.factored_rows()))
+        except Exception as ex:   # noqa: BLE001  (no peer access between these GPUs: keep the collective)
+            print(f"rank {rank}: peer exchange unavailable ({ex}); using the NCCL all-gather", file=sys.stderr)
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        exchange = "peer stores from the feasibility kernel (NVLink), flags, device-side wait" if ok.item() > 0 else "nccl all-gather"
+        if exchange == "nccl all-gather":
+            eng2.close()
+            eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
 
     cyc_stats = None
     for _ in range(max(1, min(args.warmup, 3))):
@@ -348,6 +368,8 @@ def run_engine(args):
            "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
            "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
            "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"]}
+    if exchange:
+        e2e["exchange"] = exchange
 
     # the same cycle when the caller only wants the decisions (what the scheduler adapter asks for): no matrix is written
     if world == 1:

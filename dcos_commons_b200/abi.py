@@ -489,6 +489,24 @@ class Handle:
         self._check(f(self.h, which, C.byref(ptr), C.byref(n)))
         return int(ptr.value or 0), int(n.value)
 
+    def peer_export(self, max_rows: int):
+        """oe_peer_export: (64-byte IPC handle, device pointer) of this shard's exchange region."""
+        f = self.b.fn("peer_export")
+        f.argtypes = [_p, C.c_int32, _p, C.POINTER(_p)]
+        handle = C.create_string_buffer(PEER_HANDLE_BYTES)
+        ptr = _p()
+        self._check(f(self.h, max_rows, handle, C.byref(ptr)))
+        return handle.raw, int(ptr.value or 0)
+
+    def peer_attach(self, handles=None, same_process_ptrs=None):
+        """oe_peer_attach: handles = the shards' IPC handles in rank order (bytes, world x 64) and / or, for shards whose
+        engine lives in this process, their exchange regions' device pointers (0 = use the handle)."""
+        f = self.b.fn("peer_attach")
+        f.argtypes = [_p, _p, _p]
+        hb = C.create_string_buffer(b"".join(handles), self.world * PEER_HANDLE_BYTES) if handles is not None else None
+        pa = (_p * self.world)(*[(q or None) for q in same_process_ptrs]) if same_process_ptrs is not None else None
+        self._check(f(self.h, hb, pa))
+
     def cuda_stream(self) -> int:
         f = self.b.fn("stream")
         f.argtypes, f.restype = [_p], _p
@@ -548,6 +566,7 @@ def unpack_bits(matrix: np.ndarray, n_offers: int) -> np.ndarray:
 
 
 OE_STATIC_MAX_OFFERS, OE_STATIC_MAX_ROWS = 4 * 1024 * 1024, 8192
+PEER_HANDLE_BYTES, PEER_MAX_WORLD = 64, 16
 
 
 def first_fit_static(device: int, stream: int, d_row_bits: int, stride_words: int, n_rows: int, n_offers: int, d_req_row: int,

@@ -132,6 +132,15 @@ __global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __
 // word per row with __ballot_sync.  gridDim.x covers the padded stride so every word is written.
 #define OE_K1_THREADS 128
 #define OE_K1_MAX_SMEM_NODES 1024
+#define OE_PEER_MAX_WORLD 16
+#define OE_PEER_HEADER_WORDS 64  // the flag words in front of an exchange buffer (256 B)
+// Peer exchange (world > 1, peers attached): where K1 publishes its words.  base[p] = shard p's exchange buffer of this
+// cycle's parity, already advanced to THIS rank's [rows][stride] block, so the layout is that of RowBits below.  Shard p's
+// memory is written over NVLink peer access (or is plain device memory when p is this rank).
+struct PeerOut {
+  uint32_t* base[OE_PEER_MAX_WORLD];
+  int n;
+};
 struct K1Args {
   uint32_t* F;
   int64_t stride;
@@ -140,6 +149,7 @@ struct K1Args {
   int n_nodes;           // rule nodes staged in shared memory (0 = read them from global memory)
   int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
   RuleTab tab;
+  PeerOut peers;
 };
 
 // K0c: rules whose leaves read only the offer's zone / region are evaluated once per (factored row, zone, region)
@@ -191,6 +201,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
   const oe_rule_node* nodes = a.n_nodes ? s_nodes : cx.p.nodes;
   const double* sc = a.sc_cols ? s_sc : nullptr;
   const int64_t word = i >> 5;
+  __shared__ __align__(16) uint32_t s_words[128][OE_K1_THREADS / 32];  // the CTA's four words of every row of the tile (peer exchange)
   for (int row = r0; row < r1; ++row) {
     const FastRow& fr = s_fast[row - r0];
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
@@ -202,7 +213,54 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
       pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
     }
     const uint32_t bits = __ballot_sync(0xffffffffu, pass);
-    if ((threadIdx.x & 31) == 0 && word < a.stride) a.F[(int64_t)row * a.stride + word] = bits;
+    if ((threadIdx.x & 31) == 0 && word < a.stride) {
+      a.F[(int64_t)row * a.stride + word] = bits;
+      s_words[row - r0][threadIdx.x >> 5] = bits;
+    }
+  }
+  // The all-gather of a sharded cycle, fused into the pass: the CTA stores its 16 bytes of every row straight into every
+  // shard's exchange buffer (one 128-bit store per row and shard), so the rows cross NVLink while the other CTAs still compute
+  // and no collective runs afterwards — k_peer_signal / k_peer_wait order the readers behind these stores.
+  if (a.peers.n > 0) {
+    __syncthreads();
+    const int64_t w0 = (int64_t)blockIdx.x * (OE_K1_THREADS / 32);
+    const int nrows = r1 - r0;
+    if (w0 < a.stride)
+      for (int q = threadIdx.x; q < nrows * a.peers.n; q += OE_K1_THREADS) {
+        const int p = q / nrows, rr = q - p * nrows;
+        *reinterpret_cast<uint4*>(a.peers.base[p] + (int64_t)(r0 + rr) * a.stride + w0) = *reinterpret_cast<const uint4*>(s_words[rr]);
+      }
+  }
+}
+
+// Peer exchange, the ordering half.  After K1 (same stream) every rank raises flag[rank] = epoch in every shard's exchange
+// header with a system-scope release; before the commit path reads its exchange buffer a rank waits until all of its own
+// flags have reached the epoch.  A peer that never arrives (a crashed rank) ends the wait after timeout_ns with *err = shard + 1.
+struct PeerFlags {
+  uint32_t* flags[OE_PEER_MAX_WORLD];  // each shard's flag words
+  int n, rank;
+  uint32_t epoch;
+};
+__global__ void k_peer_signal(PeerFlags f) {
+  const int p = threadIdx.x;
+  if (p < f.n) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.flags[p] + f.rank), "r"(f.epoch) : "memory");
+  }
+}
+__global__ void k_peer_wait(const uint32_t* my_flags, int n, uint32_t epoch, unsigned long long timeout_ns, int* err) {
+  const int p = threadIdx.x;
+  if (p >= n) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flags + p) : "memory");
+    if ((int32_t)(v - epoch) >= 0) break;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) { atomicExch(err, p + 1); break; }
+    __nanosleep(100);
   }
 }
 
@@ -1240,6 +1298,27 @@ struct oe_engine {
   cudaEvent_t ev_variants = nullptr, ev_side = nullptr;
   cudaStream_t side_stream = nullptr;
 
+  // ---- peer exchange (world > 1): [header: one flag word per shard][2 parities][world][exch_max_rows][exch_stride] words
+  DevBuf d_exch, d_peer_err;
+  int exch_max_rows = 0;
+  int64_t exch_stride = 0;
+  uint32_t* peer_base[OE_PEER_MAX_WORLD]{};   // every shard's exchange region, as this process addresses it
+  bool peer_opened[OE_PEER_MAX_WORLD]{};      // mapped with cudaIpcOpenMemHandle (to be closed), as opposed to a same-process pointer
+  bool peers_attached = false;
+  uint32_t peer_epoch = 0;                    // passes published so far; parity = peer_epoch & 1
+  unsigned long long peer_timeout_ns = 10ull * 1000 * 1000 * 1000;
+  size_t exch_parity_words() const { return (size_t)world * exch_max_rows * exch_stride; }
+  uint32_t* exch_rows(int shard, uint32_t epoch) const {  // shard's buffer of that epoch's parity
+    return peer_base[shard] + OE_PEER_HEADER_WORDS + (size_t)(epoch & 1u) * exch_parity_words();
+  }
+  void detach_peers() {
+    for (int p = 0; p < OE_PEER_MAX_WORLD; ++p) {
+      if (peer_opened[p] && peer_base[p]) cudaIpcCloseMemHandle(peer_base[p]);
+      peer_base[p] = nullptr; peer_opened[p] = false;
+    }
+    peers_attached = false;
+  }
+
   int fail(int code, const char* fmt, ...) {
     char buf[768];
     va_list ap;
@@ -1412,6 +1491,8 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin};
+  h->detach_peers();
+  h->d_exch.release(); h->d_peer_err.release();
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
@@ -2159,11 +2240,29 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
     a.sc_cols = 0;  // S*K <= 8: the pool entries live in registers (OE_FR_DENSE); otherwise they are read through L1
     const size_t smem = (size_t)rows_per_tile * sizeof(FastRow) + (size_t)a.n_nodes * sizeof(oe_rule_node) +
                         (size_t)a.sc_cols * OE_K1_THREADS * sizeof(double);
+    if (h->peers_attached) {
+      if (rows > h->exch_max_rows || stride != h->exch_stride)
+        return h->fail(OE_ERR_LIMIT, "oe: the peer exchange was exported for %d bit rows of %lld words, this pass has %d rows of %lld words: "
+                       "export and attach again", h->exch_max_rows, (long long)h->exch_stride, rows, (long long)stride);
+      ++h->peer_epoch;
+      a.peers.n = h->world;
+      for (int p = 0; p < h->world; ++p) a.peers.base[p] = h->exch_rows(p, h->peer_epoch) + (size_t)h->rank * rows * stride;
+    }
     dim3 grid((unsigned)xblocks, (unsigned)tiles);
     if (h->dof.R <= OE_FAST_RANGES) k_class_feasibility<true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
     else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
     ++*launches;
     CU(cudaGetLastError());
+    if (h->peers_attached) {
+      PeerFlags f{};
+      f.n = h->world; f.rank = h->rank; f.epoch = h->peer_epoch;
+      for (int p = 0; p < h->world; ++p) f.flags[p] = h->peer_base[p];
+      k_peer_signal<<<1, 32, 0, h->stream>>>(f);
+      ++*launches;
+      CU(cudaGetLastError());
+    }
+  } else if (h->peers_attached) {
+    return h->fail(OE_ERR_STATE, "oe: a peer-attached engine needs at least one requirement class");
   }
   h->class_bits_fresh = true;
   return 0;
@@ -2195,7 +2294,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   RowBits rb{};
   rb.stride = stride; rb.rows = rows;
   if (h->world > 1) {
-    rb.F = h->d_Fglobal.as<uint32_t>();
+    rb.F = h->peers_attached ? h->exch_rows(h->rank, h->peer_epoch) : h->d_Fglobal.as<uint32_t>();
     rb.shard_words = h->shard_rows / 32;
     rb.total_words = std::min<int64_t>((h->N_global + 31) / 32, (int64_t)h->world * rb.shard_words);
   } else {
@@ -2433,7 +2532,27 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   int64_t launches = 0;
   bool expand_overlapped = false;
   CU(cudaEventRecord(h->ev[0], h->stream));
-  if (h->world > 1) {
+  if (h->world > 1 && h->peers_attached) {
+    // sharded, peers attached: this shard's pass publishes its rows into every shard's exchange buffer (K1 itself stores
+    // them); the commit path then waits on the device until every shard's rows of this epoch have landed here.
+    if (!h->class_bits_fresh) {
+      if (int rc = run_counters(h, &launches)) return rc;
+      CU(cudaEventRecord(h->ev[1], h->stream));
+      if (int rc = run_class_feasibility(h, &launches)) return rc;
+      if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
+        expand_overlapped = true;
+        CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));
+        h->fork_expand = true;
+      }
+    } else {
+      CU(cudaEventRecord(h->ev[1], h->stream));
+    }
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    k_peer_wait<<<1, 32, 0, h->stream>>>(h->peer_base[h->rank], h->world, h->peer_epoch, h->peer_timeout_ns, h->d_peer_err.as<int>());
+    ++launches;
+    CU(cudaGetLastError());
+  } else if (h->world > 1) {
     // sharded: the caller ran oe_class_feasibility on every shard and gathered the rows into OE_BUF_CLASS_BITS_GLOBAL
     if (!h->class_bits_fresh) return h->fail(OE_ERR_STATE, "oe_evaluate_cycle (sharded): run oe_class_feasibility and gather first");
     if (h->d_Fglobal.cap < (size_t)h->world * h->rows_factored() * h->stride() * 4) return h->fail(OE_ERR_STATE, "gathered class bits buffer was not requested");
@@ -2468,8 +2587,16 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   int n_placed = 0;
   if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaMemcpyAsync(&n_placed, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  int peer_err = 0;
+  if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev[5], h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  if (peer_err) {
+    CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
+    h->class_bits_fresh = false;
+    return h->fail(OE_ERR_STATE, "oe_evaluate_cycle: shard %d did not publish its class rows of pass %u within %.1f s (every rank must issue the same calls)",
+                   peer_err - 1, h->peer_epoch, h->peer_timeout_ns * 1e-9);
+  }
   h->h_last_dec.assign(out, out + h->M);
   h->cycle_done = true;
   if (stats) {
@@ -2608,6 +2735,79 @@ int32_t oe_export_tasks(oe_engine* h, int64_t* n_tasks, int32_t* name_id, int32_
   for (int q = 0; q < t.Q; ++q) CU(cudaMemcpyAsync(rr_key + (size_t)q * n, t.rr + (size_t)q * t.cap, n * 4, cudaMemcpyDeviceToHost, h->stream));
   for (int w = 0; w < t.FW; ++w) CU(cudaMemcpyAsync(filter_bits + (size_t)w * n, t.filter + (size_t)w * t.cap, n * 4, cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  return OE_OK;
+}
+
+int32_t oe_peer_export(oe_engine* h, int32_t max_rows, void* handle, void** dev_ptr) {
+  if (!h) return OE_ERR_INVALID;
+  if (h->world < 2) return h->fail(OE_ERR_STATE, "oe_peer_export: the engine is not sharded (world = 1)");
+  if (h->world > OE_PEER_MAX_WORLD) return h->fail(OE_ERR_LIMIT, "oe_peer_export: at most %d shards", OE_PEER_MAX_WORLD);
+  if (!h->hasO) return h->fail(OE_ERR_STATE, "oe_peer_export: load the offers first (the row stride comes from shard_rows)");
+  if (max_rows < 1) return h->fail(OE_ERR_INVALID, "oe_peer_export: max_rows");
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  h->detach_peers();
+  h->exch_max_rows = max_rows;
+  h->exch_stride = h->stride();
+  const size_t bytes = (OE_PEER_HEADER_WORDS + 2 * h->exch_parity_words()) * 4;
+  if (h->d_exch.cap < bytes) {   // a region of its own, exactly one cudaMalloc: that is what an IPC handle names
+    h->d_exch.release();
+    CU(cudaMalloc(&h->d_exch.p, bytes));
+    h->d_exch.cap = bytes;
+  }
+  CU(h->d_peer_err.ensure(sizeof(int)));
+  CU(cudaMemsetAsync(h->d_exch.p, 0, OE_PEER_HEADER_WORDS * 4, h->stream));
+  CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->peer_epoch = 0;
+  if (const char* ms = getenv("OE_PEER_TIMEOUT_MS")) {
+    const long long v = atoll(ms);
+    if (v > 0) h->peer_timeout_ns = (unsigned long long)v * 1000000ull;
+  }
+  if (handle) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == OE_PEER_HANDLE_BYTES, "OE_PEER_HANDLE_BYTES");
+    cudaIpcMemHandle_t ih;
+    CU(cudaIpcGetMemHandle(&ih, h->d_exch.p));
+    std::memcpy(handle, &ih, sizeof ih);
+  }
+  if (dev_ptr) *dev_ptr = h->d_exch.p;
+  return OE_OK;
+}
+
+int32_t oe_peer_attach(oe_engine* h, const void* handles, void* const* same_process_ptrs) {
+  if (!h) return OE_ERR_INVALID;
+  if (!h->d_exch.p || h->exch_max_rows < 1) return h->fail(OE_ERR_STATE, "oe_peer_attach: call oe_peer_export first");
+  if (!handles && !same_process_ptrs) return h->fail(OE_ERR_INVALID, "oe_peer_attach: neither handles nor pointers");
+  CU(cudaSetDevice(h->device));
+  h->detach_peers();
+  for (int p = 0; p < h->world; ++p) {
+    if (p == h->rank) { h->peer_base[p] = h->d_exch.as<uint32_t>(); continue; }
+    if (same_process_ptrs && same_process_ptrs[p]) {
+      cudaPointerAttributes at{};
+      CU(cudaPointerGetAttributes(&at, same_process_ptrs[p]));
+      if (at.type != cudaMemoryTypeDevice) { h->detach_peers(); return h->fail(OE_ERR_INVALID, "oe_peer_attach: pointer of shard %d is not device memory", p); }
+      if (at.device != h->device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, h->device, at.device));
+        if (!can) { h->detach_peers(); return h->fail(OE_ERR_CUDA, "oe_peer_attach: device %d cannot access device %d", h->device, at.device); }
+        cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { h->detach_peers(); return h->cuda_fail(e, "cudaDeviceEnablePeerAccess"); }
+        cudaGetLastError();
+      }
+      h->peer_base[p] = static_cast<uint32_t*>(same_process_ptrs[p]);
+      continue;
+    }
+    if (!handles) { h->detach_peers(); return h->fail(OE_ERR_INVALID, "oe_peer_attach: no handle and no pointer for shard %d", p); }
+    cudaIpcMemHandle_t ih;
+    std::memcpy(&ih, static_cast<const unsigned char*>(handles) + (size_t)p * OE_PEER_HANDLE_BYTES, sizeof ih);
+    void* q = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&q, ih, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { cudaGetLastError(); h->detach_peers(); return h->fail(OE_ERR_CUDA, "oe_peer_attach: cudaIpcOpenMemHandle for shard %d: %s", p, cudaGetErrorString(e)); }
+    h->peer_base[p] = static_cast<uint32_t*>(q);
+    h->peer_opened[p] = true;
+  }
+  h->peers_attached = true;
+  h->class_bits_fresh = false;
   return OE_OK;
 }
 

@@ -60,6 +60,26 @@ def first_fit(rows: np.ndarray, req_row: np.ndarray, n_offers: int) -> np.ndarra
     return out
 
 
+def attach_peers(engine: "abi.Engine", dist, max_rows: int) -> None:
+    """One process per GPU: every rank exports its exchange region (oe_peer_export), the 64-byte IPC handles go round
+    through the process group, and every rank maps all of them (oe_peer_attach).  From then on the engine's feasibility
+    pass stores its class rows into every shard's region itself and oe_evaluate_cycle is the whole sharded cycle: no
+    all-gather call.  Collective: all ranks call it, after loading their offer shard."""
+    handle, _ = engine.peer_export(max_rows)
+    handles = [None] * engine.world
+    dist.all_gather_object(handles, handle)
+    engine.peer_attach(handles=handles)
+    dist.barrier()   # nobody publishes before everybody has mapped everybody
+
+
+def attach_local(engines, max_rows: int) -> None:
+    """The same wiring for shards whose engines all live in THIS process (tests: several handles on one device, or one
+    handle per device of the box): the exchange regions are handed over as plain device pointers."""
+    ptrs = [e.peer_export(max_rows)[1] for e in engines]
+    for e in engines:
+        e.peer_attach(same_process_ptrs=[0 if r == e.rank else ptrs[r] for r in range(len(engines))])
+
+
 class _CudaView:
     """Exposes a raw device pointer through __cuda_array_interface__ so torch.distributed can gather engine memory."""
 

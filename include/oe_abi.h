@@ -398,7 +398,8 @@ int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats);
  * takes the FIRST offer in list order whose stages all pass (OfferEvaluator.java:137-245) among the offers not yet
  * taken by an earlier requirement of this cycle (:61-66).  out[M].  When world > 1 the caller must run
  * oe_class_feasibility() on every shard, gather the shards' rows (see oe_device_buffer) and then call this on every
- * rank: all ranks compute the same decisions.                                                                      */
+ * rank: all ranks compute the same decisions.  With peers attached (oe_peer_attach) the gather is part of the pass
+ * and this call alone is the sharded cycle.                                                                        */
 int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats);
 
 /* Why did an offer not fit?  For requirements [req_begin, req_end) and every loaded offer: bit min(s, 63) of
@@ -439,6 +440,33 @@ typedef enum {
 int32_t oe_device_buffer(oe_engine* h, int32_t which, void** dev_ptr, int64_t* n_bytes);
 /* The stream the engine launches on (cudaStream_t), so that callers can order their own work / events after it.   */
 void* oe_stream(oe_engine* h);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Peer exchange for sharded engines (world > 1, one engine per GPU of an NVLink box).  The reference evaluates every
+ * requirement against the ONE list of all offers (S/scheduler/plan/PlanScheduler.java:56-66: `availableOffers`), so a
+ * sharded cycle has one exchange step: every rank needs every shard's class-factored rows before it replays the commit.
+ * With peers attached that step is part of the feasibility pass: the kernel stores each 16 bytes of rows it produces
+ * straight into the exchange region of EVERY shard (its own included) through NVLink peer memory, raises a flag per
+ * shard behind them, and oe_evaluate_cycle waits on the device for all shards' flags before the commit reads its own
+ * region.  No collective library call and no host round trip sit between the pass and the commit, and
+ * oe_evaluate_cycle alone is then the whole sharded cycle (it runs the pass itself when the class rows are stale).
+ *
+ *   oe_peer_export  after oe_load_offers (the row stride comes from shard_rows): allocates this shard's region for up
+ *                   to max_rows factored rows (classes + variants; a pass with more fails with OE_ERR_LIMIT — export
+ *                   and attach again with a larger bound), resets the pass counter, and returns the region's CUDA IPC
+ *                   handle (OE_PEER_HANDLE_BYTES, may be NULL) and its device address (may be NULL).
+ *   oe_peer_attach  handles: world x OE_PEER_HANDLE_BYTES in rank order, from every rank's oe_peer_export (NULL when
+ *                   all shards are given as pointers); same_process_ptrs: NULL, or world entries, non-NULL where the
+ *                   shard's engine lives in THIS process (an IPC handle cannot be opened by the process that made it).
+ * Both are collective in the sense that every rank calls them, in this order, and nobody evaluates before all have
+ * attached.  All ranks must then issue the same sequence of evaluation calls; a rank may publish at most one pass ahead
+ * of a peer that is still committing (two buffers alternate), which oe_evaluate_cycle guarantees by waiting — so call
+ * it (not only oe_class_feasibility) once per pass.  A shard that does not publish within 10 s (OE_PEER_TIMEOUT_MS in
+ * the environment at export time) makes oe_evaluate_cycle fail with OE_ERR_STATE instead of waiting forever.  At most
+ * 16 shards.  Without peers attached the gather stays the caller's job (oe_device_buffer).                           */
+#define OE_PEER_HANDLE_BYTES 64
+int32_t oe_peer_export(oe_engine* h, int32_t max_rows, void* handle, void** dev_ptr);
+int32_t oe_peer_attach(oe_engine* h, const void* handles, void* const* same_process_ptrs);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Allocation-free first-fit.  This entry point has no counterpart in the reference (the JVM allocates freely); it
