@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -64,6 +65,43 @@ __global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, 
       prev_e = e;
     }
   }
+}
+
+// The same checks for the rows [r0, r1) of a freshly copied offer chunk, in one launch (OE_CFG_ASYNC_LOADS: the table arrives
+// in row chunks and every chunk is checked as soon as it has landed).  Same codes as the per-column checks.
+struct OfferLimits { int32_t n_agents, n_hostnames, n_zones, n_regions, n_attrs, n_rr_values; };
+__global__ void k_validate_offer_rows(oe::DevOffers o, OfferLimits lim, int64_t r0, int64_t r1, int* err) {
+  const int64_t i = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= r1) return;
+  int code = 0;
+  auto chk = [&](int32_t v, int32_t lo, int32_t hi, int c) { if (v < lo || v >= hi) code = max(code, c); };
+  chk(o.agent[i], 0, max(lim.n_agents, 1), 11);
+  chk(o.host[i], 0, max(lim.n_hostnames, 1), 12);
+  chk(o.zone[i], -1, lim.n_zones, 13);
+  chk(o.region[i], -1, lim.n_regions, 14);
+  for (int a = 0; a < o.A; ++a) chk(o.attr[(int64_t)a * o.N + i], -1, lim.n_attrs, 15);
+  for (int q = 0; q < o.Q; ++q) chk(o.rr[(int64_t)q * o.N + i], -1, lim.n_rr_values, 16);
+  for (int d = 0; d < o.D; ++d) chk(o.mprof[(int64_t)d * o.N + i], -1, OE_MAX_PROFILES, 17);
+  for (int s = 0; s < o.S; ++s) {
+    int prev_e = -1;
+    for (int r = 0; r < o.R; ++r) {
+      const uint32_t pr = o.port[((int64_t)s * o.R + r) * o.N + i];
+      const int b = pr & 0xFFFF, e = pr >> 16;
+      if (b > e) continue;
+      if (b <= prev_e) code = max(code, 18);
+      prev_e = e;
+    }
+  }
+  if (code) atomicMax(err, code);
+}
+
+// Small tables while a large offer table occupies the host-to-device copy engine (OE_CFG_ASYNC_LOADS): copies are served in
+// submission order, so a 400 KB column queued behind 100 MB of offers would arrive last.  The SMs read such a table straight
+// out of the caller's pinned host memory over PCIe instead, beside the running DMA.  16 bytes per thread and step.
+__global__ void __launch_bounds__(256) k_fetch_host(uint4* __restrict__ dst, const uint4* __restrict__ src, size_t n16, unsigned char* __restrict__ dst_tail,
+                                                    const unsigned char* __restrict__ src_tail, int tail) {
+  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n16; q += (size_t)gridDim.x * blockDim.x) dst[q] = src[q];
+  if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
 }
 
 // K0: one thread per deployed task; every counter set whose filter the task passes gets the task's keys tallied.
@@ -150,6 +188,7 @@ struct K1Args {
   int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
   RuleTab tab;
   PeerOut peers;
+  int64_t xb0;           // first 128-offer block of this launch (the offer table may be evaluated in row chunks)
 };
 
 // K0c: rules whose leaves read only the offer's zone / region are evaluated once per (factored row, zone, region)
@@ -178,7 +217,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
   double* s_sc = reinterpret_cast<double*>(s_nodes + a.n_nodes);
   const int r0 = blockIdx.y * a.rows_per_tile;
   const int r1 = min(a.rows, r0 + a.rows_per_tile);
-  const int64_t i = (int64_t)blockIdx.x * OE_K1_THREADS + threadIdx.x;
+  const int64_t i = (a.xb0 + blockIdx.x) * OE_K1_THREADS + threadIdx.x;
   const bool valid = i < cx.o.N;
   {  // stage
     const uint4* src = reinterpret_cast<const uint4*>(a.fast);
@@ -223,7 +262,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
   // and no collective runs afterwards — k_peer_signal / k_peer_wait order the readers behind these stores.
   if (a.peers.n > 0) {
     __syncthreads();
-    const int64_t w0 = (int64_t)blockIdx.x * (OE_K1_THREADS / 32);
+    const int64_t w0 = (a.xb0 + blockIdx.x) * (OE_K1_THREADS / 32);
     const int nrows = r1 - r0;
     if (w0 < a.stride)
       for (int q = threadIdx.x; q < nrows * a.peers.n; q += OE_K1_THREADS) {
@@ -271,9 +310,9 @@ __global__ void k_peer_wait(const uint32_t* my_flags, int n, uint32_t epoch, uns
 #define OE_KX_ROWS 4
 __global__ void __launch_bounds__(OE_KX_LANES * OE_KX_ROWS) k_expand_matrix(const uint32_t* __restrict__ F, const int32_t* __restrict__ req_row,
                                                                             uint32_t* __restrict__ out, int64_t stride, int64_t M,
-                                                                            int reqs_per_block) {
-  const int64_t w4 = ((int64_t)blockIdx.x * OE_KX_LANES + threadIdx.x) * 4;  // first word of this lane's uint4
-  if (w4 >= stride) return;
+                                                                            int reqs_per_block, int64_t xb0, int64_t w_end) {
+  const int64_t w4 = ((xb0 + blockIdx.x) * OE_KX_LANES + threadIdx.x) * 4;  // first word of this lane's uint4
+  if (w4 >= w_end) return;
   const int64_t j0 = (int64_t)blockIdx.y * reqs_per_block;
   const int64_t j1 = min(M, j0 + reqs_per_block);
   int64_t j = j0 + threadIdx.y;
@@ -1298,6 +1337,22 @@ struct oe_engine {
   cudaEvent_t ev_variants = nullptr, ev_side = nullptr;
   cudaStream_t side_stream = nullptr;
 
+  // ---- OE_CFG_ASYNC_LOADS: the offer table arrives on a copy stream of its own, in row chunks; a chunk is checked as soon as
+  // it has landed and the feasibility pass evaluates it while the next ones are still on the bus
+  static constexpr int kMaxChunks = 8;
+  struct OfferChunk { int64_t r0 = 0, r1 = 0; cudaEvent_t landed = nullptr; };
+  OfferChunk chunks[kMaxChunks];
+  int n_chunks = 1;                  // 1 = the whole table at once
+  bool offers_in_flight = false;     // chunk events are pending on copy_stream and nobody has waited for them yet
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_main = nullptr, ev_k1[kMaxChunks]{};
+  DevBuf d_offer_err;                // one flag per chunk, read back into h_offer_err behind the chunk's checks
+  int* h_offer_err = nullptr;        // pinned
+  char* pin_arena = nullptr;         // pinned staging for the engine's own (pageable) host tables while offers are in flight
+  size_t pin_cap = 0, pin_used = 0;
+  int64_t expand_from_word = 0;      // evaluate_cycle: words below this were expanded chunk by chunk beside the pass
+  bool expand_started = false;
+
   // ---- peer exchange (world > 1): [header: one flag word per shard][2 parities][world][exch_max_rows][exch_stride] words
   DevBuf d_exch, d_peer_err;
   int exch_max_rows = 0;
@@ -1355,10 +1410,34 @@ struct oe_engine {
 
 namespace {
 
+// While the offer table is on the bus: a table of up to 16 MB that lives in pinned (device-visible) host memory is fetched by
+// a kernel, not queued behind the offers on the copy engine (see k_fetch_host).  Pageable sources keep the plain copy.
+bool fetch_instead_of_copy(oe_engine* h, void* dst, const void* src, size_t bytes, cudaStream_t on) {
+  if (!h->offers_in_flight || bytes < 4096 || bytes > ((size_t)16 << 20)) return false;
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, src) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (at.type != cudaMemoryTypeHost || !at.devicePointer || (reinterpret_cast<uintptr_t>(at.devicePointer) & 15)) {
+    // pageable (or not 16-byte aligned): through the engine's pinned arena (reset by the next oe_load_offers), when it still has room
+    const size_t need = (bytes + 15) / 16 * 16;
+    if (!h->pin_arena || h->pin_used + need > h->pin_cap) return false;
+    char* q = h->pin_arena + h->pin_used;
+    std::memcpy(q, src, bytes);
+    h->pin_used += need;
+    at.devicePointer = q;   // cudaMallocHost memory has one address on both sides (unified addressing)
+  }
+  const size_t n16 = bytes / 16;
+  const int tail = (int)(bytes - n16 * 16);
+  const unsigned blocks = (unsigned)std::min<size_t>(296, (n16 + 255) / 256);
+  k_fetch_host<<<blocks, 256, 0, on>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(at.devicePointer), n16,
+                                       static_cast<unsigned char*>(dst) + n16 * 16, static_cast<const unsigned char*>(at.devicePointer) + n16 * 16, tail);
+  return cudaGetLastError() == cudaSuccess;
+}
+
 template <class T>
 int upload(oe_engine* h, DevBuf& b, const T* src, size_t n, cudaStream_t on = nullptr) {
   CU(b.ensure(std::max<size_t>(n, 1) * sizeof(T)));
-  if (n) CU(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, on ? on : h->stream));
+  if (!on) on = h->stream;
+  if (n && !fetch_instead_of_copy(h, b.p, src, n * sizeof(T), on)) CU(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, on));
   return 0;
 }
 // The requirement-side uploads are small and come from pageable memory; on the main stream they would queue behind a large
@@ -1383,6 +1462,37 @@ int fetch_err_flag(oe_engine* h, const char* what) {
     CU(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
     return h->fail(OE_ERR_INVALID, flag == 18 ? "%s: a ports column holds ranges that are not ascending and disjoint (code %d)"
                                               : "%s: id column %d holds a value outside its dictionary", what, flag);
+  }
+  return 0;
+}
+
+int offer_flag_error(oe_engine* h, int flag, const char* what) {
+  h->hasO = false;
+  return h->fail(OE_ERR_INVALID, flag == 18 ? "%s: a ports column holds ranges that are not ascending and disjoint (code %d)"
+                                            : "%s: id column %d holds a value outside its dictionary", what, flag);
+}
+// OE_CFG_ASYNC_LOADS: host-side wait for offer chunk c (copies + checks), and its verdict.
+int wait_offer_chunk(oe_engine* h, int c, const char* what) {
+  CU(cudaEventSynchronize(h->chunks[c].landed));
+  if (int flag = h->h_offer_err[c]) { h->offers_in_flight = false; return offer_flag_error(h, flag, what); }
+  return 0;
+}
+int wait_offers(oe_engine* h, const char* what) {
+  if (!h->offers_in_flight) return 0;
+  for (int c = 0; c < h->n_chunks; ++c) if (int rc = wait_offer_chunk(h, c, what)) return rc;
+  h->offers_in_flight = false;
+  return 0;
+}
+// rows [r0, r1) of a slot-major column (dst and src are [slots][N]) onto the copy stream
+int copy_rows(oe_engine* h, void* dst, const void* src, size_t elem, int slots, int64_t N, int64_t r0, int64_t r1) {
+  if (slots <= 0 || r1 <= r0) return 0;
+  char* d = static_cast<char*>(dst) + (size_t)r0 * elem;
+  const char* sp = static_cast<const char*>(src) + (size_t)r0 * elem;
+  const size_t pitch = (size_t)N * elem, width = (size_t)(r1 - r0) * elem;
+  if (slots == 1 || pitch > (size_t)0x7fffffff) {
+    for (int q = 0; q < slots; ++q) CU(cudaMemcpyAsync(d + q * pitch, sp + q * pitch, width, cudaMemcpyHostToDevice, h->copy_stream));
+  } else {
+    CU(cudaMemcpy2DAsync(d, pitch, sp, pitch, width, (size_t)slots, cudaMemcpyHostToDevice, h->copy_stream));
   }
   return 0;
 }
@@ -1452,6 +1562,15 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
       g_create_error = "oe_create: auxiliary streams"; delete h; return OE_ERR_CUDA;
     }
   }
+  {
+    bool ok = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming) == cudaSuccess &&
+              cudaMallocHost(reinterpret_cast<void**>(&h->h_offer_err), oe_engine::kMaxChunks * sizeof(int)) == cudaSuccess &&
+              h->d_offer_err.ensure(oe_engine::kMaxChunks * sizeof(int)) == cudaSuccess;
+    for (int c = 0; ok && c < oe_engine::kMaxChunks; ++c)
+      ok = cudaEventCreateWithFlags(&h->chunks[c].landed, cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&h->ev_k1[c], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { g_create_error = "oe_create: copy stream"; delete h; return OE_ERR_CUDA; }
+    std::memset(h->h_offer_err, 0, oe_engine::kMaxChunks * sizeof(int));
+  }
   if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
@@ -1491,6 +1610,15 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin};
+  if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+  for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
+    if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
+    if (h->ev_k1[c]) cudaEventDestroy(h->ev_k1[c]);
+  }
+  if (h->ev_main) cudaEventDestroy(h->ev_main);
+  if (h->h_offer_err) cudaFreeHost(h->h_offer_err);
+  if (h->pin_arena) cudaFreeHost(h->pin_arena);
+  h->d_offer_err.release();
   h->detach_peers();
   h->d_exch.release(); h->d_peer_err.release();
   for (auto* b : all) b->release();
@@ -1713,10 +1841,14 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   const int32_t* cols[7] = {t->name_id, t->pod_type_id, t->pod_index, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
   int32_t* dst[7] = {d.name, d.type, d.index, d.agent, d.host, d.zone, d.region};
   if (T > 0) {
-    for (int c = 0; c < 7; ++c) CU(cudaMemcpyAsync(dst[c], cols[c], (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
-    for (int a = 0; a < d.TA; ++a) CU(cudaMemcpyAsync(d.attr + (size_t)a * d.cap, t->attr_id + (size_t)a * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
-    for (int q = 0; q < d.Q; ++q) CU(cudaMemcpyAsync(d.rr + (size_t)q * d.cap, t->rr_key + (size_t)q * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
-    for (int w = 0; w < d.FW; ++w) CU(cudaMemcpyAsync(d.filter + (size_t)w * d.cap, t->filter_bits + (size_t)w * T, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream));
+    auto put = [&](void* to, const void* from) -> cudaError_t {
+      if (fetch_instead_of_copy(h, to, from, (size_t)T * 4, h->stream)) return cudaSuccess;
+      return cudaMemcpyAsync(to, from, (size_t)T * 4, cudaMemcpyHostToDevice, h->stream);
+    };
+    for (int c = 0; c < 7; ++c) CU(put(dst[c], cols[c]));
+    for (int a = 0; a < d.TA; ++a) CU(put(d.attr + (size_t)a * d.cap, t->attr_id + (size_t)a * T));
+    for (int q = 0; q < d.Q; ++q) CU(put(d.rr + (size_t)q * d.cap, t->rr_key + (size_t)q * T));
+    for (int w = 0; w < d.FW; ++w) CU(put(d.filter + (size_t)w * d.cap, t->filter_bits + (size_t)w * T));
   }
   d.T = T;
   const oe_dict_sizes& dc = h->dict;
@@ -1789,43 +1921,106 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   h->N = N; h->row_offset = t->row_offset; h->shard_rows = t->shard_rows; h->n_reserved = t->n_reserved;
   h->N_global = t->n_offers_global > 0 ? t->n_offers_global : N;
   const size_t n = (size_t)N;
-  if (int rc = upload(h, h->d_scalar, t->scalar, n * o.S * o.K)) return rc;
-  if (int rc = upload(h, h->d_present, t->scalar_present, n)) return rc;
-  if (int rc = upload(h, h->d_port, t->port_range, n * o.S * o.R)) return rc;
-  if (int rc = upload(h, h->d_msize, t->mount_size, n * o.D)) return rc;
-  if (int rc = upload(h, h->d_mprof, t->mount_profile, n * o.D)) return rc;
-  const int32_t* cols[5] = {t->alloc_role, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
-  for (int c = 0; c < 5; ++c) if (int rc = upload(h, h->d_ocols[c], cols[c], n)) return rc;
-  if (int rc = upload(h, h->d_oattr, t->attr_id, n * o.A)) return rc;
-  if (int rc = upload(h, h->d_orr, t->rr_key, n * o.Q)) return rc;
-  if (int rc = upload(h, h->d_oexec, t->exec_id, n * o.E)) return rc;
+  if (h->offers_in_flight) {  // a table that was never evaluated is being replaced: its verdict no longer matters
+    CU(cudaStreamSynchronize(h->copy_stream));
+    h->offers_in_flight = false;
+  }
+  h->n_chunks = 1;
+  h->chunks[0].r0 = 0; h->chunks[0].r1 = N;
+  const bool chunked = (h->flags & OE_CFG_ASYNC_LOADS) && N > 0;
+  if (chunked) {
+    // The table goes over the bus in row chunks on a stream of its own; behind each chunk its checks, the flag's way back to
+    // the host and an event.  The feasibility pass waits chunk by chunk (run_class_feasibility), so the first chunks are being
+    // evaluated (and expanded) while the later ones are still arriving.
+    CU(h->d_scalar.ensure(std::max<size_t>(n * o.S * o.K, 1) * 8)); CU(h->d_present.ensure(n * 4)); CU(h->d_port.ensure(std::max<size_t>(n * o.S * o.R, 1) * 4));
+    CU(h->d_msize.ensure(std::max<size_t>(n * o.D, 1) * 8)); CU(h->d_mprof.ensure(std::max<size_t>(n * o.D, 1) * 4));
+    for (int c = 0; c < 5; ++c) CU(h->d_ocols[c].ensure(n * 4));
+    CU(h->d_oattr.ensure(std::max<size_t>(n * o.A, 1) * 4)); CU(h->d_orr.ensure(std::max<size_t>(n * o.Q, 1) * 4)); CU(h->d_oexec.ensure(std::max<size_t>(n * o.E, 1) * 4));
+  } else {
+    if (int rc = upload(h, h->d_scalar, t->scalar, n * o.S * o.K)) return rc;
+    if (int rc = upload(h, h->d_present, t->scalar_present, n)) return rc;
+    if (int rc = upload(h, h->d_port, t->port_range, n * o.S * o.R)) return rc;
+    if (int rc = upload(h, h->d_msize, t->mount_size, n * o.D)) return rc;
+    if (int rc = upload(h, h->d_mprof, t->mount_profile, n * o.D)) return rc;
+    const int32_t* cols[5] = {t->alloc_role, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
+    for (int c = 0; c < 5; ++c) if (int rc = upload(h, h->d_ocols[c], cols[c], n)) return rc;
+    if (int rc = upload(h, h->d_oattr, t->attr_id, n * o.A)) return rc;
+    if (int rc = upload(h, h->d_orr, t->rr_key, n * o.Q)) return rc;
+    if (int rc = upload(h, h->d_oexec, t->exec_id, n * o.E)) return rc;
+  }
   o.scalar = h->d_scalar.as<double>(); o.present = h->d_present.as<uint32_t>(); o.port = h->d_port.as<uint32_t>();
   o.msize = h->d_msize.as<double>(); o.mprof = h->d_mprof.as<int32_t>();
   o.alloc = h->d_ocols[0].as<int32_t>(); o.agent = h->d_ocols[1].as<int32_t>(); o.host = h->d_ocols[2].as<int32_t>();
   o.zone = h->d_ocols[3].as<int32_t>(); o.region = h->d_ocols[4].as<int32_t>();
   o.attr = h->d_oattr.as<int32_t>(); o.rr = h->d_orr.as<int32_t>(); o.exec = h->d_oexec.as<int32_t>();
+  cudaStream_t ls = chunked ? h->copy_stream : h->stream;
+  if (chunked) {
+    if (h->pin_used) {  // staged tables of an earlier load may still be on their way
+      CU(cudaStreamSynchronize(h->side_stream));
+      CU(cudaStreamSynchronize(h->stream));
+      h->pin_used = 0;
+    }
+    if (!h->pin_arena && cudaMallocHost(reinterpret_cast<void**>(&h->pin_arena), (size_t)8 << 20) == cudaSuccess) h->pin_cap = (size_t)8 << 20;
+    cudaGetLastError();
+  }
+  if (chunked) {  // the copy stream starts behind whatever the main stream still does with the old table
+    CU(cudaEventRecord(h->ev_main, h->stream));
+    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_main, 0));
+    CU(cudaMemsetAsync(h->d_offer_err.p, 0, oe_engine::kMaxChunks * sizeof(int), h->copy_stream));
+  }
   if (t->n_reserved > 0) {
-    if (int rc = upload(h, h->d_rbegin, t->reserved_begin, n + 1)) return rc;
-    if (int rc = upload(h, h->d_rid, t->reserved_id, (size_t)t->n_reserved)) return rc;
-    if (int rc = upload(h, h->d_rkind, t->reserved_kind, (size_t)t->n_reserved)) return rc;
-    if (int rc = upload(h, h->d_rval, t->reserved_value, (size_t)t->n_reserved)) return rc;
+    if (int rc = upload(h, h->d_rbegin, t->reserved_begin, n + 1, ls)) return rc;
+    if (int rc = upload(h, h->d_rid, t->reserved_id, (size_t)t->n_reserved, ls)) return rc;
+    if (int rc = upload(h, h->d_rkind, t->reserved_kind, (size_t)t->n_reserved, ls)) return rc;
+    if (int rc = upload(h, h->d_rval, t->reserved_value, (size_t)t->n_reserved, ls)) return rc;
     o.rbegin = h->d_rbegin.as<int64_t>(); o.rid = h->d_rid.as<int32_t>(); o.rkind = h->d_rkind.as<int32_t>(); o.rval = h->d_rval.as<double>();
   } else {
     o.rbegin = nullptr; o.rid = nullptr; o.rkind = nullptr; o.rval = nullptr;
   }
   const oe_dict_sizes& dc = h->dict;
-  check_ids(h, o.agent, N, 0, std::max(dc.n_agents, 1), 11);
-  check_ids(h, o.host, N, 0, std::max(dc.n_hostnames, 1), 12);
-  check_ids(h, o.zone, N, -1, dc.n_zones, 13);
-  check_ids(h, o.region, N, -1, dc.n_regions, 14);
-  check_ids(h, o.attr, N * o.A, -1, dc.n_attrs, 15);
-  check_ids(h, o.rr, N * o.Q, -1, dc.n_rr_values, 16);
-  check_ids(h, o.mprof, N * o.D, -1, OE_MAX_PROFILES, 17);
-  if (t->n_reserved > 0) check_ids(h, o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19);
-  if (N > 0 && o.R > 0)
-    k_validate_ranges<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(o.port, N, o.S, o.R, 18, h->d_err.as<int>());
-  if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
-  else if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
+  if (chunked) {
+    int nch = (int)std::max<int64_t>(1, std::min<int64_t>(4, N / 131072));  // >= 128 Ki rows (~0.25 ms of PCIe) per chunk; more than four only add copy calls
+    if (const char* ev = getenv("OE_OFFER_CHUNKS")) nch = std::max(1, std::min(oe_engine::kMaxChunks, atoi(ev)));
+    const int64_t chunk_rows = round_up((N + nch - 1) / nch, 8192);  // whole K1x slabs (256 words)
+    nch = (int)((N + chunk_rows - 1) / chunk_rows);
+    h->n_chunks = nch;
+    if (t->n_reserved > 0)
+      k_validate_ids<<<(unsigned)((t->n_reserved + 255) / 256), 256, 0, h->copy_stream>>>(o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19, h->d_offer_err.as<int>());
+    const OfferLimits lim{dc.n_agents, dc.n_hostnames, dc.n_zones, dc.n_regions, dc.n_attrs, dc.n_rr_values};
+    for (int c = 0; c < nch; ++c) {
+      const int64_t r0 = c * chunk_rows, r1 = std::min<int64_t>(N, r0 + chunk_rows);
+      h->chunks[c].r0 = r0; h->chunks[c].r1 = r1;
+      if (int rc = copy_rows(h, h->d_scalar.p, t->scalar, 8, o.S * o.K, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_present.p, t->scalar_present, 4, 1, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_port.p, t->port_range, 4, o.S * o.R, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_msize.p, t->mount_size, 8, o.D, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_mprof.p, t->mount_profile, 4, o.D, N, r0, r1)) return rc;
+      const int32_t* cols[5] = {t->alloc_role, t->agent_id, t->hostname_id, t->zone_id, t->region_id};
+      for (int q = 0; q < 5; ++q) if (int rc = copy_rows(h, h->d_ocols[q].p, cols[q], 4, 1, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_oattr.p, t->attr_id, 4, o.A, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_orr.p, t->rr_key, 4, o.Q, N, r0, r1)) return rc;
+      if (int rc = copy_rows(h, h->d_oexec.p, t->exec_id, 4, o.E, N, r0, r1)) return rc;
+      k_validate_offer_rows<<<(unsigned)((r1 - r0 + 255) / 256), 256, 0, h->copy_stream>>>(o, lim, r0, r1, h->d_offer_err.as<int>() + c);
+      CU(cudaGetLastError());
+      CU(cudaMemcpyAsync(h->h_offer_err + c, h->d_offer_err.as<int>() + c, sizeof(int), cudaMemcpyDeviceToHost, h->copy_stream));
+      CU(cudaEventRecord(h->chunks[c].landed, h->copy_stream));
+    }
+    h->offers_in_flight = true;
+    h->validation_pending = true;
+  } else {
+    check_ids(h, o.agent, N, 0, std::max(dc.n_agents, 1), 11);
+    check_ids(h, o.host, N, 0, std::max(dc.n_hostnames, 1), 12);
+    check_ids(h, o.zone, N, -1, dc.n_zones, 13);
+    check_ids(h, o.region, N, -1, dc.n_regions, 14);
+    check_ids(h, o.attr, N * o.A, -1, dc.n_attrs, 15);
+    check_ids(h, o.rr, N * o.Q, -1, dc.n_rr_values, 16);
+    check_ids(h, o.mprof, N * o.D, -1, OE_MAX_PROFILES, 17);
+    if (t->n_reserved > 0) check_ids(h, o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19);
+    if (N > 0 && o.R > 0)
+      k_validate_ranges<<<(unsigned)((N + 255) / 256), 256, 0, h->stream>>>(o.port, N, o.S, o.R, 18, h->d_err.as<int>());
+    if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
+    else if (int rc = fetch_err_flag(h, "oe_load_offers")) return rc;  // also makes the caller's buffers reusable
+  }
   h->hasO = true;
   return OE_OK;
 }
@@ -1833,6 +2028,7 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
 int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* t) {
   if (!h || !t || (n_rows > 0 && !rows)) return OE_ERR_INVALID;
   if (!h->hasO) return h->fail(OE_ERR_STATE, "oe_update_offers: no resident offer table (oe_load_offers first)");
+  if (int rc = wait_offers(h, "oe_update_offers")) return rc;
   CU(cudaSetDevice(h->device));
   const DevOffers& o = h->dof;
   if (h->n_reserved > 0 || t->n_reserved > 0)
@@ -2211,18 +2407,38 @@ int build_fast_rows(oe_engine* h) {
   return 0;
 }
 
-int run_class_feasibility(oe_engine* h, int64_t* launches) {
+// OE_CYCLE_TRACE=1: host-side timestamps of one oe_evaluate_cycle on stderr (where the call's wall time goes)
+struct CycleTrace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  std::string line;
+  CycleTrace() : on(getenv("OE_CYCLE_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char* what) {
+    if (!on) return;
+    char b[64];
+    snprintf(b, sizeof b, " %s=%.3f", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    line += b;
+  }
+  ~CycleTrace() { if (on) fprintf(stderr, "[oe cycle, host ms]%s\n", line.c_str()); }
+};
+
+thread_local CycleTrace* g_trace = nullptr;
+
+int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64_t w0 = 0, int64_t w1 = -1);
+
+// K1 over the whole offer table, or — while an OE_CFG_ASYNC_LOADS table is still arriving — chunk by chunk as the chunks land.
+// expand_beside (oe_evaluate_cycle with OE_CFG_MATERIALIZE_MATRIX): the matrix columns of every chunk but the last are expanded on
+// the auxiliary stream as soon as the chunk's class bits exist; the last chunk's are left to the fork at the commit launch.
+int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
+  h->expand_from_word = 0;
+  h->expand_started = false;
   CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
   if (rows > 0) {
     if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;
-    // enough row tiles to fill the machine when there are few offers, few enough to amortise the offer-row loads
-    const int64_t xblocks = stride * 32 / OE_K1_THREADS;
-    int tiles = (int)std::min<int64_t>(rows, std::max<int64_t>(1, (148 * 16 + xblocks - 1) / xblocks));
-    int rows_per_tile = std::min(128, (rows + tiles - 1) / tiles);  // 128 descriptors = 16 KiB of shared memory
-    tiles = (rows + rows_per_tile - 1) / rows_per_tile;
-    if (tiles > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one feasibility launch covers", rows);
+    const int64_t xblocks_all = stride * 32 / OE_K1_THREADS;
+    const int n_chunks = h->offers_in_flight ? h->n_chunks : 1;
     K1Args a{};
     a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
     if (h->any_rule_tab) {
@@ -2234,12 +2450,10 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
                                                   h->tab_zdim, h->tab_rdim);
       ++*launches;
     }
-    a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows; a.rows_per_tile = rows_per_tile;
+    a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows;
     a.fast = h->d_fast.as<FastRow>();
     a.n_nodes = h->n_rule_nodes <= OE_K1_MAX_SMEM_NODES ? h->n_rule_nodes : 0;
     a.sc_cols = 0;  // S*K <= 8: the pool entries live in registers (OE_FR_DENSE); otherwise they are read through L1
-    const size_t smem = (size_t)rows_per_tile * sizeof(FastRow) + (size_t)a.n_nodes * sizeof(oe_rule_node) +
-                        (size_t)a.sc_cols * OE_K1_THREADS * sizeof(double);
     if (h->peers_attached) {
       if (rows > h->exch_max_rows || stride != h->exch_stride)
         return h->fail(OE_ERR_LIMIT, "oe: the peer exchange was exported for %d bit rows of %lld words, this pass has %d rows of %lld words: "
@@ -2248,11 +2462,42 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
       a.peers.n = h->world;
       for (int p = 0; p < h->world; ++p) a.peers.base[p] = h->exch_rows(p, h->peer_epoch) + (size_t)h->rank * rows * stride;
     }
-    dim3 grid((unsigned)xblocks, (unsigned)tiles);
-    if (h->dof.R <= OE_FAST_RANGES) k_class_feasibility<true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-    else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-    ++*launches;
-    CU(cudaGetLastError());
+    if (expand_beside && n_chunks > 1) CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
+    for (int c = 0; c < n_chunks; ++c) {
+      // x-blocks of this launch: the chunk's rows; the last launch also covers the padding up to the stride
+      const int64_t xb0 = n_chunks > 1 ? h->chunks[c].r0 / OE_K1_THREADS : 0;
+      const int64_t xb1 = (n_chunks > 1 && c + 1 < n_chunks) ? h->chunks[c].r1 / OE_K1_THREADS : xblocks_all;
+      const int64_t xblocks = xb1 - xb0;
+      // enough row tiles to fill the machine when there are few offers, few enough to amortise the offer-row loads
+      int tiles = (int)std::min<int64_t>(rows, std::max<int64_t>(1, (148 * 16 + xblocks - 1) / xblocks));
+      if (const char* ev = getenv("OE_K1_TILES")) tiles = std::max(1, std::min(rows, atoi(ev)));   // tuning probe (tools/k1_tiles_probe.py)
+      int rows_per_tile = std::min(128, (rows + tiles - 1) / tiles);  // 128 descriptors = 16 KiB of shared memory
+      tiles = (rows + rows_per_tile - 1) / rows_per_tile;
+      if (tiles > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one feasibility launch covers", rows);
+      a.rows_per_tile = rows_per_tile;
+      a.xb0 = xb0;
+      const size_t smem = (size_t)rows_per_tile * sizeof(FastRow) + (size_t)a.n_nodes * sizeof(oe_rule_node) +
+                          (size_t)a.sc_cols * OE_K1_THREADS * sizeof(double);
+      if (h->offers_in_flight) {
+        // the host reads the chunk's checks before any kernel gathers through its ids; the launch goes out the moment it landed
+        if (int rc = wait_offer_chunk(h, c, "oe_load_offers")) return rc;
+        if (g_trace) g_trace->mark("chunk");
+      }
+      dim3 grid((unsigned)xblocks, (unsigned)tiles);
+      if (h->dof.R <= OE_FAST_RANGES) k_class_feasibility<true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      ++*launches;
+      CU(cudaGetLastError());
+      if (expand_beside && c + 1 < n_chunks) {
+        CU(cudaEventRecord(h->ev_k1[c], h->stream));
+        CU(cudaStreamWaitEvent(h->aux_stream, h->ev_k1[c], 0));
+        if (!h->expand_started) { CU(cudaEventRecord(h->ev_x0, h->aux_stream)); h->expand_started = true; }
+        const int64_t w0 = h->chunks[c].r0 / 32, w1 = h->chunks[c].r1 / 32;
+        if (int rc = run_expand(h, launches, h->aux_stream, w0, w1)) return rc;
+        h->expand_from_word = w1;
+      }
+    }
+    h->offers_in_flight = false;
     if (h->peers_attached) {
       PeerFlags f{};
       f.n = h->world; f.rank = h->rank; f.epoch = h->peer_epoch;
@@ -2268,12 +2513,13 @@ int run_class_feasibility(oe_engine* h, int64_t* launches) {
   return 0;
 }
 
-int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr) {
+int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on, int64_t w0, int64_t w1) {
   if (!on) on = h->stream;
   const int64_t stride = h->stride();
+  if (w1 < 0) w1 = stride;
   CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
-  if (h->M > 0) {
-    const unsigned xblocks = (unsigned)((stride / 4 + OE_KX_LANES - 1) / OE_KX_LANES);
+  if (h->M > 0 && w1 > w0) {
+    const unsigned xblocks = (unsigned)(((w1 - w0) / 4 + OE_KX_LANES - 1) / OE_KX_LANES);
     // ~64 CTAs per SM overall (profiles/r01e_bw_probe.txt: 6.75 TB/s vs 6.50 at 32); each CTA streams a
     // [reqs_per_block x 1 KiB] slab
     int64_t yblocks = std::max<int64_t>(1, std::min<int64_t>((h->M + 15) / 16, (148 * 64 + xblocks - 1) / xblocks));
@@ -2281,7 +2527,8 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr) {
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);
     k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
-                                                                         h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block);
+                                                                         h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block,
+                                                                         w0 / (4 * OE_KX_LANES), w1);
     ++*launches;
     CU(cudaGetLastError());
   }
@@ -2377,8 +2624,8 @@ int run_commit(oe_engine* h, int64_t* launches) {
       materialized = true;
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
-      CU(cudaEventRecord(h->ev_x0, h->aux_stream));
-      if (int rc = run_expand(h, launches, h->aux_stream)) return rc;
+      if (!h->expand_started) CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+      if (int rc = run_expand(h, launches, h->aux_stream, h->expand_from_word)) return rc;
       CU(cudaEventRecord(h->ev_x1, h->aux_stream));
       CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
     } else {
@@ -2462,7 +2709,8 @@ float ms_between(cudaEvent_t a, cudaEvent_t b) {
   return ms;
 }
 
-int ready(oe_engine* h, const char* who) {
+// offers_deferred: the caller is a feasibility pass, which waits for an arriving offer table chunk by chunk itself
+int ready(oe_engine* h, const char* who, bool offers_deferred = false) {
   if (!h) return OE_ERR_INVALID;
   if (!(h->hasP && h->hasT && h->hasO && h->hasR)) return h->fail(OE_ERR_STATE, "%s: tables not loaded (programs, tasks, offers, requirements)", who);
   for (auto& cs : h->h_csets)
@@ -2472,13 +2720,14 @@ int ready(oe_engine* h, const char* who) {
     h->validation_pending = false;
     if (int rc = fetch_err_flag(h, who)) { h->hasT = h->hasO = h->hasR = false; return rc; }
   }
+  if (!offers_deferred) if (int rc = wait_offers(h, who)) return rc;
   return 0;
 }
 
 }  // namespace
 
 int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
-  if (int rc = ready(h, "oe_class_feasibility")) return rc;
+  if (int rc = ready(h, "oe_class_feasibility", true)) return rc;
   int64_t launches = 0;
   CU(cudaEventRecord(h->ev[0], h->stream));
   if (int rc = run_counters(h, &launches)) return rc;
@@ -2501,7 +2750,7 @@ int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
 }
 
 int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
-  if (int rc = ready(h, "oe_feasibility")) return rc;
+  if (int rc = ready(h, "oe_feasibility", true)) return rc;
   int64_t launches = 0;
   CU(cudaEventRecord(h->ev[0], h->stream));
   if (int rc = run_counters(h, &launches)) return rc;
@@ -2527,7 +2776,10 @@ int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
 }
 
 int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
-  if (int rc = ready(h, "oe_evaluate_cycle")) return rc;
+  CycleTrace tr;
+  struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
+  if (int rc = ready(h, "oe_evaluate_cycle", true)) return rc;
+  tr.mark("ready");
   if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
   bool expand_overlapped = false;
@@ -2538,7 +2790,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     if (!h->class_bits_fresh) {
       if (int rc = run_counters(h, &launches)) return rc;
       CU(cudaEventRecord(h->ev[1], h->stream));
-      if (int rc = run_class_feasibility(h, &launches)) return rc;
+      if (int rc = run_class_feasibility(h, &launches, (h->flags & OE_CFG_MATERIALIZE_MATRIX) != 0)) return rc;
       if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
         expand_overlapped = true;
         CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));
@@ -2562,7 +2814,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   } else {
     if (int rc = run_counters(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[1], h->stream));
-    if (int rc = run_class_feasibility(h, &launches)) return rc;
+    if (int rc = run_class_feasibility(h, &launches, (h->flags & OE_CFG_MATERIALIZE_MATRIX) != 0)) return rc;
     CU(cudaEventRecord(h->ev[2], h->stream));
     CU(cudaEventRecord(h->ev[3], h->stream));
     if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
@@ -2571,15 +2823,17 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       h->fork_expand = true;
     }
   }
+  tr.mark("pass_enqueued");
   if (int rc = run_commit(h, &launches)) { h->fork_expand = false; return rc; }
+  tr.mark("commit_enqueued");
   CU(cudaEventRecord(h->ev[4], h->stream));
   if (expand_overlapped) {
     if (h->fork_expand) {  // the commit path had no fork point (no requirements, or more bit rows than the union path takes)
       h->fork_expand = false;
       CU(cudaEventRecord(h->ev_fork, h->stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
-      CU(cudaEventRecord(h->ev_x0, h->aux_stream));
-      if (int rc = run_expand(h, &launches, h->aux_stream)) return rc;
+      if (!h->expand_started) CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+      if (int rc = run_expand(h, &launches, h->aux_stream, h->expand_from_word)) return rc;
       CU(cudaEventRecord(h->ev_x1, h->aux_stream));
     }
     CU(cudaStreamWaitEvent(h->stream, h->ev_x1, 0));
@@ -2591,13 +2845,13 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev[5], h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  tr.mark("synced");
   if (peer_err) {
     CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
     h->class_bits_fresh = false;
     return h->fail(OE_ERR_STATE, "oe_evaluate_cycle: shard %d did not publish its class rows of pass %u within %.1f s (every rank must issue the same calls)",
                    peer_err - 1, h->peer_epoch, h->peer_timeout_ns * 1e-9);
   }
-  h->h_last_dec.assign(out, out + h->M);
   h->cycle_done = true;
   if (stats) {
     std::memset(stats, 0, sizeof *stats);
@@ -2671,6 +2925,10 @@ int32_t oe_apply_launches(oe_engine* h) {
   if (h->dt.TA < h->dof.A) return h->fail(OE_ERR_INVALID, "oe_apply_launches: task table has fewer attribute slots than the offer table");
   std::vector<int32_t> dst, req, name;
   std::vector<uint32_t> filt;
+  // the decisions of the last cycle still sit in device memory (no per-cycle host copy is kept for this rarely used entry)
+  h->h_last_dec.resize((size_t)h->M);
+  if (h->M > 0) CU(cudaMemcpyAsync(h->h_last_dec.data(), h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
   if (!h->name_map_built) {
     h->name_to_row.reserve(h->h_tname.size() * 2 + 16);
     for (size_t r = 0; r < h->h_tname.size(); ++r) h->name_to_row[h->h_tname[r]] = (int32_t)r;

@@ -156,6 +156,61 @@ def test_async_loads_give_the_same_answers_and_still_validate():
     eng.close()
 
 
+@pytest.mark.parametrize("flags", [abi.OE_CFG_ASYNC_LOADS, abi.OE_CFG_ASYNC_LOADS | abi.OE_CFG_MATERIALIZE_MATRIX])
+def test_async_offer_table_arrives_and_is_evaluated_in_row_chunks(flags, monkeypatch):
+    """OE_CFG_ASYNC_LOADS: the offer table goes over the bus in row chunks and the pass evaluates (and, with the matrix
+    requested, expands) every chunk as it lands.  Same answers as a load that waits; a bad id in a late chunk is reported."""
+    monkeypatch.setenv("OE_OFFER_CHUNKS", "5")
+    eng = Engine(device=0, flags=flags)
+    ref = Engine(device=0)
+    for seed, n in ((11, 40000), (12, 70001), (13, 8192 * 3)):
+        cl = synth.make_cluster(n, 900, 8, 3, 4, 200, "c5", seed=seed)
+        t = cl.tables
+        ref.load(t)
+        want, _ = ref.evaluate_cycle()
+        eng.load(t)
+        got, st = eng.evaluate_cycle()
+        assert got.tobytes() == want.tobytes()
+        if flags & abi.OE_CFG_MATERIALIZE_MATRIX:     # the matrix the chunked expansion left in device memory
+            import torch
+            ptr, nbytes = eng.device_buffer(abi.BUF_MATRIX)
+            from dcos_commons_b200 import sharded
+            m = torch.as_tensor(sharded._CudaView(ptr, nbytes // 4), device="cuda").cpu().numpy().view(np.uint32).reshape(t.n_reqs, -1)
+            full, _ = ref.feasibility()
+            assert np.array_equal(unpack_bits(m, t.n_offers), unpack_bits(full, t.n_offers))
+        eng.load(t)
+        f1, _ = eng.feasibility()
+        f2, _ = ref.feasibility()
+        assert np.array_equal(f1, f2)
+        eng.load(t)
+        c1, _ = eng.class_feasibility()
+        c2, _ = ref.class_feasibility()
+        assert np.array_equal(c1, c2)
+    # fuzzed tables (general interpreter, reserved side table) through the chunked path
+    for seed in (21, 22, 23):
+        t = random_tables(seed, n_offers=20000)
+        orc = Oracle().load(t)
+        eng.load(t)
+        assert eng.evaluate_cycle()[0].tobytes() == orc.evaluate_cycle()[0].tobytes()
+        orc.close()
+    cl = synth.make_cluster(40000, 100, 8, 3, 4, 50, "c5", seed=5)
+    bad = cl.tables
+    bad.zone_id = bad.zone_id.copy()
+    bad.zone_id[39000] = 10 ** 6              # last chunk
+    eng.load(bad)
+    with pytest.raises(abi.EngineError) as ei:
+        eng.evaluate_cycle()
+    assert "13" in str(ei.value)
+    with pytest.raises(abi.EngineError):
+        eng.evaluate_cycle()                  # offers must be loaded again
+    eng.load(bad)
+    with pytest.raises(abi.EngineError):
+        eng.stage_failures(0, 1)              # an entry that is not a pass waits for the whole table and reports, too
+    eng.load(cl.tables if False else synth.make_cluster(40000, 100, 8, 3, 4, 50, "c5", seed=5).tables)
+    assert eng.evaluate_cycle()[0].tobytes() == ref.load(synth.make_cluster(40000, 100, 8, 3, 4, 50, "c5", seed=5).tables).evaluate_cycle()[0].tobytes()
+    eng.close(); ref.close()
+
+
 def _patched(t, rows, src_rows):
     """A copy of the tables whose offer rows `rows` hold what rows `src_rows` held."""
     import copy
