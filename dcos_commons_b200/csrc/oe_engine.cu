@@ -19,6 +19,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <limits>
 #include <string>
 #include <unordered_map>
@@ -1151,6 +1152,42 @@ __global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
   if (lane == 0 && placed) atomicAdd(a.n_placed, placed);
 }
 
+// Commit in two passes (the offer table still arriving, see oe_evaluate_cycle): the requirements that the pass over the prefix
+// left without an offer, in plan order.  sub_idx[k] = requirement, sub_row[k] = its bit row, *count = how many.  One CTA.
+__global__ void __launch_bounds__(1024) k_collect_unplaced(const oe_decision* __restrict__ dec, const int32_t* __restrict__ req_row, int64_t M,
+                                                           int32_t* __restrict__ sub_idx, int32_t* __restrict__ sub_row, int* __restrict__ count) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t j0 = 0; j0 < M; j0 += 1024) {
+    const int64_t j = j0 + threadIdx.x;
+    const bool open = j < M && dec[j].offer_row < 0;
+    const uint32_t b = __ballot_sync(0xffffffffu, open);
+    if (lane == 0) warp_tot[warp] = __popc(b);
+    __syncthreads();
+    int before = carry_s;
+    for (int w = 0; w < warp; ++w) before += warp_tot[w];
+    if (open) {
+      const int k = before + __popc(b & ((1u << lane) - 1u));
+      sub_idx[k] = (int32_t)j;
+      sub_row[k] = req_row[j];
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = before + __popc(b);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *count = carry_s;
+}
+// ... and what the pass over the rest of the offers found for them (its offer indices start at `offset`).
+__global__ void k_merge_unplaced(const oe_decision* __restrict__ dec_sub, const int32_t* __restrict__ sub_idx, int n, int32_t offset, oe_decision* __restrict__ dec) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int32_t o = dec_sub[k].offer_row;
+  if (o >= 0) dec[sub_idx[k]].offer_row = o + offset;
+}
+
 // K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
 __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1348,6 +1385,8 @@ struct oe_engine {
   cudaEvent_t ev_main = nullptr, ev_k1[kMaxChunks]{};
   DevBuf d_offer_err;                // one flag per chunk, read back into h_offer_err behind the chunk's checks
   int* h_offer_err = nullptr;        // pinned
+  DevBuf d_sub_idx, d_sub_row, d_dec_sub, d_sub_count;   // commit in two passes: the requirements left open by the prefix pass
+  cudaEvent_t ev_prefix = nullptr, ev_phase_a = nullptr, ev_k1_last = nullptr;
   char* pin_arena = nullptr;         // pinned staging for the engine's own (pageable) host tables while offers are in flight
   size_t pin_cap = 0, pin_used = 0;
   int64_t expand_from_word = 0;      // evaluate_cycle: words below this were expanded chunk by chunk beside the pass
@@ -1564,12 +1603,14 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
   }
   {
     bool ok = cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming) == cudaSuccess &&
-              cudaMallocHost(reinterpret_cast<void**>(&h->h_offer_err), oe_engine::kMaxChunks * sizeof(int)) == cudaSuccess &&
+              cudaMallocHost(reinterpret_cast<void**>(&h->h_offer_err), (oe_engine::kMaxChunks + 1) * sizeof(int)) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_prefix, cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&h->ev_phase_a, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&h->ev_k1_last, cudaEventDisableTiming) == cudaSuccess && h->d_sub_count.ensure(sizeof(int)) == cudaSuccess &&
               h->d_offer_err.ensure(oe_engine::kMaxChunks * sizeof(int)) == cudaSuccess;
     for (int c = 0; ok && c < oe_engine::kMaxChunks; ++c)
       ok = cudaEventCreateWithFlags(&h->chunks[c].landed, cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&h->ev_k1[c], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { g_create_error = "oe_create: copy stream"; delete h; return OE_ERR_CUDA; }
-    std::memset(h->h_offer_err, 0, oe_engine::kMaxChunks * sizeof(int));
+    std::memset(h->h_offer_err, 0, (oe_engine::kMaxChunks + 1) * sizeof(int));
   }
   if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
@@ -1616,6 +1657,8 @@ void oe_destroy(oe_engine* h) {
     if (h->ev_k1[c]) cudaEventDestroy(h->ev_k1[c]);
   }
   if (h->ev_main) cudaEventDestroy(h->ev_main);
+  for (cudaEvent_t e : {h->ev_prefix, h->ev_phase_a, h->ev_k1_last}) if (e) cudaEventDestroy(e);
+  h->d_sub_idx.release(); h->d_sub_row.release(); h->d_dec_sub.release(); h->d_sub_count.release();
   if (h->h_offer_err) cudaFreeHost(h->h_offer_err);
   if (h->pin_arena) cudaFreeHost(h->pin_arena);
   h->d_offer_err.release();
@@ -2429,7 +2472,8 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64
 // K1 over the whole offer table, or — while an OE_CFG_ASYNC_LOADS table is still arriving — chunk by chunk as the chunks land.
 // expand_beside (oe_evaluate_cycle with OE_CFG_MATERIALIZE_MATRIX): the matrix columns of every chunk but the last are expanded on
 // the auxiliary stream as soon as the chunk's class bits exist; the last chunk's are left to the fork at the commit launch.
-int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false) {
+int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false, bool expand_last = false,
+                          const std::function<int()>* after_prefix = nullptr) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
   h->expand_from_word = 0;
@@ -2488,14 +2532,15 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
       ++*launches;
       CU(cudaGetLastError());
-      if (expand_beside && c + 1 < n_chunks) {
+      if (expand_beside && (c + 1 < n_chunks || expand_last)) {
         CU(cudaEventRecord(h->ev_k1[c], h->stream));
         CU(cudaStreamWaitEvent(h->aux_stream, h->ev_k1[c], 0));
         if (!h->expand_started) { CU(cudaEventRecord(h->ev_x0, h->aux_stream)); h->expand_started = true; }
-        const int64_t w0 = h->chunks[c].r0 / 32, w1 = h->chunks[c].r1 / 32;
+        const int64_t w0 = h->chunks[c].r0 / 32, w1 = c + 1 < n_chunks ? h->chunks[c].r1 / 32 : stride;
         if (int rc = run_expand(h, launches, h->aux_stream, w0, w1)) return rc;
         h->expand_from_word = w1;
       }
+      if (after_prefix && c == n_chunks - 2) if (int rc = (*after_prefix)()) return rc;
     }
     h->offers_in_flight = false;
     if (h->peers_attached) {
@@ -2535,6 +2580,112 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on, int64_t w0, int
   return 0;
 }
 
+// The union-list commit (see k_commit_union) of requirements req_row[0..M) over the offers of `rb`, on stream `st`: K3d, the
+// components, one union list per component, the sort by component, the replay.  Decisions (offer indices relative to rb) go to
+// dec[0..M).  Also used on a PREFIX of the offers and then on the rest with the requirements the prefix left unplaced
+// (oe_evaluate_cycle while the offer table is still arriving): first fit takes the lowest free index, so what a requirement gets
+// inside a prefix does not depend on the offers behind it, and a requirement that found nothing took nothing.
+bool union_commit_fits(const oe_engine* h, int rows, int64_t total_words) {
+  const size_t union_smem = ((size_t)total_words * 4 + 15) / 16 * 16 + (size_t)OE_RING * 32 * sizeof(int2);
+  return rows <= OE_UNION_MAX_ROWS && union_smem + 1024 <= (size_t)h->smem_optin - h->union_static_smem;
+}
+int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const int32_t* req_row, int64_t M, oe_decision* dec, cudaStream_t st,
+                      bool zero_placed, bool fork_ok, bool materialize) {
+  const int rows = rb.rows;
+  const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
+  const size_t union_smem = ((size_t)rb.total_words * 4 + 15) / 16 * 16 + (size_t)OE_RING * 32 * sizeof(int2);
+  {
+    const unsigned long long* adj = nullptr;
+    if (rows > 1) {
+      CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
+      CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, st));
+      k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, st>>>(rb, h->d_adj.as<unsigned long long>());
+      ++*launches;
+      adj = h->d_adj.as<unsigned long long>();
+    }
+    CU(h->d_meta.ensure(sizeof(CommitMeta)));
+    CommitMeta* meta = h->d_meta.as<CommitMeta>();
+    k_label_components<<<1, 32, 0, st>>>(rows, adj, meta);
+    const int64_t ustride = rb.total_words;
+    CU(h->d_union.ensure(std::max<size_t>((size_t)32 * ustride, 1) * 4));
+    k_union_bits<<<dim3((unsigned)std::max<int64_t>(1, (ustride + 255) / 256), 32), 256, 0, st>>>(rb, meta, h->d_union.as<uint32_t>(), ustride);
+    RowBits ub{};
+    ub.F = h->d_union.as<uint32_t>(); ub.stride = ustride; ub.rows = 32; ub.shard_words = ustride; ub.total_words = ustride;
+    CU(h->d_tile_cnt.ensure((size_t)32 * tiles * 4));
+    CU(h->d_row_base.ensure((size_t)33 * 8));
+    CU(h->d_row_len.ensure((size_t)32 * 4));
+    // components share no offer, so all union lists together hold at most one entry per offer: no size read-back needed
+    CU(h->d_cand.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
+    CU(h->d_umask.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
+    dim3 ugrid((unsigned)tiles, 32);
+    k_tile_popc<<<ugrid, 256, 0, st>>>(ub, tiles, h->d_tile_cnt.as<int32_t>());
+    k_row_offsets<<<1, 1024, 0, st>>>(32, tiles, (int64_t)0x7fffffff, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>());
+    k_compact_rows<<<ugrid, 256, 0, st>>>(ub, tiles, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(),
+                                                 h->d_cand.as<int32_t>());
+    k_union_masks<<<dim3((unsigned)std::max<int64_t>(1, std::min<int64_t>(1024, (ustride * 32 + 255) / 256)), 32), 256, 0, st>>>(
+        rb, meta, h->d_cand.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(), h->d_umask.as<uint32_t>());
+    *launches += 6;
+    CU(cudaGetLastError());
+    UnionArgs ua{};
+    ua.meta = meta; ua.ucand = h->d_cand.as<int32_t>(); ua.umask = h->d_umask.as<uint32_t>(); ua.ubase = h->d_row_base.as<int64_t>();
+    ua.ulen = h->d_row_len.as<int32_t>(); ua.used_words = rb.total_words; ua.req_row = req_row; ua.M = M;
+    ua.dec = dec; ua.n_placed = h->d_nplaced.as<int>();
+    CU(h->d_order.ensure(std::max<size_t>((size_t)M, 1) * sizeof(int2)));
+    ua.order = h->d_order.as<int2>();
+    CU(h->d_sort_hist.ensure((size_t)OE_SORT_BLOCKS * 32 * sizeof(int)));
+    CU(h->d_comp_begin.ensure(33 * sizeof(int)));
+    k_sort_hist<<<OE_SORT_BLOCKS, 256, 0, st>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>());
+    k_sort_scatter<<<OE_SORT_BLOCKS, 256, 0, st>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>(), ua.order, h->d_comp_begin.as<int>());
+    *launches += 2;
+    ua.comp_begin = h->d_comp_begin.as<int>();
+    if (zero_placed) CU(cudaMemsetAsync(ua.n_placed, 0, sizeof(int), st));
+    static const bool trace_on = getenv("OE_COMMIT_TRACE") != nullptr;   // debugging aid (tools/commit_probe.py): per-warp counters on stderr
+    if (trace_on) {
+      CU(h->d_dbg.ensure(32 * 8 * sizeof(long long)));
+      CU(cudaMemsetAsync(h->d_dbg.p, 0, 32 * 8 * sizeof(long long), st));
+      ua.trace = h->d_dbg.as<long long>();
+    }
+    bool materialized = false;
+    if (h->fork_expand && fork_ok) {
+      // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
+      // kernel on the highest-priority stream, so that its CTAs (one per component, each with the claimed bitmap in shared
+      // memory) are placed while the SMs are still empty, K1x on the lowest-priority one, filling the rest.  (Started any
+      // earlier, K1x occupies every SM and the commit waits for the expansion to drain.)
+      h->fork_expand = false;
+      CU(cudaEventRecord(h->ev_fork, st));
+      CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
+      k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
+      // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
+      // behind the expansion's grid
+      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec);
+      materialized = true;
+      CU(cudaEventRecord(h->ev_commit, h->hi_stream));
+      CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
+      if (!h->expand_started) CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+      if (int rc = run_expand(h, launches, h->aux_stream, h->expand_from_word)) return rc;
+      CU(cudaEventRecord(h->ev_x1, h->aux_stream));
+      CU(cudaStreamWaitEvent(st, h->ev_commit, 0));
+    } else {
+      k_commit_union<<<32, 32, union_smem, st>>>(ua);
+    }
+    ++*launches;
+    CU(cudaGetLastError());
+    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec);
+    ++*launches;
+    CU(cudaGetLastError());
+    if (trace_on) {
+      long long d[32 * 8];
+      CU(cudaMemcpyAsync(d, ua.trace, sizeof d, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      for (int w = 0; w < 32; ++w)
+        if (d[w * 8])
+          fprintf(stderr, "commit trace: warp %2d  %6lld requirements  %8lld cycles  %4lld slides  %4lld top-ups  %5lld deferred  %5lld searches beyond  (prologue %lld cycles)\n",
+                  w, d[w * 8], d[w * 8 + 1], d[w * 8 + 2], d[w * 8 + 3], d[w * 8 + 4], d[w * 8 + 5], d[w * 8 + 6]);
+    }
+    return 0;
+  }
+}
+
 int run_commit(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
@@ -2555,98 +2706,8 @@ int run_commit(oe_engine* h, int64_t* launches) {
     return 0;
   }
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
-  const size_t union_smem = ((size_t)rb.total_words * 4 + 15) / 16 * 16 + (size_t)OE_RING * 32 * sizeof(int2);
-  if (rows <= OE_UNION_MAX_ROWS && union_smem + 1024 <= (size_t)h->smem_optin - h->union_static_smem) {
-    // ---- commit over union lists (see k_commit_union)
-    const unsigned long long* adj = nullptr;
-    if (rows > 1) {
-      CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
-      CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, h->stream));
-      k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
-      ++*launches;
-      adj = h->d_adj.as<unsigned long long>();
-    }
-    CU(h->d_meta.ensure(sizeof(CommitMeta)));
-    CommitMeta* meta = h->d_meta.as<CommitMeta>();
-    k_label_components<<<1, 32, 0, h->stream>>>(rows, adj, meta);
-    const int64_t ustride = rb.total_words;
-    CU(h->d_union.ensure(std::max<size_t>((size_t)32 * ustride, 1) * 4));
-    k_union_bits<<<dim3((unsigned)std::max<int64_t>(1, (ustride + 255) / 256), 32), 256, 0, h->stream>>>(rb, meta, h->d_union.as<uint32_t>(), ustride);
-    RowBits ub{};
-    ub.F = h->d_union.as<uint32_t>(); ub.stride = ustride; ub.rows = 32; ub.shard_words = ustride; ub.total_words = ustride;
-    CU(h->d_tile_cnt.ensure((size_t)32 * tiles * 4));
-    CU(h->d_row_base.ensure((size_t)33 * 8));
-    CU(h->d_row_len.ensure((size_t)32 * 4));
-    // components share no offer, so all union lists together hold at most one entry per offer: no size read-back needed
-    CU(h->d_cand.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
-    CU(h->d_umask.ensure(std::max<size_t>((size_t)ustride * 32, 1) * 4));
-    dim3 ugrid((unsigned)tiles, 32);
-    k_tile_popc<<<ugrid, 256, 0, h->stream>>>(ub, tiles, h->d_tile_cnt.as<int32_t>());
-    k_row_offsets<<<1, 1024, 0, h->stream>>>(32, tiles, (int64_t)0x7fffffff, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>());
-    k_compact_rows<<<ugrid, 256, 0, h->stream>>>(ub, tiles, h->d_tile_cnt.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(),
-                                                 h->d_cand.as<int32_t>());
-    k_union_masks<<<dim3((unsigned)std::max<int64_t>(1, std::min<int64_t>(1024, (ustride * 32 + 255) / 256)), 32), 256, 0, h->stream>>>(
-        rb, meta, h->d_cand.as<int32_t>(), h->d_row_base.as<int64_t>(), h->d_row_len.as<int32_t>(), h->d_umask.as<uint32_t>());
-    *launches += 6;
-    CU(cudaGetLastError());
-    UnionArgs ua{};
-    ua.meta = meta; ua.ucand = h->d_cand.as<int32_t>(); ua.umask = h->d_umask.as<uint32_t>(); ua.ubase = h->d_row_base.as<int64_t>();
-    ua.ulen = h->d_row_len.as<int32_t>(); ua.used_words = rb.total_words; ua.req_row = h->d_req_row.as<int32_t>(); ua.M = h->M;
-    ua.dec = h->d_dec.as<oe_decision>(); ua.n_placed = h->d_nplaced.as<int>();
-    CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
-    ua.order = h->d_order.as<int2>();
-    CU(h->d_sort_hist.ensure((size_t)OE_SORT_BLOCKS * 32 * sizeof(int)));
-    CU(h->d_comp_begin.ensure(33 * sizeof(int)));
-    k_sort_hist<<<OE_SORT_BLOCKS, 256, 0, h->stream>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>());
-    k_sort_scatter<<<OE_SORT_BLOCKS, 256, 0, h->stream>>>(ua.req_row, ua.M, meta, h->d_sort_hist.as<int>(), ua.order, h->d_comp_begin.as<int>());
-    *launches += 2;
-    ua.comp_begin = h->d_comp_begin.as<int>();
-    CU(cudaMemsetAsync(ua.n_placed, 0, sizeof(int), h->stream));
-    static const bool trace_on = getenv("OE_COMMIT_TRACE") != nullptr;   // debugging aid (tools/commit_probe.py): per-warp counters on stderr
-    if (trace_on) {
-      CU(h->d_dbg.ensure(32 * 8 * sizeof(long long)));
-      CU(cudaMemsetAsync(h->d_dbg.p, 0, 32 * 8 * sizeof(long long), h->stream));
-      ua.trace = h->d_dbg.as<long long>();
-    }
-    bool materialized = false;
-    if (h->fork_expand) {
-      // K1x needs only the class bits, the commit does not need the matrix.  Both become runnable at this event: the commit
-      // kernel on the highest-priority stream, so that its CTAs (one per component, each with the claimed bitmap in shared
-      // memory) are placed while the SMs are still empty, K1x on the lowest-priority one, filling the rest.  (Started any
-      // earlier, K1x occupies every SM and the commit waits for the expansion to drain.)
-      h->fork_expand = false;
-      CU(cudaEventRecord(h->ev_fork, h->stream));
-      CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
-      k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
-      // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
-      // behind the expansion's grid
-      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
-      materialized = true;
-      CU(cudaEventRecord(h->ev_commit, h->hi_stream));
-      CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
-      if (!h->expand_started) CU(cudaEventRecord(h->ev_x0, h->aux_stream));
-      if (int rc = run_expand(h, launches, h->aux_stream, h->expand_from_word)) return rc;
-      CU(cudaEventRecord(h->ev_x1, h->aux_stream));
-      CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
-    } else {
-      k_commit_union<<<32, 32, union_smem, h->stream>>>(ua);
-    }
-    ++*launches;
-    CU(cudaGetLastError());
-    if (!materialized) k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
-    ++*launches;
-    CU(cudaGetLastError());
-    if (trace_on) {
-      long long d[32 * 8];
-      CU(cudaMemcpyAsync(d, ua.trace, sizeof d, cudaMemcpyDeviceToHost, h->stream));
-      CU(cudaStreamSynchronize(h->stream));
-      for (int w = 0; w < 32; ++w)
-        if (d[w * 8])
-          fprintf(stderr, "commit trace: warp %2d  %6lld requirements  %8lld cycles  %4lld slides  %4lld top-ups  %5lld deferred  %5lld searches beyond  (prologue %lld cycles)\n",
-                  w, d[w * 8], d[w * 8 + 1], d[w * 8 + 2], d[w * 8 + 3], d[w * 8 + 4], d[w * 8 + 5], d[w * 8 + 6]);
-    }
-    return 0;
-  }
+  if (union_commit_fits(h, rows, rb.total_words))
+    return commit_union_pass(h, launches, rb, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, true);
   // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
   const int64_t cap = h->M + 16;
   CU(h->d_tile_cnt.ensure((size_t)rows * tiles * 4));
@@ -2782,7 +2843,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   tr.mark("ready");
   if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
-  bool expand_overlapped = false;
+  bool expand_overlapped = false, two_pass = false;
   CU(cudaEventRecord(h->ev[0], h->stream));
   if (h->world > 1 && h->peers_attached) {
     // sharded, peers attached: this shard's pass publishes its rows into every shard's exchange buffer (K1 itself stores
@@ -2814,17 +2875,73 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   } else {
     if (int rc = run_counters(h, &launches)) return rc;
     CU(cudaEventRecord(h->ev[1], h->stream));
-    if (int rc = run_class_feasibility(h, &launches, (h->flags & OE_CFG_MATERIALIZE_MATRIX) != 0)) return rc;
-    CU(cudaEventRecord(h->ev[2], h->stream));
-    CU(cudaEventRecord(h->ev[3], h->stream));
-    if (h->flags & OE_CFG_MATERIALIZE_MATRIX) {
-      expand_overlapped = true;
-      CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));  // before the fork: an allocation would serialise the device
-      h->fork_expand = true;
+    const bool want_matrix = (h->flags & OE_CFG_MATERIALIZE_MATRIX) != 0;
+    const int rows = h->rows_factored();
+    static const bool no_prefix_commit = getenv("OE_NO_PREFIX_COMMIT") != nullptr;
+    if (h->offers_in_flight && h->n_chunks > 1 && h->M > 0 && rows > 0 && !no_prefix_commit && union_commit_fits(h, rows, (h->N + 31) / 32)) {
+      // The offer table is still arriving.  First fit takes the lowest free index, so the commit over the chunks that have
+      // landed already is final for every requirement it places; it runs (highest priority) while the last chunk is on the bus,
+      // and only the requirements it left open are committed over the last chunk afterwards.
+      two_pass = true;
+      const int64_t stride = h->stride();
+      const int64_t wA = h->chunks[h->n_chunks - 2].r1 / 32, wT = (h->N + 31) / 32;
+      CU(h->d_dec.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
+      CU(h->d_dec_sub.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
+      CU(h->d_sub_idx.ensure((size_t)h->M * 4)); CU(h->d_sub_row.ensure((size_t)h->M * 4));
+      if (want_matrix) CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
+      int* h_open = h->h_offer_err + oe_engine::kMaxChunks;
+      const std::function<int()> prefix_commit = [&]() -> int {
+        CU(cudaEventRecord(h->ev_prefix, h->stream));
+        CU(cudaStreamWaitEvent(h->hi_stream, h->ev_prefix, 0));
+        CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->hi_stream));
+        RowBits rbA{};
+        rbA.F = h->d_F.as<uint32_t>(); rbA.stride = stride; rbA.rows = rows; rbA.shard_words = stride; rbA.total_words = wA;
+        if (int rc = commit_union_pass(h, &launches, rbA, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
+        k_collect_unplaced<<<1, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->d_req_row.as<int32_t>(), h->M, h->d_sub_idx.as<int32_t>(),
+                                                         h->d_sub_row.as<int32_t>(), h->d_sub_count.as<int>());
+        ++launches;
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(h_open, h->d_sub_count.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
+        CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
+        tr.mark("prefix_commit_enqueued");
+        return 0;
+      };
+      if (int rc = run_class_feasibility(h, &launches, want_matrix, true, &prefix_commit)) return rc;
+      CU(cudaEventRecord(h->ev[2], h->stream));
+      CU(cudaEventRecord(h->ev[3], h->stream));
+      CU(cudaEventRecord(h->ev_k1_last, h->stream));
+      if (want_matrix) { expand_overlapped = true; CU(cudaEventRecord(h->ev_x1, h->aux_stream)); }
+      tr.mark("pass_enqueued");
+      CU(cudaEventSynchronize(h->ev_phase_a));
+      const int n_open = *h_open;
+      tr.mark("prefix_commit_done");
+      CU(cudaStreamWaitEvent(h->hi_stream, h->ev_k1_last, 0));
+      if (n_open > 0) {
+        RowBits rbB{};
+        rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
+        if (int rc = commit_union_pass(h, &launches, rbB, h->d_sub_row.as<int32_t>(), n_open, h->d_dec_sub.as<oe_decision>(), h->hi_stream, false, false, false)) return rc;
+        k_merge_unplaced<<<(unsigned)((n_open + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec_sub.as<oe_decision>(), h->d_sub_idx.as<int32_t>(), n_open, (int32_t)(wA * 32),
+                                                                                  h->d_dec.as<oe_decision>());
+        ++launches;
+      }
+      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+      ++launches;
+      CU(cudaGetLastError());
+      CU(cudaEventRecord(h->ev_commit, h->hi_stream));
+      CU(cudaStreamWaitEvent(h->stream, h->ev_commit, 0));
+    } else {
+      if (int rc = run_class_feasibility(h, &launches, want_matrix)) return rc;
+      CU(cudaEventRecord(h->ev[2], h->stream));
+      CU(cudaEventRecord(h->ev[3], h->stream));
+      if (want_matrix) {
+        expand_overlapped = true;
+        CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * h->stride(), 1) * 4));  // before the fork: an allocation would serialise the device
+        h->fork_expand = true;
+      }
     }
   }
   tr.mark("pass_enqueued");
-  if (int rc = run_commit(h, &launches)) { h->fork_expand = false; return rc; }
+  if (!two_pass) if (int rc = run_commit(h, &launches)) { h->fork_expand = false; return rc; }
   tr.mark("commit_enqueued");
   CU(cudaEventRecord(h->ev[4], h->stream));
   if (expand_overlapped) {

@@ -15,11 +15,24 @@ from dcos_commons_b200 import tables as tb
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def engine():
-    e = Engine(device=0)
+@pytest.fixture(scope="module", params=["resident", "arriving"])
+def engine(request):
+    """"arriving": OE_CFG_ASYNC_LOADS with the offer table cut into row chunks, so that the cycle commits in two passes — over
+    the chunks that have landed, then the requirements still open over the last chunk — and must reach the same decisions."""
+    import os
+    if request.param == "arriving":
+        old = os.environ.get("OE_OFFER_CHUNKS")
+        os.environ["OE_OFFER_CHUNKS"] = "3"
+        e = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    else:
+        e = Engine(device=0)
     yield e
     e.close()
+    if request.param == "arriving":
+        if old is None:
+            os.environ.pop("OE_OFFER_CHUNKS", None)
+        else:
+            os.environ["OE_OFFER_CHUNKS"] = old
 
 
 def tables_for_rows(rows: np.ndarray, class_seq: np.ndarray) -> abi.CycleTables:
