@@ -16,7 +16,9 @@
 
 #include <algorithm>
 #include <chrono>
+#include <climits>
 #include <cstdarg>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <functional>
@@ -1366,7 +1368,7 @@ struct oe_engine {
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
   DevBuf d_sort_hist, d_comp_begin;
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
-  std::vector<int32_t> h_vcand;
+  std::vector<int32_t> h_vcand, h_vspan;
   DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -2134,12 +2136,31 @@ int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, cons
 namespace {
 // Variants: requirements that have deployed tasks of the same pod type + index (S/offer/TaskUtils.java:136-145) AND
 // whose class reads tallies.  Each gets a factored row of its own (row C + v) evaluated with those tasks taken out.
+// OE_CYCLE_TRACE=1: host-side timestamps of one oe_evaluate_cycle on stderr (where the call's wall time goes)
+struct CycleTrace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  std::string line;
+  CycleTrace() : on(getenv("OE_CYCLE_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char* what) {
+    if (!on) return;
+    char b[64];
+    snprintf(b, sizeof b, " %s=%.3f", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    line += b;
+  }
+  const char* title = "oe cycle";
+  ~CycleTrace() { if (on) fprintf(stderr, "[%s, host ms]%s\n", title, line.c_str()); }
+};
+
+thread_local CycleTrace* g_trace = nullptr;
+
 int rebuild_variants(oe_engine* h) {
   const int64_t M = h->M;
   const int64_t T = (int64_t)h->h_ttype.size();
   // members, not locals: their uploads may still be in flight when this returns (OE_CFG_ASYNC_LOADS)
   std::vector<int32_t>& vcls = h->h_vcls; std::vector<int32_t>& vself_begin = h->h_vself_begin; std::vector<int32_t>& vself_rows = h->h_vself_rows;
   CU(cudaEventSynchronize(h->ev_variants));  // ... and their previous upload must be finished before they are rewritten
+  if (g_trace) g_trace->mark("prev_upload_done");
   vcls.clear(); vself_begin.assign(1, 0); vself_rows.clear();
   h->h_req_row.assign(h->h_class.begin(), h->h_class.end());
   auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
@@ -2162,19 +2183,45 @@ int rebuild_variants(oe_engine* h) {
     // then an open-addressing table pod key -> chain of task rows is built over the tasks that are left.
     auto key_of = [](int32_t type, int32_t index) { return ((uint64_t)(uint32_t)type << 32) | (uint32_t)index; };
     auto mix = [](uint64_t key) { return (key * 0x9E3779B97F4A7C15ull) >> 17; };
+    // Before any hashing: per pod type, the index ranges of the deployed tasks and of the requirements.  Scaling a service out
+    // asks for indices above everything deployed, so the ranges of most (usually all) types are disjoint and nothing can match;
+    // two streaming passes over tables of n_pod_types entries settle that.
+    const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
+    std::vector<int32_t>& span = h->h_vspan;   // [4][n_types]: task min, task max, requirement min, requirement max
+    span.assign(4 * n_types, 0);
+    int32_t *tmin = span.data(), *tmax = tmin + n_types, *rmin = tmax + n_types, *rmax = rmin + n_types;
+    std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
+    std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN);
+    bool odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
+    for (int64_t r = 0; r < T; ++r) {
+      const int32_t ty = h->h_ttype[r], ix = h->h_tindex[r];
+      if (ty < 0 || ix == OE_NO_INDEX) continue;
+      if ((size_t)ty >= n_types) { odd_type = true; continue; }
+      tmin[ty] = std::min(tmin[ty], ix); tmax[ty] = std::max(tmax[ty], ix);
+    }
+    bool any_overlap = odd_type;
+    if (g_trace) g_trace->mark("task_spans");
+    for (int64_t j = 0; j < M; ++j) {
+      if (!h->class_self_sensitive[h->h_class[j]]) continue;
+      const int32_t ty = h->h_rtype[j], ix = h->h_rindex[j];
+      rmin[ty] = std::min(rmin[ty], ix); rmax[ty] = std::max(rmax[ty], ix);
+    }
+    for (size_t ty = 0; ty < n_types && !any_overlap; ++ty) any_overlap = rmin[ty] <= tmax[ty] && tmin[ty] <= rmax[ty];
+    auto may_match = [&](int32_t ty) { return odd_type || (size_t)ty >= n_types || (rmin[ty] <= tmax[ty] && tmin[ty] <= rmax[ty]); };
+    if (any_overlap) {
     size_t fbits = 1u << 16;
     while (fbits < (size_t)M * 32 && fbits < (1u << 24)) fbits <<= 1;
     std::vector<uint64_t>& filter = h->h_vfilter;
     filter.assign(fbits / 64, 0ull);
     for (int64_t j = 0; j < M; ++j) {
-      if (!h->class_self_sensitive[h->h_class[j]]) continue;
+      if (!h->class_self_sensitive[h->h_class[j]] || !may_match(h->h_rtype[j])) continue;
       const uint64_t q = mix(key_of(h->h_rtype[j], h->h_rindex[j])) & (fbits - 1);
       filter[q >> 6] |= 1ull << (q & 63);
     }
     std::vector<int32_t>& cand = h->h_vcand;  // task rows that may match a requirement, ascending
     cand.clear();
     for (int64_t r = 0; r < T; ++r) {
-      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX) continue;
+      if (h->h_ttype[r] < 0 || h->h_tindex[r] == OE_NO_INDEX || !may_match(h->h_ttype[r])) continue;
       const uint64_t q = mix(key_of(h->h_ttype[r], h->h_tindex[r])) & (fbits - 1);
       if ((filter[q >> 6] >> (q & 63)) & 1ull) cand.push_back((int32_t)r);
     }
@@ -2199,7 +2246,7 @@ int rebuild_variants(oe_engine* h) {
       }
       std::vector<int32_t> chain;
       for (int64_t j = 0; j < M; ++j) {
-        if (!h->class_self_sensitive[h->h_class[j]]) continue;
+        if (!h->class_self_sensitive[h->h_class[j]] || !may_match(h->h_rtype[j])) continue;
         const size_t q = slot_of(key_of(h->h_rtype[j], h->h_rindex[j]));
         if (keys[q] == EMPTY) continue;
         chain.clear();
@@ -2207,8 +2254,10 @@ int rebuild_variants(oe_engine* h) {
         if (int rc = add_variant(j, chain.data(), (int)chain.size())) return rc;
       }
     }
+    }  // any_overlap
   }
   h->V = (int)vcls.size();
+  if (g_trace) g_trace->mark("variants");
   // the previous contents of these device buffers may still be read by kernels of the main stream: the side stream starts behind it
   CU(cudaEventRecord(h->ev_side, h->stream));
   if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamWaitEvent(h->side_stream, h->ev_side, 0));
@@ -2229,6 +2278,9 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   CU(cudaSetDevice(h->device));
   h->hasR = false;
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  CycleTrace tr;
+  tr.title = "oe_load_requirements";
+  struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
   const int64_t M = t->n_reqs;
   if (M < 0 || M > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_reqs");
   if (M > 0 && (!t->class_id || !t->pod_type_id || !t->pod_index)) return h->fail(OE_ERR_INVALID, "oe_load_requirements: missing column");
@@ -2241,6 +2293,7 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   h->h_rtype.assign(t->pod_type_id, t->pod_type_id + M);
   h->h_rindex.assign(t->pod_index, t->pod_index + M);
 
+  tr.mark("checked_and_kept");
   h->self_provided = t->self_begin != nullptr;
   h->h_self_begin.clear(); h->h_self_rows.clear();
   if (h->self_provided) {
@@ -2251,6 +2304,7 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
     for (int32_t r : h->h_self_rows) if (r < 0 || r >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
   }
   if (int rc = rebuild_variants(h)) return rc;
+  tr.mark("variants_uploaded");
   if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M, h->side_stream)) return rc;
   if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M, h->side_stream)) return rc;
   if (int rc = join_side_uploads(h)) return rc;
@@ -2266,6 +2320,7 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
     h->h_launch_name.assign(t->launch_name_id, t->launch_name_id + nl);
     h->h_launch_filter.assign(t->launch_filter_bits, t->launch_filter_bits + nl * h->dt.FW);
   }
+  tr.mark("launch_rows_kept");
   if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamSynchronize(h->stream));
   h->hasR = true;
   return OE_OK;
@@ -2450,22 +2505,6 @@ int build_fast_rows(oe_engine* h) {
   return 0;
 }
 
-// OE_CYCLE_TRACE=1: host-side timestamps of one oe_evaluate_cycle on stderr (where the call's wall time goes)
-struct CycleTrace {
-  bool on;
-  std::chrono::steady_clock::time_point t0;
-  std::string line;
-  CycleTrace() : on(getenv("OE_CYCLE_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
-  void mark(const char* what) {
-    if (!on) return;
-    char b[64];
-    snprintf(b, sizeof b, " %s=%.3f", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
-    line += b;
-  }
-  ~CycleTrace() { if (on) fprintf(stderr, "[oe cycle, host ms]%s\n", line.c_str()); }
-};
-
-thread_local CycleTrace* g_trace = nullptr;
 
 int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64_t w0 = 0, int64_t w1 = -1);
 

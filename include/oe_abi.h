@@ -82,7 +82,11 @@ typedef struct {
 /* oe_load_* only ENQUEUE their host→device copies and return; the caller keeps every table buffer alive and unchanged until
  * the next evaluation call on the handle returns (that call reports a malformed id column, which a synchronous load would
  * have reported itself).  With pinned host buffers the upload of the offer table then overlaps the host-side part of the
- * other loads.  Without this flag a load returns only when the caller may reuse its buffers.                             */
+ * other loads AND the evaluation: the table travels in row chunks, every chunk is checked when it has landed, and the next
+ * oe_evaluate_cycle / oe_feasibility / oe_class_feasibility evaluates the landed chunks while the later ones are still on
+ * the bus (oe_evaluate_cycle also commits over them: first fit takes the lowest free index, so what a requirement gets among
+ * the landed offers does not depend on the offers behind them).  Load the offers before the requirements to use it.
+ * Without this flag a load returns only when the caller may reuse its buffers.                                           */
 #define OE_CFG_ASYNC_LOADS 2u
 
 int32_t oe_abi_version(void);
