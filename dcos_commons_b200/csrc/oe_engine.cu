@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   const uint32_t bits = __ballot_sync(0xffffffffu, v);
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
-template <bool REG_RANGES>
+template <bool REG_RANGES, bool PEERS>
 __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx cx, K1Args a) {
   extern __shared__ __align__(16) unsigned char k1_smem[];
   FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
   const oe_rule_node* nodes = a.n_nodes ? s_nodes : cx.p.nodes;
   const double* sc = a.sc_cols ? s_sc : nullptr;
   const int64_t word = i >> 5;
-  __shared__ __align__(16) uint32_t s_words[128][OE_K1_THREADS / 32];  // the CTA's four words of every row of the tile (peer exchange)
+  __shared__ __align__(16) uint32_t s_words[PEERS ? 128 : 1][OE_K1_THREADS / 32];  // the CTA's four words of every row of the tile (peer exchange)
   for (int row = r0; row < r1; ++row) {
     const FastRow& fr = s_fast[row - r0];
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
@@ -257,13 +257,13 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
     const uint32_t bits = __ballot_sync(0xffffffffu, pass);
     if ((threadIdx.x & 31) == 0 && word < a.stride) {
       a.F[(int64_t)row * a.stride + word] = bits;
-      s_words[row - r0][threadIdx.x >> 5] = bits;
+      if (PEERS) s_words[row - r0][threadIdx.x >> 5] = bits;
     }
   }
   // The all-gather of a sharded cycle, fused into the pass: the CTA stores its 16 bytes of every row straight into every
   // shard's exchange buffer (one 128-bit store per row and shard), so the rows cross NVLink while the other CTAs still compute
   // and no collective runs afterwards — k_peer_signal / k_peer_wait order the readers behind these stores.
-  if (a.peers.n > 0) {
+  if (PEERS) {
     __syncthreads();
     const int64_t w0 = (a.xb0 + blockIdx.x) * (OE_K1_THREADS / 32);
     const int nrows = r1 - r0;
@@ -1158,29 +1158,23 @@ __global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
 // left without an offer, in plan order.  sub_idx[k] = requirement, sub_row[k] = its bit row, *count = how many.  One CTA.
 __global__ void __launch_bounds__(1024) k_collect_unplaced(const oe_decision* __restrict__ dec, const int32_t* __restrict__ req_row, int64_t M,
                                                            int32_t* __restrict__ sub_idx, int32_t* __restrict__ sub_row, int* __restrict__ count) {
+  // thread t owns the contiguous run [t * per, (t + 1) * per): count, one block-wide scan of the counts, then write the run
   __shared__ int warp_tot[32];
-  __shared__ int carry_s;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
+  const int64_t per = (M + 1023) / 1024;
+  const int64_t j0 = min(M, (int64_t)threadIdx.x * per), j1 = min(M, j0 + per);
+  int mine = 0;
+  for (int64_t j = j0; j < j1; ++j) mine += dec[j].offer_row < 0;
+  int incl = mine;
+  for (int d = 1; d < 32; d <<= 1) { const int n = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += n; }
+  if (lane == 31) warp_tot[warp] = incl;
   __syncthreads();
-  for (int64_t j0 = 0; j0 < M; j0 += 1024) {
-    const int64_t j = j0 + threadIdx.x;
-    const bool open = j < M && dec[j].offer_row < 0;
-    const uint32_t b = __ballot_sync(0xffffffffu, open);
-    if (lane == 0) warp_tot[warp] = __popc(b);
-    __syncthreads();
-    int before = carry_s;
-    for (int w = 0; w < warp; ++w) before += warp_tot[w];
-    if (open) {
-      const int k = before + __popc(b & ((1u << lane) - 1u));
-      sub_idx[k] = (int32_t)j;
-      sub_row[k] = req_row[j];
-    }
-    __syncthreads();
-    if (threadIdx.x == 1023) carry_s = before + __popc(b);
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) *count = carry_s;
+  int before = incl - mine;
+  for (int w = 0; w < warp; ++w) before += warp_tot[w];
+  if (threadIdx.x == 1023) *count = before + mine;
+  if (mine)
+    for (int64_t j = j0; j < j1; ++j)
+      if (dec[j].offer_row < 0) { sub_idx[before] = (int32_t)j; sub_row[before] = req_row[j]; ++before; }
 }
 // ... and what the pass over the rest of the offers found for them (its offer indices start at `offset`).
 __global__ void k_merge_unplaced(const oe_decision* __restrict__ dec_sub, const int32_t* __restrict__ sub_idx, int n, int32_t offset, oe_decision* __restrict__ dec) {
@@ -2567,8 +2561,14 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
         if (g_trace) g_trace->mark("chunk");
       }
       dim3 grid((unsigned)xblocks, (unsigned)tiles);
-      if (h->dof.R <= OE_FAST_RANGES) k_class_feasibility<true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-      else k_class_feasibility<false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      const bool fast_ranges = h->dof.R <= OE_FAST_RANGES;
+      if (h->peers_attached) {
+        if (fast_ranges) k_class_feasibility<true, true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+        else k_class_feasibility<false, true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      } else {
+        if (fast_ranges) k_class_feasibility<true, false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+        else k_class_feasibility<false, false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      }
       ++*launches;
       CU(cudaGetLastError());
       if (expand_beside && (c + 1 < n_chunks || expand_last)) {
