@@ -387,6 +387,27 @@ def run_engine(args):
         e2e["decisions_only"] = {"cycle_latency_ms": 1e3 * (time.perf_counter() - t0) / e2e_steps,
                                  "device_ms": {k: st3[k] for k in ("ms_counters", "ms_feasibility", "ms_commit", "ms_d2h")},
                                  "note": "same tables and copies, OE_CFG_MATERIALIZE_MATRIX off: K0 + K1 + commit, the N x M matrix stays factored"}
+        # steady state (INTEGRATION.md "Offers that change between cycles"): the table stays resident, 1 % of the offers changed
+        # since the last cycle and arrive through oe_update_offers; tasks unchanged; new requirements; decisions only
+        import ctypes as C
+        rng = np.random.Generator(np.random.PCG64(7))
+        changed = np.sort(rng.choice(N, max(1, N // 100), replace=False)).astype(np.int64)
+        small = pt.c_offer_rows(changed)               # the adapter's encoding of the changed offers, prepared outside the timing
+        upd = eng3.b.fn("update_offers")
+        upd.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+
+        def cycle_steady():
+            eng3._check(upd(eng3.h, changed.ctypes.data, len(changed), C.byref(small)))
+            eng3.load_requirements(pt)
+            return eng3.evaluate_cycle_into(out.data_ptr())
+        for _ in range(2):
+            cycle_steady()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            st4 = cycle_steady()
+        e2e["steady_state"] = {"cycle_latency_ms": 1e3 * (time.perf_counter() - t0) / e2e_steps, "changed_offers": int(len(changed)),
+                               "device_ms": {k: st4[k] for k in ("ms_counters", "ms_feasibility", "ms_commit", "ms_d2h")},
+                               "note": "resident offer table, 1 % of the rows replaced through oe_update_offers, requirements reloaded, decisions only"}
         eng3.close()
 
     if rank != 0:

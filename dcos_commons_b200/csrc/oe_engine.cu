@@ -1155,26 +1155,40 @@ __global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
 }
 
 // Commit in two passes (the offer table still arriving, see oe_evaluate_cycle): the requirements that the pass over the prefix
-// left without an offer, in plan order.  sub_idx[k] = requirement, sub_row[k] = its bit row, *count = how many.  One CTA.
+// left without an offer, in plan order.  sub_idx[k] = requirement, sub_row[k] = its bit row, *count = how many.
+__global__ void __launch_bounds__(1024) k_count_unplaced(const oe_decision* __restrict__ dec, int64_t M, int* __restrict__ tile_open) {
+  const int64_t j = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+  const int n = __syncthreads_count(j < M && dec[j].offer_row < 0);
+  if (threadIdx.x == 0) tile_open[blockIdx.x] = n;
+}
 __global__ void __launch_bounds__(1024) k_collect_unplaced(const oe_decision* __restrict__ dec, const int32_t* __restrict__ req_row, int64_t M,
-                                                           int32_t* __restrict__ sub_idx, int32_t* __restrict__ sub_row, int* __restrict__ count) {
-  // thread t owns the contiguous run [t * per, (t + 1) * per): count, one block-wide scan of the counts, then write the run
+                                                           const int* __restrict__ tile_open, int32_t* __restrict__ sub_idx, int32_t* __restrict__ sub_row,
+                                                           int* __restrict__ count) {
+  // tile = 1024 requirements; its base = the open ones of the tiles before it (every CTA adds those up itself)
   __shared__ int warp_tot[32];
+  __shared__ int base_s;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t per = (M + 1023) / 1024;
-  const int64_t j0 = min(M, (int64_t)threadIdx.x * per), j1 = min(M, j0 + per);
-  int mine = 0;
-  for (int64_t j = j0; j < j1; ++j) mine += dec[j].offer_row < 0;
-  int incl = mine;
-  for (int d = 1; d < 32; d <<= 1) { const int n = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += n; }
-  if (lane == 31) warp_tot[warp] = incl;
+  int part = 0;
+  for (int t = threadIdx.x; t < (int)blockIdx.x; t += 1024) part += tile_open[t];
+  for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+  if (lane == 0) warp_tot[warp] = part;
   __syncthreads();
-  int before = incl - mine;
+  if (threadIdx.x == 0) { int b = 0; for (int w = 0; w < 32; ++w) b += warp_tot[w]; base_s = b; }
+  __syncthreads();
+  const int64_t j = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+  const bool open = j < M && dec[j].offer_row < 0;
+  const uint32_t b = __ballot_sync(0xffffffffu, open);
+  __syncthreads();
+  if (lane == 0) warp_tot[warp] = __popc(b);
+  __syncthreads();
+  int before = base_s;
   for (int w = 0; w < warp; ++w) before += warp_tot[w];
-  if (threadIdx.x == 1023) *count = before + mine;
-  if (mine)
-    for (int64_t j = j0; j < j1; ++j)
-      if (dec[j].offer_row < 0) { sub_idx[before] = (int32_t)j; sub_row[before] = req_row[j]; ++before; }
+  if (open) {
+    const int k = before + __popc(b & ((1u << lane) - 1u));
+    sub_idx[k] = (int32_t)j;
+    sub_row[k] = req_row[j];
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 1023) *count = before + __popc(b);
 }
 // ... and what the pass over the rest of the offers found for them (its offer indices start at `offset`).
 __global__ void k_merge_unplaced(const oe_decision* __restrict__ dec_sub, const int32_t* __restrict__ sub_idx, int n, int32_t offset, oe_decision* __restrict__ dec) {
@@ -1381,7 +1395,7 @@ struct oe_engine {
   cudaEvent_t ev_main = nullptr, ev_k1[kMaxChunks]{};
   DevBuf d_offer_err;                // one flag per chunk, read back into h_offer_err behind the chunk's checks
   int* h_offer_err = nullptr;        // pinned
-  DevBuf d_sub_idx, d_sub_row, d_dec_sub, d_sub_count;   // commit in two passes: the requirements left open by the prefix pass
+  DevBuf d_sub_idx, d_sub_row, d_dec_sub, d_sub_count, d_tile_open;   // commit in two passes: the requirements left open by the prefix pass
   cudaEvent_t ev_prefix = nullptr, ev_phase_a = nullptr, ev_k1_last = nullptr;
   char* pin_arena = nullptr;         // pinned staging for the engine's own (pageable) host tables while offers are in flight
   size_t pin_cap = 0, pin_used = 0;
@@ -1654,7 +1668,7 @@ void oe_destroy(oe_engine* h) {
   }
   if (h->ev_main) cudaEventDestroy(h->ev_main);
   for (cudaEvent_t e : {h->ev_prefix, h->ev_phase_a, h->ev_k1_last}) if (e) cudaEventDestroy(e);
-  h->d_sub_idx.release(); h->d_sub_row.release(); h->d_dec_sub.release(); h->d_sub_count.release();
+  h->d_sub_idx.release(); h->d_sub_row.release(); h->d_dec_sub.release(); h->d_sub_count.release(); h->d_tile_open.release();
   if (h->h_offer_err) cudaFreeHost(h->h_offer_err);
   if (h->pin_arena) cudaFreeHost(h->pin_arena);
   h->d_offer_err.release();
@@ -2927,6 +2941,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       CU(h->d_dec.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_dec_sub.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_sub_idx.ensure((size_t)h->M * 4)); CU(h->d_sub_row.ensure((size_t)h->M * 4));
+      CU(h->d_tile_open.ensure(((size_t)h->M + 1023) / 1024 * 4));
       if (want_matrix) CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
       int* h_open = h->h_offer_err + oe_engine::kMaxChunks;
       const std::function<int()> prefix_commit = [&]() -> int {
@@ -2936,9 +2951,11 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
         RowBits rbA{};
         rbA.F = h->d_F.as<uint32_t>(); rbA.stride = stride; rbA.rows = rows; rbA.shard_words = stride; rbA.total_words = wA;
         if (int rc = commit_union_pass(h, &launches, rbA, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
-        k_collect_unplaced<<<1, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->d_req_row.as<int32_t>(), h->M, h->d_sub_idx.as<int32_t>(),
-                                                         h->d_sub_row.as<int32_t>(), h->d_sub_count.as<int>());
-        ++launches;
+        const unsigned n_tiles = (unsigned)((h->M + 1023) / 1024);
+        k_count_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M, h->d_tile_open.as<int>());
+        k_collect_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->d_req_row.as<int32_t>(), h->M, h->d_tile_open.as<int>(),
+                                                               h->d_sub_idx.as<int32_t>(), h->d_sub_row.as<int32_t>(), h->d_sub_count.as<int>());
+        launches += 2;
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(h_open, h->d_sub_count.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
         CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
