@@ -564,9 +564,11 @@ struct RuleTab {
   int words, zdim;
 };
 
-template <bool REG_RANGES>
+// NQ = pool entries kept in registers and tested by the dense form (4 when S*K <= 4, else 8).  tab_word / tab_bit: where the
+// tabulated rule verdict of this (row, zone, region) sits — the caller advances the pointer from row to row.
+template <bool REG_RANGES, int NQ>
 __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* nodes, const FastRow& fr, const double* sc, int64_t i,
-                                          const OfferRegs& r, int var, const RuleTab& tab, int row) {
+                                          const OfferRegs& r, int var, const uint32_t* tab_word, int tab_bit) {
   const DevOffers& o = cx.o;
   bool pass = !(fr.flags & OE_FR_NEVER);
   uint32_t present = r.present;
@@ -578,7 +580,7 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
     const uint32_t need = *reinterpret_cast<const uint32_t*>(fr.thr_q);
     pass = pass && (present & need) == need;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) pass = pass && !(r.sv[q] < fr.thr[q]);
+    for (int q = 0; q < NQ; ++q) pass = pass && !(r.sv[q] < fr.thr[q]);
   } else {
     for (int t = 0; t < fr.n_thr; ++t) {
       const int q = fr.thr_q[t];
@@ -598,16 +600,15 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
         pool_ports += b <= e ? e - b + 1 : 0;
       }
     }
-    for (int u = 0; u < fr.n_ports; ++u) {
-      const bool m = port_member(o, i, REG_RANGES, r, fr.port[u]);
-      listed += m;
-      statics = statics && (m || !((fr.static_mask >> u) & 1u));
-    }
+    uint32_t member = 0u, bit = 1u;   // bit u: listed port u is offered
+    for (int u = 0; u < fr.n_ports; ++u, bit <<= 1)
+      if (port_member(o, i, REG_RANGES, r, fr.port[u])) member |= bit;
+    listed = __popc(member);
+    statics = (member & fr.static_mask) == fr.static_mask;
     pass = pass && statics && (pool_ports - listed >= (int)fr.n_dyn);
   }
   if (fr.flags & OE_FR_RULE_TAB) {
-    const int idx = (r.ok.region + 1) * tab.zdim + (r.ok.zone + 1);
-    pass = pass && ((__ldg(tab.bits + (int64_t)row * tab.words + (idx >> 5)) >> (idx & 31)) & 1u);
+    pass = pass && ((__ldg(tab_word) >> tab_bit) & 1u);
   } else if (fr.rule_count > 0) {
     pass = pass && eval_rule(cx, nodes, i, r.ok, var, fr.rule_begin, fr.rule_count);
   }

@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   const uint32_t bits = __ballot_sync(0xffffffffu, v);
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
-template <bool REG_RANGES, bool PEERS>
+template <bool REG_RANGES, bool PEERS, int NQ>
 __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx cx, K1Args a) {
   extern __shared__ __align__(16) unsigned char k1_smem[];
   FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
@@ -244,19 +244,26 @@ __global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx c
   const double* sc = a.sc_cols ? s_sc : nullptr;
   const int64_t word = i >> 5;
   __shared__ __align__(16) uint32_t s_words[PEERS ? 128 : 1][OE_K1_THREADS / 32];  // the CTA's four words of every row of the tile (peer exchange)
-  for (int row = r0; row < r1; ++row) {
-    const FastRow& fr = s_fast[row - r0];
+  // what changes from row to row is kept as running pointers: the row's descriptor, its output word, its rule-table word
+  const bool writer = (threadIdx.x & 31) == 0 && word < a.stride;
+  uint32_t* out = a.F + (int64_t)r0 * a.stride + word;
+  const int tab_idx = (regs.ok.region + 1) * a.tab.zdim + (regs.ok.zone + 1);
+  const int tab_bit = tab_idx & 31;
+  const uint32_t* tab_word = a.tab.bits + (int64_t)r0 * a.tab.words + (tab_idx >> 5);
+  const FastRow* frp = s_fast;
+  for (int row = r0; row < r1; ++row, ++frp, out += a.stride, tab_word += a.tab.words) {
+    const FastRow& fr = *frp;
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
     bool pass = false;
     if (fr.flags & OE_FR_FAST) {
-      if (valid) pass = eval_fast<REG_RANGES>(cx, nodes, fr, sc, i, regs, var, a.tab, row);
+      if (valid) pass = eval_fast<REG_RANGES, NQ>(cx, nodes, fr, sc, i, regs, var, tab_word, tab_bit);
     } else if (valid) {
       const int cls = var < 0 ? row : cx.v.cls[var];
       pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
     }
     const uint32_t bits = __ballot_sync(0xffffffffu, pass);
-    if ((threadIdx.x & 31) == 0 && word < a.stride) {
-      a.F[(int64_t)row * a.stride + word] = bits;
+    if (writer) {
+      *out = bits;
       if (PEERS) s_words[row - r0][threadIdx.x >> 5] = bits;
     }
   }
@@ -2576,12 +2583,17 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       }
       dim3 grid((unsigned)xblocks, (unsigned)tiles);
       const bool fast_ranges = h->dof.R <= OE_FAST_RANGES;
-      if (h->peers_attached) {
-        if (fast_ranges) k_class_feasibility<true, true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-        else k_class_feasibility<false, true><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-      } else {
-        if (fast_ranges) k_class_feasibility<true, false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
-        else k_class_feasibility<false, false><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a);
+      const bool few = h->dof.S * h->dof.K <= 4;   // the dense form then tests four pool entries, not eight
+      const int variant = (fast_ranges ? 4 : 0) | (h->peers_attached ? 2 : 0) | (few ? 1 : 0);
+      switch (variant) {
+        case 7: k_class_feasibility<true, true, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 6: k_class_feasibility<true, true, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 5: k_class_feasibility<true, false, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 4: k_class_feasibility<true, false, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 3: k_class_feasibility<false, true, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 2: k_class_feasibility<false, true, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        case 1: k_class_feasibility<false, false, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        default: k_class_feasibility<false, false, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
       }
       ++*launches;
       CU(cudaGetLastError());
