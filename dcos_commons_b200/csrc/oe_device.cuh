@@ -557,6 +557,27 @@ __device__ __forceinline__ bool port_member(const DevOffers& o, int64_t i, bool 
   return m;
 }
 
+// `bit` if port p lies in one of the eight register-held ranges, else 0.  Written as PTX so that the eight tests stay one
+// subtract and one predicate-accumulating compare each (the compiler's own choice for the C++ form was a chain of selects).
+__device__ __forceinline__ uint32_t port_member_bit(const OfferRegs& r, uint32_t p, uint32_t bit) {
+  static_assert(OE_FAST_RANGES == 8, "port_member_bit tests eight ranges");
+  uint32_t out;
+  asm("{\n\t.reg .pred q;\n\t.reg .u32 t;\n\t"
+      "sub.u32 t, %1, %2;\n\tsetp.le.u32 q, t, %3;\n\t"
+      "sub.u32 t, %1, %4;\n\tsetp.le.or.u32 q, t, %5, q;\n\t"
+      "sub.u32 t, %1, %6;\n\tsetp.le.or.u32 q, t, %7, q;\n\t"
+      "sub.u32 t, %1, %8;\n\tsetp.le.or.u32 q, t, %9, q;\n\t"
+      "sub.u32 t, %1, %10;\n\tsetp.le.or.u32 q, t, %11, q;\n\t"
+      "sub.u32 t, %1, %12;\n\tsetp.le.or.u32 q, t, %13, q;\n\t"
+      "sub.u32 t, %1, %14;\n\tsetp.le.or.u32 q, t, %15, q;\n\t"
+      "sub.u32 t, %1, %16;\n\tsetp.le.or.u32 q, t, %17, q;\n\t"
+      "selp.u32 %0, %18, 0, q;\n\t}"
+      : "=r"(out)
+      : "r"(p), "r"(r.rb[0]), "r"(r.rlen[0]), "r"(r.rb[1]), "r"(r.rlen[1]), "r"(r.rb[2]), "r"(r.rlen[2]), "r"(r.rb[3]), "r"(r.rlen[3]),
+        "r"(r.rb[4]), "r"(r.rlen[4]), "r"(r.rb[5]), "r"(r.rlen[5]), "r"(r.rb[6]), "r"(r.rlen[6]), "r"(r.rb[7]), "r"(r.rlen[7]), "r"(bit));
+  return out;
+}
+
 // `sc` = this CTA's shared-memory copy of the scalar columns, [S*K][blockDim.x], or nullptr (read through L1 instead).
 // Rule verdicts tabulated over (zone, region): bit (region + 1) * zdim + (zone + 1) of row `row` (absent = -1 -> 0).
 struct RuleTab {
@@ -570,17 +591,19 @@ template <bool REG_RANGES, int NQ>
 __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* nodes, const FastRow& fr, const double* sc, int64_t i,
                                           const OfferRegs& r, int var, const uint32_t* tab_word, int tab_bit) {
   const DevOffers& o = cx.o;
+  // every test is evaluated and AND-ed (no short circuit): a branch per test costs more than the test, and a compare that feeds
+  // a branch cannot overlap with the next one
   bool pass = !(fr.flags & OE_FR_NEVER);
   uint32_t present = r.present;
   if (fr.flags & OE_FR_NEEDS_POOL) {
     // consumableResource (MesosResourcePool.java:87-97)
-    pass = pass && !(fr.pod_role >= 0 && r.alloc >= 0 && r.alloc != fr.pod_role);
+    pass &= !((fr.pod_role >= 0) & (r.alloc >= 0) & (r.alloc != fr.pod_role));
   }
   if (fr.flags & OE_FR_DENSE) {
     const uint32_t need = *reinterpret_cast<const uint32_t*>(fr.thr_q);
-    pass = pass && (present & need) == need;
+    pass &= (present & need) == need;
 #pragma unroll
-    for (int q = 0; q < NQ; ++q) pass = pass && !(r.sv[q] < fr.thr[q]);
+    for (int q = 0; q < NQ; ++q) pass &= !(r.sv[q] < fr.thr[q]);
   } else {
     for (int t = 0; t < fr.n_thr; ++t) {
       const int q = fr.thr_q[t];
@@ -601,14 +624,16 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
       }
     }
     uint32_t member = 0u, bit = 1u;   // bit u: listed port u is offered
-    for (int u = 0; u < fr.n_ports; ++u, bit <<= 1)
-      if (port_member(o, i, REG_RANGES, r, fr.port[u])) member |= bit;
+    for (int u = 0; u < fr.n_ports; ++u, bit <<= 1) {
+      if (REG_RANGES) member |= port_member_bit(r, fr.port[u], bit);
+      else if (port_member(o, i, false, r, fr.port[u])) member |= bit;
+    }
     listed = __popc(member);
     statics = (member & fr.static_mask) == fr.static_mask;
-    pass = pass && statics && (pool_ports - listed >= (int)fr.n_dyn);
+    pass &= statics & (pool_ports - listed >= (int)fr.n_dyn);
   }
   if (fr.flags & OE_FR_RULE_TAB) {
-    pass = pass && ((__ldg(tab_word) >> tab_bit) & 1u);
+    pass &= (bool)((__ldg(tab_word) >> tab_bit) & 1u);
   } else if (fr.rule_count > 0) {
     pass = pass && eval_rule(cx, nodes, i, r.ok, var, fr.rule_begin, fr.rule_count);
   }
