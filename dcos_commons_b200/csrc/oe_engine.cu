@@ -172,6 +172,9 @@ __global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __
 // its offer's keys and port ranges into registers once and then walks the tile's rows.  Each warp emits one 32-offer
 // word per row with __ballot_sync.  gridDim.x covers the padded stride so every word is written.
 #define OE_K1_THREADS 128
+#ifndef OE_K1_MIN_CTAS
+#define OE_K1_MIN_CTAS 6
+#endif
 #define OE_K1_MAX_SMEM_NODES 1024
 #define OE_PEER_MAX_WORLD 16
 #define OE_PEER_HEADER_WORDS 64  // the flag words in front of an exchange buffer (256 B)
@@ -213,7 +216,7 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
 template <bool REG_RANGES, bool PEERS, int NQ>
-__global__ void __launch_bounds__(OE_K1_THREADS, 6) k_class_feasibility(DevCtx cx, K1Args a) {
+__global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibility(DevCtx cx, K1Args a) {
   extern __shared__ __align__(16) unsigned char k1_smem[];
   FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
   oe_rule_node* s_nodes = reinterpret_cast<oe_rule_node*>(s_fast + a.rows_per_tile);
