@@ -1472,7 +1472,7 @@ namespace {
 // While the offer table is on the bus: a table of up to 16 MB that lives in pinned (device-visible) host memory is fetched by
 // a kernel, not queued behind the offers on the copy engine (see k_fetch_host).  Pageable sources keep the plain copy.
 bool fetch_instead_of_copy(oe_engine* h, void* dst, const void* src, size_t bytes, cudaStream_t on) {
-  if (!h->offers_in_flight || bytes < 4096 || bytes > ((size_t)16 << 20)) return false;
+  if (!h->offers_in_flight || bytes < 4096 || bytes > ((size_t)16 << 20) || (reinterpret_cast<uintptr_t>(dst) & 15)) return false;
   cudaPointerAttributes at{};
   if (cudaPointerGetAttributes(&at, src) != cudaSuccess) { cudaGetLastError(); return false; }
   if (at.type != cudaMemoryTypeHost || !at.devicePointer || (reinterpret_cast<uintptr_t>(at.devicePointer) & 15)) {
@@ -1856,7 +1856,7 @@ namespace {
 int reserve_tasks(oe_engine* h, int64_t cap, int64_t keep) {
   DevTasks& t = h->dt;
   if (cap <= t.cap) return 0;
-  cap = cap + cap / 4 + 64;
+  cap = (cap + cap / 4 + 64 + 3) / 4 * 4;   // slots of a column stay 16-byte aligned
   auto grow = [&](DevBuf& b, int slots, void** field) -> int {
     DevBuf nb;
     CU(nb.ensure((size_t)cap * slots * 4));

@@ -211,6 +211,34 @@ def test_async_offer_table_arrives_and_is_evaluated_in_row_chunks(flags, monkeyp
     eng.close(); ref.close()
 
 
+def test_small_tables_fetched_from_pinned_host_memory_while_offers_arrive():
+    """OE_CFG_ASYNC_LOADS with every column in pinned memory (what bench.py and a JNI adapter with registered direct buffers do): the
+    task and requirement tables are read by k_fetch_host while the offer chunks are on the bus.  Odd sizes: 16-byte tails, columns
+    whose slots are not 16-byte aligned among themselves."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    eng = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    ref = Engine(device=0)
+    for seed, (n, m, dep) in enumerate(((30001, 3001, 2501), (17003, 1999, 4099), (9000, 1500, 1237))):
+        t = synth.make_cluster(n, m, 8, 3, 4, dep, "c5", seed=40 + seed).tables
+        t.normalise()
+        pt = bench.pin_tables(t)
+        want, _ = ref.load(t).evaluate_cycle()
+        for order in ("tasks-first", "offers-first"):
+            eng.tables = pt
+            eng.load_programs(pt)
+            if order == "tasks-first":
+                eng.load_tasks(pt)
+            eng.load_offers(pt)
+            if order != "tasks-first":
+                eng.load_tasks(pt)
+            eng.load_requirements(pt)
+            got, _ = eng.evaluate_cycle()
+            assert got.tobytes() == want.tobytes(), (seed, order)
+    eng.close(); ref.close()
+
+
 def _patched(t, rows, src_rows):
     """A copy of the tables whose offer rows `rows` hold what rows `src_rows` held."""
     import copy
