@@ -1387,6 +1387,7 @@ struct oe_engine {
   DevBuf d_sort_hist, d_comp_begin;
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
   std::vector<int32_t> h_vcand, h_vspan;
+  bool task_spans_valid = false, task_odd_type = false;
   DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -1716,6 +1717,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   if (C < 0 || C > OE_MAX_CLASSES) return h->fail(OE_ERR_LIMIT, "n_classes %d exceeds OE_MAX_CLASSES", C);
   if (!t->op_begin || (t->n_ops && !t->ops) || (C > 0 && !t->pod_role) || !t->port_excl_begin)
     return h->fail(OE_ERR_INVALID, "oe_load_programs: missing column");
+  h->task_spans_valid = false;
   const oe_dict_sizes& d = t->dict;
   if (d.n_agents < 0 || d.n_hostnames < 0 || d.n_zones < 0 || d.n_regions < 0 || d.n_attrs < 0 || d.n_rr_values < 0 ||
       d.n_pod_types < 0 || d.n_filters < 0)
@@ -1924,6 +1926,7 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   for (int q = 0; q < d.Q; ++q) check_ids(h, d.rr + (size_t)q * d.cap, T, -1, dc.n_rr_values, 7);
   h->h_tname.assign(t->name_id, t->name_id + T);
   h->h_ttype.assign(t->pod_type_id, t->pod_type_id + T);
+  h->task_spans_valid = false;
   h->h_tindex.assign(t->pod_index, t->pod_index + T);
   h->name_to_row.clear();
   h->name_map_built = false;  // only oe_apply_launches needs it: built on first use
@@ -2206,17 +2209,21 @@ int rebuild_variants(oe_engine* h) {
     // two streaming passes over tables of n_pod_types entries settle that.
     const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
     std::vector<int32_t>& span = h->h_vspan;   // [4][n_types]: task min, task max, requirement min, requirement max
-    span.assign(4 * n_types, 0);
+    if (span.size() != 4 * n_types) { span.assign(4 * n_types, 0); h->task_spans_valid = false; }
     int32_t *tmin = span.data(), *tmax = tmin + n_types, *rmin = tmax + n_types, *rmax = rmin + n_types;
-    std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
     std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN);
-    bool odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
-    for (int64_t r = 0; r < T; ++r) {
-      const int32_t ty = h->h_ttype[r], ix = h->h_tindex[r];
-      if (ty < 0 || ix == OE_NO_INDEX) continue;
-      if ((size_t)ty >= n_types) { odd_type = true; continue; }
-      tmin[ty] = std::min(tmin[ty], ix); tmax[ty] = std::max(tmax[ty], ix);
+    if (!h->task_spans_valid) {   // the tasks' half only changes with the task table (oe_load_tasks, oe_apply_launches)
+      std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
+      h->task_odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
+      for (int64_t r = 0; r < T; ++r) {
+        const int32_t ty = h->h_ttype[r], ix = h->h_tindex[r];
+        if (ty < 0 || ix == OE_NO_INDEX) continue;
+        if ((size_t)ty >= n_types) { h->task_odd_type = true; continue; }
+        tmin[ty] = std::min(tmin[ty], ix); tmax[ty] = std::max(tmax[ty], ix);
+      }
+      h->task_spans_valid = true;
     }
+    const bool odd_type = h->task_odd_type;
     bool any_overlap = odd_type;
     if (g_trace) g_trace->mark("task_spans");
     for (int64_t j = 0; j < M; ++j) {
@@ -3138,6 +3145,7 @@ int32_t oe_apply_launches(oe_engine* h) {
         row = it->second;
       }
       h->h_ttype[row] = h->h_rtype[j];
+      h->task_spans_valid = false;
       h->h_tindex[row] = h->h_rindex[j];
       dst.push_back(row); req.push_back((int32_t)j); name.push_back(nm);
       for (int w = 0; w < FW; ++w) filt.push_back(h->h_launch_filter[(size_t)l * FW + w]);
