@@ -1387,7 +1387,7 @@ struct oe_engine {
   DevBuf d_sort_hist, d_comp_begin;
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
   std::vector<int32_t> h_vcand, h_vspan;
-  bool task_spans_valid = false, task_odd_type = false;
+  bool task_spans_valid = false, task_odd_type = false, req_spans_valid = false;
   DevBuf d_stage, d_stage_rows;      // oe_update_offers: the changed rows on their way into the resident table
   bool counters_fresh = false, class_bits_fresh = false, cycle_done = false;
   std::vector<oe_decision> h_last_dec;
@@ -1717,7 +1717,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   if (C < 0 || C > OE_MAX_CLASSES) return h->fail(OE_ERR_LIMIT, "n_classes %d exceeds OE_MAX_CLASSES", C);
   if (!t->op_begin || (t->n_ops && !t->ops) || (C > 0 && !t->pod_role) || !t->port_excl_begin)
     return h->fail(OE_ERR_INVALID, "oe_load_programs: missing column");
-  h->task_spans_valid = false;
+  h->task_spans_valid = h->req_spans_valid = false;
   const oe_dict_sizes& d = t->dict;
   if (d.n_agents < 0 || d.n_hostnames < 0 || d.n_zones < 0 || d.n_regions < 0 || d.n_attrs < 0 || d.n_rr_values < 0 ||
       d.n_pod_types < 0 || d.n_filters < 0)
@@ -2209,9 +2209,9 @@ int rebuild_variants(oe_engine* h) {
     // two streaming passes over tables of n_pod_types entries settle that.
     const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
     std::vector<int32_t>& span = h->h_vspan;   // [4][n_types]: task min, task max, requirement min, requirement max
-    if (span.size() != 4 * n_types) { span.assign(4 * n_types, 0); h->task_spans_valid = false; }
+    if (span.size() != 4 * n_types) { span.assign(4 * n_types, 0); h->task_spans_valid = h->req_spans_valid = false; }
     int32_t *tmin = span.data(), *tmax = tmin + n_types, *rmin = tmax + n_types, *rmax = rmin + n_types;
-    std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN);
+    if (!h->req_spans_valid) { std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN); }
     if (!h->task_spans_valid) {   // the tasks' half only changes with the task table (oe_load_tasks, oe_apply_launches)
       std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
       h->task_odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
@@ -2226,10 +2226,13 @@ int rebuild_variants(oe_engine* h) {
     const bool odd_type = h->task_odd_type;
     bool any_overlap = odd_type;
     if (g_trace) g_trace->mark("task_spans");
-    for (int64_t j = 0; j < M; ++j) {
-      if (!h->class_self_sensitive[h->h_class[j]]) continue;
-      const int32_t ty = h->h_rtype[j], ix = h->h_rindex[j];
-      rmin[ty] = std::min(rmin[ty], ix); rmax[ty] = std::max(rmax[ty], ix);
+    if (!h->req_spans_valid) {
+      for (int64_t j = 0; j < M; ++j) {
+        if (!h->class_self_sensitive[h->h_class[j]]) continue;
+        const int32_t ty = h->h_rtype[j], ix = h->h_rindex[j];
+        rmin[ty] = std::min(rmin[ty], ix); rmax[ty] = std::max(rmax[ty], ix);
+      }
+      h->req_spans_valid = true;
     }
     for (size_t ty = 0; ty < n_types && !any_overlap; ++ty) any_overlap = rmin[ty] <= tmax[ty] && tmin[ty] <= rmax[ty];
     auto may_match = [&](int32_t ty) { return odd_type || (size_t)ty >= n_types || (rmin[ty] <= tmax[ty] && tmin[ty] <= rmax[ty]); };
@@ -2309,14 +2312,24 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   const int64_t M = t->n_reqs;
   if (M < 0 || M > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_reqs");
   if (M > 0 && (!t->class_id || !t->pod_type_id || !t->pod_index)) return h->fail(OE_ERR_INVALID, "oe_load_requirements: missing column");
+  // one pass: the id checks, the host copies, and per pod type the index range of the requirements whose class reads tallies
+  // (rebuild_variants compares it with the deployed tasks' range before it hashes anything)
+  const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
+  if (h->h_vspan.size() != 4 * n_types) { h->h_vspan.assign(4 * n_types, 0); h->task_spans_valid = false; }
+  int32_t *rmin = h->h_vspan.data() + 2 * n_types, *rmax = rmin + n_types;
+  std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN);
+  h->req_spans_valid = false;
+  h->h_class.resize((size_t)M); h->h_rtype.resize((size_t)M); h->h_rindex.resize((size_t)M);
+  const bool sensitive_known = h->class_self_sensitive.size() == (size_t)h->C;
   for (int64_t j = 0; j < M; ++j) {
-    if (t->class_id[j] < 0 || t->class_id[j] >= h->C) return h->fail(OE_ERR_INVALID, "requirement %lld: class id %d", (long long)j, t->class_id[j]);
-    if (t->pod_type_id[j] < 0 || t->pod_type_id[j] >= std::max(h->dict.n_pod_types, 1)) return h->fail(OE_ERR_INVALID, "requirement %lld: pod type", (long long)j);
+    const int32_t c = t->class_id[j], ty = t->pod_type_id[j], ix = t->pod_index[j];
+    if (c < 0 || c >= h->C) return h->fail(OE_ERR_INVALID, "requirement %lld: class id %d", (long long)j, c);
+    if (ty < 0 || (size_t)ty >= n_types) return h->fail(OE_ERR_INVALID, "requirement %lld: pod type", (long long)j);
+    h->h_class[j] = c; h->h_rtype[j] = ty; h->h_rindex[j] = ix;
+    if (sensitive_known && h->class_self_sensitive[c]) { rmin[ty] = std::min(rmin[ty], ix); rmax[ty] = std::max(rmax[ty], ix); }
   }
+  h->req_spans_valid = sensitive_known;
   h->M = M;
-  h->h_class.assign(t->class_id, t->class_id + M);
-  h->h_rtype.assign(t->pod_type_id, t->pod_type_id + M);
-  h->h_rindex.assign(t->pod_index, t->pod_index + M);
 
   tr.mark("checked_and_kept");
   h->self_provided = t->self_begin != nullptr;
