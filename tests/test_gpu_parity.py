@@ -451,6 +451,67 @@ def test_c5_tenth_scale_properties(engine):
     assert dec.tobytes() == dec2.tobytes()
 
 
+def test_c5_full_size_properties_and_sampled_oracle_pairs(engine):
+    """BASELINE config 5 at full size (1 M offers x 100 k requirements, 100 k deployed tasks).  The oracle needs months for one
+    such cycle, so: (1) the class rows against the oracle on sampled (requirement, offer block) pairs, (2) the decisions against a
+    linear-time replay of first fit over the class rows, (3) the same decisions from the engine that evaluates the table while it
+    arrives in chunks and commits in two passes, and from eight shards with the peer exchange, (4) determinism."""
+    from dcos_commons_b200 import sharded
+    cl = synth.config_c5(1.0)
+    t = cl.tables
+    engine.load(t)
+    f, st = engine.class_feasibility()
+    assert st["n_pairs"] == t.n_offers * t.n_reqs == 10 ** 11
+    N = t.n_offers
+    fb = unpack_bits(f, N)
+    # (1) oracle rows over blocks of 256 offers (it re-walks all deployed tasks for every rule of every pair)
+    rng = np.random.default_rng(5)
+    for lo in (0, 499_968, N - 256):
+        orc = Oracle()
+        orc.tables = t
+        orc.load_programs(t); orc.load_tasks(t); orc.load_offers(t, lo, lo + 256); orc.load_requirements(t)
+        for j in rng.integers(0, t.n_reqs, 3):
+            row = unpack_bits(orc.feasibility_rows(int(j), int(j) + 1), 256)[0]
+            assert np.array_equal(row, fb[t.class_id[j], lo:lo + 256]), f"requirement {j}, offers {lo}.."
+        orc.close()
+    # (2) first fit in plan order, replayed over the class rows
+    dec, st = engine.evaluate_cycle()
+    used = np.zeros(N, bool)
+    cursors = np.zeros(fb.shape[0], np.int64)
+    order = [np.flatnonzero(fb[c]) for c in range(fb.shape[0])]
+    want = np.full(t.n_reqs, -1, np.int32)
+    for j in range(t.n_reqs):
+        c = t.class_id[j]
+        cand, k = order[c], cursors[c]
+        while k < len(cand) and used[cand[k]]:
+            k += 1
+        cursors[c] = k
+        if k < len(cand):
+            want[j] = cand[k]
+            used[cand[k]] = True
+    assert np.array_equal(dec["offer_row"], want)
+    assert st["n_placed"] == int((want >= 0).sum()) > 0
+    # (4) determinism
+    assert engine.evaluate_cycle()[0].tobytes() == dec.tobytes()
+    # (3a) arriving in chunks, committed in two passes
+    arriving = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    arriving.load(t)
+    assert arriving.evaluate_cycle()[0].tobytes() == dec.tobytes()
+    arriving.close()
+    # (3b) eight shards on this device, class rows exchanged through the peer regions
+    shard_rows, bounds = sharded.shard_plan(N, 8)
+    shards = [Engine(device=0, rank=r, world=8) for r in range(8)]
+    for e, (lo, hi) in zip(shards, bounds):
+        e.load(t, lo, hi, shard_rows)
+    sharded.attach_local(shards, shards[0].factored_rows())
+    for e in shards:
+        e.class_feasibility(fetch=False)
+    for e in shards:
+        assert np.array_equal(e.evaluate_cycle()[0]["offer_row"], want)
+    for e in shards:
+        e.close()
+
+
 def test_invalid_tables_are_rejected_not_faulted(engine):
     t = random_tables(3, n_offers=50, n_reqs=5, n_tasks=10)
     t.hostname_id = t.hostname_id.copy()
