@@ -353,7 +353,10 @@ typedef struct {
 typedef struct {
   float ms_h2d;          /* host→device copies issued by the last evaluate call (0 when tables were resident)    */
   float ms_counters;     /* K0: task table → per-key tallies                                                      */
-  float ms_feasibility;  /* K1: offers × classes stage programs + rule programs                                   */
+  float ms_feasibility;  /* K1: offers × classes stage programs + rule programs.  While an OE_CFG_ASYNC_LOADS offer
+                            table is still arriving this span includes the waits for its chunks (the bus), and
+                            ms_commit is only what remains of the commit after the last chunk's K1: the pass over
+                            the landed chunks ran beside the bus                                                  */
   float ms_expand;       /* K1x: class bits → offers × requirements bit matrix (in oe_evaluate_cycle it runs BESIDE
                             the commit: ms_expand and ms_commit + ms_d2h then overlap)                            */
   float ms_commit;       /* K2: ordered greedy commit + winner materialisation                                    */
