@@ -2659,7 +2659,19 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on, int64_t w0, int
     const int reqs_per_block = (int)((h->M + yblocks - 1) / yblocks);
     yblocks = (h->M + reqs_per_block - 1) / reqs_per_block;
     dim3 grid(xblocks, (unsigned)yblocks);
-    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), 0, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
+    // An expansion that runs beside other work (one chunk beside the bus and the commit over the landed chunks, or the whole
+    // matrix on the auxiliary stream beside the commit) asks for 56 KiB of shared memory it
+    // never touches: that caps it at 4 CTAs (1024 threads) per SM, which still writes at the HBM rate but leaves the SMs' other
+    // half to the commit path's kernels — measured on C5: cycle 3.41 ms vs 3.65 ms without the cap (36 KiB 3.45, 75 KiB 3.44,
+    // 110 KiB 3.68; OE_KX_SMEM_KB overrides).
+    static const int pad_kb = getenv("OE_KX_SMEM_KB") ? atoi(getenv("OE_KX_SMEM_KB")) : 56;
+    size_t pad = 0;
+    if (pad_kb > 0 && (w0 > 0 || w1 < stride || on == h->aux_stream)) {
+      static bool attr_set = false;
+      if (!attr_set) { cudaFuncSetAttribute(k_expand_matrix, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
+      pad = (size_t)pad_kb * 1024;
+    }
+    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), pad, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
                                                                          h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block,
                                                                          w0 / (4 * OE_KX_LANES), w1);
     ++*launches;
