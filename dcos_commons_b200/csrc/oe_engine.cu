@@ -1557,6 +1557,25 @@ int copy_rows(oe_engine* h, void* dst, const void* src, size_t elem, int slots, 
   return 0;
 }
 
+// Per pod type, the index range of the deployed tasks (h_vspan rows 0 and 1).  It only changes with the task table
+// (oe_load_tasks, oe_apply_launches), so it is kept across requirement loads.
+void ensure_task_spans(oe_engine* h) {
+  const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
+  if (h->h_vspan.size() != 4 * n_types) { h->h_vspan.assign(4 * n_types, 0); h->task_spans_valid = h->req_spans_valid = false; }
+  if (h->task_spans_valid) return;
+  int32_t *tmin = h->h_vspan.data(), *tmax = tmin + n_types;
+  std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
+  h->task_odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
+  const int64_t T = (int64_t)h->h_ttype.size();
+  for (int64_t r = 0; r < T; ++r) {
+    const int32_t ty = h->h_ttype[r], ix = h->h_tindex[r];
+    if (ty < 0 || ix == OE_NO_INDEX) continue;
+    if ((size_t)ty >= n_types) { h->task_odd_type = true; continue; }
+    tmin[ty] = std::min(tmin[ty], ix); tmax[ty] = std::max(tmax[ty], ix);
+  }
+  h->task_spans_valid = true;
+}
+
 int keyspace_size(const oe_dict_sizes& d, int ks) {
   switch (ks) {
     case OE_KS_HOSTNAME: return d.n_hostnames;
@@ -2212,17 +2231,7 @@ int rebuild_variants(oe_engine* h) {
     if (span.size() != 4 * n_types) { span.assign(4 * n_types, 0); h->task_spans_valid = h->req_spans_valid = false; }
     int32_t *tmin = span.data(), *tmax = tmin + n_types, *rmin = tmax + n_types, *rmax = rmin + n_types;
     if (!h->req_spans_valid) { std::fill(rmin, rmin + n_types, INT32_MAX); std::fill(rmax, rmax + n_types, INT32_MIN); }
-    if (!h->task_spans_valid) {   // the tasks' half only changes with the task table (oe_load_tasks, oe_apply_launches)
-      std::fill(tmin, tmin + n_types, INT32_MAX); std::fill(tmax, tmax + n_types, INT32_MIN);
-      h->task_odd_type = false;   // a task type outside the dictionary (the device-side check will report it): no shortcut
-      for (int64_t r = 0; r < T; ++r) {
-        const int32_t ty = h->h_ttype[r], ix = h->h_tindex[r];
-        if (ty < 0 || ix == OE_NO_INDEX) continue;
-        if ((size_t)ty >= n_types) { h->task_odd_type = true; continue; }
-        tmin[ty] = std::min(tmin[ty], ix); tmax[ty] = std::max(tmax[ty], ix);
-      }
-      h->task_spans_valid = true;
-    }
+    ensure_task_spans(h);
     const bool odd_type = h->task_odd_type;
     bool any_overlap = odd_type;
     if (g_trace) g_trace->mark("task_spans");
