@@ -3023,7 +3023,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       CU(cudaEventRecord(h->ev[3], h->stream));
       CU(cudaEventRecord(h->ev_k1_last, h->stream));
       if (want_matrix) { expand_overlapped = true; CU(cudaEventRecord(h->ev_x1, h->aux_stream)); }
-      tr.mark("pass_enqueued");
+      tr.mark("last_chunk_enqueued");
       CU(cudaEventSynchronize(h->ev_phase_a));
       const int n_open = *h_open;
       tr.mark("prefix_commit_done");
