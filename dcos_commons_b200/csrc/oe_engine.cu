@@ -2,13 +2,20 @@
 //
 // Kernels (all integer / fp64 compare-and-mask work, HBM- or latency-bound; no tensor cores by design):
 //   K0  k_count_tasks / k_rr_summary    task table → per-key tallies that the placement rules read
-//   K1  k_class_feasibility             offers × requirement classes → class-factored feasibility bits
+//   K0c k_rule_tables                   zone/region-only rule verdicts per (row, zone, region), looked up by K1
+//   K1  k_class_feasibility             offers × requirement classes → class-factored feasibility bits; one launch per landed
+//                                       offer chunk while the table is arriving; the PEERS variant also stores its words into
+//                                       every shard's exchange region over NVLink (k_peer_signal / k_peer_wait order the readers)
 //   K1x k_expand_matrix                 class bits → full offers × requirements bit matrix (the HBM-bound pass)
-//   K3  k_tile_popc / k_row_offsets / k_compact_rows   class bits → ascending candidate lists per factored row
+//   K3  k_tile_popc / k_row_offsets / k_compact_rows (+ k_label_components, k_union_bits, k_union_masks)
+//                                       class bits → one ascending offer list per component with row-membership masks
 //   K3d k_row_overlap                   which bit rows share an offer (components that commit independently)
-//   K2  k_commit                        ordered greedy first-fit: one lane per component, shared-memory claimed bitmap
+//   K2a k_sort_hist / k_sort_scatter    requirements grouped by component, plan order kept
+//   K2  k_commit_union (k_commit)       ordered greedy first-fit: one warp per component replays its requirements
+//   K2c k_count_unplaced / k_collect_unplaced / k_merge_unplaced   commit in two passes while the offer table is arriving
 //   K2b k_materialize                   winners → chosen dynamic ports / MOUNT slots
 //   K4  k_apply_launches                multi-cycle replay: placed pods → task rows
+//   loads: k_validate_* (id and range checks), k_fetch_host (small tables read from pinned host memory), k_scatter_rows
 //
 // There is no CPU fallback: every entry point needs a CUDA device and fails with an oe_status otherwise.
 #include <cuda_pipeline.h>
