@@ -333,16 +333,8 @@ def run_engine(args):
     if world > 1:
         # the exchange regions are wired up once, outside the cycles (a scheduler does it at start-up): needs the offers' shape
         eng2.load_programs(pt); eng2.load_tasks(pt); eng2.load_offers(pt, lo, hi, shard_rows); eng2.load_requirements(pt)
-        ok = torch.ones(1, device="cuda")
-        try:
-            if os.environ.get("OE_BENCH_EXCHANGE", "peer") != "peer":
-                raise RuntimeError("OE_BENCH_EXCHANGE asks for the NCCL all-gather")
-            sharded.attach_peers(eng2, dist, max_rows=max(64, 2 * eng2.factored_rows()))
-        except Exception as ex:   # noqa: BLE001  (no peer access between these GPUs: keep the collective)
-            print(f"rank {rank}: peer exchange unavailable ({ex}); using the NCCL all-gather", file=sys.stderr)
-            ok.zero_()
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        exchange = "peer stores from the feasibility kernel (NVLink), flags, device-side wait" if ok.item() > 0 else "nccl all-gather"
+        attached = os.environ.get("OE_BENCH_EXCHANGE", "peer") == "peer" and sharded.attach_peers(eng2, dist, max_rows=max(64, 2 * eng2.factored_rows()))
+        exchange = "peer stores from the feasibility kernel (NVLink), flags, device-side wait" if attached else "nccl all-gather"
         if exchange == "nccl all-gather":
             eng2.close()
             eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)

@@ -507,6 +507,11 @@ class Handle:
         pa = (_p * self.world)(*[(q or None) for q in same_process_ptrs]) if same_process_ptrs is not None else None
         self._check(f(self.h, hb, pa))
 
+    def peer_detach(self):
+        f = self.b.fn("peer_detach")
+        f.argtypes = [_p]
+        self._check(f(self.h))
+
     def cuda_stream(self) -> int:
         f = self.b.fn("stream")
         f.argtypes, f.restype = [_p], _p

@@ -3306,6 +3306,15 @@ int32_t oe_peer_attach(oe_engine* h, const void* handles, void* const* same_proc
   return OE_OK;
 }
 
+int32_t oe_peer_detach(oe_engine* h) {
+  if (!h) return OE_ERR_INVALID;
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  h->detach_peers();
+  h->class_bits_fresh = false;
+  return OE_OK;
+}
+
 int32_t oe_device_buffer(oe_engine* h, int32_t which, void** dev_ptr, int64_t* n_bytes) {
   if (!h || !dev_ptr || !n_bytes) return OE_ERR_INVALID;
   CU(cudaSetDevice(h->device));

@@ -60,16 +60,36 @@ def first_fit(rows: np.ndarray, req_row: np.ndarray, n_offers: int) -> np.ndarra
     return out
 
 
-def attach_peers(engine: "abi.Engine", dist, max_rows: int) -> None:
+def attach_peers(engine: "abi.Engine", dist, max_rows: int) -> bool:
     """One process per GPU: every rank exports its exchange region (oe_peer_export), the 64-byte IPC handles go round
     through the process group, and every rank maps all of them (oe_peer_attach).  From then on the engine's feasibility
     pass stores its class rows into every shard's region itself and oe_evaluate_cycle is the whole sharded cycle: no
-    all-gather call.  Collective: all ranks call it, after loading their offer shard."""
-    handle, _ = engine.peer_export(max_rows)
+    all-gather call.  Collective: all ranks call it, after loading their offer shard.  Returns False — on EVERY rank, with
+    every rank detached again — when any rank could not export or map (no peer access between the GPUs): the caller then
+    keeps gather_class_bits between oe_class_feasibility and oe_evaluate_cycle."""
+    handle, err = None, None
+    try:
+        handle, _ = engine.peer_export(max_rows)
+    except abi.EngineError as ex:
+        err = ex
     handles = [None] * engine.world
     dist.all_gather_object(handles, handle)
-    engine.peer_attach(handles=handles)
-    dist.barrier()   # nobody publishes before everybody has mapped everybody
+    ok = err is None and all(h is not None for h in handles)
+    if ok:
+        try:
+            engine.peer_attach(handles=handles)
+        except abi.EngineError as ex:
+            err, ok = ex, False
+    verdicts = [None] * engine.world
+    dist.all_gather_object(verdicts, ok)      # also: nobody publishes before everybody has mapped everybody
+    if all(verdicts):
+        return True
+    if ok:
+        engine.peer_detach()
+    elif err is not None:
+        import sys
+        print(f"rank {engine.rank}: peer exchange unavailable: {err}", file=sys.stderr)
+    return False
 
 
 def attach_local(engines, max_rows: int) -> None:

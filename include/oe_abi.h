@@ -474,6 +474,8 @@ void* oe_stream(oe_engine* h);
 #define OE_PEER_HANDLE_BYTES 64
 int32_t oe_peer_export(oe_engine* h, int32_t max_rows, void* handle, void** dev_ptr);
 int32_t oe_peer_attach(oe_engine* h, const void* handles, void* const* same_process_ptrs);
+/* Back to the caller-side gather: unmaps the other shards' regions (when one rank could not attach, all ranks detach). */
+int32_t oe_peer_detach(oe_engine* h);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Allocation-free first-fit.  This entry point has no counterpart in the reference (the JVM allocates freely); it

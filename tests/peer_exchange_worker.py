@@ -35,7 +35,7 @@ def main():
             want, _ = Oracle().load(sub).evaluate_cycle()
         eng.load(t, lo, hi, shard_rows)
         if not attached:
-            sharded.attach_peers(eng, dist, max_rows=256)
+            assert sharded.attach_peers(eng, dist, max_rows=256), "these GPUs should reach each other over NVLink"
             attached = True
         got, st = eng.evaluate_cycle()                           # pass + exchange + commit, one call
         ref.load(t, lo, hi, shard_rows)

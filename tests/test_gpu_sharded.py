@@ -185,5 +185,18 @@ def test_peer_exchange_rejects_more_rows_than_exported_and_reports_a_missing_pee
     with pytest.raises(abi.EngineError) as ei:
         engines[0].evaluate_cycle()
     assert ei.value.code == -2 and "shard 1" in str(ei.value)
+    # detached again, the engines take the caller-side gather as before
+    import torch
+    for e in engines:
+        e.peer_detach()
+    want, _ = Oracle().load(t).evaluate_cycle()
+    rows = [e.class_feasibility()[0] for e in engines]
+    gathered = np.ascontiguousarray(np.stack(rows))
+    for e in engines:
+        ptr, nbytes = e.device_buffer(abi.BUF_CLASS_BITS_GLOBAL)
+        dst = torch.as_tensor(sharded._CudaView(ptr, nbytes // 4), device="cuda")
+        dst.copy_(torch.from_numpy(gathered.view(np.int32).reshape(-1)))
+        torch.cuda.synchronize()
+        assert np.array_equal(e.evaluate_cycle()[0]["offer_row"], want["offer_row"])
     for e in engines:
         e.close()
