@@ -468,15 +468,19 @@ __global__ void __launch_bounds__(256) k_compact_rows(RowBits rb, int tiles, con
 // K3d: which bit rows share an offer.  adj[r] gets bit q set iff rows r and q are both feasible for some offer.  Rows that
 // share nothing can be committed independently of each other.  thread = one 32-offer word; only used when rows <= 64.
 #define OE_ADJ_MAX_ROWS 64
-__global__ void __launch_bounds__(128) k_row_overlap(RowBits rb, unsigned long long* __restrict__ adj) {
+#define OE_ADJ_SPLIT 8   // threads per word: each takes every eighth row r (a single thread per word left the SMs at 4-8 warps
+                         // each, walking a chain of rows^2 dependent tests: 41 us on C5)
+__global__ void __launch_bounds__(128 * OE_ADJ_SPLIT) k_row_overlap(RowBits rb, unsigned long long* __restrict__ adj) {
   __shared__ uint32_t tile[OE_ADJ_MAX_ROWS][128];
-  const int64_t gw = (int64_t)blockIdx.x * 128 + threadIdx.x;
-  for (int r = 0; r < rb.rows; ++r) tile[r][threadIdx.x] = gw < rb.total_words ? rb.word(r, gw) : 0u;
-  for (int r = 0; r < rb.rows; ++r) {
-    const uint32_t w = tile[r][threadIdx.x];
+  const int x = threadIdx.x & 127, y = threadIdx.x >> 7;
+  const int64_t gw = (int64_t)blockIdx.x * 128 + x;
+  for (int r = y; r < rb.rows; r += OE_ADJ_SPLIT) tile[r][x] = gw < rb.total_words ? rb.word(r, gw) : 0u;
+  __syncthreads();
+  for (int r = y; r < rb.rows; r += OE_ADJ_SPLIT) {
+    const uint32_t w = tile[r][x];
     unsigned long long acc = 0ull;
     if (w)
-      for (int q = 0; q < rb.rows; ++q) acc |= (unsigned long long)((w & tile[q][threadIdx.x]) != 0u) << q;
+      for (int q = 0; q < rb.rows; ++q) acc |= (unsigned long long)((w & tile[q][x]) != 0u) << q;
     for (int d = 16; d > 0; d >>= 1) acc |= __shfl_xor_sync(0xffffffffu, acc, d);
     if ((threadIdx.x & 31) == 0 && acc) atomicOr(adj + r, acc);
   }
@@ -2715,7 +2719,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
     if (rows > 1) {
       CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
       CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, st));
-      k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, st>>>(rb, h->d_adj.as<unsigned long long>());
+      k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128 * OE_ADJ_SPLIT, 0, st>>>(rb, h->d_adj.as<unsigned long long>());
       ++*launches;
       adj = h->d_adj.as<unsigned long long>();
     }
@@ -2852,7 +2856,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   if (rows <= OE_ADJ_MAX_ROWS && rows > 1) {
     CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
     CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, h->stream));
-    k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
+    k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128 * OE_ADJ_SPLIT, 0, h->stream>>>(rb, h->d_adj.as<unsigned long long>());
     ++*launches;
     a.adj = h->d_adj.as<unsigned long long>();
   }
