@@ -1697,6 +1697,12 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
       return OE_ERR_CUDA;
     }
     h->union_static_smem = (int)fu.sharedSizeBytes;
+    // K1x beside other work requests shared memory only to cap its residency (run_expand); per device, hence here
+    if ((e = cudaFuncSetAttribute(k_expand_matrix, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)) != cudaSuccess) {
+      g_create_error = std::string("oe_create: shared memory opt-in for the expansion kernel: ") + cudaGetErrorString(e);
+      delete h;
+      return OE_ERR_CUDA;
+    }
   }
   *out = h;
   return OE_OK;
@@ -2698,11 +2704,7 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on, int64_t w0, int
     // 110 KiB 3.68; OE_KX_SMEM_KB overrides).
     static const int pad_kb = getenv("OE_KX_SMEM_KB") ? atoi(getenv("OE_KX_SMEM_KB")) : 56;
     size_t pad = 0;
-    if (pad_kb > 0 && (w0 > 0 || w1 < stride || on == h->aux_stream)) {
-      static bool attr_set = false;
-      if (!attr_set) { cudaFuncSetAttribute(k_expand_matrix, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_set = true; }
-      pad = (size_t)pad_kb * 1024;
-    }
+    if (pad_kb > 0 && (w0 > 0 || w1 < stride || on == h->aux_stream)) pad = (size_t)std::min(pad_kb, 200) * 1024;   // opt-in: oe_create
     k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), pad, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
                                                                          h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block,
                                                                          w0 / (4 * OE_KX_LANES), w1);
