@@ -484,3 +484,102 @@ KAT(ExactMatcherTest_numbersAndStrings) {
   assertEquals(std::string("ExactMatcher{str='rack:1'}"), ExactMatcher::createAttribute("rack", "1")->toString());  // "rack:1" is not a number
   assertEquals(std::string("ExactMatcher{str='1000'}"), ExactMatcher::create("1e3")->toString());
 }
+
+// ---- PT/AbstractRoundRobinRuleTest.java:15-157.  The reference's TestRoundRobinRule hands arbitrary offer / task keys to
+// AbstractRoundRobinRule.filter; here the keys are the values of attribute "rack_id" under a RoundRobinByAttributeRule (a null
+// key = the attribute is missing).  TASK_INFO carries no type / index labels there, so no task is "the same pod" (:60-68 of
+// P/AbstractRoundRobinRule.java); the restated tasks have distinct indexes of another type.
+namespace {
+std::vector<mesos::TaskInfo> keyTasks(const std::vector<std::string>& keys) {
+  std::vector<mesos::TaskInfo> tasks;
+  for (size_t k = 0; k < keys.size(); ++k) tasks.push_back(rrTask("dummy" + std::to_string(k), keys[k]));
+  return tasks;
+}
+bool roundRobin(MatcherPtr taskFilter, std::optional<int> distinct, const char* offerKey, const std::vector<mesos::TaskInfo>& tasks) {
+  RulePtr rule = std::make_shared<RoundRobinByAttributeRule>(ATTRIB_NAME, distinct, std::move(taskFilter));
+  mesos::Offer offer = offerKey ? offerWithAttribute(offerKey) : OfferTestUtils::getEmptyOfferBuilder();
+  return filter(rule, offer, PodTestUtils::getPodInstance(0), tasks);
+}
+mesos::TaskInfo taskWithoutKey(const std::string& name) {   // getKey(task) == null: the attribute label is absent
+  mesos::TaskInfo t = getTaskInfo(name);
+  TaskLabelWriter(t).setType(TestConstants::TASK_TYPE).setIndex(nextIndex++);
+  return t;
+}
+}  // namespace
+KAT(AbstractRoundRobinRuleTest_offerKeyNull) { assertFalse(roundRobin(AnyMatcher::create(), 1, nullptr, {})); }                                     // :15-31
+KAT(AbstractRoundRobinRuleTest_noTasksMatch) { assertTrue(roundRobin(ExactMatcher::create("banana"), 1, "key0", {taskWithoutKey("t")})); }          // :33-47
+KAT(AbstractRoundRobinRuleTest_allTasksMatch) { assertTrue(roundRobin(AnyMatcher::create(), 1, "key0", {taskWithoutKey("t")})); }                   // :49-63
+KAT(AbstractRoundRobinRuleTest_rejectDueToInsufficientSpread) { assertFalse(roundRobin(AnyMatcher::create(), 2, "key0", keyTasks({"key0"}))); }     // :69-83
+KAT(AbstractRoundRobinRuleTest_acceptSufficientSpread) { assertTrue(roundRobin(AnyMatcher::create(), 2, "key1", keyTasks({"key0"}))); }             // :89-103
+KAT(AbstractRoundRobinRuleTest_acceptSecondLayerOfRoundRobining) { assertTrue(roundRobin(AnyMatcher::create(), 2, "key0", keyTasks({"key0", "key1"}))); }   // :109-123
+KAT(AbstractRoundRobinRuleTest_rejectFullKey) { assertFalse(roundRobin(AnyMatcher::create(), 2, "key0", keyTasks({"key0", "key1", "key0"}))); }     // :129-143
+
+// ---- PT/RoundRobinByZoneRuleTest.java:24-62 and RoundRobinByRegionRuleTest.java:24-62 assert on getKey(offer) / getKey(task); the
+// same four facts seen through filter(): an offer without a fault domain has no key (FAIL, AbstractRoundRobinRule.java:56-59), an
+// offer's key is its zone (region) name, a task without the label has no key (it is not tallied), a task's key is its zone
+// (region) label.  TestConstants.LOCAL_DOMAIN_INFO = region "test-region", zone "test-zone".
+namespace {
+const mesos::DomainInfo LOCAL{"test-region", "test-zone"}, REMOTE{"other-region", "other-zone"};
+mesos::TaskInfo domainTask(const std::string& name, std::optional<mesos::DomainInfo> d) {
+  return placedTask(name, TestConstants::TASK_TYPE, nextIndex++, "h-" + name, "a-" + name, d);
+}
+}  // namespace
+KAT(RoundRobinByZoneRuleTest_getNullOfferKey) {
+  assertFalse(filter(std::make_shared<RoundRobinByZoneRule>(2), OfferTestUtils::getEmptyOfferBuilder(), typePod(), {}));
+}
+KAT(RoundRobinByZoneRuleTest_getZoneOfferKey_getZoneTaskKey) {
+  RulePtr rule = std::make_shared<RoundRobinByZoneRule>(2);
+  // one task in the local zone: the offer's zone key equals the task's, 1 of 2 zones used -> this zone is full for now
+  std::vector<mesos::TaskInfo> tasks = {domainTask("t0", LOCAL)};
+  assertFalse(filter(rule, hostOffer("h", LOCAL), typePod(), tasks));
+  assertTrue(filter(rule, hostOffer("h", REMOTE), typePod(), tasks));
+  // the key is the ZONE name: same region, other zone is a different key
+  assertTrue(filter(rule, hostOffer("h", mesos::DomainInfo{"test-region", "zone-b"}), typePod(), tasks));
+}
+KAT(RoundRobinByZoneRuleTest_getNullTaskKey) {
+  RulePtr rule = std::make_shared<RoundRobinByZoneRule>(2);
+  assertTrue(filter(rule, hostOffer("h", LOCAL), typePod(), {domainTask("t0", std::nullopt)}));   // an unlabelled task is not tallied
+}
+KAT(RoundRobinByRegionRuleTest_getNullOfferKey) {
+  assertFalse(filter(std::make_shared<RoundRobinByRegionRule>(2), OfferTestUtils::getEmptyOfferBuilder(), typePod(), {}));
+}
+KAT(RoundRobinByRegionRuleTest_getRegionOfferKey_getRegionTaskKey) {
+  RulePtr rule = std::make_shared<RoundRobinByRegionRule>(2);
+  std::vector<mesos::TaskInfo> tasks = {domainTask("t0", LOCAL)};
+  assertFalse(filter(rule, hostOffer("h", LOCAL), typePod(), tasks));
+  assertFalse(filter(rule, hostOffer("h", mesos::DomainInfo{"test-region", "zone-b"}), typePod(), tasks));   // the key is the REGION name
+  assertTrue(filter(rule, hostOffer("h", REMOTE), typePod(), tasks));
+}
+KAT(RoundRobinByRegionRuleTest_getNullTaskKey) {
+  RulePtr rule = std::make_shared<RoundRobinByRegionRule>(2);
+  assertTrue(filter(rule, hostOffer("h", LOCAL), typePod(), {domainTask("t0", std::nullopt)}));
+}
+
+// ---- PT/MaxPerAttributeRuleTest.java:57-97 assert on getKeys(task) / getKeys(offer) of MaxPerAttributeRule(2, matcher[, taskFilter]);
+// through filter(): keys that exist are counted (offer 1 + tasks), keys the matcher rejects or tasks the filter rejects are not.
+namespace {
+mesos::Offer fooOffer() {
+  mesos::Offer o = OfferTestUtils::getEmptyOfferBuilder();
+  o.attributes.push_back(textAttr("footext", "123"));
+  return o;
+}
+mesos::TaskInfo fooTask(const std::string& name) {   // getTask("match-1__abc", OFFER_ATTR_MATCH_1): the offer's attributes as the task's label
+  mesos::TaskInfo t = getTaskInfo(name);
+  TaskLabelWriter(t).setType("different-type").setIndex(nextIndex++);
+  t.labels[labels::OFFER_ATTRIBUTES] = "footext:123";
+  return t;
+}
+}  // namespace
+KAT(MaxPerAttributeRuleTest_getAllTaskKeys_getAllOfferKeys) {
+  RulePtr rule = std::make_shared<MaxPerAttributeRule>(2, AnyMatcher::create());
+  assertTrue(filter(rule, fooOffer(), typePod(), {fooTask("match-1")}));                       // "footext:123": offer 1 + task 1 <= 2
+  assertFalse(filter(rule, fooOffer(), typePod(), {fooTask("match-1"), fooTask("match-2")}));  // 3 > 2
+}
+KAT(MaxPerAttributeRuleTest_getTaskKeysMatchNoAttributes_getOfferKeysMatchNoAttributes) {
+  RulePtr rule = std::make_shared<MaxPerAttributeRule>(2, RegexMatcher::create("banana"));
+  assertTrue(filter(rule, fooOffer(), typePod(), {fooTask("match-1"), fooTask("match-2"), fooTask("match-3")}));   // no key matches: nothing to exceed
+}
+KAT(MaxPerAttributeRuleTest_getTaskKeysMatchNoTasks) {
+  RulePtr rule = std::make_shared<MaxPerAttributeRule>(2, AnyMatcher::create(), RegexMatcher::create("banana"));
+  assertTrue(filter(rule, fooOffer(), typePod(), {fooTask("match-1"), fooTask("match-2"), fooTask("match-3")}));   // no task passes the filter
+}

@@ -751,3 +751,19 @@ KAT(PlanSchedulerTest_testEvaluateNoRecommendations) {  // the reference mocks t
   assertTrue(scheduler.resourceOffers({planSchedulerOffer()}, steps).empty());
   assertTrue(steps[0].isPrepared());
 }
+
+// ---- T/offer/evaluate/PlacementRuleEvaluationStageTest.java:25-104: AgentRule.require(agent) as the pod's placement rule; the
+// offer from that agent passes (and the stage leaves the pool alone: the launch that follows still finds its 1.0 cpus + 0.1 of the
+// executor in the 1.1 offered), the offer from another agent fails.
+namespace {
+size_t requireAgent(const std::string& offerAgent) {
+  Fixture f;
+  auto req = PodInstanceRequirementTestUtils::getRequirement(PodInstanceRequirementTestUtils::getCpuResourceSet(1.0), TestConstants::POD_TYPE, 0,
+                                                             std::optional<RulePtr>(AgentRule::require(std::vector<std::string>{"test-agent"})));
+  mesos::Offer offer = OfferTestUtils::getCompleteOffer(ResourceTestUtils::getUnreservedCpus(1.1));
+  offer.slave_id = offerAgent;
+  return f.evaluator.evaluate(req, {offer}).size();
+}
+}  // namespace
+KAT(PlacementRuleEvaluationStageTest_testOfferPassesPlacementRule) { assertEquals(6u, requireAgent("test-agent")); }
+KAT(PlacementRuleEvaluationStageTest_testOfferFailsPlacementRule) { assertEquals(0u, requireAgent("other-agent")); }
