@@ -433,6 +433,15 @@ struct PlacementUtils {
     if (!collocateAgents.empty()) return AgentRule::require(collocateAgents);
     return std::nullopt;
   }
+  // :126-141 — does the pod's rule tree read the offer's region (zone)?  SchedulerBuilder asks before it injects an
+  // IsLocalRegionRule (S/scheduler/SchedulerBuilder.java: region-aware placement); takes PodSpec::placementRule.
+  static bool placementRuleReferencesField(PlacementField field, const std::optional<RulePtr>& rule) {
+    if (!rule || !*rule) return false;
+    for (PlacementField f : (*rule)->getPlacementFields()) if (f == field) return true;
+    return false;
+  }
+  static bool placementRuleReferencesRegion(const std::optional<RulePtr>& rule) { return placementRuleReferencesField(PlacementField::REGION, rule); }
+  static bool placementRuleReferencesZone(const std::optional<RulePtr>& rule) { return placementRuleReferencesField(PlacementField::ZONE, rule); }
 };
 
 // ---- P/MarathonConstraintParser.java -----------------------------------------------------------------------------------

@@ -583,3 +583,29 @@ KAT(MaxPerAttributeRuleTest_getTaskKeysMatchNoTasks) {
   RulePtr rule = std::make_shared<MaxPerAttributeRule>(2, AnyMatcher::create(), RegexMatcher::create("banana"));
   assertTrue(filter(rule, fooOffer(), typePod(), {fooTask("match-1"), fooTask("match-2"), fooTask("match-3")}));   // no task passes the filter
 }
+
+// ---- PT/PlacementUtilsTest.java:40-112: which rule trees read the offer's region (PlacementUtils.java:126-141 over every rule's
+// getPlacementFields()).  getPodSpec(rule) there only wraps the rule into a PodSpec; the restatement hands PodSpec::placementRule over.
+namespace {
+RulePtr regionRule() { return std::make_shared<RegionRule>(ExactMatcher::create("region")); }
+RulePtr zoneRule() { return std::make_shared<ZoneRule>(ExactMatcher::create("zone")); }
+RulePtr attributeRule() { return std::make_shared<AttributeRule>(ExactMatcher::create("attribute")); }
+bool refsRegion(std::optional<RulePtr> rule) {
+  PodSpec pod;
+  pod.placementRule = std::move(rule);
+  return PlacementUtils::placementRuleReferencesRegion(pod.placementRule);
+}
+}  // namespace
+KAT(PlacementUtilsTest_emptyRuleNotRegion) { assertFalse(refsRegion(std::nullopt)); }
+KAT(PlacementUtilsTest_passThroughRuleNotRegion) { assertFalse(refsRegion(RulePtr(std::make_shared<PassthroughRule>()))); }
+KAT(PlacementUtilsTest_simpleRegionRuleSucceeds) { assertTrue(refsRegion(regionRule())); }
+KAT(PlacementUtilsTest_simpleNotRegionRuleFails) { assertFalse(refsRegion(zoneRule())); }
+KAT(PlacementUtilsTest_orRegionRuleSucceeds) { assertTrue(refsRegion(RulePtr(std::make_shared<OrRule>(std::vector<RulePtr>{regionRule(), zoneRule()})))); }
+KAT(PlacementUtilsTest_orNotRegionRuleFails) { assertFalse(refsRegion(RulePtr(std::make_shared<OrRule>(std::vector<RulePtr>{attributeRule(), zoneRule()})))); }
+KAT(PlacementUtilsTest_nestedOrRegionRuleSucceeds) {
+  assertTrue(refsRegion(RulePtr(std::make_shared<AndRule>(attributeRule(), std::make_shared<OrRule>(std::vector<RulePtr>{regionRule(), zoneRule()})))));
+}
+KAT(PlacementUtilsTest_nestedOrNotRegionRuleFails) {
+  assertFalse(refsRegion(RulePtr(std::make_shared<AndRule>(attributeRule(), std::make_shared<OrRule>(std::vector<RulePtr>{attributeRule(), zoneRule()})))));
+  assertTrue(PlacementUtils::placementRuleReferencesZone(std::optional<RulePtr>(zoneRule())));
+}
