@@ -12,6 +12,7 @@
 // loader from EngineLibrary in tests/kat/kat.hpp to point the same host code at the oracle and so pin the ORACLE against the
 // reference's JUnit vectors; that subclass lives under tests/.)
 #pragma once
+#include <algorithm>
 #include <dlfcn.h>
 
 #include <functional>
@@ -129,6 +130,19 @@ struct OfferRecommendation {
   mesos::Resource resource;               // RESERVE / CREATE
   std::optional<mesos::TaskInfo> task;    // LAUNCH_GROUP / STORE_TASK
   bool hasOperation() const { return type != STORE_TASK; }   // StoreTaskInfoRecommendation carries no Mesos operation
+};
+
+// S/offer/OfferUtils.java:26-38: the offers no recommendation WITH an operation refers to (an offer that only led to internal
+// bookkeeping — a StoreTaskInfoRecommendation — is not "used").  PlanScheduler.resourceOffers (:61-66) and the multi-service
+// fan-out narrow the offer list with it between steps / services; the engine's ordered commit does the same on the device.
+struct OfferUtils {
+  static std::vector<mesos::Offer> filterOutAcceptedOffers(const std::vector<mesos::Offer>& offers, const std::vector<OfferRecommendation>& recommendations) {
+    std::vector<std::string> used;
+    for (auto& r : recommendations) if (r.hasOperation()) used.push_back(r.offerId);
+    std::vector<mesos::Offer> out;
+    for (auto& o : offers) if (std::find(used.begin(), used.end(), o.id) == used.end()) out.push_back(o);
+    return out;
+  }
 };
 
 // S/state/StateStore.java:340 fetchTasks / storeTasks, reduced to an in-memory map (the MemPersister role in the

@@ -767,3 +767,48 @@ size_t requireAgent(const std::string& offerAgent) {
 }  // namespace
 KAT(PlacementRuleEvaluationStageTest_testOfferPassesPlacementRule) { assertEquals(6u, requireAgent("test-agent")); }
 KAT(PlacementRuleEvaluationStageTest_testOfferFailsPlacementRule) { assertEquals(0u, requireAgent("other-agent")); }
+
+// ---- T/offer/OfferUtilsTest.java:24-113: filterOutAcceptedOffers keeps the offers that no recommendation with an operation names
+namespace {
+struct OfferUtilsFixture {
+  std::vector<mesos::Offer> OFFERS;
+  std::vector<Rec> RECS;
+  static Rec rec(const std::string& offerId, bool withOperation) {
+    Rec r;
+    r.type = withOperation ? Rec::RESERVE : Rec::STORE_TASK;   // toOfferRecommendation(offer, withOperation), :114-135
+    r.offerId = offerId;
+    return r;
+  }
+  OfferUtilsFixture() {
+    for (const char* id : {"no-operation", "with-without-operation", "with-operation", "no-recommendation"}) {
+      mesos::Offer o = OfferTestUtils::getOffer({ResourceTestUtils::getUnreservedCpus(2), ResourceTestUtils::getUnreservedMem(1000), ResourceTestUtils::getUnreservedDisk(10000)});
+      o.id = id;
+      OFFERS.push_back(o);
+    }
+    RECS = {rec("no-operation", false), rec("with-without-operation", false), rec("with-without-operation", true), rec("with-operation", true)};
+  }
+  std::vector<std::string> left(const std::vector<Rec>& recs) const {
+    std::vector<std::string> ids;
+    for (auto& o : OfferUtils::filterOutAcceptedOffers(OFFERS, recs)) ids.push_back(o.id);
+    return ids;
+  }
+};
+using Ids = std::vector<std::string>;
+}  // namespace
+KAT(OfferUtilsTest_testFilterAcceptedOffers) {
+  OfferUtilsFixture f;
+  assertTrue(f.left({f.RECS[2]}) == (Ids{"no-operation", "with-operation", "no-recommendation"}));
+}
+KAT(OfferUtilsTest_testFilterAcceptedOffersNoAccepted) {
+  OfferUtilsFixture f;
+  assertTrue(f.left({}) == (Ids{"no-operation", "with-without-operation", "with-operation", "no-recommendation"}));
+}
+KAT(OfferUtilsTest_testFilterAcceptedOffersAllAccepted) {
+  OfferUtilsFixture f;
+  assertTrue(f.left(f.RECS) == (Ids{"no-operation", "no-recommendation"}));
+}
+KAT(OfferUtilsTest_testFilterAcceptedOffersAcceptedInvalidId) {
+  OfferUtilsFixture f;
+  assertTrue(f.left({OfferUtilsFixture::rec("abc", false), OfferUtilsFixture::rec("def", true)}) ==
+             (Ids{"no-operation", "with-without-operation", "with-operation", "no-recommendation"}));
+}
