@@ -1232,7 +1232,10 @@ __global__ void k_merge_unplaced(const oe_decision* __restrict__ dec_sub, const 
 }
 
 // K2b: one thread per requirement re-runs the winner's pipeline with recording on (ports, MOUNT slots, new ids).
-__global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec) {
+// `mismatch` receives requirement + 1 when the recorded re-run of a winner fails although the feasibility pass (folded form
+// or rule table) set its bit: the two formulations disagree, and the decision's ports / MOUNT slots cannot be trusted —
+// oe_evaluate_cycle turns that into OE_ERR_STATE instead of returning them.
+__global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec, int* __restrict__ mismatch) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= M) return;
   oe_decision d = dec[j];
@@ -1247,7 +1250,7 @@ __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, in
     const int cls = var < 0 ? row : cx.v.cls[var];
     OfferKeys ok{cx.o.agent[i], cx.o.host[i], cx.o.zone[i], cx.o.region[i]};
     const bool pass = eval_pair<true>(cx, i, ok, cls, var, &d);
-    if (!pass) d.reserved0 = 0xDEADu;  // cannot happen: the commit only picks offers whose bit is set
+    if (!pass) atomicCAS(mismatch, 0, (int)min(j + 1, (int64_t)INT_MAX));  // the commit only picks offers whose bit is set
   }
   dec[j] = d;
 }
@@ -1316,7 +1319,7 @@ __global__ void k_apply_launches(LaunchArgs a, DevOffers o, DevTasks t, const oe
   t.zone[r] = o.zone[i];
   t.region[r] = o.region[i];
   for (int q = 0; q < t.TA; ++q) t.attr[(int64_t)q * t.cap + r] = q < o.A ? o.attr[(int64_t)q * o.N + i] : -1;
-  for (int q = 0; q < t.Q; ++q) t.rr[(int64_t)q * t.cap + r] = o.rr[(int64_t)q * o.N + i];
+  for (int q = 0; q < t.Q; ++q) t.rr[(int64_t)q * t.cap + r] = q < o.Q ? o.rr[(int64_t)q * o.N + i] : -1;
   for (int q = 0; q < t.FW; ++q) t.filter[(int64_t)q * t.cap + r] = a.filter[x * t.FW + q];
 }
 
@@ -1675,10 +1678,11 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
     if (!ok) { g_create_error = "oe_create: copy stream"; delete h; return OE_ERR_CUDA; }
     std::memset(h->h_offer_err, 0, (oe_engine::kMaxChunks + 1) * sizeof(int));
   }
-  if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(sizeof(int)) != cudaSuccess) {
+  if (h->d_err.ensure(sizeof(int)) != cudaSuccess || h->d_nplaced.ensure(2 * sizeof(int)) != cudaSuccess) {
     g_create_error = "oe_create: cudaMalloc failed"; delete h; return OE_ERR_CUDA;
   }
   cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream);
+  cudaMemsetAsync(h->d_nplaced.p, 0, 2 * sizeof(int), h->stream);   // [0] requirements placed, [1] winner whose recorded re-run disagreed
   {  // the commit kernel may use all the shared memory left beside its static arrays
     cudaFuncAttributes fa{};
     if ((e = cudaFuncGetAttributes(&fa, k_commit<true>)) != cudaSuccess ||
@@ -1798,9 +1802,21 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
     if (t->pod_role[c] < -1) return h->fail(OE_ERR_INVALID, "class %d: pod_role", c);
     if (t->port_excl_begin[c + 1] < t->port_excl_begin[c]) return h->fail(OE_ERR_INVALID, "class %d: port_excl_begin not monotone", c);
     int n_port_ops = 0, n_free_ports = 0, n_free_mounts = 0;
+    int32_t res_seen[OE_MAX_STAGE_OPS];
+    int n_res_seen = 0;
     for (int x = ob; x < oe_; ++x) {
       const oe_stage_op& op = t->ops[x];
       if (op.opcode >= OE_OP__COUNT) return h->fail(OE_ERR_INVALID, "class %d op %d: unknown opcode %d", c, x - ob, op.opcode);
+      if (op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_PORT_RESERVED || op.opcode == OE_OP_MOUNT_RESERVED || op.opcode == OE_OP_FREE) {
+        // A reservation is consumed (or handed back) by the one stage that names it: the mappers pair every previously reserved
+        // resource with at most one spec (S/offer/evaluate/TaskResourceMapper.java:80-194, ExecutorResourceMapper.java:66-129),
+        // and consumeReserved / free take the id out of the pool (S/offer/MesosResourcePool.java:259-271,374-430).  The device
+        // pipeline looks the id up in the offer without tracking that, so a second stage on the same id is refused here.
+        if (op.arg < 0 || op.arg >= d.n_res_ids) return h->fail(OE_ERR_INVALID, "class %d op %d: resource id %d outside the dictionary (%d ids)", c, x - ob, op.arg, d.n_res_ids);
+        for (int q = 0; q < n_res_seen; ++q)
+          if (res_seen[q] == op.arg) return h->fail(OE_ERR_INVALID, "class %d op %d: resource id %d is named by two stages of one pipeline", c, x - ob, op.arg);
+        res_seen[n_res_seen++] = op.arg;
+      }
       const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
       const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
       if (slotted && op.slot >= OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_INVALID, "class %d op %d: role slot %d", c, x - ob, op.slot);
@@ -2013,6 +2029,10 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
     if (t->shard_rows <= 0 || t->shard_rows % 1024 != 0) return h->fail(OE_ERR_INVALID, "sharded offer table needs shard_rows, a multiple of 1024");
     if (t->row_offset != (int64_t)h->rank * t->shard_rows) return h->fail(OE_ERR_INVALID, "row_offset must be rank * shard_rows");
     if (N > t->shard_rows) return h->fail(OE_ERR_INVALID, "shard holds more than shard_rows offers");
+    const int64_t Ng = t->n_offers_global;
+    if (Ng < 0 || Ng > (int64_t)h->world * t->shard_rows) return h->fail(OE_ERR_INVALID, "n_offers_global %lld does not fit %d shards of %lld rows", (long long)Ng, h->world, (long long)t->shard_rows);
+    const int64_t want = std::max<int64_t>(0, std::min<int64_t>(t->shard_rows, Ng - t->row_offset));
+    if (N != want) return h->fail(OE_ERR_INVALID, "shard %d must hold %lld of the %lld offers (every shard but the last is full), got %lld", h->rank, (long long)want, (long long)Ng, (long long)N);
   } else if (t->row_offset != 0) {
     return h->fail(OE_ERR_INVALID, "row_offset must be 0 when not sharded");
   }
@@ -2791,7 +2811,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
       k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
       // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
       // behind the expansion's grid
-      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec);
+      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
       materialized = true;
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
@@ -2804,7 +2824,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
     }
     ++*launches;
     CU(cudaGetLastError());
-    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec);
+    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
     ++*launches;
     CU(cudaGetLastError());
     if (trace_on) {
@@ -2892,7 +2912,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   }
   ++*launches;
   CU(cudaGetLastError());
-  k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+  k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1);
   ++*launches;
   CU(cudaGetLastError());
   return 0;
@@ -3061,7 +3081,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
                                                                                   h->d_dec.as<oe_decision>());
         ++launches;
       }
-      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>());
+      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1);
       ++launches;
       CU(cudaGetLastError());
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
@@ -3092,9 +3112,10 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     }
     CU(cudaStreamWaitEvent(h->stream, h->ev_x1, 0));
   }
-  int n_placed = 0;
+  int placed_and_mismatch[2] = {0, 0};
+  int& n_placed = placed_and_mismatch[0];
   if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
-  CU(cudaMemcpyAsync(&n_placed, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(placed_and_mismatch, h->d_nplaced.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   int peer_err = 0;
   if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev[5], h->stream));
@@ -3105,6 +3126,12 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     h->class_bits_fresh = false;
     return h->fail(OE_ERR_STATE, "oe_evaluate_cycle: shard %d did not publish its class rows of pass %u within %.1f s (every rank must issue the same calls)",
                    peer_err - 1, h->peer_epoch, h->peer_timeout_ns * 1e-9);
+  }
+  if (placed_and_mismatch[1]) {
+    CU(cudaMemsetAsync(h->d_nplaced.as<int>() + 1, 0, sizeof(int), h->stream));
+    h->class_bits_fresh = false;
+    return h->fail(OE_ERR_STATE, "oe_evaluate_cycle: requirement %d was given an offer whose stage pipeline fails when it is re-run to record the "
+                   "ports and volumes (feasibility pass and pipeline disagree): the decisions of this cycle are not usable", placed_and_mismatch[1] - 1);
   }
   h->cycle_done = true;
   if (stats) {

@@ -24,6 +24,7 @@ SEED = 20240607
 KIND_CPUS, KIND_MEM, KIND_DISK, KIND_GPUS = 0, 1, 2, 3
 N_RACKS, N_TIERS = 200, 3
 BASE_PORT_RANGES = [(1025, 2180), (2182, 3887), (3889, 5049), (5052, 8079), (8082, 8180), (8182, 32000)]
+MOUNT_SIZES = (10240.0, 20480.0, 51200.0)
 EXECUTOR_OVERHEAD = ((KIND_CPUS, 0.1), (KIND_DISK, 256.0), (KIND_MEM, 32.0))  # TreeMap order: cpus, disk, mem
 
 
@@ -56,7 +57,11 @@ def _class_rule(kind: str, c: int, n_regions: int, zones_per_region: int, maxper
         if pick == 2:
             return max_per
         return ("and", [like, group_by, max_per])
-    if kind == "c5":
+    if kind == "c5-hostname":
+        # no zone / region leaf: MaxPerHostname reads a tally per hostname (a gather over as many keys as there are agents)
+        # and the AttributeRule walks the offer's attribute slots (P/MaxPerHostnameRule.java:112-124, P/AttributeRule.java:30-60)
+        return ("and", [max_per, like])
+    if kind in ("c5", "c5-mount"):
         region_bits = np.zeros(n_regions, bool)
         region_bits[c % n_regions] = True
         return ("and", [("region_in", region_bits), ("maxper_zone", f, maxper_zone), ("rr", abi.KS_ZONE, 0, f, zones_per_region)])
@@ -64,7 +69,11 @@ def _class_rule(kind: str, c: int, n_regions: int, zones_per_region: int, maxper
 
 
 def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zones_per_region: int, n_deployed: int = 0,
-                 rules: str = "c4", seed: int = SEED, name: str = "synthetic") -> Cluster:
+                 rules: str = "c4", seed: int = SEED, name: str = "synthetic", redeploy_every: int = 0) -> Cluster:
+    """rules: "c4" | "c5" | "c5-hostname" (MaxPerHostname + AttributeRule, no zone / region leaf) | "c5-mount" (c5's rules,
+    plus one MOUNT volume with a profile list and a range-constrained dynamic port per pod; the agents carry two MOUNT disks).
+    redeploy_every = k > 0: every k-th requirement re-deploys a pod that is already running (same type and index as a
+    deployed task, S/offer/TaskUtils.java:136-145), so its rules must not count the pod's own tasks."""
     rng = np.random.Generator(np.random.PCG64(seed))
     N, M, Cn = n_offers, n_reqs, n_classes
     n_zones = n_regions * zones_per_region
@@ -94,9 +103,13 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
     for c in range(Cn):
         ops = [("exec", -1), ("rule", _class_rule(rules, c, n_regions, zones_per_region, maxper_zone))]
         ops += [("scalar", k, v) for k, v in EXECUTOR_OVERHEAD]
-        ops += [("port", class_ports[c][0]), ("port", class_ports[c][1]), ("dynport", None)]
+        dyn_ranges = [(1200 + 10 * c, 1299 + 10 * c), (3000, 3049)] if rules == "c5-mount" else None
+        ops += [("port", class_ports[c][0]), ("port", class_ports[c][1]), ("dynport", dyn_ranges)]
         ops += [("scalar", KIND_CPUS, float(class_cpus[c])), ("scalar", KIND_MEM, float(class_mem[c]))]
-        ops += [("scalar", KIND_DISK, float(class_disk[c])), ("nop",)]
+        ops += [("scalar", KIND_DISK, float(class_disk[c]))]
+        if rules == "c5-mount":   # VolumeSpec MOUNT with a profile list (S/specification/VolumeSpec.java:13-38): profiles {c % 3, 2}
+            ops += [("mount", float(MOUNT_SIZES[c % 3]), (1 << (c % 3)) | 4)]
+        ops += [("nop",)]
         prog.add_class(ops)
 
     # ---- ports: stock ranges; 3 % of the agents have one statically requested port already taken
@@ -121,7 +134,12 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
         for q, (b, e) in enumerate(ranges):
             port[0, q, i] = tb.pack_range(b, e)
 
-    offers = dict(scalar=scalar, scalar_present=present, port_range=port, mount_size=np.zeros((0, N)), mount_profile=np.zeros((0, N), np.int32),
+    if rules == "c5-mount":   # two MOUNT disks per agent: sizes around what the classes ask for, a profile on three of four
+        msize = np.array(MOUNT_SIZES + (8192.0,))[rng.integers(0, 4, (2, N))]
+        mprof = rng.integers(-1, 3, (2, N)).astype(np.int32)
+    else:
+        msize, mprof = np.zeros((0, N)), np.zeros((0, N), np.int32)
+    offers = dict(scalar=scalar, scalar_present=present, port_range=port, mount_size=msize, mount_profile=mprof,
                   alloc_role=np.full(N, -1, np.int32), agent_id=ids, hostname_id=ids, zone_id=zone, region_id=region,
                   attr_id=np.stack([rack, tier]), rr_key=np.zeros((0, N), np.int32), exec_id=np.zeros((0, N), np.int32))
 
@@ -130,9 +148,17 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
     deployed_per_class = n_deployed // Cn
     pod_index = np.zeros(M, np.int32)
     nxt = np.full(Cn, deployed_per_class, np.int64)
+    redo = np.zeros(Cn, np.int64)      # deployed pods of the class already chosen for a re-deployment
+    redeployed = np.zeros(M, bool)
     for j in range(M):
-        pod_index[j] = nxt[class_id[j]]
-        nxt[class_id[j]] += 1
+        c = class_id[j]
+        if redeploy_every > 0 and j % redeploy_every == 0 and redo[c] < deployed_per_class:
+            pod_index[j] = redo[c]
+            redo[c] += 1
+            redeployed[j] = True
+        else:
+            pod_index[j] = nxt[c]
+            nxt[c] += 1
 
     # ---- deployed tasks: `deployed_per_class` pods of every class on random agents (one task per pod)
     T = deployed_per_class * Cn
@@ -140,7 +166,7 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
     if T > 0:
         t_type = np.repeat(np.arange(Cn, dtype=np.int32), deployed_per_class)
         t_index = np.tile(np.arange(deployed_per_class, dtype=np.int32), Cn)
-        if rules == "c5":
+        if rules in ("c5", "c5-mount"):
             # pods deployed earlier obeyed the same RegionRule: class c lives in region c % n_regions
             by_region = [np.flatnonzero(region == r) for r in range(n_regions)]
             t_agent = np.empty(T, np.int32)
@@ -161,6 +187,8 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
     # launch rows for multi-cycle replay: one stored task per pod, named <type>-<index>-server
     launch_begin = np.arange(M + 1, dtype=np.int32)
     launch_name = (T + np.arange(M)).astype(np.int32)
+    # a re-deployed pod overwrites its stored task (same name): row class * deployed_per_class + index of the task table
+    launch_name[redeployed] = (class_id[redeployed].astype(np.int64) * deployed_per_class + pod_index[redeployed]).astype(np.int32)
     lf = np.zeros((M, FW), np.uint32)
     lf[np.arange(M), class_id >> 5] = (np.uint32(1) << (class_id & 31).astype(np.uint32))
 
@@ -174,6 +202,23 @@ def make_cluster(n_offers: int, n_reqs: int, n_classes: int, n_regions: int, zon
 def config_c4(scale: float = 1.0, seed: int = SEED) -> Cluster:
     """BASELINE config 4: 10k agents x 5k pod instances, 8 classes, 3 regions x 4 zones, T = 0 at cycle start."""
     return make_cluster(int(10_000 * scale), int(5_000 * scale), 8, 3, 4, 0, "c4", seed, "c4-10k-agents-x-5k-instances")
+
+
+def config_c5_variant(which: str, scale: float = 1.0, seed: int = SEED) -> Cluster:
+    """C5-sized workloads that leave the headline configuration's fast paths (same 1 M offers x 100 k instances, 32 classes,
+    100 k deployed pods): "hostname" = MaxPerHostname(2) + AttributeRule LIKE instead of the zone / region rules; "mount" = one
+    MOUNT volume with profiles and a range-constrained dynamic port per pod; "redeploy" = 5 % of the requirements re-deploy a
+    running pod (5 000 bit rows of their own); "one-region" = all classes compete for the same offers (one commit component)."""
+    N, M, T = int(1_000_000 * scale), int(100_000 * scale), int(100_000 * scale)
+    if which == "hostname":
+        return make_cluster(N, M, 32, 8, 6, T, "c5-hostname", seed, "c5-hostname-1M-offers-x-100k-instances")
+    if which == "mount":
+        return make_cluster(N, M, 32, 8, 6, T, "c5-mount", seed, "c5-mount-1M-offers-x-100k-instances")
+    if which == "redeploy":
+        return make_cluster(N, M, 32, 8, 6, T, "c5", seed, "c5-redeploy-1M-offers-x-100k-instances", redeploy_every=20)
+    if which == "one-region":
+        return make_cluster(N, M, 32, 1, 6, T, "c5", seed, "c5-one-region-1M-offers-x-100k-instances")
+    raise ValueError(which)
 
 
 def config_c5(scale: float = 1.0, seed: int = SEED) -> Cluster:

@@ -8,6 +8,17 @@
 // resource pool per (requirement, offer), every stage run without short-circuit, and every placement rule re-walking
 // ALL deployed tasks for every offer.  Nothing is factored by class and no tallies are cached.
 //
+// Second mode (oeo_set_mode(h, 1, threads)), for inputs the literal walk cannot finish (C5: 10^11 pairs x 10^5 tasks per
+// rule): the SAME pair-at-a-time pipeline, but the three rule families that re-walk the task table read tallies built once
+// per cycle instead — per-key counts per (key space, task filter), tasks per (pod type, agent) — with the requirement's own
+// "equivalent" tasks (S/offer/TaskUtils.java:136-145) subtracted, which is the arithmetic of P/MaxPerRule.java:58-87,
+// P/AbstractRoundRobinRule.java:70-112 and P/TaskTypeRule.java:98-217 with the loop over tasks hoisted out of the loop over
+// offers.  The cycle keeps one cursor per (class, equivalent-task set): within a cycle the verdict of a pair is a pure
+// function of those, and a taken offer never returns (PlanScheduler.java:61-66), so every offer before the cursor stays
+// unusable for the requirements that share it.  tests/test_oracle_modes.py pins this mode to the literal one (matrix, masks
+// and decisions, byte for byte) on every fuzz table and on config C4; it is NOT how the reference evaluates and is never
+// the timed "reference" baseline.
+//
 // Reference files followed (S/ = sdk/scheduler/src/main/java/com/mesosphere/sdk/, P/ = S/offer/evaluate/placement/):
 //   S/scheduler/plan/PlanScheduler.java:50-70            cycle(): steps in order, used offers removed whole
 //   S/offer/evaluate/OfferEvaluator.java:113-248         first_fit(): offers in order, all stages, first all-pass wins
@@ -34,6 +45,8 @@
 #include <limits>
 #include <map>
 #include <string>
+#include <thread>
+#include <unordered_map>
 #include <utility>
 #include <vector>
 
@@ -195,12 +208,24 @@ struct Pool {
   }
 };
 
+// Tallies of the cached mode (see the file header): what the literal rule functions recompute per pair.
+struct TallyCache {
+  bool valid = false;
+  std::vector<std::unordered_map<int32_t, int>> cnt;   // [counter set] key -> tasks passing the set's filter that carry the key
+  std::vector<std::map<int, int>> hist;                // [counter set] tally value -> number of keys with that tally (> 0)
+  std::vector<int64_t> type_total;                     // [type set] tasks of that pod type
+  std::vector<std::unordered_map<int32_t, int>> type_agent;  // [type set] agent -> tasks of that pod type on it
+  std::vector<std::vector<int64_t>> self;              // [requirement] task rows equivalent to it, ascending
+};
+
 struct Oracle {
   Programs P;
   Tasks T;
   Offers O;
   Reqs R;
   bool hasP = false, hasT = false, hasO = false, hasR = false;
+  int mode = 0, threads = 1;   // mode 1 = tallies cached per cycle
+  TallyCache cache;
   std::vector<oe_decision> last_decisions;
   std::string err;
   int64_t pairs_evaluated = 0;
@@ -361,6 +386,122 @@ struct Oracle {
     return avoid ? true : false;
   }
 
+
+  // ---- cached mode ---------------------------------------------------------------------------------------------------
+  void build_cache() {
+    TallyCache& c = cache;
+    c = TallyCache();
+    c.cnt.resize(P.csets.size());
+    c.hist.resize(P.csets.size());
+    std::vector<int32_t> keys;
+    for (size_t s = 0; s < P.csets.size(); ++s) {
+      const oe_counter_set& cs = P.csets[s];
+      for (int64_t t = 0; t < T.T; ++t) {
+        if (!task_passes_filter(t, cs.filter_id)) continue;
+        if (cs.keyspace == OE_KS_ATTR) {  // every attribute string of the task; the matcher is applied on the offer side
+          for (int a = 0; a < T.TA; ++a) { int32_t v = T.attr_id[(size_t)t * T.TA + a]; if (v >= 0) c.cnt[s][v] += 1; }
+        } else {
+          task_keys(cs, t, 0, keys);
+          if (!keys.empty()) c.cnt[s][keys[0]] += 1;
+        }
+      }
+      for (auto& kv : c.cnt[s]) c.hist[s][kv.second] += 1;
+    }
+    c.type_total.assign(P.type_set_pod_type.size(), 0);
+    c.type_agent.resize(P.type_set_pod_type.size());
+    for (size_t s = 0; s < P.type_set_pod_type.size(); ++s)
+      for (int64_t t = 0; t < T.T; ++t)
+        if (T.pod_type_id[t] == P.type_set_pod_type[s]) { c.type_total[s] += 1; c.type_agent[s][T.agent_id[t]] += 1; }
+    // equivalent tasks of every requirement (TaskUtils.areEquivalent: same pod type and index)
+    std::map<std::pair<int32_t, int32_t>, std::vector<int64_t>> by_pod;
+    for (int64_t t = 0; t < T.T; ++t)
+      if (T.pod_type_id[t] >= 0 && T.pod_index[t] != OE_NO_INDEX) by_pod[{T.pod_type_id[t], T.pod_index[t]}].push_back(t);
+    c.self.assign((size_t)R.M, {});
+    for (int64_t j = 0; j < R.M; ++j) {
+      auto it = by_pod.find({R.pod_type_id[j], R.pod_index[j]});
+      if (it != by_pod.end()) c.self[(size_t)j] = it->second;
+    }
+    c.valid = true;
+  }
+  // how often key k occurs among the keys of requirement j's equivalent tasks that pass the set's filter
+  int self_key_count(const oe_counter_set& cs, int32_t matcher_off, int64_t j, int32_t k) const {
+    int n = 0;
+    std::vector<int32_t> tkeys;
+    for (int64_t t : cache.self[(size_t)j]) {
+      if (!task_passes_filter(t, cs.filter_id)) continue;
+      task_keys(cs, t, matcher_off, tkeys);
+      if (cs.keyspace == OE_KS_ATTR) { for (int32_t q : tkeys) n += q == k; }
+      else if (!tkeys.empty()) n += tkeys[0] == k;
+    }
+    return n;
+  }
+  // P/MaxPerRule.java:52-87 with the tallies of :58-76 read from the cache
+  bool max_per_cached(int set, int32_t max, int32_t matcher_off, int64_t i, int64_t j) const {
+    const oe_counter_set& cs = P.csets[set];
+    std::vector<int32_t> okeys;
+    offer_keys(cs, i, matcher_off, okeys);
+    std::map<int32_t, int> counts;
+    for (int32_t k : okeys) counts[k] += 1;
+    for (auto& kv : counts) {
+      auto it = cache.cnt[set].find(kv.first);
+      int tally = it == cache.cnt[set].end() ? 0 : it->second;
+      if (tally > 0 && !cache.self[(size_t)j].empty()) tally -= self_key_count(cs, matcher_off, j, kv.first);
+      if (kv.second + tally > max) return false;
+    }
+    return true;
+  }
+  // P/AbstractRoundRobinRule.java:53-151 with `counts` of :70-89 read from the cache
+  bool round_robin_cached(int set, int32_t distinct, int64_t i, int64_t j) const {
+    const oe_counter_set& cs = P.csets[set];
+    if (cs.keyspace == OE_KS_ATTR) return round_robin(cs, distinct, i, j);  // not a single-key space: no tally kept
+    std::vector<int32_t> okeys;
+    offer_keys(cs, i, 0, okeys);
+    if (okeys.empty()) return false;
+    const int32_t offer_key = okeys[0];
+    const std::unordered_map<int32_t, int>& cnt = cache.cnt[set];
+    auto oc = cnt.find(offer_key);
+    int offer_count = oc == cnt.end() ? 0 : oc->second;
+    int max_known = 0, min_known = 0, n_keys = 0;
+    if (cache.self[(size_t)j].empty()) {
+      const std::map<int, int>& h = cache.hist[set];
+      if (!h.empty()) { min_known = h.begin()->first; max_known = h.rbegin()->first; }
+      n_keys = (int)cnt.size();
+    } else {
+      // the requirement's own tasks leave the tallies: adjust the histogram of tally values for the keys they touch
+      std::map<int32_t, int> minus;
+      std::vector<int32_t> tkeys;
+      for (int64_t t : cache.self[(size_t)j]) {
+        if (!task_passes_filter(t, cs.filter_id)) continue;
+        task_keys(cs, t, 0, tkeys);
+        if (!tkeys.empty()) minus[tkeys[0]] += 1;
+      }
+      std::map<int, int> h = cache.hist[set];
+      n_keys = (int)cnt.size();
+      for (auto& kv : minus) {
+        const int before = cnt.at(kv.first), after = before - kv.second;
+        if (--h[before] == 0) h.erase(before);
+        if (after > 0) h[after] += 1; else --n_keys;
+        if (kv.first == offer_key) offer_count = after;
+      }
+      if (!h.empty()) { min_known = h.begin()->first; max_known = h.rbegin()->first; }
+    }
+    if (min_known == max_known || offer_count <= min_known) {
+      if (distinct < 0) return true;
+      if (n_keys >= distinct) return true;
+      return offer_count == 0;
+    }
+    return false;
+  }
+  // P/TaskTypeRule.java:98-217 with the matching tasks counted per agent once
+  bool task_type_cached(int set, bool avoid, int64_t i, int64_t j) const {
+    if (cache.type_total[set] == 0) return true;
+    auto it = cache.type_agent[set].find(O.agent_id[i]);
+    int on = it == cache.type_agent[set].end() ? 0 : it->second;
+    for (int64_t t : cache.self[(size_t)j])
+      on -= T.pod_type_id[t] == P.type_set_pod_type[set] && T.agent_id[t] == O.agent_id[i];
+    return avoid ? on == 0 : on > 0;
+  }
+
   // PlacementRuleEvaluationStage.java:30-42 → PlacementRule.filter; postfix form of the rule tree
   bool rule_program(int32_t begin, int32_t count, int64_t i, int64_t j) const {
     std::vector<char> st;
@@ -391,13 +532,13 @@ struct Oracle {
         case OE_R_LOCAL_REGION:  // P/IsLocalRegionRule.java:24-67
           v = O.region_id[i] < 0 || nd.b == 0 || O.region_id[i] == nd.a;
           break;
-        case OE_R_MAXPER_HOST: v = max_per(P.csets[nd.a], nd.b, 0, i, j); break;
-        case OE_R_MAXPER_ZONE: v = O.zone_id[i] >= 0 && max_per(P.csets[nd.a], nd.b, 0, i, j); break;
-        case OE_R_MAXPER_REGION: v = max_per(P.csets[nd.a], nd.b, 0, i, j); break;
-        case OE_R_MAXPER_ATTR: v = max_per(P.csets[nd.a], nd.b, nd.c, i, j); break;
-        case OE_R_RR: v = round_robin(P.csets[nd.a], nd.b, i, j); break;
-        case OE_R_TYPE_AVOID: v = task_type(P.type_set_pod_type[nd.a], true, i, j); break;
-        case OE_R_TYPE_COLOCATE: v = task_type(P.type_set_pod_type[nd.a], false, i, j); break;
+        case OE_R_MAXPER_HOST: v = mode ? max_per_cached(nd.a, nd.b, 0, i, j) : max_per(P.csets[nd.a], nd.b, 0, i, j); break;
+        case OE_R_MAXPER_ZONE: v = O.zone_id[i] >= 0 && (mode ? max_per_cached(nd.a, nd.b, 0, i, j) : max_per(P.csets[nd.a], nd.b, 0, i, j)); break;
+        case OE_R_MAXPER_REGION: v = mode ? max_per_cached(nd.a, nd.b, 0, i, j) : max_per(P.csets[nd.a], nd.b, 0, i, j); break;
+        case OE_R_MAXPER_ATTR: v = mode ? max_per_cached(nd.a, nd.b, nd.c, i, j) : max_per(P.csets[nd.a], nd.b, nd.c, i, j); break;
+        case OE_R_RR: v = mode ? round_robin_cached(nd.a, nd.b, i, j) : round_robin(P.csets[nd.a], nd.b, i, j); break;
+        case OE_R_TYPE_AVOID: v = mode ? task_type_cached(nd.a, true, i, j) : task_type(P.type_set_pod_type[nd.a], true, i, j); break;
+        case OE_R_TYPE_COLOCATE: v = mode ? task_type_cached(nd.a, false, i, j) : task_type(P.type_set_pod_type[nd.a], false, i, j); break;
         default: v = false;
       }
       st.push_back(v);
@@ -525,6 +666,7 @@ struct Oracle {
 
   int check_loaded() {
     if (!(hasP && hasT && hasO && hasR)) return fail(OE_ERR_STATE, "tables not loaded (programs, tasks, offers, requirements)");
+    if (mode && !cache.valid) build_cache();
     return 0;
   }
 };
@@ -546,6 +688,7 @@ const char* oeo_last_error(const Oracle* h) { return h ? h->err.c_str() : ""; }
 
 int32_t oeo_load_programs(Oracle* h, const oe_program_table* t) {
   h->last_decisions.clear();
+  h->cache.valid = false;
   Programs& P = h->P;
   P = Programs();
   P.C = t->n_classes;
@@ -568,6 +711,7 @@ int32_t oeo_load_programs(Oracle* h, const oe_program_table* t) {
 
 int32_t oeo_load_tasks(Oracle* h, const oe_task_table* t) {
   h->last_decisions.clear();
+  h->cache.valid = false;
   Tasks& T = h->T;
   T = Tasks();
   size_t n = (size_t)t->n_tasks;
@@ -592,6 +736,7 @@ int32_t oeo_load_tasks(Oracle* h, const oe_task_table* t) {
 
 int32_t oeo_load_offers(Oracle* h, const oe_offer_table* t) {
   h->last_decisions.clear();
+  h->cache.valid = false;
   Offers& O = h->O;
   O = Offers();
   size_t n = (size_t)t->n_offers;
@@ -624,6 +769,7 @@ int32_t oeo_load_offers(Oracle* h, const oe_offer_table* t) {
 
 int32_t oeo_load_requirements(Oracle* h, const oe_req_table* t) {
   h->last_decisions.clear();
+  h->cache.valid = false;
   Reqs& R = h->R;
   R = Reqs();
   size_t m = (size_t)t->n_reqs;
@@ -645,20 +791,49 @@ int32_t oeo_load_requirements(Oracle* h, const oe_req_table* t) {
 int64_t oeo_matrix_stride_words(const Oracle* h) { return stride_words(h->O.N); }
 
 // Full matrix, literally: for every requirement, for every offer, run the whole pipeline.
-// `stage_fail` (optional, [M][N] u64) receives the failed-stage mask of every pair.
+// `stage_fail` (optional, [M][N] u64) receives the failed-stage mask of every pair.  With threads > 1 (oeo_set_mode) the
+// offers of a row are split into word-aligned blocks, one per thread: pairs are independent of each other.
 int32_t oeo_feasibility_ex(Oracle* h, uint32_t* bits, uint64_t* stage_fail, int64_t j_begin, int64_t j_end) {
   if (int rc = h->check_loaded()) return rc;
   int64_t stride = stride_words(h->O.N);
+  const int64_t N = h->O.N;
   for (int64_t j = j_begin; j < j_end; ++j) {
     uint32_t* row = bits + (size_t)j * stride;
     std::memset(row, 0, (size_t)stride * 4);
-    for (int64_t i = 0; i < h->O.N; ++i) {
-      uint64_t f = h->evaluate_pair(i, j, nullptr);
-      if (stage_fail) stage_fail[(size_t)j * h->O.N + i] = f;
-      if (f == 0) row[i >> 5] |= 1u << (i & 31);
+    auto span = [&](int64_t i0, int64_t i1) {
+      for (int64_t i = i0; i < i1; ++i) {
+        uint64_t f = h->evaluate_pair(i, j, nullptr);
+        if (stage_fail) stage_fail[(size_t)j * N + i] = f;
+        if (f == 0) row[i >> 5] |= 1u << (i & 31);
+      }
+    };
+    const int nt = (int)std::max<int64_t>(1, std::min<int64_t>(h->threads, N / 4096));
+    if (nt <= 1) { span(0, N); continue; }
+    const int64_t per = ((N + nt - 1) / nt + 31) / 32 * 32;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; ++t) {
+      const int64_t i0 = std::min<int64_t>(N, t * per), i1 = std::min<int64_t>(N, i0 + per);
+      if (i1 > i0) pool.emplace_back(span, i0, i1);
     }
+    for (auto& th : pool) th.join();
   }
   h->pairs_evaluated = (j_end - j_begin) * h->O.N;
+  return 0;
+}
+
+// One matrix row into a buffer of `stride` words (large tables: the caller need not hold M rows).
+int32_t oeo_feasibility_row(Oracle* h, int64_t j, uint32_t* row_bits) {
+  if (int rc = h->check_loaded()) return rc;
+  if (j < 0 || j >= h->R.M) return h->fail(OE_ERR_INVALID, "requirement out of range");
+  return oeo_feasibility_ex(h, row_bits - (size_t)j * stride_words(h->O.N), nullptr, j, j + 1);
+}
+
+// mode 0 = literal (the reference's own loops), 1 = tallies cached per cycle (see the file header); threads = host threads
+// a feasibility row may use.
+int32_t oeo_set_mode(Oracle* h, int32_t mode, int32_t threads) {
+  h->mode = mode ? 1 : 0;
+  h->threads = std::max(1, threads);
+  h->cache.valid = false;
   return 0;
 }
 
@@ -671,6 +846,44 @@ int32_t oeo_feasibility(Oracle* h, uint32_t* bits, oe_stats* stats) {
 // PlanScheduler.resourceOffers (:50-70) over OfferEvaluator.evaluate (:113-248).
 int32_t oeo_evaluate_cycle(Oracle* h, oe_decision* out, oe_stats* stats) {
   if (int rc = h->check_loaded()) return rc;
+  if (h->mode) {
+    // One cursor per (class, equivalent-task set): the pairs' verdicts depend on nothing else within a cycle and taken offers
+    // never return, so the offers before a cursor stay unusable for every requirement that shares it.
+    const int64_t N = h->O.N;
+    std::vector<char> taken((size_t)N, 0);
+    std::map<std::pair<int32_t, std::vector<int64_t>>, int64_t> cursor;
+    int64_t pairs = 0;
+    int placed = 0;
+    for (int64_t j = 0; j < h->R.M; ++j) {
+      oe_decision dec;
+      std::memset(&dec, 0, sizeof dec);
+      dec.offer_row = -1;
+      for (auto& m : dec.mount_slot) m = -1;
+      int64_t& cur = cursor[{h->R.class_id[j], h->cache.self[(size_t)j]}];
+      int64_t i = cur;
+      for (; i < N; ++i) {
+        if (taken[(size_t)i]) continue;
+        oe_decision trial;
+        std::memset(&trial, 0, sizeof trial);
+        ++pairs;
+        if (h->evaluate_pair(i, j, &trial) == 0) {
+          dec = trial;
+          dec.offer_row = (int32_t)(i + h->O.row_offset);
+          dec.reserved0 = 0;
+          taken[(size_t)i] = 1;
+          ++placed;
+          break;
+        }
+      }
+      cur = i;
+      if (dec.offer_row < 0) dec.n_new_reservations = 0;
+      out[j] = dec;
+    }
+    h->last_decisions.assign(out, out + h->R.M);
+    h->pairs_evaluated = pairs;
+    if (stats) { std::memset(stats, 0, sizeof *stats); stats->n_pairs = pairs; stats->n_placed = placed; }
+    return 0;
+  }
   std::vector<int64_t> available((size_t)h->O.N);  // availableOffers: list of rows, shrinking
   for (int64_t i = 0; i < h->O.N; ++i) available[i] = i;
   int64_t pairs = 0;
@@ -712,6 +925,7 @@ int32_t oeo_apply_launches(Oracle* h) {
   Tasks& T = h->T;
   const Offers& O = h->O;
   if (T.TA < O.A) return h->fail(OE_ERR_INVALID, "task table has fewer attribute slots than the offer table");
+  h->cache.valid = false;
   for (int64_t j = 0; j < h->R.M; ++j) {
     int64_t row = h->last_decisions[j].offer_row;
     if (row < 0) continue;

@@ -25,8 +25,25 @@ def oracle_library() -> BoundLibrary:
 
 
 class Oracle(Handle):
-    def __init__(self):
+    def __init__(self, cached=False, threads=1):
+        """cached=True: the oracle's second mode (tallies built once per cycle, see oracle/oe_oracle.cpp) — pinned to the
+        literal mode by tests/test_oracle_modes.py; for tables the literal walk cannot finish."""
         super().__init__(oracle_library())
+        if cached or threads > 1:
+            self.set_mode(cached, threads)
+
+    def set_mode(self, cached: bool, threads: int = 1):
+        f = self.b.fn("set_mode")
+        f.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        self._check(f(self.h, 1 if cached else 0, int(threads)))
+
+    def feasibility_row(self, j: int) -> np.ndarray:
+        """One matrix row ([stride] words) without allocating the whole matrix."""
+        f = self.b.fn("feasibility_row")
+        f.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+        row = np.zeros(self.stride(), np.uint32)
+        self._check(f(self.h, int(j), row.ctypes.data))
+        return row
 
     def stage_failures(self):
         """[n_reqs, n_offers] uint64 failed-stage masks and the [n_reqs, stride] bit matrix."""

@@ -1,4 +1,6 @@
 """GPU parity: the CUDA engine, driven through the C ABI, against the CPU oracle on identical encoded tables."""
+import os
+
 import numpy as np
 import pytest
 
@@ -451,65 +453,86 @@ def test_c5_tenth_scale_properties(engine):
     assert dec.tobytes() == dec2.tobytes()
 
 
-def test_c5_full_size_properties_and_sampled_oracle_pairs(engine):
-    """BASELINE config 5 at full size (1 M offers x 100 k requirements, 100 k deployed tasks).  The oracle needs months for one
-    such cycle, so: (1) the class rows against the oracle on sampled (requirement, offer block) pairs, (2) the decisions against a
-    linear-time replay of first fit over the class rows, (3) the same decisions from the engine that evaluates the table while it
-    arrives in chunks and commits in two passes, and from eight shards with the peer exchange, (4) determinism."""
+def _factored_row_of(t):
+    """Bit row of every requirement, as the engine numbers them: its class, or — when the pod is already deployed (a task of
+    the same type and index exists) and the class reads tallies — a row of its own behind the classes, in plan order."""
+    twins = set(zip(t.t_pod_type_id.tolist(), t.t_pod_index.tolist()))
+    is_var = np.fromiter(((a, b) in twins for a, b in zip(t.r_pod_type_id.tolist(), t.r_pod_index.tolist())), bool, t.n_reqs)
+    row = t.class_id.astype(np.int64).copy()
+    row[is_var] = t.n_classes + np.arange(int(is_var.sum()))
+    return row, is_var
+
+
+def _full_size_against_cached_oracle(engine, cl, variant_rows=8, shards=0, arriving=True):
+    """A workload at its full size against the oracle's cached mode (pinned to the literal one by tests/test_oracle_modes.py):
+    EVERY bit of every class row, sampled rows of re-deployed pods, and all decisions byte for byte (offer, dynamic ports,
+    MOUNT slots, number of fresh reservation ids)."""
     from dcos_commons_b200 import sharded
-    cl = synth.config_c5(1.0)
     t = cl.tables
+    N, M = t.n_offers, t.n_reqs
+    orc = Oracle(cached=True, threads=os.cpu_count() or 1).load(t)
     engine.load(t)
     f, st = engine.class_feasibility()
-    assert st["n_pairs"] == t.n_offers * t.n_reqs == 10 ** 11
-    N = t.n_offers
-    fb = unpack_bits(f, N)
-    # (1) oracle rows over blocks of 256 offers (it re-walks all deployed tasks for every rule of every pair)
-    rng = np.random.default_rng(5)
-    for lo in (0, 499_968, N - 256):
-        orc = Oracle()
-        orc.tables = t
-        orc.load_programs(t); orc.load_tasks(t); orc.load_offers(t, lo, lo + 256); orc.load_requirements(t)
-        for j in rng.integers(0, t.n_reqs, 3):
-            row = unpack_bits(orc.feasibility_rows(int(j), int(j) + 1), 256)[0]
-            assert np.array_equal(row, fb[t.class_id[j], lo:lo + 256]), f"requirement {j}, offers {lo}.."
-        orc.close()
-    # (2) first fit in plan order, replayed over the class rows
-    dec, st = engine.evaluate_cycle()
-    used = np.zeros(N, bool)
-    cursors = np.zeros(fb.shape[0], np.int64)
-    order = [np.flatnonzero(fb[c]) for c in range(fb.shape[0])]
-    want = np.full(t.n_reqs, -1, np.int32)
-    for j in range(t.n_reqs):
-        c = t.class_id[j]
-        cand, k = order[c], cursors[c]
-        while k < len(cand) and used[cand[k]]:
-            k += 1
-        cursors[c] = k
-        if k < len(cand):
-            want[j] = cand[k]
-            used[cand[k]] = True
-    assert np.array_equal(dec["offer_row"], want)
-    assert st["n_placed"] == int((want >= 0).sum()) > 0
-    # (4) determinism
-    assert engine.evaluate_cycle()[0].tobytes() == dec.tobytes()
-    # (3a) arriving in chunks, committed in two passes
-    arriving = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
-    arriving.load(t)
-    assert arriving.evaluate_cycle()[0].tobytes() == dec.tobytes()
-    arriving.close()
-    # (3b) eight shards on this device, class rows exchanged through the peer regions
-    shard_rows, bounds = sharded.shard_plan(N, 8)
-    shards = [Engine(device=0, rank=r, world=8) for r in range(8)]
-    for e, (lo, hi) in zip(shards, bounds):
-        e.load(t, lo, hi, shard_rows)
-    sharded.attach_local(shards, shards[0].factored_rows())
-    for e in shards:
-        e.class_feasibility(fetch=False)
-    for e in shards:
-        assert np.array_equal(e.evaluate_cycle()[0]["offer_row"], want)
-    for e in shards:
-        e.close()
+    assert st["n_pairs"] == N * M
+    row_of, is_var = _factored_row_of(t)
+    assert f.shape[0] == engine.factored_rows() == t.n_classes + int(is_var.sum())
+    words = (N + 31) // 32
+    fresh = np.flatnonzero(~is_var)
+    for c in range(t.n_classes):
+        js = fresh[t.class_id[fresh] == c]
+        if len(js) == 0:
+            continue
+        want = orc.feasibility_row(int(js[0]))
+        assert np.array_equal(f[c, :words], want[:words]), f"class row {c}"
+        assert not f[c, words:].any()
+    rng = np.random.default_rng(9)
+    var_js = np.flatnonzero(is_var)
+    for j in (rng.choice(var_js, min(variant_rows, len(var_js)), replace=False) if len(var_js) else []):
+        want = orc.feasibility_row(int(j))
+        assert np.array_equal(f[row_of[j], :words], want[:words]), f"row of re-deployed requirement {j}"
+    d_cpu, s_cpu = orc.evaluate_cycle()
+    d_gpu, s_gpu = engine.evaluate_cycle()
+    assert np.array_equal(d_gpu["offer_row"], d_cpu["offer_row"])
+    assert d_gpu.tobytes() == d_cpu.tobytes()
+    assert s_gpu["n_placed"] == s_cpu["n_placed"] > 0
+    assert engine.evaluate_cycle()[0].tobytes() == d_cpu.tobytes()      # run to run
+    orc.close()
+    if arriving:   # the table evaluated while it arrives in chunks, committed in two passes
+        eng2 = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+        eng2.load(t)
+        assert eng2.evaluate_cycle()[0].tobytes() == d_cpu.tobytes()
+        eng2.close()
+    if shards:     # shards on this device, class rows exchanged through the peer regions
+        shard_rows, bounds = sharded.shard_plan(N, shards)
+        engs = [Engine(device=0, rank=r, world=shards) for r in range(shards)]
+        for e, (lo, hi) in zip(engs, bounds):
+            e.load(t, lo, hi, shard_rows)
+        sharded.attach_local(engs, engs[0].factored_rows())
+        for e in engs:
+            e.class_feasibility(fetch=False)
+        for e in engs:
+            assert np.array_equal(e.evaluate_cycle()[0]["offer_row"], d_cpu["offer_row"])
+        for e in engs:
+            e.close()
+    return d_cpu
+
+
+def test_c5_full_size_every_class_row_and_every_decision(engine):
+    """BASELINE config 5 at full size (1 M offers x 100 k requirements, 100 k deployed tasks, 10^11 pairs): all 32 class rows
+    x 1 M offers and all 100 k decisions against the oracle; the same from the chunked / two-pass cycle and from eight shards."""
+    _full_size_against_cached_oracle(engine, synth.config_c5(1.0), shards=8)
+
+
+@pytest.mark.parametrize("which", ["hostname", "mount", "one-region", "redeploy"])
+def test_c5_variants_full_size(engine, which):
+    """The C5-sized workloads that leave the headline's fast paths (bench.py --workload c5-<which>)."""
+    _full_size_against_cached_oracle(engine, synth.config_c5_variant(which, 1.0), arriving=which != "redeploy")
+
+
+@pytest.mark.parametrize("which", ["hostname", "mount", "one-region", "redeploy"])
+def test_c5_variants_small_against_the_literal_oracle(engine, which):
+    cl = synth.config_c5_variant(which, 0.004)
+    _compare_all(engine, cl.tables)
 
 
 def test_invalid_tables_are_rejected_not_faulted(engine):
@@ -523,5 +546,22 @@ def test_invalid_tables_are_rejected_not_faulted(engine):
     t2.class_id[0] = 99
     with pytest.raises(abi.EngineError):
         engine.load(t2)
+    # a reservation named by two stages of one pipeline, or an id outside the dictionary: the device pipeline does not track
+    # consumed reservations the way MesosResourcePool.consumeReserved does, so the load refuses what it could not evaluate
+    from dcos_commons_b200 import tables as tb
+    for ops in ([("scalar_reserved", 0, 1.0, 2), ("scalar_reserved", 1, 1.0, 2)], [("mount_reserved", 1), ("free", 0, 1.0, 1, 0)],
+                [("scalar_reserved", 0, 1.0, 8)], [("port_reserved", -1, 1000)]):
+        prog = tb.ProgramBuilder()
+        prog.add_class([("exec", -1)] + ops + [("nop",)])
+        offers = tb.offers_from_rows([dict(scalars={(0, 0): 4.0, (0, 1): 4.0}, reserved=[(2, 0, 1.0)])], S=1, K=4, R=1, D=0, A=1)
+        t3 = tb.make_tables(dict(n_res_ids=8), prog, tb.empty_tasks(), offers, [0], [0], [0])
+        with pytest.raises(abi.EngineError, match="resource id"):
+            engine.load(t3)
+    # a shard that is not full although shards follow it
+    t4 = random_tables(5, n_offers=3000, n_reqs=5, n_tasks=10)
+    e2 = Engine(device=0, rank=0, world=2)
+    with pytest.raises(abi.EngineError, match="must hold"):
+        e2.load(t4, 0, 1000, 2048)
+    e2.close()
     # the engine is still usable afterwards
     _compare_all(engine, random_tables(4))

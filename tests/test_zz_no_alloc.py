@@ -8,7 +8,8 @@ This file sorts last on purpose: a `pytest -x` run reaches it only after every o
 import numpy as np
 import pytest
 
-from dcos_commons_b200 import Engine, abi, synth
+from dcos_commons_b200 import Engine, abi, sharded, synth
+from oracle_binding import Oracle
 
 
 def test_sizes_beyond_the_fixed_scratch_are_refused_with_a_reason(engine_lib):
@@ -39,6 +40,14 @@ def test_same_placements_as_evaluate_cycle_on_consecutive_calls():
         eng.load(t)
         want, _ = eng.evaluate_cycle()                     # existing entry point: leaves the class bit rows on the device
         assert eng.factored_rows() == t.n_classes
+        # ... and independently of any CUDA code: the same greedy order replayed in numpy over the rows, and the CPU oracle's
+        # own cycle on the same tables
+        rows, _ = eng.class_feasibility()
+        replay = sharded.first_fit(rows, t.class_id, t.n_offers)
+        assert np.array_equal(want["offer_row"], replay), cl.name
+        orc = Oracle(cached=True).load(t)
+        assert np.array_equal(orc.evaluate_cycle()[0]["offer_row"], replay), cl.name
+        orc.close()
         bits_ptr, _ = eng.device_buffer(abi.BUF_CLASS_BITS_LOCAL)
         req_row = torch.from_numpy(t.class_id.astype(np.int32)).cuda()
         for _ in range(2):                                 # twice in a row on the same inputs
@@ -47,4 +56,5 @@ def test_same_placements_as_evaluate_cycle_on_consecutive_calls():
                                  out.data_ptr())
             torch.cuda.synchronize()
             assert np.array_equal(out.cpu().numpy(), want["offer_row"]), cl.name   # integer result: exact
+            assert np.array_equal(out.cpu().numpy(), replay), cl.name
     eng.close()
