@@ -35,7 +35,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
-    ap.add_argument("--workload", default="c5", choices=["c5", "c4"])
+    ap.add_argument("--workload", default="c5", choices=["c5", "c4", "c5-hostname", "c5-mount", "c5-redeploy", "c5-one-region"],
+                    help="c5 = the headline configuration; c5-* = same size, shapes that leave its fast paths (DESIGN.md section 6)")
+    ap.add_argument("--no-oracle-check", action="store_true", help="skip the decisions-vs-oracle check and the factored CPU leg (about 30 s)")
+    ap.add_argument("--no-ncu", action="store_true", help="do not run the two-launch ncu pass that measures roofline.traffic and roofline.issue")
+    ap.add_argument("--probe", default=None, help=argparse.SUPPRESS)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debugging only; invalid as a bench number)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     return ap.parse_args()
@@ -43,8 +47,11 @@ def parse_args():
 
 def make_workload(args):
     from dcos_commons_b200 import synth
-    cl = synth.config_c5(args.scale) if args.workload == "c5" else synth.config_c4(args.scale)
-    return cl
+    if args.workload == "c5":
+        return synth.config_c5(args.scale)
+    if args.workload == "c4":
+        return synth.config_c4(args.scale)
+    return synth.config_c5_variant(args.workload[3:], args.scale)
 
 
 def table_bytes(t, lo=0, hi=None):
@@ -183,6 +190,77 @@ def cpu_baseline_sample(t, seconds, n_sample_offers=1000):
                       f"{dt:.1f} s, CPU oracle oracle/oe_oracle.cpp -O2"}
 
 
+
+def oracle_check_and_factored_cpu(t, offer_rows, full_decisions=None):
+    """The decisions of the last timed cycle against the CPU oracle's own cycle on the same tables (cached mode: tallies built
+    once per cycle, pinned to the literal mode by tests/test_oracle_modes.py), and — from the same run — what the host cores do
+    when THEY use the engine's factoring (one bit row per class instead of per requirement): NOT reference behaviour, reported so
+    that the share of the speed-up that is algorithm and the share that is GPU can be told apart."""
+    from oracle_binding import Oracle
+    cores = os.cpu_count() or 1
+    orc = Oracle(cached=True, threads=cores)
+    orc.load(t)
+    sample_classes = list(range(0, t.n_classes, max(1, t.n_classes // 4)))[:4]
+    t0 = time.perf_counter()
+    for c in sample_classes:
+        j = int(np.flatnonzero(t.class_id == c)[0])
+        orc.feasibility_row(j)
+    t_rows = (time.perf_counter() - t0) * t.n_classes / len(sample_classes)
+    t0 = time.perf_counter()
+    d_cpu, st = orc.evaluate_cycle()
+    t_cycle = time.perf_counter() - t0
+    orc.close()
+    same_offers = bool(np.array_equal(d_cpu["offer_row"], offer_rows))
+    same_all = None if full_decisions is None else bool(d_cpu.tobytes() == full_decisions.tobytes())
+    factored = {"value": t.n_offers * t.n_reqs / (t_rows + t_cycle), "unit": UNIT, "cores": cores, "kind": "port, factored (not reference behaviour)",
+                "sample": f"{len(sample_classes)} of {t.n_classes} class rows x all {t.n_offers} offers on {cores} threads ({t_rows:.1f} s for all rows, extrapolated) "
+                          f"+ the whole ordered cycle on 1 thread ({t_cycle:.1f} s, {st['n_pairs']} pairs): tallies built once, one bit row per class"}
+    return same_offers, same_all, factored
+
+
+def ncu_probe(args, shard):
+    """DRAM bytes and warp instructions per launch of K1 and K1x, measured now: a second process runs two passes of the same
+    workload under `ncu` (nothing timed there).  None when ncu is not usable on this box."""
+    import csv
+    import shutil
+    import tempfile
+    ncu = shutil.which("ncu") or "/usr/local/cuda/bin/ncu"
+    if not os.path.exists(ncu):
+        return None, "ncu not found"
+    log = os.path.join(tempfile.mkdtemp(prefix="oe_ncu_"), "probe.csv")
+    cmd = [ncu, "--metrics", "dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,gpu__time_duration.sum", "--clock-control", "none",
+           "-k", "regex:k_expand_matrix|k_class_feasibility", "-c", "4", "--csv", "--log-file", log,
+           sys.executable, os.path.abspath(__file__), "--probe", shard, "--workload", args.workload, "--scale", str(args.scale)]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
+    except Exception as ex:  # noqa: BLE001
+        return None, f"ncu pass failed: {ex}"
+    if r.returncode != 0 or not os.path.exists(log):
+        return None, f"ncu pass exited {r.returncode}: {(r.stderr or r.stdout)[-200:]}"
+    rows = [ln for ln in open(log) if ln.startswith('"')]
+    acc = {}
+    for rec in csv.DictReader(rows):
+        name = "k_expand_matrix" if "k_expand_matrix" in rec["Kernel Name"] else "k_class_feasibility"
+        val = float(rec["Metric Value"].replace(",", ""))
+        unit = rec.get("Metric Unit", "")
+        if rec["Metric Name"].startswith("dram__bytes"):
+            val *= {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+        acc.setdefault(name, {}).setdefault(rec["Metric Name"], []).append(val)
+    out = {k: {m: sum(v) / len(v) for m, v in d.items()} for k, d in acc.items()}
+    return (out or None), ("ncu pass of this run" if out else "ncu pass produced no rows")
+
+
+def run_probe(args):
+    """Child of ncu_probe: two passes of K0 + K1 + K1x over the shard `lo,hi,shard_rows,rank,world` (no timing, no output)."""
+    from dcos_commons_b200 import Engine
+    lo, hi, shard_rows, rank, world = (int(x) for x in args.probe.split(","))
+    t = make_workload(args).tables
+    eng = Engine(device=0, rank=rank, world=world)
+    eng.load(t, lo, hi, shard_rows)
+    for _ in range(2):
+        eng.feasibility(fetch=False)
+    eng.close()
+
 # ----------------------------------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference's own CPU path for the same metric: the CPU oracle (the JVM reference cannot run on this box), one
@@ -273,6 +351,10 @@ def run_engine(args):
     # ---- resident-in-HBM arm -------------------------------------------------------------------------------------------
     eng = Engine(device=local_rank, rank=rank, world=world)
     eng.load(t, lo, hi, shard_rows)
+    value_exchange = None
+    if world > 1:   # the pass that is timed publishes its class rows to every shard, as the sharded cycle's pass does
+        ok = os.environ.get("OE_BENCH_EXCHANGE", "peer") == "peer" and sharded.attach_peers(eng, dist, max_rows=max(64, 2 * eng.factored_rows()))
+        value_exchange = "peer stores inside the feasibility kernel" if ok else "none (no peer access): rows stay local"
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     ext = torch.cuda.ExternalStream(eng.cuda_stream())
 
@@ -344,12 +426,22 @@ def run_engine(args):
         cyc_stats = cycle()
     barrier()
     host_ms.clear()
-    e2e_steps = max(1, min(args.steps, 5))
+    e2e_steps = max(1, args.steps)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         cyc_stats = cycle()
     barrier()
     e2e_s = time.perf_counter() - t0
+    # what the last timed cycle decided: every rank's digest must be the same one (the reference has ONE list of offers,
+    # S/scheduler/plan/PlanScheduler.java:56-67), and the same at every N
+    import hashlib
+    decisions = np.frombuffer(out.numpy().tobytes(), dtype=abi.DECISION_DTYPE)
+    offer_rows = np.ascontiguousarray(decisions["offer_row"])
+    digest = hashlib.sha256(offer_rows.tobytes()).hexdigest()
+    digests = [digest]
+    if dist is not None:
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
     if dist is not None:
         tmax = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -359,7 +451,10 @@ def run_engine(args):
     e2e = {"value": e2e_steps * N * M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
            "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
-           "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"]}
+           "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"],
+           "decisions_sha256": digest, "ranks_agree": len(set(digests)) == 1}
+    if len(set(digests)) != 1:
+        raise SystemExit(f"bench: the ranks disagree on the placement decisions: {digests}")
     if exchange:
         e2e["exchange"] = exchange
 
@@ -402,9 +497,11 @@ def run_engine(args):
                                "note": "resident offer table, 1 % of the rows replaced through oe_update_offers, requirements reloaded, decisions only"}
         eng3.close()
 
+    if dist is not None:   # nothing below is collective: rank 0 alone measures the CPU legs and the ncu pass
+        barrier()
+        dist.destroy_process_group()
+        dist = None
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
         return
 
     # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
@@ -421,21 +518,56 @@ def run_engine(args):
         {"kernel": "k_count_tasks+k_rr_summary", "ms": k0 / args.steps},
     ]
     dom = max(kernels[:2], key=lambda k: k["ms"])
-    # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this same command
-    traffic, traffic_path = None, os.path.join(ROOT, "profiles", "kernel_traffic.json")
-    if world == 1 and args.workload == "c5" and args.scale == 1.0 and os.path.exists(traffic_path):
-        kt = json.load(open(traffic_path)).get(dom["kernel"])
-        if kt:
-            traffic = kt["dram_bytes_read"] + kt["dram_bytes_write"]
+    # DRAM bytes and warp instructions per launch: measured by a two-pass ncu run of this same workload and shard right now;
+    # when ncu cannot run here, the committed capture of the headline configuration (one GPU) or null, and the line says which
+    probe, probe_src = (None, "--no-ncu") if args.no_ncu else ncu_probe(args, f"{lo},{hi},{shard_rows},{rank},{world}")
+    traffic = insts = None
+    if probe and dom["kernel"] in probe:
+        traffic = int(probe[dom["kernel"]].get("dram__bytes_read.sum", 0) + probe[dom["kernel"]].get("dram__bytes_write.sum", 0))
+        traffic_src = probe_src
+    else:
+        traffic_path = os.path.join(ROOT, "profiles", "kernel_traffic.json")
+        traffic_src = f"null: {probe_src}"
+        if world == 1 and args.workload == "c5" and args.scale == 1.0 and os.path.exists(traffic_path):
+            kt = json.load(open(traffic_path)).get(dom["kernel"])
+            if kt:
+                traffic = kt["dram_bytes_read"] + kt["dram_bytes_write"]
+                traffic_src = f"committed capture profiles/kernel_traffic.json ({probe_src})"
+    if probe and "k_class_feasibility" in probe:
+        insts = probe["k_class_feasibility"].get("smsp__inst_executed.sum")
+    # the feasibility kernel is bound by issue slots, not by HBM — 148 SMs x 4 schedulers x SM clock
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    rows_evaluated = eng.factored_rows()
+    issue = {"kernel": "k_class_feasibility", "warp_inst": insts, "inst_per_pair": insts * 32 / max(n_local * rows_evaluated, 1) if insts else None,
+             "issue_slots_per_s": 148 * 4 * sm_hz, "issue_frac": insts / (148 * 4 * sm_hz * k1_ms * 1e-3) if insts and k1_ms else None,
+             "pairs": n_local * rows_evaluated, "ms": k1_ms, "hbm_frac": (ab["k1"] / (k1_ms * 1e-3) / 1e9 / peak) if k1_ms else None,
+             "source": probe_src if insts else f"null: {probe_src}",
+             "note": "pairs = offers x factored bit rows (classes + re-deployed pods); inst_per_pair = warp instructions x 32 lanes / pairs"}
     roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s",
                 "frac": dom["achieved_gbs"] / peak if dom["achieved_gbs"] else None, "traffic": traffic,
-                "traffic_source": "profiles/kernel_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)" if traffic else None,
+                "traffic_source": traffic_src,
                 "algorithmic_bytes": dom["algorithmic_bytes"], "peak_source": peak_src,
                 "pass_achieved": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9, "pass_frac": ab["total"] / (dev_ms / args.steps * 1e-3) / 1e9 / peak,
                 "pass_note": "pass_* = SURVEY.md §8(d) bytes_K1 (un-factored: one bit per pair written) over K0+K1+K1x device time",
-                "bytes_per_eval": ab["total"] / max(n_local * M, 1), "kernels": kernels}
+                "bytes_per_eval": ab["total"] / max(n_local * M, 1), "kernels": kernels, "issue": issue}
+    if value_exchange:
+        roofline["pass_exchange"] = value_exchange
 
     cpu = cpu_baseline_sample(t, args.cpu_seconds) if world == 1 else None
+    factored = None
+    if not args.no_oracle_check:
+        same_offers, same_all, factored = oracle_check_and_factored_cpu(t, offer_rows, decisions if world == 1 else None)
+        e2e["decisions_match_oracle"] = same_offers
+        if same_all is not None:
+            e2e["decisions_match_oracle_all_fields"] = same_all     # dynamic ports, MOUNT slots, fresh reservation ids too
+        if not same_offers or same_all is False:
+            raise SystemExit("bench: the engine's placement decisions differ from the CPU oracle's")
+    digests_path = os.path.join(ROOT, "profiles", "decisions_digests.json")
+    if os.path.exists(digests_path) and args.scale == 1.0:
+        committed = json.load(open(digests_path)).get(cl.name)
+        e2e["decisions_sha256_committed"] = committed
+        if committed and committed != digest:
+            raise SystemExit(f"bench: decisions digest {digest} differs from the committed one {committed} for {cl.name}")
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -446,9 +578,9 @@ def run_engine(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if factored is not None:
+        line["cpu_baseline_factored"] = factored
     print(json.dumps(line))
-    if dist is not None:
-        dist.destroy_process_group()
 
 
 def main():
@@ -458,7 +590,9 @@ def main():
     real_stdout = os.dup(1)
     os.dup2(2, 1)
     sys.stdout = os.fdopen(real_stdout, "w")
-    if args.impl == "reference":
+    if args.probe:
+        run_probe(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_engine(args)

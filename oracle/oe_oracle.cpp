@@ -571,8 +571,20 @@ struct Oracle {
   }
 
   // One (requirement, offer) pass of OfferEvaluator.java:140-184: every stage runs; returns the failed-stage mask.
-  uint64_t evaluate_pair(int64_t i, int64_t j, oe_decision* dec) const {
+  // `quick` (cached mode's searches only): stop at the first failed stage — failed stages never deduct, so the verdict
+  // "every stage passes" does not depend on the stages behind a failure — and build the pool only when a stage reads it.
+  uint64_t evaluate_pair(int64_t i, int64_t j, oe_decision* dec, bool quick = false) const {
     int cls = R.class_id[j];
+    if (quick) {   // stages that read nothing but the offer's placement columns come first in every pipeline
+      for (int32_t o = P.op_begin[cls]; o < P.op_begin[cls + 1]; ++o) {
+        const oe_stage_op& op = P.ops[o];
+        if (op.flags) break;
+        if (op.opcode == OE_OP_NOP) continue;
+        if (op.opcode == OE_OP_EXEC_ID) { if (!(op.arg < 0 || offer_has_executor(i, op.arg))) return 1ull << std::min(o - P.op_begin[cls], 63); continue; }
+        if (op.opcode == OE_OP_RULE) { if (!rule_program(op.arg, (int32_t)op.aux, i, j)) return 1ull << std::min(o - P.op_begin[cls], 63); continue; }
+        break;
+      }
+    }
     Pool pool = make_pool(i, cls);
     std::vector<int> placed_ports;  // host ports already put into the pod's builders by earlier stages (:264-269)
     uint64_t failed = 0;
@@ -659,6 +671,7 @@ struct Oracle {
         default: pass = false;
       }
       if (!pass) failed |= 1ull << std::min(o - P.op_begin[cls], 63);
+      if (!pass && quick) return failed;
     }
     if (dec) dec->n_new_reservations = n_reserve;
     return failed;
@@ -802,7 +815,7 @@ int32_t oeo_feasibility_ex(Oracle* h, uint32_t* bits, uint64_t* stage_fail, int6
     std::memset(row, 0, (size_t)stride * 4);
     auto span = [&](int64_t i0, int64_t i1) {
       for (int64_t i = i0; i < i1; ++i) {
-        uint64_t f = h->evaluate_pair(i, j, nullptr);
+        uint64_t f = h->evaluate_pair(i, j, nullptr, h->mode && !stage_fail);
         if (stage_fail) stage_fail[(size_t)j * N + i] = f;
         if (f == 0) row[i >> 5] |= 1u << (i & 31);
       }
@@ -860,20 +873,48 @@ int32_t oeo_evaluate_cycle(Oracle* h, oe_decision* out, oe_stats* stats) {
       dec.offer_row = -1;
       for (auto& m : dec.mount_slot) m = -1;
       int64_t& cur = cursor[{h->R.class_id[j], h->cache.self[(size_t)j]}];
+      // first offer at or after the cursor that is free and passes: the first 512 one by one, then in blocks that the host
+      // threads search side by side (the lowest hit wins, so the answer is that of the plain scan)
+      auto first_hit = [&](int64_t a, int64_t b) -> int64_t {
+        for (int64_t i = a; i < b; ++i)
+          if (!taken[(size_t)i] && h->evaluate_pair(i, j, nullptr, true) == 0) return i;
+        return b;
+      };
       int64_t i = cur;
-      for (; i < N; ++i) {
-        if (taken[(size_t)i]) continue;
+      {
+        const int64_t head_end = std::min<int64_t>(N, i + 512);
+        const int64_t hit = first_hit(i, head_end);
+        pairs += std::min(hit + 1, head_end) - i;
+        i = hit;
+        if (hit == head_end) {
+          int64_t block = 4096;
+          while (i < N) {
+            const int nt = h->threads;
+            const int64_t span_end = std::min<int64_t>(N, i + block * nt);
+            std::vector<int64_t> hits((size_t)nt, span_end);
+            std::vector<std::thread> pool;
+            for (int t = 0; t < nt; ++t) {
+              const int64_t a = std::min(span_end, i + t * block), b = std::min(span_end, a + block);
+              if (b > a) pool.emplace_back([&, t, a, b] { const int64_t x = first_hit(a, b); hits[(size_t)t] = x < b ? x : span_end; });
+            }
+            for (auto& th : pool) th.join();
+            const int64_t best = *std::min_element(hits.begin(), hits.end());
+            pairs += std::min(best + 1, span_end) - i;
+            i = best;
+            if (best < span_end) break;
+            block = std::min<int64_t>(block * 2, 65536);
+          }
+        }
+      }
+      if (i < N) {
         oe_decision trial;
         std::memset(&trial, 0, sizeof trial);
-        ++pairs;
-        if (h->evaluate_pair(i, j, &trial) == 0) {
-          dec = trial;
-          dec.offer_row = (int32_t)(i + h->O.row_offset);
-          dec.reserved0 = 0;
-          taken[(size_t)i] = 1;
-          ++placed;
-          break;
-        }
+        h->evaluate_pair(i, j, &trial);
+        dec = trial;
+        dec.offer_row = (int32_t)(i + h->O.row_offset);
+        dec.reserved0 = 0;
+        taken[(size_t)i] = 1;
+        ++placed;
       }
       cur = i;
       if (dec.offer_row < 0) dec.n_new_reservations = 0;

@@ -558,7 +558,7 @@ def test_invalid_tables_are_rejected_not_faulted(engine):
         with pytest.raises(abi.EngineError, match="resource id"):
             engine.load(t3)
     # a shard that is not full although shards follow it
-    t4 = random_tables(5, n_offers=3000, n_reqs=5, n_tasks=10)
+    t4 = random_tables(5, n_offers=3000, n_reqs=5, n_tasks=10, with_reserved=False)
     e2 = Engine(device=0, rank=0, world=2)
     with pytest.raises(abi.EngineError, match="must hold"):
         e2.load(t4, 0, 1000, 2048)
