@@ -39,6 +39,8 @@ def parse_args():
                     help="c5 = the headline configuration; c5-* = same size, shapes that leave its fast paths (DESIGN.md section 6)")
     ap.add_argument("--no-oracle-check", action="store_true", help="skip the decisions-vs-oracle check and the factored CPU leg (about 30 s)")
     ap.add_argument("--no-ncu", action="store_true", help="do not run the two-launch ncu pass that measures roofline.traffic and roofline.issue")
+    ap.add_argument("--wire", default="packed", choices=["packed", "plain"],
+                    help="offer table as oe_load_offers_packed takes it (narrow ids, fp32-exact scalars, `ports` as ids of distinct range lists) or full width")
     ap.add_argument("--probe", default=None, help=argparse.SUPPRESS)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debugging only; invalid as a bench number)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
@@ -230,7 +232,7 @@ def ncu_probe(args, shard):
     log = os.path.join(tempfile.mkdtemp(prefix="oe_ncu_"), "probe.csv")
     cmd = [ncu, "--metrics", "dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,gpu__time_duration.sum", "--clock-control", "none",
            "-k", "regex:k_expand_matrix|k_class_feasibility", "-c", "4", "--csv", "--log-file", log,
-           sys.executable, os.path.abspath(__file__), "--probe", shard, "--workload", args.workload, "--scale", str(args.scale)]
+           sys.executable, os.path.abspath(__file__), "--probe", shard, "--workload", args.workload, "--scale", str(args.scale), "--wire", args.wire]
     try:
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
     except Exception as ex:  # noqa: BLE001
@@ -255,8 +257,16 @@ def run_probe(args):
     from dcos_commons_b200 import Engine
     lo, hi, shard_rows, rank, world = (int(x) for x in args.probe.split(","))
     t = make_workload(args).tables
+    from dcos_commons_b200 import abi
     eng = Engine(device=0, rank=rank, world=world)
-    eng.load(t, lo, hi, shard_rows)
+    eng.tables = t
+    eng.load_programs(t)
+    eng.load_tasks(t)
+    if args.wire == "packed":
+        eng.load_offers_packed(abi.PackedOffers(t, lo, hi), shard_rows)
+    else:
+        eng.load_offers(t, lo, hi, shard_rows)
+    eng.load_requirements(t)
     for _ in range(2):
         eng.feasibility(fetch=False)
     eng.close()
@@ -349,8 +359,20 @@ def run_engine(args):
             torch.cuda.synchronize()
 
     # ---- resident-in-HBM arm -------------------------------------------------------------------------------------------
+    packed = abi.PackedOffers(t, lo, hi) if args.wire == "packed" else None
+
+    def load_all(e, tabs, pk):
+        e.tables = tabs
+        e.load_programs(tabs)
+        e.load_tasks(tabs)
+        if pk is not None:
+            e.load_offers_packed(pk, shard_rows)
+        else:
+            e.load_offers(tabs, lo, hi, shard_rows)
+        e.load_requirements(tabs)
+
     eng = Engine(device=local_rank, rank=rank, world=world)
-    eng.load(t, lo, hi, shard_rows)
+    load_all(eng, t, packed)
     value_exchange = None
     if world > 1:   # the pass that is timed publishes its class rows to every shard, as the sharded cycle's pass does
         ok = os.environ.get("OE_BENCH_EXCHANGE", "peer") == "peer" and sharded.attach_peers(eng, dist, max_rows=max(64, 2 * eng.factored_rows()))
@@ -386,6 +408,7 @@ def run_engine(args):
 
     # ---- end-to-end arm: pinned host tables -> C ABI -> decisions in pinned host memory ------------------------------------
     pt = pin_tables(t.cut_offers(lo, hi) if world > 1 else t)   # each rank keeps only its shard of the offers, pinned
+    ppk = abi.PackedOffers(t, lo, hi).pin() if args.wire == "packed" else None   # ... in the wire form the encoder emits
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     # the tables stay alive in pinned memory for the whole cycle, so the loads may return before their copies have landed
     eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
@@ -404,7 +427,7 @@ def run_engine(args):
         eng2.tables = pt
         timed("load_programs", lambda: eng2.load_programs(pt))
         timed("load_tasks", lambda: eng2.load_tasks(pt))
-        timed("load_offers", lambda: eng2.load_offers(pt, lo, hi, shard_rows))
+        timed("load_offers", (lambda: eng2.load_offers_packed(ppk, shard_rows)) if ppk is not None else (lambda: eng2.load_offers(pt, lo, hi, shard_rows)))
         timed("load_requirements", lambda: eng2.load_requirements(pt))
         if world > 1 and exchange == "nccl all-gather":
             eng2.feasibility(fetch=False)                 # K0 + K1 + K1x on this rank's shard
@@ -414,7 +437,7 @@ def run_engine(args):
 
     if world > 1:
         # the exchange regions are wired up once, outside the cycles (a scheduler does it at start-up): needs the offers' shape
-        eng2.load_programs(pt); eng2.load_tasks(pt); eng2.load_offers(pt, lo, hi, shard_rows); eng2.load_requirements(pt)
+        load_all(eng2, pt, ppk)
         attached = os.environ.get("OE_BENCH_EXCHANGE", "peer") == "peer" and sharded.attach_peers(eng2, dist, max_rows=max(64, 2 * eng2.factored_rows()))
         exchange = "peer stores from the feasibility kernel (NVLink), flags, device-side wait" if attached else "nccl all-gather"
         if exchange == "nccl all-gather":
@@ -447,6 +470,8 @@ def run_engine(args):
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         e2e_s = float(tmax.item())
     h2d, _ = table_bytes(t, lo, hi)
+    if ppk is not None:
+        h2d = table_bytes(t, 0, 0)[0] + ppk.nbytes     # programs, tasks, requirements at full width + the packed offer columns
     d2h = M * abi.DECISION_DTYPE.itemsize + 4
     e2e = {"value": e2e_steps * N * M / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
@@ -463,8 +488,7 @@ def run_engine(args):
         eng3 = Engine(device=local_rank, flags=abi.OE_CFG_ASYNC_LOADS)
 
         def cycle_decisions_only():
-            eng3.tables = pt
-            eng3.load_programs(pt); eng3.load_tasks(pt); eng3.load_offers(pt, lo, hi, shard_rows); eng3.load_requirements(pt)
+            load_all(eng3, pt, ppk)
             return eng3.evaluate_cycle_into(out.data_ptr())
         for _ in range(2):
             cycle_decisions_only()
@@ -573,7 +597,7 @@ def run_engine(args):
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64+int32", "data": "synthetic",
             "config": {"workload": cl.name, "offers": N, "requirements": M, "classes": t.n_classes, "deployed_tasks": t.n_tasks,
-                       "offers_per_gpu": n_local, "parallelism": f"offers row-sharded x{world}" if world > 1 else "single GPU",
+                       "offers_per_gpu": n_local, "wire": args.wire, "parallelism": f"offers row-sharded x{world}" if world > 1 else "single GPU",
                        "l2": "256 MiB memset between timed steps flushes L2; the written matrix (N*M/8 bytes per step) is far larger than L2"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
     if cpu is not None:

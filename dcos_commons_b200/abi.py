@@ -65,6 +65,14 @@ class OeOfferTable(C.Structure):
                 ("reserved_value", _p)]
 
 
+class OeOfferPacking(C.Structure):
+    _fields_ = [("scalar_is_f32", C.c_uint8), ("present_bytes", C.c_uint8), ("zone_bytes", C.c_uint8), ("region_bytes", C.c_uint8),
+                ("attr_bytes", C.c_uint8), ("rr_bytes", C.c_uint8), ("mount_profile_bytes", C.c_uint8), ("exec_bytes", C.c_uint8),
+                ("hostname_is_agent", C.c_uint8), ("alloc_role_is_const", C.c_uint8), ("port_tuple_bytes", C.c_uint8),
+                ("reserved0", C.c_uint8 * 5), ("alloc_role_const", C.c_int32), ("n_port_tuples", C.c_int32),
+                ("port_tuples", _p), ("port_tuple_id", _p)]
+
+
 class OeTaskTable(C.Structure):
     _fields_ = [("n_tasks", C.c_int64), ("n_attr_slots", C.c_int32), ("n_rr_cols", C.c_int32),
                 ("n_filter_words", C.c_int32), ("reserved0", C.c_int32),
@@ -316,6 +324,104 @@ class CycleTables:
         return t
 
 
+def _narrow_ids(a: np.ndarray, dict_size: int):
+    """Narrowest unsigned type whose all-ones value can stand for -1 and that holds every id of the dictionary."""
+    for dt in (np.uint8, np.uint16):
+        if dict_size < np.iinfo(dt).max:
+            return np.where(a < 0, np.iinfo(dt).max, a).astype(dt), dt().itemsize
+    return np.ascontiguousarray(a, np.int32), 4
+
+
+class PackedOffers:
+    """The compact wire form of (a shard of) an offer table — what an encoder that sees every value would emit instead of
+    oe_offer_table's full-width columns (oe_offer_packing in include/oe_abi.h).  Built once per table; `pin()` moves the
+    columns into page-locked memory."""
+
+    def __init__(self, t: CycleTables, lo: int = 0, hi: Optional[int] = None):
+        if t.n_offers_global is not None:    # a pre-cut shard: all of its rows
+            lo_, hi_ = 0, t.n_offers
+            self.row_lo, self.n_global = t.offer_lo, t.n_offers_global
+        else:
+            hi = t.n_offers if hi is None else hi
+            lo_, hi_ = lo, hi
+            self.row_lo, self.n_global = lo, t.n_offers
+        cut = lambda a: np.ascontiguousarray(a[..., lo_:hi_])
+        d = t.dict_sizes
+        self.n = hi_ - lo_
+        self.shape = (t.scalar.shape[0], t.scalar.shape[1], t.port_range.shape[1], t.mount_size.shape[0], t.attr_id.shape[0],
+                      t.rr_key.shape[0], t.exec_id.shape[0])
+        S, K, R = self.shape[:3]
+        self.cols = {}
+        scalar = cut(t.scalar)
+        f32 = scalar.astype(np.float32)
+        self.scalar_is_f32 = bool(np.array_equal(f32.astype(np.float64), scalar, equal_nan=True))
+        self.cols["scalar"] = f32 if self.scalar_is_f32 else scalar
+        pb = 1 if S * K <= 8 else 2 if S * K <= 16 else 4
+        self.cols["scalar_present"], self.present_bytes = cut(t.scalar_present).astype({1: np.uint8, 2: np.uint16, 4: np.uint32}[pb]), pb
+        self.cols["mount_size"] = cut(t.mount_size)
+        self.cols["mount_profile"], self.mount_profile_bytes = _narrow_ids(cut(t.mount_profile), 64)
+        self.cols["zone_id"], self.zone_bytes = _narrow_ids(cut(t.zone_id), d["n_zones"])
+        self.cols["region_id"], self.region_bytes = _narrow_ids(cut(t.region_id), d["n_regions"])
+        self.cols["attr_id"], self.attr_bytes = _narrow_ids(cut(t.attr_id), d["n_attrs"])
+        self.cols["rr_key"], self.rr_bytes = _narrow_ids(cut(t.rr_key), d["n_rr_values"])
+        self.cols["exec_id"], self.exec_bytes = _narrow_ids(cut(t.exec_id), d["n_exec_ids"])
+        agent, host, alloc = cut(t.agent_id), cut(t.hostname_id), cut(t.alloc_role)
+        self.cols["agent_id"] = agent
+        self.hostname_is_agent = bool(np.array_equal(agent, host))
+        if not self.hostname_is_agent:
+            self.cols["hostname_id"] = host
+        self.alloc_role_is_const = bool(self.n == 0 or (alloc == alloc[0]).all())
+        self.alloc_role_const = int(alloc[0]) if self.n and self.alloc_role_is_const else -1
+        if not self.alloc_role_is_const:
+            self.cols["alloc_role"] = alloc
+        # the distinct `ports` range lists and every (slot, offer)'s list
+        ports = cut(t.port_range)                                      # [S, R, n]
+        self.port_tuple_bytes = 0
+        if R > 0 and self.n > 0:
+            lists = np.ascontiguousarray(ports.transpose(0, 2, 1).reshape(S * self.n, R))
+            uniq, inv = np.unique(lists, axis=0, return_inverse=True)
+            if len(uniq) * 4 <= max(self.n, 4096):
+                self.port_tuple_bytes = 2 if len(uniq) <= 65536 else 4
+                self.cols["port_tuples"] = np.ascontiguousarray(uniq, np.uint32)
+                self.cols["port_tuple_id"] = np.ascontiguousarray(inv.reshape(S, self.n), np.uint16 if self.port_tuple_bytes == 2 else np.uint32)
+        if not self.port_tuple_bytes:
+            self.cols["port_range"] = ports
+        self.reserved = None
+        if t.reserved_begin is not None and len(t.reserved_id):
+            if lo_ != 0 or hi_ != t.n_offers:
+                raise NotImplementedError("sharding a table with a reserved side table")
+            self.reserved = (t.reserved_begin, t.reserved_id, t.reserved_kind, t.reserved_value)
+
+    def pin(self):
+        import torch
+        self._pinned = {k: torch.from_numpy(v.copy()).pin_memory() for k, v in self.cols.items() if v.size}
+        self.cols.update({k: v.numpy() for k, v in self._pinned.items()})
+        return self
+
+    @property
+    def nbytes(self) -> int:
+        return int(sum(v.nbytes for v in self.cols.values()))
+
+    def c_structs(self, shard_rows: int = 0, row_offset: Optional[int] = None):
+        c, t, pk = self.cols, OeOfferTable(), OeOfferPacking()
+        t.n_offers, t.row_offset, t.n_offers_global, t.shard_rows = self.n, (self.row_lo if row_offset is None else row_offset), self.n_global, shard_rows
+        (t.n_role_slots, t.n_scalar_kinds, t.n_port_ranges, t.n_mount_slots, t.n_attr_slots, t.n_rr_cols, t.n_exec_slots) = self.shape
+        for name in ("scalar", "scalar_present", "port_range", "mount_size", "mount_profile", "alloc_role", "agent_id", "hostname_id", "zone_id",
+                     "region_id", "attr_id", "rr_key", "exec_id"):
+            setattr(t, name, _ptr(c.get(name)))
+        if self.reserved is not None:
+            rb, rid, rk, rv = self.reserved
+            t.n_reserved, t.reserved_begin, t.reserved_id, t.reserved_kind, t.reserved_value = len(rid), _ptr(rb), _ptr(rid), _ptr(rk), _ptr(rv)
+        pk.scalar_is_f32, pk.present_bytes = int(self.scalar_is_f32), self.present_bytes
+        pk.zone_bytes, pk.region_bytes, pk.attr_bytes, pk.rr_bytes = self.zone_bytes, self.region_bytes, self.attr_bytes, self.rr_bytes
+        pk.mount_profile_bytes, pk.exec_bytes = self.mount_profile_bytes, self.exec_bytes
+        pk.hostname_is_agent, pk.alloc_role_is_const, pk.alloc_role_const = int(self.hostname_is_agent), int(self.alloc_role_is_const), self.alloc_role_const
+        pk.port_tuple_bytes = self.port_tuple_bytes
+        if self.port_tuple_bytes:
+            pk.n_port_tuples, pk.port_tuples, pk.port_tuple_id = len(c["port_tuples"]), _ptr(c["port_tuples"]), _ptr(c["port_tuple_id"])
+        return t, pk
+
+
 class EngineError(RuntimeError):
     def __init__(self, code, text):
         super().__init__(f"oe status {code}: {text}")
@@ -398,6 +504,14 @@ class Handle:
         self._co = t.c_offers(lo, hi, shard_rows, self.rank * shard_rows if (shard_rows and self.world > 1) else None)
         self._n_local = int(self._co.n_offers)
         self._check(self.b.fn("load_offers")(self.h, C.byref(self._co)))
+
+    def load_offers_packed(self, packed: PackedOffers, shard_rows=0):
+        """oe_load_offers_packed: the same table in its compact wire form (widened on the device)."""
+        self._co, self._cpk = packed.c_structs(shard_rows, self.rank * shard_rows if (shard_rows and self.world > 1) else None)
+        self._n_local = int(self._co.n_offers)
+        f = self.b.fn("load_offers_packed")
+        f.argtypes = [_p, _p, _p]
+        self._check(f(self.h, C.byref(self._co), C.byref(self._cpk)))
 
     def update_offers(self, rows, values: CycleTables, value_rows=None):
         """oe_update_offers: resident row rows[k] <- row value_rows[k] of `values` (default: the same row numbers)."""

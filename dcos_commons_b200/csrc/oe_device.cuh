@@ -33,6 +33,8 @@ struct DevOffers {
   const int32_t* attr;
   const int32_t* rr;
   const int32_t* exec;
+  const int32_t* ptuple;  // [S][N] id of the (slot, offer)'s `ports` range list among the table's distinct lists, or null
+  int32_t n_ptuples;
   const int64_t* rbegin;  // may be null
   const int32_t* rid;
   const int32_t* rkind;
@@ -497,7 +499,8 @@ struct alignas(16) FastRow {
   uint16_t port[16];
   uint8_t thr_q[8];       // pool index slot * K + kind of each threshold
   uint32_t flags;         // OE_FR_*
-  int32_t rule_begin, rule_count;
+  int32_t rule_begin;
+  uint16_t rule_count, cls;   // cls: the class itself (a tile's descriptors are copies, one per factored row)
   uint32_t static_mask;   // bit u: port[u] is requested statically
   uint8_t n_thr, n_ports, n_dyn, reserved0;
   int32_t pod_role;
@@ -585,11 +588,32 @@ struct RuleTab {
   int words, zdim;
 };
 
+// Port verdicts tabulated over the table's distinct `ports` range lists (oe_load_offers_packed): bit t of row `cls` = the
+// class's port stages pass on list t.  Built by k_port_tables, read by K1 instead of testing ranges per offer.
+struct PortTab {
+  const uint32_t* bits;  // [C][words], or null
+  int words;
+};
+
+// The port stages of a folded class over one range list given as eight (begin, length) pairs: every statically requested port
+// offered, and enough other ports left for the dynamic ones.
+__device__ __forceinline__ bool fast_ports_pass(const FastRow& fr, const uint32_t* rb, const uint32_t* rlen, int pool_ports) {
+  uint32_t member = 0u;
+  for (int u = 0; u < fr.n_ports; ++u) {
+    bool m = false;
+#pragma unroll
+    for (int q = 0; q < OE_FAST_RANGES; ++q) m = m || ((uint32_t)fr.port[u] - rb[q]) <= rlen[q];
+    member |= m ? 1u << u : 0u;
+  }
+  return (member & fr.static_mask) == fr.static_mask && pool_ports - __popc(member) >= (int)fr.n_dyn;
+}
+
 // NQ = pool entries kept in registers and tested by the dense form (4 when S*K <= 4, else 8).  tab_word / tab_bit: where the
 // tabulated rule verdict of this (row, zone, region) sits — the caller advances the pointer from row to row.
-template <bool REG_RANGES, int NQ>
+template <int PORTS, int NQ>
 __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* nodes, const FastRow& fr, const double* sc, int64_t i,
-                                          const OfferRegs& r, int var, const uint32_t* tab_word, int tab_bit) {
+                                          const OfferRegs& r, int var, const uint32_t* tab_word, int tab_bit, const PortTab& ptab, int32_t ptuple) {
+  constexpr bool REG_RANGES = PORTS == 1;
   const DevOffers& o = cx.o;
   // every test is evaluated and AND-ed (no short circuit): a branch per test costs more than the test, and a compare that feeds
   // a branch cannot overlap with the next one
@@ -611,7 +635,10 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
       pass = pass && ((present >> q) & 1u) && !(v < fr.thr[t]);
     }
   }
-  if (fr.n_ports | fr.n_dyn) {
+  if (PORTS == 2) {
+    // one lookup: the class's port stages were evaluated once per distinct range list (k_port_tables)
+    if (fr.n_ports | fr.n_dyn) pass &= (bool)((__ldg(ptab.bits + (int64_t)fr.cls * ptab.words + (ptuple >> 5)) >> (ptuple & 31)) & 1u);
+  } else if (fr.n_ports | fr.n_dyn) {
     int listed = 0;
     bool statics = true;
     int pool_ports = r.pool_ports;

@@ -62,6 +62,55 @@ __global__ void k_scatter_rows(T* __restrict__ dst, int64_t N, const T* __restri
   dst[slot * N + rows[k]] = src[q];
 }
 
+// oe_load_offers_packed: rows [r0, r1) of a slot-major column widened on the device from what crossed the bus.  Ids: unsigned
+// 8 / 16 bit, all-ones = -1.  Presence masks: zero-extended.  Scalars: fp32 -> fp64 (exact; the encoder sent fp32 only because
+// every value survives the round trip).
+template <class TS, bool ALL_ONES_IS_ABSENT>
+__global__ void k_widen_ids(int32_t* __restrict__ dst, const TS* __restrict__ src, int slots, int64_t N, int64_t r0, int64_t r1) {
+  const int64_t n = r1 - r0, q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * slots) return;
+  const int64_t slot = q / n, i = r0 + (q - slot * n);
+  const TS v = src[slot * N + i];
+  dst[slot * N + i] = (ALL_ONES_IS_ABSENT && v == (TS) ~(TS)0) ? -1 : (int32_t)v;
+}
+__global__ void k_widen_f32(double* __restrict__ dst, const float* __restrict__ src, int slots, int64_t N, int64_t r0, int64_t r1) {
+  const int64_t n = r1 - r0, q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * slots) return;
+  const int64_t slot = q / n, i = r0 + (q - slot * n);
+  dst[slot * N + i] = (double)src[slot * N + i];
+}
+__global__ void k_fill_i32(int32_t* __restrict__ dst, int32_t v, int64_t r0, int64_t r1) {
+  const int64_t i = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < r1) dst[i] = v;
+}
+// ... and the `ports` column rebuilt from the table's distinct range lists: port[s][r][i] = tuples[id[s][i]][r]; the id is kept
+// (as int32) for the feasibility kernel's per-list lookup.  An id outside the list dictionary raises code 20.
+template <class TS>
+__global__ void k_expand_tuples(uint32_t* __restrict__ port, int32_t* __restrict__ id_out, const TS* __restrict__ ids, const uint32_t* __restrict__ tuples,
+                                int n_tuples, int S, int R, int64_t N, int64_t r0, int64_t r1, int* err) {
+  const int64_t n = r1 - r0, q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= n * S) return;
+  const int64_t s = q / n, i = r0 + (q - s * n);
+  int64_t t = (int64_t)ids[s * N + i];
+  if (t >= n_tuples) { atomicMax(err, 20); t = -1; }
+  id_out[s * N + i] = (int32_t)t;
+  for (int r = 0; r < R; ++r) port[(s * R + r) * N + i] = t >= 0 ? __ldg(tuples + t * R + r) : OE_PORT_EMPTY;
+}
+
+// the same check for range lists stored list-major ([n][R]: oe_offer_packing.port_tuples)
+__global__ void k_validate_tuples(const uint32_t* __restrict__ tuples, int n, int R, int code, int* err) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  int prev_e = -1;
+  for (int r = 0; r < R; ++r) {
+    const uint32_t pr = tuples[(int64_t)t * R + r];
+    const int b = pr & 0xFFFF, e = pr >> 16;
+    if (b > e) continue;
+    if (b <= prev_e) atomicMax(err, code);
+    prev_e = e;
+  }
+}
+
 __global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, int S, int R, int code, int* err) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -200,6 +249,7 @@ struct K1Args {
   int n_nodes;           // rule nodes staged in shared memory (0 = read them from global memory)
   int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
   RuleTab tab;
+  PortTab ptab;
   PeerOut peers;
   int64_t xb0;           // first 128-offer block of this launch (the offer table may be evaluated in row chunks)
 };
@@ -222,8 +272,37 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   const uint32_t bits = __ballot_sync(0xffffffffu, v);
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
-template <bool REG_RANGES, bool PEERS, int NQ>
+// K0p: the port stages of every folded class over every distinct `ports` range list of the offer table (slot 0), once —
+// thread = one list, blockIdx.y = class.  K1 (PORTS == 2) then looks the verdict up instead of testing ranges per offer.
+__global__ void __launch_bounds__(128) k_port_tables(const FastRow* __restrict__ fast, const uint32_t* __restrict__ tuples, int n_tuples, int R,
+                                                     uint32_t* __restrict__ out, int words) {
+  const int cls = blockIdx.y;
+  const int t = blockIdx.x * 128 + threadIdx.x;
+  const FastRow fr = fast[cls];
+  bool v = false;
+  if (t < n_tuples && (fr.flags & OE_FR_FAST)) {
+    uint32_t rb[OE_FAST_RANGES], rlen[OE_FAST_RANGES];
+    int pool_ports = 0;
+#pragma unroll
+    for (int q = 0; q < OE_FAST_RANGES; ++q) {
+      const uint32_t pr = q < R ? tuples[(int64_t)t * R + q] : OE_PORT_EMPTY;
+      const uint32_t b = pr & 0xFFFFu, e = pr >> 16;
+      const bool some = b <= e;
+      rb[q] = some ? b : 0x100000u;
+      rlen[q] = some ? e - b : 0u;
+      pool_ports += some ? (int)(e - b + 1) : 0;
+    }
+    v = fast_ports_pass(fr, rb, rlen, pool_ports);
+  }
+  const uint32_t bits = __ballot_sync(0xffffffffu, v);
+  if ((threadIdx.x & 31) == 0 && (t >> 5) < words) out[(int64_t)cls * words + (t >> 5)] = bits;
+}
+
+// PORTS: how a folded class's port stages are tested — 0 = the offer's ranges through L1, 1 = its (at most eight) ranges in
+// registers, 2 = one lookup in the table k_port_tables built over the table's distinct range lists.
+template <int PORTS, bool PEERS, int NQ>
 __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibility(DevCtx cx, K1Args a) {
+  constexpr bool REG_RANGES = PORTS == 1;
   extern __shared__ __align__(16) unsigned char k1_smem[];
   FastRow* s_fast = reinterpret_cast<FastRow*>(k1_smem);
   oe_rule_node* s_nodes = reinterpret_cast<oe_rule_node*>(s_fast + a.rows_per_tile);
@@ -250,6 +329,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
   OfferRegs regs;
   regs.ok = OfferKeys{0, 0, -1, -1};
   if (valid) load_offer_regs(cx.o, i, REG_RANGES, regs);
+  const int32_t ptuple = (PORTS == 2 && valid) ? __ldg(cx.o.ptuple + i) : 0;
   const oe_rule_node* nodes = a.n_nodes ? s_nodes : cx.p.nodes;
   const double* sc = a.sc_cols ? s_sc : nullptr;
   const int64_t word = i >> 5;
@@ -266,7 +346,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
     bool pass = false;
     if (fr.flags & OE_FR_FAST) {
-      if (valid) pass = eval_fast<REG_RANGES, NQ>(cx, nodes, fr, sc, i, regs, var, tab_word, tab_bit);
+      if (valid) pass = eval_fast<PORTS, NQ>(cx, nodes, fr, sc, i, regs, var, tab_word, tab_bit, a.ptab, ptuple);
     } else if (valid) {
       const int cls = var < 0 ? row : cx.v.cls[var];
       pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
@@ -1395,6 +1475,11 @@ struct oe_engine {
   DevOffers dof{};
   int64_t N = 0, N_global = 0, row_offset = 0, shard_rows = 0, n_reserved = 0;
   DevBuf d_scalar, d_present, d_port, d_msize, d_mprof, d_ocols[5], d_oattr, d_orr, d_oexec, d_rbegin, d_rid, d_rkind, d_rval;
+  // oe_load_offers_packed: the narrow columns as they came over the bus (widened into the buffers above on the device), the
+  // table's distinct `ports` range lists, every (slot, offer)'s list id, and the classes' port verdicts per list
+  DevBuf d_wire[12], d_ptuples, d_ptuple_id, d_port_tab;
+  int32_t n_port_tuples = 0;
+  bool tuples_valid = false;
 
   // ---- requirements
   int64_t M = 0;
@@ -1554,6 +1639,7 @@ int fetch_err_flag(oe_engine* h, const char* what) {
 
 int offer_flag_error(oe_engine* h, int flag, const char* what) {
   h->hasO = false;
+  if (flag == 20) return h->fail(OE_ERR_INVALID, "%s: port_tuple_id names a range list outside port_tuples (code 20)", what);
   return h->fail(OE_ERR_INVALID, flag == 18 ? "%s: a ports column holds ranges that are not ascending and disjoint (code %d)"
                                             : "%s: id column %d holds a value outside its dictionary", what, flag);
 }
@@ -1570,15 +1656,16 @@ int wait_offers(oe_engine* h, const char* what) {
   return 0;
 }
 // rows [r0, r1) of a slot-major column (dst and src are [slots][N]) onto the copy stream
-int copy_rows(oe_engine* h, void* dst, const void* src, size_t elem, int slots, int64_t N, int64_t r0, int64_t r1) {
+int copy_rows(oe_engine* h, void* dst, const void* src, size_t elem, int slots, int64_t N, int64_t r0, int64_t r1, cudaStream_t on = nullptr) {
   if (slots <= 0 || r1 <= r0) return 0;
+  if (!on) on = h->copy_stream;
   char* d = static_cast<char*>(dst) + (size_t)r0 * elem;
   const char* sp = static_cast<const char*>(src) + (size_t)r0 * elem;
   const size_t pitch = (size_t)N * elem, width = (size_t)(r1 - r0) * elem;
   if (slots == 1 || pitch > (size_t)0x7fffffff) {
-    for (int q = 0; q < slots; ++q) CU(cudaMemcpyAsync(d + q * pitch, sp + q * pitch, width, cudaMemcpyHostToDevice, h->copy_stream));
+    for (int q = 0; q < slots; ++q) CU(cudaMemcpyAsync(d + q * pitch, sp + q * pitch, width, cudaMemcpyHostToDevice, on));
   } else {
-    CU(cudaMemcpy2DAsync(d, pitch, sp, pitch, width, (size_t)slots, cudaMemcpyHostToDevice, h->copy_stream));
+    CU(cudaMemcpy2DAsync(d, pitch, sp, pitch, width, (size_t)slots, cudaMemcpyHostToDevice, on));
   }
   return 0;
 }
@@ -1723,7 +1810,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
-                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin};
+                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -1740,6 +1827,7 @@ void oe_destroy(oe_engine* h) {
   for (auto* b : all) b->release();
   for (auto& b : h->d_tcols) b.release();
   for (auto& b : h->d_ocols) b.release();
+  for (auto& b : h->d_wire) b.release();
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
   if (h->ev_variants) cudaEventDestroy(h->ev_variants);
   if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
@@ -2000,54 +2088,21 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   return OE_OK;
 }
 
+namespace {
+// Shape checks shared by oe_load_offers and oe_load_offers_packed (pk != null: the columns the packing replaces may be NULL).
+int check_offer_table(oe_engine* h, const oe_offer_table* t, const oe_offer_packing* pk);
+}  // namespace
+
 int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   if (!h || !t) return OE_ERR_INVALID;
   if (!h->hasP) return h->fail(OE_ERR_STATE, "oe_load_offers: load programs first");
   CU(cudaSetDevice(h->device));
   h->hasO = false;
   h->class_bits_fresh = h->cycle_done = false;
+  h->tuples_valid = false; h->n_port_tuples = 0;
+  h->dof.ptuple = nullptr; h->dof.n_ptuples = 0;
+  if (int rc = check_offer_table(h, t, nullptr)) return rc;
   const int64_t N = t->n_offers;
-  if (N < 0 || N > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_offers");
-  if (t->n_role_slots < 1 || t->n_role_slots > OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_LIMIT, "n_role_slots %d", t->n_role_slots);
-  if (t->n_scalar_kinds < 1 || t->n_scalar_kinds > OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_LIMIT, "n_scalar_kinds %d", t->n_scalar_kinds);
-  if (t->n_role_slots * t->n_scalar_kinds > 32) return h->fail(OE_ERR_LIMIT, "role slots x scalar kinds exceeds the 32-bit presence mask");
-  if (t->n_port_ranges < 0 || t->n_port_ranges > OE_MAX_PORT_RANGES) return h->fail(OE_ERR_LIMIT, "n_port_ranges %d", t->n_port_ranges);
-  if (t->n_mount_slots < 0 || t->n_mount_slots > OE_MAX_MOUNT_SLOTS) return h->fail(OE_ERR_LIMIT, "n_mount_slots %d", t->n_mount_slots);
-  if (t->n_attr_slots < 0 || t->n_attr_slots > OE_MAX_ATTR_SLOTS) return h->fail(OE_ERR_LIMIT, "n_attr_slots %d", t->n_attr_slots);
-  if (t->n_rr_cols < 0 || t->n_rr_cols > OE_MAX_RR_COLS) return h->fail(OE_ERR_LIMIT, "n_rr_cols %d", t->n_rr_cols);
-  if (t->n_exec_slots < 0 || t->n_exec_slots > OE_MAX_EXEC_SLOTS) return h->fail(OE_ERR_LIMIT, "n_exec_slots %d", t->n_exec_slots);
-  for (auto& op : h->h_ops) {
-    const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
-    const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
-    if (slotted && op.slot >= t->n_role_slots) return h->fail(OE_ERR_INVALID, "a stage op names role slot %d, offer table has %d", op.slot, t->n_role_slots);
-    const bool free_other = op.opcode == OE_OP_FREE && (op.kind == OE_KIND_PORTS || op.kind == OE_KIND_MOUNT);
-    if (scalar_like && !free_other && op.kind >= t->n_scalar_kinds) return h->fail(OE_ERR_INVALID, "a stage op names scalar kind %d, offer table has %d", op.kind, t->n_scalar_kinds);
-  }
-  for (auto& cs : h->h_csets)
-    if (cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= t->n_rr_cols) return h->fail(OE_ERR_INVALID, "a counter set names rr column %d, offer table has %d", cs.rr_col, t->n_rr_cols);
-  if (h->world > 1) {
-    if (t->shard_rows <= 0 || t->shard_rows % 1024 != 0) return h->fail(OE_ERR_INVALID, "sharded offer table needs shard_rows, a multiple of 1024");
-    if (t->row_offset != (int64_t)h->rank * t->shard_rows) return h->fail(OE_ERR_INVALID, "row_offset must be rank * shard_rows");
-    if (N > t->shard_rows) return h->fail(OE_ERR_INVALID, "shard holds more than shard_rows offers");
-    const int64_t Ng = t->n_offers_global;
-    if (Ng < 0 || Ng > (int64_t)h->world * t->shard_rows) return h->fail(OE_ERR_INVALID, "n_offers_global %lld does not fit %d shards of %lld rows", (long long)Ng, h->world, (long long)t->shard_rows);
-    const int64_t want = std::max<int64_t>(0, std::min<int64_t>(t->shard_rows, Ng - t->row_offset));
-    if (N != want) return h->fail(OE_ERR_INVALID, "shard %d must hold %lld of the %lld offers (every shard but the last is full), got %lld", h->rank, (long long)want, (long long)Ng, (long long)N);
-  } else if (t->row_offset != 0) {
-    return h->fail(OE_ERR_INVALID, "row_offset must be 0 when not sharded");
-  }
-  if (N > 0 && (!t->scalar || !t->scalar_present || !t->alloc_role || !t->agent_id || !t->hostname_id || !t->zone_id || !t->region_id ||
-                (t->n_port_ranges && !t->port_range) || (t->n_mount_slots && (!t->mount_size || !t->mount_profile)) ||
-                (t->n_attr_slots && !t->attr_id) || (t->n_rr_cols && !t->rr_key) || (t->n_exec_slots && !t->exec_id)))
-    return h->fail(OE_ERR_INVALID, "oe_load_offers: missing column");
-  if (t->n_reserved < 0 || (t->n_reserved > 0 && (!t->reserved_begin || !t->reserved_id || !t->reserved_kind || !t->reserved_value)))
-    return h->fail(OE_ERR_INVALID, "oe_load_offers: reserved side table");
-  if (t->n_reserved > 0) {
-    if (t->reserved_begin[0] != 0 || t->reserved_begin[N] != t->n_reserved) return h->fail(OE_ERR_INVALID, "reserved_begin does not span the side table");
-    for (int64_t i = 0; i < N; ++i)
-      if (t->reserved_begin[i + 1] < t->reserved_begin[i]) return h->fail(OE_ERR_INVALID, "reserved_begin not monotone");
-  }
-
   DevOffers& o = h->dof;
   o.N = N; o.row_offset = t->row_offset;
   o.S = t->n_role_slots; o.K = t->n_scalar_kinds; o.R = t->n_port_ranges; o.D = t->n_mount_slots;
@@ -2159,6 +2214,233 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   return OE_OK;
 }
 
+namespace {
+int check_offer_table(oe_engine* h, const oe_offer_table* t, const oe_offer_packing* pk) {
+  const int64_t N = t->n_offers;
+  if (N < 0 || N > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_offers");
+  if (t->n_role_slots < 1 || t->n_role_slots > OE_MAX_ROLE_SLOTS) return h->fail(OE_ERR_LIMIT, "n_role_slots %d", t->n_role_slots);
+  if (t->n_scalar_kinds < 1 || t->n_scalar_kinds > OE_MAX_SCALAR_KINDS) return h->fail(OE_ERR_LIMIT, "n_scalar_kinds %d", t->n_scalar_kinds);
+  if (t->n_role_slots * t->n_scalar_kinds > 32) return h->fail(OE_ERR_LIMIT, "role slots x scalar kinds exceeds the 32-bit presence mask");
+  if (t->n_port_ranges < 0 || t->n_port_ranges > OE_MAX_PORT_RANGES) return h->fail(OE_ERR_LIMIT, "n_port_ranges %d", t->n_port_ranges);
+  if (t->n_mount_slots < 0 || t->n_mount_slots > OE_MAX_MOUNT_SLOTS) return h->fail(OE_ERR_LIMIT, "n_mount_slots %d", t->n_mount_slots);
+  if (t->n_attr_slots < 0 || t->n_attr_slots > OE_MAX_ATTR_SLOTS) return h->fail(OE_ERR_LIMIT, "n_attr_slots %d", t->n_attr_slots);
+  if (t->n_rr_cols < 0 || t->n_rr_cols > OE_MAX_RR_COLS) return h->fail(OE_ERR_LIMIT, "n_rr_cols %d", t->n_rr_cols);
+  if (t->n_exec_slots < 0 || t->n_exec_slots > OE_MAX_EXEC_SLOTS) return h->fail(OE_ERR_LIMIT, "n_exec_slots %d", t->n_exec_slots);
+  for (auto& op : h->h_ops) {
+    const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
+    const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
+    if (slotted && op.slot >= t->n_role_slots) return h->fail(OE_ERR_INVALID, "a stage op names role slot %d, offer table has %d", op.slot, t->n_role_slots);
+    const bool free_other = op.opcode == OE_OP_FREE && (op.kind == OE_KIND_PORTS || op.kind == OE_KIND_MOUNT);
+    if (scalar_like && !free_other && op.kind >= t->n_scalar_kinds) return h->fail(OE_ERR_INVALID, "a stage op names scalar kind %d, offer table has %d", op.kind, t->n_scalar_kinds);
+  }
+  for (auto& cs : h->h_csets)
+    if (cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= t->n_rr_cols) return h->fail(OE_ERR_INVALID, "a counter set names rr column %d, offer table has %d", cs.rr_col, t->n_rr_cols);
+  if (h->world > 1) {
+    if (t->shard_rows <= 0 || t->shard_rows % 1024 != 0) return h->fail(OE_ERR_INVALID, "sharded offer table needs shard_rows, a multiple of 1024");
+    if (t->row_offset != (int64_t)h->rank * t->shard_rows) return h->fail(OE_ERR_INVALID, "row_offset must be rank * shard_rows");
+    if (N > t->shard_rows) return h->fail(OE_ERR_INVALID, "shard holds more than shard_rows offers");
+    const int64_t Ng = t->n_offers_global;
+    if (Ng < 0 || Ng > (int64_t)h->world * t->shard_rows) return h->fail(OE_ERR_INVALID, "n_offers_global %lld does not fit %d shards of %lld rows", (long long)Ng, h->world, (long long)t->shard_rows);
+    const int64_t want = std::max<int64_t>(0, std::min<int64_t>(t->shard_rows, Ng - t->row_offset));
+    if (N != want) return h->fail(OE_ERR_INVALID, "shard %d must hold %lld of the %lld offers (every shard but the last is full), got %lld", h->rank, (long long)want, (long long)Ng, (long long)N);
+  } else if (t->row_offset != 0) {
+    return h->fail(OE_ERR_INVALID, "row_offset must be 0 when not sharded");
+  }
+  const bool no_alloc = pk && pk->alloc_role_is_const, no_host = pk && pk->hostname_is_agent, no_port = pk && pk->port_tuple_bytes;
+  if (N > 0 && (!t->scalar || !t->scalar_present || (!no_alloc && !t->alloc_role) || !t->agent_id || (!no_host && !t->hostname_id) || !t->zone_id || !t->region_id ||
+                (t->n_port_ranges && !no_port && !t->port_range) || (t->n_mount_slots && (!t->mount_size || !t->mount_profile)) ||
+                (t->n_attr_slots && !t->attr_id) || (t->n_rr_cols && !t->rr_key) || (t->n_exec_slots && !t->exec_id)))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers: missing column");
+  if (t->n_reserved < 0 || (t->n_reserved > 0 && (!t->reserved_begin || !t->reserved_id || !t->reserved_kind || !t->reserved_value)))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers: reserved side table");
+  if (t->n_reserved > 0) {
+    if (t->reserved_begin[0] != 0 || t->reserved_begin[N] != t->n_reserved) return h->fail(OE_ERR_INVALID, "reserved_begin does not span the side table");
+    for (int64_t i = 0; i < N; ++i)
+      if (t->reserved_begin[i + 1] < t->reserved_begin[i]) return h->fail(OE_ERR_INVALID, "reserved_begin not monotone");
+  }
+
+  return 0;
+}
+}  // namespace
+
+int32_t oe_load_offers_packed(oe_engine* h, const oe_offer_table* t, const oe_offer_packing* pk) {
+  if (!h || !t || !pk) return OE_ERR_INVALID;
+  if (!h->hasP) return h->fail(OE_ERR_STATE, "oe_load_offers_packed: load programs first");
+  CU(cudaSetDevice(h->device));
+  h->hasO = false;
+  h->class_bits_fresh = h->cycle_done = false;
+  h->tuples_valid = false; h->n_port_tuples = 0;
+  h->dof.ptuple = nullptr; h->dof.n_ptuples = 0;
+  if (int rc = check_offer_table(h, t, pk)) return rc;
+  auto width_ok = [](uint8_t b) { return b == 1 || b == 2 || b == 4; };
+  if (!width_ok(pk->present_bytes) || !width_ok(pk->zone_bytes) || !width_ok(pk->region_bytes) || !width_ok(pk->attr_bytes) || !width_ok(pk->rr_bytes) ||
+      !width_ok(pk->mount_profile_bytes) || !width_ok(pk->exec_bytes))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: a column width is not 1, 2 or 4 bytes");
+  if (pk->port_tuple_bytes != 0 && pk->port_tuple_bytes != 2 && pk->port_tuple_bytes != 4) return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: port_tuple_bytes must be 0, 2 or 4");
+  const int64_t N = t->n_offers;
+  const bool tuples = pk->port_tuple_bytes != 0 && t->n_port_ranges > 0;
+  if (tuples && (pk->n_port_tuples < 1 || !pk->port_tuples || (N > 0 && !pk->port_tuple_id))) return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: port_tuples / port_tuple_id missing");
+  if (tuples && pk->port_tuple_bytes == 2 && pk->n_port_tuples > 65536) return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: %d range lists do not fit 16-bit ids", pk->n_port_tuples);
+  const int present_bits = t->n_role_slots * t->n_scalar_kinds;
+  if (pk->present_bytes * 8 < present_bits) return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: %d presence bits do not fit %d byte(s)", present_bits, pk->present_bytes);
+  auto dict_fits = [](int n, uint8_t bytes) { return bytes == 4 || (int64_t)n < (1ll << (8 * bytes)) - 1; };
+  const oe_dict_sizes& dc = h->dict;
+  if (!dict_fits(dc.n_zones, pk->zone_bytes) || !dict_fits(dc.n_regions, pk->region_bytes) || !dict_fits(dc.n_attrs, pk->attr_bytes) ||
+      !dict_fits(dc.n_rr_values, pk->rr_bytes) || !dict_fits(OE_MAX_PROFILES, pk->mount_profile_bytes) || !dict_fits(dc.n_exec_ids, pk->exec_bytes))
+    return h->fail(OE_ERR_INVALID, "oe_load_offers_packed: a dictionary is too large for its column's width (the all-ones value stands for -1)");
+
+  DevOffers& o = h->dof;
+  o.N = N; o.row_offset = t->row_offset;
+  o.S = t->n_role_slots; o.K = t->n_scalar_kinds; o.R = t->n_port_ranges; o.D = t->n_mount_slots;
+  o.A = t->n_attr_slots; o.Q = t->n_rr_cols; o.E = t->n_exec_slots;
+  h->N = N; h->row_offset = t->row_offset; h->shard_rows = t->shard_rows; h->n_reserved = t->n_reserved;
+  h->N_global = t->n_offers_global > 0 ? t->n_offers_global : N;
+  const size_t n = (size_t)N;
+  if (h->offers_in_flight) {
+    CU(cudaStreamSynchronize(h->copy_stream));
+    h->offers_in_flight = false;
+  }
+  CU(h->d_scalar.ensure(std::max<size_t>(n * o.S * o.K, 1) * 8)); CU(h->d_present.ensure(std::max<size_t>(n, 1) * 4)); CU(h->d_port.ensure(std::max<size_t>(n * o.S * o.R, 1) * 4));
+  CU(h->d_msize.ensure(std::max<size_t>(n * o.D, 1) * 8)); CU(h->d_mprof.ensure(std::max<size_t>(n * o.D, 1) * 4));
+  for (int c = 0; c < 5; ++c) CU(h->d_ocols[c].ensure(std::max<size_t>(n, 1) * 4));
+  CU(h->d_oattr.ensure(std::max<size_t>(n * o.A, 1) * 4)); CU(h->d_orr.ensure(std::max<size_t>(n * o.Q, 1) * 4)); CU(h->d_oexec.ensure(std::max<size_t>(n * o.E, 1) * 4));
+  o.scalar = h->d_scalar.as<double>(); o.present = h->d_present.as<uint32_t>(); o.port = h->d_port.as<uint32_t>();
+  o.msize = h->d_msize.as<double>(); o.mprof = h->d_mprof.as<int32_t>();
+  o.alloc = h->d_ocols[0].as<int32_t>(); o.agent = h->d_ocols[1].as<int32_t>(); o.host = h->d_ocols[2].as<int32_t>();
+  o.zone = h->d_ocols[3].as<int32_t>(); o.region = h->d_ocols[4].as<int32_t>();
+  o.attr = h->d_oattr.as<int32_t>(); o.rr = h->d_orr.as<int32_t>(); o.exec = h->d_oexec.as<int32_t>();
+
+  // one wire column: where it lands (staging when narrower than the device column), and how it is widened
+  enum { W_SCALAR, W_PRESENT, W_MPROF, W_ZONE, W_REGION, W_ATTR, W_RR, W_EXEC, W_TUPLE, W_COUNT };
+  struct Wire { const void* src; void* dev; int slots; int wire_bytes, dev_bytes; void* stage; } w[W_COUNT] = {
+      {t->scalar, o.S * o.K ? h->d_scalar.p : nullptr, o.S * o.K, pk->scalar_is_f32 ? 4 : 8, 8, nullptr},
+      {t->scalar_present, h->d_present.p, 1, pk->present_bytes, 4, nullptr},
+      {t->mount_profile, h->d_mprof.p, o.D, pk->mount_profile_bytes, 4, nullptr},
+      {t->zone_id, h->d_ocols[3].p, 1, pk->zone_bytes, 4, nullptr},
+      {t->region_id, h->d_ocols[4].p, 1, pk->region_bytes, 4, nullptr},
+      {t->attr_id, h->d_oattr.p, o.A, pk->attr_bytes, 4, nullptr},
+      {t->rr_key, h->d_orr.p, o.Q, pk->rr_bytes, 4, nullptr},
+      {t->exec_id, h->d_oexec.p, o.E, pk->exec_bytes, 4, nullptr},
+      {tuples ? pk->port_tuple_id : nullptr, nullptr, tuples ? o.S : 0, pk->port_tuple_bytes, 4, nullptr},
+  };
+  static_assert(W_COUNT <= 12, "d_wire");
+  for (int c = 0; c < W_COUNT; ++c) {
+    if (w[c].slots > 0 && w[c].wire_bytes != w[c].dev_bytes) {
+      CU(h->d_wire[c].ensure(std::max<size_t>(n * w[c].slots, 1) * w[c].wire_bytes));
+      w[c].stage = h->d_wire[c].p;
+    }
+  }
+  if (tuples) {
+    CU(h->d_ptuple_id.ensure(std::max<size_t>(n * o.S, 1) * 4));
+    if (pk->port_tuple_bytes == 4) { CU(h->d_wire[W_TUPLE].ensure(std::max<size_t>(n * o.S, 1) * 4)); w[W_TUPLE].stage = h->d_wire[W_TUPLE].p; }
+  }
+
+  const bool async = (h->flags & OE_CFG_ASYNC_LOADS) != 0 && N > 0;
+  cudaStream_t ls = async ? h->copy_stream : h->stream;
+  if (async) {
+    if (h->pin_used) {
+      CU(cudaStreamSynchronize(h->side_stream));
+      CU(cudaStreamSynchronize(h->stream));
+      h->pin_used = 0;
+    }
+    if (!h->pin_arena && cudaMallocHost(reinterpret_cast<void**>(&h->pin_arena), (size_t)8 << 20) == cudaSuccess) h->pin_cap = (size_t)8 << 20;
+    cudaGetLastError();
+    CU(cudaEventRecord(h->ev_main, h->stream));
+    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_main, 0));
+  }
+  CU(cudaMemsetAsync(h->d_offer_err.p, 0, oe_engine::kMaxChunks * sizeof(int), ls));
+  if (t->n_reserved > 0) {
+    if (int rc = upload(h, h->d_rbegin, t->reserved_begin, n + 1, ls)) return rc;
+    if (int rc = upload(h, h->d_rid, t->reserved_id, (size_t)t->n_reserved, ls)) return rc;
+    if (int rc = upload(h, h->d_rkind, t->reserved_kind, (size_t)t->n_reserved, ls)) return rc;
+    if (int rc = upload(h, h->d_rval, t->reserved_value, (size_t)t->n_reserved, ls)) return rc;
+    o.rbegin = h->d_rbegin.as<int64_t>(); o.rid = h->d_rid.as<int32_t>(); o.rkind = h->d_rkind.as<int32_t>(); o.rval = h->d_rval.as<double>();
+    k_validate_ids<<<(unsigned)((t->n_reserved + 255) / 256), 256, 0, ls>>>(o.rid, t->n_reserved, 0, std::max(dc.n_res_ids, 1), 19, h->d_offer_err.as<int>());
+  } else {
+    o.rbegin = nullptr; o.rid = nullptr; o.rkind = nullptr; o.rval = nullptr;
+  }
+  if (tuples) {   // the distinct range lists: small, first over the bus, checked like a ports column of n_port_tuples rows
+    const size_t words = (size_t)pk->n_port_tuples * o.R;
+    CU(h->d_ptuples.ensure(std::max<size_t>(words, 1) * 4));
+    CU(cudaMemcpyAsync(h->d_ptuples.p, pk->port_tuples, words * 4, cudaMemcpyHostToDevice, ls));
+    k_validate_tuples<<<(unsigned)((pk->n_port_tuples + 255) / 256), 256, 0, ls>>>(h->d_ptuples.as<uint32_t>(), pk->n_port_tuples, o.R, 18, h->d_offer_err.as<int>());
+  }
+
+  int nch = 1;
+  if (async) {
+    nch = (int)std::max<int64_t>(1, std::min<int64_t>(4, N / 131072));
+    if (const char* ev = getenv("OE_OFFER_CHUNKS")) nch = std::max(1, std::min(oe_engine::kMaxChunks, atoi(ev)));
+  }
+  const int64_t chunk_rows = std::max<int64_t>(8192, round_up((N + nch - 1) / nch, 8192));
+  nch = (int)std::max<int64_t>(1, (N + chunk_rows - 1) / chunk_rows);
+  h->n_chunks = nch;
+  const OfferLimits lim{dc.n_agents, dc.n_hostnames, dc.n_zones, dc.n_regions, dc.n_attrs, dc.n_rr_values};
+  auto blocks = [](int64_t elems) { return (unsigned)std::max<int64_t>(1, (elems + 255) / 256); };
+  for (int c = 0; c < nch; ++c) {
+    const int64_t r0 = c * chunk_rows, r1 = std::min<int64_t>(N, r0 + chunk_rows);
+    h->chunks[c].r0 = r0; h->chunks[c].r1 = r1;
+    if (r1 > r0) {
+      for (int q = 0; q < W_COUNT; ++q) {
+        if (w[q].slots <= 0) continue;
+        void* dst = w[q].stage ? w[q].stage : w[q].dev;
+        if (int rc = copy_rows(h, dst, w[q].src, (size_t)w[q].wire_bytes, w[q].slots, N, r0, r1, ls)) return rc;
+      }
+      if (int rc = copy_rows(h, h->d_msize.p, t->mount_size, 8, o.D, N, r0, r1, ls)) return rc;
+      if (int rc = copy_rows(h, h->d_ocols[1].p, t->agent_id, 4, 1, N, r0, r1, ls)) return rc;
+      if (!tuples) if (int rc = copy_rows(h, h->d_port.p, t->port_range, 4, o.S * o.R, N, r0, r1, ls)) return rc;
+      if (pk->hostname_is_agent) CU(cudaMemcpyAsync(h->d_ocols[2].as<int32_t>() + r0, h->d_ocols[1].as<int32_t>() + r0, (size_t)(r1 - r0) * 4, cudaMemcpyDeviceToDevice, ls));
+      else if (int rc = copy_rows(h, h->d_ocols[2].p, t->hostname_id, 4, 1, N, r0, r1, ls)) return rc;
+      if (pk->alloc_role_is_const) k_fill_i32<<<blocks(r1 - r0), 256, 0, ls>>>(h->d_ocols[0].as<int32_t>(), pk->alloc_role_const, r0, r1);
+      else if (int rc = copy_rows(h, h->d_ocols[0].p, t->alloc_role, 4, 1, N, r0, r1, ls)) return rc;
+      // widen what came narrow
+      if (w[W_SCALAR].stage) k_widen_f32<<<blocks((r1 - r0) * w[W_SCALAR].slots), 256, 0, ls>>>(h->d_scalar.as<double>(), static_cast<const float*>(w[W_SCALAR].stage), w[W_SCALAR].slots, N, r0, r1);
+      auto widen = [&](int q, bool absent) {
+        if (!w[q].stage || w[q].slots <= 0) return;
+        int32_t* dst = static_cast<int32_t*>(w[q].dev);
+        const unsigned g = blocks((r1 - r0) * w[q].slots);
+        if (w[q].wire_bytes == 1) {
+          if (absent) k_widen_ids<uint8_t, true><<<g, 256, 0, ls>>>(dst, static_cast<const uint8_t*>(w[q].stage), w[q].slots, N, r0, r1);
+          else k_widen_ids<uint8_t, false><<<g, 256, 0, ls>>>(dst, static_cast<const uint8_t*>(w[q].stage), w[q].slots, N, r0, r1);
+        } else {
+          if (absent) k_widen_ids<uint16_t, true><<<g, 256, 0, ls>>>(dst, static_cast<const uint16_t*>(w[q].stage), w[q].slots, N, r0, r1);
+          else k_widen_ids<uint16_t, false><<<g, 256, 0, ls>>>(dst, static_cast<const uint16_t*>(w[q].stage), w[q].slots, N, r0, r1);
+        }
+      };
+      widen(W_PRESENT, false);
+      widen(W_MPROF, true); widen(W_ZONE, true); widen(W_REGION, true); widen(W_ATTR, true); widen(W_RR, true); widen(W_EXEC, true);
+      if (tuples) {
+        const unsigned g = blocks((r1 - r0) * o.S);
+        if (pk->port_tuple_bytes == 2)
+          k_expand_tuples<uint16_t><<<g, 256, 0, ls>>>(h->d_port.as<uint32_t>(), h->d_ptuple_id.as<int32_t>(), static_cast<const uint16_t*>(w[W_TUPLE].stage), h->d_ptuples.as<uint32_t>(),
+                                                       pk->n_port_tuples, o.S, o.R, N, r0, r1, h->d_offer_err.as<int>() + c);
+        else
+          k_expand_tuples<uint32_t><<<g, 256, 0, ls>>>(h->d_port.as<uint32_t>(), h->d_ptuple_id.as<int32_t>(), static_cast<const uint32_t*>(w[W_TUPLE].stage), h->d_ptuples.as<uint32_t>(),
+                                                       pk->n_port_tuples, o.S, o.R, N, r0, r1, h->d_offer_err.as<int>() + c);
+      }
+      k_validate_offer_rows<<<blocks(r1 - r0), 256, 0, ls>>>(o, lim, r0, r1, h->d_offer_err.as<int>() + c);
+      CU(cudaGetLastError());
+    }
+    CU(cudaMemcpyAsync(h->h_offer_err + c, h->d_offer_err.as<int>() + c, sizeof(int), cudaMemcpyDeviceToHost, ls));
+    CU(cudaEventRecord(h->chunks[c].landed, ls));
+  }
+  if (tuples) {
+    h->n_port_tuples = pk->n_port_tuples;
+    h->tuples_valid = true;
+    o.ptuple = h->d_ptuple_id.as<int32_t>();   // slot 0's ids come first
+    o.n_ptuples = pk->n_port_tuples;
+  }
+  h->hasO = true;
+  if (async) {
+    h->offers_in_flight = true;
+    h->validation_pending = true;
+  } else {
+    h->offers_in_flight = true;   // wait_offers reads every chunk's verdict
+    if (int rc = wait_offers(h, "oe_load_offers_packed")) return rc;
+    CU(cudaStreamSynchronize(ls));
+  }
+  return OE_OK;
+}
+
 int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* t) {
   if (!h || !t || (n_rows > 0 && !rows)) return OE_ERR_INVALID;
   if (!h->hasO) return h->fail(OE_ERR_STATE, "oe_update_offers: no resident offer table (oe_load_offers first)");
@@ -2178,6 +2460,7 @@ int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, cons
   for (int64_t k = 0; k < n_rows; ++k)
     if (rows[k] < 0 || rows[k] >= o.N) return h->fail(OE_ERR_INVALID, "oe_update_offers: rows[%lld] = %lld is not a row of the resident table", (long long)k, (long long)rows[k]);
   h->class_bits_fresh = h->cycle_done = false;
+  h->tuples_valid = false;   // the patched rows' range lists are no longer the ones their list ids name: per-offer port tests from here on
   const size_t n = (size_t)n_rows;
   // one staging buffer, column after column, each 8-byte aligned
   const size_t slots8 = (size_t)o.S * o.K + o.D, slots4 = 1 + (size_t)o.S * o.R + o.D + 5 + o.A + o.Q + o.E;
@@ -2516,7 +2799,7 @@ int build_fast_rows(oe_engine* h) {
         case OE_OP_EXEC_ID: ok = op.arg < 0; break;
         case OE_OP_RULE:
           if (++n_rules > 1) { ok = false; break; }
-          fr.rule_begin = op.arg; fr.rule_count = (int32_t)op.aux;
+          fr.rule_begin = op.arg; fr.rule_count = (uint16_t)op.aux;
           break;
         case OE_OP_SCALAR_NEW: {
           const int q = op.slot * K + op.kind;
@@ -2590,6 +2873,7 @@ int build_fast_rows(oe_engine* h) {
       if (zone_region_only) fr.flags |= OE_FR_RULE_TAB;
     }
     if (ok) fr.flags |= OE_FR_FAST; else fr.flags = 0;
+    fr.cls = (uint16_t)c;
     any_tab = any_tab || (fr.flags & OE_FR_RULE_TAB);
     rows[c] = fr;
   }
@@ -2629,6 +2913,19 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
                                                   h->tab_zdim, h->tab_rdim);
       ++*launches;
     }
+    a.ptab.bits = nullptr; a.ptab.words = 0;
+    if (h->tuples_valid && h->dof.ptuple && h->dof.R <= OE_FAST_RANGES && h->n_port_tuples > 0 && h->C > 0) {
+      // few distinct `ports` range lists (stock agents offer the same ranges): a class's port stages once per list.  With
+      // nearly as many lists as offers the table would cost what it saves, and the per-offer test stays.
+      if ((int64_t)h->n_port_tuples * 4 <= std::max<int64_t>(h->N, 4096)) {
+        a.ptab.words = (h->n_port_tuples + 31) / 32;
+        CU(h->d_port_tab.ensure((size_t)h->C * a.ptab.words * 4));
+        k_port_tables<<<dim3((unsigned)((h->n_port_tuples + 127) / 128), (unsigned)h->C), 128, 0, h->stream>>>(
+            h->d_fast.as<FastRow>(), h->d_ptuples.as<uint32_t>(), h->n_port_tuples, h->dof.R, h->d_port_tab.as<uint32_t>(), a.ptab.words);
+        ++*launches;
+        a.ptab.bits = h->d_port_tab.as<uint32_t>();
+      }
+    }
     a.F = h->d_F.as<uint32_t>(); a.stride = stride; a.rows = rows;
     a.fast = h->d_fast.as<FastRow>();
     a.n_nodes = h->n_rule_nodes <= OE_K1_MAX_SMEM_NODES ? h->n_rule_nodes : 0;
@@ -2665,16 +2962,14 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       dim3 grid((unsigned)xblocks, (unsigned)tiles);
       const bool fast_ranges = h->dof.R <= OE_FAST_RANGES;
       const bool few = h->dof.S * h->dof.K <= 4;   // the dense form then tests four pool entries, not eight
-      const int variant = (fast_ranges ? 4 : 0) | (h->peers_attached ? 2 : 0) | (few ? 1 : 0);
+      const int ports = a.ptab.bits ? 2 : fast_ranges ? 1 : 0;
+      const int variant = ports * 4 + (h->peers_attached ? 2 : 0) + (few ? 1 : 0);
       switch (variant) {
-        case 7: k_class_feasibility<true, true, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 6: k_class_feasibility<true, true, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 5: k_class_feasibility<true, false, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 4: k_class_feasibility<true, false, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 3: k_class_feasibility<false, true, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 2: k_class_feasibility<false, true, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        case 1: k_class_feasibility<false, false, 4><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
-        default: k_class_feasibility<false, false, 8><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+#define OE_K1_CASE(V, P, X, Q) case V: k_class_feasibility<P, X, Q><<<grid, OE_K1_THREADS, smem, h->stream>>>(h->ctx(), a); break;
+        OE_K1_CASE(0, 0, false, 8) OE_K1_CASE(1, 0, false, 4) OE_K1_CASE(2, 0, true, 8) OE_K1_CASE(3, 0, true, 4)
+        OE_K1_CASE(4, 1, false, 8) OE_K1_CASE(5, 1, false, 4) OE_K1_CASE(6, 1, true, 8) OE_K1_CASE(7, 1, true, 4)
+        OE_K1_CASE(8, 2, false, 8) OE_K1_CASE(9, 2, false, 4) OE_K1_CASE(10, 2, true, 8) OE_K1_CASE(11, 2, true, 4)
+#undef OE_K1_CASE
       }
       ++*launches;
       CU(cudaGetLastError());

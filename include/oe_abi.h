@@ -385,6 +385,39 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t);
 int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* values);
 int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t);
 
+/* Compact wire format of the offer table.  An offer row of oe_offer_table is ~100 bytes, and at 10^6 offers the PCIe copy of
+ * the table IS the placement cycle's latency; most of those bytes carry no information: the allocation role is the same for
+ * every row, zone / region / attribute ids fit one byte, the scalar amounts Mesos reports are exact in fp32, and nearly all
+ * agents offer one of a handful of `ports` range lists.  oe_load_offers_packed takes the same oe_offer_table, but its column
+ * pointers are read as this struct says; the engine widens the columns on the device (exactly: no value changes) into the
+ * layout oe_load_offers builds, so every evaluation call behaves as after a plain load.  The encoder decides per column and
+ * per table (the host side of S/offer/MesosResourcePool.java:76-147: it sees every value while it sums the pools).
+ *   *_bytes           element size on the wire of that id column: 4 (int32 as in oe_offer_table), 2 or 1 (unsigned; the type's
+ *                     all-ones value stands for -1, so the dictionary must be smaller than that)
+ *   scalar_is_f32     `scalar` points at float [S][K][N]; the encoder verified value == (double)(float)value for every entry
+ *   hostname_is_agent hostname_id is not read: every row's hostname id equals its agent id (one hostname per agent, ids
+ *                     assigned together)
+ *   alloc_role_is_const  alloc_role is not read: every row holds alloc_role_const (-1 when no offer carries an allocation role)
+ *   port_tuple_bytes  0: port_range is sent per offer as in oe_load_offers.  2 or 4: port_range is NOT read; port_tuples holds
+ *                     the n_port_tuples DISTINCT range lists of the table ([n_port_tuples][R], each sorted, disjoint,
+ *                     OE_PORT_EMPTY padded) and port_tuple_id [S][N] (unsigned, that many bytes) names each (slot, offer)'s list.
+ *                     The feasibility kernel then evaluates a class's port stages once per distinct list instead of once per offer.
+ * Everything else (row counts, slot counts, mount_size, agent_id, the reserved side table) is as in oe_offer_table.           */
+typedef struct {
+  uint8_t scalar_is_f32;
+  uint8_t present_bytes;
+  uint8_t zone_bytes, region_bytes, attr_bytes, rr_bytes, mount_profile_bytes, exec_bytes;
+  uint8_t hostname_is_agent;
+  uint8_t alloc_role_is_const;
+  uint8_t port_tuple_bytes;
+  uint8_t reserved0[5];
+  int32_t alloc_role_const;
+  int32_t n_port_tuples;
+  const uint32_t* port_tuples;
+  const void* port_tuple_id;
+} oe_offer_packing;
+int32_t oe_load_offers_packed(oe_engine* h, const oe_offer_table* t, const oe_offer_packing* pk);
+
 /* ------------------------------------------------------------------------------------------------------------------
  * Evaluation
  * ---------------------------------------------------------------------------------------------------------------- */

@@ -497,9 +497,13 @@ def _full_size_against_cached_oracle(engine, cl, variant_rows=8, shards=0, arriv
     assert s_gpu["n_placed"] == s_cpu["n_placed"] > 0
     assert engine.evaluate_cycle()[0].tobytes() == d_cpu.tobytes()      # run to run
     orc.close()
-    if arriving:   # the table evaluated while it arrives in chunks, committed in two passes
+    if arriving:   # the table evaluated while it arrives in chunks, committed in two passes — plain and packed wire form
         eng2 = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
         eng2.load(t)
+        assert eng2.evaluate_cycle()[0].tobytes() == d_cpu.tobytes()
+        _load_packed(eng2, t)
+        assert np.array_equal(eng2.class_feasibility()[0], f)
+        _load_packed(eng2, t)
         assert eng2.evaluate_cycle()[0].tobytes() == d_cpu.tobytes()
         eng2.close()
     if shards:     # shards on this device, class rows exchanged through the peer regions
@@ -533,6 +537,67 @@ def test_c5_variants_full_size(engine, which):
 def test_c5_variants_small_against_the_literal_oracle(engine, which):
     cl = synth.config_c5_variant(which, 0.004)
     _compare_all(engine, cl.tables)
+
+
+def _load_packed(eng, t, packed=None, **kw):
+    eng.tables = t
+    eng.load_programs(t)
+    eng.load_tasks(t)
+    eng.load_offers_packed(packed or abi.PackedOffers(t), **kw)
+    eng.load_requirements(t)
+    return eng
+
+
+@pytest.mark.parametrize("flags", [0, abi.OE_CFG_ASYNC_LOADS], ids=["sync", "async"])
+def test_packed_offer_table_gives_what_the_plain_table_gives(engine, flags):
+    """oe_load_offers_packed: narrow ids, fp32 scalars where exact, `ports` as ids of distinct range lists — widened on the
+    device; matrix, failed-stage masks and decisions must be those of the plain load and of the oracle."""
+    eng = Engine(device=0, flags=flags)
+    for seed in list(range(40)) + list(range(2000, 2020)):
+        t = random_tables(seed, new_pods_only=seed >= 2000)
+        if seed % 3 == 0:          # scalars that do not survive fp32: that column must travel as fp64
+            t.scalar = t.scalar + 1e-9
+        orc = Oracle().load(t)
+        packed = abi.PackedOffers(t)
+        assert packed.scalar_is_f32 == (seed % 3 != 0) or t.n_offers == 0 or not t.scalar.any()
+        _load_packed(eng, t, packed)
+        m_cpu, _ = orc.feasibility()
+        m_gpu, _ = eng.feasibility()
+        assert np.array_equal(unpack_bits(m_gpu, t.n_offers), unpack_bits(m_cpu, t.n_offers)), seed
+        assert eng.evaluate_cycle()[0].tobytes() == orc.evaluate_cycle()[0].tobytes(), seed
+        assert np.array_equal(eng.stage_failures(), orc.stage_failures()[0]), seed
+        orc.close()
+    # the C5 shape: few distinct range lists, so the port stages run once per list (k_port_tables) instead of once per offer
+    for cl in (synth.make_cluster(6000, 500, 8, 3, 4, 160, "c5"), synth.config_c5_variant("mount", 0.004), synth.config_c4(0.3)):
+        t = cl.tables
+        packed = abi.PackedOffers(t)
+        assert packed.port_tuple_bytes == 2 and len(packed.cols["port_tuples"]) < 200
+        engine.load(t)
+        want_f, _ = engine.class_feasibility()
+        want_d, _ = engine.evaluate_cycle()
+        _load_packed(eng, t, packed)
+        got_f, _ = eng.class_feasibility()
+        assert np.array_equal(got_f, want_f)
+        assert eng.evaluate_cycle()[0].tobytes() == want_d.tobytes()
+        # rows replaced in place afterwards: their range lists change, the per-list lookup must not be used any more
+        rows = np.arange(0, t.n_offers, 7)
+        t2 = synth.make_cluster(t.n_offers, 10, 8, 3, 4, 0, "c5", seed=99).tables if cl.name != "c5-mount-1M-offers-x-100k-instances" else None
+        if t2 is not None and t2.port_range.shape == t.port_range.shape and t2.mount_size.shape == t.mount_size.shape:
+            t2.port_range = t2.port_range.copy()
+            t2.port_range[0, 0, rows] = (1025) | (1030 << 16)
+            eng.update_offers(rows, t2)
+            engine.update_offers(rows, t2)
+            eng.load_requirements(t); engine.load_requirements(t)
+            assert np.array_equal(eng.class_feasibility()[0], engine.class_feasibility()[0])
+    # a list id outside the dictionary is reported, not followed
+    t = synth.make_cluster(3000, 20, 4, 2, 2, 0, "c5").tables
+    packed = abi.PackedOffers(t)
+    packed.cols["port_tuple_id"] = packed.cols["port_tuple_id"].copy()
+    packed.cols["port_tuple_id"][0, 17] = 60000
+    with pytest.raises(abi.EngineError, match="range list"):
+        _load_packed(eng, t, packed)
+        eng.evaluate_cycle()
+    eng.close()
 
 
 def test_invalid_tables_are_rejected_not_faulted(engine):
