@@ -1267,6 +1267,313 @@ __global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
   if (lane == 0 && placed) atomicAdd(a.n_placed, placed);
 }
 
+// ---- K2 from the offers' side (any number of bit rows, at most 32 per component) ----------------------------------------------
+// The greedy order of PlanScheduler.resourceOffers (requirements in plan order, each takes the lowest free offer of its row) is a
+// stable matching in which every requirement ranks offers by index and every offer ranks requirements by plan position; with one
+// ranking per side that matching is unique, and it is reached from either side.  From the offers' side: offers in ascending
+// index order, each goes to the EARLIEST unmatched requirement whose row lists it.  (Proof sketch: let offer i list requirement j.
+// If j, at its turn, finds i free, then every lower offer of its row was taken by then, so j takes i unless an earlier requirement
+// that lists i did — which is "the earliest unmatched requirement that lists i" once all lower offers have been handed out.)
+// Requirements of one row are interchangeable, so the earliest unmatched one of a row is the head of the row's queue, and the
+// replay state is one queue position per row — no bitmap of taken offers, no windows, no search.  Per component (rows that share
+// offers, K3d) one warp walks the component's offers; lane k keeps the head of the component's k-th row; a step is
+//     v = offer lists my row ? my head : none;   winner = warp-wide minimum;   the winning lane records the match and advances.
+// The chain from one step to the next is select -> REDUX.MIN -> compare -> select on `head`; offers and masks arrive 32 at a
+// time, a chunk nobody can use costs one ballot, and a pass over a later part of the offers (the table arriving in chunks) simply
+// resumes from the rows' queue positions.
+#define OE_OS_MAX_ROWS 2048       // bit rows (classes + re-deployed pods) this path takes; beyond: k_commit
+#define OE_OS_SORT_BLOCK 1024     // items per block of the stable counting sorts
+
+// Rows > 64: components by union-find over "rows that list the same offer".  thread = one offer.
+__device__ __forceinline__ int uf_find(int* parent, int x) {
+  for (;;) {
+    const int px = *reinterpret_cast<volatile int*>(parent + x);
+    if (px == x) return x;
+    const int ppx = *reinterpret_cast<volatile int*>(parent + px);
+    if (ppx != px) parent[x] = ppx;   // path halving; a lost update only costs a step
+    x = px;
+  }
+}
+__global__ void __launch_bounds__(128) k_row_link(RowBits rb, int* __restrict__ parent) {
+  extern __shared__ uint32_t link_tile[];   // [rows][4]
+  const int64_t gw0 = (int64_t)blockIdx.x * 4;
+  for (int q = threadIdx.x; q < rb.rows * 4; q += 128) {
+    const int r = q >> 2;
+    const int64_t gw = gw0 + (q & 3);
+    link_tile[q] = gw < rb.total_words ? rb.word(r, gw) : 0u;
+  }
+  __syncthreads();
+  const int wq = threadIdx.x >> 5, b = threadIdx.x & 31;
+  int first = -1;
+  for (int r = 0; r < rb.rows; ++r) {
+    const uint32_t w = link_tile[r * 4 + wq];
+    if (!((w >> b) & 1u)) continue;
+    if (first < 0) { first = r; continue; }
+    int a = first, c = r;
+    for (;;) {
+      a = uf_find(parent, a); c = uf_find(parent, c);
+      if (a == c) break;
+      if (a > c) { const int t = a; a = c; c = t; }
+      if (atomicCAS(parent + c, c, a) == c) break;
+    }
+  }
+}
+
+// Components -> dense ids in order of their lowest row, every row's index inside its component, the rows grouped by component.
+// info[0] = components, info[1] = rows of the widest one.  One CTA; the numbering itself is serial (rows <= OE_OS_MAX_ROWS).
+struct RowGroups {
+  int* comp_of;         // [rows]
+  int* lrow;            // [rows]
+  int* comp_rows;       // [rows] rows, component by component
+  int* comp_row_begin;  // [rows + 1]
+  int* info;            // [2]
+};
+__global__ void __launch_bounds__(256) k_group_rows(int rows, const unsigned long long* __restrict__ adj, int* __restrict__ parent, RowGroups g) {
+  extern __shared__ int grp_smem[];
+  int* comp = grp_smem;           // [rows]
+  int* count = comp + rows;       // [rows]
+  int* begin = count + rows;      // [rows + 1]
+  __shared__ unsigned long long s_adj[64];
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) { comp[r] = -1; count[r] = 0; }
+  if (adj) for (int r = threadIdx.x; r < rows && r < 64; r += blockDim.x) s_adj[r] = adj[r];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int n = 0;
+    if (!parent) {            // rows <= 64: breadth-first over the adjacency masks (or one row: one component)
+      unsigned long long seen = 0ull;
+      for (int r = 0; r < rows; ++r) {
+        if ((seen >> r) & 1ull) continue;
+        unsigned long long group = 1ull << r, frontier = group;
+        while (adj && frontier) {
+          const int q = __ffsll((long long)frontier) - 1;
+          frontier &= frontier - 1;
+          const unsigned long long nb = s_adj[q] & ~group;
+          group |= nb;
+          frontier |= nb;
+        }
+        seen |= group;
+        for (int q = 0; q < rows; ++q) if ((group >> q) & 1ull) comp[q] = n;
+        ++n;
+      }
+    } else {
+      // roots carry the lowest row of their set (unions attach the higher root under the lower)
+      for (int r = 0; r < rows; ++r) {
+        const int root = uf_find(parent, r);
+        if (comp[root] < 0) comp[root] = n++;   // root <= r: numbered when its lowest row comes by
+        comp[r] = comp[root];
+      }
+    }
+    int widest = 0;
+    for (int r = 0; r < rows; ++r) { g.lrow[r] = count[comp[r]]++; g.comp_of[r] = comp[r]; }
+    int run = 0;
+    for (int c = 0; c < n; ++c) { begin[c] = run; run += count[c]; widest = max(widest, count[c]); }
+    begin[n] = run;
+    for (int c = 0; c <= n; ++c) g.comp_row_begin[c] = begin[c];
+    for (int r = 0; r < rows; ++r) g.comp_rows[begin[comp[r]] + g.lrow[r]] = r;
+    g.info[0] = n; g.info[1] = widest;
+  }
+}
+
+// Per offer: its component and which of the component's rows list it (bit k = the component's k-th row); -1 when no row does.
+// CTA = OE_OS_SORT_BLOCK offers; it also counts its offers per component for the sort that follows.
+__global__ void __launch_bounds__(256) k_offer_masks(RowBits rb, const int* __restrict__ comp_of, const int* __restrict__ lrow, const int* __restrict__ info,
+                                                     int32_t* __restrict__ ocomp, uint32_t* __restrict__ omask, int* __restrict__ hist) {
+  extern __shared__ int om_smem[];
+  const int rows = rb.rows;
+  const int n_comp = info[0];
+  int* s_comp = om_smem;                 // [rows]
+  int* s_lrow = s_comp + rows;           // [rows]
+  int* s_hist = s_lrow + rows;           // [rows] (n_comp <= rows)
+  uint32_t* s_words = reinterpret_cast<uint32_t*>(s_hist + rows);   // [rows][8]: the 8 words of this pass of 256 offers
+  for (int r = threadIdx.x; r < rows; r += 256) { s_comp[r] = comp_of[r]; s_lrow[r] = lrow[r]; s_hist[r] = 0; }
+  const int64_t words_per_block = OE_OS_SORT_BLOCK / 32;
+  for (int pass = 0; pass < OE_OS_SORT_BLOCK / 256; ++pass) {
+    const int64_t gw0 = (int64_t)blockIdx.x * words_per_block + pass * 8;
+    __syncthreads();
+    for (int q = threadIdx.x; q < rows * 8; q += 256) {
+      const int64_t gw = gw0 + (q & 7);
+      s_words[q] = gw < rb.total_words ? rb.word(q >> 3, gw) : 0u;
+    }
+    __syncthreads();
+    const int wq = threadIdx.x >> 5, b = threadIdx.x & 31;
+    int c = -1;
+    uint32_t m = 0u;
+    for (int r = 0; r < rows; ++r) {
+      const uint32_t w = s_words[r * 8 + wq];
+      if ((w >> b) & 1u) { c = s_comp[r]; m |= 1u << (s_lrow[r] & 31); }
+    }
+    const int64_t gi = (gw0 + wq) * 32 + b;
+    if (gw0 + wq < rb.total_words) { ocomp[gi] = c; omask[gi] = m; }
+    if (c >= 0) atomicAdd(&s_hist[c], 1);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < n_comp; c += 256) hist[(int64_t)blockIdx.x * rows + c] = s_hist[c];
+}
+
+// Stable counting sort, three kernels.  keys[i] in [0, *n_keys) or negative (dropped); blocks of OE_OS_SORT_BLOCK items.
+//   k_key_hist     per block: items per key                     (the offers' histogram comes from k_offer_masks instead)
+//   k_key_scan     one CTA: where every (block, key) starts; key_begin[k] = start of key k, key_begin[n_keys] = items kept
+//   k_key_scatter  one warp per block walks its items in order: out_idx[pos] = item, out_aux[pos] = aux[item]
+__global__ void __launch_bounds__(256) k_key_hist(const int32_t* __restrict__ keys, int64_t n, int key_stride, int* __restrict__ hist) {
+  extern __shared__ int kh_smem[];
+  for (int k = threadIdx.x; k < key_stride; k += 256) kh_smem[k] = 0;
+  __syncthreads();
+  const int64_t lo = (int64_t)blockIdx.x * OE_OS_SORT_BLOCK;
+  for (int q = threadIdx.x; q < OE_OS_SORT_BLOCK; q += 256) {
+    const int64_t i = lo + q;
+    if (i < n) { const int k = keys[i]; if (k >= 0) atomicAdd(&kh_smem[k], 1); }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < key_stride; k += 256) hist[(int64_t)blockIdx.x * key_stride + k] = kh_smem[k];
+}
+__global__ void __launch_bounds__(1024) k_key_scan(int* __restrict__ hist, int n_blocks, int key_stride, const int* __restrict__ n_keys_ptr, int n_keys_fixed,
+                                                   int* __restrict__ key_begin) {
+  __shared__ int warp_sum[32];
+  __shared__ int carry;
+  const int n_keys = n_keys_ptr ? *n_keys_ptr : n_keys_fixed;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int k0 = 0; k0 < n_keys; k0 += 1024) {
+    const int k = k0 + threadIdx.x;
+    int total = 0;
+    if (k < n_keys)
+      for (int b = 0; b < n_blocks; ++b) { const int v = hist[(int64_t)b * key_stride + k]; hist[(int64_t)b * key_stride + k] = total; total += v; }
+    int incl = total;
+    for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_sum[lane], wi = w;
+      for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, wi, d); if (lane >= d) wi += x; }
+      warp_sum[lane] = wi - w;
+    }
+    __syncthreads();
+    const int excl = carry + warp_sum[warp] + incl - total;
+    if (k < n_keys) key_begin[k] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) key_begin[n_keys] = carry;
+}
+__global__ void __launch_bounds__(32) k_key_scatter(const int32_t* __restrict__ keys, int64_t n, int key_stride, const int* __restrict__ hist,
+                                                    const int* __restrict__ key_begin, const uint32_t* __restrict__ aux, int32_t* __restrict__ out_idx,
+                                                    uint32_t* __restrict__ out_aux) {
+  extern __shared__ int ks_run[];   // [key_stride]: next slot of every key for this block
+  const int lane = threadIdx.x;
+  const int64_t lo = (int64_t)blockIdx.x * OE_OS_SORT_BLOCK;
+  // only the keys this block holds are looked at, so only those are initialised: first touch below
+  for (int q = 0; q < OE_OS_SORT_BLOCK; q += 32) {
+    const int64_t i = lo + q + lane;
+    const int k = i < n ? keys[i] : -1;
+    if (k >= 0) ks_run[k] = -1;
+  }
+  __syncwarp();
+  for (int q = 0; q < OE_OS_SORT_BLOCK; q += 32) {
+    const int64_t i = lo + q + lane;
+    const int k = i < n ? keys[i] : -1;
+    const uint32_t same = __match_any_sync(0xffffffffu, k);
+    if (k >= 0) {
+      const int leader = __ffs(same) - 1;
+      int base = 0;
+      if (lane == leader) {
+        base = ks_run[k];
+        if (base < 0) base = key_begin[k] + hist[(int64_t)blockIdx.x * key_stride + k];
+        ks_run[k] = base + __popc(same);
+      }
+      base = __shfl_sync(same, base, leader);
+      const int pos = base + __popc(same & ((1u << lane) - 1u));
+      out_idx[pos] = (int32_t)i;
+      if (out_aux) out_aux[pos] = aux[i];
+    }
+    __syncwarp();
+  }
+}
+
+// Decisions before the replay: no offer.
+__global__ void k_clear_decisions(oe_decision* __restrict__ dec, int64_t M) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  uint4* p = reinterpret_cast<uint4*>(dec + j);
+  p[0] = make_uint4(0xffffffffu, 0u, 0u, 0u);   // offer_row = -1
+  p[1] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+struct OfferSideArgs {
+  const int* info;             // [0] = components
+  const int* comp_begin;       // [components + 1] into list / mask (offers sorted by component, ascending inside)
+  const int32_t* list;         // offer index relative to the pass's first offer
+  const uint32_t* mask;
+  const int* comp_rows;
+  const int* comp_row_begin;
+  const int* row_begin;        // [rows + 1] into queue (requirements sorted by row, plan order inside)
+  const int32_t* queue;
+  int* row_cursor;             // [rows] requirements of the row matched so far (carried from pass to pass)
+  int32_t offer_offset;        // global index of the pass's first offer
+  oe_decision* dec;
+  int* n_placed;
+  long long* trace;            // optional: per component {steps, cycles, chunks, chunks skipped}
+};
+#define OE_OS_NONE 0x7fffffff
+__global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
+  const int comp = blockIdx.x, lane = threadIdx.x;
+  if (comp >= a.info[0]) return;
+  const long long t0 = clock64();
+  const int rb0 = a.comp_row_begin[comp], n_rows = a.comp_row_begin[comp + 1] - rb0;
+  const int row = lane < n_rows ? a.comp_rows[rb0 + lane] : -1;
+  int idx = 0, end = 0;
+  if (row >= 0) { idx = a.row_begin[row] + a.row_cursor[row]; end = a.row_begin[row + 1]; }
+  const int32_t* __restrict__ Q = a.queue;
+  // the lane's next four requirements: the queue is read three matches ahead of its use
+  int h = idx < end ? __ldg(Q + idx) : OE_OS_NONE;
+  int n1 = idx + 1 < end ? __ldg(Q + idx + 1) : OE_OS_NONE;
+  int n2 = idx + 2 < end ? __ldg(Q + idx + 2) : OE_OS_NONE;
+  int n3 = idx + 3 < end ? __ldg(Q + idx + 3) : OE_OS_NONE;
+  const int e0 = a.comp_begin[comp], e1 = a.comp_begin[comp + 1];
+  int placed = 0, steps = 0, chunks = 0, skipped = 0;
+  int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
+  uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
+  for (int base = e0; base < e1; base += 32) {
+    const int o_mine = o_next;
+    const uint32_t m_mine = m_next;
+    {  // the chunk after this one, a chunk ahead of its use
+      const int e = base + 32 + lane;
+      o_next = e < e1 ? __ldg(a.list + e) : -1;
+      m_next = e < e1 ? __ldg(a.mask + e) : 0u;
+    }
+    const uint32_t active = __ballot_sync(0xffffffffu, h != OE_OS_NONE);   // rows that still have a requirement waiting
+    if (!active) break;
+    uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
+    ++chunks;
+    skipped += want == 0u;
+    while (want) {
+      const int e = __ffs(want) - 1;
+      want &= want - 1;
+      const uint32_t m = __shfl_sync(0xffffffffu, m_mine, e);
+      const int o = __shfl_sync(0xffffffffu, o_mine, e);
+      const int v = ((m >> lane) & 1u) ? h : OE_OS_NONE;
+      const int mn = __reduce_min_sync(0xffffffffu, v);
+      const bool won = v == mn && mn != OE_OS_NONE;
+      if (won) {
+        a.dec[h].offer_row = o + a.offer_offset;
+        h = n1; n1 = n2; n2 = n3;
+        n3 = idx + 4 < end ? __ldg(Q + idx + 4) : OE_OS_NONE;
+        ++idx;
+        ++placed;
+      }
+      ++steps;
+    }
+  }
+  if (row >= 0) a.row_cursor[row] = idx - a.row_begin[row];
+  for (int d = 16; d > 0; d >>= 1) placed += __shfl_xor_sync(0xffffffffu, placed, d);
+  if (lane == 0 && placed) atomicAdd(a.n_placed, placed);
+  if (a.trace && lane == 0) {
+    long long* d = a.trace + (long long)comp * 4;
+    d[0] = steps; d[1] = clock64() - t0; d[2] = chunks; d[3] = skipped;
+  }
+}
+
 // Commit in two passes (the offer table still arriving, see oe_evaluate_cycle): the requirements that the pass over the prefix
 // left without an offer, in plan order.  sub_idx[k] = requirement, sub_row[k] = its bit row, *count = how many.
 __global__ void __launch_bounds__(1024) k_count_unplaced(const oe_decision* __restrict__ dec, int64_t M, int* __restrict__ tile_open) {
@@ -1496,6 +1803,9 @@ struct oe_engine {
   DevBuf d_l_dst, d_l_req, d_l_name, d_l_filter, d_tile_cnt, d_row_base, d_row_len, d_cand;
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
   DevBuf d_sort_hist, d_comp_begin;
+  // commit from the offers' side: row groups, per-offer (component, mask), offers sorted by component, requirements sorted by row
+  DevBuf d_os_parent, d_os_groups, d_os_ocomp, d_os_omask, d_os_ohist, d_os_comp_begin, d_os_list, d_os_mask, d_os_rhist, d_os_row_begin, d_os_queue, d_os_cursor;
+  int* h_os_info = nullptr;          // pinned: {components, rows of the widest component} of the last grouping
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
   std::vector<int32_t> h_vcand, h_vspan;
   bool task_spans_valid = false, task_odd_type = false, req_spans_valid = false;
@@ -1788,6 +2098,12 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
       return OE_ERR_CUDA;
     }
     h->union_static_smem = (int)fu.sharedSizeBytes;
+    if ((e = cudaFuncSetAttribute(k_offer_masks, cudaFuncAttributeMaxDynamicSharedMemorySize, OE_OS_MAX_ROWS * 44)) != cudaSuccess ||
+        (e = cudaMallocHost(reinterpret_cast<void**>(&h->h_os_info), 4 * sizeof(int))) != cudaSuccess) {
+      g_create_error = std::string("oe_create: set-up of the offer-side commit: ") + cudaGetErrorString(e);
+      delete h;
+      return OE_ERR_CUDA;
+    }
     // K1x beside other work requests shared memory only to cap its residency (run_expand); per device, hence here
     if ((e = cudaFuncSetAttribute(k_expand_matrix, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)) != cudaSuccess) {
       g_create_error = std::string("oe_create: shared memory opt-in for the expansion kernel: ") + cudaGetErrorString(e);
@@ -1810,7 +2126,8 @@ void oe_destroy(oe_engine* h) {
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
-                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab};
+                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -1820,6 +2137,7 @@ void oe_destroy(oe_engine* h) {
   for (cudaEvent_t e : {h->ev_prefix, h->ev_phase_a, h->ev_k1_last}) if (e) cudaEventDestroy(e);
   h->d_sub_idx.release(); h->d_sub_row.release(); h->d_dec_sub.release(); h->d_sub_count.release(); h->d_tile_open.release();
   if (h->h_offer_err) cudaFreeHost(h->h_offer_err);
+  if (h->h_os_info) cudaFreeHost(h->h_os_info);
   if (h->pin_arena) cudaFreeHost(h->pin_arena);
   h->d_offer_err.release();
   h->detach_peers();
@@ -3135,6 +3453,125 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
   }
 }
 
+
+// ---- the commit from the offers' side (k_commit_offers) -------------------------------------------------------------------------
+// `OE_COMMIT=union` in the environment keeps the requirement-side union-list commit (k_commit_union) for comparison.
+bool offer_side_ok(int rows) {
+  static const bool forced_union = getenv("OE_COMMIT") && std::string(getenv("OE_COMMIT")) == "union";
+  return !forced_union && rows >= 1 && rows <= OE_OS_MAX_ROWS;
+}
+// Once per cycle: the requirements of every bit row in plan order (a stable counting sort by row) and the rows' queue
+// positions at zero.  Needs only the requirement table, so it is enqueued before the class bits exist.
+int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int64_t M, int rows, cudaStream_t st) {
+  const int nb = (int)std::max<int64_t>(1, (M + OE_OS_SORT_BLOCK - 1) / OE_OS_SORT_BLOCK);
+  CU(h->d_os_rhist.ensure((size_t)nb * rows * sizeof(int)));
+  CU(h->d_os_row_begin.ensure(((size_t)rows + 1) * sizeof(int)));
+  CU(h->d_os_queue.ensure(std::max<size_t>((size_t)M, 1) * sizeof(int32_t)));
+  CU(h->d_os_cursor.ensure((size_t)rows * sizeof(int)));
+  CU(cudaMemsetAsync(h->d_os_cursor.p, 0, (size_t)rows * sizeof(int), st));
+  k_key_hist<<<nb, 256, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>());
+  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_rhist.as<int>(), nb, rows, nullptr, rows, h->d_os_row_begin.as<int>());
+  k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>(), h->d_os_row_begin.as<int>(), nullptr,
+                                                          h->d_os_queue.as<int32_t>(), nullptr);
+  *launches += 3;
+  CU(cudaGetLastError());
+  return 0;
+}
+// One pass over the offers of `rb` (global index of its first offer: offer_offset).  Returns 1 (nothing enqueued beyond the
+// grouping) when a component has more than 32 rows: the caller falls back to k_commit.
+int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32_t offer_offset, int64_t M, oe_decision* dec, cudaStream_t st,
+                       bool fork_ok, bool materialize, const int32_t* req_row) {
+  const int rows = rb.rows;
+  const int64_t n_offers = rb.total_words * 32;
+  const unsigned long long* adj = nullptr;
+  int* parent = nullptr;
+  if (rows > OE_ADJ_MAX_ROWS) {
+    CU(h->d_os_parent.ensure((size_t)rows * sizeof(int)));
+    parent = h->d_os_parent.as<int>();
+    std::vector<int> iota((size_t)rows);
+    for (int r = 0; r < rows; ++r) iota[(size_t)r] = r;
+    CU(cudaMemcpyAsync(parent, iota.data(), (size_t)rows * sizeof(int), cudaMemcpyHostToDevice, st));   // pageable: staged before the call returns
+    k_row_link<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 3) / 4), 128, (size_t)rows * 16, st>>>(rb, parent);
+    ++*launches;
+  } else if (rows > 1) {
+    CU(h->d_adj.ensure(OE_ADJ_MAX_ROWS * 8));
+    CU(cudaMemsetAsync(h->d_adj.p, 0, OE_ADJ_MAX_ROWS * 8, st));
+    k_row_overlap<<<(unsigned)std::max<int64_t>(1, (rb.total_words + 127) / 128), 128 * OE_ADJ_SPLIT, 0, st>>>(rb, h->d_adj.as<unsigned long long>());
+    ++*launches;
+    adj = h->d_adj.as<unsigned long long>();
+  }
+  CU(h->d_os_groups.ensure(((size_t)rows * 4 + 4) * sizeof(int)));
+  RowGroups g{};
+  g.comp_of = h->d_os_groups.as<int>(); g.lrow = g.comp_of + rows; g.comp_rows = g.lrow + rows; g.comp_row_begin = g.comp_rows + rows;
+  CU(h->d_os_comp_begin.ensure(((size_t)rows + 4) * sizeof(int)));
+  g.info = h->d_os_comp_begin.as<int>() + rows + 1;
+  k_group_rows<<<1, 256, ((size_t)rows * 3 + 1) * sizeof(int), st>>>(rows, adj, parent, g);
+  ++*launches;
+  CU(cudaGetLastError());
+  int n_ctas = rows;
+  if (rows > 32) {   // a component of more than 32 rows does not fit the lanes of its warp: the caller must know before it goes on
+    CU(cudaMemcpyAsync(h->h_os_info, g.info, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (h->h_os_info[1] > 32) return 1;
+    n_ctas = std::max(1, h->h_os_info[0]);
+  }
+  const int nb = (int)std::max<int64_t>(1, (n_offers + OE_OS_SORT_BLOCK - 1) / OE_OS_SORT_BLOCK);
+  CU(h->d_os_ocomp.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4)); CU(h->d_os_omask.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4));
+  CU(h->d_os_ohist.ensure((size_t)nb * rows * sizeof(int)));
+  CU(h->d_os_list.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4)); CU(h->d_os_mask.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4));
+  k_offer_masks<<<nb, 256, (size_t)rows * 44, st>>>(rb, g.comp_of, g.lrow, g.info, h->d_os_ocomp.as<int32_t>(), h->d_os_omask.as<uint32_t>(), h->d_os_ohist.as<int>());
+  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, rows, g.info, 0, h->d_os_comp_begin.as<int>());
+  k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(h->d_os_ocomp.as<int32_t>(), n_offers, rows, h->d_os_ohist.as<int>(), h->d_os_comp_begin.as<int>(),
+                                                          h->d_os_omask.as<uint32_t>(), h->d_os_list.as<int32_t>(), h->d_os_mask.as<uint32_t>());
+  *launches += 3;
+  CU(cudaGetLastError());
+  OfferSideArgs a{};
+  a.info = g.info; a.comp_begin = h->d_os_comp_begin.as<int>(); a.list = h->d_os_list.as<int32_t>(); a.mask = h->d_os_mask.as<uint32_t>();
+  a.comp_rows = g.comp_rows; a.comp_row_begin = g.comp_row_begin; a.row_begin = h->d_os_row_begin.as<int>(); a.queue = h->d_os_queue.as<int32_t>();
+  a.row_cursor = h->d_os_cursor.as<int>(); a.offer_offset = offer_offset; a.dec = dec; a.n_placed = h->d_nplaced.as<int>();
+  static const bool trace_on = getenv("OE_COMMIT_TRACE") != nullptr;
+  if (trace_on) {
+    CU(h->d_dbg.ensure((size_t)n_ctas * 4 * sizeof(long long)));
+    CU(cudaMemsetAsync(h->d_dbg.p, 0, (size_t)n_ctas * 4 * sizeof(long long), st));
+    a.trace = h->d_dbg.as<long long>();
+  }
+  bool materialized = false;
+  if (h->fork_expand && fork_ok) {
+    // as in commit_union_pass: the replay on the highest-priority stream, the matrix expansion beside it on the lowest
+    h->fork_expand = false;
+    CU(cudaEventRecord(h->ev_fork, st));
+    CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
+    k_commit_offers<<<n_ctas, 32, 0, h->hi_stream>>>(a);
+    if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+    materialized = true;
+    CU(cudaEventRecord(h->ev_commit, h->hi_stream));
+    CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
+    if (!h->expand_started) CU(cudaEventRecord(h->ev_x0, h->aux_stream));
+    if (int rc = run_expand(h, launches, h->aux_stream, h->expand_from_word)) return rc;
+    CU(cudaEventRecord(h->ev_x1, h->aux_stream));
+    CU(cudaStreamWaitEvent(st, h->ev_commit, 0));
+  } else {
+    k_commit_offers<<<n_ctas, 32, 0, st>>>(a);
+  }
+  ++*launches;
+  CU(cudaGetLastError());
+  if (!materialized && materialize) {
+    k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+    CU(cudaGetLastError());
+  }
+  if (materialize) ++*launches;
+  if (trace_on) {
+    std::vector<long long> d((size_t)n_ctas * 4);
+    CU(cudaMemcpyAsync(d.data(), a.trace, d.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (int c = 0; c < n_ctas; ++c)
+      if (d[(size_t)c * 4 + 2])
+        fprintf(stderr, "commit trace: component %3d  %7lld steps  %9lld cycles  %6lld chunks of 32 offers, %lld skipped\n", c, d[(size_t)c * 4], d[(size_t)c * 4 + 1],
+                d[(size_t)c * 4 + 2], d[(size_t)c * 4 + 3]);
+  }
+  return 0;
+}
+
 int run_commit(oe_engine* h, int64_t* launches) {
   const int64_t stride = h->stride();
   const int rows = h->rows_factored();
@@ -3153,6 +3590,15 @@ int run_commit(oe_engine* h, int64_t* launches) {
   if (rows == 0 || h->M == 0) {
     CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
     return 0;
+  }
+  if (offer_side_ok(rows)) {
+    k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_dec.as<oe_decision>(), h->M);
+    CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
+    if (int rc = prepare_queues(h, launches, h->d_req_row.as<int32_t>(), h->M, rows, h->stream)) return rc;
+    const int rc = commit_offers_pass(h, launches, rb, 0, h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, h->d_req_row.as<int32_t>());
+    if (rc <= 0) return rc;
+    // a component wider than a warp: the per-row lists below
+    CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->stream));
   }
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
   if (union_commit_fits(h, rows, rb.total_words))
@@ -3327,7 +3773,8 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
     const bool want_matrix = (h->flags & OE_CFG_MATERIALIZE_MATRIX) != 0;
     const int rows = h->rows_factored();
     static const bool no_prefix_commit = getenv("OE_NO_PREFIX_COMMIT") != nullptr;
-    if (h->offers_in_flight && h->n_chunks > 1 && h->M > 0 && rows > 0 && !no_prefix_commit && union_commit_fits(h, rows, (h->N + 31) / 32)) {
+    const bool os_two_pass = offer_side_ok(rows) && rows <= 32;   // no host round trip inside a pass (rows <= 32: no component can be too wide)
+    if (h->offers_in_flight && h->n_chunks > 1 && h->M > 0 && rows > 0 && !no_prefix_commit && (os_two_pass || union_commit_fits(h, rows, (h->N + 31) / 32))) {
       // The offer table is still arriving.  First fit takes the lowest free index, so the commit over the chunks that have
       // landed already is final for every requirement it places; it runs (highest priority) while the last chunk is on the bus,
       // and only the requirements it left open are committed over the last chunk afterwards.
@@ -3343,9 +3790,20 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       const std::function<int()> prefix_commit = [&]() -> int {
         CU(cudaEventRecord(h->ev_prefix, h->stream));
         CU(cudaStreamWaitEvent(h->hi_stream, h->ev_prefix, 0));
-        CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->hi_stream));
         RowBits rbA{};
         rbA.F = h->d_F.as<uint32_t>(); rbA.stride = stride; rbA.rows = rows; rbA.shard_words = stride; rbA.total_words = wA;
+        if (os_two_pass) {
+          // from the offers' side a later pass simply resumes from the rows' queue positions: nothing to collect in between
+          k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M);
+          CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->hi_stream));
+          if (int rc = prepare_queues(h, &launches, h->d_req_row.as<int32_t>(), h->M, rows, h->hi_stream)) return rc;
+          if (int rc = commit_offers_pass(h, &launches, rbA, 0, h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
+          CU(cudaMemcpyAsync(h_open, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
+          CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
+          tr.mark("prefix_commit_enqueued");
+          return 0;
+        }
+        CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->hi_stream));
         if (int rc = commit_union_pass(h, &launches, rbA, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
         const unsigned n_tiles = (unsigned)((h->M + 1023) / 1024);
         k_count_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M, h->d_tile_open.as<int>());
@@ -3365,10 +3823,14 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       if (want_matrix) { expand_overlapped = true; CU(cudaEventRecord(h->ev_x1, h->aux_stream)); }
       tr.mark("last_chunk_enqueued");
       CU(cudaEventSynchronize(h->ev_phase_a));
-      const int n_open = *h_open;
+      const int n_open = os_two_pass ? (int)(h->M - *h_open) : *h_open;
       tr.mark("prefix_commit_done");
       CU(cudaStreamWaitEvent(h->hi_stream, h->ev_k1_last, 0));
-      if (n_open > 0) {
+      if (n_open > 0 && os_two_pass) {
+        RowBits rbB{};
+        rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
+        if (int rc = commit_offers_pass(h, &launches, rbB, (int32_t)(wA * 32), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
+      } else if (n_open > 0) {
         RowBits rbB{};
         rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
         if (int rc = commit_union_pass(h, &launches, rbB, h->d_sub_row.as<int32_t>(), n_open, h->d_dec_sub.as<oe_decision>(), h->hi_stream, false, false, false)) return rc;

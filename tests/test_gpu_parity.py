@@ -559,7 +559,7 @@ def test_packed_offer_table_gives_what_the_plain_table_gives(engine, flags):
             t.scalar = t.scalar + 1e-9
         orc = Oracle().load(t)
         packed = abi.PackedOffers(t)
-        assert packed.scalar_is_f32 == (seed % 3 != 0) or t.n_offers == 0 or not t.scalar.any()
+        assert not (packed.scalar_is_f32 and seed % 3 == 0 and t.scalar.any())
         _load_packed(eng, t, packed)
         m_cpu, _ = orc.feasibility()
         m_gpu, _ = eng.feasibility()

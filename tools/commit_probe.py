@@ -11,7 +11,7 @@ from dcos_commons_b200 import abi, synth
 def main():
     eng = abi.Engine(0)
     for name in sys.argv[1:] or ["c5", "c4"]:
-        t = (synth.config_c5() if name == "c5" else synth.config_c4()).tables
+        t = (synth.config_c5() if name == "c5" else synth.config_c4() if name == "c4" else synth.config_c5_variant(name[3:])).tables
         eng.load(t)
         out = []
         for _ in range(4):

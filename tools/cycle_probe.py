@@ -18,6 +18,7 @@ def main():
     t = synth.config_c5(1.0).tables
     t.normalise()
     pt = bench.pin_tables(t)
+    ppk = abi.PackedOffers(t).pin() if os.environ.get("OE_PROBE_WIRE", "packed") == "packed" else None
     out = torch.empty(t.n_reqs * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     flags = abi.OE_CFG_ASYNC_LOADS | (abi.OE_CFG_MATERIALIZE_MATRIX if mode == "matrix" else 0)
     eng = Engine(device=0, flags=flags)
@@ -31,7 +32,7 @@ def main():
         if order == "tasks-first":
             eng.load_tasks(pt)
         t1 = time.perf_counter()
-        eng.load_offers(pt)
+        eng.load_offers_packed(ppk) if ppk is not None else eng.load_offers(pt)
         t2 = time.perf_counter()
         if order != "tasks-first":
             eng.load_tasks(pt)
