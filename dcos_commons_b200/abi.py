@@ -557,6 +557,14 @@ class Handle:
         self._check(f(self.h, out.ctypes.data if fetch else None, C.byref(st)))
         return out, st.as_dict()
 
+    def requirement_rows(self):
+        """(bit row of every requirement, number of bit rows) as of the last feasibility pass (oe_requirement_rows)."""
+        f = self.b.fn("requirement_rows")
+        f.argtypes = [_p, _p, C.POINTER(C.c_int32)]
+        rows, n = np.zeros(self.tables.n_reqs, np.int32), C.c_int32()
+        self._check(f(self.h, rows.ctypes.data if rows.size else None, C.byref(n)))
+        return rows, int(n.value)
+
     def factored_rows(self) -> int:
         ptr, nbytes = self.device_buffer(BUF_CLASS_BITS_LOCAL)
         return nbytes // (4 * self.stride())

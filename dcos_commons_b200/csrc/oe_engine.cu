@@ -250,6 +250,7 @@ struct K1Args {
   int sc_cols;           // scalar columns staged in shared memory (0 = read them through L1)
   RuleTab tab;
   PortTab ptab;
+  const int32_t* row_map;  // bit row -> factored row (class or re-deployed requirement) it is evaluated as; null = identity
   PeerOut peers;
   int64_t xb0;           // first 128-offer block of this launch (the offer table may be evaluated in row chunks)
 };
@@ -315,7 +316,7 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
     const uint4* src = reinterpret_cast<const uint4*>(a.fast);
     uint4* dst = reinterpret_cast<uint4*>(s_fast);
     for (int q = threadIdx.x; q < (r1 - r0) * 8; q += OE_K1_THREADS) {
-      const int row = r0 + (q >> 3);
+      const int row = a.row_map ? __ldg(a.row_map + r0 + (q >> 3)) : r0 + (q >> 3);
       const int cls = row < cx.p.C ? row : cx.v.cls[row - cx.p.C];
       dst[q] = __ldg(src + (int64_t)cls * 8 + (q & 7));
     }
@@ -339,16 +340,18 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
   uint32_t* out = a.F + (int64_t)r0 * a.stride + word;
   const int tab_idx = (regs.ok.region + 1) * a.tab.zdim + (regs.ok.zone + 1);
   const int tab_bit = tab_idx & 31;
-  const uint32_t* tab_word = a.tab.bits + (int64_t)r0 * a.tab.words + (tab_idx >> 5);
+  const uint32_t* tab_col = a.tab.bits + (tab_idx >> 5);
   const FastRow* frp = s_fast;
-  for (int row = r0; row < r1; ++row, ++frp, out += a.stride, tab_word += a.tab.words) {
+  for (int row = r0; row < r1; ++row, ++frp, out += a.stride) {
     const FastRow& fr = *frp;
-    const int var = row < cx.p.C ? -1 : row - cx.p.C;
+    const int frow = a.row_map ? __ldg(a.row_map + row) : row;   // warp-uniform
+    const int var = frow < cx.p.C ? -1 : frow - cx.p.C;
+    const uint32_t* tab_word = tab_col + (int64_t)frow * a.tab.words;
     bool pass = false;
     if (fr.flags & OE_FR_FAST) {
       if (valid) pass = eval_fast<PORTS, NQ>(cx, nodes, fr, sc, i, regs, var, tab_word, tab_bit, a.ptab, ptuple);
     } else if (valid) {
-      const int cls = var < 0 ? row : cx.v.cls[var];
+      const int cls = var < 0 ? frow : cx.v.cls[var];
       pass = eval_pair<false>(cx, i, regs.ok, cls, var, nullptr);
     }
     const uint32_t bits = __ballot_sync(0xffffffffu, pass);
@@ -1516,26 +1519,39 @@ struct OfferSideArgs {
   long long* trace;            // optional: per component {steps, cycles, chunks, chunks skipped}
 };
 #define OE_OS_NONE 0x7fffffff
+#define OE_OS_RING 128    // queue entries a lane keeps staged in shared memory (topped up to 96 ahead at every chunk of 32 offers)
 __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
+  // the lanes' queues, staged: ring[(k & (OE_OS_RING - 1)) * 32 + lane] = entry k of the lane's row.  A lane matches at most 32
+  // requirements per chunk of 32 offers, so topping the ring up once per chunk (cp.async, a chunk ahead of its use) keeps every
+  // read inside a chunk in shared memory; what a step needs from memory is then one LDS whose result is used a match later.
+  __shared__ int ring[OE_OS_RING * 32];
   const int comp = blockIdx.x, lane = threadIdx.x;
   if (comp >= a.info[0]) return;
   const long long t0 = clock64();
   const int rb0 = a.comp_row_begin[comp], n_rows = a.comp_row_begin[comp + 1] - rb0;
   const int row = lane < n_rows ? a.comp_rows[rb0 + lane] : -1;
-  int idx = 0, end = 0;
-  if (row >= 0) { idx = a.row_begin[row] + a.row_cursor[row]; end = a.row_begin[row + 1]; }
+  int pos = 0, end = 0;   // queue index of the lane's head / end of its queue
+  if (row >= 0) { pos = a.row_begin[row] + a.row_cursor[row]; end = a.row_begin[row + 1]; }
+  const int pos0 = pos;
   const int32_t* __restrict__ Q = a.queue;
-  // the lane's next four requirements: the queue is read three matches ahead of its use
-  int h = idx < end ? __ldg(Q + idx) : OE_OS_NONE;
-  int n1 = idx + 1 < end ? __ldg(Q + idx + 1) : OE_OS_NONE;
-  int n2 = idx + 2 < end ? __ldg(Q + idx + 2) : OE_OS_NONE;
-  int n3 = idx + 3 < end ? __ldg(Q + idx + 3) : OE_OS_NONE;
+  int filled = pos;
+  auto top_up = [&]() {
+    const int upto = min(end, pos + 96);
+    for (; filled < upto; ++filled) __pipeline_memcpy_async(&ring[(filled & (OE_OS_RING - 1)) * 32 + lane], Q + filled, 4);
+    __pipeline_commit();
+  };
+  top_up();
+  __pipeline_wait_prior(0);
+  __syncwarp();
+  int h = pos < end ? ring[(pos & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
+  int n1 = pos + 1 < end ? ring[((pos + 1) & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
   const int e0 = a.comp_begin[comp], e1 = a.comp_begin[comp + 1];
-  int placed = 0, steps = 0, chunks = 0, skipped = 0;
+  int steps = 0, chunks = 0, skipped = 0;
   int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
   uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
+  int* const dec_row = &a.dec[0].offer_row;
   for (int base = e0; base < e1; base += 32) {
-    const int o_mine = o_next;
+    const int o_mine = o_next + a.offer_offset;
     const uint32_t m_mine = m_next;
     {  // the chunk after this one, a chunk ahead of its use
       const int e = base + 32 + lane;
@@ -1547,25 +1563,30 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
     ++chunks;
     skipped += want == 0u;
+    if (!want) continue;
+    __pipeline_wait_prior(0);   // the entries asked for a chunk ago
+    __syncwarp();
+    top_up();
     while (want) {
       const int e = __ffs(want) - 1;
       want &= want - 1;
       const uint32_t m = __shfl_sync(0xffffffffu, m_mine, e);
       const int o = __shfl_sync(0xffffffffu, o_mine, e);
+      // the entry behind n1, fetched whether or not this lane wins (no branch): used only at the lane's next match
+      const int nxt = pos + 2 < end ? ring[((pos + 2) & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
       const int v = ((m >> lane) & 1u) ? h : OE_OS_NONE;
       const int mn = __reduce_min_sync(0xffffffffu, v);
-      const bool won = v == mn && mn != OE_OS_NONE;
-      if (won) {
-        a.dec[h].offer_row = o + a.offer_offset;
-        h = n1; n1 = n2; n2 = n3;
-        n3 = idx + 4 < end ? __ldg(Q + idx + 4) : OE_OS_NONE;
-        ++idx;
-        ++placed;
-      }
+      const bool won = (v == mn) & (mn != OE_OS_NONE);
+      if (won) dec_row[(size_t)h * (sizeof(oe_decision) / sizeof(int))] = o;
+      h = won ? n1 : h;
+      n1 = won ? nxt : n1;
+      pos += won ? 1 : 0;
       ++steps;
     }
   }
-  if (row >= 0) a.row_cursor[row] = idx - a.row_begin[row];
+  __pipeline_wait_prior(0);
+  int placed = pos - pos0;
+  if (row >= 0) a.row_cursor[row] = pos - a.row_begin[row];
   for (int d = 16; d > 0; d >>= 1) placed += __shfl_xor_sync(0xffffffffu, placed, d);
   if (lane == 0 && placed) atomicAdd(a.n_placed, placed);
   if (a.trace && lane == 0) {
@@ -1797,6 +1818,14 @@ struct oe_engine {
   bool self_provided = false;
   std::vector<uint32_t> h_launch_filter;
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
+  // Re-deployed requirements whose rule verdicts over (zone, region) are identical share one bit row: V_eff rows behind the
+  // classes instead of V (-1 = not merged: every such requirement has a row of its own).  row_map[bit row] = factored row it is
+  // evaluated as; req_row_eff[j] = bit row of requirement j.
+  int V_eff = -1;
+  std::vector<int32_t> h_row_map, h_req_row_eff;
+  std::vector<uint32_t> h_rule_tab;
+  DevBuf d_row_map, d_req_row_eff;
+  const int32_t* bit_row_of_req() const { return V_eff >= 0 ? d_req_row_eff.as<int32_t>() : d_req_row.as<int32_t>(); }
 
   // ---- derived / outputs
   DevBuf d_cnt, d_rrsum, d_type_total, d_type_agent, d_F, d_Fglobal, d_matrix, d_dec, d_used, d_cursor, d_err, d_nplaced, d_order, d_adj, d_dbg, d_keep, d_gc_out, d_taken;
@@ -1871,7 +1900,7 @@ struct oe_engine {
     const int64_t rows = (world > 1 && shard_rows > 0) ? shard_rows : N;
     return std::max<int64_t>(128, round_up((rows + 31) / 32, 128));
   }
-  int rows_factored() const { return C + V; }
+  int rows_factored() const { return C + (V_eff >= 0 ? V_eff : V); }
   DevCtx ctx() const {
     DevCtx cx;
     cx.o = dof; cx.t = dt; cx.p = dp;
@@ -2127,7 +2156,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
-                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor};
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -2944,6 +2973,7 @@ int rebuild_variants(oe_engine* h) {
     }  // any_overlap
   }
   h->V = (int)vcls.size();
+  h->V_eff = -1;
   if (g_trace) g_trace->mark("variants");
   // the previous contents of these device buffers may still be read by kernels of the main stream: the side stream starts behind it
   CU(cudaEventRecord(h->ev_side, h->stream));
@@ -3204,6 +3234,69 @@ int build_fast_rows(oe_engine* h) {
 }
 
 
+// A re-deployed requirement (a pod that is already running) gets a bit row of its own because its rules must not count the pod's
+// own tasks.  For classes whose rule reads only the offer's zone and region that difference is the content of the rule table
+// k_rule_tables has just written: requirements of one class with the same table have the same bit row (and one with the class's
+// own table needs no row at all).  Thousands of re-deployed pods of a few classes over a few zones collapse into a handful of
+// rows.  The tables are small ((C + V) x tab_words words); they are compared on the host, which costs one synchronisation per
+// pass — only when re-deployed requirements exist.
+int merge_equal_variants(oe_engine* h) {
+  const int C = h->C, V = h->V, words = h->tab_words;
+  if (words <= 0) return 0;
+  h->h_rule_tab.resize((size_t)(C + V) * words);
+  std::vector<FastRow> fast((size_t)std::max(C, 1));
+  CU(cudaMemcpyAsync(h->h_rule_tab.data(), h->d_rule_tab.p, h->h_rule_tab.size() * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaMemcpyAsync(fast.data(), h->d_fast.p, (size_t)C * sizeof(FastRow), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  // key = class + table words; value = the bit row that evaluates it
+  struct KeyHash {
+    size_t operator()(const std::vector<uint32_t>& k) const {
+      uint64_t x = 1469598103934665603ull;
+      for (uint32_t w : k) { x ^= w; x *= 1099511628211ull; }
+      return (size_t)x;
+    }
+  };
+  std::unordered_map<std::vector<uint32_t>, int32_t, KeyHash> seen;
+  seen.reserve((size_t)(C + V) * 2);
+  std::vector<uint32_t> key((size_t)words + 1);
+  auto key_of = [&](int cls, int frow) {
+    key[0] = (uint32_t)cls;
+    std::memcpy(key.data() + 1, h->h_rule_tab.data() + (size_t)frow * words, (size_t)words * 4);
+  };
+  h->h_row_map.resize((size_t)C);
+  for (int c = 0; c < C; ++c) {
+    h->h_row_map[(size_t)c] = c;
+    if (fast[(size_t)c].flags & OE_FR_RULE_TAB) { key_of(c, c); seen.emplace(key, c); }
+  }
+  std::vector<int32_t> bit_row_of_variant((size_t)V);
+  for (int v = 0; v < V; ++v) {
+    const int cls = h->h_vcls[(size_t)v];
+    int32_t row;
+    if (fast[(size_t)cls].flags & OE_FR_RULE_TAB) {
+      key_of(cls, C + v);
+      auto it = seen.find(key);
+      if (it == seen.end()) { row = (int32_t)h->h_row_map.size(); h->h_row_map.push_back(C + v); seen.emplace(key, row); }
+      else row = it->second;
+    } else {
+      row = (int32_t)h->h_row_map.size();
+      h->h_row_map.push_back(C + v);
+    }
+    bit_row_of_variant[(size_t)v] = row;
+  }
+  const int V_eff = (int)h->h_row_map.size() - C;
+  if (V_eff == V) return 0;   // nothing merged: keep the plain numbering
+  h->h_req_row_eff.resize((size_t)h->M);
+  for (int64_t j = 0; j < h->M; ++j) {
+    const int32_t r = h->h_req_row[(size_t)j];
+    h->h_req_row_eff[(size_t)j] = r < C ? r : bit_row_of_variant[(size_t)(r - C)];
+  }
+  if (int rc = upload(h, h->d_row_map, h->h_row_map.data(), h->h_row_map.size())) return rc;
+  if (int rc = upload(h, h->d_req_row_eff, h->h_req_row_eff.data(), h->h_req_row_eff.size())) return rc;
+  CU(cudaStreamSynchronize(h->stream));   // the vectors are rewritten by the next pass
+  h->V_eff = V_eff;
+  return 0;
+}
+
 int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64_t w0 = 0, int64_t w1 = -1);
 
 // K1 over the whole offer table, or — while an OE_CFG_ASYNC_LOADS table is still arriving — chunk by chunk as the chunks land.
@@ -3212,25 +3305,31 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64
 int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false, bool expand_last = false,
                           const std::function<int()>* after_prefix = nullptr) {
   const int64_t stride = h->stride();
-  const int rows = h->rows_factored();
+  h->V_eff = -1;
+  const int rows_all = h->C + h->V;   // every class and every re-deployed requirement
   h->expand_from_word = 0;
   h->expand_started = false;
-  CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
-  if (rows > 0) {
+  K1Args a{};
+  a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
+  if (rows_all > 0) {
     if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;
-    const int64_t xblocks_all = stride * 32 / OE_K1_THREADS;
-    const int n_chunks = h->offers_in_flight ? h->n_chunks : 1;
-    K1Args a{};
-    a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
     if (h->any_rule_tab) {
-      CU(h->d_rule_tab.ensure((size_t)rows * h->tab_words * 4));
+      CU(h->d_rule_tab.ensure((size_t)rows_all * h->tab_words * 4));
       a.tab.bits = h->d_rule_tab.as<uint32_t>();
-      dim3 tgrid((unsigned)((h->tab_zdim * h->tab_rdim + 127) / 128), (unsigned)rows);
-      if (rows > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one rule-table launch covers", rows);
+      dim3 tgrid((unsigned)((h->tab_zdim * h->tab_rdim + 127) / 128), (unsigned)rows_all);
+      if (rows_all > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d factored rows exceed what one rule-table launch covers", rows_all);
       k_rule_tables<<<tgrid, 128, 0, h->stream>>>(h->ctx(), h->d_fast.as<FastRow>(), h->d_rule_tab.as<uint32_t>(), h->tab_words,
                                                   h->tab_zdim, h->tab_rdim);
       ++*launches;
+      if (h->V > 0 && !h->peers_attached) if (int rc = merge_equal_variants(h)) return rc;
     }
+  }
+  const int rows = h->rows_factored();
+  a.row_map = h->V_eff >= 0 ? h->d_row_map.as<int32_t>() : nullptr;
+  CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
+  if (rows > 0) {
+    const int64_t xblocks_all = stride * 32 / OE_K1_THREADS;
+    const int n_chunks = h->offers_in_flight ? h->n_chunks : 1;
     a.ptab.bits = nullptr; a.ptab.words = 0;
     if (h->tuples_valid && h->dof.ptuple && h->dof.R <= OE_FAST_RANGES && h->n_port_tuples > 0 && h->C > 0) {
       // few distinct `ports` range lists (stock agents offer the same ranges): a class's port stages once per list.  With
@@ -3338,7 +3437,7 @@ int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on, int64_t w0, int
     static const int pad_kb = getenv("OE_KX_SMEM_KB") ? atoi(getenv("OE_KX_SMEM_KB")) : 56;
     size_t pad = 0;
     if (pad_kb > 0 && (w0 > 0 || w1 < stride || on == h->aux_stream)) pad = (size_t)std::min(pad_kb, 200) * 1024;   // opt-in: oe_create
-    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), pad, on>>>(h->d_F.as<uint32_t>(), h->d_req_row.as<int32_t>(),
+    k_expand_matrix<<<grid, dim3(OE_KX_LANES, OE_KX_ROWS), pad, on>>>(h->d_F.as<uint32_t>(), h->bit_row_of_req(),
                                                                          h->d_matrix.as<uint32_t>(), stride, h->M, reqs_per_block,
                                                                          w0 / (4 * OE_KX_LANES), w1);
     ++*launches;
@@ -3424,7 +3523,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
       k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
       // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
       // behind the expansion's grid
-      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1);
       materialized = true;
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
@@ -3437,7 +3536,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
     }
     ++*launches;
     CU(cudaGetLastError());
-    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1);
     ++*launches;
     CU(cudaGetLastError());
     if (trace_on) {
@@ -3594,7 +3693,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   if (offer_side_ok(rows)) {
     k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_dec.as<oe_decision>(), h->M);
     CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
-    if (int rc = prepare_queues(h, launches, h->d_req_row.as<int32_t>(), h->M, rows, h->stream)) return rc;
+    if (int rc = prepare_queues(h, launches, h->bit_row_of_req(), h->M, rows, h->stream)) return rc;
     const int rc = commit_offers_pass(h, launches, rb, 0, h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, h->d_req_row.as<int32_t>());
     if (rc <= 0) return rc;
     // a component wider than a warp: the per-row lists below
@@ -3602,7 +3701,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   }
   const int tiles = (int)std::max<int64_t>(1, (rb.total_words + OE_TILE_WORDS - 1) / OE_TILE_WORDS);
   if (union_commit_fits(h, rows, rb.total_words))
-    return commit_union_pass(h, launches, rb, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, true);
+    return commit_union_pass(h, launches, rb, h->bit_row_of_req(), h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, true);
   // K3: per-row candidate lists, capped at what one cycle can possibly consume from a row
   const int64_t cap = h->M + 16;
   CU(h->d_tile_cnt.ensure((size_t)rows * tiles * 4));
@@ -3624,7 +3723,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
 
   CommitArgs a{};
   a.cand = h->d_cand.as<int32_t>(); a.row_base = h->d_row_base.as<int64_t>(); a.row_len = h->d_row_len.as<int32_t>();
-  a.rows = rows; a.used_words = rb.total_words; a.req_row = h->d_req_row.as<int32_t>(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
+  a.rows = rows; a.used_words = rb.total_words; a.req_row = h->bit_row_of_req(); a.M = h->M; a.dec = h->d_dec.as<oe_decision>();
   a.n_placed = h->d_nplaced.as<int>();
   CU(h->d_order.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(int2)));
   a.order = h->d_order.as<int2>();
@@ -3702,6 +3801,14 @@ int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
     stats->n_pairs = h->N * h->M;
     stats->kernel_launches = launches;
   }
+  return OE_OK;
+}
+
+int32_t oe_requirement_rows(oe_engine* h, int32_t* rows, int32_t* n_rows) {
+  if (!h) return OE_ERR_INVALID;
+  if (!h->hasR || !h->class_bits_fresh) return h->fail(OE_ERR_STATE, "oe_requirement_rows: no feasibility pass since the last load");
+  if (n_rows) *n_rows = h->rows_factored();
+  if (rows && h->M > 0) std::memcpy(rows, (h->V_eff >= 0 ? h->h_req_row_eff : h->h_req_row).data(), (size_t)h->M * sizeof(int32_t));
   return OE_OK;
 }
 
@@ -3796,7 +3903,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
           // from the offers' side a later pass simply resumes from the rows' queue positions: nothing to collect in between
           k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M);
           CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->hi_stream));
-          if (int rc = prepare_queues(h, &launches, h->d_req_row.as<int32_t>(), h->M, rows, h->hi_stream)) return rc;
+          if (int rc = prepare_queues(h, &launches, h->bit_row_of_req(), h->M, rows, h->hi_stream)) return rc;
           if (int rc = commit_offers_pass(h, &launches, rbA, 0, h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
           CU(cudaMemcpyAsync(h_open, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
           CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
@@ -3804,10 +3911,10 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
           return 0;
         }
         CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->hi_stream));
-        if (int rc = commit_union_pass(h, &launches, rbA, h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
+        if (int rc = commit_union_pass(h, &launches, rbA, h->bit_row_of_req(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
         const unsigned n_tiles = (unsigned)((h->M + 1023) / 1024);
         k_count_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M, h->d_tile_open.as<int>());
-        k_collect_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->d_req_row.as<int32_t>(), h->M, h->d_tile_open.as<int>(),
+        k_collect_unplaced<<<n_tiles, 1024, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->bit_row_of_req(), h->M, h->d_tile_open.as<int>(),
                                                                h->d_sub_idx.as<int32_t>(), h->d_sub_row.as<int32_t>(), h->d_sub_count.as<int>());
         launches += 2;
         CU(cudaGetLastError());

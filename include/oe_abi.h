@@ -434,6 +434,13 @@ int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats);
 /* Class-factored matrix: one row per requirement class (fresh instances) — what the commit kernel scans.          */
 int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats);
 
+/* Which row of the class-factored matrix (oe_class_feasibility, OE_BUF_CLASS_BITS_*) each requirement reads, as of the last
+ * feasibility pass on this handle: its class's row, or — when the requirement's pod is already deployed (a stored task of the
+ * same pod type and index, S/offer/TaskUtils.java:136-145) and its class's rule reads tallies — a row behind the classes that
+ * is evaluated without the pod's own tasks (P/MaxPerRule.java:60-62).  Such requirements share a row when their rule verdicts
+ * are identical.  rows: [n_reqs] (may be NULL); *n_rows: rows of the matrix.  OE_ERR_STATE before the first pass.          */
+int32_t oe_requirement_rows(oe_engine* h, int32_t* rows, int32_t* n_rows);
+
 /* One PlanScheduler.resourceOffers cycle (S/scheduler/plan/PlanScheduler.java:50-70): requirements in order, each
  * takes the FIRST offer in list order whose stages all pass (OfferEvaluator.java:137-245) among the offers not yet
  * taken by an earlier requirement of this cycle (:61-66).  out[M].  When world > 1 the caller must run
