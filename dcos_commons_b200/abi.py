@@ -555,6 +555,8 @@ class Handle:
         if fetch:
             out = np.zeros((rows if rows is not None else self.factored_rows(), self.stride()), dtype=np.uint32)
         self._check(f(self.h, out.ctypes.data if fetch else None, C.byref(st)))
+        if fetch and rows is None:
+            out = out[: self.factored_rows()]   # the pass may merge the rows of re-deployed requirements (oe_requirement_rows)
         return out, st.as_dict()
 
     def requirement_rows(self):

@@ -1550,6 +1550,8 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
   int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
   uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
   int* const dec_row = &a.dec[0].offer_row;
+  constexpr size_t DEC_INTS = sizeof(oe_decision) / sizeof(int);
+  __shared__ int s_offer[32];   // the chunk's offers, for the lane that records a match
   for (int base = e0; base < e1; base += 32) {
     const int o_mine = o_next + a.offer_offset;
     const uint32_t m_mine = m_next;
@@ -1564,20 +1566,40 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     ++chunks;
     skipped += want == 0u;
     if (!want) continue;
+    if (n_rows == 1) {
+      // one row: nothing to arbitrate — the k-th offer of the chunk goes to the k-th waiting requirement, all lanes at once
+      const int p0 = __shfl_sync(0xffffffffu, pos, 0), pend = __shfl_sync(0xffffffffu, end, 0);   // lane 0 holds the row
+      const int mine = p0 + __popc(want & ((1u << lane) - 1u));
+      if (((want >> lane) & 1u) && mine < pend) dec_row[(size_t)__ldg(Q + mine) * DEC_INTS] = o_mine;
+      const int taken = min(__popc(want), pend - p0);
+      steps += taken;
+      if (lane == 0) {
+        pos += taken;
+        h = pos < end ? 0 : OE_OS_NONE;   // only "is anybody waiting" is read from it on this path
+      }
+      filled = max(filled, pos);
+      continue;
+    }
     __pipeline_wait_prior(0);   // the entries asked for a chunk ago
+    s_offer[lane] = o_mine;
     __syncwarp();
     top_up();
+    // which offers of the chunk list MY row: the masks transposed, so that a step needs no shuffle to learn it
+    uint32_t mybits = 0u;
+    for (int r = 0; r < n_rows; ++r) {
+      const uint32_t b = __ballot_sync(0xffffffffu, (m_mine >> r) & 1u);
+      mybits = lane == r ? b : mybits;
+    }
     while (want) {
       const int e = __ffs(want) - 1;
       want &= want - 1;
-      const uint32_t m = __shfl_sync(0xffffffffu, m_mine, e);
-      const int o = __shfl_sync(0xffffffffu, o_mine, e);
       // the entry behind n1, fetched whether or not this lane wins (no branch): used only at the lane's next match
       const int nxt = pos + 2 < end ? ring[((pos + 2) & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
-      const int v = ((m >> lane) & 1u) ? h : OE_OS_NONE;
+      const int o = s_offer[e];
+      const int v = ((mybits >> e) & 1u) ? h : OE_OS_NONE;
       const int mn = __reduce_min_sync(0xffffffffu, v);
       const bool won = (v == mn) & (mn != OE_OS_NONE);
-      if (won) dec_row[(size_t)h * (sizeof(oe_decision) / sizeof(int))] = o;
+      if (won) dec_row[(size_t)h * DEC_INTS] = o;
       h = won ? n1 : h;
       n1 = won ? nxt : n1;
       pos += won ? 1 : 0;
@@ -3310,9 +3332,9 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
   h->expand_from_word = 0;
   h->expand_started = false;
   K1Args a{};
-  a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
   if (rows_all > 0) {
-    if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;
+    if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;   // also sizes the rule tables
+    a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
     if (h->any_rule_tab) {
       CU(h->d_rule_tab.ensure((size_t)rows_all * h->tab_words * 4));
       a.tab.bits = h->d_rule_tab.as<uint32_t>();
@@ -3321,7 +3343,8 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       k_rule_tables<<<tgrid, 128, 0, h->stream>>>(h->ctx(), h->d_fast.as<FastRow>(), h->d_rule_tab.as<uint32_t>(), h->tab_words,
                                                   h->tab_zdim, h->tab_rdim);
       ++*launches;
-      if (h->V > 0 && !h->peers_attached) if (int rc = merge_equal_variants(h)) return rc;
+      static const bool no_merge = getenv("OE_NO_ROW_MERGE") != nullptr;   // debugging aid: one bit row per re-deployed requirement
+      if (h->V > 0 && !h->peers_attached && !no_merge) if (int rc = merge_equal_variants(h)) return rc;
     }
   }
   const int rows = h->rows_factored();

@@ -477,7 +477,7 @@ def _full_size_against_cached_oracle(engine, cl, variant_rows=8, shards=0, arriv
     _, is_var = _factored_row_of(t)
     row_of, n_rows = engine.requirement_rows()     # re-deployed requirements with identical rule verdicts share a bit row
     assert engine.factored_rows() == n_rows <= t.n_classes + int(is_var.sum()) and np.array_equal(row_of[~is_var], t.class_id[~is_var])
-    f = f[:n_rows]
+    assert f.shape[0] == n_rows
     words = (N + 31) // 32
     fresh = np.flatnonzero(~is_var)
     for c in range(t.n_classes):
