@@ -1520,10 +1520,20 @@ struct OfferSideArgs {
 };
 #define OE_OS_NONE 0x7fffffff
 #define OE_OS_RING 128    // queue entries a lane keeps staged in shared memory (topped up to 96 ahead at every chunk of 32 offers)
+// Shared memory through explicit 32-bit shared-window addresses: written as array accesses beside cp.async the compiler re-derived
+// the window base (S2R CgaCtaId + LEA) inside the replay loop.
+__device__ __forceinline__ int lds_s32(uint32_t addr) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void cp_async_4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
 __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
   // the lanes' queues, staged: ring[(k & (OE_OS_RING - 1)) * 32 + lane] = entry k of the lane's row.  A lane matches at most 32
   // requirements per chunk of 32 offers, so topping the ring up once per chunk (cp.async, a chunk ahead of its use) keeps every
-  // read inside a chunk in shared memory; what a step needs from memory is then one LDS whose result is used a match later.
+  // read inside a chunk in shared memory; what a step needs from memory is then one LDS whose result is used a step later.
   __shared__ int ring[OE_OS_RING * 32];
   const int comp = blockIdx.x, lane = threadIdx.x;
   if (comp >= a.info[0]) return;
@@ -1534,79 +1544,85 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
   if (row >= 0) { pos = a.row_begin[row] + a.row_cursor[row]; end = a.row_begin[row + 1]; }
   const int pos0 = pos;
   const int32_t* __restrict__ Q = a.queue;
-  int filled = pos;
-  auto top_up = [&]() {
-    const int upto = min(end, pos + 96);
-    for (; filled < upto; ++filled) __pipeline_memcpy_async(&ring[(filled & (OE_OS_RING - 1)) * 32 + lane], Q + filled, 4);
-    __pipeline_commit();
-  };
-  top_up();
-  __pipeline_wait_prior(0);
-  __syncwarp();
-  int h = pos < end ? ring[(pos & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
-  int n1 = pos + 1 < end ? ring[((pos + 1) & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
   const int e0 = a.comp_begin[comp], e1 = a.comp_begin[comp + 1];
-  int steps = 0, chunks = 0, skipped = 0;
-  int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
-  uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
   int* const dec_row = &a.dec[0].offer_row;
   constexpr size_t DEC_INTS = sizeof(oe_decision) / sizeof(int);
-  __shared__ int s_offer[32];   // the chunk's offers, for the lane that records a match
-  for (int base = e0; base < e1; base += 32) {
-    const int o_mine = o_next + a.offer_offset;
-    const uint32_t m_mine = m_next;
-    {  // the chunk after this one, a chunk ahead of its use
-      const int e = base + 32 + lane;
-      o_next = e < e1 ? __ldg(a.list + e) : -1;
-      m_next = e < e1 ? __ldg(a.mask + e) : 0u;
-    }
-    const uint32_t active = __ballot_sync(0xffffffffu, h != OE_OS_NONE);   // rows that still have a requirement waiting
-    if (!active) break;
-    uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
-    ++chunks;
-    skipped += want == 0u;
-    if (!want) continue;
-    if (n_rows == 1) {
-      // one row: nothing to arbitrate — the k-th offer of the chunk goes to the k-th waiting requirement, all lanes at once
-      const int p0 = __shfl_sync(0xffffffffu, pos, 0), pend = __shfl_sync(0xffffffffu, end, 0);   // lane 0 holds the row
-      const int mine = p0 + __popc(want & ((1u << lane) - 1u));
-      if (((want >> lane) & 1u) && mine < pend) dec_row[(size_t)__ldg(Q + mine) * DEC_INTS] = o_mine;
-      const int taken = min(__popc(want), pend - p0);
-      steps += taken;
-      if (lane == 0) {
-        pos += taken;
-        h = pos < end ? 0 : OE_OS_NONE;   // only "is anybody waiting" is read from it on this path
-      }
-      filled = max(filled, pos);
-      continue;
-    }
-    __pipeline_wait_prior(0);   // the entries asked for a chunk ago
-    s_offer[lane] = o_mine;
-    __syncwarp();
+  int steps = 0, chunks = 0, skipped = 0;
+  if (n_rows == 1) {
+    // One row: nothing to arbitrate — the k-th offer of the component goes to the k-th waiting requirement (every offer of the
+    // list is one the row lists).  No chain at all: 32 matches per iteration, loads of several iterations in flight.
+    const int p0 = __shfl_sync(0xffffffffu, pos, 0), pend = __shfl_sync(0xffffffffu, end, 0);   // lane 0 holds the row
+    const int n = min(e1 - e0, pend - p0);
+#pragma unroll 4
+    for (int k = lane; k < n; k += 32) dec_row[(size_t)__ldg(Q + p0 + k) * DEC_INTS] = __ldg(a.list + e0 + k) + a.offer_offset;
+    if (lane == 0) pos += max(n, 0);
+    steps = max(n, 0);
+  } else {
+    const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring) + lane * 4u;
+    auto ring_addr = [&](int k) { return ring_base + (uint32_t)(k & (OE_OS_RING - 1)) * 128u; };
+    int filled = pos;
+    auto top_up = [&]() {
+      const int upto = min(end, pos + 96);
+      for (; filled < upto; ++filled) cp_async_4(ring_addr(filled), Q + filled);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
     top_up();
-    // which offers of the chunk list MY row: the masks transposed, so that a step needs no shuffle to learn it
-    uint32_t mybits = 0u;
-    for (int r = 0; r < n_rows; ++r) {
-      const uint32_t b = __ballot_sync(0xffffffffu, (m_mine >> r) & 1u);
-      mybits = lane == r ? b : mybits;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    int h = pos < end ? lds_s32(ring_addr(pos)) : OE_OS_NONE;
+    int n1 = pos + 1 < end ? lds_s32(ring_addr(pos + 1)) : OE_OS_NONE;
+    int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
+    uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
+    for (int base = e0; base < e1; base += 32) {
+      const int o_mine = o_next + a.offer_offset;
+      const uint32_t m_mine = m_next;
+      {  // the chunk after this one, a chunk ahead of its use
+        const int e = base + 32 + lane;
+        o_next = e < e1 ? __ldg(a.list + e) : -1;
+        m_next = e < e1 ? __ldg(a.mask + e) : 0u;
+      }
+      const uint32_t active = __ballot_sync(0xffffffffu, h != OE_OS_NONE);   // rows that still have a requirement waiting
+      if (!active) break;
+      uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
+      ++chunks;
+      skipped += want == 0u;
+      if (!want) continue;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");   // the entries asked for a chunk ago
+      __syncwarp();
+      top_up();
+      // which offers of the chunk list MY row: the masks transposed, so that a step needs no shuffle to learn it
+      uint32_t mybits = 0u;
+      for (int r = 0; r < n_rows; ++r) {
+        const uint32_t b = __ballot_sync(0xffffffffu, (m_mine >> r) & 1u);
+        mybits = lane == r ? b : mybits;
+      }
+      // One step per offer somebody waits for.  The entry behind n1 is read at the top of a step and moves into n1 at the top
+      // of the NEXT one (`won_prev`): the load has a whole step to land and never stalls the chain
+      //     select (my row listed ? my head : none) -> REDUX.MIN -> compare -> select (head <- n1).
+      bool won_prev = false;
+      int nxt_prev = OE_OS_NONE;
+      while (want) {
+        const int e = __ffs(want) - 1;
+        want &= want - 1;
+        n1 = won_prev ? nxt_prev : n1;
+        const int nxt = pos + 2 < end ? lds_s32(ring_addr(pos + 2)) : OE_OS_NONE;
+        const int v = ((mybits >> e) & 1u) ? h : OE_OS_NONE;
+        const int mn = __reduce_min_sync(0xffffffffu, v);   // = the requirement that gets offer e (every lane knows it now)
+        const bool any = mn != OE_OS_NONE;
+        const bool won = (v == mn) & any;
+        // recorded by the lane that holds offer e in a register: no shuffle, no load
+        int* const dst = dec_row + (size_t)(any ? mn : 0) * DEC_INTS;
+        if ((lane == e) & any) *dst = o_mine;
+        h = won ? n1 : h;
+        pos += won ? 1 : 0;
+        won_prev = won;
+        nxt_prev = nxt;
+        ++steps;
+      }
+      n1 = won_prev ? nxt_prev : n1;
     }
-    while (want) {
-      const int e = __ffs(want) - 1;
-      want &= want - 1;
-      // the entry behind n1, fetched whether or not this lane wins (no branch): used only at the lane's next match
-      const int nxt = pos + 2 < end ? ring[((pos + 2) & (OE_OS_RING - 1)) * 32 + lane] : OE_OS_NONE;
-      const int o = s_offer[e];
-      const int v = ((mybits >> e) & 1u) ? h : OE_OS_NONE;
-      const int mn = __reduce_min_sync(0xffffffffu, v);
-      const bool won = (v == mn) & (mn != OE_OS_NONE);
-      if (won) dec_row[(size_t)h * DEC_INTS] = o;
-      h = won ? n1 : h;
-      n1 = won ? nxt : n1;
-      pos += won ? 1 : 0;
-      ++steps;
-    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
   }
-  __pipeline_wait_prior(0);
   int placed = pos - pos0;
   if (row >= 0) a.row_cursor[row] = pos - a.row_begin[row];
   for (int d = 16; d > 0; d >>= 1) placed += __shfl_xor_sync(0xffffffffu, placed, d);
