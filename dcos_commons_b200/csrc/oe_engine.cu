@@ -1429,8 +1429,26 @@ __global__ void __launch_bounds__(256) k_key_hist(const int32_t* __restrict__ ke
   __syncthreads();
   for (int k = threadIdx.x; k < key_stride; k += 256) hist[(int64_t)blockIdx.x * key_stride + k] = kh_smem[k];
 }
-__global__ void __launch_bounds__(1024) k_key_scan(int* __restrict__ hist, int n_blocks, int key_stride, const int* __restrict__ n_keys_ptr, int n_keys_fixed,
-                                                   int* __restrict__ key_begin) {
+// warp = one key: the key's counts over the blocks become exclusive prefixes in place (lanes stride over the blocks), totals[key]
+// = its items; then one CTA scans the totals.  (As one thread per key walking the blocks it was a chain of ~1000 dependent
+// global loads: 0.3 ms.)
+__global__ void __launch_bounds__(1024) k_key_scan_cols(int* __restrict__ hist, int n_blocks, int key_stride, const int* __restrict__ n_keys_ptr, int n_keys_fixed,
+                                                        int* __restrict__ totals) {
+  const int n_keys = n_keys_ptr ? *n_keys_ptr : n_keys_fixed;
+  const int lane = threadIdx.x & 31, k = blockIdx.x * 32 + (threadIdx.x >> 5);
+  if (k >= n_keys) return;
+  int run = 0;
+  for (int b0 = 0; b0 < n_blocks; b0 += 32) {
+    const int b = b0 + lane;
+    const int v = b < n_blocks ? hist[(int64_t)b * key_stride + k] : 0;
+    int incl = v;
+    for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
+    if (b < n_blocks) hist[(int64_t)b * key_stride + k] = run + incl - v;
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) totals[k] = run;
+}
+__global__ void __launch_bounds__(1024) k_key_scan(const int* __restrict__ totals, const int* __restrict__ n_keys_ptr, int n_keys_fixed, int* __restrict__ key_begin) {
   __shared__ int warp_sum[32];
   __shared__ int carry;
   const int n_keys = n_keys_ptr ? *n_keys_ptr : n_keys_fixed;
@@ -1439,9 +1457,7 @@ __global__ void __launch_bounds__(1024) k_key_scan(int* __restrict__ hist, int n
   __syncthreads();
   for (int k0 = 0; k0 < n_keys; k0 += 1024) {
     const int k = k0 + threadIdx.x;
-    int total = 0;
-    if (k < n_keys)
-      for (int b = 0; b < n_blocks; ++b) { const int v = hist[(int64_t)b * key_stride + k]; hist[(int64_t)b * key_stride + k] = total; total += v; }
+    const int total = k < n_keys ? totals[k] : 0;
     int incl = total;
     for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
     if (lane == 31) warp_sum[warp] = incl;
@@ -1520,6 +1536,7 @@ struct OfferSideArgs {
 };
 #define OE_OS_NONE 0x7fffffff
 #define OE_OS_RING 128    // queue entries a lane keeps staged in shared memory (topped up to 96 ahead at every chunk of 32 offers)
+#define OE_OS_MIRROR 36   // slots mirrored behind the ring's end (a chunk reads at most 34 consecutive entries)
 // Shared memory through explicit 32-bit shared-window addresses: written as array accesses beside cp.async the compiler re-derived
 // the window base (S2R CgaCtaId + LEA) inside the replay loop.
 __device__ __forceinline__ int lds_s32(uint32_t addr) {
@@ -1534,7 +1551,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
   // the lanes' queues, staged: ring[(k & (OE_OS_RING - 1)) * 32 + lane] = entry k of the lane's row.  A lane matches at most 32
   // requirements per chunk of 32 offers, so topping the ring up once per chunk (cp.async, a chunk ahead of its use) keeps every
   // read inside a chunk in shared memory; what a step needs from memory is then one LDS whose result is used a step later.
-  __shared__ int ring[OE_OS_RING * 32];
+  __shared__ int ring[(OE_OS_RING + OE_OS_MIRROR) * 32];
   const int comp = blockIdx.x, lane = threadIdx.x;
   if (comp >= a.info[0]) return;
   const long long t0 = clock64();
@@ -1558,19 +1575,30 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     if (lane == 0) pos += max(n, 0);
     steps = max(n, 0);
   } else {
+    // ring: entry k of the lane's queue sits at slot k & 127; slots 0..33 are mirrored behind slot 127, so the 34 entries a
+    // chunk can touch are contiguous wherever the chunk starts and a step advances its read address by one slot, no wrap
     const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring) + lane * 4u;
-    auto ring_addr = [&](int k) { return ring_base + (uint32_t)(k & (OE_OS_RING - 1)) * 128u; };
     int filled = pos;
     auto top_up = [&]() {
-      const int upto = min(end, pos + 96);
-      for (; filled < upto; ++filled) cp_async_4(ring_addr(filled), Q + filled);
+      const int upto = pos + 96;
+      for (; filled < upto; ++filled) {
+        const uint32_t slot = (uint32_t)filled & (OE_OS_RING - 1);
+        if (filled < end) {
+          cp_async_4(ring_base + slot * 128u, Q + filled);
+          if (slot < OE_OS_MIRROR) cp_async_4(ring_base + (slot + OE_OS_RING) * 128u, Q + filled);
+        } else {   // behind the queue's end: "nobody waiting", so that a step needs no bound check
+          asm volatile("st.shared.s32 [%0], %1;" ::"r"(ring_base + slot * 128u), "r"(OE_OS_NONE) : "memory");
+          if (slot < OE_OS_MIRROR) asm volatile("st.shared.s32 [%0], %1;" ::"r"(ring_base + (slot + OE_OS_RING) * 128u), "r"(OE_OS_NONE) : "memory");
+        }
+      }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
     top_up();
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
-    int h = pos < end ? lds_s32(ring_addr(pos)) : OE_OS_NONE;
-    int n1 = pos + 1 < end ? lds_s32(ring_addr(pos + 1)) : OE_OS_NONE;
+    int h = lds_s32(ring_base + ((uint32_t)pos & (OE_OS_RING - 1)) * 128u);
+    int n1 = lds_s32(ring_base + ((uint32_t)(pos + 1) & (OE_OS_RING - 1)) * 128u);
+    if (row < 0) h = n1 = OE_OS_NONE;
     int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
     uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
     for (int base = e0; base < e1; base += 32) {
@@ -1583,7 +1611,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
       }
       const uint32_t active = __ballot_sync(0xffffffffu, h != OE_OS_NONE);   // rows that still have a requirement waiting
       if (!active) break;
-      uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
+      const uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
       ++chunks;
       skipped += want == 0u;
       if (!want) continue;
@@ -1596,30 +1624,33 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
         const uint32_t b = __ballot_sync(0xffffffffu, (m_mine >> r) & 1u);
         mybits = lane == r ? b : mybits;
       }
-      // One step per offer somebody waits for.  The entry behind n1 is read at the top of a step and moves into n1 at the top
-      // of the NEXT one (`won_prev`): the load has a whole step to land and never stalls the chain
-      //     select (my row listed ? my head : none) -> REDUX.MIN -> compare -> select (head <- n1).
+      // 32 steps, one per offer of the chunk, straight line (a lone warp pays ~4 cycles per instruction issued, so the step is
+      // counted in instructions).  Chain from step to step: select (my row listed ? head : none) -> REDUX.MIN -> compare ->
+      // select (head <- n1).  The entry behind n1 is read at the top of a step and moves into n1 at the top of the NEXT one,
+      // so its load never stalls the chain; the match is kept by the lane that holds the offer and stored after the chunk.
+      const uint32_t ra0 = ring_base + ((uint32_t)(pos + 2) & (OE_OS_RING - 1)) * 128u;
+      uint32_t ra = ra0;          // shared address of entry pos + 2
+      int match = OE_OS_NONE;     // requirement that gets MY offer of this chunk
       bool won_prev = false;
       int nxt_prev = OE_OS_NONE;
-      while (want) {
-        const int e = __ffs(want) - 1;
-        want &= want - 1;
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
         n1 = won_prev ? nxt_prev : n1;
-        const int nxt = pos + 2 < end ? lds_s32(ring_addr(pos + 2)) : OE_OS_NONE;
-        const int v = ((mybits >> e) & 1u) ? h : OE_OS_NONE;
-        const int mn = __reduce_min_sync(0xffffffffu, v);   // = the requirement that gets offer e (every lane knows it now)
-        const bool any = mn != OE_OS_NONE;
-        const bool won = (v == mn) & any;
-        // recorded by the lane that holds offer e in a register: no shuffle, no load
-        int* const dst = dec_row + (size_t)(any ? mn : 0) * DEC_INTS;
-        if ((lane == e) & any) *dst = o_mine;
+        const int nxt = lds_s32(ra);
+        const bool listed = (mybits >> e) & 1u;
+        const int v = listed ? h : OE_OS_NONE;
+        const int mn = __reduce_min_sync(0xffffffffu, v);   // the requirement that gets offer e, known to every lane
+        const bool won = listed & (v == mn) & (mn != OE_OS_NONE);
+        match = lane == e ? mn : match;
         h = won ? n1 : h;
-        pos += won ? 1 : 0;
+        ra += won ? 128u : 0u;
         won_prev = won;
         nxt_prev = nxt;
-        ++steps;
       }
       n1 = won_prev ? nxt_prev : n1;
+      pos += (int)((ra - ra0) >> 7);
+      steps += 32;
+      if (match != OE_OS_NONE) dec_row[(size_t)match * DEC_INTS] = o_mine;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
   }
@@ -1871,7 +1902,7 @@ struct oe_engine {
   DevBuf d_meta, d_union, d_umask;   // commit over union lists (rows <= OE_UNION_MAX_ROWS)
   DevBuf d_sort_hist, d_comp_begin;
   // commit from the offers' side: row groups, per-offer (component, mask), offers sorted by component, requirements sorted by row
-  DevBuf d_os_parent, d_os_groups, d_os_ocomp, d_os_omask, d_os_ohist, d_os_comp_begin, d_os_list, d_os_mask, d_os_rhist, d_os_row_begin, d_os_queue, d_os_cursor;
+  DevBuf d_os_totals, d_os_parent, d_os_groups, d_os_ocomp, d_os_omask, d_os_ohist, d_os_comp_begin, d_os_list, d_os_mask, d_os_rhist, d_os_row_begin, d_os_queue, d_os_cursor;
   int* h_os_info = nullptr;          // pinned: {components, rows of the widest component} of the last grouping
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
   std::vector<int32_t> h_vcand, h_vspan;
@@ -2194,7 +2225,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
-                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff};
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -3608,7 +3639,9 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
   CU(h->d_os_cursor.ensure((size_t)rows * sizeof(int)));
   CU(cudaMemsetAsync(h->d_os_cursor.p, 0, (size_t)rows * sizeof(int), st));
   k_key_hist<<<nb, 256, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>());
-  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_rhist.as<int>(), nb, rows, nullptr, rows, h->d_os_row_begin.as<int>());
+  CU(h->d_os_totals.ensure((size_t)rows * sizeof(int)));
+  k_key_scan_cols<<<(rows + 31) / 32, 1024, 0, st>>>(h->d_os_rhist.as<int>(), nb, rows, nullptr, rows, h->d_os_totals.as<int>());
+  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_totals.as<int>(), nullptr, rows, h->d_os_row_begin.as<int>());
   k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>(), h->d_os_row_begin.as<int>(), nullptr,
                                                           h->d_os_queue.as<int32_t>(), nullptr);
   *launches += 3;
@@ -3658,7 +3691,9 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
   CU(h->d_os_ohist.ensure((size_t)nb * rows * sizeof(int)));
   CU(h->d_os_list.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4)); CU(h->d_os_mask.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4));
   k_offer_masks<<<nb, 256, (size_t)rows * 44, st>>>(rb, g.comp_of, g.lrow, g.info, h->d_os_ocomp.as<int32_t>(), h->d_os_omask.as<uint32_t>(), h->d_os_ohist.as<int>());
-  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, rows, g.info, 0, h->d_os_comp_begin.as<int>());
+  CU(h->d_os_totals.ensure((size_t)rows * sizeof(int)));
+  k_key_scan_cols<<<(rows + 31) / 32, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, rows, g.info, 0, h->d_os_totals.as<int>());
+  k_key_scan<<<1, 1024, 0, st>>>(h->d_os_totals.as<int>(), g.info, 0, h->d_os_comp_begin.as<int>());
   k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(h->d_os_ocomp.as<int32_t>(), n_offers, rows, h->d_os_ohist.as<int>(), h->d_os_comp_begin.as<int>(),
                                                           h->d_os_omask.as<uint32_t>(), h->d_os_list.as<int32_t>(), h->d_os_mask.as<uint32_t>());
   *launches += 3;
