@@ -1285,7 +1285,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_union(UnionArgs a) {
 // time, a chunk nobody can use costs one ballot, and a pass over a later part of the offers (the table arriving in chunks) simply
 // resumes from the rows' queue positions.
 #define OE_OS_MAX_ROWS 2048       // bit rows (classes + re-deployed pods) this path takes; beyond: k_commit
-#define OE_OS_SORT_BLOCK 1024     // items per block of the stable counting sorts
+#define OE_OS_SORT_BLOCK 256      // items per block of the stable counting sorts (one warp ranks a block: 8 rounds of 32)
 
 // Rows > 64: components by union-find over "rows that list the same offer".  thread = one offer.
 __device__ __forceinline__ int uf_find(int* parent, int x) {
@@ -1437,16 +1437,17 @@ __global__ void __launch_bounds__(1024) k_key_scan_cols(int* __restrict__ hist, 
   const int n_keys = n_keys_ptr ? *n_keys_ptr : n_keys_fixed;
   const int lane = threadIdx.x & 31, k = blockIdx.x * 32 + (threadIdx.x >> 5);
   if (k >= n_keys) return;
-  int run = 0;
-  for (int b0 = 0; b0 < n_blocks; b0 += 32) {
-    const int b = b0 + lane;
-    const int v = b < n_blocks ? hist[(int64_t)b * key_stride + k] : 0;
-    int incl = v;
-    for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
-    if (b < n_blocks) hist[(int64_t)b * key_stride + k] = run + incl - v;
-    run += __shfl_sync(0xffffffffu, incl, 31);
-  }
-  if (lane == 0) totals[k] = run;
+  // lane l owns the contiguous run of blocks [l * per, (l + 1) * per): its sum first (independent loads), the lanes' sums scanned,
+  // then the run's exclusive prefixes written back
+  const int per = (n_blocks + 31) / 32;
+  const int b_lo = min(n_blocks, lane * per), b_hi = min(n_blocks, b_lo + per);
+  int sum = 0;
+  for (int b = b_lo; b < b_hi; ++b) sum += hist[(int64_t)b * key_stride + k];
+  int incl = sum;
+  for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
+  int run = incl - sum;
+  for (int b = b_lo; b < b_hi; ++b) { const int v = hist[(int64_t)b * key_stride + k]; hist[(int64_t)b * key_stride + k] = run; run += v; }
+  if (lane == 31) totals[k] = incl;
 }
 __global__ void __launch_bounds__(1024) k_key_scan(const int* __restrict__ totals, const int* __restrict__ n_keys_ptr, int n_keys_fixed, int* __restrict__ key_begin) {
   __shared__ int warp_sum[32];
@@ -1904,6 +1905,9 @@ struct oe_engine {
   // commit from the offers' side: row groups, per-offer (component, mask), offers sorted by component, requirements sorted by row
   DevBuf d_os_totals, d_os_parent, d_os_groups, d_os_ocomp, d_os_omask, d_os_ohist, d_os_comp_begin, d_os_list, d_os_mask, d_os_rhist, d_os_row_begin, d_os_queue, d_os_cursor;
   int* h_os_info = nullptr;          // pinned: {components, rows of the widest component} of the last grouping
+  bool want_queues = false;          // set by oe_evaluate_cycle around its feasibility pass
+  int queues_rows = -1;              // rows the requirement queues on the side stream were built for (-1: not built for this pass)
+  cudaEvent_t ev_queues = nullptr;
   std::vector<uint64_t> h_vfilter;   // rebuild_variants scratch, kept between calls (no allocation per cycle)
   std::vector<int32_t> h_vcand, h_vspan;
   bool task_spans_valid = false, task_odd_type = false, req_spans_valid = false;
@@ -2149,6 +2153,7 @@ int32_t oe_create(const oe_config* cfg, oe_engine** out) {
   }
   for (auto& ev : h->ev) cudaEventCreate(&ev);
   cudaEventCreate(&h->ev_variants);
+  cudaEventCreateWithFlags(&h->ev_queues, cudaEventDisableTiming);
   cudaEventRecord(h->ev_variants, h->stream);
   if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&h->ev_side) != cudaSuccess) {
     g_create_error = "oe_create: side stream"; delete h; return OE_ERR_CUDA;
@@ -2246,6 +2251,7 @@ void oe_destroy(oe_engine* h) {
   for (auto& b : h->d_wire) b.release();
   for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
   if (h->ev_variants) cudaEventDestroy(h->ev_variants);
+  if (h->ev_queues) cudaEventDestroy(h->ev_queues);
   if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
   if (h->ev_side) cudaEventDestroy(h->ev_side);
   if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
@@ -3367,6 +3373,8 @@ int merge_equal_variants(oe_engine* h) {
 }
 
 int run_expand(oe_engine* h, int64_t* launches, cudaStream_t on = nullptr, int64_t w0 = 0, int64_t w1 = -1);
+bool offer_side_ok(int rows);
+int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int64_t M, int rows, cudaStream_t st);
 
 // K1 over the whole offer table, or — while an OE_CFG_ASYNC_LOADS table is still arriving — chunk by chunk as the chunks land.
 // expand_beside (oe_evaluate_cycle with OE_CFG_MATERIALIZE_MATRIX): the matrix columns of every chunk but the last are expanded on
@@ -3396,6 +3404,16 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
   }
   const int rows = h->rows_factored();
   a.row_map = h->V_eff >= 0 ? h->d_row_map.as<int32_t>() : nullptr;
+  h->queues_rows = -1;
+  if (h->want_queues && h->M > 0 && rows > 0 && offer_side_ok(rows)) {
+    // the commit will want every bit row's requirements in plan order: that needs the requirement table only, so it is sorted
+    // on the side stream while this pass runs
+    CU(cudaEventRecord(h->ev_side, h->stream));
+    CU(cudaStreamWaitEvent(h->side_stream, h->ev_side, 0));
+    if (int rc = prepare_queues(h, launches, h->bit_row_of_req(), h->M, rows, h->side_stream)) return rc;
+    CU(cudaEventRecord(h->ev_queues, h->side_stream));
+    h->queues_rows = rows;
+  }
   CU(h->d_F.ensure(std::max<size_t>((size_t)rows * stride, 1) * 4));
   if (rows > 0) {
     const int64_t xblocks_all = stride * 32 / OE_K1_THREADS;
@@ -3648,6 +3666,11 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
   CU(cudaGetLastError());
   return 0;
 }
+// The same, enqueued early (beside the feasibility pass) on the side stream; `st` waits for it.
+int queues_ready(oe_engine* h, int64_t* launches, int rows, cudaStream_t st) {
+  if (h->queues_rows == rows) { h->queues_rows = -1; CU(cudaStreamWaitEvent(st, h->ev_queues, 0)); return 0; }
+  return prepare_queues(h, launches, h->bit_row_of_req(), h->M, rows, st);
+}
 // One pass over the offers of `rb` (global index of its first offer: offer_offset).  Returns 1 (nothing enqueued beyond the
 // grouping) when a component has more than 32 rows: the caller falls back to k_commit.
 int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32_t offer_offset, int64_t M, oe_decision* dec, cudaStream_t st,
@@ -3767,7 +3790,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   if (offer_side_ok(rows)) {
     k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_dec.as<oe_decision>(), h->M);
     CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->stream));
-    if (int rc = prepare_queues(h, launches, h->bit_row_of_req(), h->M, rows, h->stream)) return rc;
+    if (int rc = queues_ready(h, launches, rows, h->stream)) return rc;
     const int rc = commit_offers_pass(h, launches, rb, 0, h->M, h->d_dec.as<oe_decision>(), h->stream, true, true, h->d_req_row.as<int32_t>());
     if (rc <= 0) return rc;
     // a component wider than a warp: the per-row lists below
@@ -3917,6 +3940,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
   if (int rc = ready(h, "oe_evaluate_cycle", true)) return rc;
   tr.mark("ready");
+  struct WantQueues { oe_engine* e; WantQueues(oe_engine* x) : e(x) { e->want_queues = true; } ~WantQueues() { e->want_queues = false; e->queues_rows = -1; } } want_queues(h);
   if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
   bool expand_overlapped = false, two_pass = false;
@@ -3977,7 +4001,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
           // from the offers' side a later pass simply resumes from the rows' queue positions: nothing to collect in between
           k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M);
           CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->hi_stream));
-          if (int rc = prepare_queues(h, &launches, h->bit_row_of_req(), h->M, rows, h->hi_stream)) return rc;
+          if (int rc = queues_ready(h, &launches, rows, h->hi_stream)) return rc;
           if (int rc = commit_offers_pass(h, &launches, rbA, 0, h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
           CU(cudaMemcpyAsync(h_open, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
           CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
