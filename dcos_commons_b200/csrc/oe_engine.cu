@@ -1410,7 +1410,7 @@ __global__ void __launch_bounds__(256) k_offer_masks(RowBits rb, const int* __re
     if (c >= 0) atomicAdd(&s_hist[c], 1);
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < n_comp; c += 256) hist[(int64_t)blockIdx.x * rows + c] = s_hist[c];
+  for (int c = threadIdx.x; c < n_comp; c += 256) hist[(int64_t)c * gridDim.x + blockIdx.x] = s_hist[c];   // key-major: a key's counts over the blocks are contiguous
 }
 
 // Stable counting sort, three kernels.  keys[i] in [0, *n_keys) or negative (dropped); blocks of OE_OS_SORT_BLOCK items.
@@ -1427,27 +1427,41 @@ __global__ void __launch_bounds__(256) k_key_hist(const int32_t* __restrict__ ke
     if (i < n) { const int k = keys[i]; if (k >= 0) atomicAdd(&kh_smem[k], 1); }
   }
   __syncthreads();
-  for (int k = threadIdx.x; k < key_stride; k += 256) hist[(int64_t)blockIdx.x * key_stride + k] = kh_smem[k];
+  for (int k = threadIdx.x; k < key_stride; k += 256) hist[(int64_t)k * gridDim.x + blockIdx.x] = kh_smem[k];
 }
-// warp = one key: the key's counts over the blocks become exclusive prefixes in place (lanes stride over the blocks), totals[key]
-// = its items; then one CTA scans the totals.  (As one thread per key walking the blocks it was a chain of ~1000 dependent
-// global loads: 0.3 ms.)
-__global__ void __launch_bounds__(1024) k_key_scan_cols(int* __restrict__ hist, int n_blocks, int key_stride, const int* __restrict__ n_keys_ptr, int n_keys_fixed,
+// CTA = one key: the key's counts over the blocks (contiguous: the histogram is key-major) become exclusive prefixes in place,
+// totals[key] = its items; then one CTA scans the totals.
+__global__ void __launch_bounds__(1024) k_key_scan_cols(int* __restrict__ hist, int n_blocks, const int* __restrict__ n_keys_ptr, int n_keys_fixed,
                                                         int* __restrict__ totals) {
+  __shared__ int warp_sum[32];
+  __shared__ int carry;
   const int n_keys = n_keys_ptr ? *n_keys_ptr : n_keys_fixed;
-  const int lane = threadIdx.x & 31, k = blockIdx.x * 32 + (threadIdx.x >> 5);
+  const int k = blockIdx.x;
   if (k >= n_keys) return;
-  // lane l owns the contiguous run of blocks [l * per, (l + 1) * per): its sum first (independent loads), the lanes' sums scanned,
-  // then the run's exclusive prefixes written back
-  const int per = (n_blocks + 31) / 32;
-  const int b_lo = min(n_blocks, lane * per), b_hi = min(n_blocks, b_lo + per);
-  int sum = 0;
-  for (int b = b_lo; b < b_hi; ++b) sum += hist[(int64_t)b * key_stride + k];
-  int incl = sum;
-  for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
-  int run = incl - sum;
-  for (int b = b_lo; b < b_hi; ++b) { const int v = hist[(int64_t)b * key_stride + k]; hist[(int64_t)b * key_stride + k] = run; run += v; }
-  if (lane == 31) totals[k] = incl;
+  int* col = hist + (int64_t)k * n_blocks;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < n_blocks; b0 += 1024) {
+    const int b = b0 + threadIdx.x;
+    const int v = b < n_blocks ? col[b] : 0;
+    int incl = v;
+    for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += x; }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_sum[lane], wi = w;
+      for (int d = 1; d < 32; d <<= 1) { const int x = __shfl_up_sync(0xffffffffu, wi, d); if (lane >= d) wi += x; }
+      warp_sum[lane] = wi - w;
+    }
+    __syncthreads();
+    const int excl = carry + warp_sum[warp] + incl - v;
+    if (b < n_blocks) col[b] = excl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[k] = carry;
 }
 __global__ void __launch_bounds__(1024) k_key_scan(const int* __restrict__ totals, const int* __restrict__ n_keys_ptr, int n_keys_fixed, int* __restrict__ key_begin) {
   __shared__ int warp_sum[32];
@@ -1499,7 +1513,7 @@ __global__ void __launch_bounds__(32) k_key_scatter(const int32_t* __restrict__ 
       int base = 0;
       if (lane == leader) {
         base = ks_run[k];
-        if (base < 0) base = key_begin[k] + hist[(int64_t)blockIdx.x * key_stride + k];
+        if (base < 0) base = key_begin[k] + hist[(int64_t)k * gridDim.x + blockIdx.x];
         ks_run[k] = base + __popc(same);
       }
       base = __shfl_sync(same, base, leader);
@@ -3658,7 +3672,7 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
   CU(cudaMemsetAsync(h->d_os_cursor.p, 0, (size_t)rows * sizeof(int), st));
   k_key_hist<<<nb, 256, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>());
   CU(h->d_os_totals.ensure((size_t)rows * sizeof(int)));
-  k_key_scan_cols<<<(rows + 31) / 32, 1024, 0, st>>>(h->d_os_rhist.as<int>(), nb, rows, nullptr, rows, h->d_os_totals.as<int>());
+  k_key_scan_cols<<<rows, 1024, 0, st>>>(h->d_os_rhist.as<int>(), nb, nullptr, rows, h->d_os_totals.as<int>());
   k_key_scan<<<1, 1024, 0, st>>>(h->d_os_totals.as<int>(), nullptr, rows, h->d_os_row_begin.as<int>());
   k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>(), h->d_os_row_begin.as<int>(), nullptr,
                                                           h->d_os_queue.as<int32_t>(), nullptr);
@@ -3715,7 +3729,7 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
   CU(h->d_os_list.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4)); CU(h->d_os_mask.ensure((size_t)nb * OE_OS_SORT_BLOCK * 4));
   k_offer_masks<<<nb, 256, (size_t)rows * 44, st>>>(rb, g.comp_of, g.lrow, g.info, h->d_os_ocomp.as<int32_t>(), h->d_os_omask.as<uint32_t>(), h->d_os_ohist.as<int>());
   CU(h->d_os_totals.ensure((size_t)rows * sizeof(int)));
-  k_key_scan_cols<<<(rows + 31) / 32, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, rows, g.info, 0, h->d_os_totals.as<int>());
+  k_key_scan_cols<<<n_ctas, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, g.info, 0, h->d_os_totals.as<int>());
   k_key_scan<<<1, 1024, 0, st>>>(h->d_os_totals.as<int>(), g.info, 0, h->d_os_comp_begin.as<int>());
   k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(h->d_os_ocomp.as<int32_t>(), n_offers, rows, h->d_os_ohist.as<int>(), h->d_os_comp_begin.as<int>(),
                                                           h->d_os_omask.as<uint32_t>(), h->d_os_list.as<int32_t>(), h->d_os_mask.as<uint32_t>());
