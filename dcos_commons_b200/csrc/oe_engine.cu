@@ -1552,6 +1552,7 @@ struct OfferSideArgs {
 #define OE_OS_NONE 0x7fffffff
 #define OE_OS_RING 128    // queue entries a lane keeps staged in shared memory (topped up to 96 ahead at every chunk of 32 offers)
 #define OE_OS_MIRROR 36   // slots mirrored behind the ring's end (a chunk reads at most 34 consecutive entries)
+#define OE_OS_LANE_SLOTS (OE_OS_RING + OE_OS_MIRROR)   // 164 words per lane: 16-byte aligned rows; lanes 8 apart share banks
 // Shared memory through explicit 32-bit shared-window addresses: written as array accesses beside cp.async the compiler re-derived
 // the window base (S2R CgaCtaId + LEA) inside the replay loop.
 __device__ __forceinline__ int lds_s32(uint32_t addr) {
@@ -1566,7 +1567,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
   // the lanes' queues, staged: ring[(k & (OE_OS_RING - 1)) * 32 + lane] = entry k of the lane's row.  A lane matches at most 32
   // requirements per chunk of 32 offers, so topping the ring up once per chunk (cp.async, a chunk ahead of its use) keeps every
   // read inside a chunk in shared memory; what a step needs from memory is then one LDS whose result is used a step later.
-  __shared__ int ring[(OE_OS_RING + OE_OS_MIRROR) * 32];
+  __shared__ __align__(16) int ring[OE_OS_LANE_SLOTS * 32];
   const int comp = blockIdx.x, lane = threadIdx.x;
   if (comp >= a.info[0]) return;
   const long long t0 = clock64();
@@ -1590,20 +1591,30 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     if (lane == 0) pos += max(n, 0);
     steps = max(n, 0);
   } else {
-    // ring: entry k of the lane's queue sits at slot k & 127; slots 0..33 are mirrored behind slot 127, so the 34 entries a
-    // chunk can touch are contiguous wherever the chunk starts and a step advances its read address by one slot, no wrap
-    const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring) + lane * 4u;
-    int filled = pos;
+    // ring: lane-major, entry k of the lane's queue (k = its index in the queue array) at slot k & 127 of the lane's ring; slots
+    // 0..35 are mirrored behind slot 127, so the 34 entries a chunk can touch are contiguous wherever the chunk starts and a
+    // step advances its read address by one slot, no wrap.  Topped up four entries (16 bytes) per cp.async.
+    const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring) + lane * (uint32_t)(OE_OS_LANE_SLOTS * 4);
+    int filled = pos & ~3;   // entries below `filled` are staged (or on their way); groups of four, aligned in the queue array
     auto top_up = [&]() {
       const int upto = pos + 96;
-      for (; filled < upto; ++filled) {
+      for (; filled < upto; filled += 4) {
         const uint32_t slot = (uint32_t)filled & (OE_OS_RING - 1);
-        if (filled < end) {
-          cp_async_4(ring_base + slot * 128u, Q + filled);
-          if (slot < OE_OS_MIRROR) cp_async_4(ring_base + (slot + OE_OS_RING) * 128u, Q + filled);
-        } else {   // behind the queue's end: "nobody waiting", so that a step needs no bound check
-          asm volatile("st.shared.s32 [%0], %1;" ::"r"(ring_base + slot * 128u), "r"(OE_OS_NONE) : "memory");
-          if (slot < OE_OS_MIRROR) asm volatile("st.shared.s32 [%0], %1;" ::"r"(ring_base + (slot + OE_OS_RING) * 128u), "r"(OE_OS_NONE) : "memory");
+        const uint32_t dst = ring_base + slot * 4u;
+        if (filled + 4 <= end) {
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(Q + filled) : "memory");
+          if (slot < OE_OS_MIRROR) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + OE_OS_RING * 4u), "l"(Q + filled) : "memory");
+        } else {   // the queue's end: what is left of it entry by entry, "nobody waiting" behind it (a step needs no bound check)
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t d = dst + (uint32_t)q * 4u;
+            if (filled + q < end) {
+              cp_async_4(d, Q + filled + q);
+              if (slot < OE_OS_MIRROR) cp_async_4(d + OE_OS_RING * 4u, Q + filled + q);
+            } else {
+              asm volatile("st.shared.s32 [%0], %1;" ::"r"(d), "r"(OE_OS_NONE) : "memory");
+              if (slot < OE_OS_MIRROR) asm volatile("st.shared.s32 [%0], %1;" ::"r"(d + OE_OS_RING * 4u), "r"(OE_OS_NONE) : "memory");
+            }
+          }
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -1611,8 +1622,8 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     top_up();
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncwarp();
-    int h = lds_s32(ring_base + ((uint32_t)pos & (OE_OS_RING - 1)) * 128u);
-    int n1 = lds_s32(ring_base + ((uint32_t)(pos + 1) & (OE_OS_RING - 1)) * 128u);
+    int h = lds_s32(ring_base + ((uint32_t)pos & (OE_OS_RING - 1)) * 4u);
+    int n1 = lds_s32(ring_base + ((uint32_t)(pos + 1) & (OE_OS_RING - 1)) * 4u);
     if (row < 0) h = n1 = OE_OS_NONE;
     int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
     uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
@@ -1633,17 +1644,20 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
       asm volatile("cp.async.wait_group 0;" ::: "memory");   // the entries asked for a chunk ago
       __syncwarp();
       top_up();
-      // which offers of the chunk list MY row: the masks transposed, so that a step needs no shuffle to learn it
-      uint32_t mybits = 0u;
-      for (int r = 0; r < n_rows; ++r) {
-        const uint32_t b = __ballot_sync(0xffffffffu, (m_mine >> r) & 1u);
-        mybits = lane == r ? b : mybits;
+      // which offers of the chunk list MY row: the 32 x 32 bit matrix (lane = offer, bit = row) transposed with five butterfly
+      // exchanges, so that a step needs no shuffle to learn it (bit e of lane r <- bit r of lane e)
+      uint32_t mybits = m_mine;
+#pragma unroll
+      for (int j = 16; j >= 1; j >>= 1) {
+        const uint32_t keep = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;   // bit positions with bit j clear
+        const uint32_t other = __shfl_xor_sync(0xffffffffu, mybits, j);
+        mybits = (lane & j) ? ((mybits & ~keep) | ((other >> j) & keep)) : ((mybits & keep) | ((other << j) & ~keep));
       }
       // 32 steps, one per offer of the chunk, straight line (a lone warp pays ~4 cycles per instruction issued, so the step is
       // counted in instructions).  Chain from step to step: select (my row listed ? head : none) -> REDUX.MIN -> compare ->
       // select (head <- n1).  The entry behind n1 is read at the top of a step and moves into n1 at the top of the NEXT one,
       // so its load never stalls the chain; the match is kept by the lane that holds the offer and stored after the chunk.
-      const uint32_t ra0 = ring_base + ((uint32_t)(pos + 2) & (OE_OS_RING - 1)) * 128u;
+      const uint32_t ra0 = ring_base + ((uint32_t)(pos + 2) & (OE_OS_RING - 1)) * 4u;
       uint32_t ra = ra0;          // shared address of entry pos + 2
       int match = OE_OS_NONE;     // requirement that gets MY offer of this chunk
       bool won_prev = false;
@@ -1658,12 +1672,12 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
         const bool won = listed & (v == mn) & (mn != OE_OS_NONE);
         match = lane == e ? mn : match;
         h = won ? n1 : h;
-        ra += won ? 128u : 0u;
+        ra += won ? 4u : 0u;
         won_prev = won;
         nxt_prev = nxt;
       }
       n1 = won_prev ? nxt_prev : n1;
-      pos += (int)((ra - ra0) >> 7);
+      pos += (int)((ra - ra0) >> 2);
       steps += 32;
       if (match != OE_OS_NONE) dec_row[(size_t)match * DEC_INTS] = o_mine;
     }
