@@ -577,6 +577,14 @@ class Handle:
         self._check(self.b.fn("evaluate_cycle")(self.h, out.ctypes.data, C.byref(st)))
         return out, st.as_dict()
 
+    def gather_decisions(self):
+        """oe_gather_decisions: the merged decision table of a sharded cycle (peers attached)."""
+        out = np.zeros(self.tables.n_reqs, dtype=DECISION_DTYPE)
+        f = self.b.fn("gather_decisions")
+        f.argtypes = [_p, _p]
+        self._check(f(self.h, out.ctypes.data if out.size else None))
+        return out
+
     def evaluate_cycle_into(self, out_ptr: int):
         """Decisions written to caller-owned host memory (e.g. a pinned buffer)."""
         st = OeStats()

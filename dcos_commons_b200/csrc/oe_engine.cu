@@ -191,16 +191,19 @@ __global__ void k_count_tasks(DevTasks t, DevProg p, int32_t* __restrict__ cnt, 
 }
 
 // K0b: per counter set (blockIdx.x) and, for blockIdx.y > 0, per variant y-1 with that variant's self rows taken out:
-// {min over keys with a tally, max, number of keys with a tally}.  One CTA strides over the key space.
-__global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __restrict__ cnt, int4* __restrict__ out_base,
+// {min over keys with a tally, max, number of keys with a tally}.  Only the sets a RoundRobin rule reads (rr_used) — a MaxPer
+// rule looks at single tallies.  gridDim.z CTAs share a large key space (hostnames: one key per agent) and merge with atomics
+// into a cell preset to {INT_MAX, 0, 0}; k_rr_finish then turns "no key" into min = 0.
+__global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __restrict__ cnt, const uint8_t* __restrict__ rr_used, int4* __restrict__ out_base,
                                                     int4* __restrict__ out_var) {
   const int c = blockIdx.x;
+  if (!rr_used[c]) return;
   const int var = (int)blockIdx.y - 1;
   const oe_counter_set cs = cx.p.csets[c];
   const int64_t n = cx.p.cs_off[c + 1] - cx.p.cs_off[c];
   const int32_t* base = cnt + cx.p.cs_off[c];
   int mn = 0x7fffffff, mx = 0, nk = 0;
-  for (int64_t k = threadIdx.x; k < n; k += blockDim.x) {
+  for (int64_t k = (int64_t)blockIdx.z * blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.z * blockDim.x) {
     int v = base[k];
     if (var >= 0 && v > 0) v -= self_key_count(cx, var, cs, (int32_t)k);
     if (v > 0) { mn = min(mn, v); mx = max(mx, v); ++nk; }
@@ -217,10 +220,21 @@ __global__ void __launch_bounds__(256) k_rr_summary(DevCtx cx, const int32_t* __
     __syncthreads();
   }
   if (threadIdx.x == 0) {
-    int4 r = make_int4(smn[0] == 0x7fffffff ? 0 : smn[0], smx[0], snk[0], 0);
-    if (var < 0) out_base[c] = r;
-    else out_var[(int64_t)var * cx.p.n_csets + c] = r;
+    int4* cell = var < 0 ? out_base + c : out_var + (int64_t)var * cx.p.n_csets + c;
+    if (gridDim.z == 1) {
+      *cell = make_int4(smn[0] == 0x7fffffff ? 0 : smn[0], smx[0], snk[0], 0);
+    } else {
+      atomicMin(&cell->x, smn[0]); atomicMax(&cell->y, smx[0]); atomicAdd(&cell->z, snk[0]);
+    }
   }
+}
+__global__ void k_rr_preset(int4* __restrict__ cells, int64_t n) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < n) cells[q] = make_int4(0x7fffffff, 0, 0, 0);
+}
+__global__ void k_rr_finish(int4* __restrict__ cells, int64_t n) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < n && cells[q].x == 0x7fffffff) cells[q].x = 0;
 }
 
 // K1: thread = one offer row, blockIdx.y = a tile of factored rows (classes first, then variants).  The CTA stages the
@@ -1741,7 +1755,15 @@ __global__ void k_merge_unplaced(const oe_decision* __restrict__ dec_sub, const 
 // `mismatch` receives requirement + 1 when the recorded re-run of a winner fails although the feasibility pass (folded form
 // or rule table) set its bit: the two formulations disagree, and the decision's ports / MOUNT slots cannot be trusted —
 // oe_evaluate_cycle turns that into OE_ERR_STATE instead of returning them.
-__global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec, int* __restrict__ mismatch) {
+// Sharded engines with peers attached (push.n > 0): only the shard that holds the winning offer can fill the decision in; it
+// also stores the decision and the offer's placement columns (what a launch records, LaunchEvaluationStage.java:58-68) into
+// every shard's exchange region, record j of the pass's parity: [8 words oe_decision][agent, host, zone, region, A attrs, Q rr].
+struct DecisionPush {
+  uint32_t* area[OE_PEER_MAX_WORLD];   // every shard's decision records of this pass (null when not sharded)
+  int n, rec_words;
+};
+__global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, int64_t M, oe_decision* __restrict__ dec, int* __restrict__ mismatch,
+                              DecisionPush push) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= M) return;
   oe_decision d = dec[j];
@@ -1750,7 +1772,8 @@ __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, in
   for (int q = 0; q < OE_MAX_MOUNT_OPS; ++q) d.mount_slot[q] = -1;
   d.reserved0 = 0;
   const int64_t i = (int64_t)d.offer_row - cx.o.row_offset;
-  if (d.offer_row >= 0 && i >= 0 && i < cx.o.N) {
+  const bool local = d.offer_row >= 0 && i >= 0 && i < cx.o.N;
+  if (local) {
     const int row = req_row[j];
     const int var = row < cx.p.C ? -1 : row - cx.p.C;
     const int cls = var < 0 ? row : cx.v.cls[var];
@@ -1759,6 +1782,30 @@ __global__ void k_materialize(DevCtx cx, const int32_t* __restrict__ req_row, in
     if (!pass) atomicCAS(mismatch, 0, (int)min(j + 1, (int64_t)INT_MAX));  // the commit only picks offers whose bit is set
   }
   dec[j] = d;
+  if (push.n > 0 && local) {
+    uint32_t w[8];
+    memcpy(w, &d, sizeof d);
+    for (int p = 0; p < push.n; ++p) {
+      uint32_t* rec = push.area[p] + (int64_t)j * push.rec_words;
+      reinterpret_cast<uint4*>(rec)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      reinterpret_cast<uint4*>(rec)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+      rec[8] = (uint32_t)cx.o.agent[i]; rec[9] = (uint32_t)cx.o.host[i]; rec[10] = (uint32_t)cx.o.zone[i]; rec[11] = (uint32_t)cx.o.region[i];
+      for (int q = 0; q < cx.o.A; ++q) rec[12 + q] = (uint32_t)cx.o.attr[(int64_t)q * cx.o.N + i];
+      for (int q = 0; q < cx.o.Q; ++q) rec[12 + cx.o.A + q] = (uint32_t)cx.o.rr[(int64_t)q * cx.o.N + i];
+    }
+  }
+}
+// ... and the other half: the decisions whose winner lives on another shard, read from this shard's own region once every
+// shard's records of the pass have landed (k_peer_wait on the decision flags).
+__global__ void k_gather_decisions(oe_decision* __restrict__ dec, int64_t M, const uint32_t* __restrict__ area, int rec_words, int64_t row_offset, int64_t N) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const int32_t o = dec[j].offer_row;
+  const int64_t i = (int64_t)o - row_offset;
+  if (o < 0 || (i >= 0 && i < N)) return;
+  const uint4* rec = reinterpret_cast<const uint4*>(area + j * rec_words);
+  uint4* out = reinterpret_cast<uint4*>(dec + j);
+  out[0] = rec[0]; out[1] = rec[1];
 }
 
 // Kdbg: failed-stage mask of every (requirement in [j0, j1), offer) pair — what OfferEvaluator.java:173-214 feeds into the
@@ -1811,6 +1858,22 @@ struct LaunchArgs {
   const int32_t* req_type;
   const int32_t* req_index;
 };
+// the same on a sharded engine: the winning offer may live on another shard, its placement columns come from the decision
+// record that shard pushed into this shard's exchange region (k_materialize)
+__global__ void k_apply_launches_records(LaunchArgs a, DevTasks t, const uint32_t* __restrict__ area, int rec_words, int A, int Q) {
+  const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (x >= a.n) return;
+  const int32_t j = a.req[x];
+  const uint32_t* rec = area + (int64_t)j * rec_words + 8;
+  const int64_t r = a.dst_row[x];
+  t.name[r] = a.name_id[x];
+  t.type[r] = a.req_type[j];
+  t.index[r] = a.req_index[j];
+  t.agent[r] = (int32_t)rec[0]; t.host[r] = (int32_t)rec[1]; t.zone[r] = (int32_t)rec[2]; t.region[r] = (int32_t)rec[3];
+  for (int q = 0; q < t.TA; ++q) t.attr[(int64_t)q * t.cap + r] = q < A ? (int32_t)rec[4 + q] : -1;
+  for (int q = 0; q < t.Q; ++q) t.rr[(int64_t)q * t.cap + r] = q < Q ? (int32_t)rec[4 + A + q] : -1;
+  for (int q = 0; q < t.FW; ++q) t.filter[(int64_t)q * t.cap + r] = a.filter[x * t.FW + q];
+}
 __global__ void k_apply_launches(LaunchArgs a, DevOffers o, DevTasks t, const oe_decision* __restrict__ dec) {
   const int64_t x = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (x >= a.n) return;
@@ -1879,14 +1942,16 @@ struct oe_engine {
   std::vector<oe_rule_node> h_nodes;
   std::vector<oe_counter_set> h_csets;
   std::vector<int64_t> h_cs_off;
-  std::vector<uint8_t> class_self_sensitive;
+  std::vector<uint8_t> class_self_sensitive, h_rr_used;   // h_rr_used[c]: a RoundRobin rule reads counter set c's {min, max, #keys}
+  bool any_rr_used = false;
+  int64_t max_rr_keys = 0;
   std::vector<int32_t> h_pod_role, h_excl_begin;
   std::vector<uint16_t> h_excl;
   int n_rule_nodes = 0;
   int fast_K = -1, fast_S = -1;  // offer-table shape the folded class descriptors were built for (-1 = stale)
   int tab_words = 0, tab_zdim = 1, tab_rdim = 1;
   bool any_rule_tab = false;
-  DevBuf d_fast, d_rule_tab;
+  DevBuf d_fast, d_rule_tab, d_rr_used;
   DevBuf d_op_begin, d_ops, d_nodes, d_pod_role, d_excl_begin, d_excl, d_rs_begin, d_rs, d_csets, d_cs_off, d_ts_type, d_mbits;
   DevProg dp{};
 
@@ -1973,7 +2038,15 @@ struct oe_engine {
   bool peers_attached = false;
   uint32_t peer_epoch = 0;                    // passes published so far; parity = peer_epoch & 1
   unsigned long long peer_timeout_ns = 10ull * 1000 * 1000 * 1000;
+  // ... followed by the decision records [2 parities][exch_max_reqs][exch_rec_words] (k_materialize pushes, oe_gather_decisions
+  // and oe_apply_launches read); flag words 16.. of the header carry the pass number of every shard's records
+  int64_t exch_max_reqs = 0;
+  int exch_rec_words = 0;
+  bool decisions_gathered = false;            // this pass's records of the other shards were merged into d_dec already
   size_t exch_parity_words() const { return (size_t)world * exch_max_rows * exch_stride; }
+  uint32_t* exch_records(int shard, uint32_t epoch) const {
+    return peer_base[shard] + OE_PEER_HEADER_WORDS + 2 * exch_parity_words() + (size_t)(epoch & 1u) * (size_t)exch_max_reqs * exch_rec_words;
+  }
   uint32_t* exch_rows(int shard, uint32_t epoch) const {  // shard's buffer of that epoch's parity
     return peer_base[shard] + OE_PEER_HEADER_WORDS + (size_t)(epoch & 1u) * exch_parity_words();
   }
@@ -2020,6 +2093,16 @@ struct oe_engine {
   } while (0)
 
 namespace {
+
+// Where k_materialize stores the decision records of this pass (sharded engines with peers attached and a decision area).
+DecisionPush decision_push(const oe_engine* h) {
+  DecisionPush p{};
+  if (h->world > 1 && h->peers_attached && h->exch_max_reqs >= h->M && h->exch_rec_words > 0) {
+    p.n = h->world; p.rec_words = h->exch_rec_words;
+    for (int r = 0; r < h->world; ++r) p.area[r] = h->exch_records(r, h->peer_epoch);
+  }
+  return p;
+}
 
 // While the offer table is on the bus: a table of up to 16 MB that lives in pinned (device-visible) host memory is fetched by
 // a kernel, not queued behind the offers on the copy engine (see k_fetch_host).  Pageable sources keep the plain copy.
@@ -2258,7 +2341,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
-                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals};
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -2334,6 +2417,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
 
   // rule programs: node fields + postfix stack discipline
   h->class_self_sensitive.assign((size_t)C, 0);
+  h->h_rr_used.assign((size_t)std::max(t->n_counter_sets, 1), 0);
   for (int c = 0; c < C; ++c) {
     const int ob = t->op_begin[c], oe_ = t->op_begin[c + 1];
     if (oe_ < ob || oe_ - ob > OE_MAX_STAGE_OPS) return h->fail(OE_ERR_LIMIT, "class %d: %d stage ops (max %d)", c, oe_ - ob, OE_MAX_STAGE_OPS);
@@ -2394,6 +2478,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
               if (want >= 0 && ks != want) return h->fail(OE_ERR_INVALID, "class %d rule node %d: counter set key space %d does not fit the rule", c, n - nb, ks);
               if (nd.op == OE_R_RR && ks == OE_KS_ATTR) return h->fail(OE_ERR_INVALID, "class %d rule node %d: round robin over the multi-key space", c, n - nb);
               if (nd.op == OE_R_MAXPER_ATTR && !matcher_ok(nd.c, d.n_attrs)) return h->fail(OE_ERR_INVALID, "class %d rule node %d: matcher offset", c, n - nb);
+              if (nd.op == OE_R_RR) h->h_rr_used[(size_t)nd.a] = 1;
               h->class_self_sensitive[c] = 1;
             } break;
             case OE_R_TYPE_AVOID: case OE_R_TYPE_COLOCATE:
@@ -2438,6 +2523,10 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   if (int rc = upload(h, h->d_cs_off, h->h_cs_off.data(), h->h_cs_off.size())) return rc;
   if (int rc = upload(h, h->d_ts_type, t->type_set_pod_type, (size_t)t->n_type_sets)) return rc;
   if (int rc = upload(h, h->d_mbits, t->matcher_bits, (size_t)t->n_matcher_words)) return rc;
+  if (int rc = upload(h, h->d_rr_used, h->h_rr_used.data(), h->h_rr_used.size())) return rc;
+  h->any_rr_used = false; h->max_rr_keys = 0;
+  for (int c = 0; c < t->n_counter_sets; ++c)
+    if (h->h_rr_used[(size_t)c]) { h->any_rr_used = true; h->max_rr_keys = std::max(h->max_rr_keys, h->h_cs_off[(size_t)c + 1] - h->h_cs_off[(size_t)c]); }
 
   CU(h->d_cnt.ensure(std::max<size_t>((size_t)h->h_cs_off.back(), 1) * 4));
   CU(h->d_rrsum.ensure(std::max<size_t>((size_t)h->n_csets, 1) * sizeof(int4)));
@@ -3175,10 +3264,21 @@ int run_counters(oe_engine* h, int64_t* launches) {
                                                                          h->d_type_agent.as<int32_t>());
     ++*launches;
   }
-  if (h->n_csets) {
-    dim3 grid((unsigned)h->n_csets, (unsigned)(1 + h->V));
-    k_rr_summary<<<grid, 256, 0, h->stream>>>(h->ctx(), h->d_cnt.as<int32_t>(), h->d_rrsum.as<int4>(), h->d_vrrsum.as<int4>());
+  if (h->n_csets && h->any_rr_used) {
+    // CTAs per counter set: one for a few thousand keys (zones, regions, attributes), up to 64 for a key per agent
+    const int splits = (int)std::max<int64_t>(1, std::min<int64_t>(64, h->max_rr_keys / 16384));
+    if ((1 + (int64_t)h->V) > 65535) return h->fail(OE_ERR_LIMIT, "oe: %d re-deployed requirements exceed what one tally-summary launch covers", h->V);
+    dim3 grid((unsigned)h->n_csets, (unsigned)(1 + h->V), (unsigned)splits);
+    if (splits > 1) {
+      k_rr_preset<<<(unsigned)((h->n_csets + 255) / 256), 256, 0, h->stream>>>(h->d_rrsum.as<int4>(), h->n_csets);
+      if (h->V > 0) k_rr_preset<<<(unsigned)(((int64_t)h->V * h->n_csets + 255) / 256), 256, 0, h->stream>>>(h->d_vrrsum.as<int4>(), (int64_t)h->V * h->n_csets);
+    }
+    k_rr_summary<<<grid, 256, 0, h->stream>>>(h->ctx(), h->d_cnt.as<int32_t>(), h->d_rr_used.as<uint8_t>(), h->d_rrsum.as<int4>(), h->d_vrrsum.as<int4>());
     ++*launches;
+    if (splits > 1) {
+      k_rr_finish<<<(unsigned)((h->n_csets + 255) / 256), 256, 0, h->stream>>>(h->d_rrsum.as<int4>(), h->n_csets);
+      if (h->V > 0) k_rr_finish<<<(unsigned)(((int64_t)h->V * h->n_csets + 255) / 256), 256, 0, h->stream>>>(h->d_vrrsum.as<int4>(), (int64_t)h->V * h->n_csets);
+    }
   }
   CU(cudaGetLastError());
   h->counters_fresh = true;
@@ -3639,7 +3739,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
       k_commit_union<<<32, 32, union_smem, h->hi_stream>>>(ua);
       // the winners' pipelines re-run right behind it, on the same stream: at the main stream's priority they would queue
       // behind the expansion's grid
-      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1);
+      if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1, decision_push(h));
       materialized = true;
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
       CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
@@ -3652,7 +3752,7 @@ int commit_union_pass(oe_engine* h, int64_t* launches, const RowBits& rb, const 
     }
     ++*launches;
     CU(cudaGetLastError());
-    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1);
+    if (!materialized && materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), h->d_req_row.as<int32_t>(), M, dec, h->d_nplaced.as<int>() + 1, decision_push(h));
     ++*launches;
     CU(cudaGetLastError());
     if (trace_on) {
@@ -3766,7 +3866,7 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
     CU(cudaEventRecord(h->ev_fork, st));
     CU(cudaStreamWaitEvent(h->hi_stream, h->ev_fork, 0));
     k_commit_offers<<<n_ctas, 32, 0, h->hi_stream>>>(a);
-    if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+    if (materialize) k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1, decision_push(h));
     materialized = true;
     CU(cudaEventRecord(h->ev_commit, h->hi_stream));
     CU(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0));
@@ -3780,7 +3880,7 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
   ++*launches;
   CU(cudaGetLastError());
   if (!materialized && materialize) {
-    k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1);
+    k_materialize<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(h->ctx(), req_row, M, dec, h->d_nplaced.as<int>() + 1, decision_push(h));
     CU(cudaGetLastError());
   }
   if (materialize) ++*launches;
@@ -3877,7 +3977,7 @@ int run_commit(oe_engine* h, int64_t* launches) {
   }
   ++*launches;
   CU(cudaGetLastError());
-  k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1);
+  k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1, decision_push(h));
   ++*launches;
   CU(cudaGetLastError());
   return 0;
@@ -3969,7 +4069,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   if (int rc = ready(h, "oe_evaluate_cycle", true)) return rc;
   tr.mark("ready");
   struct WantQueues { oe_engine* e; WantQueues(oe_engine* x) : e(x) { e->want_queues = true; } ~WantQueues() { e->want_queues = false; e->queues_rows = -1; } } want_queues(h);
-  if (!out && h->M > 0) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
+  if (!out && h->M > 0 && !(h->world > 1 && h->peers_attached)) return h->fail(OE_ERR_INVALID, "oe_evaluate_cycle: out is NULL");
   int64_t launches = 0;
   bool expand_overlapped = false, two_pass = false;
   CU(cudaEventRecord(h->ev[0], h->stream));
@@ -4071,7 +4171,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
                                                                                   h->d_dec.as<oe_decision>());
         ++launches;
       }
-      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1);
+      k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1, decision_push(h));
       ++launches;
       CU(cudaGetLastError());
       CU(cudaEventRecord(h->ev_commit, h->hi_stream));
@@ -4104,7 +4204,17 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   }
   int placed_and_mismatch[2] = {0, 0};
   int& n_placed = placed_and_mismatch[0];
-  if (h->M > 0) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
+  h->decisions_gathered = false;
+  if (decision_push(h).n > 0) {
+    // every shard's k_materialize has stored its winners' records into all regions: raise this shard's decision flag behind them
+    PeerFlags f{};
+    f.n = h->world; f.rank = h->rank; f.epoch = h->peer_epoch;
+    for (int p = 0; p < h->world; ++p) f.flags[p] = h->peer_base[p] + 16;
+    k_peer_signal<<<1, 32, 0, h->stream>>>(f);
+    ++launches;
+    CU(cudaGetLastError());
+  }
+  if (h->M > 0 && out) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaMemcpyAsync(placed_and_mismatch, h->d_nplaced.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   int peer_err = 0;
   if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -4188,10 +4298,53 @@ int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t
   return OE_OK;
 }
 
+namespace {
+// Sharded engines: waits (on the device) until every shard's decision records of this pass have landed in this shard's region
+// and copies the decisions of winners that live on other shards into the decision table.
+int gather_decisions(oe_engine* h) {
+  if (!h->cycle_done) return h->fail(OE_ERR_STATE, "no cycle evaluated since the last load");
+  if (!(h->world > 1 && h->peers_attached && h->exch_max_reqs >= h->M && h->exch_rec_words > 0))
+    return h->fail(OE_ERR_STATE, "the merged decision table needs attached peers and a decision area sized for the requirement table: load the requirements, then "
+                   "oe_peer_export / oe_peer_attach (area for %lld requirements, table has %lld)", (long long)h->exch_max_reqs, (long long)h->M);
+  if (h->decisions_gathered || h->M == 0) return 0;
+  k_peer_wait<<<1, 32, 0, h->stream>>>(h->peer_base[h->rank] + 16, h->world, h->peer_epoch, h->peer_timeout_ns, h->d_peer_err.as<int>());
+  k_gather_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_dec.as<oe_decision>(), h->M, h->exch_records(h->rank, h->peer_epoch), h->exch_rec_words,
+                                                                          h->row_offset, h->N);
+  CU(cudaGetLastError());
+  int peer_err = 0;
+  CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  if (peer_err) {
+    CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
+    return h->fail(OE_ERR_STATE, "shard %d did not publish its decisions of pass %u within %.1f s (every rank must call oe_evaluate_cycle)", peer_err - 1, h->peer_epoch,
+                   h->peer_timeout_ns * 1e-9);
+  }
+  h->decisions_gathered = true;
+  return 0;
+}
+}  // namespace
+
+int32_t oe_gather_decisions(oe_engine* h, oe_decision* out) {
+  if (!h) return OE_ERR_INVALID;
+  CU(cudaSetDevice(h->device));
+  if (int rc = gather_decisions(h)) return rc;
+  if (out && h->M > 0) {
+    CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+  }
+  return OE_OK;
+}
+
 int32_t oe_apply_launches(oe_engine* h) {
   if (int rc = ready(h, "oe_apply_launches")) return rc;
   if (!h->cycle_done) return h->fail(OE_ERR_STATE, "oe_apply_launches: no cycle evaluated since the last load");
-  if (h->world > 1) return h->fail(OE_ERR_STATE, "oe_apply_launches: not available on a sharded engine (winning rows live on other shards)");
+  const bool from_records = h->world > 1;
+  if (from_records) {
+    if (!(h->peers_attached && h->exch_max_reqs >= h->M && h->exch_rec_words > 0))
+      return h->fail(OE_ERR_STATE, "oe_apply_launches on a sharded engine needs attached peers and a decision area (oe_peer_export after the requirements were loaded): "
+                     "the winning offers' placement columns live on other shards");
+    if (int rc = gather_decisions(h)) return rc;
+  }
   if (h->h_launch_begin.empty()) return h->fail(OE_ERR_STATE, "oe_apply_launches: the requirement table carries no launch rows");
   if (h->dt.TA < h->dof.A) return h->fail(OE_ERR_INVALID, "oe_apply_launches: task table has fewer attribute slots than the offer table");
   std::vector<int32_t> dst, req, name;
@@ -4236,7 +4389,10 @@ int32_t oe_apply_launches(oe_engine* h) {
     LaunchArgs a{(int64_t)dst.size(), h->d_l_dst.as<int32_t>(), h->d_l_req.as<int32_t>(), h->d_l_name.as<int32_t>(), h->d_l_filter.as<uint32_t>(),
                  h->d_rtype.as<int32_t>(), h->d_rindex.as<int32_t>()};
     // a pod stores each task name once, and names are unique rows, so no two threads write one row
-    k_apply_launches<<<(unsigned)((a.n + 127) / 128), 128, 0, h->stream>>>(a, h->dof, h->dt, h->d_dec.as<oe_decision>());
+    if (from_records)
+      k_apply_launches_records<<<(unsigned)((a.n + 127) / 128), 128, 0, h->stream>>>(a, h->dt, h->exch_records(h->rank, h->peer_epoch), h->exch_rec_words, h->dof.A, h->dof.Q);
+    else
+      k_apply_launches<<<(unsigned)((a.n + 127) / 128), 128, 0, h->stream>>>(a, h->dof, h->dt, h->d_dec.as<oe_decision>());
     CU(cudaGetLastError());
   }
   h->dt.T = T;
@@ -4279,7 +4435,10 @@ int32_t oe_peer_export(oe_engine* h, int32_t max_rows, void* handle, void** dev_
   h->detach_peers();
   h->exch_max_rows = max_rows;
   h->exch_stride = h->stride();
-  const size_t bytes = (OE_PEER_HEADER_WORDS + 2 * h->exch_parity_words()) * 4;
+  // decision records (merged decision table, launches on a sharded engine): sized for the requirement table loaded now, with head room
+  h->exch_rec_words = ((8 + 4 + h->dof.A + h->dof.Q) + 3) / 4 * 4;
+  h->exch_max_reqs = h->hasR ? std::max<int64_t>(1024, h->M + h->M / 4) : 0;
+  const size_t bytes = (OE_PEER_HEADER_WORDS + 2 * h->exch_parity_words() + 2 * (size_t)h->exch_max_reqs * h->exch_rec_words) * 4;
   if (h->d_exch.cap < bytes) {   // a region of its own, exactly one cudaMalloc: that is what an IPC handle names
     h->d_exch.release();
     CU(cudaMalloc(&h->d_exch.p, bytes));

@@ -468,7 +468,8 @@ int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t
 
 /* Multi-cycle replay: store the tasks of every pod placed by the last oe_evaluate_cycle into the device task table
  * (rows with the same task name are overwritten, as StateStore.storeTasks does), so that the next cycle's tallies
- * see them (LaunchEvaluationStage.java:58-68 → PersistentLaunchRecorder.java:74-137).                              */
+ * see them (LaunchEvaluationStage.java:58-68 → PersistentLaunchRecorder.java:74-137).  On a sharded engine: see
+ * oe_gather_decisions; every rank calls it after its oe_evaluate_cycle and ends up with the same task table.         */
 int32_t oe_apply_launches(oe_engine* h);
 
 /* Current device task table (after oe_apply_launches), slot-major columns sized by *n_tasks; pass name_id == NULL to
@@ -516,6 +517,16 @@ int32_t oe_peer_export(oe_engine* h, int32_t max_rows, void* handle, void** dev_
 int32_t oe_peer_attach(oe_engine* h, const void* handles, void* const* same_process_ptrs);
 /* Back to the caller-side gather: unmaps the other shards' regions (when one rank could not attach, all ranks detach). */
 int32_t oe_peer_detach(oe_engine* h);
+/* The complete decision table of a sharded cycle, in one place.  Every rank computes every offer_row, but the dynamic ports,
+ * MOUNT slots and the number of fresh reservation ids of a winner (S/offer/evaluate/PortEvaluationStage.java:242-298,
+ * S/offer/MesosResourcePool.java:282-328) can only be filled in by the shard that holds the winning offer.  With peers attached
+ * and a decision area in the exchange regions (oe_peer_export AFTER the requirement table was loaded: the area is sized for
+ * it, plus a quarter), oe_evaluate_cycle stores each shard's winners into every shard's region; this call waits on the device
+ * until all shards' records of the pass have landed and writes the merged table to out[M] (may be NULL: only merge on the
+ * device).  Call it on the ranks that want the table — oe_evaluate_cycle itself accepts out == NULL on a peer-attached engine,
+ * so that only one rank pays for the copy.  oe_apply_launches on a sharded engine does this step itself and reads the winning
+ * offers' placement columns from the same records (S/state/PersistentLaunchRecorder.java:74-137 has ONE task store).       */
+int32_t oe_gather_decisions(oe_engine* h, oe_decision* out);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Allocation-free first-fit.  This entry point has no counterpart in the reference (the JVM allocates freely); it

@@ -95,8 +95,56 @@ def test_peer_exchange_decisions_equal_unsharded(world):
             lo, hi = bounds[rank]
             mine = (want["offer_row"] >= lo) & (want["offer_row"] < hi)
             assert d[mine].tobytes() == want[mine].tobytes()
+        # the merged table: every shard's winners (ports, MOUNT slots, fresh reservation ids) on every rank that asks for it
+        for rank, e in enumerate(engines):
+            assert e.gather_decisions().tobytes() == want.tobytes(), f"cycle {cycle} rank {rank}"
     for e in engines:
         e.close()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_replay_records_launches_on_every_rank(world):
+    """Several cycles with the launches recorded in between (oe_apply_launches) on sharded, peer-attached engines: every rank
+    must end up with the oracle's task table although a winning offer's placement columns live on one shard only."""
+    import copy
+    cl = synth.make_cluster(6000, 900, 8, 3, 4, 120, "c4")
+    t = cl.tables
+    per = 300
+    orc = Oracle()
+    engines = None
+    for cyc in range(3):
+        sub = copy.copy(t)
+        sl = slice(cyc * per, (cyc + 1) * per)
+        sub.class_id, sub.r_pod_type_id, sub.r_pod_index = t.class_id[sl].copy(), t.r_pod_type_id[sl].copy(), t.r_pod_index[sl].copy()
+        sub.launch_begin = (t.launch_begin[sl.start: sl.stop + 1] - t.launch_begin[sl.start]).astype(np.int32)
+        sub.launch_name_id = t.launch_name_id[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.launch_filter_bits = t.launch_filter_bits[t.launch_begin[sl.start]: t.launch_begin[sl.stop]].copy()
+        sub.normalise()
+        if cyc == 0:
+            orc.load(sub)
+            engines, bounds, shard_rows = _attached_engines(sub, world, max_rows=64)
+        else:
+            orc.tables = sub
+            orc.load_requirements(sub)
+            for e in engines:
+                e.tables = sub
+                e.load_requirements(sub)
+        want, _ = orc.evaluate_cycle()
+        for e in engines:
+            e.class_feasibility(fetch=False)
+        for e in engines:
+            assert np.array_equal(e.evaluate_cycle()[0]["offer_row"], want["offer_row"]), f"cycle {cyc}"
+        orc.apply_launches()
+        for e in engines:
+            e.apply_launches()
+        tc = orc.export_tasks()
+        for rank, e in enumerate(engines):
+            tg = e.export_tasks()
+            for k in tc:
+                assert np.array_equal(tc[k], tg[k]), f"cycle {cyc} rank {rank}: task column {k}"
+    for e in engines:
+        e.close()
+    orc.close()
 
 
 @pytest.mark.parametrize("seed", range(3100, 3108))
