@@ -422,6 +422,7 @@ def run_engine(args):
         return r
 
     exchange = None
+    merged_on_rank0 = False
 
     def cycle():
         eng2.tables = pt
@@ -432,7 +433,13 @@ def run_engine(args):
         if world > 1 and exchange == "nccl all-gather":
             eng2.feasibility(fetch=False)                 # K0 + K1 + K1x on this rank's shard
             sharded.gather_class_bits(eng2, dist)         # the one exchange step: class rows of every shard
-        # peers attached: the pass publishes its rows into every rank's exchange region itself, this call is the whole cycle
+        # peers attached: the pass publishes its rows into every rank's exchange region itself, this call is the whole cycle;
+        # every rank pushes its winners' ports / volumes into every region, and only rank 0 fetches the merged table
+        if world > 1 and merged_on_rank0:
+            st = timed("evaluate_cycle", lambda: eng2.evaluate_cycle_into(None))
+            if rank == 0:
+                timed("gather_decisions", lambda: eng2.gather_decisions_into(out.data_ptr()))
+            return st
         return timed("evaluate_cycle", lambda: eng2.evaluate_cycle_into(out.data_ptr()))   # [K0 + K1 (+ K1x beside)] K3 + K2 (replayed identically on every rank) + D2H
 
     if world > 1:
@@ -440,6 +447,7 @@ def run_engine(args):
         load_all(eng2, pt, ppk)
         attached = os.environ.get("OE_BENCH_EXCHANGE", "peer") == "peer" and sharded.attach_peers(eng2, dist, max_rows=max(64, 2 * eng2.factored_rows()))
         exchange = "peer stores from the feasibility kernel (NVLink), flags, device-side wait" if attached else "nccl all-gather"
+        merged_on_rank0 = bool(attached)
         if exchange == "nccl all-gather":
             eng2.close()
             eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
@@ -458,13 +466,16 @@ def run_engine(args):
     # what the last timed cycle decided: every rank's digest must be the same one (the reference has ONE list of offers,
     # S/scheduler/plan/PlanScheduler.java:56-67), and the same at every N
     import hashlib
+    if world > 1 and merged_on_rank0 and rank != 0:
+        eng2.gather_decisions_into(out.data_ptr())     # outside the timing: every rank's own table, for the agreement check below
     decisions = np.frombuffer(out.numpy().tobytes(), dtype=abi.DECISION_DTYPE)
     offer_rows = np.ascontiguousarray(decisions["offer_row"])
     digest = hashlib.sha256(offer_rows.tobytes()).hexdigest()
-    digests = [digest]
+    digest_all_fields = hashlib.sha256(decisions.tobytes()).hexdigest()
+    digests = [digest + digest_all_fields if merged_on_rank0 else digest]
     if dist is not None:
         digests = [None] * world
-        dist.all_gather_object(digests, digest)
+        dist.all_gather_object(digests, digests_mine := (digest + digest_all_fields if merged_on_rank0 else digest))
     if dist is not None:
         tmax = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -580,7 +591,7 @@ def run_engine(args):
     cpu = cpu_baseline_sample(t, args.cpu_seconds) if world == 1 else None
     factored = None
     if not args.no_oracle_check:
-        same_offers, same_all, factored = oracle_check_and_factored_cpu(t, offer_rows, decisions if world == 1 else None)
+        same_offers, same_all, factored = oracle_check_and_factored_cpu(t, offer_rows, decisions if (world == 1 or merged_on_rank0) else None)
         e2e["decisions_match_oracle"] = same_offers
         if same_all is not None:
             e2e["decisions_match_oracle_all_fields"] = same_all     # dynamic ports, MOUNT slots, fresh reservation ids too

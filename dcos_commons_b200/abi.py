@@ -585,11 +585,19 @@ class Handle:
         self._check(f(self.h, out.ctypes.data if out.size else None))
         return out
 
-    def evaluate_cycle_into(self, out_ptr: int):
-        """Decisions written to caller-owned host memory (e.g. a pinned buffer)."""
+    def evaluate_cycle_into(self, out_ptr):
+        """Decisions written to caller-owned host memory (e.g. a pinned buffer); None on a peer-attached shard that leaves the
+        table to oe_gather_decisions on another rank."""
         st = OeStats()
-        self._check(self.b.fn("evaluate_cycle")(self.h, out_ptr, C.byref(st)))
+        f = self.b.fn("evaluate_cycle")
+        f.argtypes = [_p, _p, C.POINTER(OeStats)]
+        self._check(f(self.h, out_ptr, C.byref(st)))
         return st.as_dict()
+
+    def gather_decisions_into(self, out_ptr):
+        f = self.b.fn("gather_decisions")
+        f.argtypes = [_p, _p]
+        self._check(f(self.h, out_ptr))
 
     def stage_failures(self, j0=0, j1=None):
         """[j1 - j0, n_local_offers] uint64 failed-stage masks (oe_stage_failures)."""

@@ -47,6 +47,13 @@ def main():
         assert got[mine].tobytes() == exp[mine].tobytes()
         if want is not None:
             assert np.array_equal(got["offer_row"], want["offer_row"]), f"pass {k}: engine and oracle disagree"
+        # the merged table (every shard's winners, all fields): asked for on ranks 0 and world - 1 only, the others skip the copy
+        if rank in (0, world - 1):
+            merged = eng.gather_decisions()
+            assert np.array_equal(merged["offer_row"], exp["offer_row"])
+            assert (merged["n_new_reservations"][merged["offer_row"] >= 0] > 0).all(), "a winner of another shard was not filled in"
+            if want is not None:
+                assert merged.tobytes() == want.tobytes(), f"pass {k}: merged decisions differ from the oracle's"
         # every rank reached the same decisions
         mineT = torch.from_numpy(got["offer_row"].astype(np.int32)).cuda()
         allT = [torch.empty_like(mineT) for _ in range(world)]
