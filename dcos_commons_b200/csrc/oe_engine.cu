@@ -97,6 +97,82 @@ __global__ void k_expand_tuples(uint32_t* __restrict__ port, int32_t* __restrict
   for (int r = 0; r < R; ++r) port[(s * R + r) * N + i] = t >= 0 ? __ldg(tuples + t * R + r) : OE_PORT_EMPTY;
 }
 
+struct OfferLimits { int32_t n_agents, n_hostnames, n_zones, n_regions, n_attrs, n_rr_values; };
+// oe_load_offers_packed, one launch per landed chunk: everything that came narrow is widened into the device columns, the
+// columns that did not travel are filled in (hostname = agent, one allocation role), the `ports` column is rebuilt from the
+// distinct range lists, and the rows are checked like k_validate_offer_rows checks them (same codes; 20 = list id out of range).
+struct WireCols {
+  const void *scalar, *present, *mprof, *zone, *region, *attr, *rr, *exec, *tuple_id;   // staging (null: the column arrived at full width, in place)
+  uint8_t present_b, mprof_b, zone_b, region_b, attr_b, rr_b, exec_b, tuple_b;          // bytes per element of each staged column
+  uint8_t host_is_agent, alloc_is_const;
+  int32_t alloc_const;
+  const uint32_t* tuples;
+  int32_t n_tuples;
+};
+struct OfferDst {
+  double* scalar; uint32_t* present; uint32_t* port; int32_t *mprof, *alloc, *host, *zone, *region, *attr, *rr, *exec, *ptuple;
+};
+__device__ __forceinline__ int32_t wire_id(const void* col, int bytes, int64_t idx) {
+  if (bytes == 1) { const uint8_t v = static_cast<const uint8_t*>(col)[idx]; return v == 0xffu ? -1 : (int32_t)v; }
+  if (bytes == 2) { const uint16_t v = static_cast<const uint16_t*>(col)[idx]; return v == 0xffffu ? -1 : (int32_t)v; }
+  return static_cast<const int32_t*>(col)[idx];
+}
+__global__ void __launch_bounds__(256) k_unpack_offer_rows(WireCols w, OfferDst d, oe::DevOffers o, OfferLimits lim, int64_t r0, int64_t r1, int* err) {
+  const int64_t i = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= r1) return;
+  const int64_t N = o.N;
+  int code = 0;
+  auto chk = [&](int32_t v, int32_t lo, int32_t hi, int c) { if (v < lo || v >= hi) code = max(code, c); };
+  if (w.scalar) for (int q = 0; q < o.S * o.K; ++q) d.scalar[q * N + i] = (double)static_cast<const float*>(w.scalar)[q * N + i];
+  if (w.present) d.present[i] = w.present_b == 1 ? (uint32_t)static_cast<const uint8_t*>(w.present)[i] : (uint32_t)static_cast<const uint16_t*>(w.present)[i];
+  const int32_t agent = o.agent[i];
+  chk(agent, 0, max(lim.n_agents, 1), 11);
+  const int32_t host = w.host_is_agent ? agent : o.host[i];
+  if (w.host_is_agent) d.host[i] = host;
+  chk(host, 0, max(lim.n_hostnames, 1), 12);
+  if (w.alloc_is_const) d.alloc[i] = w.alloc_const;
+  const int32_t zone = w.zone ? wire_id(w.zone, w.zone_b, i) : o.zone[i];
+  if (w.zone) d.zone[i] = zone;
+  chk(zone, -1, lim.n_zones, 13);
+  const int32_t region = w.region ? wire_id(w.region, w.region_b, i) : o.region[i];
+  if (w.region) d.region[i] = region;
+  chk(region, -1, lim.n_regions, 14);
+  for (int a = 0; a < o.A; ++a) {
+    const int32_t v = w.attr ? wire_id(w.attr, w.attr_b, a * N + i) : o.attr[a * N + i];
+    if (w.attr) d.attr[a * N + i] = v;
+    chk(v, -1, lim.n_attrs, 15);
+  }
+  for (int q = 0; q < o.Q; ++q) {
+    const int32_t v = w.rr ? wire_id(w.rr, w.rr_b, q * N + i) : o.rr[q * N + i];
+    if (w.rr) d.rr[q * N + i] = v;
+    chk(v, -1, lim.n_rr_values, 16);
+  }
+  for (int e = 0; e < o.E; ++e) if (w.exec) d.exec[e * N + i] = wire_id(w.exec, w.exec_b, e * N + i);
+  for (int q = 0; q < o.D; ++q) {
+    const int32_t v = w.mprof ? wire_id(w.mprof, w.mprof_b, q * N + i) : o.mprof[q * N + i];
+    if (w.mprof) d.mprof[q * N + i] = v;
+    chk(v, -1, OE_MAX_PROFILES, 17);
+  }
+  for (int s = 0; s < o.S; ++s) {
+    if (w.tuple_id) {
+      int64_t t = w.tuple_b == 2 ? (int64_t)static_cast<const uint16_t*>(w.tuple_id)[s * N + i] : (int64_t)static_cast<const uint32_t*>(w.tuple_id)[s * N + i];
+      if (t >= w.n_tuples) { code = max(code, 20); t = -1; }
+      d.ptuple[s * N + i] = (int32_t)t;
+      for (int r = 0; r < o.R; ++r) d.port[(s * o.R + r) * N + i] = t >= 0 ? __ldg(w.tuples + t * o.R + r) : OE_PORT_EMPTY;   // the lists were checked by k_validate_tuples
+    } else {
+      int prev_e = -1;
+      for (int r = 0; r < o.R; ++r) {
+        const uint32_t pr = o.port[((int64_t)s * o.R + r) * N + i];
+        const int b = pr & 0xFFFF, e = pr >> 16;
+        if (b > e) continue;
+        if (b <= prev_e) code = max(code, 18);
+        prev_e = e;
+      }
+    }
+  }
+  if (code) atomicMax(err, code);
+}
+
 // the same check for range lists stored list-major ([n][R]: oe_offer_packing.port_tuples)
 __global__ void k_validate_tuples(const uint32_t* __restrict__ tuples, int n, int R, int code, int* err) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -128,7 +204,6 @@ __global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, 
 
 // The same checks for the rows [r0, r1) of a freshly copied offer chunk, in one launch (OE_CFG_ASYNC_LOADS: the table arrives
 // in row chunks and every chunk is checked as soon as it has landed).  Same codes as the per-column checks.
-struct OfferLimits { int32_t n_agents, n_hostnames, n_zones, n_regions, n_attrs, n_rr_values; };
 __global__ void k_validate_offer_rows(oe::DevOffers o, OfferLimits lim, int64_t r0, int64_t r1, int* err) {
   const int64_t i = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= r1) return;
@@ -1980,6 +2055,8 @@ struct oe_engine {
   bool validation_pending = false;
   bool self_provided = false;
   std::vector<uint32_t> h_launch_filter;
+  const int32_t *pending_launch_begin = nullptr, *pending_launch_name = nullptr;   // OE_CFG_ASYNC_LOADS: launch rows still in the caller's memory
+  const uint32_t* pending_launch_filter = nullptr;
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
   // Re-deployed requirements whose rule verdicts over (zone, region) are identical share one bit row: V_eff rows behind the
   // classes instead of V (-1 = not merged: every such requirement has a row of its own).  row_map[bit row] = factored row it is
@@ -2927,36 +3004,21 @@ int32_t oe_load_offers_packed(oe_engine* h, const oe_offer_table* t, const oe_of
       if (int rc = copy_rows(h, h->d_msize.p, t->mount_size, 8, o.D, N, r0, r1, ls)) return rc;
       if (int rc = copy_rows(h, h->d_ocols[1].p, t->agent_id, 4, 1, N, r0, r1, ls)) return rc;
       if (!tuples) if (int rc = copy_rows(h, h->d_port.p, t->port_range, 4, o.S * o.R, N, r0, r1, ls)) return rc;
-      if (pk->hostname_is_agent) CU(cudaMemcpyAsync(h->d_ocols[2].as<int32_t>() + r0, h->d_ocols[1].as<int32_t>() + r0, (size_t)(r1 - r0) * 4, cudaMemcpyDeviceToDevice, ls));
-      else if (int rc = copy_rows(h, h->d_ocols[2].p, t->hostname_id, 4, 1, N, r0, r1, ls)) return rc;
-      if (pk->alloc_role_is_const) k_fill_i32<<<blocks(r1 - r0), 256, 0, ls>>>(h->d_ocols[0].as<int32_t>(), pk->alloc_role_const, r0, r1);
-      else if (int rc = copy_rows(h, h->d_ocols[0].p, t->alloc_role, 4, 1, N, r0, r1, ls)) return rc;
-      // widen what came narrow
-      if (w[W_SCALAR].stage) k_widen_f32<<<blocks((r1 - r0) * w[W_SCALAR].slots), 256, 0, ls>>>(h->d_scalar.as<double>(), static_cast<const float*>(w[W_SCALAR].stage), w[W_SCALAR].slots, N, r0, r1);
-      auto widen = [&](int q, bool absent) {
-        if (!w[q].stage || w[q].slots <= 0) return;
-        int32_t* dst = static_cast<int32_t*>(w[q].dev);
-        const unsigned g = blocks((r1 - r0) * w[q].slots);
-        if (w[q].wire_bytes == 1) {
-          if (absent) k_widen_ids<uint8_t, true><<<g, 256, 0, ls>>>(dst, static_cast<const uint8_t*>(w[q].stage), w[q].slots, N, r0, r1);
-          else k_widen_ids<uint8_t, false><<<g, 256, 0, ls>>>(dst, static_cast<const uint8_t*>(w[q].stage), w[q].slots, N, r0, r1);
-        } else {
-          if (absent) k_widen_ids<uint16_t, true><<<g, 256, 0, ls>>>(dst, static_cast<const uint16_t*>(w[q].stage), w[q].slots, N, r0, r1);
-          else k_widen_ids<uint16_t, false><<<g, 256, 0, ls>>>(dst, static_cast<const uint16_t*>(w[q].stage), w[q].slots, N, r0, r1);
-        }
-      };
-      widen(W_PRESENT, false);
-      widen(W_MPROF, true); widen(W_ZONE, true); widen(W_REGION, true); widen(W_ATTR, true); widen(W_RR, true); widen(W_EXEC, true);
-      if (tuples) {
-        const unsigned g = blocks((r1 - r0) * o.S);
-        if (pk->port_tuple_bytes == 2)
-          k_expand_tuples<uint16_t><<<g, 256, 0, ls>>>(h->d_port.as<uint32_t>(), h->d_ptuple_id.as<int32_t>(), static_cast<const uint16_t*>(w[W_TUPLE].stage), h->d_ptuples.as<uint32_t>(),
-                                                       pk->n_port_tuples, o.S, o.R, N, r0, r1, h->d_offer_err.as<int>() + c);
-        else
-          k_expand_tuples<uint32_t><<<g, 256, 0, ls>>>(h->d_port.as<uint32_t>(), h->d_ptuple_id.as<int32_t>(), static_cast<const uint32_t*>(w[W_TUPLE].stage), h->d_ptuples.as<uint32_t>(),
-                                                       pk->n_port_tuples, o.S, o.R, N, r0, r1, h->d_offer_err.as<int>() + c);
-      }
-      k_validate_offer_rows<<<blocks(r1 - r0), 256, 0, ls>>>(o, lim, r0, r1, h->d_offer_err.as<int>() + c);
+      if (!pk->hostname_is_agent) if (int rc = copy_rows(h, h->d_ocols[2].p, t->hostname_id, 4, 1, N, r0, r1, ls)) return rc;
+      if (!pk->alloc_role_is_const) if (int rc = copy_rows(h, h->d_ocols[0].p, t->alloc_role, 4, 1, N, r0, r1, ls)) return rc;
+      WireCols wc{};
+      wc.scalar = w[W_SCALAR].stage; wc.present = w[W_PRESENT].stage; wc.mprof = w[W_MPROF].slots > 0 ? w[W_MPROF].stage : nullptr;
+      wc.zone = w[W_ZONE].stage; wc.region = w[W_REGION].stage; wc.attr = w[W_ATTR].slots > 0 ? w[W_ATTR].stage : nullptr;
+      wc.rr = w[W_RR].slots > 0 ? w[W_RR].stage : nullptr; wc.exec = w[W_EXEC].slots > 0 ? w[W_EXEC].stage : nullptr;
+      wc.tuple_id = tuples ? w[W_TUPLE].stage : nullptr;
+      wc.present_b = pk->present_bytes; wc.mprof_b = pk->mount_profile_bytes; wc.zone_b = pk->zone_bytes; wc.region_b = pk->region_bytes;
+      wc.attr_b = pk->attr_bytes; wc.rr_b = pk->rr_bytes; wc.exec_b = pk->exec_bytes; wc.tuple_b = pk->port_tuple_bytes;
+      wc.host_is_agent = pk->hostname_is_agent; wc.alloc_is_const = pk->alloc_role_is_const; wc.alloc_const = pk->alloc_role_const;
+      wc.tuples = h->d_ptuples.as<uint32_t>(); wc.n_tuples = pk->n_port_tuples;
+      OfferDst od{h->d_scalar.as<double>(), h->d_present.as<uint32_t>(), h->d_port.as<uint32_t>(), h->d_mprof.as<int32_t>(), h->d_ocols[0].as<int32_t>(),
+                  h->d_ocols[2].as<int32_t>(), h->d_ocols[3].as<int32_t>(), h->d_ocols[4].as<int32_t>(), h->d_oattr.as<int32_t>(), h->d_orr.as<int32_t>(),
+                  h->d_oexec.as<int32_t>(), h->d_ptuple_id.as<int32_t>()};
+      k_unpack_offer_rows<<<blocks(r1 - r0), 256, 0, ls>>>(wc, od, o, lim, r0, r1, h->d_offer_err.as<int>() + c);
       CU(cudaGetLastError());
     }
     CU(cudaMemcpyAsync(h->h_offer_err + c, h->d_offer_err.as<int>() + c, sizeof(int), cudaMemcpyDeviceToHost, ls));
@@ -3181,6 +3243,23 @@ int rebuild_variants(oe_engine* h) {
 }
 }  // namespace
 
+namespace {
+// The tasks a launch of each requirement's pod stores (oe_req_table.launch_*), kept on the host for oe_apply_launches.
+int keep_launch_rows(oe_engine* h, const int32_t* begin, const int32_t* name, const uint32_t* filter) {
+  const int64_t M = h->M;
+  if (begin[0] != 0) return h->fail(OE_ERR_INVALID, "launch_begin[0] != 0");
+  bool monotone = true;
+  for (int64_t j = 0; j < M; ++j) monotone &= begin[j + 1] >= begin[j];
+  if (!monotone) return h->fail(OE_ERR_INVALID, "launch_begin not monotone");
+  const size_t nl = (size_t)begin[M];
+  if (nl && (!name || (h->dt.FW && !filter))) return h->fail(OE_ERR_INVALID, "launch rows missing");
+  h->h_launch_begin.assign(begin, begin + M + 1);
+  h->h_launch_name.assign(name, name + nl);
+  h->h_launch_filter.assign(filter, filter + nl * h->dt.FW);
+  return 0;
+}
+}  // namespace
+
 int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   if (!h || !t) return OE_ERR_INVALID;
   if (!h->hasP || !h->hasT) return h->fail(OE_ERR_STATE, "oe_load_requirements: load programs and tasks first");
@@ -3230,14 +3309,15 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   CU(h->d_dec.ensure(std::max<size_t>((size_t)M, 1) * sizeof(oe_decision)));
 
   h->h_launch_begin.clear(); h->h_launch_name.clear(); h->h_launch_filter.clear();
+  h->pending_launch_begin = nullptr;
   if (t->launch_begin) {
-    if (t->launch_begin[0] != 0) return h->fail(OE_ERR_INVALID, "launch_begin[0] != 0");
-    for (int64_t j = 0; j < M; ++j) if (t->launch_begin[j + 1] < t->launch_begin[j]) return h->fail(OE_ERR_INVALID, "launch_begin not monotone");
-    const size_t nl = (size_t)t->launch_begin[M];
-    if (nl && (!t->launch_name_id || (h->dt.FW && !t->launch_filter_bits))) return h->fail(OE_ERR_INVALID, "launch rows missing");
-    h->h_launch_begin.assign(t->launch_begin, t->launch_begin + M + 1);
-    h->h_launch_name.assign(t->launch_name_id, t->launch_name_id + nl);
-    h->h_launch_filter.assign(t->launch_filter_bits, t->launch_filter_bits + nl * h->dt.FW);
+    if (h->flags & OE_CFG_ASYNC_LOADS) {
+      // the caller keeps its tables until the next evaluation call returns: the launch rows (only oe_apply_launches reads them)
+      // are checked and copied inside that call, while the host waits for the device anyway
+      h->pending_launch_begin = t->launch_begin; h->pending_launch_name = t->launch_name_id; h->pending_launch_filter = t->launch_filter_bits;
+    } else if (int rc = keep_launch_rows(h, t->launch_begin, t->launch_name_id, t->launch_filter_bits)) {
+      return rc;
+    }
   }
   tr.mark("launch_rows_kept");
   if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamSynchronize(h->stream));
@@ -4219,8 +4299,14 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   int peer_err = 0;
   if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev[5], h->stream));
+  int launch_rc = 0;
+  if (h->pending_launch_begin) {   // host work that nobody waits for, done while the device finishes the cycle
+    launch_rc = keep_launch_rows(h, h->pending_launch_begin, h->pending_launch_name, h->pending_launch_filter);
+    h->pending_launch_begin = nullptr;
+  }
   CU(cudaStreamSynchronize(h->stream));
   tr.mark("synced");
+  if (launch_rc) return launch_rc;
   if (peer_err) {
     CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
     h->class_bits_fresh = false;
