@@ -430,12 +430,13 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
   const int tab_idx = (regs.ok.region + 1) * a.tab.zdim + (regs.ok.zone + 1);
   const int tab_bit = tab_idx & 31;
   const uint32_t* tab_col = a.tab.bits + (tab_idx >> 5);
+  const uint32_t* tab_run = tab_col + (int64_t)r0 * a.tab.words;   // the row's table word when bit rows are factored rows (no row_map)
   const FastRow* frp = s_fast;
-  for (int row = r0; row < r1; ++row, ++frp, out += a.stride) {
+  for (int row = r0; row < r1; ++row, ++frp, out += a.stride, tab_run += a.tab.words) {
     const FastRow& fr = *frp;
     const int frow = a.row_map ? __ldg(a.row_map + row) : row;   // warp-uniform
     const int var = frow < cx.p.C ? -1 : frow - cx.p.C;
-    const uint32_t* tab_word = tab_col + (int64_t)frow * a.tab.words;
+    const uint32_t* tab_word = a.row_map ? tab_col + (int64_t)frow * a.tab.words : tab_run;
     bool pass = false;
     if (fr.flags & OE_FR_FAST) {
       if (valid) pass = eval_fast<PORTS, NQ>(cx, nodes, fr, sc, i, regs, var, tab_word, tab_bit, a.ptab, ptuple);
