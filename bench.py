@@ -411,7 +411,9 @@ def run_engine(args):
     ppk = abi.PackedOffers(t, lo, hi).pin() if args.wire == "packed" else None   # ... in the wire form the encoder emits
     out = torch.empty(M * abi.DECISION_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
     # the tables stay alive in pinned memory for the whole cycle, so the loads may return before their copies have landed
-    eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
+    e2e_matrix = os.environ.get("OE_BENCH_E2E_MATRIX", "1") != "0"     # 0: the timed cycle asks for the decisions only (diagnostics)
+    e2e_flags = abi.OE_CFG_ASYNC_LOADS | (abi.OE_CFG_MATERIALIZE_MATRIX if e2e_matrix else 0)
+    eng2 = Engine(device=local_rank, rank=rank, world=world, flags=e2e_flags)
 
     host_ms = {}
 
@@ -450,7 +452,7 @@ def run_engine(args):
         merged_on_rank0 = bool(attached)
         if exchange == "nccl all-gather":
             eng2.close()
-            eng2 = Engine(device=local_rank, rank=rank, world=world, flags=abi.OE_CFG_MATERIALIZE_MATRIX | abi.OE_CFG_ASYNC_LOADS)
+            eng2 = Engine(device=local_rank, rank=rank, world=world, flags=e2e_flags)
 
     cyc_stats = None
     for _ in range(max(1, min(args.warmup, 3))):
@@ -488,7 +490,7 @@ def run_engine(args):
            "cycle_latency_ms": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
            "device_ms": {k: cyc_stats[k] for k in ("ms_counters", "ms_feasibility", "ms_expand", "ms_commit", "ms_d2h")},
            "host_ms_per_call": {k: v / e2e_steps for k, v in host_ms.items()}, "placed": cyc_stats["n_placed"],
-           "decisions_sha256": digest, "ranks_agree": len(set(digests)) == 1}
+           "decisions_sha256": digest, "ranks_agree": len(set(digests)) == 1, "matrix_written": e2e_matrix}
     if len(set(digests)) != 1:
         raise SystemExit(f"bench: the ranks disagree on the placement decisions: {digests}")
     if exchange:

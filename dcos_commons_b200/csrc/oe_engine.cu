@@ -2462,6 +2462,11 @@ int64_t oe_matrix_stride_words(const oe_engine* h) { return h ? h->stride() : 0;
 int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   if (!h || !t) return OE_ERR_INVALID;
   CU(cudaSetDevice(h->device));
+  // A resident offer table survives a re-load of the programs when its ids stay valid (no dictionary it indexes shrank) and the
+  // new stage ops fit its shape (checked below): between two cycles the classes change with the plan, the offers mostly do not
+  // (oe_update_offers).  Tasks and requirements carry filter bits / class ids of the old programs and are always re-loaded.
+  const bool had_offers = h->hasO;
+  const oe_dict_sizes old_dict = h->dict;
   h->hasP = h->hasT = h->hasO = h->hasR = false;
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
   const int C = t->n_classes;
@@ -2619,6 +2624,19 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   p.cs_off = h->d_cs_off.as<int64_t>(); p.ts_type = h->d_ts_type.as<int32_t>(); p.mbits = h->d_mbits.as<uint32_t>();
   if (!(h->flags & OE_CFG_ASYNC_LOADS)) CU(cudaStreamSynchronize(h->stream));  // the caller may free its buffers after return
   h->hasP = true;
+  if (had_offers && d.n_agents >= old_dict.n_agents && d.n_hostnames >= old_dict.n_hostnames && d.n_zones >= old_dict.n_zones && d.n_regions >= old_dict.n_regions &&
+      d.n_attrs >= old_dict.n_attrs && d.n_rr_values >= old_dict.n_rr_values && d.n_exec_ids >= old_dict.n_exec_ids && d.n_res_ids >= old_dict.n_res_ids) {
+    bool fits = true;
+    const DevOffers& o = h->dof;
+    for (auto& op : h->h_ops) {
+      const bool scalar_like = op.opcode == OE_OP_SCALAR_NEW || op.opcode == OE_OP_SCALAR_RESERVED || op.opcode == OE_OP_FREE;
+      const bool slotted = scalar_like || op.opcode == OE_OP_PORT_STATIC || op.opcode == OE_OP_PORT_DYNAMIC || op.opcode == OE_OP_PORT_RESERVED;
+      const bool free_other = op.opcode == OE_OP_FREE && (op.kind == OE_KIND_PORTS || op.kind == OE_KIND_MOUNT);
+      fits = fits && !(slotted && op.slot >= o.S) && !(scalar_like && !free_other && op.kind >= o.K);
+    }
+    for (auto& cs : h->h_csets) fits = fits && !(cs.keyspace == OE_KS_RR_ATTR && cs.rr_col >= o.Q);
+    h->hasO = fits;   // otherwise: oe_load_offers again, as after any program load before
+  }
   return OE_OK;
 }
 

@@ -97,6 +97,13 @@ class Dictionary {
   std::vector<std::string> values_;
 };
 
+// The dictionaries an encoded offer row refers to.  One CycleEncoder owns a fresh set; an adapter that keeps the offer table on
+// the device from cycle to cycle (ResidentOffers below) owns one set for as long as the table lives: ids handed out once stay
+// valid, dictionaries only grow, and the engine keeps the resident table across program re-loads on exactly that condition.
+struct OfferDictionaries {
+  Dictionary agents, hosts, zones, regions, attrs, rrValues, rrAttrs, execs, roles, slots, kinds, resids, profiles;
+};
+
 // Host-side shadow of one OfferEvaluationStage of a class, index-aligned with the class's oe_stage_op list.  It is what
 // the adapter needs to turn the engine's decision for the WINNING offer back into recommendations.
 struct StageInfo {
@@ -152,6 +159,12 @@ struct EncodedCycle {
   std::vector<uint32_t> o_present, o_port;
   std::vector<int32_t> o_mprof, o_alloc, o_agent, o_host, o_zone, o_region, o_attr, o_rr, o_exec, o_rid, o_rkind;
   std::vector<int64_t> o_rbegin;
+  // Resident offer table (ResidentOffers): when `resident` is set the o_* columns above hold only the rows in `delta_rows` (row k
+  // of the columns = resident row delta_rows[k]) unless `full_reload` says the whole table is in them; N_resident = rows of the
+  // table on the device.
+  bool resident = false, full_reload = true;
+  std::vector<int64_t> delta_rows;
+  int64_t N_resident = 0;
   // requirements
   std::vector<int32_t> r_class, r_type, r_index, l_begin{0}, l_name;
   std::vector<uint32_t> l_filter;
@@ -217,13 +230,46 @@ struct EncoderRequirement {
 
 class CycleEncoder : private RuleDictionary, private RuleEmitter {
  public:
-  explicit CycleEncoder(SchedulerConfig cfg = SchedulerConfig()) : cfg_(cfg) {}
+  // `persistent`: dictionaries that outlive this cycle (ResidentOffers); null = the encoder's own, fresh ones
+  explicit CycleEncoder(SchedulerConfig cfg = SchedulerConfig(), OfferDictionaries* persistent = nullptr)
+      : cfg_(cfg), od_(persistent ? *persistent : ownDicts_), agents_(od_.agents), hosts_(od_.hosts), zones_(od_.zones), regions_(od_.regions), attrs_(od_.attrs),
+        rrValues_(od_.rrValues), rrAttrs_(od_.rrAttrs), execs_(od_.execs), roles_(od_.roles), slots_(od_.slots), kinds_(od_.kinds), resids_(od_.resids),
+        profiles_(od_.profiles) {}
 
   // `taskServices`: empty, or one service name per task (the state store the task came from)
+  // The rows of a resident offer table as ResidentOffers hands them over: `slots` in row order (null = withdrawn offer), `dirty` =
+  // the rows whose offer changed since the table was last sent, `shape` = {S, K, R, D, A, E, Q, has side table} of the table on the
+  // device (all -1: nothing loaded yet).
+  struct ResidentRows {
+    const std::vector<const mesos::Offer*>* slots = nullptr;
+    const std::vector<int64_t>* dirty = nullptr;
+    int shape[8] = {-1, -1, -1, -1, -1, -1, -1, 0};
+  };
+
   EncodedCycle encode(const std::vector<mesos::Offer>& offers, const std::vector<mesos::TaskInfo>& tasks,
                       const std::vector<EncoderRequirement>& reqs, const std::vector<std::string>& taskServices = {}) {
+    std::vector<const mesos::Offer*> rows;
+    rows.reserve(offers.size());
+    for (auto& o : offers) rows.push_back(&o);
+    return encodeRows(rows, nullptr, tasks, reqs, taskServices);
+  }
+  // The same cycle over a resident offer table: only the dirty rows are encoded (and later sent) when the table on the device
+  // still has room for them; otherwise every row is, and EncodedCycle::full_reload says so.
+  EncodedCycle encodeResident(const ResidentRows& resident, const std::vector<mesos::TaskInfo>& tasks, const std::vector<EncoderRequirement>& reqs,
+                              const std::vector<std::string>& taskServices = {}) {
+    return encodeRows(*resident.slots, &resident, tasks, reqs, taskServices);
+  }
+
+ private:
+  EncodedCycle encodeRows(const std::vector<const mesos::Offer*>& allRows, const ResidentRows* resident, const std::vector<mesos::TaskInfo>& tasks,
+                          const std::vector<EncoderRequirement>& reqs, const std::vector<std::string>& taskServices) {
     if (used_) throw std::logic_error("CycleEncoder: one encoder per cycle");
     used_ = true;
+    // the offers whose strings this cycle has to look at: all of them, or — resident table — the ones that changed
+    const bool tableLoaded = resident && resident->shape[0] >= 0;
+    std::vector<const mesos::Offer*> offers;
+    if (tableLoaded) { for (int64_t r : *resident->dirty) if (allRows[(size_t)r]) offers.push_back(allRows[(size_t)r]); }
+    else for (auto* o : allRows) if (o) offers.push_back(o);
     if (!taskServices.empty() && taskServices.size() != tasks.size()) throw std::logic_error("CycleEncoder: one service name per task");
     auto serviceOf = [&](size_t t) -> const std::string& { static const std::string none; return taskServices.empty() ? none : taskServices[t]; };
     roles_.intern(ANY_ROLE);  // role slot 0
@@ -231,7 +277,8 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     for (const char* k : {"cpus", "mem", "disk", "gpus"}) kinds_.intern(k);
 
     // ---- pass 1: dictionaries
-    for (auto& o : offers) {
+    for (auto* op : offers) {
+      const mesos::Offer& o = *op;
       agents_.intern(o.slave_id);
       hosts_.intern(o.hostname);
       if (o.domain) { zones_.intern(o.domain->zone); regions_.intern(o.domain->region); }
@@ -283,7 +330,9 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     if (profiles_.size() > OE_MAX_PROFILES) throw InvalidRequirementException("more volume profiles than OE_MAX_PROFILES");
     if (rrAttrs_.size() > OE_MAX_RR_COLS) throw InvalidRequirementException("more round-robin attribute names than OE_MAX_RR_COLS");
     // round-robin value dictionary: the values of the named attributes, on offers and in task labels
-    for (auto& o : offers) for (auto& a : o.attributes) if (rrColumn(a.name) >= 0) rrValues_.intern(AttributeStringUtils::toString(a.value));
+    // (a round-robin attribute name that is new this cycle adds a column to the table: every row is looked at again, and re-sent)
+    if (tableLoaded && rrAttrs_.size() != resident->shape[6]) { offers.clear(); for (auto* x : allRows) if (x) offers.push_back(x); }
+    for (auto* o : offers) for (auto& a : o->attributes) if (rrColumn(a.name) >= 0) rrValues_.intern(AttributeStringUtils::toString(a.value));
     for (auto& t : tasks)
       if (auto v = label(t, labels::OFFER_ATTRIBUTES))
         for (auto& a : AttributeStringUtils::toStringList(*v)) {
@@ -291,7 +340,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
           if (k != std::string::npos && rrColumn(a.substr(0, k)) >= 0) rrValues_.intern(a.substr(k + 1));
         }
 
-    encodeOffers(offers);
+    encodeOffers(allRows, resident);
     encodeTasks(tasks, taskServices);
 
     // ---- programs and requirements
@@ -345,6 +394,7 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     return std::move(out_);
   }
 
+ public:
   const Dictionary& hostnames() const { return hosts_; }
   const Dictionary& resourceIds() const { return resids_; }
 
@@ -367,69 +417,116 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   }
 
   // ---- offers -------------------------------------------------------------------------------------------------------
-  void encodeOffers(const std::vector<mesos::Offer>& offers) {
+  // One offer, reduced to what its table row holds — `new MesosResourcePool(offer, role)` (MesosResourcePool.java:53-147) plus the
+  // placement getters — before the table's slot counts are known.
+  struct OfferRow {
+    std::vector<double> scalar;                       // [S * K]
+    uint32_t present = 0;
+    std::vector<IntervalSet> ports;                   // [S]
+    std::vector<std::pair<double, int32_t>> mounts;   // (size, profile id)
+    int32_t alloc = -1, agent = 0, host = 0, zone = -1, region = -1;
+    std::vector<int32_t> attrs, rr, execs;
+    std::vector<int32_t> rid, rkind;                  // id-carrying resources (dynamicallyReservedPoolByResourceId)
+    std::vector<double> rval;
+  };
+  OfferRow rowOf(const mesos::Offer* ofp, int S, int K, int Q) const {
+    OfferRow row;
+    row.scalar.assign((size_t)S * K, 0.0);
+    row.ports.resize((size_t)S);
+    row.rr.assign((size_t)Q, -1);
+    if (!ofp) return row;   // a withdrawn offer: no pool entry, no port, nothing fits it
+    const mesos::Offer& of = *ofp;
+    row.agent = agents_.find(of.slave_id);
+    row.host = hosts_.find(of.hostname);
+    if (of.domain) { row.zone = zones_.find(of.domain->zone); row.region = regions_.find(of.domain->region); }
+    std::optional<std::string> alloc;
+    for (auto& r : of.resources) {
+      if (r.allocation_role) {
+        if (alloc && *alloc != *r.allocation_role)
+          throw InvalidRequirementException("offer " + of.id + " mixes allocation roles; the table carries one per offer");
+        alloc = r.allocation_role;
+      }
+      if (auto id = ResourceUtils::getResourceId(r)) {  // dynamicallyReservedPoolByResourceId (MesosResourcePool.java:119-131)
+        row.rid.push_back(resids_.find(*id));
+        if (ResourceUtils::isAtomic(r)) { row.rkind.push_back(OE_KIND_MOUNT); row.rval.push_back(r.value.scalar); }
+        else if (r.value.type == mesos::Value::RANGES) { row.rkind.push_back(OE_KIND_PORTS); row.rval.push_back(r.value.ranges.empty() ? 0.0 : (double)r.value.ranges[0].first); }
+        else { row.rkind.push_back(kinds_.find(r.name)); row.rval.push_back(r.value.scalar); }
+        continue;
+      }
+      if (ResourceUtils::isAtomic(r)) {  // unreservedAtomicPool (MesosResourcePool.java:99-117)
+        if (r.name == "disk") row.mounts.push_back({r.value.scalar, r.disk->profile ? profiles_.find(*r.disk->profile) : -1});
+        continue;
+      }
+      const int slot = slots_.find(ResourceUtils::getRole(r));  // reservableMergedPoolByRole (MesosResourcePool.java:432-455)
+      if (r.value.type == mesos::Value::SCALAR) {
+        const int q = slot * K + kinds_.find(r.name);
+        const bool had = (row.present >> q) & 1u;
+        // ValueUtils.add(zero, v) then + v2 ...: the sum runs in offer-resource order (MesosResourcePool.java:133-147)
+        row.scalar[(size_t)q] = (had ? row.scalar[(size_t)q] : 0.0) + r.value.scalar;
+        row.present |= 1u << q;
+      } else if (r.value.type == mesos::Value::RANGES && r.name == "ports") {
+        for (auto& iv : r.value.ranges) row.ports[(size_t)slot].add((int)iv.first, (int)iv.second);  // RangeUtils.java:65-67 narrows with (int)
+      }
+    }
+    if (alloc) row.alloc = roles_.find(*alloc);
+    for (auto& a : of.attributes) row.attrs.push_back(attrs_.find(AttributeStringUtils::toString(a)));
+    for (int q = 0; q < Q; ++q)
+      for (auto& a : of.attributes)
+        if (rrColumn(a.name) == q) { row.rr[(size_t)q] = rrValues_.find(AttributeStringUtils::toString(a.value)); break; }  // first match wins
+    for (auto& e : of.executor_ids) row.execs.push_back(execs_.find(e));
+    return row;
+  }
+
+  // `resident` null: the plain table of all rows.  Otherwise: the dirty rows only, in the shape of the table on the device, when
+  // they fit it; else all rows in a shape that holds everything (full_reload).
+  void encodeOffers(const std::vector<const mesos::Offer*>& allRows, const ResidentRows* resident) {
     EncodedCycle& o = out_;
-    const int64_t N = (int64_t)offers.size();
-    o.N = N;
     o.S = std::max(1, slots_.size());
     o.K = std::max(4, kinds_.size());
     o.Q = rrAttrs_.size();
-    struct Row { std::vector<IntervalSet> ports; std::vector<std::pair<double, int32_t>> mounts; };
-    std::vector<Row> rows((size_t)N);
+    o.resident = resident != nullptr;
+    o.N_resident = (int64_t)allRows.size();
+    const bool tableLoaded = resident && resident->shape[0] >= 0;
+    std::vector<OfferRow> rows;
+    std::vector<int64_t> which;   // table row of rows[k]
     int R = 1, D = 0, A = 1, E = 0;
-    for (int64_t i = 0; i < N; ++i) {
-      rows[(size_t)i].ports.resize((size_t)o.S);
-      A = std::max<int>(A, (int)offers[(size_t)i].attributes.size());
-      E = std::max<int>(E, (int)offers[(size_t)i].executor_ids.size());
+    bool side = false;
+    auto take = [&](int64_t r) {
+      rows.push_back(rowOf(allRows[(size_t)r], o.S, o.K, o.Q));
+      which.push_back(r);
+      const OfferRow& x = rows.back();
+      for (auto& p : x.ports) R = std::max<int>(R, (int)p.iv.size());
+      D = std::max<int>(D, (int)x.mounts.size());
+      A = std::max<int>(A, (int)x.attrs.size());
+      E = std::max<int>(E, (int)x.execs.size());
+      side = side || !x.rid.empty();
+    };
+    bool delta = tableLoaded && resident->shape[0] == o.S && resident->shape[1] == o.K && resident->shape[6] == o.Q && !resident->shape[7];
+    if (delta) {
+      for (int64_t r : *resident->dirty) take(r);
+      // a changed offer with more port ranges / MOUNT disks / attributes / executor ids than the table has slots for, or with
+      // reserved resources (oe_update_offers cannot patch the reserved side table): everything is sent again
+      delta = R <= resident->shape[2] && D <= resident->shape[3] && A <= resident->shape[4] && E <= resident->shape[5] && !side;
+      if (delta) { R = resident->shape[2]; D = resident->shape[3]; A = resident->shape[4]; E = resident->shape[5]; }
+    }
+    if (!delta) {
+      rows.clear(); which.clear();
+      R = tableLoaded ? std::max(1, resident->shape[2]) : 1; D = tableLoaded ? resident->shape[3] : 0;
+      A = tableLoaded ? std::max(1, resident->shape[4]) : 1; E = tableLoaded ? resident->shape[5] : 0;
+      for (int64_t r = 0; r < (int64_t)allRows.size(); ++r) take(r);
     }
     if (A > OE_MAX_ATTR_SLOTS || E > OE_MAX_EXEC_SLOTS) throw InvalidRequirementException("offer exceeds the attribute / executor-id slot limits");
+    if (R > OE_MAX_PORT_RANGES || D > OE_MAX_MOUNT_SLOTS) throw InvalidRequirementException("offer exceeds the port-range / MOUNT-disk slot limits");
+    o.full_reload = !delta;
+    o.delta_rows = delta ? which : std::vector<int64_t>();
+    const int64_t N = (int64_t)rows.size();
+    o.N = N;
+    o.R = R; o.D = D; o.A = A; o.E = E;
     const size_t n = (size_t)std::max<int64_t>(N, 1);
     o.o_scalar.assign((size_t)o.S * o.K * n, 0.0);
     o.o_present.assign(n, 0u);
     o.o_alloc.assign(n, -1); o.o_agent.assign(n, 0); o.o_host.assign(n, 0); o.o_zone.assign(n, -1); o.o_region.assign(n, -1);
     o.o_rbegin.assign((size_t)N + 1, 0);
-    for (int64_t i = 0; i < N; ++i) {
-      const mesos::Offer& of = offers[(size_t)i];
-      o.o_agent[(size_t)i] = agents_.find(of.slave_id);
-      o.o_host[(size_t)i] = hosts_.find(of.hostname);
-      if (of.domain) { o.o_zone[(size_t)i] = zones_.find(of.domain->zone); o.o_region[(size_t)i] = regions_.find(of.domain->region); }
-      std::optional<std::string> alloc;
-      for (auto& r : of.resources) {
-        if (r.allocation_role) {
-          if (alloc && *alloc != *r.allocation_role)
-            throw InvalidRequirementException("offer " + of.id + " mixes allocation roles; the table carries one per offer");
-          alloc = r.allocation_role;
-        }
-        if (auto id = ResourceUtils::getResourceId(r)) {  // dynamicallyReservedPoolByResourceId (MesosResourcePool.java:119-131)
-          o.o_rid.push_back(resids_.find(*id));
-          if (ResourceUtils::isAtomic(r)) { o.o_rkind.push_back(OE_KIND_MOUNT); o.o_rval.push_back(r.value.scalar); }
-          else if (r.value.type == mesos::Value::RANGES) { o.o_rkind.push_back(OE_KIND_PORTS); o.o_rval.push_back(r.value.ranges.empty() ? 0.0 : (double)r.value.ranges[0].first); }
-          else { o.o_rkind.push_back(kinds_.find(r.name)); o.o_rval.push_back(r.value.scalar); }
-          continue;
-        }
-        if (ResourceUtils::isAtomic(r)) {  // unreservedAtomicPool (MesosResourcePool.java:99-117)
-          if (r.name == "disk") rows[(size_t)i].mounts.push_back({r.value.scalar, r.disk->profile ? profiles_.find(*r.disk->profile) : -1});
-          continue;
-        }
-        const int slot = slots_.find(ResourceUtils::getRole(r));  // reservableMergedPoolByRole (MesosResourcePool.java:432-455)
-        if (r.value.type == mesos::Value::SCALAR) {
-          const int kind = kinds_.find(r.name);
-          const size_t q = ((size_t)slot * o.K + kind) * n + (size_t)i;
-          const bool had = (o.o_present[(size_t)i] >> (slot * o.K + kind)) & 1u;
-          // ValueUtils.add(zero, v) then + v2 ...: the sum runs in offer-resource order (MesosResourcePool.java:133-147)
-          o.o_scalar[q] = (had ? o.o_scalar[q] : 0.0) + r.value.scalar;
-          o.o_present[(size_t)i] |= 1u << (slot * o.K + kind);
-        } else if (r.value.type == mesos::Value::RANGES && r.name == "ports") {
-          for (auto& iv : r.value.ranges) rows[(size_t)i].ports[(size_t)slot].add((int)iv.first, (int)iv.second);  // RangeUtils.java:65-67 narrows with (int)
-        }
-      }
-      if (alloc) o.o_alloc[(size_t)i] = roles_.find(*alloc);
-      o.o_rbegin[(size_t)i + 1] = (int64_t)o.o_rid.size();
-      for (auto& p : rows[(size_t)i].ports) R = std::max<int>(R, (int)p.iv.size());
-      D = std::max<int>(D, (int)rows[(size_t)i].mounts.size());
-    }
-    if (R > OE_MAX_PORT_RANGES || D > OE_MAX_MOUNT_SLOTS) throw InvalidRequirementException("offer exceeds the port-range / MOUNT-disk slot limits");
-    o.R = R; o.D = D; o.A = A; o.E = E;
     o.o_port.assign((size_t)o.S * R * n, OE_PORT_EMPTY);
     o.o_msize.assign((size_t)std::max(D, 1) * n, -std::numeric_limits<double>::infinity());
     o.o_mprof.assign((size_t)std::max(D, 1) * n, -1);
@@ -437,21 +534,24 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
     o.o_rr.assign((size_t)std::max(o.Q, 1) * n, -1);
     o.o_exec.assign((size_t)std::max(E, 1) * n, -1);
     for (int64_t i = 0; i < N; ++i) {
-      const mesos::Offer& of = offers[(size_t)i];
+      const OfferRow& x = rows[(size_t)i];
+      for (int q = 0; q < o.S * o.K; ++q) o.o_scalar[(size_t)q * n + (size_t)i] = x.scalar[(size_t)q];
+      o.o_present[(size_t)i] = x.present;
+      o.o_alloc[(size_t)i] = x.alloc; o.o_agent[(size_t)i] = std::max(x.agent, 0); o.o_host[(size_t)i] = std::max(x.host, 0);
+      o.o_zone[(size_t)i] = x.zone; o.o_region[(size_t)i] = x.region;
       for (int s = 0; s < o.S; ++s)
-        for (size_t r = 0; r < rows[(size_t)i].ports[(size_t)s].iv.size(); ++r) {
-          auto iv = rows[(size_t)i].ports[(size_t)s].iv[r];
+        for (size_t r = 0; r < x.ports[(size_t)s].iv.size(); ++r) {
+          auto iv = x.ports[(size_t)s].iv[r];
           o.o_port[((size_t)s * R + r) * n + (size_t)i] = OE_PORT_PACK(iv.first, iv.second);
         }
-      for (size_t d = 0; d < rows[(size_t)i].mounts.size(); ++d) {
-        o.o_msize[d * n + (size_t)i] = rows[(size_t)i].mounts[d].first;
-        o.o_mprof[d * n + (size_t)i] = rows[(size_t)i].mounts[d].second;
-      }
-      for (size_t a = 0; a < of.attributes.size(); ++a) o.o_attr[a * n + (size_t)i] = attrs_.find(AttributeStringUtils::toString(of.attributes[a]));
-      for (int q = 0; q < o.Q; ++q)
-        for (auto& a : of.attributes)
-          if (rrColumn(a.name) == q) { o.o_rr[(size_t)q * n + (size_t)i] = rrValues_.find(AttributeStringUtils::toString(a.value)); break; }  // first match wins
-      for (size_t e = 0; e < of.executor_ids.size(); ++e) o.o_exec[e * n + (size_t)i] = execs_.find(of.executor_ids[e]);
+      for (size_t d = 0; d < x.mounts.size(); ++d) { o.o_msize[d * n + (size_t)i] = x.mounts[d].first; o.o_mprof[d * n + (size_t)i] = x.mounts[d].second; }
+      for (size_t a = 0; a < x.attrs.size(); ++a) o.o_attr[a * n + (size_t)i] = x.attrs[a];
+      for (int q = 0; q < o.Q; ++q) o.o_rr[(size_t)q * n + (size_t)i] = x.rr[(size_t)q];
+      for (size_t e = 0; e < x.execs.size(); ++e) o.o_exec[e * n + (size_t)i] = x.execs[e];
+      o.o_rid.insert(o.o_rid.end(), x.rid.begin(), x.rid.end());
+      o.o_rkind.insert(o.o_rkind.end(), x.rkind.begin(), x.rkind.end());
+      o.o_rval.insert(o.o_rval.end(), x.rval.begin(), x.rval.end());
+      o.o_rbegin[(size_t)i + 1] = (int64_t)o.o_rid.size();
     }
   }
 
@@ -906,7 +1006,10 @@ class CycleEncoder : private RuleDictionary, private RuleEmitter {
   SchedulerConfig cfg_;
   EncodedCycle out_;
   bool used_ = false;
-  Dictionary agents_, hosts_, zones_, regions_, attrs_, rrValues_, rrAttrs_, types_, names_, filters_, execs_, roles_, slots_, kinds_, resids_, profiles_;
+  OfferDictionaries ownDicts_;
+  OfferDictionaries& od_;
+  Dictionary &agents_, &hosts_, &zones_, &regions_, &attrs_, &rrValues_, &rrAttrs_, &execs_, &roles_, &slots_, &kinds_, &resids_, &profiles_;
+  Dictionary types_, names_, filters_;
   std::vector<MatcherPtr> filterMatchers_;
   std::vector<std::string> filterService_;  // the service whose tasks filter f looks at
   std::string curService_;                  // the service of the requirement being declared / emitted

@@ -16,6 +16,7 @@
 #include <dlfcn.h>
 
 #include <functional>
+#include <set>
 #include <random>
 
 #include "encoder.hpp"
@@ -29,8 +30,19 @@ struct EngineError : std::runtime_error {  // surfaces as IOException in the Jav
 
 class EngineLibrary {
  public:
-  // The CUDA engine (liboe_b200.so, built from dcos_commons_b200/csrc).
-  static EngineLibrary open(const std::string& path) { return EngineLibrary(path, "oe_"); }
+  // The CUDA engine (liboe_b200.so, built from dcos_commons_b200/csrc): the entry points of include/oe_abi.h, by their own names.
+  static EngineLibrary open(const std::string& path) {
+    void* h = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!h) throw std::runtime_error(std::string("cannot load ") + path + ": " + dlerror());
+    EngineLibrary lib;
+    lib.path = path;
+    lib.bind([&](const char* name) {
+      void* s = dlsym(h, name);
+      if (!s) throw std::runtime_error(path + " does not export " + name);
+      return s;
+    });
+    return lib;
+  }
 
   int32_t (*create)(const oe_config*, oe_engine**) = nullptr;
   void (*destroy)(oe_engine*) = nullptr;
@@ -38,6 +50,7 @@ class EngineLibrary {
   int32_t (*load_programs)(oe_engine*, const oe_program_table*) = nullptr;
   int32_t (*load_tasks)(oe_engine*, const oe_task_table*) = nullptr;
   int32_t (*load_offers)(oe_engine*, const oe_offer_table*) = nullptr;
+  int32_t (*update_offers)(oe_engine*, const int64_t*, int64_t, const oe_offer_table*) = nullptr;
   int32_t (*load_requirements)(oe_engine*, const oe_req_table*) = nullptr;
   int64_t (*matrix_stride_words)(const oe_engine*) = nullptr;
   int32_t (*feasibility)(oe_engine*, uint32_t*, oe_stats*) = nullptr;
@@ -47,22 +60,18 @@ class EngineLibrary {
   std::string path;
 
  protected:
-  EngineLibrary(const std::string& p, const std::string& prefix) : path(p) {
-    void* h = dlopen(p.c_str(), RTLD_NOW | RTLD_LOCAL);
-    if (!h) throw std::runtime_error(std::string("cannot load ") + p + ": " + dlerror());
-    auto sym = [&](const char* name) {
-      void* s = dlsym(h, (prefix + name).c_str());
-      if (!s) throw std::runtime_error(p + " does not export " + prefix + name);
-      return s;
-    };
-    create = (decltype(create))sym("create"); destroy = (decltype(destroy))sym("destroy");
-    last_error = (decltype(last_error))sym("last_error");
-    load_programs = (decltype(load_programs))sym("load_programs"); load_tasks = (decltype(load_tasks))sym("load_tasks");
-    load_offers = (decltype(load_offers))sym("load_offers"); load_requirements = (decltype(load_requirements))sym("load_requirements");
-    matrix_stride_words = (decltype(matrix_stride_words))sym("matrix_stride_words");
-    feasibility = (decltype(feasibility))sym("feasibility"); evaluate_cycle = (decltype(evaluate_cycle))sym("evaluate_cycle");
-    apply_launches = (decltype(apply_launches))sym("apply_launches");
-    unexpected_resources = (decltype(unexpected_resources))sym("unexpected_resources");
+  EngineLibrary() = default;
+  // `symbol` resolves an entry point of include/oe_abi.h by its declared name ("oe_create", ...) or throws.
+  void bind(const std::function<void*(const char*)>& symbol) {
+    create = (decltype(create))symbol("oe_create"); destroy = (decltype(destroy))symbol("oe_destroy");
+    last_error = (decltype(last_error))symbol("oe_last_error");
+    load_programs = (decltype(load_programs))symbol("oe_load_programs"); load_tasks = (decltype(load_tasks))symbol("oe_load_tasks");
+    load_offers = (decltype(load_offers))symbol("oe_load_offers"); update_offers = (decltype(update_offers))symbol("oe_update_offers");
+    load_requirements = (decltype(load_requirements))symbol("oe_load_requirements");
+    matrix_stride_words = (decltype(matrix_stride_words))symbol("oe_matrix_stride_words");
+    feasibility = (decltype(feasibility))symbol("oe_feasibility"); evaluate_cycle = (decltype(evaluate_cycle))symbol("oe_evaluate_cycle");
+    apply_launches = (decltype(apply_launches))symbol("oe_apply_launches");
+    unexpected_resources = (decltype(unexpected_resources))symbol("oe_unexpected_resources");
   }
 };
 
@@ -79,13 +88,23 @@ class Engine {
   Engine(const Engine&) = delete;
   Engine& operator=(const Engine&) = delete;
 
+  // A cycle over a resident offer table (EncodedCycle::resident) sends only the rows that changed (oe_update_offers) unless the
+  // encoder had to re-encode the whole table; the programs are re-loaded either way (the engine keeps the table across that).
   void load(const EncodedCycle& c) {
     auto p = c.programTable(); check(lib_.load_programs(h_, &p), "oe_load_programs");
     auto t = c.taskTable(); check(lib_.load_tasks(h_, &t), "oe_load_tasks");
-    auto o = c.offerTable(); check(lib_.load_offers(h_, &o), "oe_load_offers");
+    auto o = c.offerTable();
+    if (c.resident && !c.full_reload) {
+      if (!c.delta_rows.empty()) check(lib_.update_offers(h_, c.delta_rows.data(), (int64_t)c.delta_rows.size(), &o), "oe_update_offers");
+      ++deltaLoads; rowsSent += (int64_t)c.delta_rows.size();
+    } else {
+      check(lib_.load_offers(h_, &o), "oe_load_offers");
+      ++fullLoads; rowsSent += c.N;
+    }
     auto r = c.reqTable(); check(lib_.load_requirements(h_, &r), "oe_load_requirements");
-    M_ = c.M; N_ = c.N;
+    M_ = c.M; N_ = c.resident ? c.N_resident : c.N;
   }
+  int64_t fullLoads = 0, deltaLoads = 0, rowsSent = 0;   // what crossed the boundary so far (tests, diagnostics)
   std::vector<oe_decision> evaluateCycle() {
     std::vector<oe_decision> d((size_t)std::max<int64_t>(M_, 1));
     oe_stats st{};
@@ -188,6 +207,52 @@ struct PlacementRuleFilter {
   }
 };
 
+// The offers a scheduler holds between cycles, kept as ONE table on the device.  The reference's queue takes what the master
+// sends and drops what it rescinds (S/framework/OfferQueue.java:46-85: offer(), remove(offerId)); every cycle the evaluator sees
+// the current list (S/framework/OfferProcessor.java:240-262) and the offers it accepted leave it (PlanScheduler.java:61-66).
+// Here an agent keeps its ROW: a new offer of an agent replaces the agent's row in place, an agent seen for the first time
+// appends a row, and an offer that was rescinded or accepted leaves an empty row behind (no pool entry, no port: nothing fits
+// it).  The list the evaluator is given is the rows in row order — list() — so first fit (OfferEvaluator.java:137) means the same
+// thing on both sides; only the rows that changed since the last cycle are encoded and sent (oe_update_offers).
+class ResidentOffers {
+ public:
+  void offer(const mesos::Offer& o) {
+    auto it = rowOfAgent_.find(o.slave_id);
+    size_t row;
+    if (it == rowOfAgent_.end()) { row = slots_.size(); slots_.emplace_back(); rowOfAgent_[o.slave_id] = row; }
+    else { row = it->second; if (slots_[row]) rowOfOffer_.erase(slots_[row]->id); }
+    slots_[row] = o;
+    rowOfOffer_[o.id] = row;
+    dirty_.insert((int64_t)row);
+  }
+  // OfferQueue.remove(offerId) — rescinded by the master — and what PlanScheduler does with an accepted offer
+  void remove(const std::string& offerId) {
+    auto it = rowOfOffer_.find(offerId);
+    if (it == rowOfOffer_.end()) return;
+    slots_[it->second].reset();
+    dirty_.insert((int64_t)it->second);
+    rowOfOffer_.erase(it);
+  }
+  // the evaluator's `offers` argument: the standing offers in row order
+  std::vector<mesos::Offer> list() const {
+    std::vector<mesos::Offer> out;
+    for (auto& s : slots_) if (s) out.push_back(*s);
+    return out;
+  }
+  size_t rows() const { return slots_.size(); }
+  const std::optional<mesos::Offer>& row(size_t r) const { return slots_[r]; }
+
+ private:
+  friend class OfferEvaluator;
+  std::vector<std::optional<mesos::Offer>> slots_;
+  std::map<std::string, size_t> rowOfAgent_, rowOfOffer_;
+  std::set<int64_t> dirty_;                 // rows whose offer changed since the table was last sent
+  OfferDictionaries dicts_;                 // ids live as long as the table
+  int shape_[8] = {-1, -1, -1, -1, -1, -1, -1, 0};
+  size_t capacity_ = 0;                     // rows of the table on the device (the offers' rows and spare ones behind them)
+  std::unique_ptr<Engine> engine_;          // the handle that holds the table
+};
+
 class OfferEvaluator {
  public:
   OfferEvaluator(const EngineLibrary& lib, StateStore& stateStore, std::string serviceName = "test-service", SchedulerConfig cfg = SchedulerConfig())
@@ -218,6 +283,47 @@ class OfferEvaluator {
         out[j] = materialise(requirements[j], offers[(size_t)dec[j].offer_row], c.classStages[(size_t)c.r_class[j]], dec[j], ers[j].existing.get());
     return out;
   }
+
+  // The same cycle over the scheduler's standing offers: result[j] names offers of `resident.list()`; accepted offers leave the
+  // table (PlanScheduler.java:61-66), as they leave the reference's list.
+  std::vector<std::vector<OfferRecommendation>> evaluateCycle(const std::vector<PodInstanceRequirement>& requirements, ResidentOffers& resident) {
+    std::vector<std::vector<OfferRecommendation>> out(requirements.size());
+    if (requirements.empty()) return out;
+    const std::vector<mesos::TaskInfo> allTasks = stateStore_.fetchTasks();
+    CycleEncoder enc(cfg_, &resident.dicts_);
+    std::vector<EncoderRequirement> ers = encoderRequirements(requirements, allTasks);
+    // the table on the device has spare (empty) rows at its end, so that an agent seen for the first time is a changed row like
+    // any other; only when they run out is the table re-sent, with an eighth more room
+    if (resident.slots_.size() > resident.capacity_) {
+      resident.capacity_ = resident.slots_.size() + std::max<size_t>(16, resident.slots_.size() / 8);
+      resident.shape_[0] = -1;
+    }
+    std::vector<const mesos::Offer*> slots;
+    for (auto& s : resident.slots_) slots.push_back(s ? &*s : nullptr);
+    slots.resize(resident.capacity_, nullptr);
+    const std::vector<int64_t> dirty(resident.dirty_.begin(), resident.dirty_.end());
+    CycleEncoder::ResidentRows rr;
+    rr.slots = &slots; rr.dirty = &dirty;
+    std::copy(resident.shape_, resident.shape_ + 8, rr.shape);
+    EncodedCycle c = enc.encodeResident(rr, allTasks, ers);
+    if (!resident.engine_) resident.engine_ = std::make_unique<Engine>(lib_);
+    resident.engine_->load(c);
+    if (c.full_reload) {
+      const int shape[8] = {c.S, c.K, c.R, c.D, c.A, c.E, c.Q, c.o_rid.empty() ? 0 : 1};
+      std::copy(shape, shape + 8, resident.shape_);
+    }
+    resident.dirty_.clear();
+    const std::vector<oe_decision> dec = resident.engine_->evaluateCycle();
+    lastDecisions_ = dec;
+    for (size_t j = 0; j < requirements.size(); ++j)
+      if (dec[j].offer_row >= 0) {
+        const mesos::Offer winner = *resident.slots_[(size_t)dec[j].offer_row];
+        out[j] = materialise(requirements[j], winner, c.classStages[(size_t)c.r_class[j]], dec[j], ers[j].existing.get());
+        resident.remove(winner.id);
+      }
+    return out;
+  }
+  const Engine* residentEngine(const ResidentOffers& r) const { return r.engine_.get(); }
 
   // The two halves of evaluateCycle, for callers that put several services' requirements into ONE engine cycle
   // (MultiServiceEventClient below).  `requirements` must outlive the returned vector.

@@ -368,8 +368,13 @@ typedef struct {
 } oe_stats;
 
 /* ------------------------------------------------------------------------------------------------------------------
- * Loading.  Order: programs, tasks, offers, requirements (each may be re-loaded between cycles; re-loading programs
- * invalidates the other three).
+ * Loading.  Order: programs, tasks, offers, requirements (each may be re-loaded between cycles).  Re-loading programs
+ * invalidates tasks and requirements.  The RESIDENT OFFER TABLE stays valid across a program re-load when every dictionary
+ * it indexes (agents, hostnames, zones, regions, attributes, round-robin values, executor ids, resource ids) is at least as
+ * large as before — ids are never re-numbered by a growing dictionary — and the new stage ops name only role slots, scalar
+ * kinds and round-robin columns the table has; otherwise the next call that needs offers fails with OE_ERR_STATE until
+ * oe_load_offers ran again.  That is what lets an adapter keep the table on the device from cycle to cycle and send only the
+ * offers that changed (oe_update_offers) although the plan, and with it the classes, changes every cycle.
  * ---------------------------------------------------------------------------------------------------------------- */
 int32_t oe_load_programs(oe_engine* h, const oe_program_table* t);
 int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t);

@@ -718,7 +718,7 @@ int32_t oeo_load_programs(Oracle* h, const oe_program_table* t) {
   P.matcher_bits = copy_col(t->matcher_bits, (size_t)t->n_matcher_words);
   P.dict = t->dict;
   h->hasP = true;
-  h->hasT = h->hasO = h->hasR = false;
+  h->hasT = h->hasR = false;   // a resident offer table survives (include/oe_abi.h, "Loading"): its ids stay valid as dictionaries grow
   return 0;
 }
 
@@ -777,6 +777,33 @@ int32_t oeo_load_offers(Oracle* h, const oe_offer_table* t) {
     O.reserved_value = copy_col(t->reserved_value, (size_t)t->n_reserved);
   }
   h->hasO = true;
+  return 0;
+}
+
+// oe_update_offers: rows of the resident table replaced in place (no reserved side table on either side, as in the engine).
+int32_t oeo_update_offers(Oracle* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* t) {
+  h->last_decisions.clear();
+  h->cache.valid = false;
+  Offers& O = h->O;
+  if (!h->hasO) return h->fail(OE_ERR_STATE, "no resident offer table");
+  if (!O.reserved_begin.empty() || t->n_reserved > 0) return h->fail(OE_ERR_STATE, "a table with a reserved side table cannot be patched in place");
+  if (t->n_offers != n_rows || t->n_role_slots != O.S || t->n_scalar_kinds != O.K || t->n_port_ranges != O.R || t->n_mount_slots != O.D ||
+      t->n_attr_slots != O.A || t->n_rr_cols != O.Q || t->n_exec_slots != O.E)
+    return h->fail(OE_ERR_INVALID, "slot counts differ from the resident table");
+  const size_t N = (size_t)O.N, n = (size_t)n_rows;
+  for (size_t k = 0; k < n; ++k) {
+    if (rows[k] < 0 || rows[k] >= O.N) return h->fail(OE_ERR_INVALID, "row outside the resident table");
+    const size_t i = (size_t)rows[k];
+    for (int q = 0; q < O.S * O.K; ++q) O.scalar[(size_t)q * N + i] = t->scalar[(size_t)q * n + k];
+    O.scalar_present[i] = t->scalar_present[k];
+    for (int q = 0; q < O.S * O.R; ++q) O.port_range[(size_t)q * N + i] = t->port_range[(size_t)q * n + k];
+    for (int q = 0; q < O.D; ++q) { O.mount_size[(size_t)q * N + i] = t->mount_size[(size_t)q * n + k]; O.mount_profile[(size_t)q * N + i] = t->mount_profile[(size_t)q * n + k]; }
+    O.alloc_role[i] = t->alloc_role[k]; O.agent_id[i] = t->agent_id[k]; O.hostname_id[i] = t->hostname_id[k];
+    O.zone_id[i] = t->zone_id[k]; O.region_id[i] = t->region_id[k];
+    for (int q = 0; q < O.A; ++q) O.attr_id[(size_t)q * N + i] = t->attr_id[(size_t)q * n + k];
+    for (int q = 0; q < O.Q; ++q) O.rr_key[(size_t)q * N + i] = t->rr_key[(size_t)q * n + k];
+    for (int q = 0; q < O.E; ++q) O.exec_id[(size_t)q * N + i] = t->exec_id[(size_t)q * n + k];
+  }
   return 0;
 }
 

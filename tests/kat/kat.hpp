@@ -14,9 +14,20 @@
 
 namespace kat {
 
-// Test-only loader: the same ABI exported under another prefix (the CPU oracle, "oeo_").  The product header offers no such door.
+// Test-only loader: the same ABI exported under another prefix (the CPU oracle's "oeo_" entry points).  The product header knows
+// nothing about prefixes; this subclass resolves the names itself.
 struct OracleLibrary : sdk::EngineLibrary {
-  OracleLibrary(const std::string& path, const std::string& prefix) : sdk::EngineLibrary(path, prefix) {}
+  OracleLibrary(const std::string& file, const std::string& prefix) {
+    void* h = dlopen(file.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!h) throw std::runtime_error(std::string("cannot load ") + file + ": " + dlerror());
+    path = file;
+    bind([&](const char* name) {
+      const std::string renamed = prefix + (std::string(name).rfind("oe_", 0) == 0 ? std::string(name).substr(3) : std::string(name));
+      void* s = dlsym(h, renamed.c_str());
+      if (!s) throw std::runtime_error(file + " does not export " + renamed);
+      return s;
+    });
+  }
 };
 
 struct Failure : std::runtime_error { using std::runtime_error::runtime_error; };
