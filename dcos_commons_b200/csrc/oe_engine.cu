@@ -465,6 +465,109 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
   }
 }
 
+// K1, lean form.  When every class is a folded new-pod pipeline whose scalar pools fit four registers, whose rule (if any) is
+// tabulated over (zone, region) and whose port stages are tabulated over the table's distinct range lists — the headline shape —
+// a (offer, bit row) pair needs no interpretation at all: four fp64 compares, one presence mask, the allocation-role test and two
+// bits that the thread fetched ONCE per tile of 32 rows (k_transpose_tables lays the two tables out as [zone-region combination
+// or range list][32 rows per word]).  ~25 instructions per pair instead of ~110.
+struct LeanRow {
+  double thr[4];
+  uint32_t need;        // pool entries that must be present; all ones = the class can never fit (a port requested twice)
+  int32_t role;         // pod role when the class consumes from the pool (offers allocated to another role fail), else -1
+  uint32_t pad[2];
+};
+static_assert(sizeof(LeanRow) == 48, "LeanRow is staged as three uint4");
+struct LeanArgs {
+  uint32_t* F;
+  int64_t stride;
+  int rows, row_words;            // bit rows; 32-row words per table entry
+  const LeanRow* lean;            // [rows]
+  const uint32_t* ruleT;          // [zone-region combinations][row_words] or null (no row has a rule)
+  const uint32_t* portT;          // [range lists][row_words] or null (no row has port stages)
+  int zdim;
+  PeerOut peers;
+  int64_t xb0;
+};
+// bit rows -> the two verdict tables transposed: thread = (table entry e, 32-row word w)
+__global__ void k_transpose_tables(DevCtx cx, const FastRow* __restrict__ fast, const int32_t* __restrict__ row_map, int rows, int row_words,
+                                   const uint32_t* __restrict__ rule_tab, int tab_words, int n_combos, uint32_t* __restrict__ ruleT,
+                                   const uint32_t* __restrict__ port_tab, int ptab_words, int n_tuples, uint32_t* __restrict__ portT, LeanRow* __restrict__ lean) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n_entries = max(n_combos, n_tuples);
+  if (q >= n_entries * row_words) return;
+  const int e = q / row_words, w = q - e * row_words;
+  uint32_t rbits = 0u, pbits = 0u;
+  for (int k = 0; k < 32; ++k) {
+    const int row = w * 32 + k;
+    if (row >= rows) break;
+    const int frow = row_map ? row_map[row] : row;
+    const int cls = frow < cx.p.C ? frow : cx.v.cls[frow - cx.p.C];
+    const FastRow& fr = fast[cls];
+    const bool rule = !(fr.flags & OE_FR_RULE_TAB) || (e < n_combos && ((rule_tab[(int64_t)frow * tab_words + (e >> 5)] >> (e & 31)) & 1u));
+    const bool port = !(fr.n_ports | fr.n_dyn) || (e < n_tuples && ((port_tab[(int64_t)cls * ptab_words + (e >> 5)] >> (e & 31)) & 1u));
+    rbits |= rule ? 1u << k : 0u;
+    pbits |= port ? 1u << k : 0u;
+    if (e == 0) {   // the row's descriptor, once
+      LeanRow lr;
+      for (int x = 0; x < 4; ++x) lr.thr[x] = fr.thr[x];
+      lr.need = (fr.flags & OE_FR_NEVER) ? 0xffffffffu : *reinterpret_cast<const uint32_t*>(fr.thr_q);
+      lr.role = (fr.flags & OE_FR_NEEDS_POOL) ? fr.pod_role : -1;
+      lr.pad[0] = lr.pad[1] = 0u;
+      lean[row] = lr;
+    }
+  }
+  if (ruleT && e < n_combos) ruleT[(int64_t)e * row_words + w] = rbits;
+  if (portT && e < n_tuples) portT[(int64_t)e * row_words + w] = pbits;
+}
+template <bool PEERS>
+__global__ void __launch_bounds__(OE_K1_THREADS, 8) k_class_feasibility_lean(DevOffers o, LeanArgs a) {
+  __shared__ __align__(16) LeanRow s_rows[32];
+  __shared__ __align__(16) uint32_t s_words[PEERS ? 32 : 1][OE_K1_THREADS / 32];
+  const int tile = blockIdx.y, r0 = tile * 32, nrows = min(32, a.rows - r0);
+  for (int q = threadIdx.x; q < nrows * 3; q += OE_K1_THREADS)
+    reinterpret_cast<uint4*>(s_rows)[q] = __ldg(reinterpret_cast<const uint4*>(a.lean + r0) + q);
+  const int64_t i = (a.xb0 + blockIdx.x) * OE_K1_THREADS + threadIdx.x;
+  const bool valid = i < o.N;
+  double sv[4] = {0.0, 0.0, 0.0, 0.0};
+  uint32_t present = 0u, both = 0u;
+  int32_t alloc = -1;
+  if (valid) {
+    const int SK = o.S * o.K;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) if (q < SK) sv[q] = __ldg(o.scalar + (int64_t)q * o.N + i);
+    present = __ldg(o.present + i);
+    alloc = __ldg(o.alloc + i);
+    both = 0xffffffffu;
+    if (a.ruleT) both &= __ldg(a.ruleT + (int64_t)((__ldg(o.region + i) + 1) * a.zdim + (__ldg(o.zone + i) + 1)) * a.row_words + tile);
+    if (a.portT) { const int32_t t = __ldg(o.ptuple + i); both &= t >= 0 ? __ldg(a.portT + (int64_t)t * a.row_words + tile) : 0u; }
+  }
+  __syncthreads();
+  const int64_t word = i >> 5;
+  const bool writer = (threadIdx.x & 31) == 0 && word < a.stride;
+  uint32_t* out = a.F + (int64_t)r0 * a.stride + word;
+#pragma unroll 4
+  for (int k = 0; k < nrows; ++k, out += a.stride) {
+    const LeanRow& r = s_rows[k];
+    bool pass = ((both >> k) & 1u) & ((present & r.need) == r.need);
+    pass &= !(sv[0] < r.thr[0]) & !(sv[1] < r.thr[1]) & !(sv[2] < r.thr[2]) & !(sv[3] < r.thr[3]);
+    pass &= !((r.role >= 0) & (alloc >= 0) & (alloc != r.role));   // consumableResource (MesosResourcePool.java:87-97)
+    const uint32_t bits = __ballot_sync(0xffffffffu, pass);
+    if (writer) {
+      *out = bits;
+      if (PEERS) s_words[k][threadIdx.x >> 5] = bits;
+    }
+  }
+  if (PEERS) {   // as in k_class_feasibility: the CTA's 16 bytes of every row into every shard's exchange region
+    __syncthreads();
+    const int64_t w0 = (a.xb0 + blockIdx.x) * (OE_K1_THREADS / 32);
+    if (w0 < a.stride)
+      for (int q = threadIdx.x; q < nrows * a.peers.n; q += OE_K1_THREADS) {
+        const int p = q / nrows, rr = q - p * nrows;
+        *reinterpret_cast<uint4*>(a.peers.base[p] + (int64_t)(r0 + rr) * a.stride + w0) = *reinterpret_cast<const uint4*>(s_words[rr]);
+      }
+  }
+}
+
 // Peer exchange, the ordering half.  After K1 (same stream) every rank raises flag[rank] = epoch in every shard's exchange
 // header with a system-scope release; before the commit path reads its exchange buffer a rank waits until all of its own
 // flags have reached the epoch.  A peer that never arrives (a crashed rank) ends the wait after timeout_ns with *err = shard + 1.
@@ -2026,8 +2129,8 @@ struct oe_engine {
   int n_rule_nodes = 0;
   int fast_K = -1, fast_S = -1;  // offer-table shape the folded class descriptors were built for (-1 = stale)
   int tab_words = 0, tab_zdim = 1, tab_rdim = 1;
-  bool any_rule_tab = false;
-  DevBuf d_fast, d_rule_tab, d_rr_used;
+  bool any_rule_tab = false, all_lean = false, any_ports = false, any_rule = false;
+  DevBuf d_fast, d_rule_tab, d_rr_used, d_lean, d_ruleT, d_portT;
   DevBuf d_op_begin, d_ops, d_nodes, d_pod_role, d_excl_begin, d_excl, d_rs_begin, d_rs, d_csets, d_cs_off, d_ts_type, d_mbits;
   DevProg dp{};
 
@@ -2419,7 +2522,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
-                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used};
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used, &h->d_lean, &h->d_ruleT, &h->d_portT};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -3532,6 +3635,15 @@ int build_fast_rows(oe_engine* h) {
   h->fast_K = K;
   h->fast_S = h->dof.S;
   h->any_rule_tab = any_tab;
+  // the lean kernel takes a table whose classes are all folded, dense, and read nothing per offer but tabulated verdicts
+  h->all_lean = h->C > 0; h->any_ports = false; h->any_rule = false;
+  for (int c = 0; c < h->C; ++c) {
+    const FastRow& fr = rows[(size_t)c];
+    const bool rule_ok = fr.rule_count == 0 || (fr.flags & OE_FR_RULE_TAB);
+    h->all_lean = h->all_lean && (fr.flags & OE_FR_FAST) && (fr.flags & OE_FR_DENSE) && rule_ok;
+    h->any_ports = h->any_ports || (fr.n_ports | fr.n_dyn);
+    h->any_rule = h->any_rule || (fr.flags & OE_FR_RULE_TAB);
+  }
   return 0;
 }
 
@@ -3670,6 +3782,25 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       a.peers.n = h->world;
       for (int p = 0; p < h->world; ++p) a.peers.base[p] = h->exch_rows(p, h->peer_epoch) + (size_t)h->rank * rows * stride;
     }
+    // the lean form (k_class_feasibility_lean): every class folded, four pool entries at most, rules tabulated, ports tabulated
+    static const bool no_lean = getenv("OE_K1_GENERAL") != nullptr;   // measurement aid: always the general kernel
+    bool lean_ok = !no_lean && h->all_lean && h->dof.S * h->dof.K <= 4 && (!h->any_ports || a.ptab.bits) && (!h->any_rule || a.tab.bits);
+    LeanArgs la{};
+    if (lean_ok) {
+      la.F = a.F; la.stride = stride; la.rows = rows; la.row_words = (rows + 31) / 32; la.zdim = h->tab_zdim; la.peers = a.peers;
+      const int n_combos = h->any_rule ? h->tab_zdim * h->tab_rdim : 0, n_tuples = h->any_ports ? h->n_port_tuples : 0;
+      CU(h->d_lean.ensure((size_t)la.row_words * 32 * sizeof(LeanRow)));
+      CU(h->d_ruleT.ensure(std::max<size_t>((size_t)n_combos * la.row_words, 1) * 4));
+      CU(h->d_portT.ensure(std::max<size_t>((size_t)n_tuples * la.row_words, 1) * 4));
+      la.lean = h->d_lean.as<LeanRow>();
+      la.ruleT = n_combos ? h->d_ruleT.as<uint32_t>() : nullptr;
+      la.portT = n_tuples ? h->d_portT.as<uint32_t>() : nullptr;
+      const int n_entries = std::max(1, std::max(n_combos, n_tuples));
+      k_transpose_tables<<<(unsigned)((n_entries * la.row_words + 127) / 128), 128, 0, h->stream>>>(
+          h->ctx(), h->d_fast.as<FastRow>(), a.row_map, rows, la.row_words, a.tab.bits, h->tab_words, n_combos, h->d_ruleT.as<uint32_t>(), a.ptab.bits,
+          a.ptab.words, n_tuples, h->d_portT.as<uint32_t>(), h->d_lean.as<LeanRow>());
+      ++*launches;
+    }
     if (expand_beside && n_chunks > 1) CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
     for (int c = 0; c < n_chunks; ++c) {
       // x-blocks of this launch: the chunk's rows; the last launch also covers the padding up to the stride
@@ -3691,6 +3822,12 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
         if (int rc = wait_offer_chunk(h, c, "oe_load_offers")) return rc;
         if (g_trace) g_trace->mark("chunk");
       }
+      if (lean_ok) {
+        la.xb0 = xb0;
+        dim3 lgrid((unsigned)xblocks, (unsigned)la.row_words);
+        if (h->peers_attached) k_class_feasibility_lean<true><<<lgrid, OE_K1_THREADS, 0, h->stream>>>(h->dof, la);
+        else k_class_feasibility_lean<false><<<lgrid, OE_K1_THREADS, 0, h->stream>>>(h->dof, la);
+      } else {
       dim3 grid((unsigned)xblocks, (unsigned)tiles);
       const bool fast_ranges = h->dof.R <= OE_FAST_RANGES;
       const bool few = h->dof.S * h->dof.K <= 4;   // the dense form then tests four pool entries, not eight
@@ -3702,6 +3839,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
         OE_K1_CASE(4, 1, false, 8) OE_K1_CASE(5, 1, false, 4) OE_K1_CASE(6, 1, true, 8) OE_K1_CASE(7, 1, true, 4)
         OE_K1_CASE(8, 2, false, 8) OE_K1_CASE(9, 2, false, 4) OE_K1_CASE(10, 2, true, 8) OE_K1_CASE(11, 2, true, 4)
 #undef OE_K1_CASE
+      }
       }
       ++*launches;
       CU(cudaGetLastError());
