@@ -493,7 +493,7 @@ __global__ void k_transpose_tables(DevCtx cx, const FastRow* __restrict__ fast, 
                                    const uint32_t* __restrict__ rule_tab, int tab_words, int n_combos, uint32_t* __restrict__ ruleT,
                                    const uint32_t* __restrict__ port_tab, int ptab_words, int n_tuples, uint32_t* __restrict__ portT, LeanRow* __restrict__ lean) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  const int n_entries = max(n_combos, n_tuples);
+  const int n_entries = max(1, max(n_combos, n_tuples));   // entry 0 also writes the rows' descriptors: it always exists
   if (q >= n_entries * row_words) return;
   const int e = q / row_words, w = q - e * row_words;
   uint32_t rbits = 0u, pbits = 0u;
