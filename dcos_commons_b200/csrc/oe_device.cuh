@@ -502,15 +502,20 @@ struct alignas(16) FastRow {
   int32_t rule_begin;
   uint16_t rule_count, cls;   // cls: the class itself (a tile's descriptors are copies, one per factored row)
   uint32_t static_mask;   // bit u: port[u] is requested statically
-  uint8_t n_thr, n_ports, n_dyn, reserved0;
+  uint8_t n_thr, n_ports, n_dyn, has_mount;
   int32_t pod_role;
+  double mount_amount;    // has_mount: the one MOUNT volume of the pod (consumeAtomic, MesosResourcePool.java:282-328) ...
+  uint64_t mount_mask;    // ... and its allowed-profile mask
 };
-static_assert(sizeof(FastRow) == 128, "FastRow is staged as eight uint4");
+#define OE_FR_U4 9        // a FastRow is staged as nine uint4
+static_assert(sizeof(FastRow) == 16 * OE_FR_U4, "FastRow staging");
 #define OE_FR_FAST 1u        // the folded form is valid for this class
 #define OE_FR_NEVER 2u       // a static port is requested twice: the second stage can never pass
 #define OE_FR_NEEDS_POOL 4u  // has scalar or port stages: an offer allocated to another role fails
 #define OE_FR_DENSE 16u      // S*K <= 8: thr[] is indexed by pool entry (-inf where the class asks nothing) and the entries
                              // that must be present are the mask in thr_q[0..3]; K1 then tests register copies
+#define OE_FR_PORTS_BY_TABLE 32u   // the port stages are only known as a verdict per distinct range list (k_port_tables): a
+                                  // range-constrained dynamic port; such a class is folded only while the table has its lists
 #define OE_FR_RULE_TAB 8u    // every leaf of the rule reads only the offer's zone / region: the rule is tabulated per
                              // (factored row, zone, region) by k_rule_tables and K1 looks the verdict up
 
@@ -658,6 +663,18 @@ __device__ __forceinline__ bool eval_fast(const DevCtx& cx, const oe_rule_node* 
     listed = __popc(member);
     statics = (member & fr.static_mask) == fr.static_mask;
     pass &= statics & (pool_ports - listed >= (int)fr.n_dyn);
+  }
+  if (fr.has_mount) {
+    // one MOUNT volume: any unreserved MOUNT disk of the offer that is large enough and whose profile the volume allows
+    // (MesosResourcePool.java:282-328; with a single such stage "the first one that fits" exists iff any fits)
+    bool any = false;
+    for (int d = 0; d < o.D; ++d) {
+      const double size = __ldg(o.msize + (int64_t)d * o.N + i);
+      const int32_t prof = __ldg(o.mprof + (int64_t)d * o.N + i);
+      const bool prof_ok = prof >= 0 ? ((fr.mount_mask >> prof) & 1ull) != 0 : fr.mount_mask == 0;
+      any |= !(__dsub_rn(fr.mount_amount, size) > 0.0) & prof_ok;
+    }
+    pass &= any;
   }
   if (fr.flags & OE_FR_RULE_TAB) {
     pass &= (bool)((__ldg(tab_word) >> tab_bit) & 1u);

@@ -363,26 +363,54 @@ __global__ void __launch_bounds__(128) k_rule_tables(DevCtx cx, const FastRow* _
   if ((threadIdx.x & 31) == 0 && (idx >> 5) < words) tab[(int64_t)row * words + (idx >> 5)] = bits;
 }
 // K0p: the port stages of every folded class over every distinct `ports` range list of the offer table (slot 0), once —
-// thread = one list, blockIdx.y = class.  K1 (PORTS == 2) then looks the verdict up instead of testing ranges per offer.
-__global__ void __launch_bounds__(128) k_port_tables(const FastRow* __restrict__ fast, const uint32_t* __restrict__ tuples, int n_tuples, int R,
+// thread = one list, blockIdx.y = class.  The stages run literally (static ports, dynamic ports with or without a range
+// constraint, the pod's excluded ports: PortEvaluationStage.java:72-155,242-298) on the list instead of on an offer; K1
+// (PORTS == 2, and the lean kernel) then looks the verdict up instead of testing ranges per offer.
+__global__ void __launch_bounds__(128) k_port_tables(DevProg p, const FastRow* __restrict__ fast, const uint32_t* __restrict__ tuples, int n_tuples, int R,
                                                      uint32_t* __restrict__ out, int words) {
   const int cls = blockIdx.y;
   const int t = blockIdx.x * 128 + threadIdx.x;
-  const FastRow fr = fast[cls];
   bool v = false;
-  if (t < n_tuples && (fr.flags & OE_FR_FAST)) {
-    uint32_t rb[OE_FAST_RANGES], rlen[OE_FAST_RANGES];
-    int pool_ports = 0;
-#pragma unroll
-    for (int q = 0; q < OE_FAST_RANGES; ++q) {
-      const uint32_t pr = q < R ? tuples[(int64_t)t * R + q] : OE_PORT_EMPTY;
-      const uint32_t b = pr & 0xFFFFu, e = pr >> 16;
-      const bool some = b <= e;
-      rb[q] = some ? b : 0x100000u;
-      rlen[q] = some ? e - b : 0u;
-      pool_ports += some ? (int)(e - b + 1) : 0;
+  if (t < n_tuples && (fast[cls].flags & OE_FR_FAST)) {
+    const uint32_t* rg = tuples + (int64_t)t * R;
+    auto offered = [&](int port) {
+      for (int r = 0; r < R; ++r) { const uint32_t pr = rg[r]; if ((int)(pr & 0xFFFF) <= port && port <= (int)(pr >> 16)) return true; }
+      return false;
+    };
+    int taken[OE_DEV_MAX_TAKEN], n_taken = 0;
+    auto is_taken = [&](int port) { for (int q = 0; q < n_taken; ++q) if (taken[q] == port) return true; return false; };
+    v = true;
+    for (int x = p.op_begin[cls]; x < p.op_begin[cls + 1] && v; ++x) {
+      const oe_stage_op op = p.ops[x];
+      if (op.opcode == OE_OP_PORT_STATIC) {
+        v = offered(op.arg) && !is_taken(op.arg);
+        if (v) taken[n_taken++] = op.arg;
+      } else if (op.opcode == OE_OP_PORT_DYNAMIC) {
+        int pick = -1;
+        for (int r = 0; r < R && pick < 0; ++r) {
+          const uint32_t pr = rg[r];
+          const int b = pr & 0xFFFF, e = pr >> 16;
+          for (int port = b; port <= e && pick < 0; ) {
+            bool blocked = is_taken(port);
+            for (int q = p.excl_begin[cls]; q < p.excl_begin[cls + 1] && !blocked; ++q) blocked = p.excl[q] == port;
+            if (blocked) { ++port; continue; }
+            if (op.arg >= 0) {   // inside the PortSpec's ranges, else on to the next of them
+              bool in = false;
+              int next = 0x7fffffff;
+              for (int q = p.rs_begin[op.arg]; q < p.rs_begin[op.arg + 1]; ++q) {
+                const int rb = p.rs[q] & 0xFFFF, re = p.rs[q] >> 16;
+                if (rb <= port && port <= re) in = true;
+                else if (rb > port && rb < next) next = rb;
+              }
+              if (!in) { port = next; continue; }
+            }
+            pick = port;
+          }
+        }
+        v = pick >= 0;
+        if (v) taken[n_taken++] = pick;
+      }
     }
-    v = fast_ports_pass(fr, rb, rlen, pool_ports);
   }
   const uint32_t bits = __ballot_sync(0xffffffffu, v);
   if ((threadIdx.x & 31) == 0 && (t >> 5) < words) out[(int64_t)cls * words + (t >> 5)] = bits;
@@ -404,10 +432,11 @@ __global__ void __launch_bounds__(OE_K1_THREADS, OE_K1_MIN_CTAS) k_class_feasibi
   {  // stage
     const uint4* src = reinterpret_cast<const uint4*>(a.fast);
     uint4* dst = reinterpret_cast<uint4*>(s_fast);
-    for (int q = threadIdx.x; q < (r1 - r0) * 8; q += OE_K1_THREADS) {
-      const int row = a.row_map ? __ldg(a.row_map + r0 + (q >> 3)) : r0 + (q >> 3);
+    for (int q = threadIdx.x; q < (r1 - r0) * OE_FR_U4; q += OE_K1_THREADS) {
+      const int lrow = q / OE_FR_U4, part = q - lrow * OE_FR_U4;
+      const int row = a.row_map ? __ldg(a.row_map + r0 + lrow) : r0 + lrow;
       const int cls = row < cx.p.C ? row : cx.v.cls[row - cx.p.C];
-      dst[q] = __ldg(src + (int64_t)cls * 8 + (q & 7));
+      dst[q] = __ldg(src + (int64_t)cls * OE_FR_U4 + part);
     }
     const uint4* nsrc = reinterpret_cast<const uint4*>(cx.p.nodes);
     uint4* ndst = reinterpret_cast<uint4*>(s_nodes);
@@ -2128,6 +2157,7 @@ struct oe_engine {
   std::vector<uint16_t> h_excl;
   int n_rule_nodes = 0;
   int fast_K = -1, fast_S = -1;  // offer-table shape the folded class descriptors were built for (-1 = stale)
+  bool fast_port_lists = false;  // ... and whether the table's distinct `ports` range lists were usable then
   int tab_words = 0, tab_zdim = 1, tab_rdim = 1;
   bool any_rule_tab = false, all_lean = false, any_ports = false, any_rule = false;
   DevBuf d_fast, d_rule_tab, d_rr_used, d_lean, d_ruleT, d_portT;
@@ -3563,15 +3593,25 @@ int build_fast_rows(oe_engine* h) {
           fr.flags |= OE_FR_NEEDS_POOL;
         } break;
         case OE_OP_PORT_STATIC:
-          if (op.slot != 0 || (dyn_seen && !excluded(op.arg))) { ok = false; break; }
+          if (op.slot != 0 || (dyn_seen && !excluded(op.arg) && !h->fast_port_lists)) { ok = false; break; }
+          if (dyn_seen && !excluded(op.arg)) fr.flags |= OE_FR_PORTS_BY_TABLE;   // a static port behind a dynamic one that may have taken it
           if (std::find(statics.begin(), statics.end(), op.arg) != statics.end()) fr.flags |= OE_FR_NEVER;
           else statics.push_back(op.arg);
           fr.flags |= OE_FR_NEEDS_POOL;
           break;
         case OE_OP_PORT_DYNAMIC:
-          if (op.slot != 0 || op.arg >= 0 || fr.n_dyn == 255) { ok = false; break; }
+          if (op.slot != 0 || fr.n_dyn == 255) { ok = false; break; }
+          if (op.arg >= 0) {   // range-constrained: no closed form per offer, but a verdict per distinct range list
+            if (!h->fast_port_lists) { ok = false; break; }
+            fr.flags |= OE_FR_PORTS_BY_TABLE;
+          }
           dyn_seen = true;
           ++fr.n_dyn;
+          fr.flags |= OE_FR_NEEDS_POOL;
+          break;
+        case OE_OP_VOL_MOUNT:
+          if (fr.has_mount) { ok = false; break; }   // two MOUNT volumes compete for the disks: the interpreter keeps track
+          fr.has_mount = 1; fr.mount_amount = op.amount; fr.mount_mask = op.mask;
           fr.flags |= OE_FR_NEEDS_POOL;
           break;
         default: ok = false;
@@ -3640,7 +3680,7 @@ int build_fast_rows(oe_engine* h) {
   for (int c = 0; c < h->C; ++c) {
     const FastRow& fr = rows[(size_t)c];
     const bool rule_ok = fr.rule_count == 0 || (fr.flags & OE_FR_RULE_TAB);
-    h->all_lean = h->all_lean && (fr.flags & OE_FR_FAST) && (fr.flags & OE_FR_DENSE) && rule_ok;
+    h->all_lean = h->all_lean && (fr.flags & OE_FR_FAST) && (fr.flags & OE_FR_DENSE) && rule_ok && !fr.has_mount;
     h->any_ports = h->any_ports || (fr.n_ports | fr.n_dyn);
     h->any_rule = h->any_rule || (fr.flags & OE_FR_RULE_TAB);
   }
@@ -3727,7 +3767,13 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
   h->expand_started = false;
   K1Args a{};
   if (rows_all > 0) {
-    if (h->fast_K != h->dof.K || h->fast_S != h->dof.S) if (int rc = build_fast_rows(h)) return rc;   // also sizes the rule tables
+    // classes whose port stages exist only as a verdict per range list are folded exactly while the table has its lists
+    const bool port_lists = h->tuples_valid && h->dof.ptuple && h->dof.R <= OE_FAST_RANGES && h->n_port_tuples > 0 &&
+                            (int64_t)h->n_port_tuples * 4 <= std::max<int64_t>(h->N, 4096);
+    if (h->fast_K != h->dof.K || h->fast_S != h->dof.S || h->fast_port_lists != port_lists) {
+      h->fast_port_lists = port_lists;
+      if (int rc = build_fast_rows(h)) return rc;   // also sizes the rule tables
+    }
     a.tab.bits = nullptr; a.tab.words = h->tab_words; a.tab.zdim = h->tab_zdim;
     if (h->any_rule_tab) {
       CU(h->d_rule_tab.ensure((size_t)rows_all * h->tab_words * 4));
@@ -3738,7 +3784,8 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
                                                   h->tab_zdim, h->tab_rdim);
       ++*launches;
       static const bool no_merge = getenv("OE_NO_ROW_MERGE") != nullptr;   // debugging aid: one bit row per re-deployed requirement
-      if (h->V > 0 && !h->peers_attached && !no_merge) if (int rc = merge_equal_variants(h)) return rc;
+      // (sharded engines merge too: tasks, programs and requirements are replicated, so every rank arrives at the same rows)
+      if (h->V > 0 && !no_merge) if (int rc = merge_equal_variants(h)) return rc;
     }
   }
   const int rows = h->rows_factored();
@@ -3758,14 +3805,14 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
     const int64_t xblocks_all = stride * 32 / OE_K1_THREADS;
     const int n_chunks = h->offers_in_flight ? h->n_chunks : 1;
     a.ptab.bits = nullptr; a.ptab.words = 0;
-    if (h->tuples_valid && h->dof.ptuple && h->dof.R <= OE_FAST_RANGES && h->n_port_tuples > 0 && h->C > 0) {
+    {
       // few distinct `ports` range lists (stock agents offer the same ranges): a class's port stages once per list.  With
       // nearly as many lists as offers the table would cost what it saves, and the per-offer test stays.
-      if ((int64_t)h->n_port_tuples * 4 <= std::max<int64_t>(h->N, 4096)) {
+      if (h->fast_port_lists && h->C > 0) {
         a.ptab.words = (h->n_port_tuples + 31) / 32;
         CU(h->d_port_tab.ensure((size_t)h->C * a.ptab.words * 4));
         k_port_tables<<<dim3((unsigned)((h->n_port_tuples + 127) / 128), (unsigned)h->C), 128, 0, h->stream>>>(
-            h->d_fast.as<FastRow>(), h->d_ptuples.as<uint32_t>(), h->n_port_tuples, h->dof.R, h->d_port_tab.as<uint32_t>(), a.ptab.words);
+            h->dp, h->d_fast.as<FastRow>(), h->d_ptuples.as<uint32_t>(), h->n_port_tuples, h->dof.R, h->d_port_tab.as<uint32_t>(), a.ptab.words);
         ++*launches;
         a.ptab.bits = h->d_port_tab.as<uint32_t>();
       }
