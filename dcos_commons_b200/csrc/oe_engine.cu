@@ -517,25 +517,23 @@ struct LeanArgs {
   PeerOut peers;
   int64_t xb0;
 };
-// bit rows -> the two verdict tables transposed: thread = (table entry e, 32-row word w)
-__global__ void k_transpose_tables(DevCtx cx, const FastRow* __restrict__ fast, const int32_t* __restrict__ row_map, int rows, int row_words,
-                                   const uint32_t* __restrict__ rule_tab, int tab_words, int n_combos, uint32_t* __restrict__ ruleT,
-                                   const uint32_t* __restrict__ port_tab, int ptab_words, int n_tuples, uint32_t* __restrict__ portT, LeanRow* __restrict__ lean) {
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+// bit rows -> the two verdict tables transposed: warp = (table entry e, 32-row word w), lane = row of the word
+__global__ void __launch_bounds__(128) k_transpose_tables(DevCtx cx, const FastRow* __restrict__ fast, const int32_t* __restrict__ row_map, int rows, int row_words,
+                                                          const uint32_t* __restrict__ rule_tab, int tab_words, int n_combos, uint32_t* __restrict__ ruleT,
+                                                          const uint32_t* __restrict__ port_tab, int ptab_words, int n_tuples, uint32_t* __restrict__ portT,
+                                                          LeanRow* __restrict__ lean) {
+  const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), k = threadIdx.x & 31;
   const int n_entries = max(1, max(n_combos, n_tuples));   // entry 0 also writes the rows' descriptors: it always exists
   if (q >= n_entries * row_words) return;
   const int e = q / row_words, w = q - e * row_words;
-  uint32_t rbits = 0u, pbits = 0u;
-  for (int k = 0; k < 32; ++k) {
-    const int row = w * 32 + k;
-    if (row >= rows) break;
+  const int row = w * 32 + k;
+  bool rule = false, port = false;
+  if (row < rows) {
     const int frow = row_map ? row_map[row] : row;
     const int cls = frow < cx.p.C ? frow : cx.v.cls[frow - cx.p.C];
     const FastRow& fr = fast[cls];
-    const bool rule = !(fr.flags & OE_FR_RULE_TAB) || (e < n_combos && ((rule_tab[(int64_t)frow * tab_words + (e >> 5)] >> (e & 31)) & 1u));
-    const bool port = !(fr.n_ports | fr.n_dyn) || (e < n_tuples && ((port_tab[(int64_t)cls * ptab_words + (e >> 5)] >> (e & 31)) & 1u));
-    rbits |= rule ? 1u << k : 0u;
-    pbits |= port ? 1u << k : 0u;
+    rule = !(fr.flags & OE_FR_RULE_TAB) || (e < n_combos && ((rule_tab[(int64_t)frow * tab_words + (e >> 5)] >> (e & 31)) & 1u));
+    port = !(fr.n_ports | fr.n_dyn) || (e < n_tuples && ((port_tab[(int64_t)cls * ptab_words + (e >> 5)] >> (e & 31)) & 1u));
     if (e == 0) {   // the row's descriptor, once
       LeanRow lr;
       for (int x = 0; x < 4; ++x) lr.thr[x] = fr.thr[x];
@@ -545,8 +543,11 @@ __global__ void k_transpose_tables(DevCtx cx, const FastRow* __restrict__ fast, 
       lean[row] = lr;
     }
   }
-  if (ruleT && e < n_combos) ruleT[(int64_t)e * row_words + w] = rbits;
-  if (portT && e < n_tuples) portT[(int64_t)e * row_words + w] = pbits;
+  const uint32_t rbits = __ballot_sync(0xffffffffu, rule), pbits = __ballot_sync(0xffffffffu, port);
+  if (k == 0) {
+    if (ruleT && e < n_combos) ruleT[(int64_t)e * row_words + w] = rbits;
+    if (portT && e < n_tuples) portT[(int64_t)e * row_words + w] = pbits;
+  }
 }
 template <bool PEERS>
 __global__ void __launch_bounds__(OE_K1_THREADS, 8) k_class_feasibility_lean(DevOffers o, LeanArgs a) {
@@ -3843,7 +3844,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
       la.ruleT = n_combos ? h->d_ruleT.as<uint32_t>() : nullptr;
       la.portT = n_tuples ? h->d_portT.as<uint32_t>() : nullptr;
       const int n_entries = std::max(1, std::max(n_combos, n_tuples));
-      k_transpose_tables<<<(unsigned)((n_entries * la.row_words + 127) / 128), 128, 0, h->stream>>>(
+      k_transpose_tables<<<(unsigned)((n_entries * la.row_words + 3) / 4), 128, 0, h->stream>>>(
           h->ctx(), h->d_fast.as<FastRow>(), a.row_map, rows, la.row_words, a.tab.bits, h->tab_words, n_combos, h->d_ruleT.as<uint32_t>(), a.ptab.bits,
           a.ptab.words, n_tuples, h->d_portT.as<uint32_t>(), h->d_lean.as<LeanRow>());
       ++*launches;
