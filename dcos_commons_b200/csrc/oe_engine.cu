@@ -51,6 +51,73 @@ __global__ void k_validate_ids(const int32_t* __restrict__ col, int64_t n, int32
   }
 }
 
+// Which requirements re-deploy a pod that is already running (a stored task of the same pod type and index,
+// S/offer/TaskUtils.java:136-145), and which task rows are that pod's?  Usually none, sometimes thousands (a rolling restart).
+// The device answers (OE_CFG_ASYNC_LOADS): the requirements go into a hash table by pod, every deployed task looks its pod up
+// and emits one record per requirement found.  The host reads only those records: nothing per requirement or per task.
+#define OE_POD_EMPTY 0xffffffffffffffffull
+__device__ __forceinline__ uint64_t pod_key(int32_t type, int32_t index) { return ((uint64_t)(uint32_t)type << 32) | (uint32_t)index; }
+__device__ __forceinline__ uint32_t pod_slot(uint64_t key, uint32_t mask) { return (uint32_t)((key * 0x9E3779B97F4A7C15ull) >> 20) & mask; }
+// The requirements whose class reads tallies, hashed by pod: keys[slot] = (type, index), head[slot] / next[j] chain the requirements
+// of that pod (one, unless the caller lists a pod twice).
+struct PodHash {
+  unsigned long long* keys;
+  int32_t* head;
+  int32_t* next;
+  uint32_t mask;
+};
+__global__ void k_pod_hash_insert(const int32_t* __restrict__ cls, const int32_t* __restrict__ type, const int32_t* __restrict__ index, int64_t M, int C,
+                                  const uint8_t* __restrict__ sensitive, PodHash hs) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const int32_t c = cls[j];
+  if (c < 0 || c >= C || !sensitive[c]) return;   // (an id outside the dictionary is reported by the validation kernels)
+  const uint64_t key = pod_key(type[j], index[j]);
+  if (key == OE_POD_EMPTY) return;
+  for (uint32_t q = pod_slot(key, hs.mask);; q = (q + 1) & hs.mask) {
+    const unsigned long long old = atomicCAS(hs.keys + q, OE_POD_EMPTY, (unsigned long long)key);
+    if (old == OE_POD_EMPTY || old == key) { hs.next[j] = atomicExch(hs.head + q, (int32_t)j); return; }
+  }
+}
+// One record (requirement, task row, class of the requirement, 0) per deployed task of a pod that a requirement re-deploys.
+// count[0] = records found (those beyond `cap` are not stored: the host then searches by itself).
+__global__ void k_match_tasks(const int32_t* __restrict__ type, const int32_t* __restrict__ index, int64_t T, PodHash hs, const int32_t* __restrict__ cls,
+                              int4* __restrict__ pairs, int cap, int* __restrict__ count) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= T) return;
+  const int32_t ty = type[r], ix = index[r];
+  if (ty < 0 || ix == OE_NO_INDEX) return;
+  const uint64_t key = pod_key(ty, ix);
+  for (uint32_t q = pod_slot(key, hs.mask);; q = (q + 1) & hs.mask) {
+    const unsigned long long e = hs.keys[q];
+    if (e == OE_POD_EMPTY) return;
+    if (e != key) continue;
+    for (int32_t j = hs.head[q]; j >= 0; j = hs.next[j]) {
+      const int at = atomicAdd(count, 1);
+      if (at < cap) pairs[at] = make_int4(j, (int32_t)r, cls[j], 0);
+    }
+    return;
+  }
+}
+// req_row[twin[v]] = first_row + v: the requirements that re-deploy a pod read a bit row of their own
+__global__ void k_set_variant_rows(int32_t* __restrict__ req_row, const int32_t* __restrict__ twin, int V, int32_t first_row) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < V) req_row[twin[v]] = first_row + v;
+}
+// merged numbering (merge_equal_variants): rows below C stay, variant v reads bit row row_of_variant[v]
+__global__ void k_merged_rows(const int32_t* __restrict__ req_row, int64_t M, int C, const int32_t* __restrict__ row_of_variant, int32_t* __restrict__ out) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= M) return;
+  const int32_t r = req_row[j];
+  out[j] = r < C ? r : row_of_variant[r - C];
+}
+// a CSR offset column: begin[0] == 0 and ascending
+__global__ void k_validate_offsets(const int32_t* __restrict__ begin, int64_t n, int code, int* err) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j > n) return;
+  if (j == 0 ? begin[0] != 0 : begin[j] < begin[j - 1]) atomicMax(err, code);
+}
+
 // The `ports` ranges of one (offer, role slot) must be ascending and disjoint (the host merges them the way antlr's
 // IntervalSet does, S/offer/RangeUtils.java:23-47): the folded port test counts offered ports by range length.
 // oe_update_offers: dst[slot][rows[k]] = src[slot][k] for a slot-major column (4- or 8-byte elements)
@@ -2190,8 +2257,24 @@ struct oe_engine {
   bool validation_pending = false;
   bool self_provided = false;
   std::vector<uint32_t> h_launch_filter;
-  const int32_t *pending_launch_begin = nullptr, *pending_launch_name = nullptr;   // OE_CFG_ASYNC_LOADS: launch rows still in the caller's memory
-  const uint32_t* pending_launch_filter = nullptr;
+  // OE_CFG_ASYNC_LOADS: host mirrors that nobody waits for are filled from the caller's tables inside the next evaluation call
+  // (the tables stay valid until it returns); re-deployed pods are looked for on the device (k_find_twins) and the host-side search
+  // only runs when there are any
+  const int32_t *pending_t_name = nullptr, *pending_t_type = nullptr, *pending_t_index = nullptr;
+  int64_t pending_T = -1;                     // >= 0: h_tname / h_ttype / h_tindex not yet copied
+  // OE_CFG_ASYNC_LOADS: the host copies above are filled only when something reads them (oe_apply_launches, oe_requirement_rows,
+  // the search for re-deployed pods): from the caller's tables while those are promised to be valid (until the evaluation call
+  // after the load returns), from the device columns afterwards.  A plain cycle never touches them.
+  bool tasks_caller_valid = false, reqs_caller_valid = false;
+  DevBuf d_lr_begin, d_lr_name, d_lr_filter;  // launch rows of the requirement table, kept on the device for the same reason
+  int64_t pending_launch_rows = -1;           // >= 0: h_launch_* not yet filled, this many rows in d_lr_name / d_lr_filter
+  const int32_t *pending_r_class = nullptr, *pending_r_type = nullptr, *pending_r_index = nullptr;
+  bool reqs_pending = false, twins_unresolved = false;
+  DevBuf d_pod_hash, d_pod_head, d_pod_next, d_sensitive, d_twin, d_pairs, d_rclass, d_twin_j, d_row_of_variant;
+  std::vector<int32_t> h_twin_j;              // requirement of variant v (device-found variants; empty otherwise)
+  std::vector<int4> h_pairs;
+  int pairs_cap = 0;
+  bool req_row_eff_on_host = false;
   DevBuf d_req_row, d_rtype, d_rindex, d_vcls, d_vself_begin, d_vself_rows, d_vrrsum;
   // Re-deployed requirements whose rule verdicts over (zone, region) are identical share one bit row: V_eff rows behind the
   // classes instead of V (-1 = not merged: every such requirement has a row of its own).  row_map[bit row] = factored row it is
@@ -2366,6 +2449,7 @@ int fetch_err_flag(oe_engine* h, const char* what) {
   CU(cudaStreamSynchronize(h->stream));
   if (flag) {
     CU(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
+    if (flag == 23) return h->fail(OE_ERR_INVALID, "%s: launch_begin not monotone (code 23)", what);
     return h->fail(OE_ERR_INVALID, flag == 18 ? "%s: a ports column holds ranges that are not ascending and disjoint (code %d)"
                                               : "%s: id column %d holds a value outside its dictionary", what, flag);
   }
@@ -2553,7 +2637,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
                    &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
-                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used, &h->d_lean, &h->d_ruleT, &h->d_portT};
+                   &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used, &h->d_lean, &h->d_ruleT, &h->d_portT, &h->d_pod_hash, &h->d_pod_head, &h->d_pod_next, &h->d_sensitive, &h->d_twin, &h->d_pairs, &h->d_rclass, &h->d_twin_j, &h->d_row_of_variant, &h->d_lr_begin, &h->d_lr_name, &h->d_lr_filter};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
     if (h->chunks[c].landed) cudaEventDestroy(h->chunks[c].landed);
@@ -2602,6 +2686,7 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   const bool had_offers = h->hasO;
   const oe_dict_sizes old_dict = h->dict;
   h->hasP = h->hasT = h->hasO = h->hasR = false;
+  h->pending_T = -1; h->reqs_pending = h->twins_unresolved = false;   // tables of the old programs: nothing of them is kept
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
   const int C = t->n_classes;
   if (C < 0 || C > OE_MAX_CLASSES) return h->fail(OE_ERR_LIMIT, "n_classes %d exceeds OE_MAX_CLASSES", C);
@@ -2741,6 +2826,8 @@ int32_t oe_load_programs(oe_engine* h, const oe_program_table* t) {
   if (int rc = upload(h, h->d_ts_type, t->type_set_pod_type, (size_t)t->n_type_sets)) return rc;
   if (int rc = upload(h, h->d_mbits, t->matcher_bits, (size_t)t->n_matcher_words)) return rc;
   if (int rc = upload(h, h->d_rr_used, h->h_rr_used.data(), h->h_rr_used.size())) return rc;
+  if (int rc = upload(h, h->d_sensitive, h->class_self_sensitive.data(), h->class_self_sensitive.size())) return rc;
+  CU(h->d_sensitive.ensure(1));
   h->any_rr_used = false; h->max_rr_keys = 0;
   for (int c = 0; c < t->n_counter_sets; ++c)
     if (h->h_rr_used[(size_t)c]) { h->any_rr_used = true; h->max_rr_keys = std::max(h->max_rr_keys, h->h_cs_off[(size_t)c + 1] - h->h_cs_off[(size_t)c]); }
@@ -2801,11 +2888,36 @@ int reserve_tasks(oe_engine* h, int64_t cap, int64_t keep) {
 }
 }  // namespace
 
+namespace {
+// host mirror of the task columns that variant detection and oe_apply_launches read
+int absorb_tasks(oe_engine* h) {
+  if (h->pending_T < 0) return 0;
+  const int64_t T = h->pending_T;
+  if (h->tasks_caller_valid) {
+    h->h_tname.assign(h->pending_t_name, h->pending_t_name + T);
+    h->h_ttype.assign(h->pending_t_type, h->pending_t_type + T);
+    h->h_tindex.assign(h->pending_t_index, h->pending_t_index + T);
+  } else {
+    h->h_tname.resize((size_t)T); h->h_ttype.resize((size_t)T); h->h_tindex.resize((size_t)T);
+    if (T > 0) {
+      CU(cudaMemcpyAsync(h->h_tname.data(), h->dt.name, (size_t)T * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaMemcpyAsync(h->h_ttype.data(), h->dt.type, (size_t)T * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaMemcpyAsync(h->h_tindex.data(), h->dt.index, (size_t)T * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaStreamSynchronize(h->stream));
+    }
+  }
+  h->task_spans_valid = false;
+  h->pending_T = -1;
+  return 0;
+}
+}  // namespace
+
 int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   if (!h || !t) return OE_ERR_INVALID;
   if (!h->hasP) return h->fail(OE_ERR_STATE, "oe_load_tasks: load programs first");
   CU(cudaSetDevice(h->device));
   h->hasT = h->hasR = false;
+  h->reqs_pending = h->twins_unresolved = false;
   h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
   const int64_t T = t->n_tasks;
   if (T < 0 || T > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_tasks");
@@ -2845,12 +2957,12 @@ int32_t oe_load_tasks(oe_engine* h, const oe_task_table* t) {
   check_ids(h, d.region, T, -1, dc.n_regions, 5);
   for (int a = 0; a < d.TA; ++a) check_ids(h, d.attr + (size_t)a * d.cap, T, -1, dc.n_attrs, 6);
   for (int q = 0; q < d.Q; ++q) check_ids(h, d.rr + (size_t)q * d.cap, T, -1, dc.n_rr_values, 7);
-  h->h_tname.assign(t->name_id, t->name_id + T);
-  h->h_ttype.assign(t->pod_type_id, t->pod_type_id + T);
   h->task_spans_valid = false;
-  h->h_tindex.assign(t->pod_index, t->pod_index + T);
   h->name_to_row.clear();
   h->name_map_built = false;  // only oe_apply_launches needs it: built on first use
+  h->pending_t_name = t->name_id; h->pending_t_type = t->pod_type_id; h->pending_t_index = t->pod_index; h->pending_T = T;
+  h->tasks_caller_valid = true;
+  if (!(h->flags & OE_CFG_ASYNC_LOADS)) if (int rc = absorb_tasks(h)) return rc;   // else: when somebody needs them
   if (h->flags & OE_CFG_ASYNC_LOADS) h->validation_pending = true;
   else if (int rc = fetch_err_flag(h, "oe_load_tasks")) return rc;
   h->hasT = true;
@@ -3281,13 +3393,14 @@ struct CycleTrace {
 thread_local CycleTrace* g_trace = nullptr;
 
 int rebuild_variants(oe_engine* h) {
+  if (int rc = absorb_tasks(h)) return rc;
   const int64_t M = h->M;
   const int64_t T = (int64_t)h->h_ttype.size();
   // members, not locals: their uploads may still be in flight when this returns (OE_CFG_ASYNC_LOADS)
   std::vector<int32_t>& vcls = h->h_vcls; std::vector<int32_t>& vself_begin = h->h_vself_begin; std::vector<int32_t>& vself_rows = h->h_vself_rows;
   CU(cudaEventSynchronize(h->ev_variants));  // ... and their previous upload must be finished before they are rewritten
   if (g_trace) g_trace->mark("prev_upload_done");
-  vcls.clear(); vself_begin.assign(1, 0); vself_rows.clear();
+  vcls.clear(); vself_begin.assign(1, 0); vself_rows.clear(); h->h_twin_j.clear();
   h->h_req_row.assign(h->h_class.begin(), h->h_class.end());
   auto add_variant = [&](int64_t j, const int32_t* rows, int n) -> int {
     h->h_req_row[j] = h->C + (int32_t)vcls.size();
@@ -3413,18 +3526,10 @@ int keep_launch_rows(oe_engine* h, const int32_t* begin, const int32_t* name, co
 }
 }  // namespace
 
-int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
-  if (!h || !t) return OE_ERR_INVALID;
-  if (!h->hasP || !h->hasT) return h->fail(OE_ERR_STATE, "oe_load_requirements: load programs and tasks first");
-  CU(cudaSetDevice(h->device));
-  h->hasR = false;
-  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
-  CycleTrace tr;
-  tr.title = "oe_load_requirements";
-  struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
-  const int64_t M = t->n_reqs;
-  if (M < 0 || M > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_reqs");
-  if (M > 0 && (!t->class_id || !t->pod_type_id || !t->pod_index)) return h->fail(OE_ERR_INVALID, "oe_load_requirements: missing column");
+namespace {
+// The host side of a requirement load: id checks, host mirrors, and the search for requirements that re-deploy a running pod
+// (rebuild_variants).  Synchronous loads run it at once; asynchronous ones only when the device found such a requirement.
+int load_requirements_host(oe_engine* h, const int32_t* class_id, const int32_t* pod_type_id, const int32_t* pod_index, int64_t M, CycleTrace& tr) {
   // one pass: the id checks, the host copies, and per pod type the index range of the requirements whose class reads tallies
   // (rebuild_variants compares it with the deployed tasks' range before it hashes anything)
   const size_t n_types = (size_t)std::max(h->dict.n_pod_types, 1);
@@ -3435,39 +3540,204 @@ int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
   h->h_class.resize((size_t)M); h->h_rtype.resize((size_t)M); h->h_rindex.resize((size_t)M);
   const bool sensitive_known = h->class_self_sensitive.size() == (size_t)h->C;
   for (int64_t j = 0; j < M; ++j) {
-    const int32_t c = t->class_id[j], ty = t->pod_type_id[j], ix = t->pod_index[j];
+    const int32_t c = class_id[j], ty = pod_type_id[j], ix = pod_index[j];
     if (c < 0 || c >= h->C) return h->fail(OE_ERR_INVALID, "requirement %lld: class id %d", (long long)j, c);
     if (ty < 0 || (size_t)ty >= n_types) return h->fail(OE_ERR_INVALID, "requirement %lld: pod type", (long long)j);
     h->h_class[j] = c; h->h_rtype[j] = ty; h->h_rindex[j] = ix;
     if (sensitive_known && h->class_self_sensitive[c]) { rmin[ty] = std::min(rmin[ty], ix); rmax[ty] = std::max(rmax[ty], ix); }
   }
   h->req_spans_valid = sensitive_known;
-  h->M = M;
-
+  h->reqs_pending = false;
   tr.mark("checked_and_kept");
-  h->self_provided = t->self_begin != nullptr;
-  h->h_self_begin.clear(); h->h_self_rows.clear();
-  if (h->self_provided) {
-    const int64_t T = (int64_t)h->h_ttype.size();
-    for (int64_t j = 0; j < M; ++j) if (t->self_begin[j + 1] < t->self_begin[j]) return h->fail(OE_ERR_INVALID, "self_begin not monotone");
-    h->h_self_begin.assign(t->self_begin, t->self_begin + M + 1);
-    h->h_self_rows.assign(t->self_rows, t->self_rows + t->self_begin[M]);
-    for (int32_t r : h->h_self_rows) if (r < 0 || r >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
-  }
   if (int rc = rebuild_variants(h)) return rc;
   tr.mark("variants_uploaded");
-  if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M, h->side_stream)) return rc;
-  if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M, h->side_stream)) return rc;
-  if (int rc = join_side_uploads(h)) return rc;
+  return 0;
+}
+// host mirror of the requirement columns when no requirement re-deploys a pod (every requirement reads its class's bit row)
+int absorb_reqs(oe_engine* h) {
+  if (!h->reqs_pending) return 0;
+  const size_t M = (size_t)h->M;
+  if (h->reqs_caller_valid) {
+    h->h_class.assign(h->pending_r_class, h->pending_r_class + M);
+    h->h_rtype.assign(h->pending_r_type, h->pending_r_type + M);
+    h->h_rindex.assign(h->pending_r_index, h->pending_r_index + M);
+  } else {
+    h->h_class.resize(M); h->h_rtype.resize(M); h->h_rindex.resize(M);
+    if (M > 0) {
+      CU(cudaMemcpyAsync(h->h_class.data(), h->d_rclass.p, M * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaMemcpyAsync(h->h_rtype.data(), h->d_rtype.p, M * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaMemcpyAsync(h->h_rindex.data(), h->d_rindex.p, M * 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(cudaStreamSynchronize(h->stream));
+    }
+  }
+  h->h_req_row = h->h_class;
+  for (size_t v = 0; v < h->h_twin_j.size(); ++v) h->h_req_row[(size_t)h->h_twin_j[v]] = h->C + (int32_t)v;   // variants found on the device
+  h->req_spans_valid = false;
+  h->reqs_pending = false;
+  return 0;
+}
+int absorb_launch_rows(oe_engine* h) {
+  if (h->pending_launch_rows < 0) return 0;
+  const size_t M = (size_t)h->M, nl = (size_t)h->pending_launch_rows, FW = (size_t)h->dt.FW;
+  h->h_launch_begin.resize(M + 1); h->h_launch_name.resize(nl); h->h_launch_filter.resize(nl * FW);
+  CU(cudaMemcpyAsync(h->h_launch_begin.data(), h->d_lr_begin.p, (M + 1) * 4, cudaMemcpyDeviceToHost, h->stream));
+  if (nl) CU(cudaMemcpyAsync(h->h_launch_name.data(), h->d_lr_name.p, nl * 4, cudaMemcpyDeviceToHost, h->stream));
+  if (nl * FW) CU(cudaMemcpyAsync(h->h_launch_filter.data(), h->d_lr_filter.p, nl * FW * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  h->pending_launch_rows = -1;
+  return 0;
+}
+int absorb_host_mirrors(oe_engine* h) {
+  if (int rc = absorb_tasks(h)) return rc;
+  if (int rc = absorb_reqs(h)) return rc;
+  return absorb_launch_rows(h);
+}
+// Requirements that re-deploy running pods exist (OE_CFG_ASYNC_LOADS): their variants from the records k_match_tasks left, sorted
+// by (requirement, task row) so that variants are numbered by ascending requirement and list their rows ascending, exactly as
+// rebuild_variants does.  More records than the buffer holds (a pod listed by many requirements): the host-side search.
+int resolve_twins(oe_engine* h) {
+  const int n = h->h_os_info[3];
+  CycleTrace tr;
+  tr.title = "re-deployed pods";
+  if (n > h->pairs_cap) {
+    const int32_t *rc_ = h->pending_r_class, *rt_ = h->pending_r_type, *ri_ = h->pending_r_index;
+    if (!h->reqs_caller_valid) {   // an earlier evaluation call failed before it got here: the caller's tables may be gone
+      if (int rc = absorb_reqs(h)) return rc;
+      rc_ = h->h_class.data(); rt_ = h->h_rtype.data(); ri_ = h->h_rindex.data();
+    }
+    return load_requirements_host(h, rc_, rt_, ri_, h->M, tr);
+  }
+  std::vector<int4>& pairs = h->h_pairs;
+  pairs.resize((size_t)n);
+  CU(cudaMemcpyAsync(pairs.data(), h->d_pairs.p, (size_t)n * sizeof(int4), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  tr.mark("records");
+  std::sort(pairs.begin(), pairs.end(), [](const int4& a, const int4& b) { return a.x != b.x ? a.x < b.x : a.y < b.y; });
+  CU(cudaEventSynchronize(h->ev_variants));   // the previous upload of these vectors
+  std::vector<int32_t>& vcls = h->h_vcls; std::vector<int32_t>& vself_begin = h->h_vself_begin; std::vector<int32_t>& vself_rows = h->h_vself_rows;
+  vcls.clear(); vself_begin.assign(1, 0); vself_rows.clear(); h->h_twin_j.clear();
+  vself_rows.reserve((size_t)n);
+  for (int k = 0; k < n; ++k) {
+    if (k == 0 || pairs[(size_t)k].x != pairs[(size_t)k - 1].x) {
+      if (k) vself_begin.push_back((int32_t)vself_rows.size());
+      vcls.push_back(pairs[(size_t)k].z);
+      h->h_twin_j.push_back(pairs[(size_t)k].x);
+    }
+    vself_rows.push_back(pairs[(size_t)k].y);
+  }
+  vself_begin.push_back((int32_t)vself_rows.size());
+  h->V = (int)vcls.size();
+  h->V_eff = -1;
+  tr.mark("variants");
+  if (int rc = upload(h, h->d_vcls, vcls.data(), vcls.size())) return rc;
+  if (int rc = upload(h, h->d_vself_begin, vself_begin.data(), vself_begin.size())) return rc;
+  if (int rc = upload(h, h->d_vself_rows, vself_rows.data(), vself_rows.size())) return rc;
+  if (int rc = upload(h, h->d_twin_j, h->h_twin_j.data(), h->h_twin_j.size())) return rc;
+  CU(h->d_vrrsum.ensure(std::max<size_t>((size_t)h->V * std::max(h->n_csets, 1), 1) * sizeof(int4)));
+  k_set_variant_rows<<<(unsigned)((h->V + 255) / 256), 256, 0, h->stream>>>(h->d_req_row.as<int32_t>(), h->d_twin_j.as<int32_t>(), h->V, h->C);
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(h->ev_variants, h->stream));
+  tr.mark("uploaded");
+  return 0;
+}
+// When an evaluation entry point returns, the caller may reuse the tables it loaded (OE_CFG_ASYNC_LOADS, include/oe_abi.h).
+struct CallerTablesExpire {
+  oe_engine* h;
+  ~CallerTablesExpire() { if (h) h->tasks_caller_valid = h->reqs_caller_valid = false; }
+};
+}  // namespace
+
+int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t) {
+  if (!h || !t) return OE_ERR_INVALID;
+  if (!h->hasP || !h->hasT) return h->fail(OE_ERR_STATE, "oe_load_requirements: load programs and tasks first");
+  CU(cudaSetDevice(h->device));
+  h->hasR = false;
+  h->counters_fresh = h->class_bits_fresh = h->cycle_done = false;
+  h->reqs_pending = h->twins_unresolved = false;
+  CycleTrace tr;
+  tr.title = "oe_load_requirements";
+  struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
+  const int64_t M = t->n_reqs;
+  if (M < 0 || M > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "n_reqs");
+  if (M > 0 && (!t->class_id || !t->pod_type_id || !t->pod_index)) return h->fail(OE_ERR_INVALID, "oe_load_requirements: missing column");
+  h->M = M;
+  h->self_provided = t->self_begin != nullptr;
+  h->h_self_begin.clear(); h->h_self_rows.clear();
+  static const bool host_twins = getenv("OE_HOST_TWIN_SEARCH") != nullptr;   // measurement aid: always the host-side search
+  const bool lazy = (h->flags & OE_CFG_ASYNC_LOADS) && !h->self_provided && M > 0 && !host_twins && h->class_self_sensitive.size() == (size_t)h->C;
+  h->h_twin_j.clear();
+  if (lazy) {
+    // Nothing per requirement on the host: the three columns go to the device as they are (bit row = class), the ids are checked
+    // there, and k_match_tasks lists the deployed tasks of the pods that requirements re-deploy.  The next evaluation call reads
+    // the number of records together with the validation flags; only when it is not zero is there more to do (resolve_twins).
+    const int64_t T = h->dt.T;
+    h->V = 0; h->V_eff = -1;
+    h->h_vcls.clear(); h->h_vself_begin.assign(1, 0); h->h_vself_rows.clear();
+    if (int rc = upload(h, h->d_rclass, t->class_id, (size_t)M, h->side_stream)) return rc;
+    if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M, h->side_stream)) return rc;
+    if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M, h->side_stream)) return rc;
+    CU(h->d_req_row.ensure((size_t)M * 4));
+    CU(h->d_vcls.ensure(4)); CU(h->d_vself_begin.ensure(8)); CU(h->d_vself_rows.ensure(4)); CU(h->d_vrrsum.ensure(sizeof(int4)));
+    uint64_t size = 64;
+    while (size < (uint64_t)M * 2) size <<= 1;
+    h->pairs_cap = (int)std::min<int64_t>(T + M / 4 + 64, 0x3ffffff0);
+    CU(h->d_pod_hash.ensure(size * 8)); CU(h->d_pod_head.ensure(size * 4)); CU(h->d_pod_next.ensure((size_t)M * 4));
+    CU(h->d_pairs.ensure((size_t)h->pairs_cap * sizeof(int4))); CU(h->d_twin.ensure(sizeof(int)));
+    if (int rc = join_side_uploads(h)) return rc;
+    CU(cudaMemcpyAsync(h->d_req_row.p, h->d_rclass.p, (size_t)M * 4, cudaMemcpyDeviceToDevice, h->stream));
+    check_ids(h, h->d_rclass.as<int32_t>(), M, 0, std::max(h->C, 1), 21);
+    check_ids(h, h->d_rtype.as<int32_t>(), M, 0, std::max(h->dict.n_pod_types, 1), 22);
+    CU(cudaMemsetAsync(h->d_twin.p, 0, sizeof(int), h->stream));
+    h->h_os_info[3] = 0;
+    if (T > 0) {
+      const PodHash hs{h->d_pod_hash.as<unsigned long long>(), h->d_pod_head.as<int32_t>(), h->d_pod_next.as<int32_t>(), (uint32_t)(size - 1)};
+      CU(cudaMemsetAsync(hs.keys, 0xff, size * 8, h->stream));
+      CU(cudaMemsetAsync(hs.head, 0xff, size * 4, h->stream));
+      k_pod_hash_insert<<<(unsigned)((M + 255) / 256), 256, 0, h->stream>>>(h->d_rclass.as<int32_t>(), h->d_rtype.as<int32_t>(), h->d_rindex.as<int32_t>(), M, h->C,
+                                                                            h->d_sensitive.as<uint8_t>(), hs);
+      k_match_tasks<<<(unsigned)((T + 255) / 256), 256, 0, h->stream>>>(h->dt.type, h->dt.index, T, hs, h->d_rclass.as<int32_t>(), h->d_pairs.as<int4>(), h->pairs_cap,
+                                                                        h->d_twin.as<int>());
+      CU(cudaGetLastError());
+      CU(cudaMemcpyAsync(h->h_os_info + 3, h->d_twin.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    }
+    h->pending_r_class = t->class_id; h->pending_r_type = t->pod_type_id; h->pending_r_index = t->pod_index;
+    h->reqs_pending = h->twins_unresolved = true;
+    h->reqs_caller_valid = true;
+    h->validation_pending = true;
+    tr.mark("enqueued");
+  } else {
+    if (h->self_provided) {
+      if (int rc = absorb_tasks(h)) return rc;
+      const int64_t T = (int64_t)h->h_ttype.size();
+      for (int64_t j = 0; j < M; ++j) if (t->self_begin[j + 1] < t->self_begin[j]) return h->fail(OE_ERR_INVALID, "self_begin not monotone");
+      h->h_self_begin.assign(t->self_begin, t->self_begin + M + 1);
+      h->h_self_rows.assign(t->self_rows, t->self_rows + t->self_begin[M]);
+      for (int32_t r : h->h_self_rows) if (r < 0 || r >= T) return h->fail(OE_ERR_INVALID, "self_rows out of range");
+    }
+    if (int rc = load_requirements_host(h, t->class_id, t->pod_type_id, t->pod_index, M, tr)) return rc;
+    if (int rc = upload(h, h->d_rtype, t->pod_type_id, (size_t)M, h->side_stream)) return rc;
+    if (int rc = upload(h, h->d_rindex, t->pod_index, (size_t)M, h->side_stream)) return rc;
+    if (int rc = join_side_uploads(h)) return rc;
+  }
   CU(h->d_dec.ensure(std::max<size_t>((size_t)M, 1) * sizeof(oe_decision)));
 
   h->h_launch_begin.clear(); h->h_launch_name.clear(); h->h_launch_filter.clear();
-  h->pending_launch_begin = nullptr;
+  h->pending_launch_rows = -1;
   if (t->launch_begin) {
     if (h->flags & OE_CFG_ASYNC_LOADS) {
-      // the caller keeps its tables until the next evaluation call returns: the launch rows (only oe_apply_launches reads them)
-      // are checked and copied inside that call, while the host waits for the device anyway
-      h->pending_launch_begin = t->launch_begin; h->pending_launch_name = t->launch_name_id; h->pending_launch_filter = t->launch_filter_bits;
+      // only oe_apply_launches reads the launch rows: they go to the device as they are (checked there, code 23) and come back
+      // when that entry is called
+      const int64_t nl = t->launch_begin[M];
+      if (nl < 0 || nl > 0x7ffffff0) return h->fail(OE_ERR_INVALID, "launch_begin not monotone");
+      if (nl && (!t->launch_name_id || (h->dt.FW && !t->launch_filter_bits))) return h->fail(OE_ERR_INVALID, "launch rows missing");
+      if (int rc = upload(h, h->d_lr_begin, t->launch_begin, (size_t)M + 1, h->side_stream)) return rc;
+      if (int rc = upload(h, h->d_lr_name, t->launch_name_id, (size_t)nl, h->side_stream)) return rc;
+      if (int rc = upload(h, h->d_lr_filter, t->launch_filter_bits, (size_t)nl * h->dt.FW, h->side_stream)) return rc;
+      if (int rc = join_side_uploads(h)) return rc;
+      k_validate_offsets<<<(unsigned)((M + 256) / 256), 256, 0, h->stream>>>(h->d_lr_begin.as<int32_t>(), M, 23, h->d_err.as<int>());
+      CU(cudaGetLastError());
+      h->pending_launch_rows = nl;
+      h->validation_pending = true;
     } else if (int rc = keep_launch_rows(h, t->launch_begin, t->launch_name_id, t->launch_filter_bits)) {
       return rc;
     }
@@ -3740,13 +4010,12 @@ int merge_equal_variants(oe_engine* h) {
   }
   const int V_eff = (int)h->h_row_map.size() - C;
   if (V_eff == V) return 0;   // nothing merged: keep the plain numbering
-  h->h_req_row_eff.resize((size_t)h->M);
-  for (int64_t j = 0; j < h->M; ++j) {
-    const int32_t r = h->h_req_row[(size_t)j];
-    h->h_req_row_eff[(size_t)j] = r < C ? r : bit_row_of_variant[(size_t)(r - C)];
-  }
   if (int rc = upload(h, h->d_row_map, h->h_row_map.data(), h->h_row_map.size())) return rc;
-  if (int rc = upload(h, h->d_req_row_eff, h->h_req_row_eff.data(), h->h_req_row_eff.size())) return rc;
+  if (int rc = upload(h, h->d_row_of_variant, bit_row_of_variant.data(), bit_row_of_variant.size())) return rc;
+  CU(h->d_req_row_eff.ensure(std::max<size_t>((size_t)h->M, 1) * 4));
+  k_merged_rows<<<(unsigned)((h->M + 255) / 256), 256, 0, h->stream>>>(h->d_req_row.as<int32_t>(), h->M, C, h->d_row_of_variant.as<int32_t>(), h->d_req_row_eff.as<int32_t>());
+  CU(cudaGetLastError());
+  h->req_row_eff_on_host = false;
   CU(cudaStreamSynchronize(h->stream));   // the vectors are rewritten by the next pass
   h->V_eff = V_eff;
   return 0;
@@ -3760,7 +4029,7 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
 // expand_beside (oe_evaluate_cycle with OE_CFG_MATERIALIZE_MATRIX): the matrix columns of every chunk but the last are expanded on
 // the auxiliary stream as soon as the chunk's class bits exist; the last chunk's are left to the fork at the commit launch.
 int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false, bool expand_last = false,
-                          const std::function<int()>* after_prefix = nullptr) {
+                          const std::function<int()>* after_prefix = nullptr, int prefix_chunk = -1) {
   const int64_t stride = h->stride();
   h->V_eff = -1;
   const int rows_all = h->C + h->V;   // every class and every re-deployed requirement
@@ -3899,7 +4168,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
         if (int rc = run_expand(h, launches, h->aux_stream, w0, w1)) return rc;
         h->expand_from_word = w1;
       }
-      if (after_prefix && c == n_chunks - 2) if (int rc = (*after_prefix)()) return rc;
+      if (after_prefix && c == prefix_chunk) if (int rc = (*after_prefix)()) return rc;
     }
     h->offers_in_flight = false;
     if (h->peers_attached) {
@@ -4283,7 +4552,14 @@ int ready(oe_engine* h, const char* who, bool offers_deferred = false) {
   if (cudaSetDevice(h->device) != cudaSuccess) return h->fail(OE_ERR_CUDA, "cudaSetDevice");
   if (h->validation_pending) {  // OE_CFG_ASYNC_LOADS: the id checks of the loads are read back here, before any kernel gathers through them
     h->validation_pending = false;
-    if (int rc = fetch_err_flag(h, who)) { h->hasT = h->hasO = h->hasR = false; return rc; }
+    if (int rc = fetch_err_flag(h, who)) { h->hasT = h->hasO = h->hasR = h->twins_unresolved = h->reqs_pending = false; h->pending_T = -1; return rc; }
+  }
+  if (h->twins_unresolved) {
+    // ... and with them the number of (requirement, deployed task of its pod) records k_match_tasks wrote.  None: every
+    // requirement reads its class's bit row, which is what was loaded.
+    h->twins_unresolved = false;
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) return h->fail(OE_ERR_CUDA, "cudaStreamSynchronize");
+    if (h->h_os_info[3] > 0) if (int rc = resolve_twins(h)) { h->hasR = false; return rc; }
   }
   if (!offers_deferred) if (int rc = wait_offers(h, who)) return rc;
   return 0;
@@ -4292,6 +4568,7 @@ int ready(oe_engine* h, const char* who, bool offers_deferred = false) {
 }  // namespace
 
 int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
+  CallerTablesExpire expire_guard{h};
   if (int rc = ready(h, "oe_class_feasibility", true)) return rc;
   int64_t launches = 0;
   CU(cudaEventRecord(h->ev[0], h->stream));
@@ -4317,12 +4594,21 @@ int32_t oe_class_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
 int32_t oe_requirement_rows(oe_engine* h, int32_t* rows, int32_t* n_rows) {
   if (!h) return OE_ERR_INVALID;
   if (!h->hasR || !h->class_bits_fresh) return h->fail(OE_ERR_STATE, "oe_requirement_rows: no feasibility pass since the last load");
+  CU(cudaSetDevice(h->device));
+  if (int rc = absorb_reqs(h)) return rc;
+  if (h->V_eff >= 0 && !h->req_row_eff_on_host && h->M > 0) {
+    h->h_req_row_eff.resize((size_t)h->M);
+    CU(cudaMemcpyAsync(h->h_req_row_eff.data(), h->d_req_row_eff.p, (size_t)h->M * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->req_row_eff_on_host = true;
+  }
   if (n_rows) *n_rows = h->rows_factored();
   if (rows && h->M > 0) std::memcpy(rows, (h->V_eff >= 0 ? h->h_req_row_eff : h->h_req_row).data(), (size_t)h->M * sizeof(int32_t));
   return OE_OK;
 }
 
 int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
+  CallerTablesExpire expire_guard{h};
   if (int rc = ready(h, "oe_feasibility", true)) return rc;
   int64_t launches = 0;
   CU(cudaEventRecord(h->ev[0], h->stream));
@@ -4351,6 +4637,7 @@ int32_t oe_feasibility(oe_engine* h, uint32_t* bits, oe_stats* stats) {
 int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   CycleTrace tr;
   struct TraceScope { TraceScope(CycleTrace* t) { g_trace = t; } ~TraceScope() { g_trace = nullptr; } } trace_scope(&tr);
+  CallerTablesExpire expire_guard{h};
   if (int rc = ready(h, "oe_evaluate_cycle", true)) return rc;
   tr.mark("ready");
   struct WantQueues { oe_engine* e; WantQueues(oe_engine* x) : e(x) { e->want_queues = true; } ~WantQueues() { e->want_queues = false; e->queues_rows = -1; } } want_queues(h);
@@ -4398,7 +4685,12 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       // and only the requirements it left open are committed over the last chunk afterwards.
       two_pass = true;
       const int64_t stride = h->stride();
-      const int64_t wA = h->chunks[h->n_chunks - 2].r1 / 32, wT = (h->N + 31) / 32;
+      // Which prefix: all but the last chunk.  (An earlier one finishes its pass sooner but leaves more to the second pass; measured
+      // on the C5 workloads it gains 0.3 ms with MaxPerHostname rules and loses 0.1 ms with the matrix.  OE_PREFIX_CHUNK tries it.)
+      int prefix_chunk = h->n_chunks - 2;
+      static const char* prefix_env = getenv("OE_PREFIX_CHUNK");
+      if (prefix_env) prefix_chunk = std::max(0, std::min(h->n_chunks - 2, atoi(prefix_env)));
+      const int64_t wA = h->chunks[prefix_chunk].r1 / 32, wT = (h->N + 31) / 32;
       CU(h->d_dec.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_dec_sub.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_sub_idx.ensure((size_t)h->M * 4)); CU(h->d_sub_row.ensure((size_t)h->M * 4));
@@ -4434,7 +4726,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
         tr.mark("prefix_commit_enqueued");
         return 0;
       };
-      if (int rc = run_class_feasibility(h, &launches, want_matrix, true, &prefix_commit)) return rc;
+      if (int rc = run_class_feasibility(h, &launches, want_matrix, true, &prefix_commit, prefix_chunk)) return rc;
       CU(cudaEventRecord(h->ev[2], h->stream));
       CU(cudaEventRecord(h->ev[3], h->stream));
       CU(cudaEventRecord(h->ev_k1_last, h->stream));
@@ -4504,14 +4796,8 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
   int peer_err = 0;
   if (h->peers_attached) CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaEventRecord(h->ev[5], h->stream));
-  int launch_rc = 0;
-  if (h->pending_launch_begin) {   // host work that nobody waits for, done while the device finishes the cycle
-    launch_rc = keep_launch_rows(h, h->pending_launch_begin, h->pending_launch_name, h->pending_launch_filter);
-    h->pending_launch_begin = nullptr;
-  }
   CU(cudaStreamSynchronize(h->stream));
   tr.mark("synced");
-  if (launch_rc) return launch_rc;
   if (peer_err) {
     CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
     h->class_bits_fresh = false;
@@ -4541,6 +4827,7 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
 }
 
 int32_t oe_stage_failures(oe_engine* h, int64_t req_begin, int64_t req_end, uint64_t* failed) {
+  CallerTablesExpire expire_guard{h};
   if (int rc = ready(h, "oe_stage_failures")) return rc;
   if (req_begin < 0 || req_end < req_begin || req_end > h->M) return h->fail(OE_ERR_INVALID, "oe_stage_failures: requirement range");
   if (req_end - req_begin > 65535) return h->fail(OE_ERR_LIMIT, "oe_stage_failures: at most 65535 requirements per call");
@@ -4559,6 +4846,7 @@ int32_t oe_stage_failures(oe_engine* h, int64_t req_begin, int64_t req_end, uint
 }
 
 int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t only_unused_offers, uint8_t* unexpected, int64_t* n_unexpected) {
+  CallerTablesExpire expire_guard{h};
   if (int rc = ready(h, "oe_unexpected_resources")) return rc;
   if (n_unexpected) *n_unexpected = 0;
   const int64_t n_res = h->n_reserved;
@@ -4628,6 +4916,7 @@ int32_t oe_gather_decisions(oe_engine* h, oe_decision* out) {
 
 int32_t oe_apply_launches(oe_engine* h) {
   if (int rc = ready(h, "oe_apply_launches")) return rc;
+  if (int rc = absorb_host_mirrors(h)) return rc;
   if (!h->cycle_done) return h->fail(OE_ERR_STATE, "oe_apply_launches: no cycle evaluated since the last load");
   const bool from_records = h->world > 1;
   if (from_records) {

@@ -158,6 +158,46 @@ def test_async_loads_give_the_same_answers_and_still_validate():
     eng.close()
 
 
+@pytest.mark.parametrize("seed", range(48))
+def test_async_loads_find_redeployed_pods_on_the_device(seed):
+    """OE_CFG_ASYNC_LOADS: oe_load_requirements does nothing per requirement on the host; k_find_twins counts the requirements whose
+    pod is deployed, and only when there are some does the evaluation call run the host-side search.  Fuzzed tables (some with
+    re-deployed pods, some without), two cycles with the launches recorded in between (after which every placed pod is deployed)."""
+    eng = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    _compare_all(eng, random_tables(seed, n_offers=200 + 13 * seed))
+    eng.close()
+
+
+@pytest.mark.parametrize("redeploy_every", [0, 1, 7])
+def test_async_loads_keep_no_pointer_into_the_callers_tables(redeploy_every):
+    """The caller's task and requirement columns must stay valid until the evaluation call after the loads returns, and no longer:
+    they are overwritten right after it, and everything that reads the host-side copies afterwards (requirement rows, launches,
+    the re-deployed pods of the next cycle) must still see what was loaded."""
+    import copy
+    t = synth.make_cluster(3000, 240, 8, 3, 4, 120, "c5", seed=77, redeploy_every=redeploy_every).tables
+    t.normalise()
+    ref = Engine(device=0).load(copy.deepcopy(t))
+    eng = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS).load(t)
+    want, _ = ref.evaluate_cycle()
+    got, _ = eng.evaluate_cycle()
+    assert got.tobytes() == want.tobytes()
+    for name in ("class_id", "r_pod_type_id", "r_pod_index", "t_name_id", "t_pod_type_id", "t_pod_index", "launch_begin", "launch_name_id"):
+        getattr(t, name)[...] = 0x5a5a5a
+    rows_w, n_w = ref.requirement_rows()
+    rows_g, n_g = eng.requirement_rows()
+    assert n_w == n_g and np.array_equal(rows_w, rows_g)
+    assert (n_w > 8) == (redeploy_every > 0)
+    ref.apply_launches(); eng.apply_launches()
+    tw, tg = ref.export_tasks(), eng.export_tasks()
+    for k in tw:
+        assert np.array_equal(tw[k], tg[k]), k
+    want2, _ = ref.evaluate_cycle()
+    got2, _ = eng.evaluate_cycle()
+    assert got2.tobytes() == want2.tobytes()
+    assert np.array_equal(ref.requirement_rows()[0], eng.requirement_rows()[0])
+    eng.close(); ref.close()
+
+
 @pytest.mark.parametrize("flags", [abi.OE_CFG_ASYNC_LOADS, abi.OE_CFG_ASYNC_LOADS | abi.OE_CFG_MATERIALIZE_MATRIX])
 def test_async_offer_table_arrives_and_is_evaluated_in_row_chunks(flags, monkeypatch):
     """OE_CFG_ASYNC_LOADS: the offer table goes over the bus in row chunks and the pass evaluates (and, with the matrix

@@ -1,5 +1,6 @@
 """One engine, the C5 tables in pinned memory, a few end-to-end cycles with OE_CYCLE_TRACE=1: where a cycle's wall time goes.
-   python tools/cycle_probe.py [matrix|decisions] [chunks|auto] [offers-first|tasks-first]"""
+   python tools/cycle_probe.py [matrix|decisions] [chunks|auto] [offers-first|tasks-first]
+   OE_PROBE_WORKLOAD=c5|hostname|mount|redeploy|one-region picks the tables, OE_PROBE_WIRE=plain the unpacked offer table."""
 import os
 import sys
 import time
@@ -15,7 +16,8 @@ def main():
     if len(sys.argv) > 2 and sys.argv[2] != "auto":
         os.environ["OE_OFFER_CHUNKS"] = sys.argv[2]
     order = sys.argv[3] if len(sys.argv) > 3 else "offers-first"
-    t = synth.config_c5(1.0).tables
+    which = os.environ.get("OE_PROBE_WORKLOAD", "c5")
+    t = (synth.config_c5(1.0) if which == "c5" else synth.config_c5_variant(which)).tables
     t.normalise()
     pt = bench.pin_tables(t)
     ppk = abi.PackedOffers(t).pin() if os.environ.get("OE_PROBE_WIRE", "packed") == "packed" else None
@@ -41,7 +43,7 @@ def main():
         st = eng.evaluate_cycle_into(out.data_ptr())
         t4 = time.perf_counter()
         if k >= 4:
-            print(f"{mode} {order} chunks={os.environ.get('OE_OFFER_CHUNKS', 'auto')}: cycle {1e3 * (t4 - t0):.3f} ms = progs+tasks {1e3 * (t1 - t0):.3f} + offers {1e3 * (t2 - t1):.3f} + reqs {1e3 * (t3 - t2):.3f} "
+            print(f"{which} {mode} {order} chunks={os.environ.get('OE_OFFER_CHUNKS', 'auto')}: cycle {1e3 * (t4 - t0):.3f} ms = progs+tasks {1e3 * (t1 - t0):.3f} + offers {1e3 * (t2 - t1):.3f} + reqs {1e3 * (t3 - t2):.3f} "
                   f"+ evaluate {1e3 * (t4 - t3):.3f}; device " + " ".join(f"{k2[3:]}={v:.3f}" for k2, v in st.items() if k2.startswith("ms_")), flush=True)
     os.environ.pop("OE_CYCLE_TRACE", None)
     eng.close()
