@@ -254,6 +254,60 @@ __global__ void k_validate_tuples(const uint32_t* __restrict__ tuples, int n, in
   }
 }
 
+// The distinct `ports` range lists of the resident table (oe_load_offers_packed) stay a dictionary while rows are replaced
+// (oe_update_offers sends full range lists): a hash table over the lists' contents, slot = list id + 1 (0 = empty).  A replaced
+// row looks its list up; a list nobody had is appended (two rows that bring the same new list at once may append it twice: two
+// ids with equal contents, both right).  count[0] runs past `cap` when the dictionary is full: the host then stops using the ids.
+struct TupleHash {
+  int32_t* slot;
+  uint32_t mask;
+};
+__device__ __forceinline__ uint32_t tuple_hash_of(const uint32_t* w, int R) {
+  uint32_t x = 2166136261u;
+  for (int r = 0; r < R; ++r) { x ^= w[r]; x *= 16777619u; x ^= x >> 15; }
+  return x;
+}
+__global__ void k_tuple_hash_insert(const uint32_t* __restrict__ tuples, int n, int R, TupleHash th) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  uint32_t w[OE_MAX_PORT_RANGES];
+  for (int r = 0; r < R; ++r) w[r] = tuples[(int64_t)t * R + r];
+  for (uint32_t q = tuple_hash_of(w, R) & th.mask;; q = (q + 1) & th.mask) {
+    const int32_t old = atomicCAS(th.slot + q, 0, t + 1);
+    if (old == 0) return;
+    bool same = true;
+    for (int r = 0; r < R; ++r) same = same && tuples[(int64_t)(old - 1) * R + r] == w[r];
+    if (same) return;   // the caller's dictionary lists one range list twice: the first id answers look-ups, both stay valid
+  }
+}
+// st: the replaced rows' `ports` column as staged by oe_update_offers ([S * R][n], slot-major); id_out: [S][N]
+__global__ void k_reintern_tuples(const uint32_t* __restrict__ st, int64_t n, int S, int R, const int64_t* __restrict__ rows, int64_t N,
+                                  uint32_t* tuples, int cap, TupleHash th, int* count, int32_t* __restrict__ id_out) {
+  const int64_t q0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q0 >= n * S) return;
+  const int64_t s = q0 / n, k = q0 - s * n;
+  uint32_t w[OE_MAX_PORT_RANGES];
+  for (int r = 0; r < R; ++r) w[r] = st[(s * R + r) * n + k];
+  int32_t mine = -1, id = -1;
+  for (uint32_t q = tuple_hash_of(w, R) & th.mask;; q = (q + 1) & th.mask) {
+    int32_t v = *(volatile int32_t*)(th.slot + q);
+    if (v == 0) {
+      if (mine < 0) {
+        mine = atomicAdd(count, 1);
+        if (mine >= cap) break;   // dictionary full
+        for (int r = 0; r < R; ++r) tuples[(int64_t)mine * R + r] = w[r];
+        __threadfence();
+      }
+      v = atomicCAS(th.slot + q, 0, mine + 1);
+      if (v == 0) { id = mine; break; }
+    }
+    bool same = true;
+    for (int r = 0; r < R; ++r) same = same && *(volatile uint32_t*)(tuples + (int64_t)(v - 1) * R + r) == w[r];
+    if (same) { id = v - 1; break; }
+  }
+  id_out[s * N + rows[k]] = id;
+}
+
 __global__ void k_validate_ranges(const uint32_t* __restrict__ port, int64_t n, int S, int R, int code, int* err) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -2248,6 +2302,10 @@ struct oe_engine {
   DevBuf d_wire[12], d_ptuples, d_ptuple_id, d_port_tab;
   int32_t n_port_tuples = 0;
   bool tuples_valid = false;
+  DevBuf d_tuple_hash, d_ntuples;   // the range-list dictionary kept up while rows are replaced (k_reintern_tuples)
+  int32_t ptuple_cap = 0;
+  uint32_t tuple_mask = 0;
+  bool tuple_count_pending = false; // h_os_info[2] will hold the dictionary's size after the last oe_update_offers
 
   // ---- requirements
   int64_t M = 0;
@@ -2636,7 +2694,7 @@ void oe_destroy(oe_engine* h) {
                    &h->d_vrrsum, &h->d_cnt, &h->d_rrsum, &h->d_type_total, &h->d_type_agent, &h->d_F, &h->d_Fglobal, &h->d_matrix,
                    &h->d_dec, &h->d_used, &h->d_cursor, &h->d_err, &h->d_nplaced, &h->d_l_dst, &h->d_l_req, &h->d_l_name, &h->d_l_filter,
                    &h->d_tile_cnt, &h->d_row_base, &h->d_row_len, &h->d_cand, &h->d_fast, &h->d_rule_tab, &h->d_order, &h->d_adj, &h->d_dbg, &h->d_keep, &h->d_gc_out, &h->d_taken,
-                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
+                   &h->d_meta, &h->d_union, &h->d_umask, &h->d_stage, &h->d_stage_rows, &h->d_sort_hist, &h->d_comp_begin, &h->d_ptuples, &h->d_ptuple_id, &h->d_port_tab, &h->d_tuple_hash, &h->d_ntuples, &h->d_os_parent, &h->d_os_groups, &h->d_os_ocomp, &h->d_os_omask, &h->d_os_ohist,
                    &h->d_os_comp_begin, &h->d_os_list, &h->d_os_mask, &h->d_os_rhist, &h->d_os_row_begin, &h->d_os_queue, &h->d_os_cursor, &h->d_row_map, &h->d_req_row_eff, &h->d_os_totals, &h->d_rr_used, &h->d_lean, &h->d_ruleT, &h->d_portT, &h->d_pod_hash, &h->d_pod_head, &h->d_pod_next, &h->d_sensitive, &h->d_twin, &h->d_pairs, &h->d_rclass, &h->d_twin_j, &h->d_row_of_variant, &h->d_lr_begin, &h->d_lr_name, &h->d_lr_filter};
   if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
   for (int c = 0; c < oe_engine::kMaxChunks; ++c) {
@@ -2980,7 +3038,7 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t) {
   CU(cudaSetDevice(h->device));
   h->hasO = false;
   h->class_bits_fresh = h->cycle_done = false;
-  h->tuples_valid = false; h->n_port_tuples = 0;
+  h->tuples_valid = false; h->n_port_tuples = 0; h->tuple_count_pending = false;
   h->dof.ptuple = nullptr; h->dof.n_ptuples = 0;
   if (int rc = check_offer_table(h, t, nullptr)) return rc;
   const int64_t N = t->n_offers;
@@ -3150,7 +3208,7 @@ int32_t oe_load_offers_packed(oe_engine* h, const oe_offer_table* t, const oe_of
   CU(cudaSetDevice(h->device));
   h->hasO = false;
   h->class_bits_fresh = h->cycle_done = false;
-  h->tuples_valid = false; h->n_port_tuples = 0;
+  h->tuples_valid = false; h->n_port_tuples = 0; h->tuple_count_pending = false;
   h->dof.ptuple = nullptr; h->dof.n_ptuples = 0;
   if (int rc = check_offer_table(h, t, pk)) return rc;
   auto width_ok = [](uint8_t b) { return b == 1 || b == 2 || b == 4; };
@@ -3242,9 +3300,17 @@ int32_t oe_load_offers_packed(oe_engine* h, const oe_offer_table* t, const oe_of
   }
   if (tuples) {   // the distinct range lists: small, first over the bus, checked like a ports column of n_port_tuples rows
     const size_t words = (size_t)pk->n_port_tuples * o.R;
-    CU(h->d_ptuples.ensure(std::max<size_t>(words, 1) * 4));
+    h->ptuple_cap = pk->n_port_tuples + std::max(4096, pk->n_port_tuples / 4);   // room for the lists that oe_update_offers brings
+    CU(h->d_ptuples.ensure(std::max<size_t>((size_t)h->ptuple_cap * o.R, 1) * 4));
     CU(cudaMemcpyAsync(h->d_ptuples.p, pk->port_tuples, words * 4, cudaMemcpyHostToDevice, ls));
     k_validate_tuples<<<(unsigned)((pk->n_port_tuples + 255) / 256), 256, 0, ls>>>(h->d_ptuples.as<uint32_t>(), pk->n_port_tuples, o.R, 18, h->d_offer_err.as<int>());
+    uint32_t hsize = 1024;
+    while (hsize < (uint32_t)h->ptuple_cap * 2u) hsize <<= 1;
+    h->tuple_mask = hsize - 1;
+    CU(h->d_tuple_hash.ensure((size_t)hsize * 4)); CU(h->d_ntuples.ensure(sizeof(int)));
+    CU(cudaMemsetAsync(h->d_tuple_hash.p, 0, (size_t)hsize * 4, ls));
+    k_tuple_hash_insert<<<(unsigned)((pk->n_port_tuples + 127) / 128), 128, 0, ls>>>(h->d_ptuples.as<uint32_t>(), pk->n_port_tuples, o.R, TupleHash{h->d_tuple_hash.as<int32_t>(), h->tuple_mask});
+    k_fill_i32<<<1, 32, 0, ls>>>(h->d_ntuples.as<int32_t>(), pk->n_port_tuples, 0, 1);
   }
 
   int nch = 1;
@@ -3326,7 +3392,6 @@ int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, cons
   for (int64_t k = 0; k < n_rows; ++k)
     if (rows[k] < 0 || rows[k] >= o.N) return h->fail(OE_ERR_INVALID, "oe_update_offers: rows[%lld] = %lld is not a row of the resident table", (long long)k, (long long)rows[k]);
   h->class_bits_fresh = h->cycle_done = false;
-  h->tuples_valid = false;   // the patched rows' range lists are no longer the ones their list ids name: per-offer port tests from here on
   const size_t n = (size_t)n_rows;
   // one staging buffer, column after column, each 8-byte aligned
   const size_t slots8 = (size_t)o.S * o.K + o.D, slots4 = 1 + (size_t)o.S * o.R + o.D + 5 + o.A + o.Q + o.E;
@@ -3354,6 +3419,13 @@ int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, cons
     uint32_t* st = reinterpret_cast<uint32_t*>(cursor);
     if (int rc = column(h->d_port.as<uint32_t>(), t->port_range, o.S * o.R, 0, 0, 0)) return rc;
     k_validate_ranges<<<(unsigned)((n_rows + 255) / 256), 256, 0, h->stream>>>(st, n_rows, o.S, o.R, 18, h->d_err.as<int>());
+    if (h->tuples_valid) {   // the replaced rows' list ids: looked up (or added) in the resident dictionary
+      k_reintern_tuples<<<(unsigned)((n_rows * o.S + 127) / 128), 128, 0, h->stream>>>(st, n_rows, o.S, o.R, d_rows, o.N, h->d_ptuples.as<uint32_t>(), h->ptuple_cap,
+                                                                                     TupleHash{h->d_tuple_hash.as<int32_t>(), h->tuple_mask}, h->d_ntuples.as<int>(),
+                                                                                     h->d_ptuple_id.as<int32_t>());
+      CU(cudaMemcpyAsync(h->h_os_info + 2, h->d_ntuples.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+      h->tuple_count_pending = true;
+    }
   }
   if (int rc = column(h->d_msize.as<double>(), t->mount_size, o.D, 0, 0, 0)) return rc;
   if (int rc = column(h->d_mprof.as<int32_t>(), t->mount_profile, o.D, -1, OE_MAX_PROFILES, 17)) return rc;
@@ -4553,6 +4625,12 @@ int ready(oe_engine* h, const char* who, bool offers_deferred = false) {
   if (h->validation_pending) {  // OE_CFG_ASYNC_LOADS: the id checks of the loads are read back here, before any kernel gathers through them
     h->validation_pending = false;
     if (int rc = fetch_err_flag(h, who)) { h->hasT = h->hasO = h->hasR = h->twins_unresolved = h->reqs_pending = false; h->pending_T = -1; return rc; }
+  }
+  if (h->tuple_count_pending) {   // ... and the size of the range-list dictionary after the rows oe_update_offers replaced
+    h->tuple_count_pending = false;
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) return h->fail(OE_ERR_CUDA, "cudaStreamSynchronize");
+    if (h->h_os_info[2] > h->ptuple_cap) h->tuples_valid = false;   // dictionary full: per-offer port tests until the table is loaded whole again
+    else h->n_port_tuples = h->dof.n_ptuples = h->h_os_info[2];
   }
   if (h->twins_unresolved) {
     // ... and with them the number of (requirement, deployed task of its pod) records k_match_tasks wrote.  None: every

@@ -314,6 +314,48 @@ def test_update_offers_equals_a_full_reload(engine, seed):
     orc.close()
 
 
+@pytest.mark.parametrize("flags", [0, abi.OE_CFG_ASYNC_LOADS], ids=["sync", "async"])
+@pytest.mark.parametrize("rules,novel", [("c5", 0), ("c5", 300), ("c5-mount", 300), ("c5", 5000)])
+def test_update_offers_keeps_the_range_list_dictionary(flags, rules, novel):
+    """A table loaded in its packed form names each offer's `ports` ranges by a list id; oe_update_offers brings full range lists.
+    The replaced rows get their ids back from the resident dictionary (k_reintern_tuples), lists nobody had are appended, and a
+    dictionary that runs full (5000 new lists) falls back to per-offer port tests.  Same answers as loading the patched table."""
+    import copy
+    n = 7000
+    a = synth.make_cluster(n, 500, 8, 3, 4, 250, rules, seed=5).tables
+    b = synth.make_cluster(n, 500, 8, 3, 4, 250, rules, seed=6).tables
+    a.normalise(); b.normalise()
+    rng = np.random.default_rng(novel + 1)
+    rows = np.sort(rng.choice(n, size=max(novel, 600), replace=False)).astype(np.int64)
+    b.port_range = b.port_range.copy()
+    for k, r in enumerate(rows[:novel]):           # range lists that no offer of the resident table carries
+        b.port_range[0, 0, r] = (1 + k % 900) | ((1 + k % 900 + k // 900) << 16)
+    want = copy.copy(a)
+    want._keep = []
+    for name in abi.CycleTables.OFFER_COLUMNS:
+        col = getattr(a, name).copy()
+        col[..., rows] = getattr(b, name)[..., rows]
+        setattr(want, name, col)
+    ref = Engine(device=0)
+    eng = Engine(device=0, flags=flags)
+    eng.tables = a
+    eng.load_programs(a); eng.load_tasks(a); eng.load_offers_packed(abi.PackedOffers(a)); eng.load_requirements(a)
+    assert eng.evaluate_cycle()[0].tobytes() == ref.load(a).evaluate_cycle()[0].tobytes()
+    eng.update_offers(rows, b)
+    eng.tables = want
+    eng.load_requirements(a)
+    ref.load(want)
+    assert eng.evaluate_cycle()[0].tobytes() == ref.evaluate_cycle()[0].tobytes()
+    assert np.array_equal(eng.class_feasibility()[0], ref.class_feasibility()[0])
+    eng.update_offers(rows, a)                     # the old rows again: lists the dictionary has had from the start
+    eng.tables = a
+    eng.load_requirements(a)
+    ref.load(a)
+    assert eng.evaluate_cycle()[0].tobytes() == ref.evaluate_cycle()[0].tobytes()
+    assert np.array_equal(eng.feasibility()[0], ref.feasibility()[0])
+    eng.close(); ref.close()
+
+
 def test_update_offers_rejects_what_it_cannot_patch(engine):
     t = random_tables(7, n_offers=60, with_reserved=False)
     engine.load(t)
