@@ -210,6 +210,117 @@ struct EncodedCycle {
   }
 };
 
+// The compact wire form of an encoded offer table (oe_offer_packing, include/oe_abi.h): what goes over the bus instead of
+// EncodedCycle's full-width offer columns.  Decided per column from the values themselves — narrow unsigned ids when the
+// dictionary fits (all-ones = -1), fp32 scalars only when every amount survives the round trip, no hostname column when every
+// row's hostname id is its agent id, no allocation-role column when all rows agree, and the `ports` ranges as a dictionary of
+// the table's distinct range lists plus one list id per (slot, offer).  The engine widens all of it on the device, exactly.
+class PackedOffers {
+ public:
+  explicit PackedOffers(const EncodedCycle& c) : c_(c) {
+    const size_t N = (size_t)c.N;
+    pk_ = oe_offer_packing{};
+    // scalars
+    bool f32 = true;
+    for (double v : c.o_scalar) if (!((double)(float)v == v || v != v)) { f32 = false; break; }
+    pk_.scalar_is_f32 = f32 ? 1 : 0;
+    if (f32) { scalarF_.resize(c.o_scalar.size()); for (size_t k = 0; k < c.o_scalar.size(); ++k) scalarF_[k] = (float)c.o_scalar[k]; }
+    const int bits = c.S * c.K;
+    pk_.present_bytes = bits <= 8 ? 1 : bits <= 16 ? 2 : 4;
+    narrow(c.o_present, pk_.present_bytes, present_, false);
+    pk_.mount_profile_bytes = idBytes(64); narrow(c.o_mprof, pk_.mount_profile_bytes, mprof_, true);
+    pk_.zone_bytes = idBytes(c.dict.n_zones); narrow(c.o_zone, pk_.zone_bytes, zone_, true);
+    pk_.region_bytes = idBytes(c.dict.n_regions); narrow(c.o_region, pk_.region_bytes, region_, true);
+    pk_.attr_bytes = idBytes(c.dict.n_attrs); narrow(c.o_attr, pk_.attr_bytes, attr_, true);
+    pk_.rr_bytes = idBytes(c.dict.n_rr_values); narrow(c.o_rr, pk_.rr_bytes, rr_, true);
+    pk_.exec_bytes = idBytes(c.dict.n_exec_ids); narrow(c.o_exec, pk_.exec_bytes, exec_, true);
+    pk_.hostname_is_agent = c.o_host == c.o_agent ? 1 : 0;
+    bool constRole = true;
+    for (size_t i = 1; i < N && constRole; ++i) constRole = c.o_alloc[i] == c.o_alloc[0];
+    pk_.alloc_role_is_const = constRole ? 1 : 0;
+    pk_.alloc_role_const = constRole && N ? c.o_alloc[0] : -1;
+    // the distinct range lists, numbered in the order the rows bring them
+    pk_.port_tuple_bytes = 0;
+    const int R = c.R, S = c.S;
+    if (R > 0 && N > 0) {
+      std::map<std::vector<uint32_t>, uint32_t> seen;
+      std::vector<uint32_t> ids((size_t)S * N), list((size_t)R), last;
+      uint32_t lastId = 0;
+      bool have = false;
+      const size_t limit = std::max<size_t>(N, 4096) / 4;   // beyond this the dictionary is no shorter than the column
+      bool fits = true;
+      for (int s = 0; s < S && fits; ++s)
+        for (size_t i = 0; i < N; ++i) {
+          for (int r = 0; r < R; ++r) list[(size_t)r] = c.o_port[((size_t)s * R + r) * N + i];
+          if (have && list == last) { ids[(size_t)s * N + i] = lastId; continue; }   // most agents offer the list their neighbour offers
+          auto it = seen.find(list);
+          if (it == seen.end()) {
+            if (seen.size() >= limit) { fits = false; break; }
+            it = seen.emplace(list, (uint32_t)seen.size()).first;
+            tuples_.insert(tuples_.end(), list.begin(), list.end());
+          }
+          ids[(size_t)s * N + i] = it->second;
+          last = list; lastId = it->second; have = true;
+        }
+      if (fits) {
+        pk_.port_tuple_bytes = seen.size() <= 65536 ? 2 : 4;
+        pk_.n_port_tuples = (int32_t)seen.size();
+        narrow(ids, pk_.port_tuple_bytes, tupleId_, false);
+      } else {
+        tuples_.clear();
+      }
+    }
+  }
+  // the same oe_offer_table as EncodedCycle::offerTable(), its column pointers re-aimed at the narrow columns
+  oe_offer_table table() const {
+    oe_offer_table t = c_.offerTable();
+    if (pk_.scalar_is_f32) t.scalar = reinterpret_cast<const double*>(scalarF_.data());
+    t.scalar_present = reinterpret_cast<const uint32_t*>(present_.data());
+    t.mount_profile = reinterpret_cast<const int32_t*>(mprof_.data());
+    t.zone_id = reinterpret_cast<const int32_t*>(zone_.data());
+    t.region_id = reinterpret_cast<const int32_t*>(region_.data());
+    t.attr_id = reinterpret_cast<const int32_t*>(attr_.data());
+    t.rr_key = reinterpret_cast<const int32_t*>(rr_.data());
+    t.exec_id = reinterpret_cast<const int32_t*>(exec_.data());
+    if (pk_.hostname_is_agent) t.hostname_id = nullptr;
+    if (pk_.alloc_role_is_const) t.alloc_role = nullptr;
+    if (pk_.port_tuple_bytes) t.port_range = nullptr;
+    return t;
+  }
+  oe_offer_packing packing() const {
+    oe_offer_packing p = pk_;
+    p.port_tuples = tuples_.data();
+    p.port_tuple_id = tupleId_.data();
+    return p;
+  }
+  size_t bytes() const {   // what crosses the bus for the offer columns
+    const size_t N = (size_t)c_.N;
+    return (pk_.scalar_is_f32 ? scalarF_.size() * 4 : c_.o_scalar.size() * 8) + present_.size() + c_.o_msize.size() * 8 + mprof_.size() + zone_.size() +
+           region_.size() + attr_.size() + rr_.size() + exec_.size() + N * 4 + (pk_.hostname_is_agent ? 0 : N * 4) + (pk_.alloc_role_is_const ? 0 : N * 4) +
+           (pk_.port_tuple_bytes ? tuples_.size() * 4 + tupleId_.size() : c_.o_port.size() * 4);
+  }
+
+ private:
+  static uint8_t idBytes(int64_t dictSize) { return dictSize < 0xff ? 1 : dictSize < 0xffff ? 2 : 4; }
+  template <class T>
+  static void narrow(const std::vector<T>& src, int bytes, std::vector<uint8_t>& out, bool absentIsAllOnes) {
+    out.resize(src.size() * (size_t)bytes + 16);   // (+16: an empty column still has an address)
+    for (size_t k = 0; k < src.size(); ++k) {
+      const int64_t v = (int64_t)src[k];
+      if (bytes == 1) out[k] = (uint8_t)((absentIsAllOnes && v < 0) ? 0xff : v);
+      else if (bytes == 2) { const uint16_t w = (uint16_t)((absentIsAllOnes && v < 0) ? 0xffff : v); std::memcpy(&out[k * 2], &w, 2); }
+      else { const uint32_t w = (uint32_t)v; std::memcpy(&out[k * 4], &w, 4); }
+    }
+    out.resize(src.size() * (size_t)bytes);
+    if (out.empty()) out.reserve(16);
+  }
+  const EncodedCycle& c_;
+  oe_offer_packing pk_{};
+  std::vector<float> scalarF_;
+  std::vector<uint8_t> present_, mprof_, zone_, region_, attr_, rr_, exec_, tupleId_;
+  std::vector<uint32_t> tuples_;
+};
+
 // One requirement as the encoder sees it: either a full pod pipeline or (for rule-level tests, the counterpart of
 // calling PlacementRule.filter directly) just a rule.
 struct EncoderRequirement {

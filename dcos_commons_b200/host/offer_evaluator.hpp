@@ -14,6 +14,7 @@
 #pragma once
 #include <algorithm>
 #include <dlfcn.h>
+#include <cstdlib>
 
 #include <functional>
 #include <set>
@@ -51,6 +52,7 @@ class EngineLibrary {
   int32_t (*load_tasks)(oe_engine*, const oe_task_table*) = nullptr;
   int32_t (*load_offers)(oe_engine*, const oe_offer_table*) = nullptr;
   int32_t (*update_offers)(oe_engine*, const int64_t*, int64_t, const oe_offer_table*) = nullptr;
+  int32_t (*load_offers_packed)(oe_engine*, const oe_offer_table*, const oe_offer_packing*) = nullptr;   // optional: null when the library has only the plain load
   int32_t (*load_requirements)(oe_engine*, const oe_req_table*) = nullptr;
   int64_t (*matrix_stride_words)(const oe_engine*) = nullptr;
   int32_t (*feasibility)(oe_engine*, uint32_t*, oe_stats*) = nullptr;
@@ -72,6 +74,7 @@ class EngineLibrary {
     feasibility = (decltype(feasibility))symbol("oe_feasibility"); evaluate_cycle = (decltype(evaluate_cycle))symbol("oe_evaluate_cycle");
     apply_launches = (decltype(apply_launches))symbol("oe_apply_launches");
     unexpected_resources = (decltype(unexpected_resources))symbol("oe_unexpected_resources");
+    try { load_offers_packed = (decltype(load_offers_packed))symbol("oe_load_offers_packed"); } catch (const std::runtime_error&) { load_offers_packed = nullptr; }
   }
 };
 
@@ -97,6 +100,13 @@ class Engine {
     if (c.resident && !c.full_reload) {
       if (!c.delta_rows.empty()) check(lib_.update_offers(h_, c.delta_rows.data(), (int64_t)c.delta_rows.size(), &o), "oe_update_offers");
       ++deltaLoads; rowsSent += (int64_t)c.delta_rows.size();
+    } else if (lib_.load_offers_packed && packedWire) {
+      // a whole table goes over the bus in its compact form (PackedOffers); rows replaced later arrive at full width
+      const PackedOffers packed(c);
+      const oe_offer_table po = packed.table();
+      const oe_offer_packing pk = packed.packing();
+      check(lib_.load_offers_packed(h_, &po, &pk), "oe_load_offers_packed");
+      ++fullLoads; rowsSent += c.N; offerBytesSent += (int64_t)packed.bytes();
     } else {
       check(lib_.load_offers(h_, &o), "oe_load_offers");
       ++fullLoads; rowsSent += c.N;
@@ -105,6 +115,9 @@ class Engine {
     M_ = c.M; N_ = c.resident ? c.N_resident : c.N;
   }
   int64_t fullLoads = 0, deltaLoads = 0, rowsSent = 0;   // what crossed the boundary so far (tests, diagnostics)
+  int64_t offerBytesSent = 0;                            // ... bytes of the packed whole-table loads among them
+  // OE_HOST_WIRE=plain in the environment: whole tables at full width (oe_load_offers) although the library can take them packed
+  bool packedWire = [] { const char* w = std::getenv("OE_HOST_WIRE"); return !(w && std::string(w) == "plain"); }();
   std::vector<oe_decision> evaluateCycle() {
     std::vector<oe_decision> d((size_t)std::max<int64_t>(M_, 1));
     oe_stats st{};
@@ -275,7 +288,9 @@ class OfferEvaluator {
     std::vector<EncoderRequirement> ers = encoderRequirements(requirements, allTasks);
     EncodedCycle c = enc.encode(offers, allTasks, ers);
     Engine e(lib_);
+    e.packedWire = e.packedWire && packedWire;
     e.load(c);
+    offerBytesSent += e.offerBytesSent;
     const std::vector<oe_decision> dec = e.evaluateCycle();
     lastDecisions_ = dec;
     for (size_t j = 0; j < requirements.size(); ++j)
@@ -324,6 +339,8 @@ class OfferEvaluator {
     return out;
   }
   const Engine* residentEngine(const ResidentOffers& r) const { return r.engine_.get(); }
+  bool packedWire = true;        // false: whole offer tables cross the boundary at full width (oe_load_offers)
+  int64_t offerBytesSent = 0;    // offer-column bytes of the packed whole-table loads of evaluateCycle(requirements, offers)
 
   // The two halves of evaluateCycle, for callers that put several services' requirements into ONE engine cycle
   // (MultiServiceEventClient below).  `requirements` must outlive the returned vector.

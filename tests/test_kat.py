@@ -29,11 +29,11 @@ def _names():
 NAMES = _names()
 
 
-def _run(lib, prefix, names):
+def _run(lib, prefix, names, env=None):
     cmd = [RUNNER, "--lib", lib, "--prefix", prefix]
     for n in names:
         cmd += ["--test", n]
-    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, **(env or {})))
     verdict = {}
     for line in p.stdout.splitlines():
         if line.startswith("PASS "):
@@ -73,3 +73,13 @@ def engine_verdicts():
 def test_engine_matches_reference_vector(engine_verdicts, name):
     assert name in engine_verdicts, f"{name} did not run"
     assert engine_verdicts[name] is None, engine_verdicts[name]
+
+
+@pytest.mark.gpu
+def test_engine_matches_every_vector_with_full_width_offer_tables(engine_verdicts):
+    """The host layer sends whole offer tables in their packed form when the library takes it (oe_load_offers_packed); the same
+    vectors through the plain oe_load_offers must give the same verdicts."""
+    rc, verdict, out = _run(ENGINE, "oe_", [], env={"OE_HOST_WIRE": "plain"})
+    assert set(verdict) == set(engine_verdicts), out
+    failed = {k: v for k, v in verdict.items() if v is not None}
+    assert not failed, failed
