@@ -783,6 +783,9 @@ struct RowBits {
   int rows;
   int64_t shard_words;  // words of one shard in global word index space (== stride when not sharded)
   int64_t total_words;  // global words that hold offers
+  const int* skip_ptr;  // commit passes after the first (offer table arriving in chunks): nothing to do once *skip_ptr >= skip_at
+  int skip_at;          // (every requirement placed); null: always run
+  __device__ __forceinline__ bool skipped() const { return skip_ptr && *skip_ptr >= skip_at; }
   __device__ __forceinline__ uint32_t word(int row, int64_t gw) const {
     const int64_t shard = gw / shard_words, lw = gw - shard * shard_words;
     return F[(shard * rows + row) * stride + lw];
@@ -899,6 +902,7 @@ __global__ void __launch_bounds__(256) k_compact_rows(RowBits rb, int tiles, con
                          // each, walking a chain of rows^2 dependent tests: 41 us on C5)
 __global__ void __launch_bounds__(128 * OE_ADJ_SPLIT) k_row_overlap(RowBits rb, unsigned long long* __restrict__ adj) {
   __shared__ uint32_t tile[OE_ADJ_MAX_ROWS][128];
+  if (rb.skipped()) return;
   const int x = threadIdx.x & 127, y = threadIdx.x >> 7;
   const int64_t gw = (int64_t)blockIdx.x * 128 + x;
   for (int r = y; r < rb.rows; r += OE_ADJ_SPLIT) tile[r][x] = gw < rb.total_words ? rb.word(r, gw) : 0u;
@@ -1675,8 +1679,13 @@ struct RowGroups {
   int* comp_row_begin;  // [rows + 1]
   int* info;            // [2]
 };
-__global__ void __launch_bounds__(256) k_group_rows(int rows, const unsigned long long* __restrict__ adj, int* __restrict__ parent, RowGroups g) {
+__global__ void __launch_bounds__(256) k_group_rows(int rows, const unsigned long long* __restrict__ adj, int* __restrict__ parent, RowGroups g,
+                                                    const int* __restrict__ skip_ptr, int skip_at) {
   extern __shared__ int grp_smem[];
+  if (skip_ptr && *skip_ptr >= skip_at) {   // a later commit pass with nothing left to place: no components, so that every kernel behind this one idles
+    if (threadIdx.x == 0) { g.info[0] = 0; g.info[1] = 0; }
+    return;
+  }
   int* comp = grp_smem;           // [rows]
   int* count = comp + rows;       // [rows]
   int* begin = count + rows;      // [rows + 1]
@@ -1728,6 +1737,7 @@ __global__ void __launch_bounds__(256) k_offer_masks(RowBits rb, const int* __re
   extern __shared__ int om_smem[];
   const int rows = rb.rows;
   const int n_comp = info[0];
+  if (n_comp == 0 && rb.skip_ptr) return;   // (k_group_rows found nothing left to place)
   int* s_comp = om_smem;                 // [rows]
   int* s_lrow = s_comp + rows;           // [rows]
   int* s_hist = s_lrow + rows;           // [rows] (n_comp <= rows)
@@ -1837,8 +1847,9 @@ __global__ void __launch_bounds__(1024) k_key_scan(const int* __restrict__ total
 }
 __global__ void __launch_bounds__(32) k_key_scatter(const int32_t* __restrict__ keys, int64_t n, int key_stride, const int* __restrict__ hist,
                                                     const int* __restrict__ key_begin, const uint32_t* __restrict__ aux, int32_t* __restrict__ out_idx,
-                                                    uint32_t* __restrict__ out_aux) {
+                                                    uint32_t* __restrict__ out_aux, const int* __restrict__ n_keys_gate = nullptr) {
   extern __shared__ int ks_run[];   // [key_stride]: next slot of every key for this block
+  if (n_keys_gate && *n_keys_gate == 0) return;   // no keys at all (a skipped commit pass): `keys` was not written either
   const int lane = threadIdx.x;
   const int64_t lo = (int64_t)blockIdx.x * OE_OS_SORT_BLOCK;
   // only the keys this block holds are looked at, so only those are initialised: first touch below
@@ -4101,7 +4112,7 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
 // expand_beside (oe_evaluate_cycle with OE_CFG_MATERIALIZE_MATRIX): the matrix columns of every chunk but the last are expanded on
 // the auxiliary stream as soon as the chunk's class bits exist; the last chunk's are left to the fork at the commit launch.
 int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = false, bool expand_last = false,
-                          const std::function<int()>* after_prefix = nullptr, int prefix_chunk = -1) {
+                          const std::function<int(int)>* after_chunk = nullptr) {
   const int64_t stride = h->stride();
   h->V_eff = -1;
   const int rows_all = h->C + h->V;   // every class and every re-deployed requirement
@@ -4240,7 +4251,7 @@ int run_class_feasibility(oe_engine* h, int64_t* launches, bool expand_beside = 
         if (int rc = run_expand(h, launches, h->aux_stream, w0, w1)) return rc;
         h->expand_from_word = w1;
       }
-      if (after_prefix && c == prefix_chunk) if (int rc = (*after_prefix)()) return rc;
+      if (after_chunk && c + 1 < n_chunks) if (int rc = (*after_chunk)(c)) return rc;
     }
     h->offers_in_flight = false;
     if (h->peers_attached) {
@@ -4453,7 +4464,7 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
   g.comp_of = h->d_os_groups.as<int>(); g.lrow = g.comp_of + rows; g.comp_rows = g.lrow + rows; g.comp_row_begin = g.comp_rows + rows;
   CU(h->d_os_comp_begin.ensure(((size_t)rows + 4) * sizeof(int)));
   g.info = h->d_os_comp_begin.as<int>() + rows + 1;
-  k_group_rows<<<1, 256, ((size_t)rows * 3 + 1) * sizeof(int), st>>>(rows, adj, parent, g);
+  k_group_rows<<<1, 256, ((size_t)rows * 3 + 1) * sizeof(int), st>>>(rows, adj, parent, g, rb.skip_ptr, rb.skip_at);
   ++*launches;
   CU(cudaGetLastError());
   int n_ctas = rows;
@@ -4472,7 +4483,7 @@ int commit_offers_pass(oe_engine* h, int64_t* launches, const RowBits& rb, int32
   k_key_scan_cols<<<n_ctas, 1024, 0, st>>>(h->d_os_ohist.as<int>(), nb, g.info, 0, h->d_os_totals.as<int>());
   k_key_scan<<<1, 1024, 0, st>>>(h->d_os_totals.as<int>(), g.info, 0, h->d_os_comp_begin.as<int>());
   k_key_scatter<<<nb, 32, (size_t)rows * sizeof(int), st>>>(h->d_os_ocomp.as<int32_t>(), n_offers, rows, h->d_os_ohist.as<int>(), h->d_os_comp_begin.as<int>(),
-                                                          h->d_os_omask.as<uint32_t>(), h->d_os_list.as<int32_t>(), h->d_os_mask.as<uint32_t>());
+                                                          h->d_os_omask.as<uint32_t>(), h->d_os_list.as<int32_t>(), h->d_os_mask.as<uint32_t>(), rb.skip_ptr ? g.info : nullptr);
   *launches += 3;
   CU(cudaGetLastError());
   OfferSideArgs a{};
@@ -4763,34 +4774,51 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
       // and only the requirements it left open are committed over the last chunk afterwards.
       two_pass = true;
       const int64_t stride = h->stride();
-      // Which prefix: all but the last chunk.  (An earlier one finishes its pass sooner but leaves more to the second pass; measured
-      // on the C5 workloads it gains 0.3 ms with MaxPerHostname rules and loses 0.1 ms with the matrix.  OE_PREFIX_CHUNK tries it.)
-      int prefix_chunk = h->n_chunks - 2;
+      // Which prefixes.  From the offers' side (os_two_pass) a pass simply resumes from the rows' queue positions, and a pass that
+      // finds every requirement placed costs a few idle launches (the device decides: RowBits::skip_ptr) — so there are up to
+      // three: an EARLY one behind the first chunks that hold four offers per requirement (usually everything is placed there, long
+      // before the last chunk lands), one behind all chunks but the last, one over the last.  No host round trip in between.
+      // Measured (C5 shapes, decisions cycle, pass after chunk 1 of 4 instead of chunk 2 only): c5 1.54 -> 1.35 ms, MaxPerHostname
+      // 4.88 -> 4.54, one region 2.03 -> 1.95; with the matrix 3.02 -> 2.82.  OE_PREFIX_CHUNK = first pass after that chunk.
+      // The union commit (more than 32 bit rows cannot happen here, but OE_COMMIT=union) keeps its two passes.
+      int early_chunk = h->n_chunks - 2;
+      if (os_two_pass) for (int c = 0; c < h->n_chunks - 2; ++c) if (h->chunks[c].r1 >= 4 * h->M) { early_chunk = c; break; }
       static const char* prefix_env = getenv("OE_PREFIX_CHUNK");
-      if (prefix_env) prefix_chunk = std::max(0, std::min(h->n_chunks - 2, atoi(prefix_env)));
-      const int64_t wA = h->chunks[prefix_chunk].r1 / 32, wT = (h->N + 31) / 32;
+      if (prefix_env) early_chunk = std::max(0, std::min(h->n_chunks - 2, atoi(prefix_env)));
+      const int64_t wA = h->chunks[h->n_chunks - 2].r1 / 32, wT = (h->N + 31) / 32;
       CU(h->d_dec.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_dec_sub.ensure(std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision)));
       CU(h->d_sub_idx.ensure((size_t)h->M * 4)); CU(h->d_sub_row.ensure((size_t)h->M * 4));
       CU(h->d_tile_open.ensure(((size_t)h->M + 1023) / 1024 * 4));
       if (want_matrix) CU(h->d_matrix.ensure(std::max<size_t>((size_t)h->M * stride, 1) * 4));
       int* h_open = h->h_offer_err + oe_engine::kMaxChunks;
-      const std::function<int()> prefix_commit = [&]() -> int {
-        CU(cudaEventRecord(h->ev_prefix, h->stream));
-        CU(cudaStreamWaitEvent(h->hi_stream, h->ev_prefix, 0));
-        RowBits rbA{};
-        rbA.F = h->d_F.as<uint32_t>(); rbA.stride = stride; rbA.rows = rows; rbA.shard_words = stride; rbA.total_words = wA;
-        if (os_two_pass) {
-          // from the offers' side a later pass simply resumes from the rows' queue positions: nothing to collect in between
+      int64_t w_done = 0;   // words of the class rows the passes enqueued so far have covered
+      const auto offers_pass = [&](int64_t w1) -> int {
+        RowBits rb{};
+        rb.F = h->d_F.as<uint32_t>() + w_done; rb.stride = stride; rb.rows = rows; rb.shard_words = stride; rb.total_words = w1 - w_done;
+        if (w_done == 0) {
           k_clear_decisions<<<(unsigned)((h->M + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec.as<oe_decision>(), h->M);
           CU(cudaMemsetAsync(h->d_nplaced.p, 0, sizeof(int), h->hi_stream));
           if (int rc = queues_ready(h, &launches, rows, h->hi_stream)) return rc;
-          if (int rc = commit_offers_pass(h, &launches, rbA, 0, h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
-          CU(cudaMemcpyAsync(h_open, h->d_nplaced.p, sizeof(int), cudaMemcpyDeviceToHost, h->hi_stream));
-          CU(cudaEventRecord(h->ev_phase_a, h->hi_stream));
+        } else {
+          rb.skip_ptr = h->d_nplaced.as<int>(); rb.skip_at = (int)h->M;
+        }
+        if (int rc = commit_offers_pass(h, &launches, rb, (int32_t)(w_done * 32), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>()))
+          return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
+        w_done = w1;
+        return 0;
+      };
+      const std::function<int(int)> prefix_commit = [&](int c) -> int {
+        if (c != h->n_chunks - 2 && !(os_two_pass && c == early_chunk)) return 0;
+        CU(cudaEventRecord(h->ev_prefix, h->stream));
+        CU(cudaStreamWaitEvent(h->hi_stream, h->ev_prefix, 0));
+        if (os_two_pass) {
+          if (int rc = offers_pass(h->chunks[c].r1 / 32)) return rc;
           tr.mark("prefix_commit_enqueued");
           return 0;
         }
+        RowBits rbA{};
+        rbA.F = h->d_F.as<uint32_t>(); rbA.stride = stride; rbA.rows = rows; rbA.shard_words = stride; rbA.total_words = wA;
         CU(cudaMemsetAsync(h->d_dec.p, 0, std::max<size_t>((size_t)h->M, 1) * sizeof(oe_decision), h->hi_stream));
         if (int rc = commit_union_pass(h, &launches, rbA, h->bit_row_of_req(), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, true, false, false)) return rc;
         const unsigned n_tiles = (unsigned)((h->M + 1023) / 1024);
@@ -4804,27 +4832,28 @@ int32_t oe_evaluate_cycle(oe_engine* h, oe_decision* out, oe_stats* stats) {
         tr.mark("prefix_commit_enqueued");
         return 0;
       };
-      if (int rc = run_class_feasibility(h, &launches, want_matrix, true, &prefix_commit, prefix_chunk)) return rc;
+      if (int rc = run_class_feasibility(h, &launches, want_matrix, true, &prefix_commit)) return rc;
       CU(cudaEventRecord(h->ev[2], h->stream));
       CU(cudaEventRecord(h->ev[3], h->stream));
       CU(cudaEventRecord(h->ev_k1_last, h->stream));
       if (want_matrix) { expand_overlapped = true; CU(cudaEventRecord(h->ev_x1, h->aux_stream)); }
       tr.mark("last_chunk_enqueued");
-      CU(cudaEventSynchronize(h->ev_phase_a));
-      const int n_open = os_two_pass ? (int)(h->M - *h_open) : *h_open;
-      tr.mark("prefix_commit_done");
-      CU(cudaStreamWaitEvent(h->hi_stream, h->ev_k1_last, 0));
-      if (n_open > 0 && os_two_pass) {
-        RowBits rbB{};
-        rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
-        if (int rc = commit_offers_pass(h, &launches, rbB, (int32_t)(wA * 32), h->M, h->d_dec.as<oe_decision>(), h->hi_stream, false, false, h->d_req_row.as<int32_t>())) return rc < 0 ? rc : h->fail(OE_ERR_STATE, "commit: unexpected fallback");
-      } else if (n_open > 0) {
-        RowBits rbB{};
-        rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
-        if (int rc = commit_union_pass(h, &launches, rbB, h->d_sub_row.as<int32_t>(), n_open, h->d_dec_sub.as<oe_decision>(), h->hi_stream, false, false, false)) return rc;
-        k_merge_unplaced<<<(unsigned)((n_open + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec_sub.as<oe_decision>(), h->d_sub_idx.as<int32_t>(), n_open, (int32_t)(wA * 32),
-                                                                                  h->d_dec.as<oe_decision>());
-        ++launches;
+      if (os_two_pass) {
+        CU(cudaStreamWaitEvent(h->hi_stream, h->ev_k1_last, 0));
+        if (int rc = offers_pass(wT)) return rc;
+      } else {
+        CU(cudaEventSynchronize(h->ev_phase_a));
+        const int n_open = *h_open;
+        tr.mark("prefix_commit_done");
+        CU(cudaStreamWaitEvent(h->hi_stream, h->ev_k1_last, 0));
+        if (n_open > 0) {
+          RowBits rbB{};
+          rbB.F = h->d_F.as<uint32_t>() + wA; rbB.stride = stride; rbB.rows = rows; rbB.shard_words = stride; rbB.total_words = wT - wA;
+          if (int rc = commit_union_pass(h, &launches, rbB, h->d_sub_row.as<int32_t>(), n_open, h->d_dec_sub.as<oe_decision>(), h->hi_stream, false, false, false)) return rc;
+          k_merge_unplaced<<<(unsigned)((n_open + 255) / 256), 256, 0, h->hi_stream>>>(h->d_dec_sub.as<oe_decision>(), h->d_sub_idx.as<int32_t>(), n_open, (int32_t)(wA * 32),
+                                                                                    h->d_dec.as<oe_decision>());
+          ++launches;
+        }
       }
       k_materialize<<<(unsigned)((h->M + 127) / 128), 128, 0, h->hi_stream>>>(h->ctx(), h->d_req_row.as<int32_t>(), h->M, h->d_dec.as<oe_decision>(), h->d_nplaced.as<int>() + 1, decision_push(h));
       ++launches;

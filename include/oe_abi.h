@@ -386,7 +386,10 @@ int32_t oe_load_offers(oe_engine* h, const oe_offer_table* t);
  * row k of `values`, a table of n_rows rows with the same slot counts as the resident one (n_offers = n_rows; row_offset,
  * n_offers_global and shard_rows are ignored).  A withdrawn offer is a row whose scalar_present is 0 and whose port ranges
  * are all OE_PORT_EMPTY: nothing fits it.  Tables with a reserved side table (resident or in `values`) cannot be patched —
- * OE_ERR_STATE, reload with oe_load_offers.  Dictionary ids are validated like those of a load.                          */
+ * OE_ERR_STATE, reload with oe_load_offers.  Dictionary ids are validated like those of a load.  `values` is always at full
+ * width, also when the resident table was loaded with oe_load_offers_packed: the engine looks the replaced rows' `ports` range
+ * lists up in the resident list dictionary and appends the lists nobody had (room for max(4096, a quarter) more than were
+ * loaded; beyond that the feasibility pass goes back to per-offer port tests until the table is loaded whole again).        */
 int32_t oe_update_offers(oe_engine* h, const int64_t* rows, int64_t n_rows, const oe_offer_table* values);
 int32_t oe_load_requirements(oe_engine* h, const oe_req_table* t);
 
