@@ -558,7 +558,7 @@ def run_engine(args):
     # DRAM bytes and warp instructions per launch: measured by a two-pass ncu run of this same workload and shard right now;
     # when ncu cannot run here, the committed capture of the headline configuration (one GPU) or null, and the line says which
     probe, probe_src = (None, "--no-ncu") if args.no_ncu else ncu_probe(args, f"{lo},{hi},{shard_rows},{rank},{world}")
-    traffic = insts = None
+    traffic = insts = k1_ncu_ns = None
     if probe and dom["kernel"] in probe:
         traffic = int(probe[dom["kernel"]].get("dram__bytes_read.sum", 0) + probe[dom["kernel"]].get("dram__bytes_write.sum", 0))
         traffic_src = probe_src
@@ -572,14 +572,19 @@ def run_engine(args):
                 traffic_src = f"committed capture profiles/kernel_traffic.json ({probe_src})"
     if probe and "k_class_feasibility" in probe:
         insts = probe["k_class_feasibility"].get("smsp__inst_executed.sum")
+        k1_ncu_ns = probe["k_class_feasibility"].get("gpu__time_duration.sum")
     # the feasibility kernel is bound by issue slots, not by HBM — 148 SMs x 4 schedulers x SM clock
     sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
     rows_evaluated = eng.factored_rows()
     issue = {"kernel": "k_class_feasibility", "warp_inst": insts, "inst_per_pair": insts * 32 / max(n_local * rows_evaluated, 1) if insts else None,
              "issue_slots_per_s": 148 * 4 * sm_hz, "issue_frac": insts / (148 * 4 * sm_hz * k1_ms * 1e-3) if insts and k1_ms else None,
              "pairs": n_local * rows_evaluated, "ms": k1_ms, "hbm_frac": (ab["k1"] / (k1_ms * 1e-3) / 1e9 / peak) if k1_ms else None,
+             "kernel_ms_under_ncu": k1_ncu_ns * 1e-6 if k1_ncu_ns else None,
+             "issue_frac_kernel_alone": insts / (148 * 4 * sm_hz * k1_ncu_ns * 1e-9) if insts and k1_ncu_ns else None,
              "source": probe_src if insts else f"null: {probe_src}",
-             "note": "pairs = offers x factored bit rows (classes + re-deployed pods); inst_per_pair = warp instructions x 32 lanes / pairs"}
+             "note": "pairs = offers x factored bit rows (classes + re-deployed pods); inst_per_pair = warp instructions x 32 lanes / pairs; "
+                     "ms = live CUDA-event time of the feasibility phase (the rule / port / transpose table kernels and their launch gaps included), "
+                     "kernel_ms_under_ncu = the kernel's own duration in the ncu pass (serialised, cold cache)"}
     roofline = {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s",
                 "frac": dom["achieved_gbs"] / peak if dom["achieved_gbs"] else None, "traffic": traffic,
                 "traffic_source": traffic_src,

@@ -1951,27 +1951,23 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     // step advances its read address by one slot, no wrap.  Topped up four entries (16 bytes) per cp.async.
     const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring) + lane * (uint32_t)(OE_OS_LANE_SLOTS * 4);
     int filled = pos & ~3;   // entries below `filled` are staged (or on their way); groups of four, aligned in the queue array
-    auto top_up = [&]() {
-      const int upto = pos + 96;
-      for (; filled < upto; filled += 4) {
-        const uint32_t slot = (uint32_t)filled & (OE_OS_RING - 1);
-        const uint32_t dst = ring_base + slot * 4u;
-        if (filled + 4 <= end) {
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(Q + filled) : "memory");
-          if (slot < OE_OS_MIRROR) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + OE_OS_RING * 4u), "l"(Q + filled) : "memory");
-        } else {   // the queue's end: what is left of it entry by entry, "nobody waiting" behind it (a step needs no bound check)
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t d = dst + (uint32_t)q * 4u;
-            if (filled + q < end) {
-              cp_async_4(d, Q + filled + q);
-              if (slot < OE_OS_MIRROR) cp_async_4(d + OE_OS_RING * 4u, Q + filled + q);
-            } else {
-              asm volatile("st.shared.s32 [%0], %1;" ::"r"(d), "r"(OE_OS_NONE) : "memory");
-              if (slot < OE_OS_MIRROR) asm volatile("st.shared.s32 [%0], %1;" ::"r"(d + OE_OS_RING * 4u), "r"(OE_OS_NONE) : "memory");
-            }
-          }
-        }
-      }
+    // One group of four entries (16 bytes, aligned in the queue array) per call, branch-free (a taken branch costs a lone warp ~19
+    // cycles: the former loop was 260 cycles per chunk): the calls are spread over the steps of a chunk.  Entries behind the
+    // queue's end are never staged (the array is padded, so the last group may read up to three entries of whatever follows);
+    // the step replaces what it reads there by "nobody waiting" (ra_end below).
+    int upto = pos + 96;
+    auto stage_group = [&]() {
+      const int go = filled < upto && filled < end;
+      const uint32_t slot = (uint32_t)filled & (OE_OS_RING - 1);
+      const uint32_t dst = ring_base + slot * 4u;
+      const int go_mirror = go && slot < OE_OS_MIRROR;
+      asm volatile("{ .reg .pred p; setp.ne.b32 p, %2, 0; @p cp.async.cg.shared.global [%0], [%1], 16; }" ::"r"(dst), "l"(Q + filled), "r"(go) : "memory");
+      asm volatile("{ .reg .pred p; setp.ne.b32 p, %2, 0; @p cp.async.cg.shared.global [%0], [%1], 16; }" ::"r"(dst + OE_OS_RING * 4u), "l"(Q + filled), "r"(go_mirror) : "memory");
+      filled += go ? 4 : 0;
+    };
+    auto top_up = [&]() {   // (before the first chunk: everything at once)
+      upto = pos + 96;
+      for (int g = 0; g < 26; ++g) stage_group();
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
     top_up();
@@ -1979,12 +1975,28 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
     __syncwarp();
     int h = lds_s32(ring_base + ((uint32_t)pos & (OE_OS_RING - 1)) * 4u);
     int n1 = lds_s32(ring_base + ((uint32_t)(pos + 1) & (OE_OS_RING - 1)) * 4u);
-    if (row < 0) h = n1 = OE_OS_NONE;
+    if (pos >= end) h = OE_OS_NONE;        // (also the lanes without a row: pos = end = 0)
+    if (pos + 1 >= end) n1 = OE_OS_NONE;
     int o_next = e0 + lane < e1 ? __ldg(a.list + e0 + lane) : -1;
     uint32_t m_next = e0 + lane < e1 ? __ldg(a.mask + e0 + lane) : 0u;
+    // Which offers of a chunk list MY row: the 32 x 32 bit matrix (lane = offer, bit = row) transposed with five butterfly
+    // exchanges, so that a step needs no shuffle to learn it (bit e of lane r <- bit r of lane e).  The exchanges for the NEXT
+    // chunk are spread over the steps of this one — the step's chain leaves most issue slots idle — and so is the ring's top-up.
+    auto butterfly = [&](uint32_t x, int j) -> uint32_t {
+      const uint32_t keep = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;   // bit positions with bit j clear
+      const uint32_t other = __shfl_xor_sync(0xffffffffu, x, j);
+      return (lane & j) ? ((x & ~keep) | ((other >> j) & keep)) : ((x & keep) | ((other << j) & ~keep));
+    };
+    auto transposed = [&](uint32_t x) -> uint32_t {
+#pragma unroll
+      for (int j = 16; j >= 1; j >>= 1) x = butterfly(x, j);
+      return x;
+    };
+    uint32_t mybits_next = transposed(m_next);
     for (int base = e0; base < e1; base += 32) {
       const int o_mine = o_next + a.offer_offset;
       const uint32_t m_mine = m_next;
+      const uint32_t mybits = mybits_next;
       {  // the chunk after this one, a chunk ahead of its use
         const int e = base + 32 + lane;
         o_next = e < e1 ? __ldg(a.list + e) : -1;
@@ -1995,32 +2007,32 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
       const uint32_t want = __ballot_sync(0xffffffffu, (m_mine & active) != 0u);
       ++chunks;
       skipped += want == 0u;
-      if (!want) continue;
-      asm volatile("cp.async.wait_group 0;" ::: "memory");   // the entries asked for a chunk ago
-      __syncwarp();
-      top_up();
-      // which offers of the chunk list MY row: the 32 x 32 bit matrix (lane = offer, bit = row) transposed with five butterfly
-      // exchanges, so that a step needs no shuffle to learn it (bit e of lane r <- bit r of lane e)
-      uint32_t mybits = m_mine;
-#pragma unroll
-      for (int j = 16; j >= 1; j >>= 1) {
-        const uint32_t keep = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;   // bit positions with bit j clear
-        const uint32_t other = __shfl_xor_sync(0xffffffffu, mybits, j);
-        mybits = (lane & j) ? ((mybits & ~keep) | ((other >> j) & keep)) : ((mybits & keep) | ((other << j) & ~keep));
-      }
+      if (!want) { mybits_next = transposed(m_next); continue; }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");   // the entries asked for a chunk ago (a lane reads only what it staged itself)
       // 32 steps, one per offer of the chunk, straight line (a lone warp pays ~4 cycles per instruction issued, so the step is
       // counted in instructions).  Chain from step to step: select (my row listed ? head : none) -> REDUX.MIN -> compare ->
       // select (head <- n1).  The entry behind n1 is read at the top of a step and moves into n1 at the top of the NEXT one,
       // so its load never stalls the chain; the match is kept by the lane that holds the offer and stored after the chunk.
       const uint32_t ra0 = ring_base + ((uint32_t)(pos + 2) & (OE_OS_RING - 1)) * 4u;
       uint32_t ra = ra0;          // shared address of entry pos + 2
+      const int ra_left0 = end - (pos + 2);   // entries of the queue from entry pos + 2 on (<= 0: none)
       int match = OE_OS_NONE;     // requirement that gets MY offer of this chunk
       bool won_prev = false;
       int nxt_prev = OE_OS_NONE;
+      uint32_t tb = 0u;           // the next chunk's masks on their way through the butterfly
+      upto = pos + 96;
 #pragma unroll
       for (int e = 0; e < 32; ++e) {
+        if (e < 24 && e % 3 == 1) stage_group();    // eight groups: what the chunk before consumed (at most 32 entries)
+        if (e == 24) asm volatile("cp.async.commit_group;" ::: "memory");
+        if (e == 17) tb = butterfly(m_next, 16);    // (m_next was asked for ~700 cycles ago)
+        if (e == 20) tb = butterfly(tb, 8);
+        if (e == 23) tb = butterfly(tb, 4);
+        if (e == 26) tb = butterfly(tb, 2);
+        if (e == 29) tb = butterfly(tb, 1);
         n1 = won_prev ? nxt_prev : n1;
-        const int nxt = lds_s32(ra);
+        int nxt = lds_s32(ra);
+        nxt = (int)((ra - ra0) >> 2) < ra_left0 ? nxt : OE_OS_NONE;   // behind the queue's end: nobody waiting
         const bool listed = (mybits >> e) & 1u;
         const int v = listed ? h : OE_OS_NONE;
         const int mn = __reduce_min_sync(0xffffffffu, v);   // the requirement that gets offer e, known to every lane
@@ -2032,6 +2044,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
         nxt_prev = nxt;
       }
       n1 = won_prev ? nxt_prev : n1;
+      mybits_next = tb;
       pos += (int)((ra - ra0) >> 2);
       steps += 32;
       if (match != OE_OS_NONE) dec_row[(size_t)match * DEC_INTS] = o_mine;
@@ -4418,7 +4431,7 @@ int prepare_queues(oe_engine* h, int64_t* launches, const int32_t* req_row, int6
   const int nb = (int)std::max<int64_t>(1, (M + OE_OS_SORT_BLOCK - 1) / OE_OS_SORT_BLOCK);
   CU(h->d_os_rhist.ensure((size_t)nb * rows * sizeof(int)));
   CU(h->d_os_row_begin.ensure(((size_t)rows + 1) * sizeof(int)));
-  CU(h->d_os_queue.ensure(std::max<size_t>((size_t)M, 1) * sizeof(int32_t)));
+  CU(h->d_os_queue.ensure(((size_t)M + 8) * sizeof(int32_t)));
   CU(h->d_os_cursor.ensure((size_t)rows * sizeof(int)));
   CU(cudaMemsetAsync(h->d_os_cursor.p, 0, (size_t)rows * sizeof(int), st));
   k_key_hist<<<nb, 256, (size_t)rows * sizeof(int), st>>>(req_row, M, rows, h->d_os_rhist.as<int>());
