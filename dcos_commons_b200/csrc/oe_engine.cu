@@ -2015,7 +2015,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
       // so its load never stalls the chain; the match is kept by the lane that holds the offer and stored after the chunk.
       const uint32_t ra0 = ring_base + ((uint32_t)(pos + 2) & (OE_OS_RING - 1)) * 4u;
       uint32_t ra = ra0;          // shared address of entry pos + 2
-      const int ra_left0 = end - (pos + 2);   // entries of the queue from entry pos + 2 on (<= 0: none)
+      const int ra_end = (int)ra0 + (end - (pos + 2)) * 4;   // address behind the queue's last entry (at or below ra0: nothing left)
       int match = OE_OS_NONE;     // requirement that gets MY offer of this chunk
       bool won_prev = false;
       int nxt_prev = OE_OS_NONE;
@@ -2032,11 +2032,11 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
         if (e == 29) tb = butterfly(tb, 1);
         n1 = won_prev ? nxt_prev : n1;
         int nxt = lds_s32(ra);
-        nxt = (int)((ra - ra0) >> 2) < ra_left0 ? nxt : OE_OS_NONE;   // behind the queue's end: nobody waiting
+        nxt = (int)ra < ra_end ? nxt : OE_OS_NONE;   // behind the queue's end: nobody waiting
         const bool listed = (mybits >> e) & 1u;
         const int v = listed ? h : OE_OS_NONE;
         const int mn = __reduce_min_sync(0xffffffffu, v);   // the requirement that gets offer e, known to every lane
-        const bool won = listed & (v == mn) & (mn != OE_OS_NONE);
+        const bool won = listed & (v == mn);   // (nobody waiting at all: the listed rows "win" nothing — h stays none, pos is clamped below)
         match = lane == e ? mn : match;
         h = won ? n1 : h;
         ra += won ? 4u : 0u;
@@ -2045,7 +2045,7 @@ __global__ void __launch_bounds__(32, 1) k_commit_offers(OfferSideArgs a) {
       }
       n1 = won_prev ? nxt_prev : n1;
       mybits_next = tb;
-      pos += (int)((ra - ra0) >> 2);
+      pos = min(pos + (int)((ra - ra0) >> 2), end);
       steps += 32;
       if (match != OE_OS_NONE) dec_row[(size_t)match * DEC_INTS] = o_mine;
     }
