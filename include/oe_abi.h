@@ -86,6 +86,10 @@ typedef struct {
  * oe_evaluate_cycle / oe_feasibility / oe_class_feasibility evaluates the landed chunks while the later ones are still on
  * the bus (oe_evaluate_cycle also commits over them: first fit takes the lowest free index, so what a requirement gets among
  * the landed offers does not depend on the offers behind them).  Load the offers before the requirements to use it.
+ * With this flag the loads also do nothing per row on the host: ids are checked, and requirements that re-deploy a running
+ * pod found, on the device; what oe_apply_launches / oe_requirement_rows need of the tables on the host is fetched when they
+ * are called (from the caller's buffers while the promise above holds, from the device afterwards — the engine keeps no
+ * pointer into a caller's buffer once that evaluation call has returned).
  * Without this flag a load returns only when the caller may reuse its buffers.                                           */
 #define OE_CFG_ASYNC_LOADS 2u
 
