@@ -5000,7 +5000,7 @@ int32_t oe_unexpected_resources(oe_engine* h, const uint32_t* keep_bits, int32_t
 namespace {
 // Sharded engines: waits (on the device) until every shard's decision records of this pass have landed in this shard's region
 // and copies the decisions of winners that live on other shards into the decision table.
-int gather_decisions(oe_engine* h) {
+int gather_decisions(oe_engine* h, oe_decision* out = nullptr) {
   if (!h->cycle_done) return h->fail(OE_ERR_STATE, "no cycle evaluated since the last load");
   if (!(h->world > 1 && h->peers_attached && h->exch_max_reqs >= h->M && h->exch_rec_words > 0))
     return h->fail(OE_ERR_STATE, "the merged decision table needs attached peers and a decision area sized for the requirement table: load the requirements, then "
@@ -5012,6 +5012,7 @@ int gather_decisions(oe_engine* h) {
   CU(cudaGetLastError());
   int peer_err = 0;
   CU(cudaMemcpyAsync(&peer_err, h->d_peer_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  if (out) CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));   // same round trip
   CU(cudaStreamSynchronize(h->stream));
   if (peer_err) {
     CU(cudaMemsetAsync(h->d_peer_err.p, 0, sizeof(int), h->stream));
@@ -5026,8 +5027,9 @@ int gather_decisions(oe_engine* h) {
 int32_t oe_gather_decisions(oe_engine* h, oe_decision* out) {
   if (!h) return OE_ERR_INVALID;
   CU(cudaSetDevice(h->device));
-  if (int rc = gather_decisions(h)) return rc;
-  if (out && h->M > 0) {
+  const bool fresh = !(h->decisions_gathered || h->M == 0);
+  if (int rc = gather_decisions(h, out)) return rc;
+  if (!fresh && out && h->M > 0) {   // gathered before (oe_evaluate_cycle with a decision buffer, or an earlier call): just the copy
     CU(cudaMemcpyAsync(out, h->d_dec.p, (size_t)h->M * sizeof(oe_decision), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
   }
