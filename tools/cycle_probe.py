@@ -1,5 +1,5 @@
 """One engine, the C5 tables in pinned memory, a few end-to-end cycles with OE_CYCLE_TRACE=1: where a cycle's wall time goes.
-   python tools/cycle_probe.py [matrix|decisions] [chunks|auto] [offers-first|tasks-first]
+   python tools/cycle_probe.py [matrix|decisions] [chunks|auto] [offers-first|tasks-first|small-first]
    OE_PROBE_WORKLOAD=c5|hostname|mount|redeploy|one-region picks the tables, OE_PROBE_WIRE=plain the unpacked offer table."""
 import os
 import sys
@@ -31,14 +31,17 @@ def main():
         t0 = time.perf_counter()
         eng.tables = pt
         eng.load_programs(pt)
-        if order == "tasks-first":
+        if order in ("tasks-first", "small-first"):
             eng.load_tasks(pt)
+        if order == "small-first":          # every small table in front of the offers on the bus
+            eng.load_requirements(pt)
         t1 = time.perf_counter()
         eng.load_offers_packed(ppk) if ppk is not None else eng.load_offers(pt)
         t2 = time.perf_counter()
-        if order != "tasks-first":
+        if order == "offers-first":
             eng.load_tasks(pt)
-        eng.load_requirements(pt)
+        if order != "small-first":
+            eng.load_requirements(pt)
         t3 = time.perf_counter()
         st = eng.evaluate_cycle_into(out.data_ptr())
         t4 = time.perf_counter()
