@@ -912,7 +912,8 @@ __global__ void __launch_bounds__(128 * OE_ADJ_SPLIT) k_row_overlap(RowBits rb, 
     unsigned long long acc = 0ull;
     if (w)
       for (int q = 0; q < rb.rows; ++q) acc |= (unsigned long long)((w & tile[q][x]) != 0u) << q;
-    for (int d = 16; d > 0; d >>= 1) acc |= __shfl_xor_sync(0xffffffffu, acc, d);
+    const uint32_t lo = __reduce_or_sync(0xffffffffu, (uint32_t)acc), hi = __reduce_or_sync(0xffffffffu, (uint32_t)(acc >> 32));   // (REDUX: two instead of ten shuffles)
+    acc = ((unsigned long long)hi << 32) | lo;
     if ((threadIdx.x & 31) == 0 && acc) atomicOr(adj + r, acc);
   }
 }
