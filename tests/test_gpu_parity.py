@@ -168,6 +168,21 @@ def test_async_loads_find_redeployed_pods_on_the_device(seed):
     eng.close()
 
 
+@pytest.mark.parametrize("seed", range(6))
+def test_async_loads_with_more_match_records_than_the_buffer_holds(seed):
+    """Many requirements that name the SAME deployed pod, which has several tasks: k_match_tasks finds tasks x requirements records,
+    more than its buffer holds, and the evaluation call falls back to the host-side search over the caller's tables."""
+    t = random_tables(seed, n_offers=300, n_reqs=120, n_tasks=40, with_reserved=False)
+    t.normalise()
+    ty, ix = int(t.t_pod_type_id[0]) if t.t_pod_type_id[0] >= 0 else 0, 5
+    t.t_pod_type_id = t.t_pod_type_id.copy(); t.t_pod_index = t.t_pod_index.copy()
+    t.t_pod_type_id[:30] = ty; t.t_pod_index[:30] = ix                  # one pod of 30 tasks ...
+    t.r_pod_type_id = np.full_like(t.r_pod_type_id, ty); t.r_pod_index = np.full_like(t.r_pod_index, ix)   # ... named by all 120 requirements
+    eng = Engine(device=0, flags=abi.OE_CFG_ASYNC_LOADS)
+    _compare_all(eng, t)
+    eng.close()
+
+
 @pytest.mark.parametrize("redeploy_every", [0, 1, 7])
 def test_async_loads_keep_no_pointer_into_the_callers_tables(redeploy_every):
     """The caller's task and requirement columns must stay valid until the evaluation call after the loads returns, and no longer:
